@@ -1,0 +1,429 @@
+// Small-shape CUDA-core path for the reference CNN (§8 K7 "tiny-N path", K10).
+//
+// MLModel's layers are degenerate GEMMs (N = 6 / 16 / 10, K = 75 / 150 / 84): far below one tcgen05 tile, so
+// they run as fused fp32 CUDA-core kernels whose job is to minimise launches and memory round trips:
+//   conv + bias + ReLU + 2x2 max-pool            -> one kernel (pool arg-max kept as 2 bits for backward)
+//   its backward (pool scatter, ReLU mask, wgrad, bias grad, dgrad) -> two kernels
+//   linear + bias + activation                   -> one kernel;  dX, dW, db of a linear -> one kernel
+// The step is launch-latency bound (~0.13 GFLOP); the roofline that applies is launches x ~2 us, not FLOPs.
+// Larger layers go to the tcgen05 GEMM / implicit-GEMM path instead (gemm_tcgen05.cu).
+#include "common.cuh"
+#include "../include/mlt_b200.h"
+
+namespace mlt {
+
+// =====================================================================================================
+// conv2d (stride 1, no padding, NCHW fp32) + bias [+ ReLU] [+ 2x2/2 max-pool]
+// grid = (B, co_groups); each CTA stages one input sample and its group's filters in shared memory.
+// =====================================================================================================
+template <bool RELU, bool POOL>
+__global__ void __launch_bounds__(256)
+conv2d_direct_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                         float* __restrict__ y, unsigned char* __restrict__ idx, int Cin, int H, int W, int Cout,
+                         int KH, int KW, int co_per_cta) {
+  extern __shared__ float smem[];
+  const int b = blockIdx.x;
+  const int co0 = blockIdx.y * co_per_cta;
+  const int nco = min(co_per_cta, Cout - co0);
+  const int OH = H - KH + 1, OW = W - KW + 1;
+  const int PH = POOL ? OH / 2 : OH, PW = POOL ? OW / 2 : OW;
+  const int wsz = Cin * KH * KW;
+  float* xs = smem;                    // [Cin][H][W]
+  float* ws = smem + Cin * H * W;      // [nco][Cin][KH][KW]
+  const float* xb = x + (size_t)b * Cin * H * W;
+  for (int i = threadIdx.x; i < Cin * H * W; i += blockDim.x) xs[i] = xb[i];
+  for (int i = threadIdx.x; i < nco * wsz; i += blockDim.x) ws[i] = w[(size_t)co0 * wsz + i];
+  __syncthreads();
+  const int per = PH * PW;
+  for (int o = threadIdx.x; o < nco * per; o += blockDim.x) {
+    const int cl = o / per, r = o - cl * per;
+    const int ph = r / PW, pw = r - ph * PW;
+    const float* wc = ws + cl * wsz;
+    const float bv = bias ? bias[co0 + cl] : 0.f;
+    if (POOL) {
+      float a00 = bv, a01 = bv, a10 = bv, a11 = bv;
+      const int h0 = 2 * ph, w0 = 2 * pw;
+      for (int ci = 0; ci < Cin; ++ci) {
+        const float* xc = xs + ci * H * W + h0 * W + w0;
+        const float* wk = wc + ci * KH * KW;
+        for (int kh = 0; kh < KH; ++kh) {
+          const float* r0 = xc + kh * W;
+          const float* r1 = r0 + W;
+          float p0 = r0[0], p1 = r1[0];
+          for (int kw = 0; kw < KW; ++kw) {
+            const float wv = wk[kh * KW + kw];
+            const float q0 = r0[kw + 1], q1 = r1[kw + 1];
+            a00 = fmaf(wv, p0, a00); a01 = fmaf(wv, q0, a01);
+            a10 = fmaf(wv, p1, a10); a11 = fmaf(wv, q1, a11);
+            p0 = q0; p1 = q1;
+          }
+        }
+      }
+      float m = a00; int am = 0;                       // first maximum wins, like ATen max_pool2d
+      if (a01 > m) { m = a01; am = 1; }
+      if (a10 > m) { m = a10; am = 2; }
+      if (a11 > m) { m = a11; am = 3; }
+      if (RELU) m = fmaxf(m, 0.f);
+      const size_t oi = ((size_t)b * Cout + co0 + cl) * per + r;
+      y[oi] = m;
+      idx[oi] = (unsigned char)am;
+    } else {
+      float a = bv;
+      for (int ci = 0; ci < Cin; ++ci) {
+        const float* xc = xs + ci * H * W + ph * W + pw;
+        const float* wk = wc + ci * KH * KW;
+        for (int kh = 0; kh < KH; ++kh)
+          for (int kw = 0; kw < KW; ++kw) a = fmaf(wk[kh * KW + kw], xc[kh * W + kw], a);
+      }
+      if (RELU) a = fmaxf(a, 0.f);
+      y[((size_t)b * Cout + co0 + cl) * per + r] = a;
+    }
+  }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// wgrad + bias grad.  grid = (Cout, nchunk): CTA (co, c) walks batch chunk c.  For each sample the upstream
+// gradient of channel co is turned into a sparse list (value, input offset) - with pooling only one of the
+// four pre-pool positions is live - and each thread owns one filter tap (ci,kh,kw); slot nW is the bias.
+// Chunks are combined through scratch: partial[chunk][co][nW+1] + one ticket per co; the last CTA of a
+// channel sums the partials in a fixed order (deterministic) and re-zeroes the ticket.
+// -----------------------------------------------------------------------------------------------------
+template <bool RELU, bool POOL>
+__global__ void __launch_bounds__(256)
+conv2d_direct_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy, const float* __restrict__ y,
+                           const unsigned char* __restrict__ idx, float* __restrict__ dw, float* __restrict__ db,
+                           float* __restrict__ partial, unsigned int* __restrict__ tickets, int B, int Cin, int H,
+                           int W, int Cout, int KH, int KW, int chunk, int accumulate) {
+  extern __shared__ float smem[];
+  const int co = blockIdx.x, c = blockIdx.y, nchunk = gridDim.y;
+  const int OH = H - KH + 1, OW = W - KW + 1;
+  const int PH = POOL ? OH / 2 : OH, PW = POOL ? OW / 2 : OW;
+  const int per = PH * PW, nW = Cin * KH * KW;
+  float* xs = smem;                               // [Cin*H*W]
+  float* gs = xs + Cin * H * W;                   // [per] masked upstream gradient
+  int* offs = reinterpret_cast<int*>(gs + per);   // [per] offset of the live pre-pool position in the input plane
+  __shared__ bool is_last;
+
+  // taps owned by this thread: t, t+256, ... (at most 4 -> up to 1024 taps + bias per output channel)
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  int tap_off[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int t = threadIdx.x + j * 256;
+    if (t < nW) {
+      const int ci = t / (KH * KW), r = t - ci * KH * KW;
+      tap_off[j] = ci * H * W + (r / KW) * W + (r % KW);
+    } else {
+      tap_off[j] = -1;                            // bias slot (t == nW) or idle
+    }
+  }
+  const int b_lo = c * chunk, b_hi = min(B, b_lo + chunk);
+  for (int b = b_lo; b < b_hi; ++b) {
+    __syncthreads();
+    const float* xb = x + (size_t)b * Cin * H * W;
+    for (int i = threadIdx.x; i < Cin * H * W; i += blockDim.x) xs[i] = xb[i];
+    const size_t base = ((size_t)b * Cout + co) * per;
+    for (int i = threadIdx.x; i < per; i += blockDim.x) {
+      float g = dy[base + i];
+      if (RELU && !(y[base + i] > 0.f)) g = 0.f;
+      const int ph = i / PW, pw = i - ph * PW;
+      int off;
+      if (POOL) {
+        const int am = idx[base + i];
+        off = (2 * ph + (am >> 1)) * W + 2 * pw + (am & 1);
+      } else {
+        off = ph * W + pw;
+      }
+      gs[i] = g;
+      offs[i] = off;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int t = threadIdx.x + j * 256;
+      if (t < nW) {
+        const float* xt = xs + tap_off[j];
+        float a = acc[j];
+        for (int i = 0; i < per; ++i) a = fmaf(gs[i], xt[offs[i]], a);
+        acc[j] = a;
+      } else if (t == nW) {
+        float a = acc[j];
+        for (int i = 0; i < per; ++i) a += gs[i];
+        acc[j] = a;
+      }
+    }
+  }
+  // publish
+  const int slots = nW + 1;
+  if (nchunk == 1) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int t = threadIdx.x + j * 256;
+      if (t < nW) dw[(size_t)co * nW + t] = (accumulate ? dw[(size_t)co * nW + t] : 0.f) + acc[j];
+      else if (t == nW && db) db[co] = (accumulate ? db[co] : 0.f) + acc[j];
+    }
+    return;
+  }
+  float* mine = partial + ((size_t)c * Cout + co) * slots;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const int t = threadIdx.x + j * 256;
+    if (t < slots) mine[t] = acc[j];
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(&tickets[co], 1u);
+    is_last = (tk == (unsigned int)nchunk - 1);
+    if (is_last) tickets[co] = 0u;                 // ready for the next launch
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  for (int t = threadIdx.x; t < slots; t += blockDim.x) {
+    float s = 0.f;
+    for (int k = 0; k < nchunk; ++k) s += __ldcg(partial + ((size_t)k * Cout + co) * slots + t);
+    if (t < nW) dw[(size_t)co * nW + t] = (accumulate ? dw[(size_t)co * nW + t] : 0.f) + s;
+    else if (db) db[co] = (accumulate ? db[co] : 0.f) + s;
+  }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// dgrad: dx[b,ci,h,w] = sum_{co,kh,kw} dz[b,co,h-kh,w-kw] * w[co,ci,kh,kw].  grid = B; the dense pre-pool
+// gradient plane of the sample is rebuilt in shared memory from (dy, y, idx), filters sit beside it.
+// -----------------------------------------------------------------------------------------------------
+template <bool RELU, bool POOL>
+__global__ void __launch_bounds__(256)
+conv2d_direct_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ y, const unsigned char* __restrict__ idx,
+                           const float* __restrict__ w, float* __restrict__ dx, int Cin, int H, int W, int Cout, int KH,
+                           int KW) {
+  extern __shared__ float smem[];
+  const int b = blockIdx.x;
+  const int OH = H - KH + 1, OW = W - KW + 1;
+  const int PH = POOL ? OH / 2 : OH, PW = POOL ? OW / 2 : OW;
+  const int per = PH * PW, plane = OH * OW, wsz = Cin * KH * KW;
+  float* dz = smem;                       // [Cout][OH][OW]
+  float* ws = smem + Cout * plane;        // [Cout][Cin][KH][KW]
+  for (int i = threadIdx.x; i < Cout * plane; i += blockDim.x) dz[i] = 0.f;
+  for (int i = threadIdx.x; i < Cout * wsz; i += blockDim.x) ws[i] = w[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < Cout * per; i += blockDim.x) {
+    const int co = i / per, r = i - co * per;
+    const size_t gi = ((size_t)b * Cout + co) * per + r;
+    float g = dy[gi];
+    if (RELU && !(y[gi] > 0.f)) g = 0.f;
+    int pos;
+    if (POOL) {
+      const int ph = r / PW, pw = r - ph * PW, am = idx[gi];
+      pos = (2 * ph + (am >> 1)) * OW + 2 * pw + (am & 1);
+    } else {
+      pos = r;
+    }
+    dz[co * plane + pos] = g;
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < Cin * H * W; o += blockDim.x) {
+    const int ci = o / (H * W), r = o - ci * H * W;
+    const int h = r / W, wq = r - h * W;
+    const int kh_lo = max(0, h - OH + 1), kh_hi = min(KH - 1, h);
+    const int kw_lo = max(0, wq - OW + 1), kw_hi = min(KW - 1, wq);
+    float a = 0.f;
+    for (int co = 0; co < Cout; ++co) {
+      const float* dzc = dz + co * plane;
+      const float* wk = ws + co * wsz + ci * KH * KW;
+      for (int kh = kh_lo; kh <= kh_hi; ++kh)
+        for (int kw = kw_lo; kw <= kw_hi; ++kw) a = fmaf(dzc[(h - kh) * OW + (wq - kw)], wk[kh * KW + kw], a);
+    }
+    dx[(size_t)b * Cin * H * W + o] = a;
+  }
+}
+
+// =====================================================================================================
+// small linear: y = act(x W^T + b), fp32.  One warp produces 4 batch rows of one output feature.
+// =====================================================================================================
+constexpr int kLinRows = 4;
+
+__global__ void __launch_bounds__(256)
+linear_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                        float* __restrict__ y, int B, int K, int N, int act) {
+  const int lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int row_tiles = ceil_div(B, kLinRows);
+  if (gw >= N * row_tiles) return;
+  const int n = gw % N, b0 = (gw / N) * kLinRows;
+  const float* wr = w + (size_t)n * K;
+  float acc[kLinRows] = {0.f, 0.f, 0.f, 0.f};
+  for (int k = lane; k < K; k += 32) {
+    const float wv = wr[k];
+#pragma unroll
+    for (int r = 0; r < kLinRows; ++r)
+      if (b0 + r < B) acc[r] = fmaf(wv, x[(size_t)(b0 + r) * K + k], acc[r]);
+  }
+#pragma unroll
+  for (int r = 0; r < kLinRows; ++r) acc[r] = warp_sum(acc[r]);
+  if (lane < kLinRows && b0 + lane < B) {
+    float v = acc[0];
+#pragma unroll
+    for (int r = 1; r < kLinRows; ++r) if (lane == r) v = acc[r];
+    v += bias ? bias[n] : 0.f;
+    y[(size_t)(b0 + lane) * N + n] = act_fwd_rt(act, v);
+  }
+}
+
+__device__ __forceinline__ float act_grad_from_y(int act, float yv) {
+  switch (act) {
+    case ACT_RELU: return yv > 0.f ? 1.f : 0.f;
+    case ACT_TANH: return 1.f - yv * yv;
+    default: return 1.f;
+  }
+}
+
+// blocks [0, nbx): dx[b,k] = sum_n dz[b,n] w[n,k]      (skipped when dx == nullptr)
+// blocks [nbx, ..): dw[n,k] = sum_b dz[b,n] x[b,k];  db[n] = sum_b dz[b,n]
+__global__ void __launch_bounds__(256)
+linear_small_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, const float* __restrict__ x,
+                        const float* __restrict__ w, float* __restrict__ dx, float* __restrict__ dw,
+                        float* __restrict__ db, int B, int K, int N, int act, int nbx, int accumulate) {
+  if ((int)blockIdx.x < nbx) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * K) return;
+    const int b = i / K, k = i - b * K;
+    float a = 0.f;
+    for (int n = 0; n < N; ++n) {
+      const float dz = dy[(size_t)b * N + n] * act_grad_from_y(act, y[(size_t)b * N + n]);
+      a = fmaf(dz, w[(size_t)n * K + k], a);
+    }
+    dx[i] = a;
+  } else {
+    const int i = (blockIdx.x - nbx) * blockDim.x + threadIdx.x;
+    if (i >= N * K) return;
+    const int n = i / K, k = i - n * K;
+    float a = 0.f, s = 0.f;
+    for (int b = 0; b < B; ++b) {
+      const float dz = dy[(size_t)b * N + n] * act_grad_from_y(act, y[(size_t)b * N + n]);
+      a = fmaf(dz, x[(size_t)b * K + k], a);
+      s += dz;
+    }
+    dw[i] = (accumulate ? dw[i] : 0.f) + a;
+    if (k == 0 && db) db[n] = (accumulate ? db[n] : 0.f) + s;
+  }
+}
+
+template <typename K>
+static int set_smem(K kernel, size_t bytes) {
+  if (bytes > 227 * 1024) {
+    set_error("direct conv path needs %zu B of shared memory (> 227 KB); use the implicit-GEMM path", bytes);
+    return 1;
+  }
+  if (bytes > 48 * 1024) MLT_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+}  // namespace mlt
+
+using namespace mlt;
+
+#define DISPATCH_RP(relu, pool, ...)                                              \
+  if (relu && pool) { constexpr bool R_ = true, P_ = true; __VA_ARGS__; }         \
+  else if (relu) { constexpr bool R_ = true, P_ = false; __VA_ARGS__; }           \
+  else if (pool) { constexpr bool R_ = false, P_ = true; __VA_ARGS__; }           \
+  else { constexpr bool R_ = false, P_ = false; __VA_ARGS__; }
+
+extern "C" int mlt_conv2d_direct_fwd(const void* x, const void* w, const void* bias, void* y, void* pool_idx, int B, int Cin,
+                                     int H, int W, int Cout, int KH, int KW, int relu, int pool, void* stream) {
+  MLT_REQUIRE(H >= KH && W >= KW, "mlt_conv2d_direct_fwd: kernel larger than input");
+  MLT_REQUIRE(!pool || pool_idx != nullptr, "mlt_conv2d_direct_fwd: pool needs an index buffer");
+  const int wsz = Cin * KH * KW;
+  int co_per = Cout;                                   // split output channels until the grid fills the chip
+  while (co_per > 1 && B * ceil_div(Cout, co_per) < kNumSMs) co_per = ceil_div(co_per, 2);
+  const size_t smem = ((size_t)Cin * H * W + (size_t)co_per * wsz) * sizeof(float);
+  dim3 grid(B, ceil_div(Cout, co_per));
+  DISPATCH_RP(relu, pool, {
+    auto k = conv2d_direct_fwd_kernel<R_, P_>;
+    if (set_smem(k, smem)) return 1;
+    k<<<grid, 256, smem, (cudaStream_t)stream>>>((const float*)x, (const float*)w, (const float*)bias, (float*)y,
+                                                (unsigned char*)pool_idx, Cin, H, W, Cout, KH, KW, co_per);
+  });
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+// scratch layout: [tickets: round_up(Cout*4, 256) bytes][partials: nchunk * Cout * (taps+1) floats]
+static void conv_bwd_chunks(int B, int Cout, int* nchunk, int* chunk) {
+  int n = (2 * kNumSMs) / (Cout > 0 ? Cout : 1);     // aim for ~2 CTAs per SM
+  if (n > B) n = B;
+  if (n < 1) n = 1;
+  *chunk = ceil_div(B, n);
+  *nchunk = ceil_div(B, *chunk);
+}
+static long long conv_bwd_ticket_bytes(int Cout) { return ((long long)Cout * 4 + 255) / 256 * 256; }
+
+extern "C" long long mlt_conv2d_direct_bwd_scratch_bytes(int B, int Cin, int Cout, int KH, int KW) {
+  int nchunk, chunk;
+  conv_bwd_chunks(B, Cout, &nchunk, &chunk);
+  const long long slots = (long long)Cin * KH * KW + 1;
+  return conv_bwd_ticket_bytes(Cout) + (long long)nchunk * Cout * slots * 4;
+}
+
+extern "C" int mlt_conv2d_direct_bwd(const void* x, const void* w, const void* dy, const void* y, const void* pool_idx,
+                                     void* dx, void* dw, void* db, void* scratch, long long scratch_bytes, int B, int Cin,
+                                     int H, int W, int Cout, int KH, int KW, int relu, int pool, int accumulate,
+                                     void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  const int nW = Cin * KH * KW;
+  MLT_REQUIRE(nW + 1 <= 1024, "mlt_conv2d_direct_bwd: %d filter taps per channel exceeds the direct path (1023)", nW);
+  const int OH = H - KH + 1, OW = W - KW + 1;
+  const int per = pool ? (OH / 2) * (OW / 2) : OH * OW;
+  int nchunk, chunk;
+  conv_bwd_chunks(B, Cout, &nchunk, &chunk);
+  const long long need = mlt_conv2d_direct_bwd_scratch_bytes(B, Cin, Cout, KH, KW);
+  MLT_REQUIRE(nchunk == 1 || (scratch != nullptr && scratch_bytes >= need),
+              "mlt_conv2d_direct_bwd: scratch too small (%lld < %lld bytes)", scratch_bytes, need);
+  unsigned int* tickets = (unsigned int*)scratch;
+  float* partial = scratch ? (float*)((char*)scratch + conv_bwd_ticket_bytes(Cout)) : nullptr;
+  {
+    const size_t smem = ((size_t)Cin * H * W + 2 * (size_t)per) * sizeof(float);
+    dim3 grid(Cout, nchunk);
+    DISPATCH_RP(relu, pool, {
+      auto k = conv2d_direct_wgrad_kernel<R_, P_>;
+      if (set_smem(k, smem)) return 1;
+      k<<<grid, 256, smem, st>>>((const float*)x, (const float*)dy, (const float*)y, (const unsigned char*)pool_idx,
+                                 (float*)dw, (float*)db, partial, tickets, B, Cin, H, W, Cout, KH, KW, chunk, accumulate);
+    });
+    MLT_LAUNCH_CHECK();
+  }
+  if (dx != nullptr) {
+    const size_t smem = ((size_t)Cout * OH * OW + (size_t)Cout * nW) * sizeof(float);
+    DISPATCH_RP(relu, pool, {
+      auto k = conv2d_direct_dgrad_kernel<R_, P_>;
+      if (set_smem(k, smem)) return 1;
+      k<<<B, 256, smem, st>>>((const float*)dy, (const float*)y, (const unsigned char*)pool_idx, (const float*)w,
+                              (float*)dx, Cin, H, W, Cout, KH, KW);
+    });
+    MLT_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+extern "C" int mlt_linear_small_fwd(const void* x, const void* w, const void* bias, void* y, int B, int K, int N, int act,
+                                    void* stream) {
+  MLT_REQUIRE(act == ACT_NONE || act == ACT_RELU || act == ACT_TANH, "mlt_linear_small_fwd: unsupported activation %d", act);
+  const long long warps = (long long)N * ceil_div(B, kLinRows);
+  const int grid = (int)ceil_div64(warps * 32, 256);
+  linear_small_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, (const float*)w, (const float*)bias,
+                                                                  (float*)y, B, K, N, act);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int mlt_linear_small_bwd(const void* dy, const void* y, const void* x, const void* w, void* dx, void* dw, void* db,
+                                    int B, int K, int N, int act, int accumulate, void* stream) {
+  MLT_REQUIRE(act == ACT_NONE || act == ACT_RELU || act == ACT_TANH, "mlt_linear_small_bwd: unsupported activation %d", act);
+  const int nbx = dx ? ceil_div(B * K, 256) : 0;
+  const int nbw = ceil_div(N * K, 256);
+  linear_small_bwd_kernel<<<nbx + nbw, 256, 0, (cudaStream_t)stream>>>(
+      (const float*)dy, (const float*)y, (const float*)x, (const float*)w, (float*)dx, (float*)dw, (float*)db, B, K, N, act,
+      nbx, accumulate);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}

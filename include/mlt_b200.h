@@ -1,0 +1,72 @@
+/* libmlt_b200: hand-written sm_100a kernels + native runtime of the ml-trainer B200 framework.
+ *
+ * Plain C ABI.  Conventions:
+ *   - every function returns 0 on success; on failure a non-zero code, with a message available from
+ *     mlt_last_error() (thread-local);
+ *   - pointers are device pointers unless the name says otherwise; `stream` is a cudaStream_t;
+ *   - nothing here allocates device memory unless its comment says so: callers pass outputs and scratch.
+ * The comments cite the reference call site (file:line under /root/reference) each entry point replaces.
+ */
+#ifndef MLT_B200_H_
+#define MLT_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MLT_B200_VERSION 100
+
+/* activation ids for fused epilogues */
+#define MLT_ACT_NONE 0
+#define MLT_ACT_RELU 1
+#define MLT_ACT_GELU 2
+#define MLT_ACT_TANH 3
+
+/* optimizer rule ids: reference optimizer table, src/trainer.py:123-138 */
+#define MLT_RULE_SGD 0
+#define MLT_RULE_ADAM 1
+#define MLT_RULE_ADAMW 2
+#define MLT_RULE_ADAGRAD 3
+#define MLT_RULE_ADAMAX 4
+
+/* ---- library ------------------------------------------------------------------------------------ */
+const char* mlt_last_error(void);
+int mlt_version(void);
+int mlt_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, long long* total_mem);
+
+/* Host-side gradient bucket planner (replaces DDP's bucket assignment behind src/trainer.py:98).
+ * out_bounds gets nb+1 entries; returns nb. */
+int mlt_plan_buckets(const long long* sizes_bytes, int n, long long cap_bytes, long long first_cap_bytes,
+                     int* out_bounds);
+
+/* ---- optimizer: src/trainer.py:188 optimizer.step() --------------------------------------------- */
+/* One fused launch over n elements (n % 4 == 0): grad scale + cast + rule + master write + bf16 shadow write.
+ * hyper_dev points at 8 device floats {lr, wd, b1|momentum, b2, eps, bias_corr1, sqrt(bias_corr2), grad_scale}. */
+int mlt_fused_update(int rule, void* master_f32, const void* grad, int grad_is_bf16, void* shadow_bf16, void* s1,
+                     void* s2, const void* hyper_dev, long long n, void* stream);
+
+/* ---- loss / metric: src/trainer.py:185-186 (criterion, loss.item()) and :165-166 (accuracy) ------ */
+/* Mean softmax cross-entropy + dlogits (=(softmax-onehot)/B) + optional accuracy, and accumulation into
+ * acc3 = {loss_sum, metric_sum, steps}.  workspace16: 16 zero-initialised bytes, self-resetting. */
+int mlt_softmax_xent(const void* logits, int is_bf16, const void* targets_i64, void* dlogits, void* loss_out,
+                     void* acc3, void* workspace16, int B, int C, int want_acc, void* stream);
+int mlt_argmax_accuracy(const void* logits, int is_bf16, const void* targets_i64, void* out_scalar, int B, int C,
+                        void* stream);
+
+/* ---- small-shape CNN path: src/model.py:18-23 (conv/relu/pool/fc of MLModel) and their backward ---- */
+int mlt_conv2d_direct_fwd(const void* x, const void* w, const void* bias, void* y, void* pool_idx, int B, int Cin,
+                          int H, int W, int Cout, int KH, int KW, int relu, int pool, void* stream);
+long long mlt_conv2d_direct_bwd_scratch_bytes(int B, int Cin, int Cout, int KH, int KW);
+/* scratch: mlt_conv2d_direct_bwd_scratch_bytes() bytes, zero-initialised once (tickets self-reset). */
+int mlt_conv2d_direct_bwd(const void* x, const void* w, const void* dy, const void* y, const void* pool_idx, void* dx,
+                          void* dw, void* db, void* scratch, long long scratch_bytes, int B, int Cin, int H, int W,
+                          int Cout, int KH, int KW, int relu, int pool, int accumulate, void* stream);
+int mlt_linear_small_fwd(const void* x, const void* w, const void* bias, void* y, int B, int K, int N, int act,
+                         void* stream);
+int mlt_linear_small_bwd(const void* dy, const void* y, const void* x, const void* w, void* dx, void* dw, void* db,
+                         int B, int K, int N, int act, int accumulate, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MLT_B200_H_ */

@@ -1,0 +1,135 @@
+"""One training / evaluation step, eager or replayed from a CUDA graph.
+
+Hot loop of the reference (src/trainer.py:180-197): ``zero_grad`` -> H2D -> forward ->
+loss -> ``loss.item()`` -> backward -> ``optimizer.step()`` -> metric on the host.
+Here a step is: forward -> fused loss -> backward, during which the reducer launches the
+fused all-reduce + update per bucket on a side stream -> join.  Loss and metric are
+added into a 3-float device accumulator ``[loss_sum, metric_sum, steps]``; nothing
+touches the host.
+
+Graph mode: after ``WARMUP`` eager steps the whole sequence is captured once per
+distinct (input buffer, target buffer) pair: the prefetcher cycles through a fixed set
+of device slots, so there are as many graphs as slots.  Per-step host work then shrinks
+to uploading eight floats of hyper-parameters and one ``cudaGraphLaunch``.  Learning
+rate and bias corrections live in device memory so a replay sees new values.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional, Tuple
+
+import torch
+
+WARMUP = 3
+
+
+class StepEngine:
+    def __init__(self, model, criterion, criterion_type, metric, reducer, device,
+                 graph="auto", compute_dtype=torch.float32):
+        self.model = model
+        self.criterion = criterion
+        self.criterion_type = criterion_type
+        self.metric = metric
+        self.reducer = reducer
+        self.device = device
+        self.compute_dtype = compute_dtype
+        self.acc = torch.zeros(3, dtype=torch.float32, device=device)
+        self._one = torch.ones((), dtype=torch.float32, device=device)
+        want = graph if isinstance(graph, bool) else (str(graph).lower() in ("1", "true", "auto", "yes"))
+        self.use_graph = bool(want) and device.type == "cuda"
+        self._graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
+        self._eager_steps = 0
+        self._pool = None
+        self.graph_replays = 0
+        self.last_loss: Optional[torch.Tensor] = None
+
+    # ------------------------------------------------------------ accumulators
+    def reset_accumulators(self):
+        self.acc.zero_()
+
+    def accumulators(self) -> torch.Tensor:
+        return self.acc.clone()
+
+    def read_accumulators(self):
+        return self.acc.tolist()
+
+    def invalidate(self):
+        """Drop captured graphs (after a checkpoint load or any out-of-band state change)."""
+        self._graphs.clear()
+        self._eager_steps = 0
+
+    # -------------------------------------------------------------------- loss
+    def _forward_loss(self, model, inputs, targets, train: bool):
+        """Forward + loss + device-side accumulation.  Returns ``(outputs, loss, dlogits_or_None)``.
+
+        With the native cross-entropy criterion the loss, its gradient w.r.t. the logits, the accuracy
+        and the accumulator update come out of ONE kernel and no autograd node is built for the loss.
+        """
+        from .utils import metrics as M
+
+        outputs = model(inputs)
+        fused = (getattr(self.criterion, "native_fused", False) and outputs.dim() == 2
+                 and targets.dtype == torch.int64)
+        if fused:
+            want_acc = self.metric == "accuracy"
+            loss, dl = self.criterion.fused_step(outputs.detach(), targets, self.acc, want_acc, need_grad=train)
+            if self.metric and not want_acc:
+                with torch.no_grad():
+                    self.acc[1] += M.evaluate(self.metric, outputs.detach(), targets).float()
+            return outputs, loss, dl
+        if self.criterion_type in ("l1", "l2", "custom") and targets.is_floating_point() \
+                and targets.dtype != outputs.dtype:
+            targets = targets.to(outputs.dtype)
+        loss = self.criterion(outputs, targets)
+        with torch.no_grad():
+            if self.metric:
+                self.acc[1] += M.evaluate(self.metric, outputs.detach(), targets).float()
+            self.acc[0] += loss.detach().float()
+            self.acc[2] += self._one
+        return outputs, loss, None
+
+    # ------------------------------------------------------------------- train
+    def _train_body(self, inputs, targets):
+        self.reducer.arm()
+        outputs, loss, dl = self._forward_loss(self.model, inputs, targets, train=True)
+        if dl is not None:
+            outputs.backward(dl)
+        else:
+            loss.backward()
+        self.reducer.finish_step()
+        self.last_loss = loss.detach()
+
+    def train_step(self, inputs, targets):
+        opt = self.reducer.opt
+        if not self.use_graph:
+            opt.begin_step()
+            self._train_body(inputs, targets)
+            return
+        key = (inputs.data_ptr(), targets.data_ptr(), tuple(inputs.shape), tuple(targets.shape))
+        g = self._graphs.get(key)
+        if g is not None:
+            opt.begin_step()
+            g.replay()
+            self.graph_replays += 1
+            return
+        if self._eager_steps < WARMUP:
+            self._eager_steps += 1
+            opt.begin_step()
+            self._train_body(inputs, targets)
+            return
+        # capture: hyper-parameters are uploaded outside the graph, everything else inside
+        opt.begin_step()
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, pool=self._pool):
+            self._train_body(inputs, targets)
+        if self._pool is None:
+            self._pool = g.pool()
+        self._graphs[key] = g
+        g.replay()          # capture does not execute; run the step that was just recorded
+        self.graph_replays += 1
+
+    # -------------------------------------------------------------------- eval
+    @torch.no_grad()
+    def eval_step(self, model, inputs, targets):
+        outputs, _, _ = self._forward_loss(model, inputs, targets, train=False)
+        return outputs

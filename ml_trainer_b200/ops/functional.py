@@ -1,0 +1,302 @@
+"""Functional op layer: autograd wrappers over the sm_100a kernel library.
+
+Every op has two statements of the same math: the native kernel (used whenever the tensors
+are on a CUDA device - the library is then mandatory, see ``_lib.native_available``) and a
+plain PyTorch one (CPU execution and the oracle the GPU tests compare against).
+
+Weight gradients: when a parameter carries ``_mlt_grad_sink`` (set by the FusedOptimizer) the
+backward kernel writes the gradient straight into the flat gradient arena and signals the
+reducer through ``_mlt_ready()``; autograd then sees ``None`` for that input, so there is no
+AccumulateGrad kernel and no flatten copy (SURVEY §7.3 "grads produced directly into bucket views").
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+import torch.nn.functional as TF
+
+from . import _lib
+from ._lib import check, launches, native_available, ptr, stream_handle  # noqa: F401 (re-exported)
+
+ACT_IDS = {None: 0, "none": 0, "relu": 1, "gelu": 2, "tanh": 3}
+_c_int, _c_ll = ctypes.c_int, ctypes.c_longlong
+
+
+def use_native(*tensors) -> bool:
+    return bool(tensors) and all(t is None or t.is_cuda for t in tensors) and native_available()
+
+
+# ----------------------------------------------------------------------------------------------
+# per-device scratch (zero-initialised once; kernels re-zero their tickets themselves)
+# ----------------------------------------------------------------------------------------------
+_scratch: dict = {}
+
+
+def scratch(device: torch.device, key: str, nbytes: int) -> torch.Tensor:
+    k = (device.index, key)
+    t = _scratch.get(k)
+    if t is None or t.numel() < nbytes:
+        t = torch.zeros(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+        _scratch[k] = t
+    return t
+
+
+# ----------------------------------------------------------------------------------------------
+# optimizer
+# ----------------------------------------------------------------------------------------------
+_hyper_ring: dict = {}
+_RING = 4096
+
+
+def upload_hyper(dev_hyper: torch.Tensor, values) -> None:
+    """Async H2D of the 8-float hyper vector through a ring of pinned slots (safe to run ahead of the GPU)."""
+    key = dev_hyper.data_ptr()
+    ent = _hyper_ring.get(key)
+    if ent is None:
+        ent = [torch.zeros(_RING, len(values), dtype=torch.float32).pin_memory(), 0]
+        _hyper_ring[key] = ent
+    ring, i = ent
+    slot = ring[i % _RING]
+    slot.copy_(torch.tensor(values, dtype=torch.float32))
+    ent[1] = i + 1
+    dev_hyper.copy_(slot, non_blocking=True)
+
+
+def fused_update(opt, lo: int, hi: int) -> None:
+    """Apply ``opt.kind`` to arena slice [lo, hi) in one launch (see csrc/optim.cu)."""
+    from ..optim.rules import RULE_IDS
+
+    n = hi - lo
+    if n <= 0:
+        return
+    L = _lib.lib()
+    shadow = None if opt.model is opt.master else opt.model[lo:hi]
+    s2 = opt.s2[lo:hi] if opt.s2.numel() > 1 else None
+    check(L.mlt_fused_update(_c_int(RULE_IDS[opt.kind]), ptr(opt.master[lo:hi]), ptr(opt.grad[lo:hi]),
+                             _c_int(int(opt.grad.dtype == torch.bfloat16)), ptr(shadow), ptr(opt.s1[lo:hi]), ptr(s2),
+                             ptr(opt.hyper), _c_ll(n), stream_handle()), "mlt_fused_update")
+    launches.bump("fused_update")
+
+
+# ----------------------------------------------------------------------------------------------
+# loss / metric
+# ----------------------------------------------------------------------------------------------
+def softmax_xent(logits: torch.Tensor, targets: torch.Tensor, acc3: Optional[torch.Tensor] = None,
+                 want_acc: bool = False, need_grad: bool = True):
+    """Mean CE loss and d(loss)/d(logits) in one pass.  Returns ``(loss, dlogits)``.
+
+    ``acc3`` (``[loss_sum, metric_sum, steps]``) is updated on the device when given.
+    """
+    B, C = logits.shape
+    if use_native(logits, targets):
+        logits = logits.contiguous()
+        loss = torch.empty((), dtype=torch.float32, device=logits.device)
+        dl = torch.empty_like(logits) if need_grad else None
+        ws = scratch(logits.device, "xent", 16)
+        check(_lib.lib().mlt_softmax_xent(ptr(logits), _c_int(int(logits.dtype == torch.bfloat16)), ptr(targets),
+                                          ptr(dl), ptr(loss), ptr(acc3), ptr(ws), _c_int(B), _c_int(C),
+                                          _c_int(int(want_acc)), stream_handle()), "mlt_softmax_xent")
+        launches.bump("softmax_xent")
+        return loss, dl
+    lf = logits.float()
+    logp = torch.log_softmax(lf, dim=-1)
+    loss = TF.nll_loss(logp, targets)
+    dl = None
+    if need_grad:
+        dl = torch.exp(logp)
+        dl[torch.arange(B, device=logits.device), targets] -= 1.0
+        dl = (dl / B).to(logits.dtype)
+    if acc3 is not None:
+        acc3[0] += loss.detach()
+        if want_acc:
+            acc3[1] += (lf.argmax(-1) == targets).float().mean()
+        acc3[2] += 1.0
+    return loss, dl
+
+
+class _CrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, targets):
+        loss, dl = softmax_xent(logits, targets, need_grad=True)
+        ctx.save_for_backward(dl)
+        return loss.to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return dl * g.to(dl.dtype), None
+
+
+def cross_entropy(logits, targets):
+    if logits.dim() != 2 or targets.dtype != torch.int64:
+        return TF.cross_entropy(logits, targets)
+    return _CrossEntropyFn.apply(logits, targets)
+
+
+def argmax_accuracy(logits: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
+    if use_native(logits, targets) and logits.dim() == 2:
+        out = torch.empty((), dtype=torch.float32, device=logits.device)
+        logits = logits.contiguous()
+        check(_lib.lib().mlt_argmax_accuracy(ptr(logits), _c_int(int(logits.dtype == torch.bfloat16)), ptr(targets),
+                                             ptr(out), _c_int(logits.shape[0]), _c_int(logits.shape[1]),
+                                             stream_handle()), "mlt_argmax_accuracy")
+        launches.bump("argmax_accuracy")
+        return out
+    return (logits.argmax(-1) == targets).float().mean()
+
+
+# ----------------------------------------------------------------------------------------------
+# gradient sinks
+# ----------------------------------------------------------------------------------------------
+def _sink(param) -> Optional[torch.Tensor]:
+    return getattr(param, "_mlt_grad_sink", None) if param is not None else None
+
+
+def _deliver(param, grad_written: Optional[torch.Tensor], sink: Optional[torch.Tensor]):
+    """What autograd should see for a weight whose gradient ``grad_written`` was just produced.
+
+    With a sink the kernel already wrote into the arena: tell the reducer and hand autograd ``None``.
+    """
+    if sink is not None:
+        ready = getattr(param, "_mlt_ready", None)
+        if ready is not None:
+            ready()
+        return None
+    return grad_written
+
+
+# ----------------------------------------------------------------------------------------------
+# small-shape CNN path (direct conv + pool, small linear)
+# ----------------------------------------------------------------------------------------------
+DIRECT_CONV_MAX_TAPS = 1023
+
+
+class _ConvReluPoolFn(torch.autograd.Function):
+    """conv2d(stride 1, no pad) + bias [+ ReLU] [+ 2x2 max-pool] as one kernel; fp32 NCHW."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu, pool, wparam, bparam):
+        B, Cin, H, W = x.shape
+        Cout, _, KH, KW = weight.shape
+        OH, OW = H - KH + 1, W - KW + 1
+        PH, PW = (OH // 2, OW // 2) if pool else (OH, OW)
+        x = x.contiguous()
+        y = torch.empty((B, Cout, PH, PW), dtype=torch.float32, device=x.device)
+        idx = torch.empty((B, Cout, PH, PW), dtype=torch.uint8, device=x.device) if pool else None
+        check(_lib.lib().mlt_conv2d_direct_fwd(ptr(x), ptr(weight), ptr(bias), ptr(y), ptr(idx), _c_int(B), _c_int(Cin),
+                                               _c_int(H), _c_int(W), _c_int(Cout), _c_int(KH), _c_int(KW),
+                                               _c_int(int(relu)), _c_int(int(pool)), stream_handle()),
+              "mlt_conv2d_direct_fwd")
+        launches.bump("conv2d_direct_fwd")
+        ctx.save_for_backward(x, weight, y, idx if idx is not None else torch.empty(0, device=x.device))
+        ctx.cfg = (relu, pool, bias is not None)
+        ctx.params = (wparam, bparam)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y, idx = ctx.saved_tensors
+        relu, pool, has_bias = ctx.cfg
+        wparam, bparam = ctx.params
+        B, Cin, H, W = x.shape
+        Cout, _, KH, KW = weight.shape
+        dy = dy.contiguous()
+        need_dx = ctx.needs_input_grad[0]
+        dx = torch.empty_like(x) if need_dx else None
+        wsink, bsink = _sink(wparam), _sink(bparam) if has_bias else None
+        dw = wsink if wsink is not None else torch.empty_like(weight)
+        db = (bsink if bsink is not None else torch.empty(Cout, dtype=torch.float32, device=x.device)) if has_bias else None
+        L = _lib.lib()
+        L.mlt_conv2d_direct_bwd_scratch_bytes.restype = _c_ll
+        nbytes = L.mlt_conv2d_direct_bwd_scratch_bytes(_c_int(B), _c_int(Cin), _c_int(Cout), _c_int(KH), _c_int(KW))
+        ws = scratch(x.device, f"convbwd{Cout}x{Cin}x{KH}x{KW}", nbytes)
+        check(L.mlt_conv2d_direct_bwd(ptr(x), ptr(weight), ptr(dy), ptr(y), ptr(idx if pool else None), ptr(dx), ptr(dw),
+                                      ptr(db), ptr(ws), _c_ll(ws.numel()), _c_int(B), _c_int(Cin), _c_int(H), _c_int(W),
+                                      _c_int(Cout), _c_int(KH), _c_int(KW), _c_int(int(relu)), _c_int(int(pool)),
+                                      _c_int(0), stream_handle()), "mlt_conv2d_direct_bwd")
+        launches.bump("conv2d_direct_bwd", 2 if need_dx else 1)
+        return dx, _deliver(wparam, dw, wsink), (_deliver(bparam, db, bsink) if has_bias else None), None, None, None, None
+
+
+def conv_relu_pool(x, weight, bias=None, relu=True, pool=True):
+    """Fused small-channel convolution block.  CPU / oracle: ``max_pool2d(relu(conv2d(x)))``."""
+    taps = weight.shape[1] * weight.shape[2] * weight.shape[3]
+    if use_native(x, weight) and x.dtype == torch.float32 and taps <= DIRECT_CONV_MAX_TAPS:
+        return _ConvReluPoolFn.apply(x, weight.detach(), None if bias is None else bias.detach(), relu, pool, weight, bias) \
+            if _has_sink(weight) else _ConvReluPoolFn.apply(x, weight, bias, relu, pool, None, None)
+    y = TF.conv2d(x, weight, bias)
+    if relu:
+        y = TF.relu(y)
+    if pool:
+        y = TF.max_pool2d(y, 2, 2)
+    return y
+
+
+def _has_sink(p) -> bool:
+    return getattr(p, "_mlt_grad_sink", None) is not None and torch.is_grad_enabled() and p.requires_grad
+
+
+class _LinearSmallFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, act, wparam, bparam):
+        B, K = x.shape
+        N = weight.shape[0]
+        x = x.contiguous()
+        y = torch.empty((B, N), dtype=torch.float32, device=x.device)
+        check(_lib.lib().mlt_linear_small_fwd(ptr(x), ptr(weight), ptr(bias), ptr(y), _c_int(B), _c_int(K), _c_int(N),
+                                              _c_int(act), stream_handle()), "mlt_linear_small_fwd")
+        launches.bump("linear_small_fwd")
+        ctx.save_for_backward(x, weight, y)
+        ctx.cfg = (act, bias is not None)
+        ctx.params = (wparam, bparam)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight, y = ctx.saved_tensors
+        act, has_bias = ctx.cfg
+        wparam, bparam = ctx.params
+        B, K = x.shape
+        N = weight.shape[0]
+        dy = dy.contiguous()
+        need_dx = ctx.needs_input_grad[0]
+        dx = torch.empty_like(x) if need_dx else None
+        wsink, bsink = _sink(wparam), _sink(bparam) if has_bias else None
+        dw = wsink if wsink is not None else torch.empty_like(weight)
+        db = (bsink if bsink is not None else torch.empty(N, dtype=torch.float32, device=x.device)) if has_bias else None
+        check(_lib.lib().mlt_linear_small_bwd(ptr(dy), ptr(y), ptr(x), ptr(weight), ptr(dx), ptr(dw), ptr(db), _c_int(B),
+                                              _c_int(K), _c_int(N), _c_int(act), _c_int(0), stream_handle()),
+              "mlt_linear_small_bwd")
+        launches.bump("linear_small_bwd")
+        return dx, _deliver(wparam, dw, wsink), (_deliver(bparam, db, bsink) if has_bias else None), None, None, None
+
+
+SMALL_LINEAR_MAX = 1 << 22      # B*K*N below this stays on the CUDA-core path
+
+
+def _torch_act(y, act):
+    if act in (None, "none"):
+        return y
+    return {"relu": TF.relu, "gelu": TF.gelu, "tanh": torch.tanh}[act](y)
+
+
+def linear_act(x, weight, bias=None, act: Optional[str] = None):
+    """``act(x @ W^T + b)`` with the activation fused into the GEMM epilogue."""
+    if use_native(x, weight):
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, x.shape[-1])
+        B, K = x2.shape
+        N = weight.shape[0]
+        if x.dtype == torch.float32 and act in (None, "none", "relu", "tanh") and B * K * N <= SMALL_LINEAR_MAX:
+            a = ACT_IDS[act]
+            if _has_sink(weight):
+                y = _LinearSmallFn.apply(x2, weight.detach(), None if bias is None else bias.detach(), a, weight, bias)
+            else:
+                y = _LinearSmallFn.apply(x2, weight, bias, a, None, None)
+            return y.reshape(*lead, N)
+        from .gemm import linear_act_tc
+
+        return linear_act_tc(x, weight, bias, act)
+    return _torch_act(TF.linear(x, weight, bias), act)
