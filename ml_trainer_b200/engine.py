@@ -40,6 +40,7 @@ class StepEngine:
         self._eager_steps = 0
         self._pool = None
         self.graph_replays = 0
+        self.launches_per_step = 0
         self.last_loss: Optional[torch.Tensor] = None
 
     # ------------------------------------------------------------ accumulators
@@ -51,6 +52,10 @@ class StepEngine:
 
     def read_accumulators(self):
         return self.acc.tolist()
+
+    def graph_replays_since(self, last_n_steps: int) -> int:
+        """How many of the last ``last_n_steps`` train steps were graph replays (all of them once captured)."""
+        return min(self.graph_replays, last_n_steps) if self.use_graph else 0
 
     def invalidate(self):
         """Drop captured graphs (after a checkpoint load or any out-of-band state change)."""
@@ -119,9 +124,13 @@ class StepEngine:
         # capture: hyper-parameters are uploaded outside the graph, everything else inside
         opt.begin_step()
         torch.cuda.synchronize(self.device)
+        from .ops._lib import launches
+
+        n0 = launches.n
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, pool=self._pool):
             self._train_body(inputs, targets)
+        self.launches_per_step = launches.n - n0      # native kernels recorded into (and replayed by) the graph
         if self._pool is None:
             self._pool = g.pool()
         self._graphs[key] = g

@@ -1,0 +1,158 @@
+"""Each sm_100a kernel against a plain PyTorch fp32 statement of the same op (SURVEY §4 GPU kernel tier)."""
+import pytest
+import torch
+import torch.nn.functional as TF
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda", 0)
+
+
+def test_native_library_is_loaded():
+    from ml_trainer_b200.ops import _lib
+
+    assert _lib.native_available()
+    assert _lib.lib().mlt_version() >= 100
+
+
+@pytest.mark.parametrize("B,Cin,H,Cout,K", [(32, 3, 32, 6, 5), (32, 6, 14, 16, 5), (4, 3, 32, 6, 5), (5, 2, 11, 3, 3),
+                                            (1, 1, 6, 1, 5), (7, 4, 9, 5, 2)])
+@pytest.mark.parametrize("relu,pool", [(True, True), (False, False), (True, False), (False, True)])
+def test_conv_relu_pool_fwd_bwd(B, Cin, H, Cout, K, relu, pool):
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(0)
+    dev = _dev()
+    x = torch.randn(B, Cin, H, H, device=dev, requires_grad=True)
+    w = torch.randn(Cout, Cin, K, K, device=dev, requires_grad=True) * 0.2
+    w = w.detach().requires_grad_()
+    b = torch.randn(Cout, device=dev, requires_grad=True)
+    y = F.conv_relu_pool(x, w, b, relu=relu, pool=pool)
+    ref = TF.conv2d(x, w, b)
+    if relu:
+        ref = TF.relu(ref)
+    if pool:
+        ref = TF.max_pool2d(ref, 2, 2)
+    assert y.shape == ref.shape
+    assert torch.allclose(y, ref, rtol=1e-4, atol=1e-4), (y - ref).abs().max()
+    g = torch.randn_like(ref)
+    gx, gw, gb = torch.autograd.grad(y, (x, w, b), g)
+    rx, rw, rb = torch.autograd.grad(ref, (x, w, b), g)
+    assert torch.allclose(gx, rx, rtol=1e-4, atol=1e-4), (gx - rx).abs().max()
+    assert torch.allclose(gw, rw, rtol=1e-3, atol=1e-3), (gw - rw).abs().max()
+    assert torch.allclose(gb, rb, rtol=1e-3, atol=1e-3), (gb - rb).abs().max()
+
+
+def test_conv_bwd_scratch_self_resets():
+    """The wgrad ticket/partial scratch must be reusable launch after launch without re-zeroing."""
+    from ml_trainer_b200.ops import functional as F
+
+    dev = _dev()
+    torch.manual_seed(1)
+    w = (torch.randn(6, 3, 5, 5, device=dev) * 0.2).requires_grad_()
+    b = torch.zeros(6, device=dev, requires_grad=True)
+    for i in range(4):
+        x = torch.randn(32, 3, 32, 32, device=dev)
+        y = F.conv_relu_pool(x, w, b)
+        ref = TF.max_pool2d(TF.relu(TF.conv2d(x, w, b)), 2, 2)
+        g = torch.randn_like(ref)
+        gw, = torch.autograd.grad(y, w, g)
+        rw, = torch.autograd.grad(ref, w, g)
+        assert torch.allclose(gw, rw, rtol=1e-3, atol=1e-3), (i, (gw - rw).abs().max())
+
+
+@pytest.mark.parametrize("B,K,N", [(32, 400, 120), (32, 120, 84), (32, 84, 10), (4, 400, 120), (3, 17, 5), (130, 33, 7)])
+@pytest.mark.parametrize("act", [None, "relu", "tanh"])
+def test_linear_small_fwd_bwd(B, K, N, act):
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(0)
+    dev = _dev()
+    x = torch.randn(B, K, device=dev, requires_grad=True)
+    w = (torch.randn(N, K, device=dev) * 0.1).requires_grad_()
+    b = torch.randn(N, device=dev, requires_grad=True)
+    y = F.linear_act(x, w, b, act)
+    ref = F._torch_act(TF.linear(x, w, b), act)
+    assert torch.allclose(y, ref, rtol=1e-4, atol=1e-4), (y - ref).abs().max()
+    g = torch.randn_like(ref)
+    got = torch.autograd.grad(y, (x, w, b), g)
+    exp = torch.autograd.grad(ref, (x, w, b), g)
+    for a, e, name in zip(got, exp, "xwb"):
+        assert torch.allclose(a, e, rtol=1e-3, atol=1e-3), (name, (a - e).abs().max())
+
+
+@pytest.mark.parametrize("B,C", [(32, 10), (4, 10), (256, 1000), (32, 2), (1000, 33), (5000, 10)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_softmax_xent(B, C, dtype):
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(0)
+    dev = _dev()
+    logits = (torch.randn(B, C, device=dev) * 3).to(dtype)
+    tgt = torch.randint(0, C, (B,), device=dev)
+    acc = torch.zeros(3, device=dev)
+    for rep in range(2):                                  # twice: the workspace must self-reset
+        loss, dl = F.softmax_xent(logits, tgt, acc, want_acc=True)
+    lf = logits.float().requires_grad_()
+    ref = TF.cross_entropy(lf, tgt)
+    rdl, = torch.autograd.grad(ref, lf)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert abs(loss.item() - ref.item()) < 1e-4 * max(1.0, abs(ref.item()))
+    assert torch.allclose(dl.float(), rdl, rtol=tol, atol=tol / 10 if dtype == torch.float32 else 1e-3)
+    ref_acc = (lf.argmax(-1) == tgt).float().mean().item()
+    a = acc.tolist()
+    assert abs(a[0] - 2 * ref.item()) < 2e-4 * max(1.0, abs(ref.item())) and abs(a[1] - 2 * ref_acc) < 1e-5 and a[2] == 2.0
+    assert abs(F.argmax_accuracy(logits, tgt).item() - ref_acc) < 1e-6
+    # autograd front end
+    l2 = logits.float().requires_grad_()
+    out = F.cross_entropy(l2, tgt)
+    out.backward()
+    assert torch.allclose(l2.grad, rdl, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("kind", ["sgd", "adam", "adamw", "adagrad", "adamax"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("wd", [0.0, 0.01])
+def test_fused_update_matches_rules(kind, dtype, wd):
+    """CUDA rule kernels vs the PyTorch oracle in optim/rules.py (itself tested against torch.optim on CPU)."""
+    from ml_trainer_b200.optim import FusedOptimizer
+
+    torch.manual_seed(0)
+    shapes = [(300, 7), (129,), (64, 64), (5,)]
+    def make(device):
+        torch.manual_seed(0)
+        ps = [torch.nn.Parameter(torch.randn(s, device=device)) for s in shapes]
+        return ps, FusedOptimizer(ps, kind=kind, lr=0.01, momentum=0.9, weight_decay=wd, compute_dtype=dtype)
+    pc, oc = make("cpu")
+    pg, og = make(_dev())
+    for step in range(4):
+        torch.manual_seed(100 + step)
+        g = torch.randn(oc.numel).to(dtype)
+        oc.grad.copy_(g)
+        og.grad.copy_(g.to(_dev()))
+        oc.begin_step(); oc.step_range(0, oc.numel)
+        og.begin_step(); og.step_range(0, og.numel)
+    assert torch.allclose(og.master.cpu(), oc.master, rtol=1e-5, atol=1e-6), (og.master.cpu() - oc.master).abs().max()
+    assert torch.allclose(og.s1.cpu(), oc.s1, rtol=1e-5, atol=1e-6)
+    if dtype == torch.bfloat16:
+        assert torch.equal(og.model.cpu(), og.master.cpu().to(torch.bfloat16))
+        assert pg[0].dtype == torch.bfloat16
+
+
+def test_fused_update_partial_ranges():
+    from ml_trainer_b200.optim import FusedOptimizer
+
+    dev = _dev()
+    ps = [torch.nn.Parameter(torch.randn(1000, device=dev)) for _ in range(3)]
+    opt = FusedOptimizer(ps, kind="sgd", lr=0.1, momentum=0.0)
+    opt.grad.fill_(1.0)
+    before = opt.master.clone()
+    opt.begin_step()
+    lo, hi = opt.span(1, 2)
+    opt.step_range(lo, hi)
+    torch.cuda.synchronize()
+    delta = opt.master - before
+    assert torch.allclose(delta[lo:hi], torch.full_like(delta[lo:hi], -0.1))
+    assert delta[:lo].abs().max() == 0 and delta[hi:].abs().max() == 0
