@@ -144,6 +144,7 @@ conv2d_direct_wgrad_kernel(const float* __restrict__ x, const float* __restrict_
       if (t < nW) {
         const float* xt = xs + tap_off[j];
         float a = acc[j];
+#pragma unroll 4
         for (int i = 0; i < per; ++i) a = fmaf(gs[i], xt[offs[i]], a);
         acc[j] = a;
       } else if (t == nW) {
@@ -189,52 +190,66 @@ conv2d_direct_wgrad_kernel(const float* __restrict__ x, const float* __restrict_
 }
 
 // -----------------------------------------------------------------------------------------------------
-// dgrad: dx[b,ci,h,w] = sum_{co,kh,kw} dz[b,co,h-kh,w-kw] * w[co,ci,kh,kw].  grid = B; the dense pre-pool
-// gradient plane of the sample is rebuilt in shared memory from (dy, y, idx), filters sit beside it.
+// dgrad: dx[b,ci,h,w] = sum_{co,kh,kw} dz[b,co,h-kh,w-kw] * w[co,ci,kh,kw].  grid = (B, Cin).  The pre-pool
+// gradient plane of the sample is rebuilt in shared memory from (dy, y, idx) with a zero halo of K-1 so the
+// tap loops carry no bounds checks; KS > 0 fixes the (square) filter size at compile time and unrolls them.
 // -----------------------------------------------------------------------------------------------------
-template <bool RELU, bool POOL>
+template <bool RELU, bool POOL, int KS>
 __global__ void __launch_bounds__(256)
 conv2d_direct_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ y, const unsigned char* __restrict__ idx,
-                           const float* __restrict__ w, float* __restrict__ dx, int Cin, int H, int W, int Cout, int KH,
-                           int KW) {
+                           const float* __restrict__ w, float* __restrict__ dx, int Cin, int H, int W, int Cout, int KH_,
+                           int KW_) {
   extern __shared__ float smem[];
-  const int b = blockIdx.x;
+  const int KH = KS > 0 ? KS : KH_, KW = KS > 0 ? KS : KW_;
+  const int b = blockIdx.x, ci = blockIdx.y;
   const int OH = H - KH + 1, OW = W - KW + 1;
   const int PH = POOL ? OH / 2 : OH, PW = POOL ? OW / 2 : OW;
-  const int per = PH * PW, plane = OH * OW, wsz = Cin * KH * KW;
-  float* dz = smem;                       // [Cout][OH][OW]
-  float* ws = smem + Cout * plane;        // [Cout][Cin][KH][KW]
-  for (int i = threadIdx.x; i < Cout * plane; i += blockDim.x) dz[i] = 0.f;
-  for (int i = threadIdx.x; i < Cout * wsz; i += blockDim.x) ws[i] = w[i];
+  const int per = PH * PW, ksz = KH * KW;
+  const int ZH = OH + 2 * (KH - 1), ZW = OW + 2 * (KW - 1), zplane = ZH * ZW;   // haloed plane
+  float* dz = smem;                       // [Cout][ZH][ZW]
+  float* ws = smem + Cout * zplane;       // [Cout][KH][KW]   (this CTA's input channel only)
+  for (int i = threadIdx.x; i < Cout * zplane; i += blockDim.x) dz[i] = 0.f;
+  for (int i = threadIdx.x; i < Cout * ksz; i += blockDim.x) {
+    const int co = i / ksz, r = i - co * ksz;
+    ws[i] = w[((size_t)co * Cin + ci) * ksz + r];
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < Cout * per; i += blockDim.x) {
     const int co = i / per, r = i - co * per;
     const size_t gi = ((size_t)b * Cout + co) * per + r;
     float g = dy[gi];
     if (RELU && !(y[gi] > 0.f)) g = 0.f;
-    int pos;
+    int oh, ow;
     if (POOL) {
       const int ph = r / PW, pw = r - ph * PW, am = idx[gi];
-      pos = (2 * ph + (am >> 1)) * OW + 2 * pw + (am & 1);
+      oh = 2 * ph + (am >> 1);
+      ow = 2 * pw + (am & 1);
     } else {
-      pos = r;
+      oh = r / OW;
+      ow = r - oh * OW;
     }
-    dz[co * plane + pos] = g;
+    dz[co * zplane + (oh + KH - 1) * ZW + (ow + KW - 1)] = g;
   }
   __syncthreads();
-  for (int o = threadIdx.x; o < Cin * H * W; o += blockDim.x) {
-    const int ci = o / (H * W), r = o - ci * H * W;
-    const int h = r / W, wq = r - h * W;
-    const int kh_lo = max(0, h - OH + 1), kh_hi = min(KH - 1, h);
-    const int kw_lo = max(0, wq - OW + 1), kw_hi = min(KW - 1, wq);
+  for (int o = threadIdx.x; o < H * W; o += blockDim.x) {
+    const int h = o / W, wq = o - h * W;
+    // dz index for tap (kh,kw): row (h - kh) + (KH-1), col (wq - kw) + (KW-1)
+    const float* base = dz + (h + KH - 1) * ZW + (wq + KW - 1);
     float a = 0.f;
     for (int co = 0; co < Cout; ++co) {
-      const float* dzc = dz + co * plane;
-      const float* wk = ws + co * wsz + ci * KH * KW;
-      for (int kh = kh_lo; kh <= kh_hi; ++kh)
-        for (int kw = kw_lo; kw <= kw_hi; ++kw) a = fmaf(dzc[(h - kh) * OW + (wq - kw)], wk[kh * KW + kw], a);
+      const float* dzc = base + co * zplane;
+      const float* wk = ws + co * ksz;
+      if (KS > 0) {
+#pragma unroll
+        for (int kh = 0; kh < (KS > 0 ? KS : 1); ++kh)
+#pragma unroll
+          for (int kw = 0; kw < (KS > 0 ? KS : 1); ++kw) a = fmaf(dzc[-kh * ZW - kw], wk[kh * KS + kw], a);
+      } else {
+        for (int kh = 0; kh < KH; ++kh)
+          for (int kw = 0; kw < KW; ++kw) a = fmaf(dzc[-kh * ZW - kw], wk[kh * KW + kw], a);
+      }
     }
-    dx[(size_t)b * Cin * H * W + o] = a;
+    dx[((size_t)b * Cin + ci) * H * W + o] = a;
   }
 }
 
@@ -393,12 +408,25 @@ extern "C" int mlt_conv2d_direct_bwd(const void* x, const void* w, const void* d
     MLT_LAUNCH_CHECK();
   }
   if (dx != nullptr) {
-    const size_t smem = ((size_t)Cout * OH * OW + (size_t)Cout * nW) * sizeof(float);
+    const size_t smem = ((size_t)Cout * (OH + 2 * (KH - 1)) * (OW + 2 * (KW - 1)) + (size_t)Cout * KH * KW) * sizeof(float);
+    dim3 grid(B, Cin);
     DISPATCH_RP(relu, pool, {
-      auto k = conv2d_direct_dgrad_kernel<R_, P_>;
-      if (set_smem(k, smem)) return 1;
-      k<<<B, 256, smem, st>>>((const float*)dy, (const float*)y, (const unsigned char*)pool_idx, (const float*)w,
-                              (float*)dx, Cin, H, W, Cout, KH, KW);
+      if (KH == 5 && KW == 5) {
+        auto k = conv2d_direct_dgrad_kernel<R_, P_, 5>;
+        if (set_smem(k, smem)) return 1;
+        k<<<grid, 256, smem, st>>>((const float*)dy, (const float*)y, (const unsigned char*)pool_idx, (const float*)w,
+                                   (float*)dx, Cin, H, W, Cout, KH, KW);
+      } else if (KH == 3 && KW == 3) {
+        auto k = conv2d_direct_dgrad_kernel<R_, P_, 3>;
+        if (set_smem(k, smem)) return 1;
+        k<<<grid, 256, smem, st>>>((const float*)dy, (const float*)y, (const unsigned char*)pool_idx, (const float*)w,
+                                   (float*)dx, Cin, H, W, Cout, KH, KW);
+      } else {
+        auto k = conv2d_direct_dgrad_kernel<R_, P_, 0>;
+        if (set_smem(k, smem)) return 1;
+        k<<<grid, 256, smem, st>>>((const float*)dy, (const float*)y, (const unsigned char*)pool_idx, (const float*)w,
+                                   (float*)dx, Cin, H, W, Cout, KH, KW);
+      }
     });
     MLT_LAUNCH_CHECK();
   }

@@ -9,6 +9,12 @@ if ROOT not in sys.path:
 
 os.environ.setdefault("MLT_LOG_LEVEL", "WARNING")
 
+import torch  # noqa: E402
+
+# the oracle for every kernel test is PLAIN fp32 PyTorch: no TF32 in cuDNN convolutions or cuBLAS matmuls
+torch.backends.cudnn.allow_tf32 = False
+torch.backends.cuda.matmul.allow_tf32 = False
+
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on a B200)")

@@ -123,7 +123,7 @@ def test_fused_update_matches_rules(kind, dtype, wd):
     shapes = [(300, 7), (129,), (64, 64), (5,)]
     def make(device):
         torch.manual_seed(0)
-        ps = [torch.nn.Parameter(torch.randn(s, device=device)) for s in shapes]
+        ps = [torch.nn.Parameter(torch.randn(s).to(device)) for s in shapes]      # same values on both devices
         return ps, FusedOptimizer(ps, kind=kind, lr=0.01, momentum=0.9, weight_decay=wd, compute_dtype=dtype)
     pc, oc = make("cpu")
     pg, og = make(_dev())
