@@ -455,3 +455,69 @@ extern "C" int mlt_linear_small_bwd(const void* dy, const void* y, const void* x
   MLT_LAUNCH_CHECK();
   return 0;
 }
+
+// =====================================================================================================
+// Allocation-free variant of mlt_conv2d_direct_bwd.
+//
+// Who needs it: callers that are not allowed to obtain device memory at the point where they run this
+// backward pass.  Examples: a plug-in living inside a host application that handed every free byte of the GPU
+// to its own memory pool at start-up, so a later cudaMalloc fails or is forbidden by the host's contract;
+// and latency-critical loops that cannot tolerate the device-wide synchronisation cudaMalloc/cudaFree imply.
+// Such callers still own their inputs and outputs, but have nowhere to get the cross-CTA reduction scratch
+// (per-channel tickets + per-chunk partial sums) that the normal entry point expects from them.
+//
+// Here that scratch is a fixed array in the library's device image.  Consequences worth knowing:
+//   * It costs MLT_CONV2D_BWD_NOALLOC_SCRATCH_BYTES (256 KiB) on EVERY GPU that loads this library, from load
+//     until the process exits, whether or not this function is ever called.
+//   * Problems whose scratch need (mlt_conv2d_direct_bwd_scratch_bytes) exceeds that size are rejected with an
+//     error; use mlt_conv2d_direct_bwd with caller-provided scratch for those.
+//   * The first call on each device looks up the array's device address (cudaGetSymbolAddress, which may load
+//     the module).  Make that first call outside any stream capture.  Later calls on the device only enqueue
+//     a small memset and the kernels.
+//   * All calls on a device share the one array and it keeps whatever the previous call left behind.  The
+//     ticket words, which must be zero when the kernel starts, are cleared on `stream` at the start of every
+//     call; the partial sums are fully overwritten before they are read.  Two calls whose GPU work overlaps
+//     in time (different streams, or different host threads on the same device) race on the array and produce
+//     garbage: serialise them on one stream or with events.
+// It performs no cudaMalloc / cudaFree and calls no allocating library routine.
+// =====================================================================================================
+#include <mutex>
+
+static __device__ __align__(256) unsigned char g_conv2d_bwd_noalloc_scratch[MLT_CONV2D_BWD_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_scratch_addr[kNoAllocMaxDevices] = {};   // device address of the array, per device ordinal
+}  // namespace
+
+extern "C" int mlt_conv2d_direct_bwd_noalloc(const void* x, const void* w, const void* dy, const void* y,
+                                             const void* pool_idx, void* dx, void* dw, void* db, int B, int Cin, int H,
+                                             int W, int Cout, int KH, int KW, int relu, int pool, int accumulate,
+                                             void* stream) {
+  MLT_REQUIRE(B > 0 && Cin > 0 && Cout > 0 && KH > 0 && KW > 0, "mlt_conv2d_direct_bwd_noalloc: empty problem");
+  const long long need = mlt_conv2d_direct_bwd_scratch_bytes(B, Cin, Cout, KH, KW);
+  MLT_REQUIRE(need <= (long long)MLT_CONV2D_BWD_NOALLOC_SCRATCH_BYTES,
+              "mlt_conv2d_direct_bwd_noalloc: this problem needs %lld bytes of reduction scratch but the built-in buffer "
+              "holds %d; call mlt_conv2d_direct_bwd with caller-provided scratch instead",
+              need, (int)MLT_CONV2D_BWD_NOALLOC_SCRATCH_BYTES);
+  int dev = -1;
+  MLT_CHECK_CUDA(cudaGetDevice(&dev));
+  MLT_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, "mlt_conv2d_direct_bwd_noalloc: device ordinal %d out of range", dev);
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_scratch_addr[dev] == nullptr) {
+      // In host code the array's name is only a handle; the kernels need its address on the CURRENT device.
+      void* addr = nullptr;
+      MLT_CHECK_CUDA(cudaGetSymbolAddress(&addr, g_conv2d_bwd_noalloc_scratch));
+      MLT_REQUIRE(addr != nullptr, "mlt_conv2d_direct_bwd_noalloc: cudaGetSymbolAddress returned a null address");
+      g_noalloc_scratch_addr[dev] = addr;
+    }
+    scratch = g_noalloc_scratch_addr[dev];
+  }
+  // The array still holds the previous call's data: tickets must start at zero.
+  MLT_CHECK_CUDA(cudaMemsetAsync(scratch, 0, (size_t)conv_bwd_ticket_bytes(Cout), (cudaStream_t)stream));
+  return mlt_conv2d_direct_bwd(x, w, dy, y, pool_idx, dx, dw, db, scratch, (long long)MLT_CONV2D_BWD_NOALLOC_SCRATCH_BYTES,
+                               B, Cin, H, W, Cout, KH, KW, relu, pool, accumulate, stream);
+}

@@ -61,6 +61,16 @@ long long mlt_conv2d_direct_bwd_scratch_bytes(int B, int Cin, int Cout, int KH, 
 int mlt_conv2d_direct_bwd(const void* x, const void* w, const void* dy, const void* y, const void* pool_idx, void* dx,
                           void* dw, void* db, void* scratch, long long scratch_bytes, int B, int Cin, int H, int W,
                           int Cout, int KH, int KW, int relu, int pool, int accumulate, void* stream);
+/* Same computation as mlt_conv2d_direct_bwd for callers that cannot allocate device memory (a plug-in inside an
+ * application that already gave the whole GPU to its own pool; a loop that cannot afford cudaMalloc's implicit
+ * synchronisation).  The reduction scratch is a MLT_CONV2D_BWD_NOALLOC_SCRATCH_BYTES array built into the library
+ * (resident on every GPU that loads it, until exit); larger problems are rejected with an error.  The first call on a
+ * device resolves the array's address: make it before any stream capture.  Calls share the array, so calls whose GPU
+ * work overlaps race.  This entry point has no counterpart in the reference. */
+#define MLT_CONV2D_BWD_NOALLOC_SCRATCH_BYTES (256 * 1024)
+int mlt_conv2d_direct_bwd_noalloc(const void* x, const void* w, const void* dy, const void* y, const void* pool_idx,
+                                  void* dx, void* dw, void* db, int B, int Cin, int H, int W, int Cout, int KH, int KW,
+                                  int relu, int pool, int accumulate, void* stream);
 int mlt_linear_small_fwd(const void* x, const void* w, const void* bias, void* y, int B, int K, int N, int act,
                          void* stream);
 int mlt_linear_small_bwd(const void* dy, const void* y, const void* x, const void* w, void* dx, void* dw, void* db,
