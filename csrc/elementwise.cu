@@ -1,0 +1,167 @@
+// Bandwidth-bound helpers around the GEMMs: activation backward, bias gradient (column sum),
+// dtype casts.  Everything is vectorised to 16-byte accesses; the roofline is bytes / HBM bandwidth.
+#include "common.cuh"
+#include "../include/mlt_b200.h"
+
+namespace mlt {
+
+__device__ __forceinline__ float act_grad(int act, int from_pre, float s) {
+  // s is the pre-activation z (from_pre) or the activation output y
+  switch (act) {
+    case ACT_RELU: return s > 0.f ? 1.f : 0.f;
+    case ACT_TANH: { const float t = from_pre ? tanhf(s) : s; return 1.f - t * t; }
+    case ACT_GELU: return gelu_bwd(s);      // needs the pre-activation
+    default: return 1.f;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+act_backward_kernel(const T* __restrict__ dy, const T* __restrict__ saved, T* __restrict__ dz, long long n, int act, int from_pre) {
+  constexpr int V = 16 / sizeof(T);
+  const long long nv = n / V;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
+    const uint4 a = reinterpret_cast<const uint4*>(dy)[i];
+    const uint4 s = reinterpret_cast<const uint4*>(saved)[i];
+    uint4 o;
+    const T* ap = reinterpret_cast<const T*>(&a);
+    const T* sp = reinterpret_cast<const T*>(&s);
+    T* op = reinterpret_cast<T*>(&o);
+#pragma unroll
+    for (int j = 0; j < V; ++j) op[j] = from_float<T>(to_float(ap[j]) * act_grad(act, from_pre, to_float(sp[j])));
+    reinterpret_cast<uint4*>(dz)[i] = o;
+  }
+  for (long long i = nv * V + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    dz[i] = from_float<T>(to_float(dy[i]) * act_grad(act, from_pre, to_float(saved[i])));
+}
+
+// Column sums of x[M][N] (row pitch ld).  grid = (ceil(N/64), R).  A warp reads 64 consecutive columns of a row
+// (2 per lane), warps stride over the CTA's rows; CTAs of one column tile combine through scratch
+// partial[R][N] + one ticket per column tile; the last one writes the result (deterministic order).
+template <typename T, typename O>
+__global__ void __launch_bounds__(256)
+colsum_kernel(const T* __restrict__ x, O* __restrict__ out, float* __restrict__ partial, unsigned int* __restrict__ tickets,
+              int M, int N, long long ld, int accumulate) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c0 = blockIdx.x * 64 + lane * 2;
+  const int R = gridDim.y;
+  const int rows_per = ceil_div(M, R);
+  const int r_lo = blockIdx.y * rows_per, r_hi = min(M, r_lo + rows_per);
+  float s0 = 0.f, s1 = 0.f;
+  if (c0 < N) {
+    const bool pair = c0 + 1 < N;
+    for (int r = r_lo + warp; r < r_hi; r += 8) {
+      const T* p = x + (size_t)r * ld + c0;
+      s0 += to_float(p[0]);
+      if (pair) s1 += to_float(p[1]);
+    }
+  }
+  __shared__ float sh[8][64];
+  __shared__ bool is_last;
+  sh[warp][lane * 2] = s0;
+  sh[warp][lane * 2 + 1] = s1;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += sh[w][threadIdx.x];
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    if (c < N) {
+      if (R == 1) out[c] = from_float<O>((accumulate ? to_float(out[c]) : 0.f) + t);
+      else partial[(size_t)blockIdx.y * N + c] = t;
+    }
+  }
+  if (R == 1) return;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(&tickets[blockIdx.x], 1u);
+    is_last = tk == (unsigned int)R - 1;
+    if (is_last) tickets[blockIdx.x] = 0u;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  if (threadIdx.x < 64) {
+    const int c = blockIdx.x * 64 + threadIdx.x;
+    if (c < N) {
+      float t = 0.f;
+      for (int k = 0; k < R; ++k) t += __ldcg(partial + (size_t)k * N + c);
+      out[c] = from_float<O>((accumulate ? to_float(out[c]) : 0.f) + t);
+    }
+  }
+}
+
+template <typename S, typename D>
+__global__ void __launch_bounds__(256) cast_kernel(const S* __restrict__ src, D* __restrict__ dst, long long n) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = from_float<D>(to_float(src[i]));
+}
+
+static int ew_grid(long long work_items) {
+  long long b = ceil_div64(work_items, 256);
+  const long long cap = (long long)kNumSMs * 8;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+static int colsum_splits(int M, int N) {
+  const int tiles = ceil_div(N, 64);
+  int R = (2 * kNumSMs) / tiles;
+  if (R > ceil_div(M, 64)) R = ceil_div(M, 64);
+  return R < 1 ? 1 : R;
+}
+
+}  // namespace mlt
+
+using namespace mlt;
+
+extern "C" int mlt_act_backward(const void* dy, const void* saved, void* dz, long long n, int act, int from_pre, int is_bf16,
+                                void* stream) {
+  MLT_REQUIRE(act != ACT_GELU || from_pre, "mlt_act_backward: GELU backward needs the pre-activation");
+  if (n <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_bf16)
+    act_backward_kernel<__nv_bfloat16><<<ew_grid(n / 8 + 1), 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)saved,
+                                                                         (__nv_bfloat16*)dz, n, act, from_pre);
+  else
+    act_backward_kernel<float><<<ew_grid(n / 4 + 1), 256, 0, st>>>((const float*)dy, (const float*)saved, (float*)dz, n, act, from_pre);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" long long mlt_colsum_scratch_bytes(int M, int N) {
+  const int tiles = ceil_div(N, 64);
+  return ((long long)tiles * 4 + 255) / 256 * 256 + (long long)colsum_splits(M, N) * N * 4;
+}
+
+// out[N] = sum over rows of x[M][N];  x bf16 or fp32, out bf16 or fp32.  scratch: mlt_colsum_scratch_bytes, zeroed once.
+extern "C" int mlt_colsum(const void* x, int x_bf16, void* out, int out_bf16, void* scratch, long long scratch_bytes, int M,
+                          int N, long long ld, int accumulate, void* stream) {
+  MLT_REQUIRE(M > 0 && N > 0, "mlt_colsum: empty problem");
+  const int tiles = ceil_div(N, 64), R = colsum_splits(M, N);
+  MLT_REQUIRE(R == 1 || (scratch && scratch_bytes >= mlt_colsum_scratch_bytes(M, N)), "mlt_colsum: scratch too small");
+  unsigned int* tickets = (unsigned int*)scratch;
+  float* partial = scratch ? (float*)((char*)scratch + ((long long)tiles * 4 + 255) / 256 * 256) : nullptr;
+  dim3 grid(tiles, R);
+  cudaStream_t st = (cudaStream_t)stream;
+#define CS(T, O) colsum_kernel<T, O><<<grid, 256, 0, st>>>((const T*)x, (O*)out, partial, tickets, M, N, ld, accumulate)
+  if (x_bf16 && out_bf16) CS(__nv_bfloat16, __nv_bfloat16);
+  else if (x_bf16) CS(__nv_bfloat16, float);
+  else if (out_bf16) CS(float, __nv_bfloat16);
+  else CS(float, float);
+#undef CS
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int mlt_cast(const void* src, int src_bf16, void* dst, int dst_bf16, long long n, void* stream) {
+  if (n <= 0) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int g = ew_grid(n);
+  if (src_bf16 && !dst_bf16) cast_kernel<__nv_bfloat16, float><<<g, 256, 0, st>>>((const __nv_bfloat16*)src, (float*)dst, n);
+  else if (!src_bf16 && dst_bf16) cast_kernel<float, __nv_bfloat16><<<g, 256, 0, st>>>((const float*)src, (__nv_bfloat16*)dst, n);
+  else MLT_CHECK_CUDA(cudaMemcpyAsync(dst, src, (size_t)n * (src_bf16 ? 2 : 4), cudaMemcpyDeviceToDevice, st));
+  MLT_LAUNCH_CHECK();
+  return 0;
+}

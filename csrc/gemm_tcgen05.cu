@@ -1,0 +1,352 @@
+// bf16 GEMM on the 5th-generation tensor cores: D[M,N] = A[M,K] * B[N,K]^T (+ epilogue).
+//
+// Structure (one persistent CTA per SM, 192 threads, warp-specialised):
+//   warp 0      TMA producer: cp.async.bulk.tensor loads of 128-byte-swizzled A/B tiles into a STAGES-deep smem ring,
+//               completion counted on `full[s]` mbarriers.
+//   warp 1      MMA issuer: one elected thread issues tcgen05.mma (M=128, N=BN, K=16) reading smem through UMMA
+//               descriptors, accumulating fp32 in TMEM; tcgen05.commit frees smem slots (`empty[s]`) and publishes the
+//               finished accumulator (`tmem_full[a]`).  Two accumulator stages: the epilogue of tile i overlaps the MMAs
+//               of tile i+1.  This warp also owns the TMEM allocation.
+//   warps 2-5   epilogue: tcgen05.ld the accumulator (each warp its own 32-lane quadrant), apply bias / activation /
+//               activation-gradient, convert and store; then release the accumulator stage (`tmem_empty[a]`).
+// Operands may be K-major (reduction dim contiguous: activations [M,K], nn.Linear weights [N,K]) or MN-major
+// (reduction dim strided: what dgrad and wgrad see), selected per operand through the instruction descriptor's
+// major bits and the matching TMA box / smem-descriptor geometry, so backward needs no transposes.
+// Replaces the cuBLAS calls behind reference src/model.py:21-23 (fc layers) and every BERT / ResNet-FC GEMM.
+#include "common.cuh"
+#include "ptx.cuh"
+#include "../include/mlt_b200.h"
+#include <mutex>
+#include <unordered_map>
+
+namespace mlt {
+
+using namespace ptx;
+
+constexpr int BM = 128;        // tile rows (UMMA M)
+constexpr int BK = 64;         // k-block: 64 bf16 = 128 bytes = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 4;
+
+struct GemmParams {
+  int M, N, K;
+  void* out;
+  long long ldo;
+  int out_f32;
+  const void* bias;
+  int bias_f32;
+  int act;        // Act
+  int aux_mode;   // 0 none | 1 store pre-activation (bf16) to aux | 2 multiply by act'(aux)
+  void* aux;
+  long long ld_aux;
+  int a_mn, b_mn;
+  int num_m, num_n, num_k;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int kABytes = BM * BK * 2;                // 16 KB
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kTmemCols = 2 * BN;                   // two accumulator stages (power of two >= 32)
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_blk, int& n_blk) {
+  // groups of 8 M-blocks walk N together so concurrently running CTAs share A and B tiles in L2
+  constexpr int G = 8;
+  const int per_group = G * num_n;
+  const int group = tile / per_group;
+  const int first_m = group * G;
+  const int gsize = min(G, num_m - first_m);
+  const int r = tile - group * per_group;
+  m_blk = first_m + r % gsize;
+  n_blk = r / gsize;
+}
+
+__device__ __forceinline__ float act_grad_from_pre(int act, float z) {
+  switch (act) {
+    case ACT_RELU: return z > 0.f ? 1.f : 0.f;
+    case ACT_GELU: return gelu_bwd(z);
+    case ACT_TANH: { const float t = tanhf(z); return 1.f - t * t; }
+    default: return 1.f;
+  }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+  using Cfg = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint64_t* empty = full + Cfg::kStages;
+  uint64_t* tmem_full = empty + Cfg::kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int num_tiles = p.num_m * p.num_n;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], kEpiWarps * 32); }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_base_slot, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  if (warp == 0) {
+    // ===================================== TMA producer =====================================
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int m_blk, n_blk;
+        tile_coords(tile, p.num_m, p.num_n, m_blk, n_blk);
+        const int m0 = m_blk * BM, n0 = n_blk * BN;
+        for (int kb = 0; kb < p.num_k; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          uint8_t* sA = smem + stage * Cfg::kStageBytes;
+          uint8_t* sB = sA + Cfg::kABytes;
+          mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
+          const int k0 = kb * BK;
+          if (!p.a_mn) {
+            tma_load_2d(sA, &tmA, &full[stage], k0, m0);                       // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j) tma_load_2d(sA + j * 8192, &tmA, &full[stage], m0 + 64 * j, k0);   // box {64 rows, 64 k}
+          }
+          if (!p.b_mn) {
+            tma_load_2d(sB, &tmB, &full[stage], k0, n0);                       // box {64 k, BN rows}
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tma_load_2d(sB + j * 8192, &tmB, &full[stage], n0 + 64 * j, k0);
+          }
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issuer ========================================
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc_bf16(BM, BN, p.a_mn, p.b_mn);
+      // per-UMMA_K advance of the descriptor start address, and LBO/SBO, for each operand's layout
+      const uint32_t a_step = p.a_mn ? (UMMA_K * 128) : (UMMA_K * 2);
+      const uint32_t b_step = p.b_mn ? (UMMA_K * 128) : (UMMA_K * 2);
+      const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
+      int stage = 0; uint32_t phase = 0;
+      int as = 0; uint32_t aphase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[as], aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = 0; kb < p.num_k; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sA = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sB = sA + Cfg::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t adesc = make_smem_desc_sw128(sA + k * a_step, a_lbo, 1024);
+            const uint64_t bdesc = make_smem_desc_sw128(sB + k * b_step, b_lbo, 1024);
+            umma_f16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty[stage]);                       // smem slot reusable once these MMAs retire
+          if (kb == p.num_k - 1) umma_commit(&tmem_full[as]);
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================================== epilogue ===========================================
+    const int q = warp & 3;                                 // TMEM lane quadrant this warp may read
+    int as = 0; uint32_t aphase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int m_blk, n_blk;
+      tile_coords(tile, p.num_m, p.num_n, m_blk, n_blk);
+      const int row = m_blk * BM + q * 32 + lane;
+      const int n0 = n_blk * BN;
+      mbar_wait(&tmem_full[as], aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + c * 32, r);
+        tmem_ld_wait();
+        const int nb = n0 + c * 32;
+        if (row < p.M && nb < p.N) {
+          float v[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+          const bool full_chunk = nb + 32 <= p.N;
+          if (p.bias != nullptr) {
+            if (p.bias_f32) {
+              const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __ldg(bp + j);
+            } else {
+              const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __bfloat162float(bp[j]);
+            }
+          }
+          if (p.aux_mode == 1) {            // keep the pre-activation for backward
+            __nv_bfloat16* ap = reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
+            if (full_chunk) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 pk;
+                pk.x = pack_bf16(v[j], v[j + 1]); pk.y = pack_bf16(v[j + 2], v[j + 3]);
+                pk.z = pack_bf16(v[j + 4], v[j + 5]); pk.w = pack_bf16(v[j + 6], v[j + 7]);
+                *reinterpret_cast<uint4*>(ap + j) = pk;
+              }
+            } else {
+              for (int j = 0; j < 32 && nb + j < p.N; ++j) ap[j] = __float2bfloat16_rn(v[j]);
+            }
+          }
+          if (p.aux_mode == 2) {            // dX = (dY W) * act'(z)
+            const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (full_chunk || nb + j < p.N) v[j] *= act_grad_from_pre(p.act, __bfloat162float(ap[j]));
+          } else if (p.act != ACT_NONE) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = act_fwd_rt(p.act, v[j]);
+          }
+          if (p.out_f32) {
+            float* op = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + nb;
+            if (full_chunk) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              for (int j = 0; j < 32 && nb + j < p.N; ++j) op[j] = v[j];
+            }
+          } else {
+            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + nb;
+            if (full_chunk) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                uint4 pk;
+                pk.x = pack_bf16(v[j], v[j + 1]); pk.y = pack_bf16(v[j + 2], v[j + 3]);
+                pk.z = pack_bf16(v[j + 4], v[j + 5]); pk.w = pack_bf16(v[j + 6], v[j + 7]);
+                *reinterpret_cast<uint4*>(op + j) = pk;
+              }
+            } else {
+              for (int j = 0; j < 32 && nb + j < p.N; ++j) op[j] = __float2bfloat16_rn(v[j]);
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&tmem_empty[as]);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// ---- host side: TMA descriptors ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 tensor [outer][inner] with row stride `ld` elements, box {box_inner, box_outer}, 128-byte swizzle.
+static int make_tmap(CUtensorMap* out, const void* base, long long inner, long long outer, long long ld, int box_inner,
+                     int box_outer) {
+  EncodeTiledFn enc = get_encode();
+  MLT_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  MLT_REQUIRE(((uintptr_t)base % 16) == 0 && (ld * 2) % 16 == 0,
+              "TMA needs a 16-byte aligned base and a row stride that is a multiple of 8 bf16 elements (ld=%lld)", ld);
+  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  MLT_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%lld outer=%lld ld=%lld box=%dx%d)",
+              (int)r, inner, outer, ld, box_inner, box_outer);
+  return 0;
+}
+
+template <int BN>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  using Cfg = GemmCfg<BN>;
+  p.num_m = ceil_div(p.M, BM);
+  p.num_n = ceil_div(p.N, BN);
+  p.num_k = ceil_div(p.K, BK);
+  static bool attr_set[64] = {};             // function attributes are per device
+  auto kern = gemm_bf16_tcgen05_kernel<BN>;
+  int dev = 0;
+  MLT_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set[dev & 63] = true;
+  }
+  int grid = p.num_m * p.num_n;
+  if (grid > kNumSMs) grid = kNumSMs;
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace mlt
+
+using namespace mlt;
+
+// D[M,N] = A * B^T with fp32 accumulation.
+//   a_mn = 0: A is [M][K] (row stride lda);   a_mn = 1: A is stored [K][M] (row stride lda)
+//   b_mn = 0: B is [N][K] (row stride ldb);   b_mn = 1: B is stored [K][N] (row stride ldb)
+extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out,
+                             long long ldo, int out_f32, int M, int N, int K, const void* bias, int bias_f32, int act,
+                             int aux_mode, void* aux, long long ld_aux, int block_n, void* stream) {
+  MLT_REQUIRE(M > 0 && N > 0 && K > 0, "mlt_gemm_bf16: empty problem (M=%d N=%d K=%d)", M, N, K);
+  MLT_REQUIRE(aux_mode == 0 || aux != nullptr, "mlt_gemm_bf16: aux_mode %d needs an aux tensor", aux_mode);
+  MLT_REQUIRE(((uintptr_t)out % 16) == 0 && (ldo * (out_f32 ? 4 : 2)) % 16 == 0, "mlt_gemm_bf16: output must be 16-byte aligned with a 16-byte multiple row pitch");
+  MLT_REQUIRE(aux_mode == 0 || (((uintptr_t)aux % 16) == 0 && (ld_aux * 2) % 16 == 0), "mlt_gemm_bf16: aux must be 16-byte aligned");
+  int BN = block_n;
+  if (BN == 0) BN = (N >= 512 || (N % 256 == 0)) ? 256 : (N > 64 ? 128 : 64);
+  MLT_REQUIRE(BN == 64 || BN == 128 || BN == 256, "mlt_gemm_bf16: block_n must be 0, 64, 128 or 256");
+  CUtensorMap tmA, tmB;
+  if (!a_mn) { if (make_tmap(&tmA, A, K, M, lda, BK, BM)) return 1; }
+  else       { if (make_tmap(&tmA, A, M, K, lda, 64, BK)) return 1; }
+  if (!b_mn) { if (make_tmap(&tmB, B, K, N, ldb, BK, BN)) return 1; }
+  else       { if (make_tmap(&tmB, B, N, K, ldb, 64, BK)) return 1; }
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.out = out; p.ldo = ldo; p.out_f32 = out_f32;
+  p.bias = bias; p.bias_f32 = bias_f32; p.act = act;
+  p.aux_mode = aux_mode; p.aux = aux; p.ld_aux = ld_aux;
+  p.a_mn = a_mn; p.b_mn = b_mn;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
+  if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
+  return launch_gemm<64>(tmA, tmB, p, st);
+}

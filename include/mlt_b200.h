@@ -76,6 +76,24 @@ int mlt_linear_small_fwd(const void* x, const void* w, const void* bias, void* y
 int mlt_linear_small_bwd(const void* dy, const void* y, const void* x, const void* w, void* dx, void* dw, void* db,
                          int B, int K, int N, int act, int accumulate, void* stream);
 
+/* ---- tensor-core GEMM: the cuBLAS calls behind nn.Linear (src/model.py:21-23) and every BERT / ResNet-FC GEMM ------ */
+/* D[M,N] = A * B^T on tcgen05 (bf16 in, fp32 accumulate in TMEM, TMA-fed), fused epilogue:
+ *   + bias[N] (fp32 or bf16), activation, aux_mode 1: also store the pre-activation (bf16) to aux,
+ *   aux_mode 2: multiply by act'(aux) instead (the dgrad-through-activation epilogue).
+ * a_mn = 0: A stored [M][K];  a_mn = 1: A stored [K][M].  b_mn = 0: B stored [N][K];  b_mn = 1: B stored [K][N].
+ * Row strides (elements) must be multiples of 8.  block_n: 0 = auto, or 64 / 128 / 256. */
+int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out,
+                  long long ldo, int out_f32, int M, int N, int K, const void* bias, int bias_f32, int act, int aux_mode,
+                  void* aux, long long ld_aux, int block_n, void* stream);
+
+/* ---- bandwidth-bound helpers around the GEMMs (ATen elementwise / sum kernels in the reference's backward) ------- */
+int mlt_act_backward(const void* dy, const void* saved, void* dz, long long n, int act, int from_pre, int is_bf16,
+                     void* stream);
+long long mlt_colsum_scratch_bytes(int M, int N);
+int mlt_colsum(const void* x, int x_bf16, void* out, int out_bf16, void* scratch, long long scratch_bytes, int M, int N,
+               long long ld, int accumulate, void* stream);
+int mlt_cast(const void* src, int src_bf16, void* dst, int dst_bf16, long long n, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

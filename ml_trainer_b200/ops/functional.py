@@ -300,3 +300,51 @@ def linear_act(x, weight, bias=None, act: Optional[str] = None):
 
         return linear_act_tc(x, weight, bias, act)
     return _torch_act(TF.linear(x, weight, bias), act)
+
+
+# ----------------------------------------------------------------------------------------------
+# helpers around the tensor-core GEMMs
+# ----------------------------------------------------------------------------------------------
+def act_backward(dy: torch.Tensor, saved: torch.Tensor, act: str, from_pre: bool) -> torch.Tensor:
+    """``dy * act'(.)`` where ``saved`` is the pre-activation (``from_pre``) or the activation output."""
+    if use_native(dy, saved) and dy.dtype in (torch.float32, torch.bfloat16) and dy.dtype == saved.dtype:
+        dy, saved = dy.contiguous(), saved.contiguous()
+        dz = torch.empty_like(dy)
+        check(_lib.lib().mlt_act_backward(ptr(dy), ptr(saved), ptr(dz), _c_ll(dy.numel()), _c_int(ACT_IDS[act]),
+                                          _c_int(int(from_pre)), _c_int(int(dy.dtype == torch.bfloat16)), stream_handle()),
+              "mlt_act_backward")
+        launches.bump("act_backward")
+        return dz
+    s = saved.float()
+    if act == "relu":
+        g = (s > 0).float()
+    elif act == "tanh":
+        t = torch.tanh(s) if from_pre else s
+        g = 1 - t * t
+    elif act == "gelu":
+        g = 0.5 * (1 + torch.erf(s * 0.7071067811865476)) + s * torch.exp(-0.5 * s * s) * 0.3989422804014327
+    else:
+        g = torch.ones_like(s)
+    return (dy.float() * g).to(dy.dtype)
+
+
+def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Column sums of a 2-D tensor (bias gradient)."""
+    M, N = x.shape
+    if use_native(x) and x.dtype in (torch.float32, torch.bfloat16) and x.stride(1) == 1:
+        if out is None:
+            out = torch.empty(N, dtype=x.dtype, device=x.device)
+        L = _lib.lib()
+        L.mlt_colsum_scratch_bytes.restype = _c_ll
+        nbytes = L.mlt_colsum_scratch_bytes(_c_int(M), _c_int(N))
+        ws = scratch(x.device, "colsum", nbytes)
+        check(L.mlt_colsum(ptr(x), _c_int(int(x.dtype == torch.bfloat16)), ptr(out), _c_int(int(out.dtype == torch.bfloat16)),
+                           ptr(ws), _c_ll(ws.numel()), _c_int(M), _c_int(N), _c_ll(x.stride(0)), _c_int(0), stream_handle()),
+              "mlt_colsum")
+        launches.bump("colsum")
+        return out
+    r = x.float().sum(0)
+    if out is not None:
+        out.copy_(r)
+        return out
+    return r.to(x.dtype)

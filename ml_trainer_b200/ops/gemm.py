@@ -1,0 +1,119 @@
+"""tcgen05 GEMM front end (csrc/gemm_tcgen05.cu) and the tensor-core Linear autograd function.
+
+``gemm(a, b, a_mn, b_mn)`` computes ``D[M,N] = A @ B^T`` where each operand is given in its *storage* form:
+``a_mn=False`` -> ``a`` is ``[M,K]``; ``a_mn=True`` -> ``a`` is ``[K,M]`` (the reduction dim is the slow one).  Likewise
+``b`` is ``[N,K]`` or ``[K,N]``.  All three GEMMs of a linear layer map onto it without any transpose:
+
+    forward   Y  = X  W^T        gemm(X,  W,  False, False)
+    dgrad     dX = dY W          gemm(dY, W,  False, True)
+    wgrad     dW = dY^T X        gemm(dY, X,  True,  True)
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+import torch.nn.functional as TF
+
+from . import _lib
+from ._lib import check, launches, ptr, stream_handle
+
+_c_int, _c_ll = ctypes.c_int, ctypes.c_longlong
+ACT_IDS = {None: 0, "none": 0, "relu": 1, "gelu": 2, "tanh": 3}
+
+
+def gemm_supported(a: torch.Tensor, b: torch.Tensor) -> bool:
+    return (a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.dim() == 2 and b.dim() == 2
+            and a.stride(1) == 1 and b.stride(1) == 1 and a.stride(0) % 8 == 0 and b.stride(0) % 8 == 0
+            and a.data_ptr() % 16 == 0 and b.data_ptr() % 16 == 0)
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = False, out: Optional[torch.Tensor] = None,
+         out_dtype: torch.dtype = torch.bfloat16, bias: Optional[torch.Tensor] = None, act: Optional[str] = None,
+         aux_mode: int = 0, aux: Optional[torch.Tensor] = None, block_n: int = 0) -> torch.Tensor:
+    M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    if K != Kb:
+        raise ValueError(f"gemm: reduction dims differ ({K} vs {Kb})")
+    if out is None:
+        n_pad = (N + 7) // 8 * 8             # keep the row pitch a multiple of 16 bytes
+        full = torch.empty((M, n_pad), dtype=out_dtype, device=a.device)
+        out = full[:, :N] if n_pad != N else full
+    check(_lib.lib().mlt_gemm_bf16(ptr(a), _c_ll(a.stride(0)), _c_int(int(a_mn)), ptr(b), _c_ll(b.stride(0)),
+                                   _c_int(int(b_mn)), ptr(out), _c_ll(out.stride(0)), _c_int(int(out.dtype == torch.float32)),
+                                   _c_int(M), _c_int(N), _c_int(K), ptr(bias),
+                                   _c_int(int(bias is not None and bias.dtype == torch.float32)), _c_int(ACT_IDS[act]),
+                                   _c_int(aux_mode), ptr(aux), _c_ll(aux.stride(0) if aux is not None else 0),
+                                   _c_int(block_n), stream_handle()), "mlt_gemm_bf16")
+    launches.bump("gemm_bf16_tcgen05")
+    return out
+
+
+def gemm_reference(a, b, a_mn=False, b_mn=False, bias=None, act=None):
+    """fp32 PyTorch statement of :func:`gemm` (oracle)."""
+    A = a.float().t() if a_mn else a.float()
+    B = b.float().t() if b_mn else b.float()
+    d = A @ B.t()
+    if bias is not None:
+        d = d + bias.float()
+    if act == "relu":
+        d = TF.relu(d)
+    elif act == "gelu":
+        d = TF.gelu(d)
+    elif act == "tanh":
+        d = torch.tanh(d)
+    return d
+
+
+class _LinearTCFn(torch.autograd.Function):
+    """``act(x W^T + b)`` on tcgen05; backward = two more tcgen05 GEMMs + a column-sum for the bias."""
+
+    @staticmethod
+    def forward(ctx, x2, weight, bias, act, wparam, bparam):
+        need_pre = act in ("gelu", "tanh")
+        aux = torch.empty((x2.shape[0], weight.shape[0]), dtype=torch.bfloat16, device=x2.device) if need_pre else None
+        y = gemm(x2, weight, False, False, bias=bias, act=act, aux_mode=1 if need_pre else 0, aux=aux)
+        ctx.save_for_backward(x2, weight, aux if need_pre else y)
+        ctx.cfg = (act, bias is not None, need_pre)
+        ctx.params = (wparam, bparam)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .functional import _deliver, _sink, act_backward, colsum
+
+        x2, weight, saved = ctx.saved_tensors
+        act, has_bias, need_pre = ctx.cfg
+        wparam, bparam = ctx.params
+        dy = dy.contiguous()
+        dz = act_backward(dy, saved, act, from_pre=need_pre) if act not in (None, "none") else dy
+        dx = gemm(dz, weight, False, True) if ctx.needs_input_grad[0] else None
+        wsink = _sink(wparam)
+        dw = gemm(dz, x2, True, True, out=wsink if (wsink is not None and wsink.dtype in (torch.bfloat16, torch.float32)) else None,
+                  out_dtype=weight.dtype if weight.dtype == torch.bfloat16 else torch.float32)
+        gw = _deliver(wparam, dw, wsink)
+        gb = None
+        if has_bias:
+            bsink = _sink(bparam)
+            db = colsum(dz, out=bsink)
+            gb = _deliver(bparam, db, bsink)
+        return dx, gw, gb, None, None, None
+
+
+def linear_act_tc(x, weight, bias=None, act: Optional[str] = None):
+    """Tensor-core linear for bf16 activations/weights; anything else goes to the PyTorch statement."""
+    from .functional import _has_sink
+
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, x.shape[-1])
+    if not (gemm_supported(x2, weight) and weight.shape[0] % 8 == 0):
+        y = TF.linear(x, weight, bias)
+        from .functional import _torch_act
+
+        return _torch_act(y, act)
+    if _has_sink(weight):
+        y = _LinearTCFn.apply(x2, weight.detach(), None if bias is None else bias.detach(), act, weight, bias)
+    else:
+        y = _LinearTCFn.apply(x2, weight, bias, act, None, None)
+    return y.reshape(*lead, weight.shape[0])

@@ -1,0 +1,114 @@
+"""tcgen05 GEMM (csrc/gemm_tcgen05.cu) against fp32 torch.matmul, all operand-major combinations and tile widths."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def _operands(M, N, K, a_mn, b_mn, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    a = (torch.randn((K, M) if a_mn else (M, K), generator=g) * 0.5).to(torch.bfloat16).to(DEV)
+    b = (torch.randn((K, N) if b_mn else (N, K), generator=g) * 0.5).to(torch.bfloat16).to(DEV)
+    return a, b
+
+
+def _check(d, ref, K, what):
+    err = (d.float() - ref).abs().max().item()
+    tol = 2e-2 * max(1.0, ref.abs().max().item()) if d.dtype == torch.bfloat16 else 1e-3 * (K ** 0.5)
+    assert err <= tol, f"{what}: max abs err {err} > {tol}"
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, False), (True, True)])
+@pytest.mark.parametrize("block_n", [64, 128, 256])
+def test_gemm_majors_and_tiles(a_mn, b_mn, block_n):
+    from ml_trainer_b200.ops.gemm import gemm, gemm_reference
+
+    M, N, K = 256, 512, 320
+    a, b = _operands(M, N, K, a_mn, b_mn)
+    d = gemm(a, b, a_mn, b_mn, out_dtype=torch.float32, block_n=block_n)
+    torch.cuda.synchronize()
+    _check(d, gemm_reference(a, b, a_mn, b_mn), K, f"a_mn={a_mn} b_mn={b_mn} BN={block_n}")
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 64, 64), (100, 72, 40), (1000, 200, 136), (4096, 768, 768), (512, 3072, 768),
+                                   (333, 2304, 776), (16384, 768, 3072)])
+def test_gemm_shapes_with_tails(M, N, K):
+    from ml_trainer_b200.ops.gemm import gemm, gemm_reference
+
+    a, b = _operands(M, N, K, False, False, seed=1)
+    d = gemm(a, b, out_dtype=torch.bfloat16)
+    torch.cuda.synchronize()
+    _check(d, gemm_reference(a, b), K, f"{M}x{N}x{K}")
+
+
+@pytest.mark.parametrize("act", [None, "relu", "gelu", "tanh"])
+@pytest.mark.parametrize("bias_dtype", [torch.bfloat16, torch.float32])
+def test_gemm_epilogues(act, bias_dtype):
+    from ml_trainer_b200.ops.gemm import gemm, gemm_reference
+
+    M, N, K = 384, 256, 192
+    a, b = _operands(M, N, K, False, False, seed=2)
+    bias = torch.randn(N, device=DEV).to(bias_dtype)
+    aux = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+    d = gemm(a, b, bias=bias, act=act, aux_mode=1, aux=aux, out_dtype=torch.float32)
+    torch.cuda.synchronize()
+    _check(d, gemm_reference(a, b, bias=bias, act=act), K, f"act={act}")
+    _check(aux, gemm_reference(a, b, bias=bias), K, "pre-activation aux")
+
+
+def test_gemm_act_grad_epilogue():
+    from ml_trainer_b200.ops.gemm import gemm, gemm_reference
+
+    M, N, K = 256, 128, 128
+    a, b = _operands(M, N, K, False, False, seed=3)
+    z = torch.randn(M, N, device=DEV).to(torch.bfloat16)
+    d = gemm(a, b, act="gelu", aux_mode=2, aux=z, out_dtype=torch.float32)
+    zf = z.float().requires_grad_()
+    torch.nn.functional.gelu(zf).sum().backward()
+    _check(d, gemm_reference(a, b) * zf.grad, K, "gelu-grad epilogue")
+
+
+@pytest.mark.parametrize("act", [None, "relu", "gelu"])
+def test_linear_tc_fwd_bwd(act):
+    from ml_trainer_b200.ops import functional as F
+    from ml_trainer_b200.ops.gemm import linear_act_tc
+
+    torch.manual_seed(0)
+    B, K, N = 512, 256, 384
+    x = torch.randn(B, K, device=DEV).to(torch.bfloat16).requires_grad_()
+    w = (torch.randn(N, K, device=DEV) * 0.05).to(torch.bfloat16).requires_grad_()
+    b = torch.randn(N, device=DEV).to(torch.bfloat16).requires_grad_()
+    y = linear_act_tc(x, w, b, act)
+    xr, wr, br = (t.detach().float().requires_grad_() for t in (x, w, b))
+    ref = F._torch_act(torch.nn.functional.linear(xr, wr, br), act)
+    _check(y, ref.detach(), K, "linear fwd")
+    g = torch.randn_like(ref)
+    gx, gw, gb = torch.autograd.grad(y, (x, w, b), g.to(torch.bfloat16))
+    rx, rw, rb = torch.autograd.grad(ref, (xr, wr, br), g.to(torch.bfloat16).float())
+    _check(gx, rx, N, "dX")
+    _check(gw, rw, B, "dW")
+    _check(gb, rb, B, "db")
+
+
+def test_gemm_throughput_report():
+    """Not an assertion on speed: prints achieved TFLOP/s next to torch.matmul (cuBLAS) for the BERT-base shapes."""
+    from ml_trainer_b200.ops.gemm import gemm
+
+    rows = []
+    for (M, N, K) in [(16384, 768, 768), (16384, 2304, 768), (16384, 3072, 768), (16384, 768, 3072), (8192, 8192, 8192)]:
+        a, b = _operands(M, N, K, False, False)
+        out = torch.empty(M, N, dtype=torch.bfloat16, device=DEV)
+        for fn, name in ((lambda: gemm(a, b, out=out), "tcgen05"), (lambda: torch.matmul(a, b.t(), out=out), "cublas")):
+            for _ in range(3):
+                fn()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            for _ in range(10):
+                fn()
+            e.record()
+            torch.cuda.synchronize()
+            rows.append((M, N, K, name, 2.0 * M * N * K * 10 / (s.elapsed_time(e) * 1e-3) / 1e12))
+    for r in rows:
+        print("GEMM %6d x %5d x %5d  %-8s %8.1f TFLOP/s" % r)
