@@ -1,0 +1,445 @@
+// Fused gradient all-reduce + optimizer update over NVLink peer memory.
+// Replaces DDP's Reducer -> ncclAllReduce -> copy-back -> torch.optim chain behind reference
+// src/trainer.py:98,187-188 (and the dead _average_gradients at :152-158, whose semantics - SUM then divide by
+// world - are kept: the 1/world factor rides in hyper.grad_scale).
+//
+// Every rank maps every peer's symmetric arena (symm.cpp), so kernels address remote HBM with plain
+// ld/st.global over NVLink; the multicast mapping adds in-switch reduction (multimem.ld_reduce) and
+// broadcast (multimem.st).  Three variants, chosen per bucket size:
+//   one-shot   push: every CTA stores its chunk of local gradients into each peer's receive slot, raises a flag,
+//              waits for the peers' flags, reduces the N copies from LOCAL memory and updates the whole bucket
+//              redundantly.  One NVLink hop of latency; receive slots are double-buffered by step parity so no
+//              trailing barrier is needed.
+//   two-shot   reduce-scatter + all-gather: rank r pulls slice r of every peer's gradients, reduces, updates its
+//              1/N slice of master/state (ZeRO-1-like), then pushes the updated compute-dtype weights to all peers.
+//   NVLS       same ownership, but the reduction is one multimem.ld_reduce per vector (done in the NVSwitch) and the
+//              weight broadcast one multimem.st.
+// All reductions accumulate in fp32 in a fixed rank order, so every replica computes bit-identical weights.
+//
+// Synchronisation: per-CTA flags in the arena, written with st.release.sys and polled with ld.acquire.sys.  Flag
+// values are tickets that only grow (one counter per CTA lives beside the flags), so there is no reset phase and
+// CUDA-graph replays keep working.  A bounded spin turns a lost peer into a recorded diagnostic, not a hang.
+//
+// Testing on ONE GPU: gridDim.y emulates the ranks (rank = blockIdx.y, cooperative launch so that all CTAs are
+// co-resident); on real multi-GPU runs gridDim.y == 1 and rank comes from the context.
+#include "optim_rules.cuh"
+#include "../include/mlt_b200.h"
+#include <cooperative_groups.h>
+
+namespace mlt {
+
+constexpr int kMaxRanks = 8;
+constexpr int kMaxCtas = 512;            // flag rows per kind
+constexpr long long kSpinTimeoutCycles = 40LL * 1000 * 1000 * 1000;   // ~20 s at 2 GHz
+
+// Flag block layout (uint32 units), identical on every rank:
+//   sig[kind][cta][src_rank]   written by peers        kind 0 = "data pushed / grads ready", 1 = "done"
+//   tick[kind][cta]            local ticket counters
+//   err[8]                     first timeout diagnostic {code, rank, peer, cta, expected, seen}
+struct FlagBlock {
+  unsigned int sig[2][kMaxCtas][kMaxRanks];
+  unsigned int tick[2][kMaxCtas];
+  unsigned int err[8];
+};
+
+struct P2PArgs {
+  char* base[kMaxRanks];     // arena base of every rank, as mapped in this process
+  char* mc_base;             // multicast mapping (nullptr when NVLS is unavailable)
+  int world;
+  int rank;                  // rank of gridDim.y index 0
+  long long flags_off;       // FlagBlock offset in the arena
+  long long recv_off;        // one-shot receive slots: [parity][src][recv_slot_bytes]
+  long long recv_slot_bytes;
+  long long grad_off;        // bucket gradient slice offset in the arena (bytes)
+  long long model_off;       // bucket compute-dtype weight slice offset in the arena (bytes)
+  // per emulated rank (index blockIdx.y): local, non-symmetric optimizer state of the bucket slice
+  float* master[kMaxRanks];
+  float* s1[kMaxRanks];
+  float* s2[kMaxRanks];
+  const Hyper* hyper[kMaxRanks];
+  long long n;               // elements in the bucket (multiple of 128 by arena construction)
+  int model_is_master;       // fp32 compute: the arena weight slice IS the master (no separate shadow)
+};
+
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ FlagBlock* flags_of(const P2PArgs& a, int r) {
+  return reinterpret_cast<FlagBlock*>(a.base[r] + a.flags_off);
+}
+
+// Signal every peer's sig[kind][cta][me] with a fresh ticket, then wait until every peer's ticket reached it.
+// Must be called by all threads of the CTA (contains __syncthreads); data written before the call by any
+// thread of this CTA is visible to peers that observe the flag, and vice versa.
+__device__ __forceinline__ void cta_exchange(const P2PArgs& a, int me, int kind, int cta, bool do_signal = true, bool do_wait = true,
+                                             unsigned int* ticket_io = nullptr) {
+  __shared__ unsigned int s_ticket;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    FlagBlock* mine = flags_of(a, me);
+    unsigned int t;
+    if (do_signal) {
+      t = mine->tick[kind][cta] + 1;
+      mine->tick[kind][cta] = t;
+      __threadfence_system();
+      for (int p = 0; p < a.world; ++p)
+        if (p != me) st_release_sys(&flags_of(a, p)->sig[kind][cta][me], t);
+    } else {
+      t = *ticket_io;
+    }
+    s_ticket = t;
+  }
+  __syncthreads();
+  const unsigned int t = s_ticket;
+  if (ticket_io && threadIdx.x == 0) *ticket_io = t;
+  if (do_wait) {
+    if (threadIdx.x < a.world && (int)threadIdx.x != me) {
+      const unsigned int* f = &flags_of(a, me)->sig[kind][cta][threadIdx.x];
+      const long long t0 = clock64();
+      unsigned int seen;
+      while ((int)((seen = ld_acquire_sys(f)) - t) < 0) {
+        if (clock64() - t0 > kSpinTimeoutCycles) {
+          unsigned int* e = flags_of(a, me)->err;
+          if (atomicCAS(&e[0], 0u, 1u) == 0u) { e[1] = me; e[2] = threadIdx.x; e[3] = cta; e[4] = t; e[5] = seen; e[6] = kind; }
+          break;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- vector helpers: 8 (bf16) or 4 (fp32) elements per 16 bytes -------------------------------------------------
+template <typename G> struct Vec;
+template <> struct Vec<float> {
+  static constexpr int kElems = 4;
+  __device__ static void add(float (&acc)[8], const uint4& raw) {
+    acc[0] += __uint_as_float(raw.x); acc[1] += __uint_as_float(raw.y); acc[2] += __uint_as_float(raw.z); acc[3] += __uint_as_float(raw.w);
+  }
+};
+template <> struct Vec<__nv_bfloat16> {
+  static constexpr int kElems = 8;
+  __device__ static void add(float (&acc)[8], const uint4& raw) {
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[j]));
+      acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+    }
+  }
+};
+
+__device__ __forceinline__ uint4 ld_peer(const void* p) {      // peer HBM: bypass L1, nothing to keep
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer(void* p, const uint4& v) {
+  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// Apply rule R to kElems consecutive elements starting at element index i of this rank's bucket-local state.
+// `g` holds the summed gradients.  Writes master/state and returns the new weights in `pnew`.
+template <typename R, int E>
+__device__ __forceinline__ void update_elems(const P2PArgs& a, int slot, long long i, float (&g)[8], const Hyper& h, float (&pnew)[8]) {
+  float* master = a.master[slot];
+#pragma unroll
+  for (int j = 0; j < E; j += 4) {
+    float4 p = *reinterpret_cast<const float4*>(master + i + j);
+    float4 s = *reinterpret_cast<const float4*>(a.s1[slot] + i + j);
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (R::kStates > 1) t = *reinterpret_cast<const float4*>(a.s2[slot] + i + j);
+    const float4 gg = make_float4(g[j] * h.grad_scale, g[j + 1] * h.grad_scale, g[j + 2] * h.grad_scale, g[j + 3] * h.grad_scale);
+    update4<R>(p, gg, s, t, h);
+    *reinterpret_cast<float4*>(master + i + j) = p;
+    *reinterpret_cast<float4*>(a.s1[slot] + i + j) = s;
+    if (R::kStates > 1) *reinterpret_cast<float4*>(a.s2[slot] + i + j) = t;
+    pnew[j] = p.x; pnew[j + 1] = p.y; pnew[j + 2] = p.z; pnew[j + 3] = p.w;
+  }
+}
+
+template <typename G, int E>
+__device__ __forceinline__ uint4 pack_weights(const float (&p)[8]) {
+  uint4 o;
+  if (E == 4) {
+    o.x = __float_as_uint(p[0]); o.y = __float_as_uint(p[1]); o.z = __float_as_uint(p[2]); o.w = __float_as_uint(p[3]);
+  } else {
+    o.x = pack_bf16(p[0], p[1]); o.y = pack_bf16(p[2], p[3]); o.z = pack_bf16(p[4], p[5]); o.w = pack_bf16(p[6], p[7]);
+  }
+  return o;
+}
+
+// =====================================================================================================
+// K1: one-shot push all-reduce + update.  grid = (nblocks, emulated_ranks).
+// =====================================================================================================
+template <typename R, typename G>
+__global__ void __launch_bounds__(256)
+allreduce_oneshot_update_kernel(const P2PArgs a) {
+  constexpr int E = Vec<G>::kElems;
+  const int slot = blockIdx.y, me = a.rank + slot, cta = blockIdx.x;
+  const Hyper h = *a.hyper[slot];
+  const long long nvec = a.n / E;
+  const long long per_cta = ceil_div64(nvec, gridDim.x);
+  const long long v_lo = (long long)cta * per_cta, v_hi = min(nvec, v_lo + per_cta);
+  // step parity for the receive slots comes from the ticket this CTA is about to use
+  const unsigned int parity = (flags_of(a, me)->tick[0][cta] + 1) & 1u;
+  const char* my_grad = a.base[me] + a.grad_off;
+  // 1. push my chunk into slot [parity][me] of every peer
+  for (int p = 0; p < a.world; ++p) {
+    if (p == me) continue;
+    char* dst = a.base[p] + a.recv_off + ((long long)parity * a.world + me) * a.recv_slot_bytes;
+    for (long long v = v_lo + threadIdx.x; v < v_hi; v += blockDim.x)
+      st_peer(dst + v * 16, *reinterpret_cast<const uint4*>(my_grad + v * 16));
+  }
+  // 2. publish + wait for the same chunk from every peer
+  cta_exchange(a, me, 0, cta);
+  // 3. reduce in rank order from local memory, update, write weights
+  const char* recv = a.base[me] + a.recv_off + (long long)parity * a.world * a.recv_slot_bytes;
+  char* model = a.base[me] + a.model_off;
+  for (long long v = v_lo + threadIdx.x; v < v_hi; v += blockDim.x) {
+    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int p = 0; p < a.world; ++p) {
+      const uint4 raw = (p == me) ? *reinterpret_cast<const uint4*>(my_grad + v * 16)
+                                  : *reinterpret_cast<const uint4*>(recv + p * a.recv_slot_bytes + v * 16);
+      Vec<G>::add(g, raw);
+    }
+    float pnew[8];
+    update_elems<R, E>(a, slot, v * E, g, h, pnew);
+    if (!a.model_is_master) *reinterpret_cast<uint4*>(model + v * 16) = pack_weights<G, E>(pnew);
+  }
+}
+
+// =====================================================================================================
+// K2 / K3: reduce-scatter (pull, or multimem.ld_reduce) + update of the owned slice + all-gather of weights
+// (push, or multimem.st).  grid = (nblocks, emulated_ranks).  USE_MC selects the NVLS data path.
+// =====================================================================================================
+template <typename G> __device__ __forceinline__ void mc_ld_reduce(const void* mc, float (&g)[8]);
+template <> __device__ __forceinline__ void mc_ld_reduce<float>(const void* mc, float (&g)[8]) {
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(g[0]), "=f"(g[1]), "=f"(g[2]), "=f"(g[3]) : "l"(mc) : "memory");
+}
+template <> __device__ __forceinline__ void mc_ld_reduce<__nv_bfloat16>(const void* mc, float (&g)[8]) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc) : "memory");
+  for (int j = 0; j < 8; ++j) g[j] = 0.f;
+  Vec<__nv_bfloat16>::add(g, r);
+}
+__device__ __forceinline__ void mc_st(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               ::"l"(mc), "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+               : "memory");
+}
+
+template <typename R, typename G, bool USE_MC>
+__global__ void __launch_bounds__(256)
+allreduce_twoshot_update_kernel(const P2PArgs a) {
+  constexpr int E = Vec<G>::kElems;
+  const int slot = blockIdx.y, me = a.rank + slot, cta = blockIdx.x;
+  const Hyper h = *a.hyper[slot];
+  const long long nvec = a.n / E;
+  const long long per_rank = ceil_div64(nvec, a.world);
+  const long long r_lo = min(nvec, (long long)me * per_rank), r_hi = min(nvec, r_lo + per_rank);     // my slice
+  const long long per_cta = ceil_div64(r_hi - r_lo, gridDim.x);
+  const long long v_lo = min(r_hi, r_lo + (long long)cta * per_cta), v_hi = min(r_hi, v_lo + per_cta);
+  // 1. everyone's gradients are final (each rank's kernel runs after its backward on the same stream)
+  cta_exchange(a, me, 0, cta);
+  // 2. reduce my slice, update, scatter the new weights
+  for (long long v = v_lo + threadIdx.x; v < v_hi; v += blockDim.x) {
+    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (USE_MC) {
+      mc_ld_reduce<G>(a.mc_base + a.grad_off + v * 16, g);
+    } else {
+      for (int p = 0; p < a.world; ++p) {
+        const char* src = a.base[p] + a.grad_off + v * 16;
+        Vec<G>::add(g, p == me ? *reinterpret_cast<const uint4*>(src) : ld_peer(src));
+      }
+    }
+    float pnew[8];
+    update_elems<R, E>(a, slot, v * E, g, h, pnew);
+    const uint4 w = pack_weights<G, E>(pnew);
+    if (USE_MC) {
+      mc_st(a.mc_base + a.model_off + v * 16, w);               // in-switch broadcast, includes myself
+    } else {
+      for (int p = 0; p < a.world; ++p) {
+        if (p == me) { if (!a.model_is_master) *reinterpret_cast<uint4*>(a.base[me] + a.model_off + v * 16) = w; }
+        else st_peer(a.base[p] + a.model_off + v * 16, w);
+      }
+    }
+  }
+  // 3. all slices have landed everywhere, and nobody still reads my gradients
+  cta_exchange(a, me, 1, cta);
+}
+
+// =====================================================================================================
+// K5: broadcast (init parameter sync, BN buffer sync): root stores into every peer, then a flag exchange.
+// K6: small-vector all-reduce (loss / metric sums) and barrier: push into slot [me] of every peer, exchange, sum.
+// =====================================================================================================
+__global__ void __launch_bounds__(256)
+bcast_store_kernel(const P2PArgs a, long long off, long long nbytes, int root) {
+  const int slot = blockIdx.y, me = a.rank + slot, cta = blockIdx.x;
+  if (me == root) {
+    const long long nvec = nbytes / 16;
+    const char* src = a.base[me] + off;
+    for (int p = 0; p < a.world; ++p) {
+      if (p == me) continue;
+      char* dst = a.base[p] + off;
+      for (long long v = (long long)cta * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x)
+        st_peer(dst + v * 16, *reinterpret_cast<const uint4*>(src + v * 16));
+    }
+  }
+  cta_exchange(a, me, 1, cta);
+}
+
+// vals: per emulated rank, k floats in/out.  Uses the first k*4 bytes of every one-shot receive slot pair region
+// reserved for scalars (scalar_off), double-buffered by ticket parity like the one-shot kernel.
+__global__ void __launch_bounds__(32)
+reduce_scalars_kernel(const P2PArgs a, long long scalar_off, float* const* vals, int k) {
+  const int slot = blockIdx.y, me = a.rank + slot;
+  const unsigned int parity = (flags_of(a, me)->tick[0][kMaxCtas - 1] + 1) & 1u;
+  float* v = vals[slot];
+  for (int p = 0; p < a.world; ++p) {
+    float* dst = reinterpret_cast<float*>(a.base[p] + scalar_off) + ((long long)parity * a.world + me) * 32;
+    for (int j = threadIdx.x; j < k; j += 32) dst[j] = v[j];
+  }
+  cta_exchange(a, me, 0, kMaxCtas - 1);
+  const float* mine = reinterpret_cast<const float*>(a.base[me] + scalar_off) + (long long)parity * a.world * 32;
+  for (int j = threadIdx.x; j < k; j += 32) {
+    float s = 0.f;
+    for (int p = 0; p < a.world; ++p) s += mine[p * 32 + j];
+    v[j] = s;
+  }
+}
+
+}  // namespace mlt
+
+using namespace mlt;
+
+// Host-visible context mirrors P2PArgs' symmetric part (see include/mlt_b200.h).
+extern "C" long long mlt_p2p_flag_block_bytes(void) { return (long long)sizeof(FlagBlock); }
+
+static int fill_args(P2PArgs& a, const mlt_p2p_ctx* c, int ranks_here) {
+  MLT_REQUIRE(c->world >= 1 && c->world <= kMaxRanks, "p2p: world size %d out of range (1..%d)", c->world, kMaxRanks);
+  MLT_REQUIRE(ranks_here >= 1 && c->rank + ranks_here <= c->world, "p2p: bad emulated rank count %d", ranks_here);
+  for (int i = 0; i < kMaxRanks; ++i) a.base[i] = (char*)c->base[i];
+  a.mc_base = (char*)c->mc_base;
+  a.world = c->world;
+  a.rank = c->rank;
+  a.flags_off = c->flags_off;
+  a.recv_off = c->recv_off;
+  a.recv_slot_bytes = c->recv_slot_bytes;
+  return 0;
+}
+
+template <typename K>
+static int launch_maybe_coop(K kernel, dim3 grid, int threads, P2PArgs& a, int ranks_here, cudaStream_t st) {
+  if (ranks_here > 1) {       // single-GPU emulation: all CTAs must be co-resident because they wait for each other
+    void* params[] = {&a};
+    MLT_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)kernel, grid, dim3(threads), params, 0, st));
+  } else {
+    kernel<<<grid, threads, 0, st>>>(a);
+  }
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+// algo: 0 one-shot, 1 two-shot, 2 NVLS.  ranks_here > 1 only for the single-GPU emulation used by the tests.
+extern "C" int mlt_p2p_allreduce_update(const mlt_p2p_ctx* ctx, int algo, int rule, int grad_is_bf16, long long grad_off,
+                                        long long model_off, int model_is_master, void* const* master, void* const* s1,
+                                        void* const* s2, void* const* hyper, long long n, int nblocks, int ranks_here,
+                                        void* stream) {
+  P2PArgs a;
+  if (fill_args(a, ctx, ranks_here)) return 1;
+  MLT_REQUIRE(n > 0 && n % 8 == 0, "p2p: bucket length %lld must be a positive multiple of 8", n);
+  MLT_REQUIRE(grad_off % 16 == 0 && model_off % 16 == 0, "p2p: arena offsets must be 16-byte aligned");
+  MLT_REQUIRE(algo != 2 || ctx->mc_base != nullptr, "p2p: NVLS variant requested but no multicast mapping exists");
+  const long long bytes = n * (grad_is_bf16 ? 2 : 4);
+  MLT_REQUIRE(algo != 0 || bytes <= ctx->recv_slot_bytes, "p2p: one-shot bucket of %lld bytes exceeds the %lld-byte receive slot",
+              bytes, ctx->recv_slot_bytes);
+  a.grad_off = grad_off; a.model_off = model_off; a.n = n; a.model_is_master = model_is_master;
+  for (int i = 0; i < ranks_here; ++i) {
+    a.master[i] = (float*)master[i]; a.s1[i] = (float*)s1[i]; a.s2[i] = s2 ? (float*)s2[i] : nullptr;
+    a.hyper[i] = (const Hyper*)hyper[i];
+  }
+  if (nblocks <= 0) {
+    const long long vecs = n / (grad_is_bf16 ? 8 : 4) / (algo == 0 ? 1 : ctx->world);
+    nblocks = (int)ceil_div64(vecs, 256 * 4);        // ~4 vectors per thread
+    const int cap = algo == 0 ? 64 : 128;            // comm kernels share the GPU with backward: leave SMs for it
+    if (nblocks > cap) nblocks = cap;
+    if (nblocks < 1) nblocks = 1;
+  }
+  MLT_REQUIRE(nblocks <= kMaxCtas - 1, "p2p: at most %d CTAs per collective", kMaxCtas - 1);
+  dim3 grid(nblocks, ranks_here);
+  cudaStream_t st = (cudaStream_t)stream;
+  MLT_DISPATCH_RULE(rule, R, {
+    if (algo == 0) {
+      if (grad_is_bf16) return launch_maybe_coop(allreduce_oneshot_update_kernel<R, __nv_bfloat16>, grid, 256, a, ranks_here, st);
+      return launch_maybe_coop(allreduce_oneshot_update_kernel<R, float>, grid, 256, a, ranks_here, st);
+    } else if (algo == 1) {
+      if (grad_is_bf16) return launch_maybe_coop(allreduce_twoshot_update_kernel<R, __nv_bfloat16, false>, grid, 256, a, ranks_here, st);
+      return launch_maybe_coop(allreduce_twoshot_update_kernel<R, float, false>, grid, 256, a, ranks_here, st);
+    } else {
+      if (grad_is_bf16) return launch_maybe_coop(allreduce_twoshot_update_kernel<R, __nv_bfloat16, true>, grid, 256, a, ranks_here, st);
+      return launch_maybe_coop(allreduce_twoshot_update_kernel<R, float, true>, grid, 256, a, ranks_here, st);
+    }
+  });
+  return 0;
+}
+
+extern "C" int mlt_p2p_broadcast(const mlt_p2p_ctx* ctx, long long off, long long nbytes, int root, int ranks_here, void* stream) {
+  P2PArgs a;
+  if (fill_args(a, ctx, ranks_here)) return 1;
+  MLT_REQUIRE(off % 16 == 0 && nbytes % 16 == 0, "p2p broadcast: offset and size must be multiples of 16 bytes");
+  int nblocks = (int)ceil_div64(nbytes / 16, 256 * 8);
+  if (nblocks > 64) nblocks = 64;
+  if (nblocks < 1) nblocks = 1;
+  dim3 grid(nblocks, ranks_here);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (ranks_here > 1) {
+    void* params[] = {&a, &off, &nbytes, &root};
+    MLT_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bcast_store_kernel, grid, dim3(256), params, 0, st));
+  } else {
+    bcast_store_kernel<<<grid, 256, 0, st>>>(a, off, nbytes, root);
+  }
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+// vals_dev: device array of `ranks_here` pointers, each to k (<= 32) floats summed across ranks in place.
+extern "C" int mlt_p2p_reduce_scalars(const mlt_p2p_ctx* ctx, long long scalar_off, void* vals_dev, int k, int ranks_here,
+                                      void* stream) {
+  P2PArgs a;
+  if (fill_args(a, ctx, ranks_here)) return 1;
+  MLT_REQUIRE(k >= 1 && k <= 32, "p2p reduce_scalars: k=%d out of range (1..32)", k);
+  dim3 grid(1, ranks_here);
+  cudaStream_t st = (cudaStream_t)stream;
+  float* const* vals = (float* const*)vals_dev;
+  if (ranks_here > 1) {
+    void* params[] = {&a, &scalar_off, &vals, &k};
+    MLT_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)reduce_scalars_kernel, grid, dim3(32), params, 0, st));
+  } else {
+    reduce_scalars_kernel<<<grid, 32, 0, st>>>(a, scalar_off, vals, k);
+  }
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+// Reads (and clears) the timeout diagnostic of the local arena.  out6 = {code, rank, peer, cta, expected, seen}.
+extern "C" int mlt_p2p_check_error(const mlt_p2p_ctx* ctx, unsigned int* out6_host) {
+  unsigned int e[8];
+  char* fb = (char*)ctx->base[ctx->rank] + ctx->flags_off + offsetof(FlagBlock, err);
+  MLT_CHECK_CUDA(cudaMemcpy(e, fb, sizeof(e), cudaMemcpyDeviceToHost));
+  for (int i = 0; i < 6; ++i) out6_host[i] = e[i];
+  if (e[0] != 0) {
+    MLT_CHECK_CUDA(cudaMemset(fb, 0, sizeof(e)));
+    set_error("p2p: rank %u timed out waiting for peer %u (cta %u, kind %u): expected ticket %u, saw %u", e[1], e[2], e[3],
+              e[6], e[4], e[5]);
+    return 2;
+  }
+  return 0;
+}

@@ -94,6 +94,42 @@ int mlt_colsum(const void* x, int x_bf16, void* out, int out_bf16, void* scratch
                long long ld, int accumulate, void* stream);
 int mlt_cast(const void* src, int src_bf16, void* dst, int dst_bf16, long long n, void* stream);
 
+/* ---- communication runtime: replaces init_process_group + DistributedDataParallel (src/trainer.py:59,98) --------- */
+/* Symmetric arena: one VMM allocation per rank, exported as a POSIX fd, passed to the peers over unix sockets
+ * (SCM_RIGHTS) and mapped by every rank at its own address; optionally bound to an NVSwitch multicast object.
+ * Protocol (the caller supplies a barrier between phases, e.g. a gloo barrier):
+ *   h = mlt_symm_create(...)  | barrier | mlt_symm_exchange(h) | barrier |
+ *   mlt_symm_multicast_setup(h, phase 0) | barrier | (h, phase 1) | barrier | (h, phase 2) | barrier
+ * These calls allocate device memory (they are set-up, not hot path). */
+void* mlt_symm_create(int rank, int world, int device, long long bytes, const char* job_tag);
+int mlt_symm_exchange(void* handle);
+int mlt_symm_multicast_setup(void* handle, int phase);   /* returns 0 ok, >0 error, -1 multicast unsupported */
+void* mlt_symm_peer_ptr(void* handle, int peer);           /* arena base of `peer` as mapped in this process */
+void* mlt_symm_multicast_ptr(void* handle);                /* NULL when NVLS is unavailable */
+long long mlt_symm_bytes(void* handle);
+int mlt_symm_destroy(void* handle);
+
+typedef struct {
+  void* base[8];              /* arena base of every rank, as mapped in this process */
+  void* mc_base;              /* multicast mapping of the arena, or NULL */
+  int world, rank;
+  long long flags_off;        /* byte offset of the flag block (mlt_p2p_flag_block_bytes()) */
+  long long recv_off;         /* byte offset of the one-shot receive slots: [2][world][recv_slot_bytes] */
+  long long recv_slot_bytes;
+} mlt_p2p_ctx;
+
+long long mlt_p2p_flag_block_bytes(void);
+/* Fused all-reduce (mean via hyper.grad_scale) + optimizer update of one gradient bucket.
+ * algo 0 one-shot push | 1 two-shot P2P | 2 NVLS multimem.  grad/model offsets are byte offsets in the arena;
+ * master/s1/s2/hyper are arrays with one local pointer per rank handled by this launch (1 in production;
+ * `ranks_here` > 1 emulates several ranks on one GPU with a cooperative launch, for tests). */
+int mlt_p2p_allreduce_update(const mlt_p2p_ctx* ctx, int algo, int rule, int grad_is_bf16, long long grad_off,
+                             long long model_off, int model_is_master, void* const* master, void* const* s1,
+                             void* const* s2, void* const* hyper, long long n, int nblocks, int ranks_here, void* stream);
+int mlt_p2p_broadcast(const mlt_p2p_ctx* ctx, long long off, long long nbytes, int root, int ranks_here, void* stream);
+int mlt_p2p_reduce_scalars(const mlt_p2p_ctx* ctx, long long scalar_off, void* vals_dev, int k, int ranks_here, void* stream);
+int mlt_p2p_check_error(const mlt_p2p_ctx* ctx, unsigned int* out6_host);
+
 #ifdef __cplusplus
 }
 #endif

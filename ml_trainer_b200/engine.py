@@ -106,23 +106,23 @@ class StepEngine:
     def train_step(self, inputs, targets):
         opt = self.reducer.opt
         if not self.use_graph:
-            opt.begin_step()
+            opt.begin_step(self.reducer.grad_scale)
             self._train_body(inputs, targets)
             return
         key = (inputs.data_ptr(), targets.data_ptr(), tuple(inputs.shape), tuple(targets.shape))
         g = self._graphs.get(key)
         if g is not None:
-            opt.begin_step()
+            opt.begin_step(self.reducer.grad_scale)
             g.replay()
             self.graph_replays += 1
             return
         if self._eager_steps < WARMUP:
             self._eager_steps += 1
-            opt.begin_step()
+            opt.begin_step(self.reducer.grad_scale)
             self._train_body(inputs, targets)
             return
         # capture: hyper-parameters are uploaded outside the graph, everything else inside
-        opt.begin_step()
+        opt.begin_step(self.reducer.grad_scale)
         torch.cuda.synchronize(self.device)
         from .ops._lib import launches
 

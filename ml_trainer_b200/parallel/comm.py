@@ -39,6 +39,9 @@ class Comm:
     name: str = "local"
     fused: bool = False          # True when allreduce_update also applies the optimizer rule
 
+    def prepare(self, param_elems: int, compute_dtype: torch.dtype) -> None:
+        """Size any backend-owned memory for a model of ``param_elems`` (padded) parameters.  Collective."""
+
     # -- collectives ---------------------------------------------------------
     def all_reduce_mean(self, flat: torch.Tensor, stream=None) -> None:
         """In-place mean across ranks of a flat tensor."""
@@ -132,7 +135,7 @@ def init_process_group(backend: str, device: torch.device, timeout_s: int = 600)
     return torch_backend
 
 
-def make_comm(backend: str, device: torch.device, is_parallel: bool) -> Comm:
+def make_comm(backend: str, device: torch.device, is_parallel: bool, algo: str = "auto") -> Comm:
     """Build the communicator for ``backend``; initialises the process group when parallel."""
     if not is_parallel:
         return LocalComm()
@@ -143,7 +146,7 @@ def make_comm(backend: str, device: torch.device, is_parallel: bool) -> Comm:
     if backend in NATIVE_NAMES and device.type == "cuda":
         from .p2p import P2PComm
 
-        return P2PComm(device)
+        return P2PComm(device, algo=algo)
     if backend in NATIVE_NAMES:
         logger.info("native P2P backend needs CUDA; using gloo collectives on CPU")
         return TorchComm("gloo", device)

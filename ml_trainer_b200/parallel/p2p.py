@@ -1,0 +1,255 @@
+"""Native NVLink communicator: symmetric arena + fused P2P / NVLS all-reduce-update kernels.
+
+Replaces ``init_process_group(backend)`` + ``DistributedDataParallel`` (reference src/trainer.py:59,98).  The torch
+process group (gloo) is used only to agree on phases of the bootstrap; every byte of gradient and parameter
+traffic moves in kernels of ``csrc/comm_p2p.cu`` over memory mapped by ``csrc/symm.cpp``.
+
+Arena layout (identical offsets on every rank):
+    [flags]   per-CTA tickets/flags        (FlagBlock)
+    [scalars] 2 x world x 32 floats        (loss / metric reduction, double-buffered)
+    [recv]    2 x world x slot bytes       (one-shot receive slots, double-buffered)
+    [heap]    bump-allocated flat buffers  (gradients, compute-dtype weights, fp32 master)
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+from ..ops._lib import check, launches, ptr, stream_handle
+from ..optim.rules import RULE_IDS
+from ..utils.logging import get_logger
+from .comm import Comm
+
+logger = get_logger(__name__)
+
+ALGO_IDS = {"oneshot": 0, "twoshot": 1, "nvls": 2}
+_c_int, _c_ll, _c_vp = ctypes.c_int, ctypes.c_longlong, ctypes.c_void_p
+
+
+class P2PCtx(ctypes.Structure):
+    _fields_ = [("base", _c_vp * 8), ("mc_base", _c_vp), ("world", _c_int), ("rank", _c_int),
+                ("flags_off", _c_ll), ("recv_off", _c_ll), ("recv_slot_bytes", _c_ll)]
+
+
+class _DevMem:
+    """Zero-copy tensor view of raw device memory (``__cuda_array_interface__``)."""
+
+    def __init__(self, addr: int, nbytes: int, owner):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (addr, False), "version": 3}
+        self._owner = owner
+
+
+def _align(x: int, a: int) -> int:
+    return (x + a - 1) // a * a
+
+
+class SymmArena:
+    def __init__(self, rank: int, world: int, device: torch.device, nbytes: int, tag: str, group=None):
+        L = _lib.lib()
+        L.mlt_symm_create.restype = _c_vp
+        L.mlt_symm_peer_ptr.restype = _c_vp
+        L.mlt_symm_multicast_ptr.restype = _c_vp
+        L.mlt_symm_bytes.restype = _c_ll
+        self.L, self.rank, self.world, self.device, self.group = L, rank, world, device, group
+        self.h = L.mlt_symm_create(_c_int(rank), _c_int(world), _c_int(device.index), _c_ll(nbytes), tag.encode())
+        if not self.h:
+            raise RuntimeError(f"symmetric arena creation failed: {L.mlt_last_error().decode()}")
+        self.h = _c_vp(self.h)
+        self._barrier()
+        check(L.mlt_symm_exchange(self.h), "mlt_symm_exchange")
+        self._barrier()
+        self.multicast = False
+        if world > 1 and os.environ.get("MLT_DISABLE_NVLS", "0") != "1":
+            oks = []
+            for phase in (0, 1, 2):
+                rc = L.mlt_symm_multicast_setup(self.h, _c_int(phase))
+                if rc > 0:
+                    logger.warning(f"NVLS multicast setup failed in phase {phase}: {L.mlt_last_error().decode()}")
+                oks.append(rc == 0)
+                ok_all = self._all_true(rc == 0)
+                if not ok_all:
+                    break
+            else:
+                self.multicast = True
+        self.nbytes = int(L.mlt_symm_bytes(self.h))
+        self.bases: List[int] = [int(L.mlt_symm_peer_ptr(self.h, _c_int(p)) or 0) for p in range(world)]
+        self.mc_base = int(L.mlt_symm_multicast_ptr(self.h) or 0) if self.multicast else 0
+        self.base = self.bases[rank]
+        self._mem = torch.as_tensor(_DevMem(self.base, self.nbytes, self), device=device)
+
+    def _barrier(self):
+        if self.world > 1:
+            dist.barrier(group=self.group)
+
+    def _all_true(self, flag: bool) -> bool:
+        if self.world == 1:
+            return flag
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=self.group)
+        return bool(t.item())
+
+    def view(self, offset: int, numel: int, dtype: torch.dtype) -> torch.Tensor:
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        return self._mem[offset:offset + nbytes].view(dtype)
+
+    def offset_of(self, t: torch.Tensor) -> Optional[int]:
+        off = t.data_ptr() - self.base
+        return off if 0 <= off < self.nbytes else None
+
+    def close(self):
+        if self.h:
+            self._mem = None
+            self.L.mlt_symm_destroy(self.h)
+            self.h = None
+
+
+class P2PComm(Comm):
+    name = "p2p"
+    fused = True
+
+    def __init__(self, device: torch.device, oneshot_max_bytes: Optional[int] = None, algo: str = "auto"):
+        self.device = device
+        self.rank = dist.get_rank()
+        self.world_size = dist.get_world_size()
+        self.local_rank = int(os.environ.get("LOCAL_RANK", self.rank))
+        if self.world_size > 8:
+            raise RuntimeError("the native P2P backend covers one NVSwitch node (<= 8 GPUs)")
+        self.algo = algo
+        self.oneshot_max = int(oneshot_max_bytes or os.environ.get("MLT_ONESHOT_MAX_BYTES", 1 << 20))
+        self.cpu_group = dist.new_group(backend="gloo")      # host-side phases of the bootstrap only
+        self.arena: Optional[SymmArena] = None
+        self._heap = 0
+        self._vals = None
+        self.L = _lib.lib()
+        self.L.mlt_p2p_flag_block_bytes.restype = _c_ll
+
+    # ------------------------------------------------------------------ arena
+    def prepare(self, param_elems: int, compute_dtype: torch.dtype):
+        """Create the arena sized for ``param_elems`` parameters (collective; same arguments on every rank)."""
+        if self.arena is not None:
+            return
+        esize = 2 if compute_dtype == torch.bfloat16 else 4
+        flags = _align(int(self.L.mlt_p2p_flag_block_bytes()), 4096)
+        scalars = _align(2 * 8 * 32 * 4, 4096)
+        recv = 2 * self.world_size * self.oneshot_max
+        heap = param_elems * (4 + esize + (esize if compute_dtype == torch.bfloat16 else 0)) + (1 << 20)
+        self.flags_off, self.scalar_off = 0, flags
+        self.recv_off = flags + scalars
+        self.heap_off = self._heap = _align(self.recv_off + recv, 4096)
+        total = self.heap_off + _align(heap, 1 << 21)
+        tag = os.environ.get("MLT_JOB_TAG") or f"{os.environ.get('MASTER_PORT', '0')}-{os.getppid()}"
+        tags = [None] * self.world_size
+        dist.all_gather_object(tags, tag if self.rank == 0 else None, group=self.cpu_group)
+        tag = tags[0]
+        self.arena = SymmArena(self.rank, self.world_size, self.device, total, tag, group=self.cpu_group)
+        self.ctx = P2PCtx()
+        for p in range(8):
+            self.ctx.base[p] = self.arena.bases[p] if p < self.world_size else 0
+        self.ctx.mc_base = self.arena.mc_base or None
+        self.ctx.world, self.ctx.rank = self.world_size, self.rank
+        self.ctx.flags_off, self.ctx.recv_off, self.ctx.recv_slot_bytes = self.flags_off, self.recv_off, self.oneshot_max
+        logger.info(f"symmetric arena: {total >> 20} MiB per rank, multicast={'yes' if self.arena.multicast else 'no'}")
+
+    def alloc(self, numel, dtype, device):
+        if self.arena is None:
+            raise RuntimeError("P2PComm.prepare() must run before buffers are allocated")
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        off = _align(self._heap, 256)
+        if off + nbytes > self.arena.nbytes:
+            raise RuntimeError("symmetric arena exhausted")
+        self._heap = off + nbytes
+        return self.arena.view(off, numel, dtype)        # arena memory is zero-filled at creation
+
+    # ------------------------------------------------------------ collectives
+    def pick_algo(self, nbytes: int) -> str:
+        if self.algo != "auto":
+            if self.algo == "nvls" and not self.arena.multicast:
+                return "twoshot"               # no multicast object on this node: same ownership, P2P data path
+            return self.algo
+        if nbytes <= self.oneshot_max and nbytes <= (256 << 10):
+            return "oneshot"
+        return "nvls" if self.arena.multicast else "twoshot"
+
+    def allreduce_update(self, opt, lo: int, hi: int, stream=None):
+        n = hi - lo
+        gsz = opt.grad.element_size()
+        algo = self.pick_algo(n * gsz)
+        if algo == "oneshot" and n * gsz > self.oneshot_max:
+            algo = "nvls" if self.arena.multicast else "twoshot"
+        grad_off = self.arena.offset_of(opt.grad) + lo * gsz
+        model_off = self.arena.offset_of(opt.model) + lo * opt.model.element_size()
+        one = lambda t: (_c_vp * 1)(t.data_ptr() if t is not None else 0)
+        s2 = opt.s2[lo:hi] if opt.s2.numel() > 1 else None
+        check(self.L.mlt_p2p_allreduce_update(
+            ctypes.byref(self.ctx), _c_int(ALGO_IDS[algo]), _c_int(RULE_IDS[opt.kind]),
+            _c_int(int(opt.grad.dtype == torch.bfloat16)), _c_ll(grad_off), _c_ll(model_off),
+            _c_int(int(opt.model is opt.master)), one(opt.master[lo:hi]), one(opt.s1[lo:hi]), one(s2), one(opt.hyper),
+            _c_ll(n), _c_int(0), _c_int(1), stream_handle(stream)), "mlt_p2p_allreduce_update")
+        launches.bump(f"p2p_allreduce_update_{algo}")
+
+    def all_reduce_mean(self, flat, stream=None):
+        """Unfused mean all-reduce (API parity with the reference's ``_average_gradients``): library collective."""
+        if self.world_size == 1:
+            return
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+        flat.div_(self.world_size)
+
+    def broadcast(self, tensor, src=0):
+        if self.world_size == 1:
+            return
+        off = self.arena.offset_of(tensor)
+        nbytes = tensor.numel() * tensor.element_size()
+        if off is not None and off % 16 == 0 and nbytes % 16 == 0 and tensor.is_contiguous():
+            check(self.L.mlt_p2p_broadcast(ctypes.byref(self.ctx), _c_ll(off), _c_ll(nbytes), _c_int(src), _c_int(1),
+                                           stream_handle()), "mlt_p2p_broadcast")
+            launches.bump("p2p_broadcast")
+            return
+        # tensors outside the arena (module buffers): bounce through the first receive slot
+        stage_bytes = _align(nbytes, 16)
+        if stage_bytes > self.oneshot_max:
+            dist.broadcast(tensor, src=src)
+            return
+        stage = self.arena.view(self.recv_off, stage_bytes, torch.uint8)
+        flat = tensor.contiguous().view(-1).view(torch.uint8)
+        stage[:nbytes].copy_(flat)
+        check(self.L.mlt_p2p_broadcast(ctypes.byref(self.ctx), _c_ll(self.recv_off), _c_ll(stage_bytes), _c_int(src),
+                                       _c_int(1), stream_handle()), "mlt_p2p_broadcast")
+        launches.bump("p2p_broadcast")
+        tensor.copy_(stage[:nbytes].view(tensor.dtype).view(tensor.shape))
+        # peers must not reuse the slot before everyone copied out
+        torch.cuda.current_stream().synchronize()
+        dist.barrier(group=self.cpu_group)
+
+    def reduce_scalars(self, values):
+        if self.world_size == 1:
+            return values
+        k = values.numel()
+        if self._vals is None:
+            self._vals = torch.zeros(32, dtype=torch.float32, device=self.device)
+            self._vals_ptr = torch.tensor([self._vals.data_ptr()], dtype=torch.int64, device=self.device)
+        self._vals[:k].copy_(values.float().view(-1))
+        check(self.L.mlt_p2p_reduce_scalars(ctypes.byref(self.ctx), _c_ll(self.scalar_off), ptr(self._vals_ptr), _c_int(k),
+                                            _c_int(1), stream_handle()), "mlt_p2p_reduce_scalars")
+        launches.bump("p2p_reduce_scalars")
+        return self._vals[:k].clone().view(values.shape)
+
+    def barrier(self):
+        if self.world_size > 1:
+            torch.cuda.current_stream().synchronize()
+            dist.barrier(group=self.cpu_group)
+
+    def check_errors(self):
+        out = (ctypes.c_uint * 6)()
+        check(self.L.mlt_p2p_check_error(ctypes.byref(self.ctx), out), "mlt_p2p_check_error")
+
+    def close(self):
+        if self.arena is not None:
+            torch.cuda.synchronize(self.device)
+            self.barrier()
+            self.arena.close()
+            self.arena = None

@@ -73,6 +73,8 @@ class Reducer:
         self.opt = optimizer
         self.comm = comm or LocalComm()
         self.world = self.comm.world_size
+        # fused backends fold the 1/world of the mean into the update kernel; others divide in all_reduce_mean
+        self.grad_scale = 1.0 / self.world if (self.world > 1 and self.comm.fused) else 1.0
         esize = optimizer.grad.element_size()
         sizes = [n * esize for n in optimizer.sizes]
         cap = int(bucket_mb * 2 ** 20)
@@ -118,7 +120,7 @@ class Reducer:
     # ------------------------------------------------------------- step cycle
     def begin_step(self):
         """Arm the buckets and publish this step's hyper-parameters (eager convenience)."""
-        self.opt.begin_step(grad_scale=1.0)
+        self.opt.begin_step(grad_scale=self.grad_scale)
         self.arm()
 
     def arm(self):

@@ -96,7 +96,7 @@ class Trainer:
         else:
             self.device = torch.device("cpu")
         logger.info(f"Training on device: {self.device}.")
-        self.comm: Comm = make_comm(cfg.backend, self.device, is_parallel) if is_parallel else LocalComm()
+        self.comm: Comm = make_comm(cfg.backend, self.device, is_parallel, algo=cfg.comm_algo) if is_parallel else LocalComm()
         self.rank, self.world_size = self.comm.rank, self.comm.world_size
 
         # ---- data
@@ -139,6 +139,8 @@ class Trainer:
         self.compute_dtype = {"fp32": torch.float32, "bf16": torch.bfloat16}[cfg.dtype]
         self.criterion = self._get_criterion()
         self.pred_function = self._get_prediction_function()
+        padded = sum((p.numel() + 127) // 128 * 128 for p in self.model.parameters() if p.requires_grad)
+        self.comm.prepare(padded, self.compute_dtype)
         self.optimizer = self._get_optimizer()
         if self.world_size > 1:
             self._sync_initial_state()

@@ -15,13 +15,16 @@ from ml_trainer_b200 import Loader, MLModel, SyntheticDataset, Trainer  # noqa: 
 
 
 def main():
+    torch.backends.cudnn.allow_tf32 = False          # the DDP oracle must be plain fp32
+    torch.backends.cuda.matmul.allow_tf32 = False
     out_dir, optimizer = sys.argv[1], sys.argv[2]
     backend = sys.argv[3] if len(sys.argv) > 3 else "gloo"
     tr = SyntheticDataset((3, 32, 32), 10, length=128, seed=11)
     va = SyntheticDataset((3, 32, 32), 10, length=64, seed=12)
     torch.manual_seed(32)
     t = Trainer(MLModel(), datasets=(tr, va), epochs=2, batch_size=32, is_parallel=True, save_history=True,
-                model_dir=out_dir, backend=backend, optimizer=optimizer, lr=0.01, progress=False, metric="accuracy")
+                model_dir=out_dir, backend=backend, optimizer=optimizer, lr=0.01, progress=False, metric="accuracy",
+                comm_algo=os.environ.get("MLT_COMM_ALGO", "auto"))
     rank, world = dist.get_rank(), dist.get_world_size()
     assert t.batch_size == 32 // world
     assert len(t.train_loader.sampler) == 128 // world
