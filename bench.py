@@ -159,49 +159,49 @@ def run_ours(a):
     cfg = MODEL_CFG[a.model]
     gb = a.batch or cfg["batch"]
     K, W = a.steps, max(a.warmup, 3)
-    train, val = make_datasets(a.model, gb, K + W + 8, a.seq_len)
+    warm, val = make_datasets(a.model, gb, W + 4, a.seq_len, seed=7)
+    timed, _ = make_datasets(a.model, gb, K, a.seq_len)
     model = build_model(a.model)
-    tr = Trainer(model, datasets=(train, val), epochs=1, batch_size=gb, is_parallel=world > 1,
+    tr = Trainer(model, datasets=(warm, val), epochs=1, batch_size=gb, is_parallel=world > 1,
                  optimizer=a.optimizer or cfg["optimizer"], lr=cfg["lr"], momentum=0.9, metric=a.metric,
                  dtype=cfg["dtype"], backend=a.backend or "p2p", graph=not a.no_graph, progress=False,
                  model_dir=os.path.join("/tmp", f"mlt_bench_{os.getpid()}"), seed=32)
     per_rank = tr.batch_size
     eng = tr.engine
-    tr.model.train()
+    # warm-up through the public epoch loop: module load, graph capture, native executor set-up, comm bootstrap
+    tr.train_epoch(1)
+    barrier_sync(dev)
 
     # ---- (1) device-timed steps, inputs already on the device --------------------------------------
+    tr.model.train()
     feed = iter(tr._feed(tr.train_loader))
-    slots = []
-    for _ in range(max(tr.cfg.prefetch, 1)):
-        x, y = next(feed)
-        slots.append((x, y))
-    for i in range(W + 4):                       # eager warm-up + graph capture per slot
-        x, y = slots[i % len(slots)]
-        eng.train_step(x, y)
-    flush = None if a.no_flush else torch.empty(256 * 2 ** 20, dtype=torch.uint8, device=dev)
+    slots = [next(feed) for _ in range(2)]
+    for i in range(4):
+        eng.train_step(*slots[i % 2])
+    # The flush must outlast the host's enqueue of the next step, otherwise the event pair would time host latency.
+    flush = None if a.no_flush else torch.empty(1 << 30, dtype=torch.uint8, device=dev)
     barrier_sync(dev)
     _lib.launches.reset()
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
-    n_before = _lib.launches.n
+    replays0 = eng.graph_replays
     for i in range(K):
-        x, y = slots[i % len(slots)]
+        x, y = slots[i % 2]
         if flush is not None:
-            flush.fill_(i & 0xFF)                # evict L2 (256 MiB > 126 MB); not timed
+            flush.fill_(i & 0xFF)                # evict L2 (1 GiB >> 126 MB); not timed
         ev[i][0].record()
         eng.train_step(x, y)
         ev[i][1].record()
     barrier_sync(dev)
-    dev_ms = sum(s.elapsed_time(e) for s, e in ev)
-    dev_ms = reduce_max(dev_ms, dev)
-    eager_launches = _lib.launches.n - n_before
-    launches_per_step = getattr(eng, "launches_per_step", None)
-    gpu_launches = eager_launches + (launches_per_step or 0) * eng.graph_replays_since(K)
+    dev_ms = reduce_max(sum(s.elapsed_time(e) for s, e in ev), dev)
+    gpu_launches = _lib.launches.n + eng.launches_per_step * (eng.graph_replays - replays0 if eng.use_graph and eng.fused is None else 0)
+    by_kernel = dict(_lib.launches.by_name)
+    del flush
 
-    # ---- (2) end to end through the Trainer loop: pinned H2D every step + D2H of the loss ----------
-    e2e = run_e2e_ours(tr, K, W, dev)
+    # ---- (2) end to end through the Trainer's public epoch loop ------------------------------------
+    e2e = run_e2e_ours(tr, timed, K, dev, world, rank)
     clk = clocks.stop() if rank == 0 else None
     tr.close()
     if rank != 0:
@@ -216,45 +216,47 @@ def run_ours(a):
         "config": {"model": a.model, "global_batch": gb, "per_rank_batch": per_rank,
                    "seq_len": a.seq_len if a.model == "bert_base" else None,
                    "parallelism": f"dp{world}", "optimizer": a.optimizer or cfg["optimizer"], "metric": a.metric,
-                   "cuda_graph": eng.use_graph, "comm": tr.comm.name,
-                   "l2": "no flush" if flush is None else "256 MiB fill before every timed step, excluded from timing"},
-        "e2e": e2e, "gpu_launches": int(gpu_launches), "launches_by_kernel": dict(_lib.launches.by_name),
+                   "step": "single fused kernel" if eng.fused is not None else ("cuda graph" if eng.use_graph else "eager"),
+                   "comm": tr.comm.name,
+                   "l2": "no flush" if a.no_flush else "1 GiB fill before every timed step, excluded from timing"},
+        "e2e": e2e, "gpu_launches": int(gpu_launches), "launches_by_kernel": by_kernel,
         "clocks": clk,
     }
     print(json.dumps(out), flush=True)
 
 
-def run_e2e_ours(tr, K, W, dev):
-    """K steps of the Trainer's own epoch loop: loader -> pinned staging -> H2D -> step -> D2H loss."""
+def run_e2e_ours(tr, timed, K, dev, world, rank):
+    """K steps of Trainer.train_epoch: host dataset -> pinned staging -> H2D -> step -> D2H of the loss, every step."""
     import torch
+    from torch.utils.data import distributed as tud
 
-    eng = tr.engine
-    feed = tr._feed(tr.train_loader)
-    loss_host = torch.zeros(K + W + 8, dtype=torch.float32).pin_memory()
-    it = iter(feed)
-    for i in range(W):
-        x, y = next(it)
-        eng.train_step(x, y)
-        loss_host[i].copy_(eng.last_loss, non_blocking=True)
+    from ml_trainer_b200 import Loader
+
+    sampler = tud.DistributedSampler(timed, num_replicas=world, rank=rank) if world > 1 else None
+    tr.train_sampler = sampler
+    tr.train_loader = Loader(timed, batch_size=tr.batch_size, shuffle=sampler is None, sampler=sampler,
+                             pin_memory=True, num_workers=0)
     barrier_sync(dev)
-    h2d0 = feed.h2d_bytes
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     s.record()
-    for i in range(K):
-        x, y = next(it)
-        eng.train_step(x, y)
-        loss_host[W + i].copy_(eng.last_loss, non_blocking=True)     # D2H read of the step's loss, every step
+    tr.train_epoch(2)
     e.record()
     barrier_sync(dev)
     wall_ms = (time.perf_counter() - t0) * 1e3
     ms = reduce_max(max(s.elapsed_time(e), 0.0), dev)
+    wall_ms = reduce_max(wall_ms, dev)
+    steps = len(tr.train_loader)
+    st = getattr(tr, "last_native_stats", {}) or {}
+    losses = tr.last_step_losses
     gb = tr.global_batch_size
-    return {"value": round(gb * K / (ms / 1e3), 2), "unit": "samples/s", "ms_per_step": round(ms / K, 5),
-            "wall_ms_per_step": round(wall_ms / K, 5),
-            "h2d_bytes_per_step": int((feed.h2d_bytes - h2d0) / max(K - 0, 1)), "d2h_bytes_per_step": 4,
-            "api": "Trainer (ml_trainer_b200.trainer) epoch loop: Loader -> PinnedPrefetcher -> StepEngine",
-            "final_loss": float(loss_host[W + K - 1])}
+    return {"value": round(gb * steps / (ms / 1e3), 2), "unit": "samples/s", "ms_per_step": round(ms / steps, 5),
+            "wall_ms_per_step": round(wall_ms / steps, 5), "steps": steps,
+            "h2d_bytes_per_step": int(st.get("h2d_bytes", 0) / max(steps, 1)),
+            "d2h_bytes_per_step": int(st.get("d2h_bytes", 0) / max(steps, 1)),
+            "api": "Trainer.train_epoch (what fit() runs): in-memory dataset -> pinned staging -> copy-stream H2D -> step",
+            "executor": "native C++ epoch executor" if tr._native_ok(tr.train_loader, tr.model) else "python loop + PinnedPrefetcher",
+            "final_loss": float(losses[steps - 1]) if losses is not None else None}
 
 
 # --------------------------------------------------------------------------------------------------

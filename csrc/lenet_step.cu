@@ -1,0 +1,606 @@
+// Whole training step of the reference model in ONE kernel (reference src/model.py:7-24 + src/trainer.py:181-188).
+//
+// The reference's MLModel step is ~0.13 GFLOP spread over ~60 library launches plus host syncs: pure launch latency.
+// Here forward, loss, accuracy, backward, the cross-GPU gradient all-reduce and the optimizer update are one
+// cooperative kernel with a single grid barrier:
+//
+//   phase A  one CTA per sample, everything in shared memory: conv1+ReLU+pool -> conv2+ReLU+pool -> fc1 -> fc2 -> fc3
+//            -> softmax cross-entropy -> dlogits -> fc backward (data) -> conv2 dgrad; the per-sample convolution
+//            weight-gradient partials and the small per-sample vectors the fc weight gradients need are written to a
+//            global scratch slab (3696 floats per sample, L2 resident).
+//   barrier  sense-reversing grid barrier (co-residency guaranteed by the cooperative launch).
+//   phase B  every thread owns fixed elements of the flat parameter arena: it reduces that element's gradient over
+//            the batch, (multi-GPU) pushes it into every peer's receive slot over NVLink, exchanges per-CTA flags,
+//            sums the ranks in a fixed order, and applies the optimizer rule in registers.  CTA 0 also folds the
+//            loss / accuracy of the batch into the trainer's device accumulators.
+//
+// Numerics are fp32 throughout, same formulas as the layer kernels in small_nn.cu / loss.cu (the tested oracle).
+#include "p2p_device.cuh"
+#include "../include/mlt_b200.h"
+
+namespace mlt {
+
+namespace lenet {
+constexpr int CIN = 3, H = 32, C1 = 6, K = 5, O1 = 28, P1 = 14, C2 = 16, O2 = 10, P2 = 5;
+constexpr int FLAT = C2 * P2 * P2;          // 400
+constexpr int F1 = 120, F2 = 84, NC = 10;
+constexpr int XN = CIN * H * H;             // 3072
+constexpr int A1N = C1 * P1 * P1;           // 1176
+constexpr int W1N = C1 * CIN * K * K;       // 450
+constexpr int W2N = C2 * C1 * K * K;        // 2400
+constexpr int ZH = O2 + 2 * (K - 1);        // 18: haloed conv2-output gradient plane
+// per-sample scratch slab (floats)
+constexpr int S_A2 = 0, S_Z1 = 400, S_Z2 = 520, S_DL = 604 /*10 dlogits, loss, correct*/, S_D2 = 616, S_D1 = 700;
+constexpr int S_PW1 = 824 /*450 w + 6 b*/, S_PW2 = 1280 /*2400 w + 16 b*/, S_STRIDE = 3696;
+// parameter ids in module registration order
+enum { P_C1W, P_C1B, P_C2W, P_C2B, P_F1W, P_F1B, P_F2W, P_F2B, P_F3W, P_F3B, NPARAM };
+__device__ __constant__ int kParamSize[NPARAM] = {W1N, C1, W2N, C2, F1 * FLAT, F1, F2 * F1, F2, NC * F2, NC};
+constexpr int kThreads = 1024;             // 32 warps: the per-sample CTA is latency bound, it needs the warps
+constexpr int NW = kThreads / 32;
+constexpr int kMaxPerThread = 8;            // arena elements owned per thread in phase B
+}  // namespace lenet
+
+struct LeNetArgs {
+  float* master;                 // flat fp32 parameter arena (model == master for fp32 compute)
+  float* s1;
+  float* s2;
+  const Hyper* hyper;
+  long long numel;               // padded arena length
+  long long off[lenet::NPARAM];  // arena element offset of each parameter
+  const float* x;                // [B,3,32,32]
+  const long long* y;            // [B]
+  int B;
+  int train;                     // 0: forward + loss only
+  int want_acc;
+  float* scratch;                // B * S_STRIDE floats
+  unsigned int* sync;            // {count, sense}, zero-initialised once
+  float* acc3;                   // {loss_sum, metric_sum, steps} or nullptr
+  float* loss_out;               // scalar or nullptr
+  P2PArgs comm;                  // world == 1: no communication
+};
+
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void grid_barrier(unsigned int* sync, unsigned int nblocks, unsigned int sense0) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int old = atomicAdd(&sync[0], 1u);
+    if (old == nblocks - 1) {
+      sync[0] = 0u;
+      __threadfence();
+      atomicExch(&sync[1], sense0 + 1u);
+    } else {
+      while (ld_acquire_gpu(&sync[1]) == sense0) {
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float dot4(const float4& a, const float4& b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+
+template <typename R>
+__global__ void __launch_bounds__(lenet::kThreads, 1)
+lenet_step_kernel(const LeNetArgs a) {
+  using namespace lenet;
+  extern __shared__ __align__(16) float sm[];
+  float* xs = sm;                       // 3072
+  float* w1s = xs + XN;                 // 456
+  float* a1s = w1s + 456;               // 1176
+  float* w2s = a1s + A1N;               // 2416
+  float* a2s = w2s + 2416;              // 400
+  float* z1s = a2s + FLAT;              // 120
+  float* z2s = z1s + F1;                // 84 (+4 pad)
+  float* lgs = z2s + 88;                // 16
+  float* dls = lgs + 16;                // 16
+  float* d2s = dls + 16;                // 84 (+4)
+  float* d1s = d2s + 88;                // 120
+  float* g2p = d1s + F1;                // 400
+  float* g1p = g2p + FLAT;              // 1176
+  float* dz2 = g1p + A1N;               // 16*18*18 = 5184 used by dgrad; 6400 reserved (reduction scratch)
+  float* dgp = dz2 + 6400;              // 4 x 1176 partial sums of the conv2 dgrad
+  int* offs1 = reinterpret_cast<int*>(dgp + 4 * A1N);        // 1176
+  int* offs2 = offs1 + A1N;                                  // 400
+  unsigned char* idx1 = reinterpret_cast<unsigned char*>(offs2 + FLAT);   // 1176
+  unsigned char* idx2 = idx1 + A1N;                                       // 400
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ unsigned int s_sense;
+  if (tid == 0) s_sense = ld_acquire_gpu(&a.sync[1]);
+
+  const float* Wc1 = a.master + a.off[P_C1W];
+  const float* Bc1 = a.master + a.off[P_C1B];
+  const float* Wc2 = a.master + a.off[P_C2W];
+  const float* Bc2 = a.master + a.off[P_C2B];
+  const float* Wf1 = a.master + a.off[P_F1W];
+  const float* Bf1 = a.master + a.off[P_F1B];
+  const float* Wf2 = a.master + a.off[P_F2W];
+  const float* Bf2 = a.master + a.off[P_F2B];
+  const float* Wf3 = a.master + a.off[P_F3W];
+  const float* Bf3 = a.master + a.off[P_F3B];
+
+  if ((int)blockIdx.x < a.B) {        // this CTA has at least one sample: stage the conv filters once
+    for (int i = tid; i < W1N; i += kThreads) w1s[i] = Wc1[i];
+    if (tid < C1) w1s[W1N + tid] = Bc1[tid];
+    for (int i = tid; i < W2N; i += kThreads) w2s[i] = Wc2[i];
+    if (tid < C2) w2s[W2N + tid] = Bc2[tid];
+  }
+  const float inv_B = 1.0f / (float)a.B;
+
+  // =========================================== phase A ===========================================
+  for (int b = blockIdx.x; b < a.B; b += gridDim.x) {
+    float* slab = a.scratch + (size_t)b * S_STRIDE;
+    __syncthreads();
+    {   // input sample -> smem
+      const float4* src = reinterpret_cast<const float4*>(a.x + (size_t)b * XN);
+      float4* dst = reinterpret_cast<float4*>(xs);
+      for (int i = tid; i < XN / 4; i += kThreads) dst[i] = src[i];
+    }
+    __syncthreads();
+    // ---- conv1 + bias + ReLU + 2x2 max-pool: [3,32,32] -> [6,14,14]
+    for (int o = tid; o < A1N; o += kThreads) {
+      const int co = o / (P1 * P1), r = o - co * (P1 * P1), ph = r / P1, pw = r - ph * P1;
+      const float bv = w1s[W1N + co];
+      float a00 = bv, a01 = bv, a10 = bv, a11 = bv;
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci) {
+        const float* xc = xs + ci * H * H + (2 * ph) * H + 2 * pw;
+        const float* wk = w1s + (co * CIN + ci) * K * K;
+#pragma unroll
+        for (int kh = 0; kh < K; ++kh) {
+          const float* r0 = xc + kh * H;
+          const float* r1 = r0 + H;
+          float p0 = r0[0], p1 = r1[0];
+#pragma unroll
+          for (int kw = 0; kw < K; ++kw) {
+            const float wv = wk[kh * K + kw];
+            const float q0 = r0[kw + 1], q1 = r1[kw + 1];
+            a00 = fmaf(wv, p0, a00); a01 = fmaf(wv, q0, a01);
+            a10 = fmaf(wv, p1, a10); a11 = fmaf(wv, q1, a11);
+            p0 = q0; p1 = q1;
+          }
+        }
+      }
+      float m = a00; int am = 0;
+      if (a01 > m) { m = a01; am = 1; }
+      if (a10 > m) { m = a10; am = 2; }
+      if (a11 > m) { m = a11; am = 3; }
+      a1s[o] = fmaxf(m, 0.f);
+      idx1[o] = (unsigned char)am;
+      offs1[o] = (2 * ph + (am >> 1)) * H + 2 * pw + (am & 1);     // live pre-pool position in the 32x32 input plane
+    }
+    __syncthreads();
+    // ---- conv2 + bias + ReLU + pool: [6,14,14] -> [16,5,5]
+    for (int o = tid; o < FLAT; o += kThreads) {
+      const int co = o / (P2 * P2), r = o - co * (P2 * P2), ph = r / P2, pw = r - ph * P2;
+      const float bv = w2s[W2N + co];
+      float a00 = bv, a01 = bv, a10 = bv, a11 = bv;
+      for (int ci = 0; ci < C1; ++ci) {
+        const float* xc = a1s + ci * P1 * P1 + (2 * ph) * P1 + 2 * pw;
+        const float* wk = w2s + (co * C1 + ci) * K * K;
+#pragma unroll
+        for (int kh = 0; kh < K; ++kh) {
+          const float* r0 = xc + kh * P1;
+          const float* r1 = r0 + P1;
+          float p0 = r0[0], p1 = r1[0];
+#pragma unroll
+          for (int kw = 0; kw < K; ++kw) {
+            const float wv = wk[kh * K + kw];
+            const float q0 = r0[kw + 1], q1 = r1[kw + 1];
+            a00 = fmaf(wv, p0, a00); a01 = fmaf(wv, q0, a01);
+            a10 = fmaf(wv, p1, a10); a11 = fmaf(wv, q1, a11);
+            p0 = q0; p1 = q1;
+          }
+        }
+      }
+      float m = a00; int am = 0;
+      if (a01 > m) { m = a01; am = 1; }
+      if (a10 > m) { m = a10; am = 2; }
+      if (a11 > m) { m = a11; am = 3; }
+      m = fmaxf(m, 0.f);
+      a2s[o] = m;
+      slab[S_A2 + o] = m;
+      idx2[o] = (unsigned char)am;
+      offs2[o] = (2 * ph + (am >> 1)) * P1 + 2 * pw + (am & 1);    // position in the 14x14 conv2 input plane
+    }
+    __syncthreads();
+    // ---- fc1 + ReLU: one warp per neuron, weight rows streamed as float4 from L2
+    {
+      const float4* xv = reinterpret_cast<const float4*>(a2s);
+      for (int n0 = warp; n0 < F1; n0 += NW * 3) {
+        float acc[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int u = 0; u < 3; ++u) {
+          const int n = n0 + NW * u;
+          if (n < F1) {
+            const float4* wr = reinterpret_cast<const float4*>(Wf1 + (size_t)n * FLAT);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              const int c4 = lane + 32 * c;
+              if (c4 < FLAT / 4) acc[u] += dot4(wr[c4], xv[c4]);
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 3; ++u) {
+          const float s = warp_sum(acc[u]);
+          const int n = n0 + NW * u;
+          if (lane == 0 && n < F1) {
+            const float v = fmaxf(s + Bf1[n], 0.f);
+            z1s[n] = v;
+            slab[S_Z1 + n] = v;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- fc2 + ReLU
+    {
+      const float4* xv = reinterpret_cast<const float4*>(z1s);
+      for (int n0 = warp; n0 < F2; n0 += NW * 4) {
+        float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int n = n0 + NW * u;
+          if (n < F2 && lane < F1 / 4) acc[u] = dot4(reinterpret_cast<const float4*>(Wf2 + (size_t)n * F1)[lane], xv[lane]);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const float s = warp_sum(acc[u]);
+          const int n = n0 + NW * u;
+          if (lane == 0 && n < F2) {
+            const float v = fmaxf(s + Bf2[n], 0.f);
+            z2s[n] = v;
+            slab[S_Z2 + n] = v;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- fc3 (logits)
+    {
+      const float4* xv = reinterpret_cast<const float4*>(z2s);
+      for (int n = warp; n < NC; n += NW) {
+        float acc = 0.f;
+        if (lane < F2 / 4) acc = dot4(reinterpret_cast<const float4*>(Wf3 + (size_t)n * F2)[lane], xv[lane]);
+        acc = warp_sum(acc);
+        if (lane == 0) lgs[n] = acc + Bf3[n];
+      }
+    }
+    __syncthreads();
+    // ---- softmax cross-entropy, accuracy, dlogits
+    if (warp == 0) {
+      const int tgt = (int)a.y[b];
+      const float v = lane < NC ? lgs[lane] : -INFINITY;
+      float m = v; int am = lane < NC ? lane : 0x7fffffff;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float om = __shfl_xor_sync(0xffffffffu, m, o);
+        const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+        if (om > m || (om == m && oa < am)) { m = om; am = oa; }
+      }
+      const float e = lane < NC ? expf(v - m) : 0.f;
+      const float s = warp_sum(e);
+      if (lane < NC) {
+        float p = e / s;
+        if (lane == tgt) p -= 1.0f;
+        p *= inv_B;
+        dls[lane] = p;
+        slab[S_DL + lane] = p;
+      }
+      if (lane == 0) {
+        const float xt = (tgt >= 0 && tgt < NC) ? lgs[tgt] : (logf(s) + m);
+        slab[S_DL + 10] = logf(s) + m - xt;                 // per-sample loss
+        slab[S_DL + 11] = (am == tgt) ? 1.f : 0.f;
+      }
+    }
+    __syncthreads();
+    if (!a.train) continue;
+    // ---- backward through fc3 / fc2 (data gradients)
+    if (tid < F2) {
+      float s = 0.f;
+#pragma unroll
+      for (int n = 0; n < NC; ++n) s = fmaf(dls[n], Wf3[n * F2 + tid], s);
+      s = z2s[tid] > 0.f ? s : 0.f;
+      d2s[tid] = s;
+      slab[S_D2 + tid] = s;
+    }
+    __syncthreads();
+    if (tid < 8 * F1) {                     // eight slices of the 84-long reduction
+      const int k = tid % F1, part = tid / F1;
+      float s = 0.f;
+      const int n_hi = min(F2, part * 11 + 11);
+#pragma unroll 11
+      for (int n = part * 11; n < n_hi; ++n) s = fmaf(d2s[n], Wf2[n * F1 + k], s);
+      dz2[tid] = s;                         // dz2 doubles as reduction scratch here
+    }
+    __syncthreads();
+    if (tid < F1) {
+      float s = 0.f;
+#pragma unroll
+      for (int part = 0; part < 8; ++part) s += dz2[part * F1 + tid];
+      s = z1s[tid] > 0.f ? s : 0.f;
+      d1s[tid] = s;
+      slab[S_D1 + tid] = s;
+    }
+    __syncthreads();
+    // ---- backward through fc1: g2p[k] = sum_n d1[n] W1[n][k]; warps = 16 row groups x 2 column halves, each
+    //      scales and accumulates its rows' float4s; partials are combined through shared memory
+    {
+      const int rg = warp & 15, half = warp >> 4;
+      float4 acc[2];
+      acc[0] = acc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+      for (int n = rg; n < F1; n += 16) {
+        const float dv = d1s[n];
+        const float4* wr = reinterpret_cast<const float4*>(Wf1 + (size_t)n * FLAT);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int c4 = lane + 32 * (2 * half + c);
+          if (c4 < FLAT / 4) {
+            const float4 w = wr[c4];
+            acc[c].x = fmaf(dv, w.x, acc[c].x); acc[c].y = fmaf(dv, w.y, acc[c].y);
+            acc[c].z = fmaf(dv, w.z, acc[c].z); acc[c].w = fmaf(dv, w.w, acc[c].w);
+          }
+        }
+      }
+      float4* part = reinterpret_cast<float4*>(dz2) + rg * (FLAT / 4);      // [16][100] float4
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const int c4 = lane + 32 * (2 * half + c);
+        if (c4 < FLAT / 4) part[c4] = acc[c];
+      }
+    }
+    __syncthreads();
+    for (int k = tid; k < FLAT; k += kThreads) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < 16; ++w) s += dz2[w * FLAT + k];
+      g2p[k] = a2s[k] > 0.f ? s : 0.f;      // through ReLU (pooled output > 0 <=> the live pre-pool value > 0)
+    }
+    __syncthreads();
+    // ---- conv2: per-sample weight / bias gradient partials, and the haloed dense gradient plane for dgrad
+    for (int i = tid; i < C2 * ZH * ZH; i += kThreads) dz2[i] = 0.f;
+    __syncthreads();
+    for (int t = tid; t < W2N + C2; t += kThreads) {
+      float s = 0.f;
+      if (t < W2N) {
+        const int co = t / (C1 * K * K), r = t - co * (C1 * K * K), ci = r / (K * K), q = r - ci * (K * K);
+        const float* xt = a1s + ci * P1 * P1 + (q / K) * P1 + (q % K);
+        const float* g = g2p + co * (P2 * P2);
+        const int* of = offs2 + co * (P2 * P2);
+#pragma unroll
+        for (int p = 0; p < P2 * P2; ++p) s = fmaf(g[p], xt[of[p]], s);
+      } else {
+        const float* g = g2p + (t - W2N) * (P2 * P2);
+#pragma unroll
+        for (int p = 0; p < P2 * P2; ++p) s += g[p];
+      }
+      slab[S_PW2 + t] = s;
+    }
+    for (int o = tid; o < FLAT; o += kThreads) {
+      const int co = o / (P2 * P2);
+      const int pos = offs2[o];                      // oh * 14 + ow  with oh, ow < 10
+      const int oh = pos / P1, ow = pos - oh * P1;
+      dz2[co * ZH * ZH + (oh + K - 1) * ZH + (ow + K - 1)] = g2p[o];
+    }
+    __syncthreads();
+    // ---- conv2 dgrad -> gradient w.r.t. the pooled conv1 output, through its ReLU.
+    //      Work item = (group of 4 output channels, ci, row h, strip of 7 columns): per (co, kh) it loads 11 gradient
+    //      values + 5 taps for 35 FMAs (shared memory is the bound here); the 4 channel groups are summed afterwards.
+    for (int it = tid; it < 4 * C1 * P1 * 2; it += kThreads) {
+      const int cog = it / (C1 * P1 * 2), r = it - cog * (C1 * P1 * 2);
+      const int ci = r / (P1 * 2), r2 = r - ci * (P1 * 2), h = r2 >> 1, w0 = (r2 & 1) * 7;
+      float acc[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      for (int co = cog * 4; co < cog * 4 + 4; ++co) {
+        const float* wk = w2s + (co * C1 + ci) * K * K;
+#pragma unroll
+        for (int kh = 0; kh < K; ++kh) {
+          // output (h, w) needs dz[h - kh + 4][w - kw + 4]; for w = w0..w0+6, kw = 0..4 that is columns w0 .. w0 + 10
+          const float* row = dz2 + co * ZH * ZH + (h - kh + K - 1) * ZH + w0;
+          float d[11];
+#pragma unroll
+          for (int j = 0; j < 11; ++j) d[j] = row[j];
+#pragma unroll
+          for (int kw = 0; kw < K; ++kw) {
+            const float wv = wk[kh * K + kw];
+#pragma unroll
+            for (int j = 0; j < 7; ++j) acc[j] = fmaf(d[j + (K - 1) - kw], wv, acc[j]);
+          }
+        }
+      }
+      float* dst = dgp + cog * A1N + ci * P1 * P1 + h * P1 + w0;
+#pragma unroll
+      for (int j = 0; j < 7; ++j) dst[j] = acc[j];
+    }
+    __syncthreads();
+    for (int o = tid; o < A1N; o += kThreads) {
+      const float s = dgp[o] + dgp[A1N + o] + dgp[2 * A1N + o] + dgp[3 * A1N + o];
+      g1p[o] = a1s[o] > 0.f ? s : 0.f;
+    }
+    __syncthreads();
+    // ---- conv1: per-sample weight / bias gradient partials
+    for (int t = tid; t < W1N + C1; t += kThreads) {
+      float s = 0.f;
+      if (t < W1N) {
+        const int co = t / (CIN * K * K), r = t - co * (CIN * K * K), ci = r / (K * K), q = r - ci * (K * K);
+        const float* xt = xs + ci * H * H + (q / K) * H + (q % K);
+        const float* g = g1p + co * (P1 * P1);
+        const int* of = offs1 + co * (P1 * P1);
+#pragma unroll 4
+        for (int p = 0; p < P1 * P1; ++p) s = fmaf(g[p], xt[of[p]], s);
+      } else {
+        const float* g = g1p + (t - W1N) * (P1 * P1);
+        for (int p = 0; p < P1 * P1; ++p) s += g[p];
+      }
+      slab[S_PW1 + t] = s;
+    }
+  }
+
+  // =========================================== barrier ===========================================
+  grid_barrier(a.sync, gridDim.x, s_sense);
+
+  // =========================================== phase B ===========================================
+  if (blockIdx.x == 0 && warp == 0) {            // batch loss / accuracy -> device accumulators
+    float l = 0.f, c = 0.f;
+    for (int b = lane; b < a.B; b += 32) {
+      l += __ldcg(a.scratch + (size_t)b * S_STRIDE + S_DL + 10);
+      c += __ldcg(a.scratch + (size_t)b * S_STRIDE + S_DL + 11);
+    }
+    l = warp_sum(l);
+    c = warp_sum(c);
+    if (lane == 0) {
+      const float loss = l * inv_B;
+      if (a.loss_out) *a.loss_out = loss;
+      if (a.acc3) {
+        a.acc3[0] += loss;
+        if (a.want_acc) a.acc3[1] += c * inv_B;
+        a.acc3[2] += 1.0f;
+      }
+    }
+  }
+  if (!a.train) return;
+
+  const Hyper h = *a.hyper;
+  const int per_cta = (int)ceil_div64(a.numel, (long long)gridDim.x * kThreads) * kThreads;   // elements owned by a CTA
+  const long long e0 = (long long)blockIdx.x * per_cta;
+  const int per_thread = per_cta / kThreads;
+  float g[kMaxPerThread];
+  const int B = a.B;
+#pragma unroll
+  for (int r = 0; r < kMaxPerThread; ++r) {
+    g[r] = 0.f;
+    if (r >= per_thread) continue;
+    const long long e = e0 + (long long)r * kThreads + tid;
+    if (e >= a.numel) continue;
+    // which parameter does arena element e belong to?
+    int pid = -1; int i = 0;
+#pragma unroll
+    for (int p = 0; p < NPARAM; ++p) {
+      const long long d = e - a.off[p];
+      if (d >= 0 && d < kParamSize[p]) { pid = p; i = (int)d; }
+    }
+    if (pid < 0) continue;                        // alignment padding between parameters
+    const float* sc = a.scratch;
+    float s = 0.f;
+    switch (pid) {
+      case P_F1W: { const int n = i / FLAT, k = i - n * FLAT;
+        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_D1 + n), __ldcg(sc + (size_t)b * S_STRIDE + S_A2 + k), s); break; }
+      case P_F2W: { const int n = i / F1, k = i - n * F1;
+        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_D2 + n), __ldcg(sc + (size_t)b * S_STRIDE + S_Z1 + k), s); break; }
+      case P_F3W: { const int n = i / F2, k = i - n * F2;
+        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_DL + n), __ldcg(sc + (size_t)b * S_STRIDE + S_Z2 + k), s); break; }
+      case P_F1B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_D1 + i); break;
+      case P_F2B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_D2 + i); break;
+      case P_F3B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_DL + i); break;
+      case P_C2W: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW2 + i); break;
+      case P_C2B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW2 + W2N + i); break;
+      case P_C1W: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW1 + i); break;
+      case P_C1B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW1 + W1N + i); break;
+    }
+    g[r] = s;
+  }
+
+  const P2PArgs& cm = a.comm;
+  unsigned int parity = 0;
+  if (cm.world > 1) {
+    // one-shot push of this CTA's gradient elements into every peer's receive slot, then a per-CTA flag exchange
+    const int me = cm.rank;
+    parity = (flags_of(cm, me)->tick[0][blockIdx.x] + 1) & 1u;
+    for (int p = 0; p < cm.world; ++p) {
+      if (p == me) continue;
+      float* dst = reinterpret_cast<float*>(cm.base[p] + cm.recv_off + ((long long)parity * cm.world + me) * cm.recv_slot_bytes);
+#pragma unroll
+      for (int r = 0; r < kMaxPerThread; ++r) {
+        const long long e = e0 + (long long)r * kThreads + tid;
+        if (r < per_thread && e < a.numel) dst[e] = g[r];
+      }
+    }
+    cta_exchange(cm, me, 0, blockIdx.x);
+  }
+#pragma unroll
+  for (int r = 0; r < kMaxPerThread; ++r) {
+    if (r >= per_thread) continue;
+    const long long e = e0 + (long long)r * kThreads + tid;
+    if (e >= a.numel) continue;
+    float gs = g[r];
+    if (cm.world > 1) {
+      gs = 0.f;
+      const char* recv = cm.base[cm.rank] + cm.recv_off + (long long)parity * cm.world * cm.recv_slot_bytes;
+      for (int p = 0; p < cm.world; ++p)        // fixed rank order: every replica computes identical bits
+        gs += (p == cm.rank) ? g[r] : __ldcg(reinterpret_cast<const float*>(recv + p * cm.recv_slot_bytes) + e);
+    }
+    float pv = a.master[e], s1 = a.s1[e], s2 = 0.f;
+    if (R::kStates > 1) s2 = a.s2[e];
+    R::apply(pv, gs * h.grad_scale, s1, s2, h);
+    a.master[e] = pv;
+    a.s1[e] = s1;
+    if (R::kStates > 1) a.s2[e] = s2;
+  }
+}
+
+namespace lenet {
+constexpr size_t kSmemBytes = (size_t)(XN + 456 + A1N + 2416 + FLAT + F1 + 88 + 16 + 16 + 88 + F1 + FLAT + A1N + 6400 + 4 * A1N) * 4 +
+                              (size_t)(A1N + FLAT) * 4 + (A1N + FLAT) + 64;
+}
+
+}  // namespace mlt
+
+using namespace mlt;
+
+extern "C" long long mlt_lenet_scratch_bytes(int B) { return (long long)B * lenet::S_STRIDE * 4 + 256; }
+
+// One fused training (train=1) or evaluation (train=0) step of the reference MLModel.  fp32; model == master.
+// param_off: arena element offsets of {conv1.w, conv1.b, conv2.w, conv2.b, fc1.w, fc1.b, fc2.w, fc2.b, fc3.w, fc3.b}.
+// scratch: mlt_lenet_scratch_bytes(B) bytes, zero-initialised once (its first 256 bytes hold the grid-barrier words).
+// ctx: NULL or world == 1 for single-GPU; otherwise gradients are all-reduced in-kernel through the symmetric arena.
+extern "C" int mlt_lenet_step(void* master, void* s1, void* s2, const void* hyper, long long numel, const long long* param_off,
+                              int rule, const void* x, const void* y_i64, int B, int train, int want_acc, void* acc3,
+                              void* loss_out, void* scratch, long long scratch_bytes, const mlt_p2p_ctx* ctx, void* stream) {
+  using namespace lenet;
+  MLT_REQUIRE(B > 0, "mlt_lenet_step: empty batch");
+  MLT_REQUIRE(scratch != nullptr && scratch_bytes >= mlt_lenet_scratch_bytes(B), "mlt_lenet_step: scratch too small");
+  LeNetArgs a;
+  a.master = (float*)master; a.s1 = (float*)s1; a.s2 = (float*)s2; a.hyper = (const Hyper*)hyper; a.numel = numel;
+  for (int i = 0; i < NPARAM; ++i) a.off[i] = param_off[i];
+  a.x = (const float*)x; a.y = (const long long*)y_i64; a.B = B; a.train = train; a.want_acc = want_acc;
+  a.sync = (unsigned int*)scratch;
+  a.scratch = (float*)((char*)scratch + 256);
+  a.acc3 = (float*)acc3; a.loss_out = (float*)loss_out;
+  a.comm.world = 1; a.comm.rank = 0;
+  if (ctx != nullptr && ctx->world > 1) {
+    MLT_REQUIRE(numel * 4 <= ctx->recv_slot_bytes, "mlt_lenet_step: parameter arena exceeds the one-shot receive slot");
+    for (int i = 0; i < kMaxRanks; ++i) a.comm.base[i] = (char*)ctx->base[i];
+    a.comm.mc_base = (char*)ctx->mc_base;
+    a.comm.world = ctx->world; a.comm.rank = ctx->rank;
+    a.comm.flags_off = ctx->flags_off; a.comm.recv_off = ctx->recv_off; a.comm.recv_slot_bytes = ctx->recv_slot_bytes;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  int dev = 0;
+  MLT_CHECK_CUDA(cudaGetDevice(&dev));
+  int rc = 0;
+  MLT_DISPATCH_RULE(rule, R, {
+    auto kern = lenet_step_kernel<R>;
+    static int grid_cache[64] = {};
+    if (grid_cache[dev & 63] == 0) {
+      MLT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+      int per_sm = 0, sms = 0;
+      MLT_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, kSmemBytes));
+      MLT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+      MLT_REQUIRE(per_sm >= 1, "mlt_lenet_step: kernel does not fit on an SM");
+      grid_cache[dev & 63] = sms;           // one CTA per SM: all co-resident, phase B spreads over the whole chip
+    }
+    int grid = grid_cache[dev & 63];
+    const long long min_grid = ceil_div64(numel, (long long)kThreads * kMaxPerThread);
+    MLT_REQUIRE(grid >= min_grid && grid <= kMaxCtas - 1, "mlt_lenet_step: grid %d cannot cover %lld parameters", grid, numel);
+    void* params[] = {&a};
+    MLT_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(kThreads), params, kSmemBytes, st));
+  });
+  return rc;
+}

@@ -1,0 +1,123 @@
+// Device-side building blocks of the NVLink communication kernels: arena flag block, sys-scope flag
+// exchange between same-index CTAs of all ranks, peer load/store helpers.  Shared by comm_p2p.cu and lenet_step.cu.
+#pragma once
+#include "optim_rules.cuh"
+
+namespace mlt {
+
+constexpr int kMaxRanks = 8;
+constexpr int kMaxCtas = 512;            // flag rows per kind
+constexpr long long kSpinTimeoutCycles = 40LL * 1000 * 1000 * 1000;   // ~20 s at 2 GHz
+
+// Flag block layout (uint32 units), identical on every rank:
+//   sig[kind][cta][src_rank]   written by peers        kind 0 = "data pushed / grads ready", 1 = "done"
+//   tick[kind][cta]            local ticket counters
+//   err[8]                     first timeout diagnostic {code, rank, peer, cta, expected, seen}
+struct FlagBlock {
+  unsigned int sig[2][kMaxCtas][kMaxRanks];
+  unsigned int tick[2][kMaxCtas];
+  unsigned int err[8];
+};
+
+struct P2PArgs {
+  char* base[kMaxRanks];     // arena base of every rank, as mapped in this process
+  char* mc_base;             // multicast mapping (nullptr when NVLS is unavailable)
+  int world;
+  int rank;                  // rank of gridDim.y index 0
+  long long flags_off;       // FlagBlock offset in the arena
+  long long recv_off;        // one-shot receive slots: [parity][src][recv_slot_bytes]
+  long long recv_slot_bytes;
+  long long grad_off;        // bucket gradient slice offset in the arena (bytes)
+  long long model_off;       // bucket compute-dtype weight slice offset in the arena (bytes)
+  // per emulated rank (index blockIdx.y): local, non-symmetric optimizer state of the bucket slice
+  float* master[kMaxRanks];
+  float* s1[kMaxRanks];
+  float* s2[kMaxRanks];
+  const Hyper* hyper[kMaxRanks];
+  long long n;               // elements in the bucket (multiple of 128 by arena construction)
+  int model_is_master;       // fp32 compute: the arena weight slice IS the master (no separate shadow)
+};
+
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ FlagBlock* flags_of(const P2PArgs& a, int r) {
+  return reinterpret_cast<FlagBlock*>(a.base[r] + a.flags_off);
+}
+
+// Signal every peer's sig[kind][cta][me] with a fresh ticket, then wait until every peer's ticket reached it.
+// Must be called by all threads of the CTA (contains __syncthreads); data written before the call by any
+// thread of this CTA is visible to peers that observe the flag, and vice versa.
+__device__ __forceinline__ void cta_exchange(const P2PArgs& a, int me, int kind, int cta, bool do_signal = true, bool do_wait = true,
+                                             unsigned int* ticket_io = nullptr) {
+  __shared__ unsigned int s_ticket;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    FlagBlock* mine = flags_of(a, me);
+    unsigned int t;
+    if (do_signal) {
+      t = mine->tick[kind][cta] + 1;
+      mine->tick[kind][cta] = t;
+      __threadfence_system();
+      for (int p = 0; p < a.world; ++p)
+        if (p != me) st_release_sys(&flags_of(a, p)->sig[kind][cta][me], t);
+    } else {
+      t = *ticket_io;
+    }
+    s_ticket = t;
+  }
+  __syncthreads();
+  const unsigned int t = s_ticket;
+  if (ticket_io && threadIdx.x == 0) *ticket_io = t;
+  if (do_wait) {
+    if (threadIdx.x < a.world && (int)threadIdx.x != me) {
+      const unsigned int* f = &flags_of(a, me)->sig[kind][cta][threadIdx.x];
+      const long long t0 = clock64();
+      unsigned int seen;
+      while ((int)((seen = ld_acquire_sys(f)) - t) < 0) {
+        if (clock64() - t0 > kSpinTimeoutCycles) {
+          unsigned int* e = flags_of(a, me)->err;
+          if (atomicCAS(&e[0], 0u, 1u) == 0u) { e[1] = me; e[2] = threadIdx.x; e[3] = cta; e[4] = t; e[5] = seen; e[6] = kind; }
+          break;
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- vector helpers: 8 (bf16) or 4 (fp32) elements per 16 bytes -------------------------------------------------
+template <typename G> struct Vec;
+template <> struct Vec<float> {
+  static constexpr int kElems = 4;
+  __device__ static void add(float (&acc)[8], const uint4& raw) {
+    acc[0] += __uint_as_float(raw.x); acc[1] += __uint_as_float(raw.y); acc[2] += __uint_as_float(raw.z); acc[3] += __uint_as_float(raw.w);
+  }
+};
+template <> struct Vec<__nv_bfloat16> {
+  static constexpr int kElems = 8;
+  __device__ static void add(float (&acc)[8], const uint4& raw) {
+    const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[j]));
+      acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+    }
+  }
+};
+
+__device__ __forceinline__ uint4 ld_peer(const void* p) {      // peer HBM: bypass L1, nothing to keep
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer(void* p, const uint4& v) {
+  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+}  // namespace mlt

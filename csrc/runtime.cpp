@@ -1,0 +1,235 @@
+// Native epoch executor + data feeder: the hot loop of reference src/trainer.py:180-197
+// (DataLoader.__next__ -> .to(device) -> step -> loss.item()) without the Python interpreter in it.
+//
+// Per step the executor does, entirely from C++:
+//   gather thread : collect the step's rows of an in-memory (host) dataset into a pinned staging slot
+//   copy stream   : cudaMemcpyAsync H2D of inputs + targets into the slot's device buffers, event `ready`
+//   compute stream: wait `ready`; H2D of the step's 8-float hyper-parameter row (lr schedule precomputed by the
+//                   caller); launch the step (either the single-kernel LeNet step or a captured CUDA graph whose
+//                   input pointers are the slot's buffers); D2H of the step's loss into a pinned result array;
+//                   event `released` (the slot's buffers may be overwritten).
+// Slots form a ring (default 3), so the gather and upload of step i+1.. overlap the compute of step i.
+// Nothing here synchronises with the device except when a ring slot is still in flight and at the end of the run.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <cstring>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+#include "../include/mlt_b200.h"
+
+namespace mlt {
+void set_error(const char* fmt, ...);
+}
+using mlt::set_error;
+
+#define RT_CHECK(expr)                                                                    \
+  do {                                                                                    \
+    cudaError_t _e = (expr);                                                              \
+    if (_e != cudaSuccess) {                                                              \
+      set_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e));     \
+      return (int)_e;                                                                     \
+    }                                                                                     \
+  } while (0)
+
+namespace {
+
+struct Slot {
+  void* pin_x = nullptr;
+  void* pin_y = nullptr;
+  void* dev_x = nullptr;
+  void* dev_y = nullptr;
+  cudaEvent_t ready = nullptr;      // H2D of this slot finished (copy stream)
+  cudaEvent_t copied = nullptr;     // same event viewed from the host: pinned staging reusable
+  cudaEvent_t released = nullptr;   // compute finished with the device buffers
+  bool used = false;
+};
+
+struct Loop {
+  int device = 0;
+  int slots = 3;
+  long long max_batch = 0;
+  size_t x_row = 0, y_row = 0;          // bytes per sample
+  std::vector<Slot> ring;
+  cudaStream_t copy = nullptr;
+  float* pin_hyper = nullptr;           // [max_steps][8] staged hyper rows
+  long long hyper_cap = 0;
+  float* pin_loss = nullptr;            // [max_steps]
+  long long loss_cap = 0;
+  // statistics of the last run
+  long long h2d_bytes = 0, d2h_bytes = 0, launches = 0;
+};
+
+// rows `idx[0..n)` of a [N][row] byte matrix -> dst
+void gather_rows(char* dst, const char* src, size_t row, const long long* idx, long long n) {
+  bool contiguous = true;
+  for (long long i = 1; i < n; ++i)
+    if (idx[i] != idx[i - 1] + 1) { contiguous = false; break; }
+  if (contiguous) {
+    std::memcpy(dst, src + (size_t)idx[0] * row, (size_t)n * row);
+    return;
+  }
+  for (long long i = 0; i < n; ++i) std::memcpy(dst + (size_t)i * row, src + (size_t)idx[i] * row, row);
+}
+
+}  // namespace
+
+extern "C" void* mlt_loop_create(int device, int slots, long long max_batch, long long x_row_bytes, long long y_row_bytes) {
+  if (cudaSetDevice(device) != cudaSuccess) { set_error("mlt_loop_create: cudaSetDevice(%d) failed", device); return nullptr; }
+  Loop* L = new Loop();
+  L->device = device;
+  L->slots = slots < 2 ? 2 : slots;
+  L->max_batch = max_batch;
+  L->x_row = (size_t)x_row_bytes;
+  L->y_row = (size_t)y_row_bytes;
+  L->ring.resize(L->slots);
+  bool ok = cudaStreamCreateWithFlags(&L->copy, cudaStreamNonBlocking) == cudaSuccess;
+  for (auto& s : L->ring) {
+    ok = ok && cudaHostAlloc(&s.pin_x, (size_t)max_batch * L->x_row, cudaHostAllocDefault) == cudaSuccess;
+    ok = ok && cudaHostAlloc(&s.pin_y, (size_t)max_batch * L->y_row, cudaHostAllocDefault) == cudaSuccess;
+    ok = ok && cudaMalloc(&s.dev_x, (size_t)max_batch * L->x_row) == cudaSuccess;
+    ok = ok && cudaMalloc(&s.dev_y, (size_t)max_batch * L->y_row) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&s.released, cudaEventDisableTiming) == cudaSuccess;
+  }
+  if (!ok) {
+    set_error("mlt_loop_create: allocation failed (%s)", cudaGetErrorString(cudaGetLastError()));
+    delete L;
+    return nullptr;
+  }
+  return L;
+}
+
+extern "C" void* mlt_loop_slot_x(void* loop, int slot) { return ((Loop*)loop)->ring[slot].dev_x; }
+extern "C" void* mlt_loop_slot_y(void* loop, int slot) { return ((Loop*)loop)->ring[slot].dev_y; }
+extern "C" int mlt_loop_num_slots(void* loop) { return ((Loop*)loop)->slots; }
+
+extern "C" int mlt_loop_destroy(void* loop) {
+  Loop* L = (Loop*)loop;
+  if (!L) return 0;
+  cudaSetDevice(L->device);
+  cudaDeviceSynchronize();
+  for (auto& s : L->ring) {
+    cudaFreeHost(s.pin_x); cudaFreeHost(s.pin_y); cudaFree(s.dev_x); cudaFree(s.dev_y);
+    cudaEventDestroy(s.ready); cudaEventDestroy(s.released);
+  }
+  if (L->pin_hyper) cudaFreeHost(L->pin_hyper);
+  if (L->pin_loss) cudaFreeHost(L->pin_loss);
+  cudaStreamDestroy(L->copy);
+  delete L;
+  return 0;
+}
+
+// Run `steps` training (or evaluation) steps.
+//   host_x / host_y   in-memory dataset, row-major, x_row_bytes / y_row_bytes per sample (pageable or pinned)
+//   indices           [steps * batch] sample ids, step-major (the sampler's order for this rank)
+//   batch_sizes       per-step batch size (<= max_batch); NULL = every step uses `batch`
+//   hyper_rows        [steps][8] floats copied to `hyper_dev` before each step (NULL for evaluation)
+//   step kind 0       LeNet single-kernel step: lenet points at the fixed arguments of mlt_lenet_step
+//   step kind 1       captured CUDA graphs, one cudaGraphExec_t per slot in graph_execs (inputs bound to the slot buffers)
+//   loss_dev          device scalar the step writes its loss to; copied to loss_host[step] every step
+extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, const long long* indices, long long steps,
+                            int batch, const int* batch_sizes, const float* hyper_rows, void* hyper_dev, int step_kind,
+                            const mlt_lenet_call* lenet, void* const* graph_execs, const void* loss_dev, float* loss_host,
+                            void* compute_stream) {
+  Loop* L = (Loop*)loop;
+  RT_CHECK(cudaSetDevice(L->device));
+  cudaStream_t cs = (cudaStream_t)compute_stream;
+  if (steps <= 0) return 0;
+  if (batch > L->max_batch) { set_error("mlt_loop_run: batch %d exceeds the loop's max_batch %lld", batch, L->max_batch); return 1; }
+  if (hyper_rows && steps > L->hyper_cap) {
+    if (L->pin_hyper) cudaFreeHost(L->pin_hyper);
+    RT_CHECK(cudaHostAlloc((void**)&L->pin_hyper, (size_t)steps * 8 * sizeof(float), cudaHostAllocDefault));
+    L->hyper_cap = steps;
+  }
+  if (hyper_rows) std::memcpy(L->pin_hyper, hyper_rows, (size_t)steps * 8 * sizeof(float));
+  if (loss_dev && steps > L->loss_cap) {
+    if (L->pin_loss) cudaFreeHost(L->pin_loss);
+    RT_CHECK(cudaHostAlloc((void**)&L->pin_loss, (size_t)steps * sizeof(float), cudaHostAllocDefault));
+    L->loss_cap = steps;
+  }
+  L->h2d_bytes = L->d2h_bytes = L->launches = 0;
+
+  // ---- gather thread: fills pinned slots ahead of the launcher ---------------------------------------
+  const int S = L->slots;
+  std::vector<std::atomic<long long>> gathered(S);      // step id (+1) whose data sits in the slot's pinned buffers
+  std::vector<std::atomic<long long>> free_for(S);      // slot may be refilled for any step <= this value
+  for (int s = 0; s < S; ++s) { gathered[s].store(0); free_for[s].store(s); }
+  std::atomic<bool> abort{false};
+  const char* hx = (const char*)host_x;
+  const char* hy = (const char*)host_y;
+  auto bs_of = [&](long long i) { return batch_sizes ? (long long)batch_sizes[i] : (long long)batch; };
+  std::vector<long long> start(steps + 1, 0);
+  for (long long i = 0; i < steps; ++i) start[i + 1] = start[i] + bs_of(i);
+  std::thread gatherer([&] {
+    for (long long i = 0; i < steps && !abort.load(); ++i) {
+      const int s = (int)(i % S);
+      while (free_for[s].load(std::memory_order_acquire) < i && !abort.load()) std::this_thread::yield();
+      const long long n = bs_of(i);
+      gather_rows((char*)L->ring[s].pin_x, hx, L->x_row, indices + start[i], n);
+      gather_rows((char*)L->ring[s].pin_y, hy, L->y_row, indices + start[i], n);
+      gathered[s].store(i + 1, std::memory_order_release);
+    }
+  });
+
+  int rc = 0;
+  for (long long i = 0; i < steps; ++i) {
+    const int s = (int)(i % S);
+    Slot& sl = L->ring[s];
+    const long long n = bs_of(i);
+    // Hand the previous step's pinned staging back to the gather thread once its H2D has completed (it has had a
+    // whole iteration to do so; block only if it has not).
+    if (i > 0 && i - 1 + S < steps) {
+      Slot& pv = L->ring[(i - 1) % S];
+      if (cudaEventQuery(pv.ready) != cudaSuccess) cudaEventSynchronize(pv.ready);
+      free_for[(i - 1) % S].store(i - 1 + S, std::memory_order_release);
+    }
+    while (gathered[s].load(std::memory_order_acquire) != i + 1) std::this_thread::yield();
+    // device buffers of this slot are free once the step that last used them has finished
+    if (sl.used) { if ((rc = (int)cudaStreamWaitEvent(L->copy, sl.released, 0)) != 0) break; }
+    if ((rc = (int)cudaMemcpyAsync(sl.dev_x, sl.pin_x, (size_t)n * L->x_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
+    if ((rc = (int)cudaMemcpyAsync(sl.dev_y, sl.pin_y, (size_t)n * L->y_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
+    if ((rc = (int)cudaEventRecord(sl.ready, L->copy)) != 0) break;
+    L->h2d_bytes += n * (long long)(L->x_row + L->y_row);
+    if ((rc = (int)cudaStreamWaitEvent(cs, sl.ready, 0)) != 0) break;
+    if (hyper_rows) {
+      if ((rc = (int)cudaMemcpyAsync(hyper_dev, L->pin_hyper + i * 8, 8 * sizeof(float), cudaMemcpyHostToDevice, cs)) != 0) break;
+      L->h2d_bytes += 32;
+    }
+    if (step_kind == 0) {
+      rc = mlt_lenet_step(lenet->master, lenet->s1, lenet->s2, lenet->hyper, lenet->numel, lenet->param_off, lenet->rule,
+                          sl.dev_x, sl.dev_y, (int)n, lenet->train, lenet->want_acc, lenet->acc3, lenet->loss_out,
+                          lenet->scratch, lenet->scratch_bytes, lenet->ctx, cs);
+      if (rc != 0) break;
+    } else {
+      if ((rc = (int)cudaGraphLaunch((cudaGraphExec_t)graph_execs[s], cs)) != 0) break;
+    }
+    L->launches += 1;
+    if (loss_dev) {
+      if ((rc = (int)cudaMemcpyAsync(L->pin_loss + i, loss_dev, sizeof(float), cudaMemcpyDeviceToHost, cs)) != 0) break;
+      L->d2h_bytes += 4;
+    }
+    if ((rc = (int)cudaEventRecord(sl.released, cs)) != 0) break;
+    sl.used = true;
+  }
+  if (rc != 0) {
+    abort.store(true);
+    set_error("mlt_loop_run: CUDA call failed with %s", cudaGetErrorString((cudaError_t)rc));
+  }
+  gatherer.join();
+  if (rc != 0) return rc;
+  RT_CHECK(cudaStreamSynchronize(cs));
+  if (loss_dev && loss_host) std::memcpy(loss_host, L->pin_loss, (size_t)steps * sizeof(float));
+  return 0;
+}
+
+extern "C" int mlt_loop_stats(void* loop, long long* h2d_bytes, long long* d2h_bytes, long long* launches) {
+  Loop* L = (Loop*)loop;
+  if (h2d_bytes) *h2d_bytes = L->h2d_bytes;
+  if (d2h_bytes) *d2h_bytes = L->d2h_bytes;
+  if (launches) *launches = L->launches;
+  return 0;
+}

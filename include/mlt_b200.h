@@ -130,6 +130,40 @@ int mlt_p2p_broadcast(const mlt_p2p_ctx* ctx, long long off, long long nbytes, i
 int mlt_p2p_reduce_scalars(const mlt_p2p_ctx* ctx, long long scalar_off, void* vals_dev, int k, int ranks_here, void* stream);
 int mlt_p2p_check_error(const mlt_p2p_ctx* ctx, unsigned int* out6_host);
 
+/* ---- the reference model's whole train step as one kernel: src/model.py:7-24 + src/trainer.py:181-188 ------------- */
+long long mlt_lenet_scratch_bytes(int B);
+/* forward + cross-entropy + accuracy + backward + (multi-GPU) in-kernel one-shot all-reduce + optimizer rule.
+ * param_off: arena element offsets of conv1.w, conv1.b, conv2.w, conv2.b, fc1.w, fc1.b, fc2.w, fc2.b, fc3.w, fc3.b.
+ * scratch: mlt_lenet_scratch_bytes(B), zero-initialised once.  ctx NULL (or world 1) = single GPU. */
+int mlt_lenet_step(void* master, void* s1, void* s2, const void* hyper, long long numel, const long long* param_off,
+                   int rule, const void* x, const void* y_i64, int B, int train, int want_acc, void* acc3,
+                   void* loss_out, void* scratch, long long scratch_bytes, const mlt_p2p_ctx* ctx, void* stream);
+
+/* ---- native epoch executor + data feeder: the Python hot loop of src/trainer.py:180-197, in C++ ------------------ */
+typedef struct {            /* fixed arguments of mlt_lenet_step; x / y / B come from the executor's ring slots */
+  void *master, *s1, *s2;
+  const void* hyper;
+  long long numel;
+  const long long* param_off;
+  int rule, train, want_acc;
+  void *acc3, *loss_out, *scratch;
+  long long scratch_bytes;
+  const mlt_p2p_ctx* ctx;
+} mlt_lenet_call;
+
+/* Allocates (set-up only): `slots` pinned staging buffers + device buffers for max_batch samples, a copy stream, events. */
+void* mlt_loop_create(int device, int slots, long long max_batch, long long x_row_bytes, long long y_row_bytes);
+void* mlt_loop_slot_x(void* loop, int slot);
+void* mlt_loop_slot_y(void* loop, int slot);
+int mlt_loop_num_slots(void* loop);
+int mlt_loop_destroy(void* loop);
+/* Runs `steps` steps: host gather -> pinned -> H2D (copy stream) -> hyper row H2D -> step -> loss D2H, ring-buffered.
+ * step_kind 0: single-kernel LeNet step (`lenet`);  1: one captured cudaGraphExec_t per slot (`graph_execs`). */
+int mlt_loop_run(void* loop, const void* host_x, const void* host_y, const long long* indices, long long steps, int batch,
+                 const int* batch_sizes, const float* hyper_rows, void* hyper_dev, int step_kind, const mlt_lenet_call* lenet,
+                 void* const* graph_execs, const void* loss_dev, float* loss_host, void* compute_stream);
+int mlt_loop_stats(void* loop, long long* h2d_bytes, long long* d2h_bytes, long long* launches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -36,6 +36,8 @@ class TrainerConfig:
     # ---- B200 additions ------------------------------------------------------
     dtype: str = "fp32"            # compute dtype: fp32 | bf16 (fp32 master weights either way)
     graph: Any = "auto"            # capture the whole train step in a CUDA graph: auto | True | False
+    fused_step: bool = True        # models that provide a single-kernel train step (MLModel) use it
+    native_loop: bool = True       # run whole epochs in the C++ executor when data and step allow it
     convert: bool = True           # swap torch.nn layers for the sm_100a op library on CUDA
     prefetch: int = 2              # pinned staging slots of the H2D prefetcher (0 = synchronous copies)
     num_workers: int = 0

@@ -24,7 +24,7 @@ WARMUP = 3
 
 class StepEngine:
     def __init__(self, model, criterion, criterion_type, metric, reducer, device,
-                 graph="auto", compute_dtype=torch.float32):
+                 graph="auto", compute_dtype=torch.float32, fused_step=True):
         self.model = model
         self.criterion = criterion
         self.criterion_type = criterion_type
@@ -42,6 +42,13 @@ class StepEngine:
         self.graph_replays = 0
         self.launches_per_step = 0
         self.last_loss: Optional[torch.Tensor] = None
+        # single-kernel step (forward + loss + backward + all-reduce + update) when the model provides one
+        self.fused = None
+        if fused_step and getattr(criterion, "native_fused", False) and hasattr(model, "make_fused_step") \
+                and device.type == "cuda" and metric in (None, "accuracy"):
+            self.fused = model.make_fused_step(reducer.opt, reducer.comm)
+        if self.fused is not None:
+            self._loss_buf = torch.zeros((), dtype=torch.float32, device=device)
 
     # ------------------------------------------------------------ accumulators
     def reset_accumulators(self):
@@ -105,6 +112,12 @@ class StepEngine:
 
     def train_step(self, inputs, targets):
         opt = self.reducer.opt
+        if self.fused is not None and self.fused.supports(inputs, targets):
+            opt.begin_step(self.reducer.grad_scale)
+            self.fused(inputs, targets, True, self.acc, self.metric == "accuracy", self._loss_buf)
+            self.last_loss = self._loss_buf
+            self.launches_per_step = 1
+            return
         if not self.use_graph:
             opt.begin_step(self.reducer.grad_scale)
             self._train_body(inputs, targets)
@@ -140,5 +153,8 @@ class StepEngine:
     # -------------------------------------------------------------------- eval
     @torch.no_grad()
     def eval_step(self, model, inputs, targets):
+        if self.fused is not None and model is self.model and self.fused.supports(inputs, targets):
+            self.fused(inputs, targets, False, self.acc, self.metric == "accuracy", self._loss_buf)
+            return None
         outputs, _, _ = self._forward_loss(model, inputs, targets, train=False)
         return outputs

@@ -1,0 +1,100 @@
+"""Python face of the native epoch executor (csrc/runtime.cpp).
+
+``NativeLoop`` owns the C++ ring of pinned staging + device buffers, the copy stream and the gather thread.  The
+Trainer hands it a whole epoch at once - the sampler's index order, the per-step hyper-parameter rows (so any LR
+schedule is honoured) and the step to run - and gets the per-step losses back.  Per step the host then costs a few
+microseconds of C++ instead of a pass through the interpreter (reference src/trainer.py:180-197).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+
+from .ops import _lib
+from .ops._lib import check, launches, ptr, stream_handle
+from .parallel.p2p import P2PCtx
+
+_c_int, _c_ll, _c_vp = ctypes.c_int, ctypes.c_longlong, ctypes.c_void_p
+
+
+class LeNetCall(ctypes.Structure):
+    _fields_ = [("master", _c_vp), ("s1", _c_vp), ("s2", _c_vp), ("hyper", _c_vp), ("numel", _c_ll),
+                ("param_off", ctypes.POINTER(_c_ll)), ("rule", _c_int), ("train", _c_int), ("want_acc", _c_int),
+                ("acc3", _c_vp), ("loss_out", _c_vp), ("scratch", _c_vp), ("scratch_bytes", _c_ll),
+                ("ctx", ctypes.POINTER(P2PCtx))]
+
+
+class NativeLoop:
+    def __init__(self, device: torch.device, max_batch: int, x_row_bytes: int, y_row_bytes: int, slots: int = 3):
+        self.L = _lib.lib()
+        self.L.mlt_loop_create.restype = _c_vp
+        self.L.mlt_loop_slot_x.restype = _c_vp
+        self.L.mlt_loop_slot_y.restype = _c_vp
+        self.device, self.max_batch = device, max_batch
+        self.x_row, self.y_row = x_row_bytes, y_row_bytes
+        h = self.L.mlt_loop_create(_c_int(device.index), _c_int(slots), _c_ll(max_batch), _c_ll(x_row_bytes), _c_ll(y_row_bytes))
+        if not h:
+            raise RuntimeError(f"mlt_loop_create failed: {self.L.mlt_last_error().decode()}")
+        self.h = _c_vp(h)
+        self.slots = int(self.L.mlt_loop_num_slots(self.h))
+        self.last_stats = {}
+
+    def close(self):
+        if self.h:
+            self.L.mlt_loop_destroy(self.h)
+            self.h = None
+
+    def __del__(self):  # best effort
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def slot_buffers(self, slot: int):
+        return int(self.L.mlt_loop_slot_x(self.h, _c_int(slot))), int(self.L.mlt_loop_slot_y(self.h, _c_int(slot)))
+
+    def _finish(self, steps):
+        a, b, c = _c_ll(0), _c_ll(0), _c_ll(0)
+        self.L.mlt_loop_stats(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
+        self.last_stats = {"h2d_bytes": a.value, "d2h_bytes": b.value, "launches": c.value, "steps": steps}
+
+    def run_lenet(self, fused, host_x: torch.Tensor, host_y: torch.Tensor, indices: torch.Tensor, batch: int,
+                  batch_sizes: Optional[Sequence[int]], hyper_rows: Optional[torch.Tensor], train: bool,
+                  acc3: Optional[torch.Tensor], want_acc: bool, loss_buf: torch.Tensor) -> torch.Tensor:
+        """Run one epoch of single-kernel LeNet steps.  Returns the per-step losses (CPU float32 tensor)."""
+        steps = len(batch_sizes) if batch_sizes is not None else indices.numel() // batch
+        fused.ensure_scratch(max(batch_sizes) if batch_sizes is not None else batch, self.device)
+        o = fused.opt
+        call = LeNetCall()
+        call.master, call.s1 = o.master.data_ptr(), o.s1.data_ptr()
+        call.s2 = o.s2.data_ptr() if o.s2.numel() > 1 else None
+        call.hyper, call.numel = o.hyper.data_ptr(), o.numel
+        call.param_off = ctypes.cast(fused.off, ctypes.POINTER(_c_ll))
+        call.rule, call.train, call.want_acc = fused.rule, int(train), int(want_acc)
+        call.acc3 = acc3.data_ptr() if acc3 is not None else None
+        call.loss_out = loss_buf.data_ptr()
+        call.scratch, call.scratch_bytes = fused._scratch.data_ptr(), fused._scratch.numel()
+        call.ctx = ctypes.pointer(fused.ctx) if fused.ctx is not None else None
+        losses = torch.empty(steps, dtype=torch.float32)
+        idx = indices.contiguous()
+        bs = (ctypes.c_int * steps)(*batch_sizes) if batch_sizes is not None else None
+        hr = hyper_rows.contiguous() if hyper_rows is not None else None
+        check(self.L.mlt_loop_run(self.h, ptr(host_x), ptr(host_y), ptr(idx), _c_ll(steps), _c_int(batch), bs,
+                                  ptr(hr), ptr(o.hyper), _c_int(0), ctypes.byref(call), None, ptr(loss_buf),
+                                  ptr(losses), stream_handle()), "mlt_loop_run")
+        launches.bump("lenet_step", steps)
+        self._finish(steps)
+        return losses
+
+
+def epoch_indices(loader) -> tuple:
+    """Flatten a Loader's batch order into (int64 index tensor, per-step batch sizes)."""
+    batches: List[List[int]] = [list(b) for b in loader.batch_sampler]
+    sizes = [len(b) for b in batches]
+    flat = torch.tensor([i for b in batches for i in b], dtype=torch.int64)
+    pool = getattr(loader, "_pool", None)
+    if pool is not None:
+        flat = flat % pool
+    return flat, sizes

@@ -147,7 +147,8 @@ class Trainer:
         self.reducer = Reducer(self.optimizer, self.comm, bucket_mb=cfg.bucket_mb)
         self.scheduler = self._get_scheduler()
         self.engine = StepEngine(self.model, self.criterion, self.criterion_type, self.metric, self.reducer,
-                                 self.device, graph=cfg.graph, compute_dtype=self.compute_dtype)
+                                 self.device, graph=cfg.graph, compute_dtype=self.compute_dtype,
+                                 fused_step=cfg.fused_step)
         self._snap = SnapshotWriter(self.device)
         if cfg.resume:
             self.load(cfg.resume)
@@ -235,6 +236,51 @@ class Trainer:
         n = max(n, 1.0)
         return loss_sum / n, metric_sum / n
 
+    # ----------------------------------------------------------- native epochs
+    def _native_ok(self, loader, model) -> bool:
+        """Whole-epoch C++ execution: single-kernel step + in-memory tensor dataset of the model's input shape."""
+        f = self.engine.fused
+        if f is None or model is not self.model or not self.cfg.native_loop or not getattr(loader, "_fast", False):
+            return False
+        x, y = loader._backing[0], loader._backing[1]
+        return (x.dtype == torch.float32 and x.dim() == 4 and tuple(x.shape[1:]) == (3, 32, 32) and x.is_contiguous()
+                and y.dtype == torch.int64 and y.dim() == 1 and y.is_contiguous())
+
+    def _native_loop_for(self, loader):
+        from .runtime import NativeLoop
+
+        x, y = loader._backing[0], loader._backing[1]
+        key = (loader.batch_size, x[0].numel() * x.element_size(), y.element_size())
+        if getattr(self, "_nloop_key", None) != key:
+            self._nloop = NativeLoop(self.device, key[0], key[1], key[2], slots=max(self.cfg.prefetch + 1, 3))
+            self._nloop_key = key
+        return self._nloop
+
+    def _run_native_epoch(self, loader, epoch, train: bool):
+        from .runtime import epoch_indices
+
+        eng, opt = self.engine, self.optimizer
+        idx, sizes = epoch_indices(loader)
+        nb = len(sizes)
+        hyper = None
+        if train:
+            rows = []
+            for i in range(nb):          # the LR schedule is evaluated up front, one row of hyper-parameters per step
+                rows.append(opt.hyper_for_next_step(self.reducer.grad_scale).pack())
+                opt.step_count += 1
+                opt._opt_called = True
+                if self.scheduler_type == "CosineAnnealingWarmRestarts":
+                    self.scheduler.step(epoch - 1 + i / nb)  # as per pytorch docs
+            hyper = torch.tensor(rows, dtype=torch.float32)
+        loop = self._native_loop_for(loader)
+        x, y = loader._backing[0], loader._backing[1]
+        losses = loop.run_lenet(eng.fused, x, y, idx, loader.batch_size, sizes, hyper, train, eng.acc,
+                                self.metric == "accuracy", eng._loss_buf)
+        if train:
+            self.last_step_losses = losses
+            self.last_native_stats = dict(loop.last_stats)
+        return nb
+
     def _train_one_epoch(self, epoch):
         self.model.train()
         if self.train_sampler is not None:
@@ -242,10 +288,23 @@ class Trainer:
         eng = self.engine
         eng.reset_accumulators()
         nb = len(self.train_loader)
+        if self._native_ok(self.train_loader, self.model):
+            self._run_native_epoch(self.train_loader, epoch, train=True)
+            if self.scheduler_type == "StepLR":
+                self.scheduler.step()
+            loss, metric = self._reduce_epoch(eng.accumulators())
+            self.train_losses.append(loss)
+            if self.metric:
+                self.train_metrics.append(metric)
+            return
         every = max(int(self.cfg.progress_every), 1)
-        with self._bar(self._feed(self.train_loader), nb) as tepoch:
+        feed = self._feed(self.train_loader)
+        pin_losses = torch.zeros(nb, dtype=torch.float32).pin_memory() if self.device.type == "cuda" else None
+        with self._bar(feed, nb) as tepoch:
             for i, (inputs, targets) in enumerate(tepoch):
                 eng.train_step(inputs, targets)
+                if pin_losses is not None and eng.last_loss is not None:
+                    pin_losses[i].copy_(eng.last_loss, non_blocking=True)      # per-step loss without a sync
                 if self.scheduler_type == "CosineAnnealingWarmRestarts":
                     self.scheduler.step(epoch - 1 + i / nb)  # as per pytorch docs
                 if self.cfg.progress and self.rank == 0 and (i + 1) % every == 0:
@@ -257,6 +316,8 @@ class Trainer:
         if self.scheduler_type == "StepLR":
             self.scheduler.step()
         loss, metric = self._reduce_epoch(eng.accumulators())
+        self.last_step_losses = pin_losses
+        self.last_native_stats = {"h2d_bytes": getattr(feed, "h2d_bytes", 0), "d2h_bytes": 4 * nb, "steps": nb}
         self.train_losses.append(loss)
         if self.metric:
             self.train_metrics.append(metric)
@@ -276,9 +337,12 @@ class Trainer:
         model.eval()
         eng = self.engine
         eng.reset_accumulators()
-        with self._bar(self._feed(loader), len(loader)) as tepoch:
-            for inputs, targets in tepoch:
-                eng.eval_step(model, inputs, targets)
+        if self._native_ok(loader, model):
+            self._run_native_epoch(loader, 0, train=False)
+        else:
+            with self._bar(self._feed(loader), len(loader)) as tepoch:
+                for inputs, targets in tepoch:
+                    eng.eval_step(model, inputs, targets)
         sums = eng.accumulators()
         if reduce and self.world_size > 1:
             sums = self.comm.reduce_scalars(sums)
@@ -383,6 +447,8 @@ class Trainer:
         self.comm.barrier()
         logger.info("Training Complete.")
         return self.history
+
+    train_epoch = _train_one_epoch      # public name for one pass over the training loader
 
     # --------------------------------------------------------------------- test
     @torch.no_grad()

@@ -13,7 +13,7 @@ def _sets():
     return (SyntheticDataset((3, 32, 32), 10, length=256, seed=3), SyntheticDataset((3, 32, 32), 10, length=64, seed=4))
 
 
-def _run(tmp_path, device_is_cuda, graph, optimizer="sgd", epochs=2, metric="accuracy"):
+def _run(tmp_path, device_is_cuda, graph, optimizer="sgd", epochs=2, metric="accuracy", fused_step=False):
     import ml_trainer_b200.trainer as T
     from ml_trainer_b200 import MLModel, Trainer
 
@@ -24,7 +24,7 @@ def _run(tmp_path, device_is_cuda, graph, optimizer="sgd", epochs=2, metric="acc
         torch.cuda.is_available = lambda: False
     try:
         tr = Trainer(model, datasets=_sets(), epochs=epochs, batch_size=32, model_dir=str(tmp_path), progress=False,
-                     optimizer=optimizer, lr=0.01, metric=metric, graph=graph, seed=32)
+                     optimizer=optimizer, lr=0.01, metric=metric, graph=graph, seed=32, fused_step=fused_step)
         # identical batch order on every run
         from ml_trainer_b200 import Loader
         tr.train_loader = Loader(tr.train_loader.dataset, batch_size=32, shuffle=False, pin_memory=device_is_cuda)
@@ -66,6 +66,16 @@ def test_native_kernels_ran_and_loss_falls(tmp_path):
     names = set(_lib.launches.by_name)
     assert {"conv2d_direct_fwd", "conv2d_direct_bwd", "linear_small_fwd", "linear_small_bwd", "softmax_xent",
             "fused_update"} <= names, names
+    assert tr.train_losses[-1] < tr.train_losses[0]
+
+
+def test_default_path_is_the_single_kernel_step(tmp_path):
+    from ml_trainer_b200.ops import _lib
+
+    _lib.launches.reset()
+    tr = _run(tmp_path, True, "auto", epochs=3, fused_step=True)
+    assert tr.engine.fused is not None
+    assert set(_lib.launches.by_name) == {"lenet_step"}, _lib.launches.by_name
     assert tr.train_losses[-1] < tr.train_losses[0]
 
 
