@@ -42,6 +42,8 @@ struct GemmParams {
   long long ld_aux;
   int a_mn, b_mn;
   int num_m, num_n, num_k;
+  int nb1, nb2;                  // batch = nb1 * nb2 independent problems (attention: heads x samples)
+  long long ob1, ob2;            // output batch strides (elements)
 };
 
 template <int BN>
@@ -88,7 +90,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int num_tiles = p.num_m * p.num_n;
+  const int tiles_per_problem = p.num_m * p.num_n;
+  const int num_tiles = tiles_per_problem * p.nb1 * p.nb2;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -112,7 +115,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int m_blk, n_blk;
-        tile_coords(tile, p.num_m, p.num_n, m_blk, n_blk);
+        const int z = tile / tiles_per_problem;
+        tile_coords(tile - z * tiles_per_problem, p.num_m, p.num_n, m_blk, n_blk);
+        const int z1 = z % p.nb1, z2 = z / p.nb1;
         const int m0 = m_blk * BM, n0 = n_blk * BN;
         for (int kb = 0; kb < p.num_k; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
@@ -121,16 +126,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
           const int k0 = kb * BK;
           if (!p.a_mn) {
-            tma_load_2d(sA, &tmA, &full[stage], k0, m0);                       // box {64 k, 128 rows}
+            tma_load_4d(sA, &tmA, &full[stage], k0, m0, z1, z2);                       // box {64 k, 128 rows}
           } else {
 #pragma unroll
-            for (int j = 0; j < BM / 64; ++j) tma_load_2d(sA + j * 8192, &tmA, &full[stage], m0 + 64 * j, k0);   // box {64 rows, 64 k}
+            for (int j = 0; j < BM / 64; ++j) tma_load_4d(sA + j * 8192, &tmA, &full[stage], m0 + 64 * j, k0, z1, z2);   // box {64 rows, 64 k}
           }
           if (!p.b_mn) {
-            tma_load_2d(sB, &tmB, &full[stage], k0, n0);                       // box {64 k, BN rows}
+            tma_load_4d(sB, &tmB, &full[stage], k0, n0, z1, z2);                       // box {64 k, BN rows}
           } else {
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j) tma_load_2d(sB + j * 8192, &tmB, &full[stage], n0 + 64 * j, k0);
+            for (int j = 0; j < BN / 64; ++j) tma_load_4d(sB + j * 8192, &tmB, &full[stage], n0 + 64 * j, k0, z1, z2);
           }
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
@@ -174,7 +179,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     int as = 0; uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
-      tile_coords(tile, p.num_m, p.num_n, m_blk, n_blk);
+      const int z = tile / tiles_per_problem;
+      tile_coords(tile - z * tiles_per_problem, p.num_m, p.num_n, m_blk, n_blk);
+      const size_t obase = (size_t)(z % p.nb1) * p.ob1 + (size_t)(z / p.nb1) * p.ob2;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * BN;
       mbar_wait(&tmem_full[as], aphase);
@@ -226,7 +233,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             for (int j = 0; j < 32; ++j) v[j] = act_fwd_rt(p.act, v[j]);
           }
           if (p.out_f32) {
-            float* op = reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + nb;
+            float* op = reinterpret_cast<float*>(p.out) + obase + (size_t)row * p.ldo + nb;
             if (full_chunk) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
@@ -234,7 +241,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               for (int j = 0; j < 32 && nb + j < p.N; ++j) op[j] = v[j];
             }
           } else {
-            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + nb;
+            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + obase + (size_t)row * p.ldo + nb;
             if (full_chunk) {
 #pragma unroll
               for (int j = 0; j < 32; j += 8) {
@@ -277,22 +284,27 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
-// 2-D bf16 tensor [outer][inner] with row stride `ld` elements, box {box_inner, box_outer}, 128-byte swizzle.
+// bf16 tensor [b2][b1][outer][inner] with strides (elements) ld / s1 / s2, box {box_inner, box_outer, 1, 1}, 128B swizzle.
 static int make_tmap(CUtensorMap* out, const void* base, long long inner, long long outer, long long ld, int box_inner,
-                     int box_outer) {
+                     int box_outer, int nb1 = 1, long long s1 = 0, int nb2 = 1, long long s2 = 0) {
   EncodeTiledFn enc = get_encode();
   MLT_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
-  MLT_REQUIRE(((uintptr_t)base % 16) == 0 && (ld * 2) % 16 == 0,
-              "TMA needs a 16-byte aligned base and a row stride that is a multiple of 8 bf16 elements (ld=%lld)", ld);
-  cuuint64_t dims[2] = {(cuuint64_t)inner, (cuuint64_t)outer};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  if (nb1 <= 1) { nb1 = 1; s1 = ld * outer; }
+  if (nb2 <= 1) { nb2 = 1; s2 = s1 * nb1; }
+  if (s1 % 8 != 0) s1 = (s1 + 7) / 8 * 8;          // only reachable for size-1 batch dims (stride never used)
+  if (s2 % 8 != 0) s2 = (s2 + 7) / 8 * 8;
+  MLT_REQUIRE(((uintptr_t)base % 16) == 0 && (ld * 2) % 16 == 0 && (s1 * 2) % 16 == 0 && (s2 * 2) % 16 == 0,
+              "TMA needs a 16-byte aligned base and strides that are multiples of 8 bf16 elements (ld=%lld s1=%lld s2=%lld)",
+              ld, s1, s2);
+  cuuint64_t dims[4] = {(cuuint64_t)inner, (cuuint64_t)outer, (cuuint64_t)nb1, (cuuint64_t)nb2};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)s1 * 2, (cuuint64_t)s2 * 2};
+  cuuint32_t box[4] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  MLT_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%lld outer=%lld ld=%lld box=%dx%d)",
-              (int)r, inner, outer, ld, box_inner, box_outer);
+  MLT_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%lld outer=%lld ld=%lld box=%dx%d nb=%dx%d)",
+              (int)r, inner, outer, ld, box_inner, box_outer, nb1, nb2);
   return 0;
 }
 
@@ -310,8 +322,8 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParam
     MLT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set[dev & 63] = true;
   }
-  int grid = p.num_m * p.num_n;
-  if (grid > kNumSMs) grid = kNumSMs;
+  long long tiles = (long long)p.num_m * p.num_n * p.nb1 * p.nb2;
+  int grid = tiles > kNumSMs ? kNumSMs : (int)tiles;
   kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
   MLT_LAUNCH_CHECK();
   return 0;
@@ -345,6 +357,38 @@ extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   p.bias = bias; p.bias_f32 = bias_f32; p.act = act;
   p.aux_mode = aux_mode; p.aux = aux; p.ld_aux = ld_aux;
   p.a_mn = a_mn; p.b_mn = b_mn;
+  p.nb1 = p.nb2 = 1; p.ob1 = p.ob2 = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
+  if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
+  return launch_gemm<64>(tmA, tmB, p, st);
+}
+
+// Batched variant: nb1 * nb2 independent problems that share M, N, K.  Operand z = (z1, z2) starts at
+// base + z1 * s1 + z2 * s2 (elements); two batch strides cover attention's [batch, seq, head, dim] layouts without copies.
+extern "C" int mlt_gemm_bf16_batched(const void* A, long long lda, long long a_s1, long long a_s2, int a_mn, const void* B,
+                                     long long ldb, long long b_s1, long long b_s2, int b_mn, void* out, long long ldo,
+                                     long long o_s1, long long o_s2, int out_f32, int M, int N, int K, int nb1, int nb2,
+                                     int block_n, void* stream) {
+  MLT_REQUIRE(M > 0 && N > 0 && K > 0 && nb1 > 0 && nb2 > 0, "mlt_gemm_bf16_batched: empty problem");
+  const int esz = out_f32 ? 4 : 2;
+  MLT_REQUIRE(((uintptr_t)out % 16) == 0 && (ldo * esz) % 16 == 0 && (o_s1 * esz) % 16 == 0 && (o_s2 * esz) % 16 == 0,
+              "mlt_gemm_bf16_batched: output base and strides must be 16-byte multiples");
+  int BN = block_n;
+  if (BN == 0) BN = (N >= 512 || (N % 256 == 0)) ? 256 : (N > 64 ? 128 : 64);
+  MLT_REQUIRE(BN == 64 || BN == 128 || BN == 256, "mlt_gemm_bf16_batched: block_n must be 0, 64, 128 or 256");
+  CUtensorMap tmA, tmB;
+  if (!a_mn) { if (make_tmap(&tmA, A, K, M, lda, BK, BM, nb1, a_s1, nb2, a_s2)) return 1; }
+  else       { if (make_tmap(&tmA, A, M, K, lda, 64, BK, nb1, a_s1, nb2, a_s2)) return 1; }
+  if (!b_mn) { if (make_tmap(&tmB, B, K, N, ldb, BK, BN, nb1, b_s1, nb2, b_s2)) return 1; }
+  else       { if (make_tmap(&tmB, B, N, K, ldb, 64, BK, nb1, b_s1, nb2, b_s2)) return 1; }
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.out = out; p.ldo = ldo; p.out_f32 = out_f32;
+  p.bias = nullptr; p.bias_f32 = 0; p.act = ACT_NONE;
+  p.aux_mode = 0; p.aux = nullptr; p.ld_aux = 0;
+  p.a_mn = a_mn; p.b_mn = b_mn;
+  p.nb1 = nb1; p.nb2 = nb2; p.ob1 = o_s1; p.ob2 = o_s2;
   cudaStream_t st = (cudaStream_t)stream;
   if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
   if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);

@@ -258,21 +258,22 @@ conv2d_direct_dgrad_kernel(const float* __restrict__ dy, const float* __restrict
 // =====================================================================================================
 constexpr int kLinRows = 4;
 
+template <typename T>
 __global__ void __launch_bounds__(256)
-linear_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                        float* __restrict__ y, int B, int K, int N, int act) {
+linear_small_fwd_kernel(const T* __restrict__ x, const T* __restrict__ w, const T* __restrict__ bias,
+                        T* __restrict__ y, int B, int K, int N, int act) {
   const int lane = threadIdx.x & 31;
   const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int row_tiles = ceil_div(B, kLinRows);
   if (gw >= N * row_tiles) return;
   const int n = gw % N, b0 = (gw / N) * kLinRows;
-  const float* wr = w + (size_t)n * K;
+  const T* wr = w + (size_t)n * K;
   float acc[kLinRows] = {0.f, 0.f, 0.f, 0.f};
   for (int k = lane; k < K; k += 32) {
-    const float wv = wr[k];
+    const float wv = to_float(wr[k]);
 #pragma unroll
     for (int r = 0; r < kLinRows; ++r)
-      if (b0 + r < B) acc[r] = fmaf(wv, x[(size_t)(b0 + r) * K + k], acc[r]);
+      if (b0 + r < B) acc[r] = fmaf(wv, to_float(x[(size_t)(b0 + r) * K + k]), acc[r]);
   }
 #pragma unroll
   for (int r = 0; r < kLinRows; ++r) acc[r] = warp_sum(acc[r]);
@@ -280,8 +281,8 @@ linear_small_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w
     float v = acc[0];
 #pragma unroll
     for (int r = 1; r < kLinRows; ++r) if (lane == r) v = acc[r];
-    v += bias ? bias[n] : 0.f;
-    y[(size_t)(b0 + lane) * N + n] = act_fwd_rt(act, v);
+    v += bias ? to_float(bias[n]) : 0.f;
+    y[(size_t)(b0 + lane) * N + n] = from_float<T>(act_fwd_rt(act, v));
   }
 }
 
@@ -295,32 +296,34 @@ __device__ __forceinline__ float act_grad_from_y(int act, float yv) {
 
 // blocks [0, nbx): dx[b,k] = sum_n dz[b,n] w[n,k]      (skipped when dx == nullptr)
 // blocks [nbx, ..): dw[n,k] = sum_b dz[b,n] x[b,k];  db[n] = sum_b dz[b,n]
+// T: activation / weight dtype, G: gradient-sink dtype (the flat gradient arena's)
+template <typename T, typename G>
 __global__ void __launch_bounds__(256)
-linear_small_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, const float* __restrict__ x,
-                        const float* __restrict__ w, float* __restrict__ dx, float* __restrict__ dw,
-                        float* __restrict__ db, int B, int K, int N, int act, int nbx, int accumulate) {
+linear_small_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x,
+                        const T* __restrict__ w, T* __restrict__ dx, G* __restrict__ dw,
+                        G* __restrict__ db, int B, int K, int N, int act, int nbx, int accumulate) {
   if ((int)blockIdx.x < nbx) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= B * K) return;
     const int b = i / K, k = i - b * K;
     float a = 0.f;
     for (int n = 0; n < N; ++n) {
-      const float dz = dy[(size_t)b * N + n] * act_grad_from_y(act, y[(size_t)b * N + n]);
-      a = fmaf(dz, w[(size_t)n * K + k], a);
+      const float dz = to_float(dy[(size_t)b * N + n]) * act_grad_from_y(act, to_float(y[(size_t)b * N + n]));
+      a = fmaf(dz, to_float(w[(size_t)n * K + k]), a);
     }
-    dx[i] = a;
+    dx[i] = from_float<T>(a);
   } else {
     const int i = (blockIdx.x - nbx) * blockDim.x + threadIdx.x;
     if (i >= N * K) return;
     const int n = i / K, k = i - n * K;
     float a = 0.f, s = 0.f;
     for (int b = 0; b < B; ++b) {
-      const float dz = dy[(size_t)b * N + n] * act_grad_from_y(act, y[(size_t)b * N + n]);
-      a = fmaf(dz, x[(size_t)b * K + k], a);
+      const float dz = to_float(dy[(size_t)b * N + n]) * act_grad_from_y(act, to_float(y[(size_t)b * N + n]));
+      a = fmaf(dz, to_float(x[(size_t)b * K + k]), a);
       s += dz;
     }
-    dw[i] = (accumulate ? dw[i] : 0.f) + a;
-    if (k == 0 && db) db[n] = (accumulate ? db[n] : 0.f) + s;
+    dw[i] = from_float<G>((accumulate ? to_float(dw[i]) : 0.f) + a);
+    if (k == 0 && db) db[n] = from_float<G>((accumulate ? to_float(db[n]) : 0.f) + s);
   }
 }
 
@@ -433,25 +436,36 @@ extern "C" int mlt_conv2d_direct_bwd(const void* x, const void* w, const void* d
   return 0;
 }
 
+// dtype: 0 = fp32 tensors, 1 = bf16 tensors (weights, activations); grads_bf16 tells the dtype of dw / db.
 extern "C" int mlt_linear_small_fwd(const void* x, const void* w, const void* bias, void* y, int B, int K, int N, int act,
-                                    void* stream) {
+                                    int is_bf16, void* stream) {
   MLT_REQUIRE(act == ACT_NONE || act == ACT_RELU || act == ACT_TANH, "mlt_linear_small_fwd: unsupported activation %d", act);
   const long long warps = (long long)N * ceil_div(B, kLinRows);
   const int grid = (int)ceil_div64(warps * 32, 256);
-  linear_small_fwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, (const float*)w, (const float*)bias,
-                                                                  (float*)y, B, K, N, act);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (is_bf16)
+    linear_small_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (const __nv_bfloat16*)w,
+                                                                 (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, B, K, N, act);
+  else
+    linear_small_fwd_kernel<float><<<grid, 256, 0, st>>>((const float*)x, (const float*)w, (const float*)bias, (float*)y, B, K, N, act);
   MLT_LAUNCH_CHECK();
   return 0;
 }
 
 extern "C" int mlt_linear_small_bwd(const void* dy, const void* y, const void* x, const void* w, void* dx, void* dw, void* db,
-                                    int B, int K, int N, int act, int accumulate, void* stream) {
+                                    int B, int K, int N, int act, int accumulate, int is_bf16, int grads_bf16, void* stream) {
   MLT_REQUIRE(act == ACT_NONE || act == ACT_RELU || act == ACT_TANH, "mlt_linear_small_bwd: unsupported activation %d", act);
+  MLT_REQUIRE(is_bf16 || !grads_bf16, "mlt_linear_small_bwd: fp32 tensors with bf16 gradient sinks is not a supported mix");
   const int nbx = dx ? ceil_div(B * K, 256) : 0;
   const int nbw = ceil_div(N * K, 256);
-  linear_small_bwd_kernel<<<nbx + nbw, 256, 0, (cudaStream_t)stream>>>(
-      (const float*)dy, (const float*)y, (const float*)x, (const float*)w, (float*)dx, (float*)dw, (float*)db, B, K, N, act,
-      nbx, accumulate);
+  cudaStream_t st = (cudaStream_t)stream;
+#define LSB(T, G)                                                                                                          \
+  linear_small_bwd_kernel<T, G><<<nbx + nbw, 256, 0, st>>>((const T*)dy, (const T*)y, (const T*)x, (const T*)w, (T*)dx, (G*)dw, \
+                                                           (G*)db, B, K, N, act, nbx, accumulate)
+  if (!is_bf16) LSB(float, float);
+  else if (grads_bf16) LSB(__nv_bfloat16, __nv_bfloat16);
+  else LSB(__nv_bfloat16, float);
+#undef LSB
   MLT_LAUNCH_CHECK();
   return 0;
 }

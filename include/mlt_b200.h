@@ -71,10 +71,11 @@ int mlt_conv2d_direct_bwd(const void* x, const void* w, const void* dy, const vo
 int mlt_conv2d_direct_bwd_noalloc(const void* x, const void* w, const void* dy, const void* y, const void* pool_idx,
                                   void* dx, void* dw, void* db, int B, int Cin, int H, int W, int Cout, int KH, int KW,
                                   int relu, int pool, int accumulate, void* stream);
+/* is_bf16: dtype of x / w / bias / y (0 fp32, 1 bf16); grads_bf16: dtype of the dw / db sinks. */
 int mlt_linear_small_fwd(const void* x, const void* w, const void* bias, void* y, int B, int K, int N, int act,
-                         void* stream);
+                         int is_bf16, void* stream);
 int mlt_linear_small_bwd(const void* dy, const void* y, const void* x, const void* w, void* dx, void* dw, void* db,
-                         int B, int K, int N, int act, int accumulate, void* stream);
+                         int B, int K, int N, int act, int accumulate, int is_bf16, int grads_bf16, void* stream);
 
 /* ---- tensor-core GEMM: the cuBLAS calls behind nn.Linear (src/model.py:21-23) and every BERT / ResNet-FC GEMM ------ */
 /* D[M,N] = A * B^T on tcgen05 (bf16 in, fp32 accumulate in TMEM, TMA-fed), fused epilogue:
@@ -85,6 +86,11 @@ int mlt_linear_small_bwd(const void* dy, const void* y, const void* x, const voi
 int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out,
                   long long ldo, int out_f32, int M, int N, int K, const void* bias, int bias_f32, int act, int aux_mode,
                   void* aux, long long ld_aux, int block_n, void* stream);
+
+/* nb1*nb2 independent GEMMs sharing M,N,K; operand (z1,z2) starts at base + z1*s1 + z2*s2 elements (attention heads). */
+int mlt_gemm_bf16_batched(const void* A, long long lda, long long a_s1, long long a_s2, int a_mn, const void* B,
+                          long long ldb, long long b_s1, long long b_s2, int b_mn, void* out, long long ldo, long long o_s1,
+                          long long o_s2, int out_f32, int M, int N, int K, int nb1, int nb2, int block_n, void* stream);
 
 /* ---- bandwidth-bound helpers around the GEMMs (ATen elementwise / sum kernels in the reference's backward) ------- */
 int mlt_act_backward(const void* dy, const void* saved, void* dz, long long n, int act, int from_pre, int is_bf16,
@@ -163,6 +169,21 @@ int mlt_loop_run(void* loop, const void* host_x, const void* host_y, const long 
                  const int* batch_sizes, const float* hyper_rows, void* hyper_dev, int step_kind, const mlt_lenet_call* lenet,
                  void* const* graph_execs, const void* loss_dev, float* loss_host, void* compute_stream);
 int mlt_loop_stats(void* loop, long long* h2d_bytes, long long* d2h_bytes, long long* launches);
+
+/* ---- transformer pieces: ATen layer_norm / softmax / embedding kernels of the BERT workload --------------------- */
+/* y = LN(x [+ res]) * gamma + beta (bf16 activations; gamma/beta fp32 or bf16); hsum (optional) receives x + res. */
+int mlt_layernorm_fwd(const void* x, const void* res, const void* gamma, const void* beta, int params_bf16, void* y,
+                      void* hsum, void* mean, void* rstd, int T, int H, float eps, void* stream);
+long long mlt_layernorm_bwd_scratch_bytes(int T, int H);
+int mlt_layernorm_bwd(const void* dy, const void* h, const void* mean, const void* rstd, const void* gamma, int params_bf16,
+                      void* dx, void* dgamma, void* dbeta, int grads_bf16, void* scratch, long long scratch_bytes, int T,
+                      int H, void* stream);
+int mlt_softmax_rows(void* scores_bf16, long long rows, int L, float scale, void* stream);               /* in place */
+int mlt_softmax_rows_bwd(void* dp_bf16, const void* p_bf16, long long rows, int L, float scale, void* stream);
+int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
+                          void* out_bf16, int T, int S, int H, void* stream);
+int mlt_embedding_bwd(const void* ids_i64, const void* dh_bf16, void* dword, long long V, void* dpos, int grads_bf16, int B,
+                      int S, int H, void* stream);
 
 #ifdef __cplusplus
 }

@@ -15,11 +15,16 @@ def register(name):
 
 def build_model(name: str, **kw):
     name = name.lower()
-    if name in ("resnet50", "resnet-50") and "resnet50" not in _REGISTRY:
-        from . import resnet  # noqa: F401  (registers itself)
-    if name in ("bert_base", "bert-base", "bert") and "bert_base" not in _REGISTRY:
-        from . import bert  # noqa: F401
     name = {"resnet-50": "resnet50", "bert-base": "bert_base", "bert": "bert_base"}.get(name, name)
+    if name not in _REGISTRY:                  # the larger model families register themselves on import
+        import importlib
+
+        for mod in ("bert", "resnet"):
+            if name.startswith(mod):
+                try:
+                    importlib.import_module(f"{__name__}.{mod}")
+                except ImportError:
+                    pass
     if name not in _REGISTRY:
         raise KeyError(f"unknown model {name!r}; known: {sorted(_REGISTRY)}")
     return _REGISTRY[name](**kw)

@@ -1,0 +1,192 @@
+"""BERT-base sequence classification (BASELINE.json config 4), written against the op library.
+
+Parameter names and shapes follow HuggingFace ``BertForSequenceClassification`` exactly
+(``bert.embeddings.word_embeddings.weight`` ... ``classifier.bias``; 109,483,778 parameters for the
+base config with 2 labels), so state dicts move between the two implementations unchanged and the
+HF model is the numerical oracle in the tests.  Forward takes ``input_ids [B, S]`` and returns logits.
+
+Hot ops ("BERT-base"): QKV / output / FFN GEMMs on tcgen05 with bias (+GELU, +pre-activation
+for backward) in the epilogue; attention as batched tcgen05 GEMMs + fused row softmax; residual+LayerNorm fused;
+embedding gather-sum.  Dropout is identity here (p = 0): the benchmark configures the reference the same way.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+from torch import nn
+
+from ..ops import functional as F
+from . import register
+
+
+class BertConfig:
+    def __init__(self, vocab_size=30522, hidden_size=768, num_hidden_layers=12, num_attention_heads=12,
+                 intermediate_size=3072, max_position_embeddings=512, type_vocab_size=2, layer_norm_eps=1e-12,
+                 num_labels=2, initializer_range=0.02):
+        self.vocab_size, self.hidden_size, self.num_hidden_layers = vocab_size, hidden_size, num_hidden_layers
+        self.num_attention_heads, self.intermediate_size = num_attention_heads, intermediate_size
+        self.max_position_embeddings, self.type_vocab_size = max_position_embeddings, type_vocab_size
+        self.layer_norm_eps, self.num_labels, self.initializer_range = layer_norm_eps, num_labels, initializer_range
+
+
+class _LN(nn.Module):
+    """Holder with HF's ``LayerNorm.weight`` / ``LayerNorm.bias`` names."""
+
+    def __init__(self, h, eps):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(h))
+        self.bias = nn.Parameter(torch.zeros(h))
+        self.eps = eps
+
+    def forward(self, x, residual=None):
+        return F.layer_norm(x, self.weight, self.bias, self.eps, residual=residual)
+
+
+class BertEmbeddings(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.word_embeddings = nn.Embedding(c.vocab_size, c.hidden_size)
+        self.position_embeddings = nn.Embedding(c.max_position_embeddings, c.hidden_size)
+        self.token_type_embeddings = nn.Embedding(c.type_vocab_size, c.hidden_size)
+        self.LayerNorm = _LN(c.hidden_size, c.layer_norm_eps)
+
+    def forward(self, ids):
+        h = F.bert_embeddings(ids, self.word_embeddings.weight, self.position_embeddings.weight,
+                              self.token_type_embeddings.weight)
+        return self.LayerNorm(h)
+
+
+class BertSelfAttention(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.query = nn.Linear(c.hidden_size, c.hidden_size)
+        self.key = nn.Linear(c.hidden_size, c.hidden_size)
+        self.value = nn.Linear(c.hidden_size, c.hidden_size)
+        self.heads = c.num_attention_heads
+
+    def forward(self, x):
+        q = F.linear_act(x, self.query.weight, self.query.bias)
+        k = F.linear_act(x, self.key.weight, self.key.bias)
+        v = F.linear_act(x, self.value.weight, self.value.bias)
+        return F.attention(q, k, v, self.heads)
+
+
+class BertSelfOutput(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.dense = nn.Linear(c.hidden_size, c.hidden_size)
+        self.LayerNorm = _LN(c.hidden_size, c.layer_norm_eps)
+
+    def forward(self, ctx, x):
+        return self.LayerNorm(F.linear_act(ctx, self.dense.weight, self.dense.bias), residual=x)
+
+
+class BertAttention(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.self = BertSelfAttention(c)
+        self.output = BertSelfOutput(c)
+
+    def forward(self, x):
+        return self.output(self.self(x), x)
+
+
+class BertIntermediate(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.dense = nn.Linear(c.hidden_size, c.intermediate_size)
+
+    def forward(self, x):
+        return F.linear_act(x, self.dense.weight, self.dense.bias, "gelu")
+
+
+class BertOutput(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.dense = nn.Linear(c.intermediate_size, c.hidden_size)
+        self.LayerNorm = _LN(c.hidden_size, c.layer_norm_eps)
+
+    def forward(self, f, x):
+        return self.LayerNorm(F.linear_act(f, self.dense.weight, self.dense.bias), residual=x)
+
+
+class BertLayer(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.attention = BertAttention(c)
+        self.intermediate = BertIntermediate(c)
+        self.output = BertOutput(c)
+
+    def forward(self, x):
+        a = self.attention(x)
+        return self.output(self.intermediate(a), a)
+
+
+class BertEncoder(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.layer = nn.ModuleList([BertLayer(c) for _ in range(c.num_hidden_layers)])
+
+    def forward(self, x):
+        for l in self.layer:
+            x = l(x)
+        return x
+
+
+class BertPooler(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.dense = nn.Linear(c.hidden_size, c.hidden_size)
+
+    def forward(self, x):
+        return F.linear_act(x[:, 0].contiguous(), self.dense.weight, self.dense.bias, "tanh")
+
+
+class BertModel(nn.Module):
+    def __init__(self, c):
+        super().__init__()
+        self.embeddings = BertEmbeddings(c)
+        self.encoder = BertEncoder(c)
+        self.pooler = BertPooler(c)
+
+    def forward(self, ids):
+        return self.pooler(self.encoder(self.embeddings(ids)))
+
+
+class BertForSequenceClassification(nn.Module):
+    _mlt_native = True
+
+    def __init__(self, config: BertConfig = None, **kw):
+        super().__init__()
+        c = self.config = config or BertConfig(**kw)
+        self.bert = BertModel(c)
+        self.classifier = nn.Linear(c.hidden_size, c.num_labels)
+        self.apply(self._init_weights)
+
+    def _init_weights(self, m):
+        std = self.config.initializer_range
+        if isinstance(m, nn.Linear):
+            nn.init.normal_(m.weight, mean=0.0, std=std)
+            if m.bias is not None:
+                nn.init.zeros_(m.bias)
+        elif isinstance(m, nn.Embedding):
+            nn.init.normal_(m.weight, mean=0.0, std=std)
+
+    def forward(self, input_ids):
+        pooled = self.bert(input_ids)
+        return F.linear_act(pooled, self.classifier.weight, self.classifier.bias).float()
+
+
+@register("bert_base")
+def bert_base(num_labels: int = 2, **kw):
+    return BertForSequenceClassification(BertConfig(num_labels=num_labels, **kw))
+
+
+@register("bert_tiny")
+def bert_tiny(num_labels: int = 2, **kw):
+    """2-layer, 128-wide configuration for tests."""
+    cfg = dict(vocab_size=1000, hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512,
+               max_position_embeddings=128)
+    cfg.update(kw)
+    return BertForSequenceClassification(BertConfig(num_labels=num_labels, **cfg))

@@ -239,14 +239,17 @@ def _has_sink(p) -> bool:
 
 
 class _LinearSmallFn(torch.autograd.Function):
+    """CUDA-core linear for shapes far below a tensor-core tile (fp32 or bf16 tensors)."""
+
     @staticmethod
     def forward(ctx, x, weight, bias, act, wparam, bparam):
         B, K = x.shape
         N = weight.shape[0]
         x = x.contiguous()
-        y = torch.empty((B, N), dtype=torch.float32, device=x.device)
+        y = torch.empty((B, N), dtype=x.dtype, device=x.device)
+        bf16 = int(x.dtype == torch.bfloat16)
         check(_lib.lib().mlt_linear_small_fwd(ptr(x), ptr(weight), ptr(bias), ptr(y), _c_int(B), _c_int(K), _c_int(N),
-                                              _c_int(act), stream_handle()), "mlt_linear_small_fwd")
+                                              _c_int(act), _c_int(bf16), stream_handle()), "mlt_linear_small_fwd")
         launches.bump("linear_small_fwd")
         ctx.save_for_backward(x, weight, y)
         ctx.cfg = (act, bias is not None)
@@ -264,11 +267,13 @@ class _LinearSmallFn(torch.autograd.Function):
         need_dx = ctx.needs_input_grad[0]
         dx = torch.empty_like(x) if need_dx else None
         wsink, bsink = _sink(wparam), _sink(bparam) if has_bias else None
-        dw = wsink if wsink is not None else torch.empty_like(weight)
-        db = (bsink if bsink is not None else torch.empty(N, dtype=torch.float32, device=x.device)) if has_bias else None
+        gdt = wsink.dtype if wsink is not None else weight.dtype
+        dw = wsink if wsink is not None else torch.empty(weight.shape, dtype=gdt, device=x.device)
+        db = (bsink if bsink is not None else torch.empty(N, dtype=gdt, device=x.device)) if has_bias else None
         check(_lib.lib().mlt_linear_small_bwd(ptr(dy), ptr(y), ptr(x), ptr(weight), ptr(dx), ptr(dw), ptr(db), _c_int(B),
-                                              _c_int(K), _c_int(N), _c_int(act), _c_int(0), stream_handle()),
-              "mlt_linear_small_bwd")
+                                              _c_int(K), _c_int(N), _c_int(act), _c_int(0),
+                                              _c_int(int(x.dtype == torch.bfloat16)), _c_int(int(gdt == torch.bfloat16)),
+                                              stream_handle()), "mlt_linear_small_bwd")
         launches.bump("linear_small_bwd")
         return dx, _deliver(wparam, dw, wsink), (_deliver(bparam, db, bsink) if has_bias else None), None, None, None
 
@@ -289,7 +294,9 @@ def linear_act(x, weight, bias=None, act: Optional[str] = None):
         x2 = x.reshape(-1, x.shape[-1])
         B, K = x2.shape
         N = weight.shape[0]
-        if x.dtype == torch.float32 and act in (None, "none", "relu", "tanh") and B * K * N <= SMALL_LINEAR_MAX:
+        small_ok = x.dtype in (torch.float32, torch.bfloat16) and weight.dtype == x.dtype and \
+            (bias is None or bias.dtype == x.dtype) and act in (None, "none", "relu", "tanh")
+        if small_ok and (B * K * N <= SMALL_LINEAR_MAX or (x.dtype == torch.bfloat16 and (N % 8 != 0 or K % 8 != 0))):
             a = ACT_IDS[act]
             if _has_sink(weight):
                 y = _LinearSmallFn.apply(x2, weight.detach(), None if bias is None else bias.detach(), a, weight, bias)
@@ -348,3 +355,174 @@ def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         out.copy_(r)
         return out
     return r.to(x.dtype)
+
+
+# ----------------------------------------------------------------------------------------------
+# transformer pieces: LayerNorm (+ residual), attention core, embeddings  (bf16 activations)
+# ----------------------------------------------------------------------------------------------
+class _LayerNormFn(torch.autograd.Function):
+    """``LN(x [+ residual]) * gamma + beta``; the residual add is fused, its gradient is the LN input gradient."""
+
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, eps, gparam, bparam):
+        H = x.shape[-1]
+        x2 = x.reshape(-1, H).contiguous()
+        r2 = residual.reshape(-1, H).contiguous() if residual is not None else None
+        T = x2.shape[0]
+        y = torch.empty_like(x2)
+        hsum = torch.empty_like(x2) if r2 is not None else None
+        mean = torch.empty(T, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(T, dtype=torch.float32, device=x.device)
+        check(_lib.lib().mlt_layernorm_fwd(ptr(x2), ptr(r2), ptr(gamma), ptr(beta), _c_int(int(gamma.dtype == torch.bfloat16)),
+                                           ptr(y), ptr(hsum), ptr(mean), ptr(rstd), _c_int(T), _c_int(H),
+                                           ctypes.c_float(eps), stream_handle()), "mlt_layernorm_fwd")
+        launches.bump("layernorm_fwd")
+        ctx.save_for_backward(hsum if hsum is not None else x2, mean, rstd, gamma)
+        ctx.shape = x.shape
+        ctx.has_res = residual is not None
+        ctx.params = (gparam, bparam)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        h, mean, rstd, gamma = ctx.saved_tensors
+        gparam, bparam = ctx.params
+        T, H = h.shape
+        dy2 = dy.reshape(T, H).contiguous()
+        dx = torch.empty_like(h)
+        gsink, bsink = _sink(gparam), _sink(bparam)
+        gdt = gsink.dtype if gsink is not None else gamma.dtype
+        dg = gsink if gsink is not None else torch.empty(H, dtype=gdt, device=h.device)
+        db = bsink if bsink is not None else torch.empty(H, dtype=gdt, device=h.device)
+        L = _lib.lib()
+        L.mlt_layernorm_bwd_scratch_bytes.restype = _c_ll
+        ws = scratch(h.device, "ln_bwd", L.mlt_layernorm_bwd_scratch_bytes(_c_int(T), _c_int(H)))
+        check(L.mlt_layernorm_bwd(ptr(dy2), ptr(h), ptr(mean), ptr(rstd), ptr(gamma), _c_int(int(gamma.dtype == torch.bfloat16)),
+                                  ptr(dx), ptr(dg), ptr(db), _c_int(int(gdt == torch.bfloat16)), ptr(ws), _c_ll(ws.numel()),
+                                  _c_int(T), _c_int(H), stream_handle()), "mlt_layernorm_bwd")
+        launches.bump("layernorm_bwd")
+        dxv = dx.view(ctx.shape)
+        return dxv, (dxv if ctx.has_res else None), _deliver(gparam, dg, gsink), _deliver(bparam, db, bsink), None, None, None
+
+
+def layer_norm(x, gamma, beta, eps: float = 1e-12, residual=None):
+    H = x.shape[-1]
+    if use_native(x, gamma) and x.dtype == torch.bfloat16 and H % 8 == 0 and H <= 1024 and gamma.dtype in (torch.bfloat16, torch.float32):
+        if _has_sink(gamma):
+            return _LayerNormFn.apply(x, residual, gamma.detach(), beta.detach(), eps, gamma, beta)
+        return _LayerNormFn.apply(x, residual, gamma, beta, eps, None, None)
+    h = x if residual is None else x + residual
+    return TF.layer_norm(h.float(), (H,), gamma.float(), beta.float(), eps).to(x.dtype)
+
+
+class _AttentionFn(torch.autograd.Function):
+    """softmax(Q K^T / sqrt(d)) V per (sample, head) as batched tcgen05 GEMMs + row-softmax kernels.
+
+    q, k, v: [B, S, heads*d] bf16 (row stride = heads*d); output the same layout.  P is kept for backward.
+    """
+
+    @staticmethod
+    def forward(ctx, q, k, v, heads):
+        from .gemm import gemm_batched
+
+        B, S, HD = q.shape
+        d = HD // heads
+        scale = 1.0 / (d ** 0.5)
+        q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+        P = torch.empty((B, heads, S, S), dtype=torch.bfloat16, device=q.device)
+        # scores[b,h] = Q[b,:,h,:] K[b,:,h,:]^T          operand (z1 = head, z2 = sample)
+        gemm_batched(q, HD, d, S * HD, False, k, HD, d, S * HD, False, P, S, S * S, heads * S * S, S, S, d, heads, B)
+        check(_lib.lib().mlt_softmax_rows(ptr(P), _c_ll(B * heads * S), _c_int(S), ctypes.c_float(scale), stream_handle()),
+              "mlt_softmax_rows")
+        launches.bump("softmax_rows")
+        ctxt = torch.empty_like(q)
+        # out[b,:,h,:] = P[b,h] V[b,:,h,:]               B operand stored [keys][d]: MN-major
+        gemm_batched(P, S, S * S, heads * S * S, False, v, HD, d, S * HD, True, ctxt, HD, d, S * HD, S, d, S, heads, B)
+        ctx.save_for_backward(q, k, v, P)
+        ctx.cfg = (heads, scale)
+        return ctxt
+
+    @staticmethod
+    def backward(ctx, do):
+        from .gemm import gemm_batched
+
+        q, k, v, P = ctx.saved_tensors
+        heads, scale = ctx.cfg
+        B, S, HD = q.shape
+        d = HD // heads
+        do = do.contiguous()
+        L = _lib.lib()
+        dP = torch.empty_like(P)
+        # dP = dO V^T
+        gemm_batched(do, HD, d, S * HD, False, v, HD, d, S * HD, False, dP, S, S * S, heads * S * S, S, S, d, heads, B)
+        # dV = P^T dO
+        dv = torch.empty_like(v)
+        gemm_batched(P, S, S * S, heads * S * S, True, do, HD, d, S * HD, True, dv, HD, d, S * HD, S, d, S, heads, B)
+        check(L.mlt_softmax_rows_bwd(ptr(dP), ptr(P), _c_ll(B * heads * S), _c_int(S), ctypes.c_float(scale), stream_handle()),
+              "mlt_softmax_rows_bwd")
+        launches.bump("softmax_rows_bwd")
+        # dQ = dS K ;  dK = dS^T Q
+        dq, dk = torch.empty_like(q), torch.empty_like(k)
+        gemm_batched(dP, S, S * S, heads * S * S, False, k, HD, d, S * HD, True, dq, HD, d, S * HD, S, d, S, heads, B)
+        gemm_batched(dP, S, S * S, heads * S * S, True, q, HD, d, S * HD, True, dk, HD, d, S * HD, S, d, S, heads, B)
+        return dq, dk, dv, None
+
+
+def attention(q, k, v, heads: int):
+    """Multi-head self-attention core (no mask, no dropout).  q, k, v: [B, S, heads*d]."""
+    B, S, HD = q.shape
+    d = HD // heads
+    if use_native(q, k, v) and q.dtype == torch.bfloat16 and d % 8 == 0 and S % 8 == 0 and S <= 1024:
+        return _AttentionFn.apply(q, k, v, heads)
+    qh, kh, vh = (t.view(B, S, heads, d).transpose(1, 2) for t in (q, k, v))
+    o = TF.scaled_dot_product_attention(qh.float(), kh.float(), vh.float())
+    return o.transpose(1, 2).reshape(B, S, HD).to(q.dtype)
+
+
+class _EmbeddingFn(torch.autograd.Function):
+    """word[ids] + position[0..S) + token_type[0] -> [B, S, H] bf16 (BERT embeddings before their LayerNorm)."""
+
+    @staticmethod
+    def forward(ctx, ids, word, pos, typ, wparam, pparam, tparam):
+        B, S = ids.shape
+        H = word.shape[1]
+        out = torch.empty((B, S, H), dtype=torch.bfloat16, device=ids.device)
+        ids = ids.contiguous()
+        check(_lib.lib().mlt_embedding_sum_fwd(ptr(ids), ptr(word), ptr(pos), ptr(typ), _c_int(int(word.dtype == torch.bfloat16)),
+                                               ptr(out), _c_int(B * S), _c_int(S), _c_int(H), stream_handle()),
+              "mlt_embedding_sum_fwd")
+        launches.bump("embedding_fwd")
+        ctx.save_for_backward(ids)
+        ctx.meta = (word.shape, pos.shape, typ.shape, word.dtype)
+        ctx.params = (wparam, pparam, tparam)
+        return out
+
+    @staticmethod
+    def backward(ctx, dh):
+        (ids,) = ctx.saved_tensors
+        wshape, pshape, tshape, wdtype = ctx.meta
+        wparam, pparam, tparam = ctx.params
+        B, S = ids.shape
+        H = wshape[1]
+        dh = dh.contiguous()
+        ws, ps, ts = _sink(wparam), _sink(pparam), _sink(tparam)
+        gdt = ws.dtype if ws is not None else wdtype
+        dev = dh.device
+        dword = ws if ws is not None else torch.empty(wshape, dtype=gdt, device=dev)
+        dpos = ps if ps is not None else torch.zeros(pshape, dtype=gdt, device=dev)
+        dtyp = ts if ts is not None else torch.zeros(tshape, dtype=gdt, device=dev)
+        check(_lib.lib().mlt_embedding_bwd(ptr(ids), ptr(dh), ptr(dword), _c_ll(wshape[0]), ptr(dpos),
+                                           _c_int(int(gdt == torch.bfloat16)), _c_int(B), _c_int(S), _c_int(H), stream_handle()),
+              "mlt_embedding_bwd")
+        launches.bump("embedding_bwd", 2)
+        colsum(dh.view(B * S, H), out=dtyp[0])
+        return None, _deliver(wparam, dword, ws), _deliver(pparam, dpos, ps), _deliver(tparam, dtyp, ts), None, None, None
+
+
+def bert_embeddings(ids, word, pos, typ):
+    if use_native(ids, word) and word.dtype in (torch.bfloat16, torch.float32) and word.shape[1] % 2 == 0:
+        if _has_sink(word):
+            return _EmbeddingFn.apply(ids, word.detach(), pos.detach(), typ.detach(), word, pos, typ)
+        return _EmbeddingFn.apply(ids, word, pos, typ, None, None, None)
+    S = ids.shape[1]
+    return (word[ids] + pos[:S].unsqueeze(0) + typ[0]).to(torch.bfloat16 if word.is_cuda else word.dtype)

@@ -50,6 +50,16 @@ def gemm(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = Fals
     return out
 
 
+def gemm_batched(a, lda, a_s1, a_s2, a_mn, b, ldb, b_s1, b_s2, b_mn, out, ldo, o_s1, o_s2, M, N, K, nb1, nb2, block_n: int = 0):
+    """``nb1*nb2`` independent ``D = A B^T`` problems addressed by two batch strides each (elements); see csrc/gemm_tcgen05.cu."""
+    check(_lib.lib().mlt_gemm_bf16_batched(ptr(a), _c_ll(lda), _c_ll(a_s1), _c_ll(a_s2), _c_int(int(a_mn)), ptr(b), _c_ll(ldb),
+                                           _c_ll(b_s1), _c_ll(b_s2), _c_int(int(b_mn)), ptr(out), _c_ll(ldo), _c_ll(o_s1),
+                                           _c_ll(o_s2), _c_int(int(out.dtype == torch.float32)), _c_int(M), _c_int(N), _c_int(K),
+                                           _c_int(nb1), _c_int(nb2), _c_int(block_n), stream_handle()), "mlt_gemm_bf16_batched")
+    launches.bump("gemm_bf16_tcgen05_batched")
+    return out
+
+
 def gemm_reference(a, b, a_mn=False, b_mn=False, bias=None, act=None):
     """fp32 PyTorch statement of :func:`gemm` (oracle)."""
     A = a.float().t() if a_mn else a.float()

@@ -1,0 +1,138 @@
+"""Transformer kernels (LayerNorm+residual, attention via batched tcgen05 GEMMs + row softmax, embeddings) and
+the native BERT path against fp32 PyTorch."""
+import pytest
+import torch
+import torch.nn.functional as TF
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _close(a, b, tol, what):
+    err = (a.float() - b.float()).abs().max().item()
+    ref = max(1.0, b.float().abs().max().item())
+    assert err <= tol * ref, f"{what}: max abs err {err} (ref scale {ref})"
+
+
+@pytest.mark.parametrize("T,H", [(64, 768), (1000, 128), (37, 1024), (4096, 768)])
+@pytest.mark.parametrize("pdtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("with_res", [False, True])
+def test_layernorm_fwd_bwd(T, H, pdtype, with_res):
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(0)
+    x = torch.randn(T, H, device=DEV).to(torch.bfloat16).requires_grad_()
+    r = torch.randn(T, H, device=DEV).to(torch.bfloat16).requires_grad_() if with_res else None
+    g = (1 + 0.1 * torch.randn(H, device=DEV)).to(pdtype).requires_grad_()
+    b = (0.1 * torch.randn(H, device=DEV)).to(pdtype).requires_grad_()
+    y = F.layer_norm(x, g, b, 1e-12, residual=r)
+    xr = x.detach().float().requires_grad_()
+    rr = r.detach().float().requires_grad_() if with_res else None
+    gr, br = g.detach().float().requires_grad_(), b.detach().float().requires_grad_()
+    h = xr + rr if with_res else xr
+    if with_res:
+        h = h + (h.to(torch.bfloat16).float() - h).detach()         # the kernel rounds the sum to bf16 once
+    ref = TF.layer_norm(h, (H,), gr, br, 1e-12)
+    _close(y, ref, 2e-2, "y")
+    dy = torch.randn_like(ref).to(torch.bfloat16)
+    ins = (x, r, g, b) if with_res else (x, g, b)
+    rins = (xr, rr, gr, br) if with_res else (xr, gr, br)
+    got = torch.autograd.grad(y, ins, dy)
+    exp = torch.autograd.grad(ref, rins, dy.float())
+    names = ("dx", "dres", "dgamma", "dbeta") if with_res else ("dx", "dgamma", "dbeta")
+    for n, a, e in zip(names, got, exp):
+        _close(a, e, 3e-2 if n.startswith("dx") or n == "dres" else 2e-2, n)
+
+
+@pytest.mark.parametrize("nb1,nb2,M,N,K", [(2, 3, 128, 128, 64), (12, 2, 512, 512, 64), (4, 2, 512, 64, 512)])
+def test_batched_gemm_strided_heads(nb1, nb2, M, N, K):
+    from ml_trainer_b200.ops.gemm import gemm_batched
+
+    torch.manual_seed(0)
+    a = (torch.randn(nb2, nb1, M, K, device=DEV) * 0.5).to(torch.bfloat16)
+    b = (torch.randn(nb2, nb1, N, K, device=DEV) * 0.5).to(torch.bfloat16)
+    out = torch.empty(nb2, nb1, M, N, dtype=torch.float32, device=DEV)
+    gemm_batched(a, K, M * K, nb1 * M * K, False, b, K, N * K, nb1 * N * K, False, out, N, M * N, nb1 * M * N, M, N, K, nb1, nb2)
+    torch.cuda.synchronize()
+    _close(out, a.float() @ b.float().transpose(-1, -2), 1e-3 * K ** 0.5, "batched")
+
+
+@pytest.mark.parametrize("B,S,heads,d", [(2, 128, 2, 64), (2, 512, 12, 64), (3, 64, 4, 32)])
+def test_attention_fwd_bwd(B, S, heads, d):
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(0)
+    q, k, v = ((torch.randn(B, S, heads * d, device=DEV) * 0.5).to(torch.bfloat16).requires_grad_() for _ in range(3))
+    o = F.attention(q, k, v, heads)
+    qr, kr, vr = (t.detach().float().requires_grad_() for t in (q, k, v))
+    sp = lambda t: t.view(B, S, heads, d).transpose(1, 2)
+    ref = TF.scaled_dot_product_attention(sp(qr), sp(kr), sp(vr)).transpose(1, 2).reshape(B, S, heads * d)
+    _close(o, ref, 2e-2, "attention out")
+    do = torch.randn_like(ref).to(torch.bfloat16)
+    got = torch.autograd.grad(o, (q, k, v), do)
+    exp = torch.autograd.grad(ref, (qr, kr, vr), do.float())
+    for n, a, e in zip(("dq", "dk", "dv"), got, exp):
+        _close(a, e, 4e-2, n)
+
+
+def test_embeddings_fwd_bwd():
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(0)
+    V, P, H, B, S = 500, 64, 128, 4, 32
+    word = torch.randn(V, H, device=DEV).to(torch.bfloat16).requires_grad_()
+    pos = torch.randn(P, H, device=DEV).to(torch.bfloat16).requires_grad_()
+    typ = torch.randn(2, H, device=DEV).to(torch.bfloat16).requires_grad_()
+    ids = torch.randint(0, V, (B, S), device=DEV)
+    h = F.bert_embeddings(ids, word, pos, typ)
+    wr, pr, tr = (t.detach().float().requires_grad_() for t in (word, pos, typ))
+    ref = wr[ids] + pr[:S].unsqueeze(0) + tr[0]
+    _close(h, ref, 1e-2, "embedding sum")
+    dh = torch.randn_like(ref).to(torch.bfloat16)
+    got = torch.autograd.grad(h, (word, pos, typ), dh)
+    exp = torch.autograd.grad(ref, (wr, pr, tr), dh.float())
+    for n, a, e in zip(("dword", "dpos", "dtype"), got, exp):
+        _close(a, e, 3e-2, n)
+
+
+def test_bert_tiny_native_matches_fp32_reference():
+    """bf16 native forward/backward of a small BERT against the same weights run in fp32 PyTorch on the CPU."""
+    from ml_trainer_b200 import build_model
+
+    torch.manual_seed(0)
+    ref = build_model("bert_tiny")
+    nat = build_model("bert_tiny")
+    nat.load_state_dict(ref.state_dict())
+    nat = nat.to(DEV).to(torch.bfloat16)
+    ids = torch.randint(0, 1000, (4, 64))
+    y = torch.tensor([0, 1, 1, 0])
+    lo = nat(ids.to(DEV))
+    lr = ref(ids)
+    _close(lo.cpu(), lr, 3e-2, "logits")
+    TF.cross_entropy(lo, y.to(DEV)).backward()
+    TF.cross_entropy(lr, y).backward()
+    rp = dict(ref.named_parameters())
+    worst = 0.0
+    for n, p in nat.named_parameters():
+        g, e = p.grad.float().cpu(), rp[n].grad
+        rel = (g - e).norm() / (e.norm() + 1e-6)
+        worst = max(worst, rel.item())
+        assert rel < 0.08, (n, rel.item())
+    print("worst relative gradient error", worst)
+
+
+def test_trainer_bert_tiny_bf16(tmp_path):
+    from ml_trainer_b200 import SyntheticDataset, Trainer, build_model
+    from ml_trainer_b200.ops import _lib
+
+    _lib.launches.reset()
+    tr = SyntheticDataset((64,), 2, length=64, kind="tokens", vocab=1000, seed=1)
+    t = Trainer(build_model("bert_tiny"), datasets=(tr, tr), epochs=3, batch_size=16, optimizer="adamw", lr=1e-3,
+                dtype="bf16", model_dir=str(tmp_path), progress=False, metric="accuracy")
+    t.fit()
+    assert t.train_losses[-1] < t.train_losses[0]
+    names = set(_lib.launches.by_name)
+    assert {"gemm_bf16_tcgen05", "gemm_bf16_tcgen05_batched", "layernorm_fwd", "layernorm_bwd", "softmax_rows",
+            "embedding_fwd", "embedding_bwd"} <= names, names
+    sd = torch.load(tmp_path / "model.pth")
+    assert all(v.dtype == torch.float32 for v in sd.values() if v.is_floating_point())
