@@ -1,0 +1,261 @@
+// Convolution support for the ResNet path (SURVEY §8 K7 conv, K10): NHWC bf16 im2col / col2im around the tcgen05 GEMM,
+// 3x3/2 max-pool and global average pool, NCHW fp32 -> NHWC bf16 input conversion.
+// A convolution is  out[B*OH*OW, Cout] = col[B*OH*OW, KH*KW*C] * W[Cout, KH*KW*C]^T  with the GEMM on tensor cores;
+// 1x1 stride-1 convolutions need no col matrix at all (the activation tensor IS the A operand).
+// All kernels move 16 bytes per thread (8 channels); the roofline is bytes / HBM bandwidth.
+#include "common.cuh"
+#include "../include/mlt_b200.h"
+
+namespace mlt {
+
+// col[(b,oh,ow)][(kh,kw,c)] = x[b][oh*s-p+kh][ow*s-p+kw][c]   (zero outside the image)
+__global__ void __launch_bounds__(256)
+im2col_nhwc_kernel(const uint4* __restrict__ x, uint4* __restrict__ col, int B, int H, int W, int C8, int KH, int KW, int stride,
+                   int pad, int OH, int OW) {
+  const long long total = (long long)B * OH * OW * KH * KW * C8;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    const int c = (int)(i % C8);
+    long long r = i / C8;
+    const int kw = (int)(r % KW); r /= KW;
+    const int kh = (int)(r % KH); r /= KH;
+    const int ow = (int)(r % OW); r /= OW;
+    const int oh = (int)(r % OH);
+    const int b = (int)(r / OH);
+    const int h = oh * stride - pad + kh, w = ow * stride - pad + kw;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((size_t)b * H + h) * W + w) * C8 + c];
+    col[i] = v;
+  }
+}
+
+__device__ __forceinline__ void add8(float (&acc)[8], const uint4& raw) {
+  const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[j]));
+    acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+  }
+}
+__device__ __forceinline__ uint4 pack8f(const float (&v)[8]) {
+  uint4 o;
+  o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]); o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+  return o;
+}
+
+// dx[b][h][w][c] = sum over the (kh,kw) whose window covers (h,w) of dcol[(b,oh,ow)][(kh,kw,c)]   (gather: deterministic)
+__global__ void __launch_bounds__(256)
+col2im_nhwc_kernel(const uint4* __restrict__ dcol, uint4* __restrict__ dx, int B, int H, int W, int C8, int KH, int KW, int stride,
+                   int pad, int OH, int OW) {
+  const long long total = (long long)B * H * W * C8;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    const int c = (int)(i % C8);
+    long long r = i / C8;
+    const int w = (int)(r % W); r /= W;
+    const int h = (int)(r % H);
+    const int b = (int)(r / H);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int kh = 0; kh < KH; ++kh) {
+      const int th = h + pad - kh;
+      if (th < 0 || th % stride != 0) continue;
+      const int oh = th / stride;
+      if (oh >= OH) continue;
+      for (int kw = 0; kw < KW; ++kw) {
+        const int tw = w + pad - kw;
+        if (tw < 0 || tw % stride != 0) continue;
+        const int ow = tw / stride;
+        if (ow >= OW) continue;
+        add8(acc, dcol[((((size_t)b * OH + oh) * OW + ow) * KH * KW + kh * KW + kw) * C8 + c]);
+      }
+    }
+    dx[i] = pack8f(acc);
+  }
+}
+
+// NCHW fp32 -> NHWC bf16 with the channel dim zero-padded to Cp (the 3-channel stem is padded to 8 for 16-byte vectors)
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int B, int C, int H, int W, int Cp) {
+  const long long total = (long long)B * H * W * Cp;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    const int c = (int)(i % Cp);
+    long long r = i / Cp;
+    const int w = (int)(r % W); r /= W;
+    const int h = (int)(r % H);
+    const int b = (int)(r / H);
+    y[i] = __float2bfloat16_rn(c < C ? x[(((size_t)b * C + c) * H + h) * W + w] : 0.f);
+  }
+}
+
+// ---- pooling (NHWC bf16) ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+maxpool_nhwc_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, unsigned char* __restrict__ idx, int B, int H, int W,
+                        int C8, int K, int stride, int pad, int OH, int OW) {
+  const long long total = (long long)B * OH * OW * C8;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    const int c = (int)(i % C8);
+    long long r = i / C8;
+    const int ow = (int)(r % OW); r /= OW;
+    const int oh = (int)(r % OH);
+    const int b = (int)(r / OH);
+    float m[8];
+    unsigned char am[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { m[j] = -INFINITY; am[j] = 0; }
+    for (int kh = 0; kh < K; ++kh) {
+      const int h = oh * stride - pad + kh;
+      if (h < 0 || h >= H) continue;
+      for (int kw = 0; kw < K; ++kw) {
+        const int w = ow * stride - pad + kw;
+        if (w < 0 || w >= W) continue;
+        float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        add8(v, x[(((size_t)b * H + h) * W + w) * C8 + c]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (v[j] > m[j]) { m[j] = v[j]; am[j] = (unsigned char)(kh * K + kw); }
+      }
+    }
+    y[i] = pack8f(m);
+    *reinterpret_cast<uint2*>(idx + i * 8) = *reinterpret_cast<const uint2*>(am);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+maxpool_nhwc_bwd_kernel(const uint4* __restrict__ dy, const unsigned char* __restrict__ idx, uint4* __restrict__ dx, int B, int H,
+                        int W, int C8, int K, int stride, int pad, int OH, int OW) {
+  const long long total = (long long)B * H * W * C8;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    const int c = (int)(i % C8);
+    long long r = i / C8;
+    const int w = (int)(r % W); r /= W;
+    const int h = (int)(r % H);
+    const int b = (int)(r / H);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int kh = 0; kh < K; ++kh) {
+      const int th = h + pad - kh;
+      if (th < 0 || th % stride != 0) continue;
+      const int oh = th / stride;
+      if (oh >= OH) continue;
+      for (int kw = 0; kw < K; ++kw) {
+        const int tw = w + pad - kw;
+        if (tw < 0 || tw % stride != 0) continue;
+        const int ow = tw / stride;
+        if (ow >= OW) continue;
+        const size_t o = (((size_t)b * OH + oh) * OW + ow) * C8 + c;
+        unsigned char am[8];
+        *reinterpret_cast<uint2*>(am) = *reinterpret_cast<const uint2*>(idx + o * 8);
+        float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        add8(g, dy[o]);
+        const unsigned char me = (unsigned char)(kh * K + kw);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (am[j] == me) acc[j] += g[j];
+      }
+    }
+    dx[i] = pack8f(acc);
+  }
+}
+
+// y[b][c] = mean over HW of x[b][hw][c]
+__global__ void __launch_bounds__(256)
+avgpool_nhwc_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int B, int HW, int C8) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * C8) return;
+  const int b = i / C8, c = i - b * C8;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int p = 0; p < HW; ++p) add8(acc, x[((size_t)b * HW + p) * C8 + c]);
+  const float inv = 1.0f / (float)HW;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] *= inv;
+  y[i] = pack8f(acc);
+}
+
+__global__ void __launch_bounds__(256)
+avgpool_nhwc_bwd_kernel(const uint4* __restrict__ dy, uint4* __restrict__ dx, int B, int HW, int C8) {
+  const long long total = (long long)B * HW * C8;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  const float inv = 1.0f / (float)HW;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    const int c = (int)(i % C8);
+    const int b = (int)(i / ((long long)HW * C8));
+    float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    add8(g, dy[(size_t)b * C8 + c]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] *= inv;
+    dx[i] = pack8f(g);
+  }
+}
+
+static int grid_for(long long items) {
+  long long b = ceil_div64(items, 256);
+  const long long cap = (long long)kNumSMs * 16;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+}  // namespace mlt
+
+using namespace mlt;
+
+extern "C" int mlt_im2col_nhwc(const void* x, void* col, int B, int H, int W, int C, int KH, int KW, int stride, int pad, int OH,
+                               int OW, void* stream) {
+  MLT_REQUIRE(C % 8 == 0, "mlt_im2col_nhwc: channels (%d) must be a multiple of 8", C);
+  const long long total = (long long)B * OH * OW * KH * KW * (C / 8);
+  im2col_nhwc_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)col, B, H, W, C / 8, KH, KW, stride,
+                                                                       pad, OH, OW);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int mlt_col2im_nhwc(const void* dcol, void* dx, int B, int H, int W, int C, int KH, int KW, int stride, int pad, int OH,
+                               int OW, void* stream) {
+  MLT_REQUIRE(C % 8 == 0, "mlt_col2im_nhwc: channels (%d) must be a multiple of 8", C);
+  const long long total = (long long)B * H * W * (C / 8);
+  col2im_nhwc_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const uint4*)dcol, (uint4*)dx, B, H, W, C / 8, KH, KW, stride,
+                                                                       pad, OH, OW);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int mlt_nchw_to_nhwc_bf16(const void* x_f32, void* y_bf16, int B, int C, int H, int W, int Cp, void* stream) {
+  MLT_REQUIRE(Cp >= C, "mlt_nchw_to_nhwc_bf16: padded channel count smaller than C");
+  nchw_to_nhwc_bf16_kernel<<<grid_for((long long)B * H * W * Cp), 256, 0, (cudaStream_t)stream>>>((const float*)x_f32,
+                                                                                                (__nv_bfloat16*)y_bf16, B, C, H, W, Cp);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int mlt_maxpool_nhwc_fwd(const void* x, void* y, void* idx_u8, int B, int H, int W, int C, int K, int stride, int pad,
+                                    int OH, int OW, void* stream) {
+  MLT_REQUIRE(C % 8 == 0 && K * K <= 255, "mlt_maxpool_nhwc_fwd: unsupported shape");
+  maxpool_nhwc_fwd_kernel<<<grid_for((long long)B * OH * OW * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)x, (uint4*)y, (unsigned char*)idx_u8, B, H, W, C / 8, K, stride, pad, OH, OW);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int mlt_maxpool_nhwc_bwd(const void* dy, const void* idx_u8, void* dx, int B, int H, int W, int C, int K, int stride,
+                                    int pad, int OH, int OW, void* stream) {
+  MLT_REQUIRE(C % 8 == 0, "mlt_maxpool_nhwc_bwd: unsupported shape");
+  maxpool_nhwc_bwd_kernel<<<grid_for((long long)B * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const uint4*)dy, (const unsigned char*)idx_u8, (uint4*)dx, B, H, W, C / 8, K, stride, pad, OH, OW);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int mlt_avgpool_nhwc_fwd(const void* x, void* y, int B, int HW, int C, void* stream) {
+  MLT_REQUIRE(C % 8 == 0, "mlt_avgpool_nhwc_fwd: channels must be a multiple of 8");
+  avgpool_nhwc_fwd_kernel<<<ceil_div(B * (C / 8), 256), 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)y, B, HW, C / 8);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+extern "C" int mlt_avgpool_nhwc_bwd(const void* dy, void* dx, int B, int HW, int C, void* stream) {
+  MLT_REQUIRE(C % 8 == 0, "mlt_avgpool_nhwc_bwd: channels must be a multiple of 8");
+  avgpool_nhwc_bwd_kernel<<<grid_for((long long)B * HW * (C / 8)), 256, 0, (cudaStream_t)stream>>>((const uint4*)dy, (uint4*)dx, B, HW,
+                                                                                                C / 8);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}

@@ -44,6 +44,7 @@ struct GemmParams {
   int num_m, num_n, num_k;
   int nb1, nb2;                  // batch = nb1 * nb2 independent problems (attention: heads x samples)
   long long ob1, ob2;            // output batch strides (elements)
+  int splits, kb_per_split;      // split-K: the batch index doubles as the K-slice id, partials go to an fp32 workspace
 };
 
 template <int BN>
@@ -117,9 +118,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         int m_blk, n_blk;
         const int z = tile / tiles_per_problem;
         tile_coords(tile - z * tiles_per_problem, p.num_m, p.num_n, m_blk, n_blk);
-        const int z1 = z % p.nb1, z2 = z / p.nb1;
+        const int z1 = p.splits > 1 ? 0 : z % p.nb1, z2 = p.splits > 1 ? 0 : z / p.nb1;
+        const int kb_lo = p.splits > 1 ? z * p.kb_per_split : 0;
+        const int kb_hi = p.splits > 1 ? min(p.num_k, kb_lo + p.kb_per_split) : p.num_k;
         const int m0 = m_blk * BM, n0 = n_blk * BN;
-        for (int kb = 0; kb < p.num_k; ++kb) {
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
           uint8_t* sB = sA + Cfg::kABytes;
@@ -155,7 +158,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         mbar_wait(&tmem_empty[as], aphase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + as * BN;
-        for (int kb = 0; kb < p.num_k; ++kb) {
+        const int zs = tile / tiles_per_problem;
+        const int kb_lo = p.splits > 1 ? zs * p.kb_per_split : 0;
+        const int kb_hi = p.splits > 1 ? min(p.num_k, kb_lo + p.kb_per_split) : p.num_k;
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t sA = smem_u32(smem + stage * Cfg::kStageBytes);
@@ -164,10 +170,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t adesc = make_smem_desc_sw128(sA + k * a_step, a_lbo, 1024);
             const uint64_t bdesc = make_smem_desc_sw128(sB + k * b_step, b_lbo, 1024);
-            umma_f16(d_tmem, adesc, bdesc, idesc, (kb | k) != 0);
+            umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb_lo) || (k != 0));
           }
           umma_commit(&empty[stage]);                       // smem slot reusable once these MMAs retire
-          if (kb == p.num_k - 1) umma_commit(&tmem_full[as]);
+          if (kb == kb_hi - 1) umma_commit(&tmem_full[as]);
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
         if (++as == 2) { as = 0; aphase ^= 1; }
@@ -289,6 +295,10 @@ static int make_tmap(CUtensorMap* out, const void* base, long long inner, long l
                      int box_outer, int nb1 = 1, long long s1 = 0, int nb2 = 1, long long s2 = 0) {
   EncodeTiledFn enc = get_encode();
   MLT_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  // Driver-API calls need the primary context bound to THIS host thread; autograd runs backward on its own threads
+  // that may not have made a runtime call yet.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) { MLT_CHECK_CUDA(cudaFree(nullptr)); ctx_bound = true; }
   if (nb1 <= 1) { nb1 = 1; s1 = ld * outer; }
   if (nb2 <= 1) { nb2 = 1; s2 = s1 * nb1; }
   if (s1 % 8 != 0) s1 = (s1 + 7) / 8 * 8;          // only reachable for size-1 batch dims (stride never used)
@@ -322,9 +332,39 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParam
     MLT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
     attr_set[dev & 63] = true;
   }
-  long long tiles = (long long)p.num_m * p.num_n * p.nb1 * p.nb2;
+  long long tiles = (long long)p.num_m * p.num_n * p.nb1 * p.nb2;      // with split-K, nb1 carries the number of K slices
   int grid = tiles > kNumSMs ? kNumSMs : (int)tiles;
   kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+// out[m][n] = sum_s ws[s][m][n]   (split-K epilogue; fp32 partials -> bf16 or fp32 output with row pitch ldo)
+template <typename O>
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float* __restrict__ ws, O* __restrict__ out, long long ldo, int M, int N, int splits) {
+  const long long total4 = (long long)M * N / 4;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long plane = (long long)M * N;
+  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < total4; v += stride) {
+    float4 a = *reinterpret_cast<const float4*>(ws + v * 4);
+    for (int s = 1; s < splits; ++s) {
+      const float4 b = *reinterpret_cast<const float4*>(ws + s * plane + v * 4);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    const long long e = v * 4;
+    const int m = (int)(e / N), n = (int)(e - (long long)m * N);
+    O* o = out + (size_t)m * ldo + n;
+    o[0] = from_float<O>(a.x); o[1] = from_float<O>(a.y); o[2] = from_float<O>(a.z); o[3] = from_float<O>(a.w);
+  }
+}
+
+static int launch_splitk_reduce(const float* ws, void* out, long long ldo, int out_f32, int M, int N, int splits, cudaStream_t st) {
+  MLT_REQUIRE(N % 4 == 0, "split-K reduce needs N %% 4 == 0 (N=%d)", N);
+  long long blocks = ceil_div64((long long)M * N / 4, 256);
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (out_f32) splitk_reduce_kernel<float><<<(int)blocks, 256, 0, st>>>(ws, (float*)out, ldo, M, N, splits);
+  else splitk_reduce_kernel<__nv_bfloat16><<<(int)blocks, 256, 0, st>>>(ws, (__nv_bfloat16*)out, ldo, M, N, splits);
   MLT_LAUNCH_CHECK();
   return 0;
 }
@@ -338,7 +378,8 @@ using namespace mlt;
 //   b_mn = 0: B is [N][K] (row stride ldb);   b_mn = 1: B is stored [K][N] (row stride ldb)
 extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out,
                              long long ldo, int out_f32, int M, int N, int K, const void* bias, int bias_f32, int act,
-                             int aux_mode, void* aux, long long ld_aux, int block_n, void* stream) {
+                             int aux_mode, void* aux, long long ld_aux, int block_n, void* splitk_ws,
+                             long long splitk_ws_bytes, void* stream) {
   MLT_REQUIRE(M > 0 && N > 0 && K > 0, "mlt_gemm_bf16: empty problem (M=%d N=%d K=%d)", M, N, K);
   MLT_REQUIRE(aux_mode == 0 || aux != nullptr, "mlt_gemm_bf16: aux_mode %d needs an aux tensor", aux_mode);
   MLT_REQUIRE(((uintptr_t)out % 16) == 0 && (ldo * (out_f32 ? 4 : 2)) % 16 == 0, "mlt_gemm_bf16: output must be 16-byte aligned with a 16-byte multiple row pitch");
@@ -358,7 +399,28 @@ extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   p.aux_mode = aux_mode; p.aux = aux; p.ld_aux = ld_aux;
   p.a_mn = a_mn; p.b_mn = b_mn;
   p.nb1 = p.nb2 = 1; p.ob1 = p.ob2 = 0;
+  p.splits = 1; p.kb_per_split = 0;
   cudaStream_t st = (cudaStream_t)stream;
+  // split-K: weight-gradient shapes (few output tiles, very long K) would otherwise occupy a handful of SMs
+  const int tiles = ceil_div(M, BM) * ceil_div(N, BN), num_k = ceil_div(K, BK);
+  int splits = 1;
+  if (splitk_ws != nullptr && bias == nullptr && act == ACT_NONE && aux_mode == 0 && tiles * 2 <= kNumSMs && num_k >= 8) {
+    splits = kNumSMs / tiles;
+    if (splits > 16) splits = 16;
+    if (splits > num_k / 4) splits = num_k / 4;
+    if ((long long)splits * M * N * 4 > splitk_ws_bytes) splits = (int)(splitk_ws_bytes / ((long long)M * N * 4));
+  }
+  if (splits > 1) {
+    const int kbps = ceil_div(num_k, splits);
+    splits = ceil_div(num_k, kbps);              // no empty slice
+    GemmParams q = p;
+    q.out = splitk_ws; q.ldo = N; q.out_f32 = 1;
+    q.nb1 = splits; q.nb2 = 1; q.ob1 = (long long)M * N; q.ob2 = 0;
+    q.splits = splits; q.kb_per_split = kbps;
+    int rc = BN == 256 ? launch_gemm<256>(tmA, tmB, q, st) : (BN == 128 ? launch_gemm<128>(tmA, tmB, q, st) : launch_gemm<64>(tmA, tmB, q, st));
+    if (rc) return rc;
+    return launch_splitk_reduce((const float*)splitk_ws, out, ldo, out_f32, M, N, splits, st);
+  }
   if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
   if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
   return launch_gemm<64>(tmA, tmB, p, st);
@@ -389,6 +451,7 @@ extern "C" int mlt_gemm_bf16_batched(const void* A, long long lda, long long a_s
   p.aux_mode = 0; p.aux = nullptr; p.ld_aux = 0;
   p.a_mn = a_mn; p.b_mn = b_mn;
   p.nb1 = nb1; p.nb2 = nb2; p.ob1 = o_s1; p.ob2 = o_s2;
+  p.splits = 1; p.kb_per_split = 0;
   cudaStream_t st = (cudaStream_t)stream;
   if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
   if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);

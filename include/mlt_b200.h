@@ -82,10 +82,12 @@ int mlt_linear_small_bwd(const void* dy, const void* y, const void* x, const voi
  *   + bias[N] (fp32 or bf16), activation, aux_mode 1: also store the pre-activation (bf16) to aux,
  *   aux_mode 2: multiply by act'(aux) instead (the dgrad-through-activation epilogue).
  * a_mn = 0: A stored [M][K];  a_mn = 1: A stored [K][M].  b_mn = 0: B stored [N][K];  b_mn = 1: B stored [K][N].
- * Row strides (elements) must be multiples of 8.  block_n: 0 = auto, or 64 / 128 / 256. */
+ * Row strides (elements) must be multiples of 8.  block_n: 0 = auto, or 64 / 128 / 256.
+ * splitk_ws (optional fp32 scratch): when the output has few tiles and K is long (weight gradients) the reduction is
+ * split over up to 16 K-slices whose partials land in the scratch and are summed by a second kernel. */
 int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void* B, long long ldb, int b_mn, void* out,
                   long long ldo, int out_f32, int M, int N, int K, const void* bias, int bias_f32, int act, int aux_mode,
-                  void* aux, long long ld_aux, int block_n, void* stream);
+                  void* aux, long long ld_aux, int block_n, void* splitk_ws, long long splitk_ws_bytes, void* stream);
 
 /* nb1*nb2 independent GEMMs sharing M,N,K; operand (z1,z2) starts at base + z1*s1 + z2*s2 elements (attention heads). */
 int mlt_gemm_bf16_batched(const void* A, long long lda, long long a_s1, long long a_s2, int a_mn, const void* B,
@@ -184,6 +186,30 @@ int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos
                           void* out_bf16, int T, int S, int H, void* stream);
 int mlt_embedding_bwd(const void* ids_i64, const void* dh_bf16, void* dword, long long V, void* dpos, int grads_bf16, int B,
                       int S, int H, void* stream);
+
+/* ---- ResNet pieces (NHWC bf16): cuDNN convolution / batch-norm / pooling calls of the ResNet-50 workload ---------- */
+/* conv = im2col (skipped for 1x1 stride 1) + mlt_gemm_bf16; dgrad = GEMM + col2im gather; wgrad = split-K GEMM. */
+int mlt_im2col_nhwc(const void* x, void* col, int B, int H, int W, int C, int KH, int KW, int stride, int pad, int OH, int OW,
+                    void* stream);
+int mlt_col2im_nhwc(const void* dcol, void* dx, int B, int H, int W, int C, int KH, int KW, int stride, int pad, int OH, int OW,
+                    void* stream);
+int mlt_nchw_to_nhwc_bf16(const void* x_f32, void* y_bf16, int B, int C, int H, int W, int Cp, void* stream);
+int mlt_maxpool_nhwc_fwd(const void* x, void* y, void* idx_u8, int B, int H, int W, int C, int K, int stride, int pad, int OH,
+                         int OW, void* stream);
+int mlt_maxpool_nhwc_bwd(const void* dy, const void* idx_u8, void* dx, int B, int H, int W, int C, int K, int stride, int pad,
+                         int OH, int OW, void* stream);
+int mlt_avgpool_nhwc_fwd(const void* x, void* y, int B, int HW, int C, void* stream);
+int mlt_avgpool_nhwc_bwd(const void* dy, void* dx, int B, int HW, int C, void* stream);
+/* Training BatchNorm over [M = B*H*W, C]: stats (+ running-stat update) -> apply (+ residual, + ReLU); backward in two passes.
+ * scratch: mlt_bn_scratch_bytes(M, C), zero-initialised once. */
+long long mlt_bn_scratch_bytes(int M, int C);
+int mlt_bn_stats(const void* x, void* mean, void* rstd, void* run_mean, void* run_var, float momentum, float eps, void* scratch,
+                 long long scratch_bytes, int M, int C, void* stream);
+int mlt_bn_apply(const void* x, const void* mean, const void* rstd, const void* gamma, const void* beta, int params_bf16,
+                 const void* residual, void* y, long long M, int C, int relu, void* stream);
+int mlt_bn_bwd(const void* dy, const void* y, const void* x, const void* mean, const void* rstd, const void* gamma, int params_bf16,
+               void* dx, void* dres, void* dgamma, void* dbeta, int grads_bf16, void* scratch, long long scratch_bytes, int M, int C,
+               int relu, void* stream);
 
 #ifdef __cplusplus
 }

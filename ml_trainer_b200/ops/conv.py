@@ -1,0 +1,252 @@
+"""NHWC bf16 convolution / batch-norm / pooling ops of the ResNet path (csrc/conv_nhwc.cu, csrc/batchnorm.cu).
+
+A convolution is ``im2col`` (skipped for 1x1 stride-1) + the tcgen05 GEMM; its backward is two more GEMMs
+(dgrad with an MN-major weight operand followed by a ``col2im`` gather, wgrad as a split-K GEMM with both operands
+MN-major).  Weights are kept *physically* in ``[Cout, KH, KW, Cin]`` order (torch channels_last) inside the optimizer
+arena, so the 2-D GEMM view of a weight and of its gradient sink is free, while ``state_dict`` still shows the
+usual logical ``[Cout, Cin, KH, KW]`` shape.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+import torch.nn.functional as TF
+
+from . import _lib
+from ._lib import check, launches, ptr, stream_handle
+from .functional import _deliver, _has_sink, _sink, scratch, use_native
+from .gemm import gemm
+
+_c_int, _c_ll, _c_f = ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+
+
+def _w2d(w: torch.Tensor) -> torch.Tensor:
+    """[Cout, Cin, KH, KW] (channels_last memory) -> contiguous [Cout, KH*KW*Cin] view (copy if not channels_last)."""
+    Co, Ci, KH, KW = w.shape
+    v = w.permute(0, 2, 3, 1)
+    if not v.is_contiguous():
+        v = v.contiguous()
+    return v.reshape(Co, KH * KW * Ci)
+
+
+def _out_hw(H, W, K, stride, pad):
+    return (H + 2 * pad - K) // stride + 1, (W + 2 * pad - K) // stride + 1
+
+
+def _im2col(x, KH, KW, stride, pad, OH, OW):
+    B, H, W, C = x.shape
+    col = torch.empty((B * OH * OW, KH * KW * C), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().mlt_im2col_nhwc(ptr(x), ptr(col), _c_int(B), _c_int(H), _c_int(W), _c_int(C), _c_int(KH), _c_int(KW),
+                                     _c_int(stride), _c_int(pad), _c_int(OH), _c_int(OW), stream_handle()), "mlt_im2col_nhwc")
+    launches.bump("im2col_nhwc")
+    return col
+
+
+class _ConvNHWCFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, stride, pad, wparam):
+        B, H, W, C = x.shape
+        Co, Ci, KH, KW = weight.shape
+        OH, OW = _out_hw(H, W, KH, stride, pad)
+        x = x.contiguous()
+        direct = KH == 1 and KW == 1 and stride == 1 and pad == 0
+        a = x.view(B * H * W, C) if direct else _im2col(x, KH, KW, stride, pad, OH, OW)
+        y = gemm(a, _w2d(weight), False, False)
+        ctx.save_for_backward(x, weight)
+        ctx.cfg = (stride, pad, OH, OW, direct)
+        ctx.wparam = wparam
+        return y.view(B, OH, OW, Co)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        stride, pad, OH, OW, direct = ctx.cfg
+        wparam = ctx.wparam
+        B, H, W, C = x.shape
+        Co, Ci, KH, KW = weight.shape
+        dy2 = dy.contiguous().view(B * OH * OW, Co)
+        w2 = _w2d(weight)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dcol = gemm(dy2, w2, False, True)                       # [M, KH*KW*C]
+            if direct:
+                dx = dcol.view(B, H, W, C)
+            else:
+                dx = torch.empty_like(x)
+                check(_lib.lib().mlt_col2im_nhwc(ptr(dcol), ptr(dx), _c_int(B), _c_int(H), _c_int(W), _c_int(C), _c_int(KH),
+                                                 _c_int(KW), _c_int(stride), _c_int(pad), _c_int(OH), _c_int(OW), stream_handle()),
+                      "mlt_col2im_nhwc")
+                launches.bump("col2im_nhwc")
+        a = x.view(B * H * W, C) if direct else _im2col(x, KH, KW, stride, pad, OH, OW)     # recomputed, not stored
+        wsink = _sink(wparam)
+        out = None
+        if wsink is not None:
+            v = wsink.permute(0, 2, 3, 1)
+            if v.is_contiguous():
+                out = v.reshape(Co, KH * KW * Ci)
+        dw2 = gemm(dy2, a, True, True, out=out, out_dtype=weight.dtype)
+        if wsink is not None and out is None:
+            wsink.copy_(dw2.view(Co, KH, KW, Ci).permute(0, 3, 1, 2))
+        dw = None if wsink is not None else dw2.view(Co, KH, KW, Ci).permute(0, 3, 1, 2)
+        return dx, _deliver(wparam, dw, wsink), None, None, None
+
+
+def conv2d_nhwc(x: torch.Tensor, weight: torch.Tensor, stride: int = 1, pad: int = 0) -> torch.Tensor:
+    """x: [B, H, W, Cin] bf16, weight: logical [Cout, Cin, KH, KW] -> [B, OH, OW, Cout]."""
+    if _has_sink(weight):
+        return _ConvNHWCFn.apply(x, weight.detach(), stride, pad, weight)
+    return _ConvNHWCFn.apply(x, weight, stride, pad, None)
+
+
+def to_nhwc_bf16(x: torch.Tensor, pad_to: int = 8) -> torch.Tensor:
+    """NCHW fp32 image batch -> NHWC bf16 with channels zero-padded to a multiple of ``pad_to``."""
+    B, C, H, W = x.shape
+    Cp = (C + pad_to - 1) // pad_to * pad_to
+    if x.dtype != torch.float32:
+        x = x.float()
+    y = torch.empty((B, H, W, Cp), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().mlt_nchw_to_nhwc_bf16(ptr(x.contiguous()), ptr(y), _c_int(B), _c_int(C), _c_int(H), _c_int(W), _c_int(Cp),
+                                           stream_handle()), "mlt_nchw_to_nhwc_bf16")
+    launches.bump("nchw_to_nhwc")
+    return y
+
+
+def pad_weight_channels(weight: torch.Tensor, Cp: int) -> torch.Tensor:
+    """Zero-pad the input-channel dim of a conv weight (the 3-channel stem) so it matches a padded NHWC input."""
+    Co, Ci, KH, KW = weight.shape
+    if Ci == Cp:
+        return weight
+    return TF.pad(weight, (0, 0, 0, 0, 0, Cp - Ci)).contiguous(memory_format=torch.channels_last)
+
+
+class _BatchNormFn(torch.autograd.Function):
+    """Training-mode BN over NHWC (+ fused residual add and ReLU); updates the running statistics in the stats kernel."""
+
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, run_mean, run_var, momentum, eps, relu, gparam, bparam):
+        C = x.shape[-1]
+        x2 = x.contiguous().view(-1, C)
+        M = x2.shape[0]
+        r2 = residual.contiguous().view(-1, C) if residual is not None else None
+        L = _lib.lib()
+        L.mlt_bn_scratch_bytes.restype = _c_ll
+        ws = scratch(x.device, "bn", L.mlt_bn_scratch_bytes(_c_int(M), _c_int(C)))
+        mean = torch.empty(C, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(C, dtype=torch.float32, device=x.device)
+        check(L.mlt_bn_stats(ptr(x2), ptr(mean), ptr(rstd), ptr(run_mean), ptr(run_var), _c_f(momentum), _c_f(eps), ptr(ws),
+                             _c_ll(ws.numel()), _c_int(M), _c_int(C), stream_handle()), "mlt_bn_stats")
+        y = torch.empty_like(x2)
+        check(L.mlt_bn_apply(ptr(x2), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta), _c_int(int(gamma.dtype == torch.bfloat16)),
+                             ptr(r2), ptr(y), _c_ll(M), _c_int(C), _c_int(int(relu)), stream_handle()), "mlt_bn_apply")
+        launches.bump("bn_fwd", 2)
+        ctx.save_for_backward(x2, y, mean, rstd, gamma)
+        ctx.cfg = (relu, residual is not None, x.shape)
+        ctx.params = (gparam, bparam)
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, y, mean, rstd, gamma = ctx.saved_tensors
+        relu, has_res, shape = ctx.cfg
+        gparam, bparam = ctx.params
+        M, C = x2.shape
+        dy2 = dy.contiguous().view(M, C)
+        dx = torch.empty_like(x2)
+        dres = torch.empty_like(x2) if has_res else None
+        gsink, bsink = _sink(gparam), _sink(bparam)
+        gdt = gsink.dtype if gsink is not None else gamma.dtype
+        dg = gsink if gsink is not None else torch.empty(C, dtype=gdt, device=x2.device)
+        db = bsink if bsink is not None else torch.empty(C, dtype=gdt, device=x2.device)
+        L = _lib.lib()
+        L.mlt_bn_scratch_bytes.restype = _c_ll
+        ws = scratch(x2.device, "bn", L.mlt_bn_scratch_bytes(_c_int(M), _c_int(C)))
+        check(L.mlt_bn_bwd(ptr(dy2), ptr(y), ptr(x2), ptr(mean), ptr(rstd), ptr(gamma), _c_int(int(gamma.dtype == torch.bfloat16)),
+                           ptr(dx), ptr(dres), ptr(dg), ptr(db), _c_int(int(gdt == torch.bfloat16)), ptr(ws), _c_ll(ws.numel()),
+                           _c_int(M), _c_int(C), _c_int(int(relu)), stream_handle()), "mlt_bn_bwd")
+        launches.bump("bn_bwd", 2)
+        return (dx.view(shape), dres.view(shape) if has_res else None, _deliver(gparam, dg, gsink), _deliver(bparam, db, bsink),
+                None, None, None, None, None, None, None)
+
+
+def batch_norm_nhwc(x, bn: torch.nn.BatchNorm2d, relu: bool = False, residual: Optional[torch.Tensor] = None):
+    """BatchNorm2d semantics on an NHWC bf16 tensor.  Training: batch statistics; eval: running statistics."""
+    C = x.shape[-1]
+    if bn.training:
+        if bn.num_batches_tracked is not None:
+            bn.num_batches_tracked.add_(1)
+        mom = bn.momentum if bn.momentum is not None else 0.1
+        if _has_sink(bn.weight):
+            return _BatchNormFn.apply(x, residual, bn.weight.detach(), bn.bias.detach(), bn.running_mean, bn.running_var,
+                                      mom, bn.eps, relu, bn.weight, bn.bias)
+        return _BatchNormFn.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, mom, bn.eps, relu, None, None)
+    x2 = x.contiguous().view(-1, C)
+    rstd = torch.rsqrt(bn.running_var.float() + bn.eps)
+    y = torch.empty_like(x2)
+    r2 = residual.contiguous().view(-1, C) if residual is not None else None
+    check(_lib.lib().mlt_bn_apply(ptr(x2), ptr(bn.running_mean), ptr(rstd), ptr(bn.weight), ptr(bn.bias),
+                                  _c_int(int(bn.weight.dtype == torch.bfloat16)), ptr(r2), ptr(y), _c_ll(x2.shape[0]), _c_int(C),
+                                  _c_int(int(relu)), stream_handle()), "mlt_bn_apply")
+    launches.bump("bn_apply")
+    return y.view(x.shape)
+
+
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, K, stride, pad):
+        B, H, W, C = x.shape
+        OH, OW = _out_hw(H, W, K, stride, pad)
+        x = x.contiguous()
+        y = torch.empty((B, OH, OW, C), dtype=x.dtype, device=x.device)
+        idx = torch.empty((B, OH, OW, C), dtype=torch.uint8, device=x.device)
+        check(_lib.lib().mlt_maxpool_nhwc_fwd(ptr(x), ptr(y), ptr(idx), _c_int(B), _c_int(H), _c_int(W), _c_int(C), _c_int(K),
+                                              _c_int(stride), _c_int(pad), _c_int(OH), _c_int(OW), stream_handle()), "mlt_maxpool_nhwc_fwd")
+        launches.bump("maxpool_fwd")
+        ctx.save_for_backward(idx)
+        ctx.cfg = (x.shape, K, stride, pad, OH, OW)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        (B, H, W, C), K, stride, pad, OH, OW = ctx.cfg
+        dx = torch.empty((B, H, W, C), dtype=dy.dtype, device=dy.device)
+        check(_lib.lib().mlt_maxpool_nhwc_bwd(ptr(dy.contiguous()), ptr(idx), ptr(dx), _c_int(B), _c_int(H), _c_int(W), _c_int(C),
+                                              _c_int(K), _c_int(stride), _c_int(pad), _c_int(OH), _c_int(OW), stream_handle()),
+              "mlt_maxpool_nhwc_bwd")
+        launches.bump("maxpool_bwd")
+        return dx, None, None, None
+
+
+def max_pool_nhwc(x, K=3, stride=2, pad=1):
+    return _MaxPoolFn.apply(x, K, stride, pad)
+
+
+class _AvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        B, H, W, C = x.shape
+        y = torch.empty((B, C), dtype=x.dtype, device=x.device)
+        check(_lib.lib().mlt_avgpool_nhwc_fwd(ptr(x.contiguous()), ptr(y), _c_int(B), _c_int(H * W), _c_int(C), stream_handle()),
+              "mlt_avgpool_nhwc_fwd")
+        launches.bump("avgpool_fwd")
+        ctx.shape = x.shape
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        B, H, W, C = ctx.shape
+        dx = torch.empty((B, H, W, C), dtype=dy.dtype, device=dy.device)
+        check(_lib.lib().mlt_avgpool_nhwc_bwd(ptr(dy.contiguous()), ptr(dx), _c_int(B), _c_int(H * W), _c_int(C), stream_handle()),
+              "mlt_avgpool_nhwc_bwd")
+        launches.bump("avgpool_bwd")
+        return dx
+
+
+def global_avg_pool_nhwc(x):
+    return _AvgPoolFn.apply(x)
+
+
+def native_conv_ok(x: torch.Tensor) -> bool:
+    return use_native(x)

@@ -21,6 +21,8 @@ from ._lib import check, launches, ptr, stream_handle
 
 _c_int, _c_ll = ctypes.c_int, ctypes.c_longlong
 ACT_IDS = {None: 0, "none": 0, "relu": 1, "gelu": 2, "tanh": 3}
+SPLITK_WS_BYTES = 256 << 20          # fp32 partials of up to 16 K-slices of the largest weight gradient
+SPLITK_MAX_OUT = 8 << 20             # outputs beyond 8M elements have plenty of tiles already
 
 
 def gemm_supported(a: torch.Tensor, b: torch.Tensor) -> bool:
@@ -31,7 +33,7 @@ def gemm_supported(a: torch.Tensor, b: torch.Tensor) -> bool:
 
 def gemm(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = False, out: Optional[torch.Tensor] = None,
          out_dtype: torch.dtype = torch.bfloat16, bias: Optional[torch.Tensor] = None, act: Optional[str] = None,
-         aux_mode: int = 0, aux: Optional[torch.Tensor] = None, block_n: int = 0) -> torch.Tensor:
+         aux_mode: int = 0, aux: Optional[torch.Tensor] = None, block_n: int = 0, split_k: bool = True) -> torch.Tensor:
     M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
     N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
     if K != Kb:
@@ -40,12 +42,18 @@ def gemm(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = Fals
         n_pad = (N + 7) // 8 * 8             # keep the row pitch a multiple of 16 bytes
         full = torch.empty((M, n_pad), dtype=out_dtype, device=a.device)
         out = full[:, :N] if n_pad != N else full
+    ws = None
+    if split_k and bias is None and act in (None, "none") and aux_mode == 0 and M * N <= SPLITK_MAX_OUT and K >= 512:
+        from .functional import scratch
+
+        ws = scratch(a.device, "gemm_splitk", SPLITK_WS_BYTES)
     check(_lib.lib().mlt_gemm_bf16(ptr(a), _c_ll(a.stride(0)), _c_int(int(a_mn)), ptr(b), _c_ll(b.stride(0)),
                                    _c_int(int(b_mn)), ptr(out), _c_ll(out.stride(0)), _c_int(int(out.dtype == torch.float32)),
                                    _c_int(M), _c_int(N), _c_int(K), ptr(bias),
                                    _c_int(int(bias is not None and bias.dtype == torch.float32)), _c_int(ACT_IDS[act]),
                                    _c_int(aux_mode), ptr(aux), _c_ll(aux.stride(0) if aux is not None else 0),
-                                   _c_int(block_n), stream_handle()), "mlt_gemm_bf16")
+                                   _c_int(block_n), ptr(ws), _c_ll(ws.numel() if ws is not None else 0), stream_handle()),
+          "mlt_gemm_bf16")
     launches.bump("gemm_bf16_tcgen05")
     return out
 

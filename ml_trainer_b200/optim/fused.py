@@ -91,24 +91,34 @@ class FusedOptimizer(torch.optim.Optimizer):
         self.s2 = torch.zeros(off if nstate > 1 else 1, dtype=torch.float32, device=dev)
         self.hyper = torch.zeros(HYPER_LEN, dtype=torch.float32, device=dev)
         self.index_of = {}
+        # conv weights marked channels-last live physically as [Cout, KH, KW, Cin] (the GEMM operand layout of the
+        # NHWC convolution path) while keeping their logical [Cout, Cin, KH, KW] shape
+        self._cl = [bool(getattr(p, "_mlt_channels_last", False)) and p.dim() == 4 for p in order]
         with torch.no_grad():
-            for i, (p, o, n) in enumerate(zip(order, self.offsets, self.sizes)):
-                self.master[o:o + n].copy_(p.detach().reshape(-1).float())
+            for i, p in enumerate(order):
+                src = p.detach().clone()
+                self._view(self.master, i).copy_(src.float())
                 if self.model is not self.master:
-                    self.model[o:o + n].copy_(p.detach().reshape(-1))
-                p.data = self.model[o:o + n].view(p.shape)
+                    self._view(self.model, i).copy_(src)
+                p.data = self._view(self.model, i)
                 p.grad = None
-                p._mlt_grad_sink = self.grad[o:o + n].view(p.shape)   # where backward kernels write
+                p._mlt_grad_sink = self._view(self.grad, i)   # where backward kernels write
                 p._mlt_index = i
                 self.index_of[id(p)] = i
 
-    def grad_view(self, i: int) -> torch.Tensor:
+    def _view(self, flat: torch.Tensor, i: int) -> torch.Tensor:
         o, n = self.offsets[i], self.sizes[i]
-        return self.grad[o:o + n].view(self.params_in_order[i].shape)
+        shape = self.params_in_order[i].shape
+        if self._cl[i]:
+            Co, Ci, KH, KW = shape
+            return flat[o:o + n].view(Co, KH, KW, Ci).permute(0, 3, 1, 2)
+        return flat[o:o + n].view(shape)
+
+    def grad_view(self, i: int) -> torch.Tensor:
+        return self._view(self.grad, i)
 
     def master_view(self, i: int) -> torch.Tensor:
-        o, n = self.offsets[i], self.sizes[i]
-        return self.master[o:o + n].view(self.params_in_order[i].shape)
+        return self._view(self.master, i)
 
     def span(self, i_lo: int, i_hi: int):
         """Element range covering params ``i_lo .. i_hi-1`` (arena order)."""
@@ -191,8 +201,7 @@ class FusedOptimizer(torch.optim.Optimizer):
     def reload_from_params(self):
         """Re-read master/model copies after someone overwrote ``param.data`` contents in place."""
         for i, p in enumerate(self.params_in_order):
-            o, n = self.offsets[i], self.sizes[i]
-            self.master[o:o + n].copy_(p.detach().reshape(-1).float())
+            self._view(self.master, i).copy_(p.detach().float())
 
     @torch.no_grad()
     def load_master(self, named_tensors: dict, model: torch.nn.Module):
@@ -200,11 +209,10 @@ class FusedOptimizer(torch.optim.Optimizer):
             i = self.index_of.get(id(p))
             if i is None or name not in named_tensors:
                 continue
-            o, n = self.offsets[i], self.sizes[i]
-            src = named_tensors[name].to(self.device).reshape(-1)
-            self.master[o:o + n].copy_(src.float())
+            src = named_tensors[name].to(self.device)
+            self._view(self.master, i).copy_(src.float())
             if self.model is not self.master:
-                self.model[o:o + n].copy_(src)
+                self._view(self.model, i).copy_(src)
 
     def state_dict(self):
         return {

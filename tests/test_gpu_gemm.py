@@ -112,3 +112,31 @@ def test_gemm_throughput_report():
             rows.append((M, N, K, name, 2.0 * M * N * K * 10 / (s.elapsed_time(e) * 1e-3) / 1e12))
     for r in rows:
         print("GEMM %6d x %5d x %5d  %-8s %8.1f TFLOP/s" % r)
+
+
+@pytest.mark.parametrize("M,N,K", [(768, 768, 16384), (768, 3072, 8192), (128, 256, 4096), (2304, 768, 1000)])
+@pytest.mark.parametrize("out_dtype", [torch.bfloat16, torch.float32])
+def test_gemm_split_k_weight_gradient_shapes(M, N, K, out_dtype):
+    """dW = dY^T X: both operands MN-major, few output tiles, long K -> the split-K path."""
+    from ml_trainer_b200.ops.gemm import gemm, gemm_reference
+
+    a, b = _operands(M, N, K, True, True, seed=5)
+    d = gemm(a, b, True, True, out_dtype=out_dtype)
+    d2 = gemm(a, b, True, True, out_dtype=out_dtype, split_k=False)
+    torch.cuda.synchronize()
+    ref = gemm_reference(a, b, True, True)
+    _check(d, ref, K, f"split-K {M}x{N}x{K}")
+    _check(d2, ref, K, f"no split {M}x{N}x{K}")
+
+
+@pytest.mark.parametrize("M,N", [(16384, 768), (16384, 3072), (1000, 136), (33, 7), (4096, 2304)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_colsum(M, N, dtype):
+    from ml_trainer_b200.ops import functional as F
+
+    x = torch.randn(M, N, device=DEV).to(dtype)
+    for _ in range(2):
+        out = F.colsum(x)
+    ref = x.float().sum(0)
+    tol = 2e-2 * max(1.0, ref.abs().max().item()) if dtype == torch.bfloat16 else 1e-3 * M ** 0.5
+    assert (out.float() - ref).abs().max().item() <= tol
