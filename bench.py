@@ -11,9 +11,9 @@ Contract (one JSON line on rank 0; see DESIGN.md "bench.py"):
   --impl reference runs the UNMODIFIED reference Trainer from baseline/_ref (stock DDP + NCCL + cuDNN/cuBLAS)
           on the same config and prints the same line with "impl": "reference".
 
-Default config = the reference's own model and published setting: MLModel, global batch 32,
-SGD lr 1e-3 momentum 0.9, fp32, cross-entropy; strong scaling (the reference divides the global batch by the
-world size, src/trainer.py:63).
+Default config = the reference's own model and published setting: MLModel, batch 32 per GPU,
+SGD lr 1e-3 momentum 0.9, fp32, cross-entropy.  Weak scaling: the reference's batch_size is GLOBAL and is divided
+by the world size (src/trainer.py:63), so both arms are handed batch_size = 32 * N and every rank keeps 32 samples.
 """
 import argparse
 import json
@@ -35,7 +35,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--model", default="mlmodel", choices=["mlmodel", "resnet50", "bert_base"])
-    ap.add_argument("--batch", type=int, default=0, help="GLOBAL batch size (0 = the model's default)")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch size (0 = the model's default); global = batch * N")
     ap.add_argument("--metric", default=None, help="None (main.py default) or accuracy")
     ap.add_argument("--optimizer", default=None)
     ap.add_argument("--backend", default=None)
@@ -157,7 +157,7 @@ def run_ours(a):
     from ml_trainer_b200.ops import _lib
 
     cfg = MODEL_CFG[a.model]
-    gb = a.batch or cfg["batch"]
+    gb = (a.batch or cfg["batch"]) * world       # weak scaling: per-GPU batch fixed, the Trainer gets the GLOBAL batch
     K, W = a.steps, max(a.warmup, 3)
     warm, val = make_datasets(a.model, gb, W + 4, a.seq_len, seed=7)
     timed, _ = make_datasets(a.model, gb, K, a.seq_len)
@@ -210,7 +210,7 @@ def run_ours(a):
     out = {
         "metric": "train samples/sec (device-timed, max over ranks)", "value": round(sps, 2), "unit": "samples/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(dev_ms / K, 5), "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": round(sps / PUBLISHED[a.model], 3) if a.model in PUBLISHED else None,
+        "scaling": "weak", "vs_baseline": round(sps / PUBLISHED[a.model], 3) if a.model in PUBLISHED else None,
         "dtype": cfg["dtype"], "data": "synthetic (random inputs/labels of the named shape, random-init weights)",
         "impl": "ours",
         "config": {"model": a.model, "global_batch": gb, "per_rank_batch": per_rank,
@@ -280,7 +280,7 @@ def run_reference(a):
         print(json.dumps({"impl": "reference", "unavailable": "no CUDA device"}))
         return
     cfg = MODEL_CFG[a.model]
-    gb = a.batch or cfg["batch"]
+    gb = (a.batch or cfg["batch"]) * world       # weak scaling: per-GPU batch fixed, the Trainer gets the GLOBAL batch
     K, W = a.steps, max(a.warmup, 3)
     train, val = make_datasets(a.model, gb, K, a.seq_len)
     warm, _ = make_datasets(a.model, gb, W, a.seq_len, seed=7)
@@ -349,7 +349,7 @@ def run_reference(a):
     out = {
         "metric": "train samples/sec (device-timed, max over ranks)", "value": round(sps, 2), "unit": "samples/s",
         "n_gpus": world, "steps": steps, "warmup": W, "ms_per_step": round(ms / steps, 5), "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": round(sps / PUBLISHED[a.model], 3) if a.model in PUBLISHED else None,
+        "scaling": "weak", "vs_baseline": round(sps / PUBLISHED[a.model], 3) if a.model in PUBLISHED else None,
         "dtype": cfg["dtype"], "data": "synthetic (random inputs/labels of the named shape, random-init weights)",
         "impl": "reference",
         "config": {"model": a.model, "global_batch": gb, "per_rank_batch": per_rank, "parallelism": f"dp{world}",

@@ -46,6 +46,9 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void st_relaxed_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ FlagBlock* flags_of(const P2PArgs& a, int r) {
   return reinterpret_cast<FlagBlock*>(a.base[r] + a.flags_off);
 }
@@ -63,9 +66,12 @@ __device__ __forceinline__ void cta_exchange(const P2PArgs& a, int me, int kind,
     if (do_signal) {
       t = mine->tick[kind][cta] + 1;
       mine->tick[kind][cta] = t;
+      // ONE system-scope fence orders every data store of this CTA (the bar.sync above made them this thread's
+      // business) before the flags; the flags themselves are relaxed stores.  A release store per peer would pay
+      // one NVLink round trip each, serially (measured: ~5 us per peer).
       __threadfence_system();
       for (int p = 0; p < a.world; ++p)
-        if (p != me) st_release_sys(&flags_of(a, p)->sig[kind][cta][me], t);
+        if (p != me) st_relaxed_sys(&flags_of(a, p)->sig[kind][cta][me], t);
     } else {
       t = *ticket_io;
     }
