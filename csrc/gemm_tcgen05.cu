@@ -26,8 +26,8 @@ using namespace ptx;
 constexpr int BM = 128;        // tile rows (UMMA M)
 constexpr int BK = 64;         // k-block: 64 bf16 = 128 bytes = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kGemmThreads = 192;
 constexpr int kEpiWarps = 4;
+constexpr int kGemmThreads = 192;
 
 struct GemmParams {
   int M, N, K;
@@ -54,7 +54,8 @@ struct GemmCfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
   static constexpr int kTmemCols = 2 * BN;                   // two accumulator stages (power of two >= 32)
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kStagingBytes = kEpiWarps * 2 * 4096;   // per epilogue warp: two 32-row x 128-byte slabs for TMA stores
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& m_blk, int& n_blk) {
@@ -80,11 +81,13 @@ __device__ __forceinline__ float act_grad_from_pre(int act, float z) {
 
 template <int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                         const __grid_constant__ CUtensorMap tmOut, const GemmParams p) {
   using Cfg = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
+  uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;                 // 1024-byte aligned (stage sizes are)
+  uint64_t* full = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
   uint64_t* empty = full + Cfg::kStages;
   uint64_t* tmem_full = empty + Cfg::kStages;
   uint64_t* tmem_empty = tmem_full + 2;
@@ -97,6 +100,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
+    prefetch_tmap(&tmOut);
     for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], kEpiWarps * 32); }
     fence_mbar_init();
@@ -181,13 +185,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
   } else {
     // ===================================== epilogue ===========================================
+    // TMEM -> registers -> (bias / activation) -> 128-byte-swizzled smem slab -> TMA store.  Each warp owns the 32 rows
+    // of its TMEM lane quadrant and two 4 KB slabs (32 rows x 128 bytes = 64 bf16 or 32 fp32 columns), so stores of one
+    // slab overlap the conversion of the next; TMA clips rows >= M and columns >= N.
     const int q = warp & 3;                                 // TMEM lane quadrant this warp may read
+    uint8_t* my_stage = staging + (warp - 2) * 8192;
+    const int chunks_per_slab = p.out_f32 ? 1 : 2;          // a 32-column chunk is 128 B of fp32 or 64 B of bf16
+    uint32_t slab_count = 0;
     int as = 0; uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
       const int z = tile / tiles_per_problem;
       tile_coords(tile - z * tiles_per_problem, p.num_m, p.num_n, m_blk, n_blk);
-      const size_t obase = (size_t)(z % p.nb1) * p.ob1 + (size_t)(z / p.nb1) * p.ob2;
+      const int z1 = z % p.nb1, z2 = z / p.nb1;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * BN;
       mbar_wait(&tmem_full[as], aphase);
@@ -199,73 +209,86 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
         tmem_ld_32x32b_x32(taddr + c * 32, r);
         tmem_ld_wait();
         const int nb = n0 + c * 32;
-        if (row < p.M && nb < p.N) {
-          float v[32];
+        const int within = c % chunks_per_slab;
+        uint8_t* slab = my_stage + (slab_count & 1) * 4096;
+        if (within == 0) {
+          // the store that last read this slab was issued two slabs ago
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+        }
+        float v[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          const bool full_chunk = nb + 32 <= p.N;
-          if (p.bias != nullptr) {
-            if (p.bias_f32) {
-              const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        const bool live = nb < p.N;                          // whole chunk beyond N: nothing to compute, TMA clips it
+        const bool full_chunk = nb + 32 <= p.N;
+        if (live && p.bias != nullptr) {
+          if (p.bias_f32) {
+            const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __ldg(bp + j);
-            } else {
-              const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
+            for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __ldg(bp + j);
+          } else {
+            const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __bfloat162float(bp[j]);
-            }
+            for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __bfloat162float(bp[j]);
           }
-          if (p.aux_mode == 1) {            // keep the pre-activation for backward
-            __nv_bfloat16* ap = reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
-            if (full_chunk) {
+        }
+        if (live && row < p.M && p.aux_mode == 1) {          // keep the pre-activation for backward (direct stores)
+          __nv_bfloat16* ap = reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
+          if (full_chunk) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                uint4 pk;
-                pk.x = pack_bf16(v[j], v[j + 1]); pk.y = pack_bf16(v[j + 2], v[j + 3]);
-                pk.z = pack_bf16(v[j + 4], v[j + 5]); pk.w = pack_bf16(v[j + 6], v[j + 7]);
-                *reinterpret_cast<uint4*>(ap + j) = pk;
-              }
-            } else {
-              for (int j = 0; j < 32 && nb + j < p.N; ++j) ap[j] = __float2bfloat16_rn(v[j]);
+            for (int j = 0; j < 32; j += 8) {
+              uint4 pk;
+              pk.x = pack_bf16(v[j], v[j + 1]); pk.y = pack_bf16(v[j + 2], v[j + 3]);
+              pk.z = pack_bf16(v[j + 4], v[j + 5]); pk.w = pack_bf16(v[j + 6], v[j + 7]);
+              *reinterpret_cast<uint4*>(ap + j) = pk;
             }
+          } else {
+            for (int j = 0; j < 32 && nb + j < p.N; ++j) ap[j] = __float2bfloat16_rn(v[j]);
           }
-          if (p.aux_mode == 2) {            // dX = (dY W) * act'(z)
+        }
+        if (p.aux_mode == 2) {                               // dX = (dY W) * act'(z)
+          if (live && row < p.M) {
             const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
 #pragma unroll
             for (int j = 0; j < 32; ++j)
               if (full_chunk || nb + j < p.N) v[j] *= act_grad_from_pre(p.act, __bfloat162float(ap[j]));
-          } else if (p.act != ACT_NONE) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = act_fwd_rt(p.act, v[j]);
           }
-          if (p.out_f32) {
-            float* op = reinterpret_cast<float*>(p.out) + obase + (size_t)row * p.ldo + nb;
-            if (full_chunk) {
+        } else if (p.act != ACT_NONE) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(op + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-              for (int j = 0; j < 32 && nb + j < p.N; ++j) op[j] = v[j];
-            }
-          } else {
-            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(p.out) + obase + (size_t)row * p.ldo + nb;
-            if (full_chunk) {
+          for (int j = 0; j < 32; ++j) v[j] = act_fwd_rt(p.act, v[j]);
+        }
+        // registers -> swizzled slab: 16-byte chunk index is XORed with (row & 7), the layout SWIZZLE_128B expects
+        uint8_t* srow = slab + lane * 128;
+        if (p.out_f32) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                uint4 pk;
-                pk.x = pack_bf16(v[j], v[j + 1]); pk.y = pack_bf16(v[j + 2], v[j + 3]);
-                pk.z = pack_bf16(v[j + 4], v[j + 5]); pk.w = pack_bf16(v[j + 6], v[j + 7]);
-                *reinterpret_cast<uint4*>(op + j) = pk;
-              }
-            } else {
-              for (int j = 0; j < 32 && nb + j < p.N; ++j) op[j] = __float2bfloat16_rn(v[j]);
-            }
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(srow + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            uint4 pk;
+            pk.x = pack_bf16(v[8 * j], v[8 * j + 1]); pk.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+            pk.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]); pk.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+            *reinterpret_cast<uint4*>(srow + (((within * 4 + j) ^ (lane & 7)) << 4)) = pk;
           }
+        }
+        if (within == chunks_per_slab - 1) {
+          fence_proxy_async();                               // generic-proxy smem writes -> visible to the TMA engine
+          __syncwarp();
+          if (lane == 0) {
+            const int col0 = nb - within * 32;
+            tma_store_4d(&tmOut, slab, col0, m_blk * BM + q * 32, z1, z2);
+            tma_store_commit();
+          }
+          ++slab_count;
         }
       }
       tc_fence_before();
       mbar_arrive(&tmem_empty[as]);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+    if (lane == 0) tma_store_wait_all();                     // smem must outlive the last bulk stores
+    __syncwarp();
   }
   tc_fence_before();
   __syncthreads();
@@ -292,7 +315,7 @@ static EncodeTiledFn get_encode() {
 
 // bf16 tensor [b2][b1][outer][inner] with strides (elements) ld / s1 / s2, box {box_inner, box_outer, 1, 1}, 128B swizzle.
 static int make_tmap(CUtensorMap* out, const void* base, long long inner, long long outer, long long ld, int box_inner,
-                     int box_outer, int nb1 = 1, long long s1 = 0, int nb2 = 1, long long s2 = 0) {
+                     int box_outer, int nb1 = 1, long long s1 = 0, int nb2 = 1, long long s2 = 0, int elem_bytes = 2) {
   EncodeTiledFn enc = get_encode();
   MLT_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
   // Driver-API calls need the primary context bound to THIS host thread; autograd runs backward on its own threads
@@ -303,14 +326,15 @@ static int make_tmap(CUtensorMap* out, const void* base, long long inner, long l
   if (nb2 <= 1) { nb2 = 1; s2 = s1 * nb1; }
   if (s1 % 8 != 0) s1 = (s1 + 7) / 8 * 8;          // only reachable for size-1 batch dims (stride never used)
   if (s2 % 8 != 0) s2 = (s2 + 7) / 8 * 8;
-  MLT_REQUIRE(((uintptr_t)base % 16) == 0 && (ld * 2) % 16 == 0 && (s1 * 2) % 16 == 0 && (s2 * 2) % 16 == 0,
-              "TMA needs a 16-byte aligned base and strides that are multiples of 8 bf16 elements (ld=%lld s1=%lld s2=%lld)",
-              ld, s1, s2);
+  const int eb = elem_bytes;
+  MLT_REQUIRE(((uintptr_t)base % 16) == 0 && (ld * eb) % 16 == 0 && (s1 * eb) % 16 == 0 && (s2 * eb) % 16 == 0,
+              "TMA needs a 16-byte aligned base and strides that are multiples of 16 bytes (ld=%lld s1=%lld s2=%lld elements of %d B)",
+              ld, s1, s2, eb);
   cuuint64_t dims[4] = {(cuuint64_t)inner, (cuuint64_t)outer, (cuuint64_t)nb1, (cuuint64_t)nb2};
-  cuuint64_t strides[3] = {(cuuint64_t)ld * 2, (cuuint64_t)s1 * 2, (cuuint64_t)s2 * 2};
+  cuuint64_t strides[3] = {(cuuint64_t)ld * eb, (cuuint64_t)s1 * eb, (cuuint64_t)s2 * eb};
   cuuint32_t box[4] = {(cuuint32_t)box_inner, (cuuint32_t)box_outer, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = enc(out, eb == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   MLT_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%lld outer=%lld ld=%lld box=%dx%d nb=%dx%d)",
@@ -321,6 +345,9 @@ static int make_tmap(CUtensorMap* out, const void* base, long long inner, long l
 template <int BN>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
   using Cfg = GemmCfg<BN>;
+  // output map: rows of 128 bytes (64 bf16 / 32 fp32 columns) x 32 rows per store, batch dims as for the operands
+  CUtensorMap tmOut;
+  if (make_tmap(&tmOut, p.out, p.N, p.M, p.ldo, p.out_f32 ? 32 : 64, 32, p.nb1, p.ob1, p.nb2, p.ob2, p.out_f32 ? 4 : 2)) return 1;
   p.num_m = ceil_div(p.M, BM);
   p.num_n = ceil_div(p.N, BN);
   p.num_k = ceil_div(p.K, BK);
@@ -334,7 +361,7 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParam
   }
   long long tiles = (long long)p.num_m * p.num_n * p.nb1 * p.nb2;      // with split-K, nb1 carries the number of K slices
   int grid = tiles > kNumSMs ? kNumSMs : (int)tiles;
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, p);
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, tmOut, p);
   MLT_LAUNCH_CHECK();
   return 0;
 }
