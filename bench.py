@@ -255,7 +255,8 @@ def run_e2e_ours(tr, timed, K, dev, world, rank):
             "h2d_bytes_per_step": int(st.get("h2d_bytes", 0) / max(steps, 1)),
             "d2h_bytes_per_step": int(st.get("d2h_bytes", 0) / max(steps, 1)),
             "api": "Trainer.train_epoch (what fit() runs): in-memory dataset -> pinned staging -> copy-stream H2D -> step",
-            "executor": "native C++ epoch executor" if tr._native_ok(tr.train_loader, tr.model) else "python loop + PinnedPrefetcher",
+            "executor": "native C++ epoch executor" if (tr._native_ok(tr.train_loader, tr.model) or
+                                                        tr._native_graph_ok(tr.train_loader, tr.model)) else "python loop + PinnedPrefetcher",
             "final_loss": float(losses[steps - 1]) if losses is not None else None}
 
 

@@ -2,6 +2,7 @@
 // for attention scores.  One warp per row, 16-byte vector accesses, statistics in fp32.  Bandwidth-bound: the
 // roofline is bytes moved / HBM bandwidth.  Replaces ATen's layer_norm / add / softmax kernels of the BERT path.
 #include "common.cuh"
+#include "colreduce.cuh"
 #include "../include/mlt_b200.h"
 
 namespace mlt {
@@ -87,94 +88,70 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
   if (lane == 0) { mean_out[row] = mean; rstd_out[row] = rstd; }
 }
 
-// dx = rstd * (g*dy - mean(g*dy) - xhat * mean(g*dy*xhat));  dgamma = sum_rows dy*xhat;  dbeta = sum_rows dy.
-// grid-stride over rows; per-CTA column partials go to scratch [gridDim.x][2][H]; the last CTA reduces them.
-template <typename P, typename GO>
+// dx = rstd * (g*dy - mean(g*dy) - xhat * mean(g*dy*xhat)).  One warp per row, nothing carried between rows, so the
+// register footprint stays small and many warps are resident (this pass is pure bandwidth).
+template <typename P>
 __global__ void __launch_bounds__(256)
-layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h, const float* __restrict__ mean,
-                     const float* __restrict__ rstd, const P* __restrict__ gamma, __nv_bfloat16* __restrict__ dx,
-                     GO* __restrict__ dgamma, GO* __restrict__ dbeta, float* __restrict__ partial, unsigned int* __restrict__ ticket,
-                     int T, int H) {
-  extern __shared__ float sm[];          // [warps][2][H]
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h, const float* __restrict__ mean,
+                        const float* __restrict__ rstd, const P* __restrict__ gamma, __nv_bfloat16* __restrict__ dx, int T, int H) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= T) return;
   const int nvec = H / 8;
-  float g[kMaxVecPerLane][8], ag[kMaxVecPerLane][8], ab[kMaxVecPerLane][8];
+  const float mu = mean[row], rs = rstd[row];
+  float gd[kMaxVecPerLane][8], xh[kMaxVecPerLane][8];
+  float s1 = 0.f, s2 = 0.f;
 #pragma unroll
   for (int c = 0; c < kMaxVecPerLane; ++c) {
     const int iv = lane + 32 * c;
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { ag[c][j] = 0.f; ab[c][j] = 0.f; g[c][j] = 0.f; }
-    if (iv < nvec) load_param8<P>(gamma, iv * 8, g[c]);
-  }
-  for (int row = blockIdx.x * nwarp + warp; row < T; row += gridDim.x * nwarp) {
-    const float mu = mean[row], rs = rstd[row];
-    float d[kMaxVecPerLane][8], xh[kMaxVecPerLane][8];
-    float s1 = 0.f, s2 = 0.f;
-#pragma unroll
-    for (int c = 0; c < kMaxVecPerLane; ++c) {
-      const int iv = lane + 32 * c;
-      if (iv < nvec) {
-        unpack8(*reinterpret_cast<const uint4*>(dy + (size_t)row * H + iv * 8), d[c]);
-        unpack8(*reinterpret_cast<const uint4*>(h + (size_t)row * H + iv * 8), xh[c]);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          xh[c][j] = (xh[c][j] - mu) * rs;
-          ag[c][j] += d[c][j] * xh[c][j];
-          ab[c][j] += d[c][j];
-          const float gd = g[c][j] * d[c][j];
-          s1 += gd;
-          s2 += gd * xh[c][j];
-        }
-      }
-    }
-    s1 = warp_sum(s1) / (float)H;
-    s2 = warp_sum(s2) / (float)H;
-#pragma unroll
-    for (int c = 0; c < kMaxVecPerLane; ++c) {
-      const int iv = lane + 32 * c;
-      if (iv < nvec) {
-        float o[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = rs * (g[c][j] * d[c][j] - s1 - xh[c][j] * s2);
-        *reinterpret_cast<uint4*>(dx + (size_t)row * H + iv * 8) = pack8(o);
-      }
-    }
-  }
-  // column partials: warps -> smem -> CTA partial -> scratch
-#pragma unroll
-  for (int c = 0; c < kMaxVecPerLane; ++c) {
-    const int iv = lane + 32 * c;
-    if (iv < nvec)
+    if (iv < nvec) {
+      float g[8];
+      unpack8(*reinterpret_cast<const uint4*>(dy + (size_t)row * H + iv * 8), gd[c]);
+      unpack8(*reinterpret_cast<const uint4*>(h + (size_t)row * H + iv * 8), xh[c]);
+      load_param8<P>(gamma, iv * 8, g);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        sm[(warp * 2 + 0) * H + iv * 8 + j] = ag[c][j];
-        sm[(warp * 2 + 1) * H + iv * 8 + j] = ab[c][j];
+        xh[c][j] = (xh[c][j] - mu) * rs;
+        gd[c][j] *= g[j];
+        s1 += gd[c][j];
+        s2 = fmaf(gd[c][j], xh[c][j], s2);
       }
+    }
   }
-  __syncthreads();
-  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) {
-    const int which = i / H, col = i - which * H;
-    float s = 0.f;
-    for (int w = 0; w < nwarp; ++w) s += sm[(w * 2 + which) * H + col];
-    partial[((size_t)blockIdx.x * 2 + which) * H + col] = s;
+  s1 = warp_sum(s1) / (float)H;
+  s2 = warp_sum(s2) / (float)H;
+#pragma unroll
+  for (int c = 0; c < kMaxVecPerLane; ++c) {
+    const int iv = lane + 32 * c;
+    if (iv < nvec) {
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = rs * (gd[c][j] - s1 - xh[c][j] * s2);
+      *reinterpret_cast<uint4*>(dx + (size_t)row * H + iv * 8) = pack8(o);
+    }
   }
-  __shared__ bool is_last;
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned int t = atomicAdd(ticket, 1u);
-    is_last = t == gridDim.x - 1;
-    if (is_last) *ticket = 0u;
-  }
-  __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) {
-    const int which = i / H, col = i - which * H;
-    float s = 0.f;
-    for (unsigned int k = 0; k < gridDim.x; ++k) s += __ldcg(partial + ((size_t)k * 2 + which) * H + col);
-    if (which == 0) dgamma[col] = from_float<GO>(s);
-    else dbeta[col] = from_float<GO>(s);
+}
+
+// dgamma[c] = sum_rows dy * xhat;  dbeta[c] = sum_rows dy   (column reduction, see colreduce.cuh)
+template <typename GO>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_params_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h, const float* __restrict__ mean,
+                            const float* __restrict__ rstd, GO* __restrict__ dgamma, GO* __restrict__ dbeta, float* __restrict__ partial,
+                            unsigned int* __restrict__ tickets, int T, int H) {
+  __shared__ float tot[2][kBnTile];
+  auto f = [&](int r, int c0, float (&a)[8], float (&b)[8]) {
+    float d[8], x[8];
+    unpack8(*reinterpret_cast<const uint4*>(dy + (size_t)r * H + c0), d);
+    unpack8(*reinterpret_cast<const uint4*>(h + (size_t)r * H + c0), x);
+    const float mu = mean[r], rs = rstd[r];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { a[j] = fmaf(d[j], (x[j] - mu) * rs, a[j]); b[j] += d[j]; }
+  };
+  if (!column_reduce2(f, partial, tickets, T, H, tot)) return;
+  const int c = blockIdx.x * kBnTile + threadIdx.x;
+  if (c < H) {
+    dgamma[c] = from_float<GO>(tot[0][threadIdx.x]);
+    dbeta[c] = from_float<GO>(tot[1][threadIdx.x]);
   }
 }
 
@@ -247,10 +224,11 @@ softmax_rows_bwd_kernel(__nv_bfloat16* __restrict__ dp, const __nv_bfloat16* __r
   }
 }
 
-static int ln_bwd_grid(int T) {
-  int g = ceil_div(T, 8 * 8);          // >= 8 rows per warp
-  if (g > 2 * kNumSMs) g = 2 * kNumSMs;
-  return g < 1 ? 1 : g;
+static int ln_rows_split(int T, int H) {
+  const int tiles = ceil_div(H, kBnTile);
+  int R = (4 * kNumSMs) / tiles;
+  if (R > ceil_div(T, 64)) R = ceil_div(T, 64);
+  return R < 1 ? 1 : R;
 }
 
 }  // namespace mlt
@@ -273,30 +251,33 @@ extern "C" int mlt_layernorm_fwd(const void* x, const void* res, const void* gam
   return 0;
 }
 
-extern "C" long long mlt_layernorm_bwd_scratch_bytes(int T, int H) { return 256 + (long long)ln_bwd_grid(T) * 2 * H * 4; }
+extern "C" long long mlt_layernorm_bwd_scratch_bytes(int T, int H) {
+  return ((long long)ceil_div(H, kBnTile) * 4 + 255) / 256 * 256 + (long long)ln_rows_split(T, H) * 2 * H * 4;
+}
 
 extern "C" int mlt_layernorm_bwd(const void* dy, const void* h, const void* mean, const void* rstd, const void* gamma,
                                  int params_bf16, void* dx, void* dgamma, void* dbeta, int grads_bf16, void* scratch,
                                  long long scratch_bytes, int T, int H, void* stream) {
   MLT_REQUIRE(H % 8 == 0 && H <= 8 * 32 * kMaxVecPerLane, "mlt_layernorm_bwd: width %d unsupported", H);
   MLT_REQUIRE(scratch && scratch_bytes >= mlt_layernorm_bwd_scratch_bytes(T, H), "mlt_layernorm_bwd: scratch too small");
-  const int grid = ln_bwd_grid(T);
-  const size_t smem = (size_t)8 * 2 * H * sizeof(float);
-  unsigned int* ticket = (unsigned int*)scratch;
-  float* partial = (float*)((char*)scratch + 256);
   cudaStream_t st = (cudaStream_t)stream;
-#define LNB(P, GO)                                                                                                        \
-  do {                                                                                                                    \
-    auto k = layernorm_bwd_kernel<P, GO>;                                                                                 \
-    if (smem > 40 * 1024) MLT_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    k<<<grid, 256, smem, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean, (const float*)rstd,  \
-                               (const P*)gamma, (__nv_bfloat16*)dx, (GO*)dgamma, (GO*)dbeta, partial, ticket, T, H);      \
-  } while (0)
-  if (params_bf16 && grads_bf16) LNB(__nv_bfloat16, __nv_bfloat16);
-  else if (params_bf16) LNB(__nv_bfloat16, float);
-  else if (grads_bf16) LNB(float, __nv_bfloat16);
-  else LNB(float, float);
-#undef LNB
+  const int grid = ceil_div(T, 8);
+  if (params_bf16)
+    layernorm_bwd_dx_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean,
+        (const float*)rstd, (const __nv_bfloat16*)gamma, (__nv_bfloat16*)dx, T, H);
+  else
+    layernorm_bwd_dx_kernel<float><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean,
+        (const float*)rstd, (const float*)gamma, (__nv_bfloat16*)dx, T, H);
+  MLT_LAUNCH_CHECK();
+  unsigned int* tickets = (unsigned int*)scratch;
+  float* partial = (float*)((char*)scratch + ((long long)ceil_div(H, kBnTile) * 4 + 255) / 256 * 256);
+  dim3 g2(ceil_div(H, kBnTile), ln_rows_split(T, H));
+  if (grads_bf16)
+    layernorm_bwd_params_kernel<__nv_bfloat16><<<g2, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean,
+        (const float*)rstd, (__nv_bfloat16*)dgamma, (__nv_bfloat16*)dbeta, partial, tickets, T, H);
+  else
+    layernorm_bwd_params_kernel<float><<<g2, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean,
+        (const float*)rstd, (float*)dgamma, (float*)dbeta, partial, tickets, T, H);
   MLT_LAUNCH_CHECK();
   return 0;
 }

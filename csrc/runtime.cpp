@@ -61,6 +61,9 @@ struct Loop {
   long long loss_cap = 0;
   // statistics of the last run
   long long h2d_bytes = 0, d2h_bytes = 0, launches = 0;
+  // Large samples (images): skip the host gather of x and let the copy engine gather instead - one cudaMemcpyAsync per
+  // sample straight from the (page-locked) dataset into the slot's device buffer.
+  bool direct_x = false;
 };
 
 // rows `idx[0..n)` of a [N][row] byte matrix -> dst
@@ -106,6 +109,8 @@ extern "C" void* mlt_loop_create(int device, int slots, long long max_batch, lon
 extern "C" void* mlt_loop_slot_x(void* loop, int slot) { return ((Loop*)loop)->ring[slot].dev_x; }
 extern "C" void* mlt_loop_slot_y(void* loop, int slot) { return ((Loop*)loop)->ring[slot].dev_y; }
 extern "C" int mlt_loop_num_slots(void* loop) { return ((Loop*)loop)->slots; }
+// on != 0: the dataset's x tensor is page-locked; copy samples device-ward one by one instead of gathering on the host
+extern "C" int mlt_loop_set_direct_rows(void* loop, int on) { ((Loop*)loop)->direct_x = on != 0; return 0; }
 
 extern "C" int mlt_loop_destroy(void* loop) {
   Loop* L = (Loop*)loop;
@@ -169,7 +174,7 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
       const int s = (int)(i % S);
       while (free_for[s].load(std::memory_order_acquire) < i && !abort.load()) std::this_thread::yield();
       const long long n = bs_of(i);
-      gather_rows((char*)L->ring[s].pin_x, hx, L->x_row, indices + start[i], n);
+      if (!L->direct_x) gather_rows((char*)L->ring[s].pin_x, hx, L->x_row, indices + start[i], n);
       gather_rows((char*)L->ring[s].pin_y, hy, L->y_row, indices + start[i], n);
       gathered[s].store(i + 1, std::memory_order_release);
     }
@@ -190,7 +195,19 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
     while (gathered[s].load(std::memory_order_acquire) != i + 1) std::this_thread::yield();
     // device buffers of this slot are free once the step that last used them has finished
     if (sl.used) { if ((rc = (int)cudaStreamWaitEvent(L->copy, sl.released, 0)) != 0) break; }
-    if ((rc = (int)cudaMemcpyAsync(sl.dev_x, sl.pin_x, (size_t)n * L->x_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
+    if (L->direct_x) {
+      const long long* idx = indices + start[i];
+      for (long long j = 0; j < n && rc == 0; ) {
+        long long run = 1;                                  // coalesce runs of consecutive sample ids into one copy
+        while (j + run < n && idx[j + run] == idx[j + run - 1] + 1) ++run;
+        rc = (int)cudaMemcpyAsync((char*)sl.dev_x + (size_t)j * L->x_row, hx + (size_t)idx[j] * L->x_row, (size_t)run * L->x_row,
+                                  cudaMemcpyHostToDevice, L->copy);
+        j += run;
+      }
+      if (rc != 0) break;
+    } else {
+      if ((rc = (int)cudaMemcpyAsync(sl.dev_x, sl.pin_x, (size_t)n * L->x_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
+    }
     if ((rc = (int)cudaMemcpyAsync(sl.dev_y, sl.pin_y, (size_t)n * L->y_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
     if ((rc = (int)cudaEventRecord(sl.ready, L->copy)) != 0) break;
     L->h2d_bytes += n * (long long)(L->x_row + L->y_row);

@@ -164,6 +164,7 @@ void* mlt_loop_create(int device, int slots, long long max_batch, long long x_ro
 void* mlt_loop_slot_x(void* loop, int slot);
 void* mlt_loop_slot_y(void* loop, int slot);
 int mlt_loop_num_slots(void* loop);
+int mlt_loop_set_direct_rows(void* loop, int on);   /* x rows are page-locked: gather by DMA (one copy per sample) */
 int mlt_loop_destroy(void* loop);
 /* Runs `steps` steps: host gather -> pinned -> H2D (copy stream) -> hyper row H2D -> step -> loss D2H, ring-buffered.
  * step_kind 0: single-kernel LeNet step (`lenet`);  1: one captured cudaGraphExec_t per slot (`graph_execs`). */

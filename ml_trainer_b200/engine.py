@@ -33,6 +33,7 @@ class StepEngine:
         self.device = device
         self.compute_dtype = compute_dtype
         self.acc = torch.zeros(3, dtype=torch.float32, device=device)
+        self.loss_static = torch.zeros((), dtype=torch.float32, device=device)   # last step's loss at a fixed address
         self._one = torch.ones((), dtype=torch.float32, device=device)
         want = graph if isinstance(graph, bool) else (str(graph).lower() in ("1", "true", "auto", "yes"))
         self.use_graph = bool(want) and device.type == "cuda"
@@ -64,6 +65,12 @@ class StepEngine:
         """How many of the last ``last_n_steps`` train steps were graph replays (all of them once captured)."""
         return min(self.graph_replays, last_n_steps) if self.use_graph else 0
 
+    def graph_exec_handle(self, inputs, targets):
+        """Raw ``cudaGraphExec_t`` of the step captured on these input buffers (None until it has been captured)."""
+        key = (inputs.data_ptr(), targets.data_ptr(), tuple(inputs.shape), tuple(targets.shape))
+        g = self._graphs.get(key)
+        return None if g is None else int(g.raw_cuda_graph_exec())
+
     def invalidate(self):
         """Drop captured graphs (after a checkpoint load or any out-of-band state change)."""
         self._graphs.clear()
@@ -78,6 +85,9 @@ class StepEngine:
         """
         from .utils import metrics as M
 
+        if self.compute_dtype != torch.float32 and inputs.is_floating_point() and inputs.dtype != self.compute_dtype \
+                and not getattr(model, "_mlt_accepts_fp32_input", False):
+            inputs = inputs.to(self.compute_dtype)       # inside the captured graph; library models convert themselves
         outputs = model(inputs)
         fused = (getattr(self.criterion, "native_fused", False) and outputs.dim() == 2
                  and targets.dtype == torch.int64)
@@ -108,7 +118,8 @@ class StepEngine:
         else:
             loss.backward()
         self.reducer.finish_step()
-        self.last_loss = loss.detach()
+        self.loss_static.copy_(loss.detach().float())
+        self.last_loss = self.loss_static
 
     def train_step(self, inputs, targets):
         opt = self.reducer.opt

@@ -64,6 +64,7 @@ class Bottleneck(nn.Module):
 
 class ResNet(nn.Module):
     _mlt_native = True
+    _mlt_accepts_fp32_input = True        # the NHWC conversion kernel reads the fp32 NCHW batch directly
 
     def __init__(self, layers=(3, 4, 6, 3), num_classes=1000, width=64):
         super().__init__()
@@ -94,7 +95,7 @@ class ResNet(nn.Module):
     def forward(self, x):
         if x.is_cuda and F.native_available() and self.conv1.weight.dtype == torch.bfloat16:
             return self._forward_native(x)
-        return self._forward_torch(x)
+        return self._forward_torch(x.to(self.conv1.weight.dtype))
 
     def _forward_torch(self, x):
         x = self.maxpool(self.relu(self.bn1(self.conv1(x))))

@@ -89,6 +89,38 @@ class NativeLoop:
         return losses
 
 
+    # ------------------------------------------------------------------ generic (CUDA-graph) steps
+    def slot_tensors(self, slot: int, x_shape, x_dtype, y_shape, y_dtype):
+        """Zero-copy torch views of a ring slot's device buffers (what the captured graphs read)."""
+        from .parallel.p2p import _DevMem
+
+        xp, yp = self.slot_buffers(slot)
+        xb = int(torch.Size(x_shape).numel()) * torch.empty((), dtype=x_dtype).element_size()
+        yb = int(torch.Size(y_shape).numel()) * torch.empty((), dtype=y_dtype).element_size()
+        x = torch.as_tensor(_DevMem(xp, xb, self), device=self.device).view(x_dtype).view(x_shape)
+        y = torch.as_tensor(_DevMem(yp, yb, self), device=self.device).view(y_dtype).view(y_shape)
+        return x, y
+
+    def set_direct_rows(self, on: bool):
+        self.L.mlt_loop_set_direct_rows(self.h, _c_int(int(on)))
+
+    def run_graphs(self, graph_execs: Sequence[int], hyper_dev: torch.Tensor, host_x, host_y, indices, batch: int,
+                   hyper_rows: Optional[torch.Tensor], loss_dev: torch.Tensor, n_launches_per_step: int = 0) -> torch.Tensor:
+        """Run full-batch steps whose work is one captured CUDA graph per ring slot."""
+        steps = indices.numel() // batch
+        execs = (_c_vp * len(graph_execs))(*graph_execs)
+        losses = torch.empty(steps, dtype=torch.float32)
+        hr = hyper_rows.contiguous() if hyper_rows is not None else None
+        idx = indices.contiguous()
+        check(self.L.mlt_loop_run(self.h, ptr(host_x), ptr(host_y), ptr(idx), _c_ll(steps), _c_int(batch), None, ptr(hr),
+                                  ptr(hyper_dev), _c_int(1), None, execs, ptr(loss_dev), ptr(losses), stream_handle()),
+              "mlt_loop_run")
+        if n_launches_per_step:
+            launches.bump("graph_replay_kernels", n_launches_per_step * steps)
+        self._finish(steps)
+        return losses
+
+
 def epoch_indices(loader) -> tuple:
     """Flatten a Loader's batch order into (int64 index tensor, per-step batch sizes)."""
     batches: List[List[int]] = [list(b) for b in loader.batch_sampler]

@@ -221,8 +221,7 @@ class Trainer:
 
     # -------------------------------------------------------------------- loops
     def _feed(self, loader):
-        cast = self.compute_dtype if self.compute_dtype != torch.float32 else None
-        return PinnedPrefetcher(loader, self.device, slots=max(self.cfg.prefetch, 1), cast_inputs=cast)
+        return PinnedPrefetcher(loader, self.device, slots=max(self.cfg.prefetch, 1))   # dtype casts happen in the step
 
     def _bar(self, it, total):
         disable = (not self.cfg.progress) or self.rank != 0
@@ -245,6 +244,83 @@ class Trainer:
         x, y = loader._backing[0], loader._backing[1]
         return (x.dtype == torch.float32 and x.dim() == 4 and tuple(x.shape[1:]) == (3, 32, 32) and x.is_contiguous()
                 and y.dtype == torch.int64 and y.dim() == 1 and y.is_contiguous())
+
+    def _native_graph_ok(self, loader, model) -> bool:
+        """Whole-epoch C++ execution of CUDA-graph steps: any model, in-memory tensor dataset, full batches."""
+        eng = self.engine
+        return (eng.fused is None and eng.use_graph and model is self.model and self.cfg.native_loop
+                and getattr(loader, "_fast", False) and self.device.type == "cuda"
+                and all(t.is_contiguous() for t in loader._backing[:2]) and len(loader._backing) == 2)
+
+    def _train_epoch_native_graph(self, epoch):
+        """Python drives the first steps (eager warm-up, then one graph capture per ring slot); the C++ executor
+        replays the captured graphs for the rest of the epoch; a trailing partial batch runs eagerly."""
+        from .runtime import epoch_indices
+
+        eng, opt, loader = self.engine, self.optimizer, self.train_loader
+        idx, sizes = epoch_indices(loader)
+        B = loader.batch_size
+        nb = len(sizes)
+        full = sum(1 for s in sizes if s == B)
+        loop = self._native_loop_for(loader)
+        x_be, y_be = loader._backing
+        if not hasattr(self, "_slot_views") or self._slot_views_key != id(loop):
+            self._slot_views = [loop.slot_tensors(s, (B, *x_be.shape[1:]), x_be.dtype, (B, *y_be.shape[1:]), y_be.dtype)
+                                for s in range(loop.slots)]
+            self._slot_views_key = id(loop)
+            row_bytes = x_be[0].numel() * x_be.element_size()
+            if row_bytes >= 32768 and x_be.numel() * x_be.element_size() <= (8 << 30):
+                try:                                   # page-lock the dataset once: samples then go device-ward by DMA
+                    if not x_be.is_pinned():
+                        rc = torch.cuda.cudart().cudaHostRegister(x_be.data_ptr(), x_be.numel() * x_be.element_size(), 0)
+                        if int(rc) != 0:
+                            raise RuntimeError(f"cudaHostRegister -> {rc}")
+                    loop.set_direct_rows(True)
+                except Exception:                      # registration refused (ulimit): keep the host gather
+                    loop.set_direct_rows(False)
+        pin_losses = torch.zeros(nb, dtype=torch.float32).pin_memory()
+        step = 0
+
+        def python_step(i):
+            sel = idx[i * B:i * B + sizes[i]]
+            if sizes[i] == B:
+                xs, ys = self._slot_views[i % loop.slots]
+                xs.copy_(x_be[sel]); ys.copy_(y_be[sel])
+            else:
+                xs, ys = x_be[sel].to(self.device), y_be[sel].to(self.device)
+            eng.train_step(xs, ys)
+            pin_losses[i].copy_(eng.last_loss, non_blocking=True)
+            if self.scheduler_type == "CosineAnnealingWarmRestarts":
+                self.scheduler.step(epoch - 1 + i / nb)
+
+        while step < full and any(eng.graph_exec_handle(*self._slot_views[s]) is None for s in range(loop.slots)):
+            python_step(step)
+            step += 1
+        if step < full:
+            # ring alignment: the executor's step j uses slot j % S, so start it on a multiple of S
+            while step % loop.slots != 0 and step < full:
+                python_step(step)
+                step += 1
+        if step < full:
+            rows = []
+            for i in range(step, full):
+                rows.append(opt.hyper_for_next_step(self.reducer.grad_scale).pack())
+                opt.step_count += 1
+                opt._opt_called = True
+                if self.scheduler_type == "CosineAnnealingWarmRestarts":
+                    self.scheduler.step(epoch - 1 + i / nb)
+            execs = [eng.graph_exec_handle(*self._slot_views[s]) for s in range(loop.slots)]
+            torch.cuda.current_stream().synchronize()
+            losses = loop.run_graphs(execs, opt.hyper, x_be, y_be, idx[step * B:full * B], B, torch.tensor(rows, dtype=torch.float32),
+                                     eng.loss_static, eng.launches_per_step)
+            pin_losses[step:full] = losses
+            eng.graph_replays += full - step
+            self.last_native_stats = dict(loop.last_stats)
+            step = full
+        for i in range(step, nb):
+            python_step(i)
+        self.last_step_losses = pin_losses
+        return nb
 
     def _native_loop_for(self, loader):
         from .runtime import NativeLoop
@@ -290,6 +366,15 @@ class Trainer:
         nb = len(self.train_loader)
         if self._native_ok(self.train_loader, self.model):
             self._run_native_epoch(self.train_loader, epoch, train=True)
+            if self.scheduler_type == "StepLR":
+                self.scheduler.step()
+            loss, metric = self._reduce_epoch(eng.accumulators())
+            self.train_losses.append(loss)
+            if self.metric:
+                self.train_metrics.append(metric)
+            return
+        if self._native_graph_ok(self.train_loader, self.model):
+            self._train_epoch_native_graph(epoch)
             if self.scheduler_type == "StepLR":
                 self.scheduler.step()
             loss, metric = self._reduce_epoch(eng.accumulators())
