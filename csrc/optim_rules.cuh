@@ -16,7 +16,7 @@ struct Hyper {
 };
 static_assert(sizeof(Hyper) == 32, "hyper vector is 8 floats");
 
-enum RuleId : int { RULE_SGD = 0, RULE_ADAM = 1, RULE_ADAMW = 2, RULE_ADAGRAD = 3, RULE_ADAMAX = 4 };
+enum RuleId : int { RULE_SGD = 0, RULE_ADAM = 1, RULE_ADAMW = 2, RULE_ADAGRAD = 3, RULE_ADAMAX = 4, RULE_MEAN_ONLY = 5 };
 
 // Each rule: update(p, g, s1, s2, h) in registers.  g arrives already scaled.
 struct SgdRule {
@@ -73,6 +73,13 @@ struct AdamaxRule {
   }
 };
 
+// "Rule" that only hands back the (scaled) reduced gradient: turns the fused kernels into a plain mean all-reduce
+// (the semantics of the reference's _average_gradients, src/trainer.py:152-158).
+struct MeanOnlyRule {
+  static constexpr int kStates = 1;
+  __device__ __forceinline__ static void apply(float& p, float g, float& s1, float& s2, const Hyper& h) { p = g; }
+};
+
 // Dispatch a runtime rule id onto a functor-templated callable:  MLT_DISPATCH_RULE(id, R, { foo<R>(...); })
 #define MLT_DISPATCH_RULE(rule_id, R, ...)                         \
   switch (rule_id) {                                               \
@@ -81,6 +88,7 @@ struct AdamaxRule {
     case ::mlt::RULE_ADAMW:   { using R = ::mlt::AdamWRule;   __VA_ARGS__; break; } \
     case ::mlt::RULE_ADAGRAD: { using R = ::mlt::AdagradRule; __VA_ARGS__; break; } \
     case ::mlt::RULE_ADAMAX:  { using R = ::mlt::AdamaxRule;  __VA_ARGS__; break; } \
+    case ::mlt::RULE_MEAN_ONLY: { using R = ::mlt::MeanOnlyRule; __VA_ARGS__; break; } \
     default: ::mlt::set_error("unknown optimizer rule id %d", (int)(rule_id)); return 1; \
   }
 

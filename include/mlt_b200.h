@@ -28,6 +28,7 @@ extern "C" {
 #define MLT_RULE_ADAMW 2
 #define MLT_RULE_ADAGRAD 3
 #define MLT_RULE_ADAMAX 4
+#define MLT_RULE_MEAN_ONLY 5 /* no update: the fused all-reduce kernels just return the mean gradient */
 
 /* ---- library ------------------------------------------------------------------------------------ */
 const char* mlt_last_error(void);

@@ -193,11 +193,30 @@ class P2PComm(Comm):
         launches.bump(f"p2p_allreduce_update_{algo}")
 
     def all_reduce_mean(self, flat, stream=None):
-        """Unfused mean all-reduce (API parity with the reference's ``_average_gradients``): library collective."""
+        """Unfused in-place mean all-reduce (the reference's ``_average_gradients``), through the same P2P / NVLS
+        kernels with the "mean only" rule: the reduced values are written back over the gradients on every rank."""
         if self.world_size == 1:
             return
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM)
-        flat.div_(self.world_size)
+        off = self.arena.offset_of(flat) if self.arena is not None else None
+        n = flat.numel()
+        esz = flat.element_size()
+        if off is None or off % 16 != 0 or n % 8 != 0 or flat.dtype not in (torch.float32, torch.bfloat16):
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM)          # tensors outside the arena: library collective
+            flat.div_(self.world_size)
+            return
+        algo = self.pick_algo(n * esz)
+        if algo == "oneshot" and n * esz > self.oneshot_max:
+            algo = "nvls" if self.arena.multicast else "twoshot"
+        tmp_p = torch.empty(n, dtype=torch.float32, device=self.device)
+        tmp_s = torch.empty(n, dtype=torch.float32, device=self.device)
+        hyper = torch.zeros(8, dtype=torch.float32, device=self.device)
+        hyper[7] = 1.0 / self.world_size
+        one = lambda t: (_c_vp * 1)(t.data_ptr() if t is not None else 0)
+        check(self.L.mlt_p2p_allreduce_update(
+            ctypes.byref(self.ctx), _c_int(ALGO_IDS[algo]), _c_int(5), _c_int(int(flat.dtype == torch.bfloat16)), _c_ll(off),
+            _c_ll(off), _c_int(0), one(tmp_p), one(tmp_s), one(None), one(hyper), _c_ll(n), _c_int(0), _c_int(1),
+            stream_handle(stream)), "mlt_p2p_allreduce_update(mean only)")
+        launches.bump(f"p2p_allreduce_{algo}")
 
     def broadcast(self, tensor, src=0):
         if self.world_size == 1:

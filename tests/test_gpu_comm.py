@@ -130,3 +130,26 @@ def test_emulated_broadcast_and_scalar_reduce(world):
         expect = torch.tensor([sum(range(world)), float(world), 10.0 * sum(range(world))])
         for r in range(world):
             assert torch.allclose(vals[r].cpu(), expect), (rep, r, vals[r])
+
+
+@pytest.mark.parametrize("algo", [0, 1])
+@pytest.mark.parametrize("gdtype", [torch.float32, torch.bfloat16])
+def test_emulated_mean_only_allreduce(algo, gdtype):
+    """Rule 5 ("mean only"): the fused kernels act as a plain in-place mean all-reduce over the gradient buffers."""
+    world, n = 4, 128 * 9
+    fw = FakeWorld(world, n, gdtype)
+    grads = [torch.randn(n).to(gdtype) for _ in range(world)]
+    for r in range(world):
+        fw.grad(r).copy_(grads[r])
+    tmp = [torch.empty(n, device=DEV) for _ in range(2 * world)]
+    hyp = [torch.tensor([0, 0, 0, 0, 0, 1, 1, 1.0 / world], device=DEV) for _ in range(world)]
+    rc = fw.L.mlt_p2p_allreduce_update(ctypes.byref(fw.ctx), C_INT(algo), C_INT(5), C_INT(int(gdtype == torch.bfloat16)),
+                                       C_LL(fw.grad_off), C_LL(fw.grad_off), C_INT(0), _ptrs(tmp[:world]), _ptrs(tmp[world:]),
+                                       _ptrs([None] * world), _ptrs(hyp), C_LL(n), C_INT(2), C_INT(world),
+                                       C_VP(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0, fw.L.mlt_last_error()
+    torch.cuda.synchronize()
+    ref = sum(g.float() for g in grads) / world
+    for r in range(world):
+        got = fw.grad(r).float().cpu()
+        assert torch.allclose(got, ref, rtol=1e-2 if gdtype == torch.bfloat16 else 1e-6, atol=1e-2 if gdtype == torch.bfloat16 else 1e-6)
