@@ -17,6 +17,8 @@
 // Numerics are fp32 throughout, same formulas as the layer kernels in small_nn.cu / loss.cu (the tested oracle).
 #include "p2p_device.cuh"
 #include "../include/mlt_b200.h"
+#include <cooperative_groups.h>
+#include <cstdlib>
 
 namespace mlt {
 
@@ -84,6 +86,110 @@ __device__ __forceinline__ void grid_barrier(unsigned int* sync, unsigned int nb
 }
 
 __device__ __forceinline__ float dot4(const float4& a, const float4& b) { return a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w; }
+
+// Phase B (after the grid barrier): batch loss / accuracy into the device accumulators, then every thread reduces the
+// gradient of the arena elements it owns over the batch, exchanges it with the peers (multi-GPU) and applies the rule.
+template <typename R>
+__device__ __forceinline__ void lenet_phase_b(const LeNetArgs& a, float inv_B) {
+  using namespace lenet;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (blockIdx.x == 0 && warp == 0) {            // batch loss / accuracy -> device accumulators
+    float l = 0.f, c = 0.f;
+    for (int b = lane; b < a.B; b += 32) {
+      l += __ldcg(a.scratch + (size_t)b * S_STRIDE + S_DL + 10);
+      c += __ldcg(a.scratch + (size_t)b * S_STRIDE + S_DL + 11);
+    }
+    l = warp_sum(l);
+    c = warp_sum(c);
+    if (lane == 0) {
+      const float loss = l * inv_B;
+      if (a.loss_out) *a.loss_out = loss;
+      if (a.acc3) {
+        a.acc3[0] += loss;
+        if (a.want_acc) a.acc3[1] += c * inv_B;
+        a.acc3[2] += 1.0f;
+      }
+    }
+  }
+  if (!a.train) return;
+
+  const Hyper h = *a.hyper;
+  const int per_cta = (int)ceil_div64(a.numel, (long long)gridDim.x * kThreads) * kThreads;   // elements owned by a CTA
+  const long long e0 = (long long)blockIdx.x * per_cta;
+  const int per_thread = per_cta / kThreads;
+  float g[kMaxPerThread];
+  const int B = a.B;
+#pragma unroll
+  for (int r = 0; r < kMaxPerThread; ++r) {
+    g[r] = 0.f;
+    if (r >= per_thread) continue;
+    const long long e = e0 + (long long)r * kThreads + tid;
+    if (e >= a.numel) continue;
+    // which parameter does arena element e belong to?
+    int pid = -1; int i = 0;
+#pragma unroll
+    for (int p = 0; p < NPARAM; ++p) {
+      const long long d = e - a.off[p];
+      if (d >= 0 && d < kParamSize[p]) { pid = p; i = (int)d; }
+    }
+    if (pid < 0) continue;                        // alignment padding between parameters
+    const float* sc = a.scratch;
+    float s = 0.f;
+    switch (pid) {
+      case P_F1W: { const int n = i / FLAT, k = i - n * FLAT;
+        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_D1 + n), __ldcg(sc + (size_t)b * S_STRIDE + S_A2 + k), s); break; }
+      case P_F2W: { const int n = i / F1, k = i - n * F1;
+        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_D2 + n), __ldcg(sc + (size_t)b * S_STRIDE + S_Z1 + k), s); break; }
+      case P_F3W: { const int n = i / F2, k = i - n * F2;
+        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_DL + n), __ldcg(sc + (size_t)b * S_STRIDE + S_Z2 + k), s); break; }
+      case P_F1B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_D1 + i); break;
+      case P_F2B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_D2 + i); break;
+      case P_F3B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_DL + i); break;
+      case P_C2W: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW2 + i); break;
+      case P_C2B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW2 + W2N + i); break;
+      case P_C1W: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW1 + i); break;
+      case P_C1B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW1 + W1N + i); break;
+    }
+    g[r] = s;
+  }
+
+  const P2PArgs& cm = a.comm;
+  unsigned int parity = 0;
+  if (cm.world > 1) {
+    // one-shot push of this CTA's gradient elements into every peer's receive slot, then a per-CTA flag exchange
+    const int me = cm.rank;
+    parity = (flags_of(cm, me)->tick[0][blockIdx.x] + 1) & 1u;
+    for (int p = 0; p < cm.world; ++p) {
+      if (p == me) continue;
+      float* dst = reinterpret_cast<float*>(cm.base[p] + cm.recv_off + ((long long)parity * cm.world + me) * cm.recv_slot_bytes);
+#pragma unroll
+      for (int r = 0; r < kMaxPerThread; ++r) {
+        const long long e = e0 + (long long)r * kThreads + tid;
+        if (r < per_thread && e < a.numel) dst[e] = g[r];
+      }
+    }
+    cta_exchange(cm, me, 0, blockIdx.x);
+  }
+#pragma unroll
+  for (int r = 0; r < kMaxPerThread; ++r) {
+    if (r >= per_thread) continue;
+    const long long e = e0 + (long long)r * kThreads + tid;
+    if (e >= a.numel) continue;
+    float gs = g[r];
+    if (cm.world > 1) {
+      gs = 0.f;
+      const char* recv = cm.base[cm.rank] + cm.recv_off + (long long)parity * cm.world * cm.recv_slot_bytes;
+      for (int p = 0; p < cm.world; ++p)        // fixed rank order: every replica computes identical bits
+        gs += (p == cm.rank) ? g[r] : __ldcg(reinterpret_cast<const float*>(recv + p * cm.recv_slot_bytes) + e);
+    }
+    float pv = a.master[e], s1 = a.s1[e], s2 = 0.f;
+    if (R::kStates > 1) s2 = a.s2[e];
+    R::apply(pv, gs * h.grad_scale, s1, s2, h);
+    a.master[e] = pv;
+    a.s1[e] = s1;
+    if (R::kStates > 1) a.s2[e] = s2;
+  }
+}
 
 template <typename R>
 __global__ void __launch_bounds__(lenet::kThreads, 1)
@@ -446,103 +552,401 @@ lenet_step_kernel(const LeNetArgs a) {
   // =========================================== barrier ===========================================
   grid_barrier(a.sync, gridDim.x, s_sense);
 
-  // =========================================== phase B ===========================================
-  if (blockIdx.x == 0 && warp == 0) {            // batch loss / accuracy -> device accumulators
-    float l = 0.f, c = 0.f;
-    for (int b = lane; b < a.B; b += 32) {
-      l += __ldcg(a.scratch + (size_t)b * S_STRIDE + S_DL + 10);
-      c += __ldcg(a.scratch + (size_t)b * S_STRIDE + S_DL + 11);
+  lenet_phase_b<R>(a, inv_B);
+}
+
+// =====================================================================================================
+// Cluster variant of phase A: a sample is carried by a cluster of 4 CTAs (4 SMs) instead of one.  Every stage's
+// outputs are split four ways; each CTA writes its share into the shared memory of all four (distributed shared
+// memory), then the cluster synchronises.  Stages whose work is tiny (fc3, loss, d2, d1) run redundantly in every CTA.
+// With 32 samples and 148 SMs this puts 128 SMs to work in phase A instead of 32.
+// =====================================================================================================
+namespace lenet {
+constexpr int CS = 4;                       // CTAs per sample
+}
+
+template <typename R>
+__global__ void __launch_bounds__(lenet::kThreads, 1)
+lenet_step_cluster_kernel(const LeNetArgs a) {
+  using namespace lenet;
+  namespace cg = cooperative_groups;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int cr = (int)cluster.block_rank();
+  extern __shared__ __align__(16) float sm[];
+  float* xs = sm;                       // 3072
+  float* w1s = xs + XN;                 // 456
+  float* a1s = w1s + 456;               // 1176
+  float* w2s = a1s + A1N;               // 2416
+  float* a2s = w2s + 2416;              // 400
+  float* z1s = a2s + FLAT;              // 120
+  float* z2s = z1s + F1;                // 88
+  float* lgs = z2s + 88;                // 16
+  float* dls = lgs + 16;                // 16
+  float* d2s = dls + 16;                // 88
+  float* d1s = d2s + 88;                // 120
+  float* g2p = d1s + F1;                // 400
+  float* g1p = g2p + FLAT;              // 1176
+  float* dz2 = g1p + A1N;               // 6400: haloed plane (5184) / reduction scratch
+  float* dgp = dz2 + 6400;              // 4 x 1176: this CTA's per-output-channel dgrad partials
+  float* g2x = dgp + 4 * A1N;           // 4 x 400 : fc1-backward partials of the 4 CTAs
+  float* g1x = g2x + CS * FLAT;         // 4 x 1176: conv2-dgrad partials of the 4 CTAs
+  float* w1x = g1x + CS * A1N;          // 4 x 128 : conv1 wgrad position-split partials
+  int* offs1 = reinterpret_cast<int*>(w1x + 4 * 128);        // 1176
+  int* offs2 = offs1 + A1N;                                  // 400
+  float* rsm[CS];
+#pragma unroll
+  for (int r = 0; r < CS; ++r) rsm[r] = cluster.map_shared_rank(sm, r);
+  auto bcast_f = [&](float* local, float v) {
+    const int off = (int)(local - sm);
+#pragma unroll
+    for (int r = 0; r < CS; ++r) rsm[r][off] = v;
+  };
+  auto bcast_i = [&](int* local, int v) {
+    const int off = (int)(reinterpret_cast<float*>(local) - sm);
+#pragma unroll
+    for (int r = 0; r < CS; ++r) reinterpret_cast<int*>(rsm[r])[off] = v;
+  };
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ unsigned int s_sense;
+  if (tid == 0) s_sense = ld_acquire_gpu(&a.sync[1]);
+
+  const float* Wc1 = a.master + a.off[P_C1W];
+  const float* Bc1 = a.master + a.off[P_C1B];
+  const float* Wc2 = a.master + a.off[P_C2W];
+  const float* Bc2 = a.master + a.off[P_C2B];
+  const float* Wf1 = a.master + a.off[P_F1W];
+  const float* Bf1 = a.master + a.off[P_F1B];
+  const float* Wf2 = a.master + a.off[P_F2W];
+  const float* Bf2 = a.master + a.off[P_F2B];
+  const float* Wf3 = a.master + a.off[P_F3W];
+  const float* Bf3 = a.master + a.off[P_F3B];
+
+  const int cluster_id = blockIdx.x / CS, nclusters = gridDim.x / CS;
+  if (cluster_id < a.B) {
+    for (int i = tid; i < W1N; i += kThreads) w1s[i] = Wc1[i];
+    if (tid < C1) w1s[W1N + tid] = Bc1[tid];
+    for (int i = tid; i < W2N; i += kThreads) w2s[i] = Wc2[i];
+    if (tid < C2) w2s[W2N + tid] = Bc2[tid];
+  }
+  const float inv_B = 1.0f / (float)a.B;
+  auto share = [&](int n, int& lo, int& hi) { const int per = (n + CS - 1) / CS; lo = min(n, cr * per); hi = min(n, lo + per); };
+
+  for (int b = cluster_id; b < a.B; b += nclusters) {
+    float* slab = a.scratch + (size_t)b * S_STRIDE;
+    cluster.sync();                    // previous sample fully consumed everywhere before anything is overwritten
+    {
+      const float4* src = reinterpret_cast<const float4*>(a.x + (size_t)b * XN);
+      float4* dst = reinterpret_cast<float4*>(xs);
+      for (int i = tid; i < XN / 4; i += kThreads) dst[i] = src[i];
     }
-    l = warp_sum(l);
-    c = warp_sum(c);
-    if (lane == 0) {
-      const float loss = l * inv_B;
-      if (a.loss_out) *a.loss_out = loss;
-      if (a.acc3) {
-        a.acc3[0] += loss;
-        if (a.want_acc) a.acc3[1] += c * inv_B;
-        a.acc3[2] += 1.0f;
+    __syncthreads();
+    int lo, hi;
+    // ---- conv1 + ReLU + pool: my quarter of the 1176 outputs, broadcast to the cluster
+    share(A1N, lo, hi);
+    for (int o = lo + tid; o < hi; o += kThreads) {
+      const int co = o / (P1 * P1), r = o - co * (P1 * P1), ph = r / P1, pw = r - ph * P1;
+      const float bv = w1s[W1N + co];
+      float a00 = bv, a01 = bv, a10 = bv, a11 = bv;
+#pragma unroll
+      for (int ci = 0; ci < CIN; ++ci) {
+        const float* xc = xs + ci * H * H + (2 * ph) * H + 2 * pw;
+        const float* wk = w1s + (co * CIN + ci) * K * K;
+#pragma unroll
+        for (int kh = 0; kh < K; ++kh) {
+          const float* r0 = xc + kh * H;
+          const float* r1 = r0 + H;
+          float p0 = r0[0], p1 = r1[0];
+#pragma unroll
+          for (int kw = 0; kw < K; ++kw) {
+            const float wv = wk[kh * K + kw];
+            const float q0 = r0[kw + 1], q1 = r1[kw + 1];
+            a00 = fmaf(wv, p0, a00); a01 = fmaf(wv, q0, a01);
+            a10 = fmaf(wv, p1, a10); a11 = fmaf(wv, q1, a11);
+            p0 = q0; p1 = q1;
+          }
+        }
+      }
+      float m = a00; int am = 0;
+      if (a01 > m) { m = a01; am = 1; }
+      if (a10 > m) { m = a10; am = 2; }
+      if (a11 > m) { m = a11; am = 3; }
+      bcast_f(a1s + o, fmaxf(m, 0.f));
+      bcast_i(offs1 + o, (2 * ph + (am >> 1)) * H + 2 * pw + (am & 1));
+    }
+    cluster.sync();
+    // ---- conv2 + ReLU + pool: my 100 of the 400 outputs
+    share(FLAT, lo, hi);
+    for (int o = lo + tid; o < hi; o += kThreads) {
+      const int co = o / (P2 * P2), r = o - co * (P2 * P2), ph = r / P2, pw = r - ph * P2;
+      const float bv = w2s[W2N + co];
+      float a00 = bv, a01 = bv, a10 = bv, a11 = bv;
+      for (int ci = 0; ci < C1; ++ci) {
+        const float* xc = a1s + ci * P1 * P1 + (2 * ph) * P1 + 2 * pw;
+        const float* wk = w2s + (co * C1 + ci) * K * K;
+#pragma unroll
+        for (int kh = 0; kh < K; ++kh) {
+          const float* r0 = xc + kh * P1;
+          const float* r1 = r0 + P1;
+          float p0 = r0[0], p1 = r1[0];
+#pragma unroll
+          for (int kw = 0; kw < K; ++kw) {
+            const float wv = wk[kh * K + kw];
+            const float q0 = r0[kw + 1], q1 = r1[kw + 1];
+            a00 = fmaf(wv, p0, a00); a01 = fmaf(wv, q0, a01);
+            a10 = fmaf(wv, p1, a10); a11 = fmaf(wv, q1, a11);
+            p0 = q0; p1 = q1;
+          }
+        }
+      }
+      float m = a00; int am = 0;
+      if (a01 > m) { m = a01; am = 1; }
+      if (a10 > m) { m = a10; am = 2; }
+      if (a11 > m) { m = a11; am = 3; }
+      m = fmaxf(m, 0.f);
+      bcast_f(a2s + o, m);
+      bcast_i(offs2 + o, (2 * ph + (am >> 1)) * P1 + 2 * pw + (am & 1));
+      slab[S_A2 + o] = m;
+    }
+    cluster.sync();
+    // ---- fc1 + ReLU: my 30 neurons, one warp each
+    share(F1, lo, hi);
+    {
+      const float4* xv = reinterpret_cast<const float4*>(a2s);
+      const int n = lo + warp;
+      if (n < hi) {
+        const float4* wr = reinterpret_cast<const float4*>(Wf1 + (size_t)n * FLAT);
+        float acc = 0.f;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int c4 = lane + 32 * c;
+          if (c4 < FLAT / 4) acc += dot4(wr[c4], xv[c4]);
+        }
+        acc = warp_sum(acc);
+        if (lane == 0) {
+          const float v = fmaxf(acc + Bf1[n], 0.f);
+          bcast_f(z1s + n, v);
+          slab[S_Z1 + n] = v;
+        }
       }
     }
-  }
-  if (!a.train) return;
-
-  const Hyper h = *a.hyper;
-  const int per_cta = (int)ceil_div64(a.numel, (long long)gridDim.x * kThreads) * kThreads;   // elements owned by a CTA
-  const long long e0 = (long long)blockIdx.x * per_cta;
-  const int per_thread = per_cta / kThreads;
-  float g[kMaxPerThread];
-  const int B = a.B;
-#pragma unroll
-  for (int r = 0; r < kMaxPerThread; ++r) {
-    g[r] = 0.f;
-    if (r >= per_thread) continue;
-    const long long e = e0 + (long long)r * kThreads + tid;
-    if (e >= a.numel) continue;
-    // which parameter does arena element e belong to?
-    int pid = -1; int i = 0;
-#pragma unroll
-    for (int p = 0; p < NPARAM; ++p) {
-      const long long d = e - a.off[p];
-      if (d >= 0 && d < kParamSize[p]) { pid = p; i = (int)d; }
-    }
-    if (pid < 0) continue;                        // alignment padding between parameters
-    const float* sc = a.scratch;
-    float s = 0.f;
-    switch (pid) {
-      case P_F1W: { const int n = i / FLAT, k = i - n * FLAT;
-        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_D1 + n), __ldcg(sc + (size_t)b * S_STRIDE + S_A2 + k), s); break; }
-      case P_F2W: { const int n = i / F1, k = i - n * F1;
-        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_D2 + n), __ldcg(sc + (size_t)b * S_STRIDE + S_Z1 + k), s); break; }
-      case P_F3W: { const int n = i / F2, k = i - n * F2;
-        for (int b = 0; b < B; ++b) s = fmaf(__ldcg(sc + (size_t)b * S_STRIDE + S_DL + n), __ldcg(sc + (size_t)b * S_STRIDE + S_Z2 + k), s); break; }
-      case P_F1B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_D1 + i); break;
-      case P_F2B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_D2 + i); break;
-      case P_F3B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_DL + i); break;
-      case P_C2W: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW2 + i); break;
-      case P_C2B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW2 + W2N + i); break;
-      case P_C1W: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW1 + i); break;
-      case P_C1B: for (int b = 0; b < B; ++b) s += __ldcg(sc + (size_t)b * S_STRIDE + S_PW1 + W1N + i); break;
-    }
-    g[r] = s;
-  }
-
-  const P2PArgs& cm = a.comm;
-  unsigned int parity = 0;
-  if (cm.world > 1) {
-    // one-shot push of this CTA's gradient elements into every peer's receive slot, then a per-CTA flag exchange
-    const int me = cm.rank;
-    parity = (flags_of(cm, me)->tick[0][blockIdx.x] + 1) & 1u;
-    for (int p = 0; p < cm.world; ++p) {
-      if (p == me) continue;
-      float* dst = reinterpret_cast<float*>(cm.base[p] + cm.recv_off + ((long long)parity * cm.world + me) * cm.recv_slot_bytes);
-#pragma unroll
-      for (int r = 0; r < kMaxPerThread; ++r) {
-        const long long e = e0 + (long long)r * kThreads + tid;
-        if (r < per_thread && e < a.numel) dst[e] = g[r];
+    cluster.sync();
+    // ---- fc2 + ReLU: my 21 neurons
+    share(F2, lo, hi);
+    {
+      const float4* xv = reinterpret_cast<const float4*>(z1s);
+      const int n = lo + warp;
+      if (n < hi) {
+        float acc = 0.f;
+        if (lane < F1 / 4) acc = dot4(reinterpret_cast<const float4*>(Wf2 + (size_t)n * F1)[lane], xv[lane]);
+        acc = warp_sum(acc);
+        if (lane == 0) {
+          const float v = fmaxf(acc + Bf2[n], 0.f);
+          bcast_f(z2s + n, v);
+          slab[S_Z2 + n] = v;
+        }
       }
     }
-    cta_exchange(cm, me, 0, blockIdx.x);
-  }
-#pragma unroll
-  for (int r = 0; r < kMaxPerThread; ++r) {
-    if (r >= per_thread) continue;
-    const long long e = e0 + (long long)r * kThreads + tid;
-    if (e >= a.numel) continue;
-    float gs = g[r];
-    if (cm.world > 1) {
-      gs = 0.f;
-      const char* recv = cm.base[cm.rank] + cm.recv_off + (long long)parity * cm.world * cm.recv_slot_bytes;
-      for (int p = 0; p < cm.world; ++p)        // fixed rank order: every replica computes identical bits
-        gs += (p == cm.rank) ? g[r] : __ldcg(reinterpret_cast<const float*>(recv + p * cm.recv_slot_bytes) + e);
+    cluster.sync();
+    // ---- fc3, loss, dlogits, d2, d1: tiny, every CTA computes them for itself (no exchange needed)
+    {
+      const float4* xv = reinterpret_cast<const float4*>(z2s);
+      if (warp < NC) {
+        float acc = 0.f;
+        if (lane < F2 / 4) acc = dot4(reinterpret_cast<const float4*>(Wf3 + (size_t)warp * F2)[lane], xv[lane]);
+        acc = warp_sum(acc);
+        if (lane == 0) lgs[warp] = acc + Bf3[warp];
+      }
     }
-    float pv = a.master[e], s1 = a.s1[e], s2 = 0.f;
-    if (R::kStates > 1) s2 = a.s2[e];
-    R::apply(pv, gs * h.grad_scale, s1, s2, h);
-    a.master[e] = pv;
-    a.s1[e] = s1;
-    if (R::kStates > 1) a.s2[e] = s2;
+    __syncthreads();
+    if (warp == 0) {
+      const int tgt = (int)a.y[b];
+      const float v = lane < NC ? lgs[lane] : -INFINITY;
+      float m = v; int am = lane < NC ? lane : 0x7fffffff;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float om = __shfl_xor_sync(0xffffffffu, m, o);
+        const int oa = __shfl_xor_sync(0xffffffffu, am, o);
+        if (om > m || (om == m && oa < am)) { m = om; am = oa; }
+      }
+      const float e = lane < NC ? expf(v - m) : 0.f;
+      const float s = warp_sum(e);
+      if (lane < NC) {
+        float p = e / s;
+        if (lane == tgt) p -= 1.0f;
+        p *= inv_B;
+        dls[lane] = p;
+        if (cr == 0) slab[S_DL + lane] = p;
+      }
+      if (lane == 0 && cr == 0) {
+        const float xt = (tgt >= 0 && tgt < NC) ? lgs[tgt] : (logf(s) + m);
+        slab[S_DL + 10] = logf(s) + m - xt;
+        slab[S_DL + 11] = (am == tgt) ? 1.f : 0.f;
+      }
+    }
+    __syncthreads();
+    if (!a.train) continue;
+    if (tid < F2) {
+      float s = 0.f;
+#pragma unroll
+      for (int n = 0; n < NC; ++n) s = fmaf(dls[n], Wf3[n * F2 + tid], s);
+      s = z2s[tid] > 0.f ? s : 0.f;
+      d2s[tid] = s;
+      if (cr == 0) slab[S_D2 + tid] = s;
+    }
+    __syncthreads();
+    if (tid < 8 * F1) {
+      const int k = tid % F1, part = tid / F1;
+      float s = 0.f;
+      const int n_hi = min(F2, part * 11 + 11);
+#pragma unroll 11
+      for (int n = part * 11; n < n_hi; ++n) s = fmaf(d2s[n], Wf2[n * F1 + k], s);
+      dz2[tid] = s;
+    }
+    __syncthreads();
+    if (tid < F1) {
+      float s = 0.f;
+#pragma unroll
+      for (int part = 0; part < 8; ++part) s += dz2[part * F1 + tid];
+      s = z1s[tid] > 0.f ? s : 0.f;
+      d1s[tid] = s;
+      if (cr == 0) slab[S_D1 + tid] = s;
+    }
+    __syncthreads();
+    // ---- backward through fc1: my 30 rows of W1, partial sums exchanged across the cluster
+    share(F1, lo, hi);
+    {
+      const int rg = warp & 15, half = warp >> 4;
+      float4 acc[2];
+      acc[0] = acc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int n = lo + rg; n < hi; n += 16) {
+        const float dv = d1s[n];
+        const float4* wr = reinterpret_cast<const float4*>(Wf1 + (size_t)n * FLAT);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          const int c4 = lane + 32 * (2 * half + c);
+          if (c4 < FLAT / 4) {
+            const float4 w = wr[c4];
+            acc[c].x = fmaf(dv, w.x, acc[c].x); acc[c].y = fmaf(dv, w.y, acc[c].y);
+            acc[c].z = fmaf(dv, w.z, acc[c].z); acc[c].w = fmaf(dv, w.w, acc[c].w);
+          }
+        }
+      }
+      float4* part = reinterpret_cast<float4*>(dz2) + rg * (FLAT / 4);
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const int c4 = lane + 32 * (2 * half + c);
+        if (c4 < FLAT / 4) part[c4] = acc[c];
+      }
+    }
+    __syncthreads();
+    for (int k = tid; k < FLAT; k += kThreads) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < 16; ++w) s += dz2[w * FLAT + k];
+      bcast_f(g2x + cr * FLAT + k, s);
+    }
+    cluster.sync();
+    for (int k = tid; k < FLAT; k += kThreads) {
+      const float s = g2x[k] + g2x[FLAT + k] + g2x[2 * FLAT + k] + g2x[3 * FLAT + k];
+      g2p[k] = a2s[k] > 0.f ? s : 0.f;
+    }
+    for (int i = tid; i < C2 * ZH * ZH; i += kThreads) dz2[i] = 0.f;
+    __syncthreads();
+    // ---- conv2 weight / bias gradient partials: my 604 of the 2416 slots
+    share(W2N + C2, lo, hi);
+    for (int t = lo + tid; t < hi; t += kThreads) {
+      float s = 0.f;
+      if (t < W2N) {
+        const int co = t / (C1 * K * K), r = t - co * (C1 * K * K), ci = r / (K * K), q = r - ci * (K * K);
+        const float* xt = a1s + ci * P1 * P1 + (q / K) * P1 + (q % K);
+        const float* g = g2p + co * (P2 * P2);
+        const int* of = offs2 + co * (P2 * P2);
+#pragma unroll
+        for (int p = 0; p < P2 * P2; ++p) s = fmaf(g[p], xt[of[p]], s);
+      } else {
+        const float* g = g2p + (t - W2N) * (P2 * P2);
+#pragma unroll
+        for (int p = 0; p < P2 * P2; ++p) s += g[p];
+      }
+      slab[S_PW2 + t] = s;
+    }
+    for (int o = tid; o < FLAT; o += kThreads) {
+      const int co = o / (P2 * P2);
+      const int pos = offs2[o];
+      const int oh = pos / P1, ow = pos - oh * P1;
+      dz2[co * ZH * ZH + (oh + K - 1) * ZH + (ow + K - 1)] = g2p[o];
+    }
+    __syncthreads();
+    // ---- conv2 dgrad: this CTA takes output channels 4*cr .. 4*cr+3, one work item per (co, ci, row, 7-column strip)
+    for (int it = tid; it < 4 * C1 * P1 * 2; it += kThreads) {
+      const int cl = it / (C1 * P1 * 2), r = it - cl * (C1 * P1 * 2);
+      const int ci = r / (P1 * 2), r2 = r - ci * (P1 * 2), h = r2 >> 1, w0 = (r2 & 1) * 7;
+      const int co = cr * 4 + cl;
+      float acc[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      const float* wk = w2s + (co * C1 + ci) * K * K;
+#pragma unroll
+      for (int kh = 0; kh < K; ++kh) {
+        const float* row = dz2 + co * ZH * ZH + (h - kh + K - 1) * ZH + w0;
+        float d[11];
+#pragma unroll
+        for (int j = 0; j < 11; ++j) d[j] = row[j];
+#pragma unroll
+        for (int kw = 0; kw < K; ++kw) {
+          const float wv = wk[kh * K + kw];
+#pragma unroll
+          for (int j = 0; j < 7; ++j) acc[j] = fmaf(d[j + (K - 1) - kw], wv, acc[j]);
+        }
+      }
+      float* dst = dgp + cl * A1N + ci * P1 * P1 + h * P1 + w0;
+#pragma unroll
+      for (int j = 0; j < 7; ++j) dst[j] = acc[j];
+    }
+    __syncthreads();
+    for (int o = tid; o < A1N; o += kThreads)
+      bcast_f(g1x + cr * A1N + o, dgp[o] + dgp[A1N + o] + dgp[2 * A1N + o] + dgp[3 * A1N + o]);
+    cluster.sync();
+    for (int o = tid; o < A1N; o += kThreads) {
+      const float s = g1x[o] + g1x[A1N + o] + g1x[2 * A1N + o] + g1x[3 * A1N + o];
+      g1p[o] = a1s[o] > 0.f ? s : 0.f;
+    }
+    __syncthreads();
+    // ---- conv1 weight / bias gradient partials: my 114 of the 456 slots, the 196 positions split 4 ways
+    share(W1N + C1, lo, hi);
+    {
+      const int nslot = hi - lo;
+      for (int it = tid; it < nslot * 4; it += kThreads) {
+        const int sl = it >> 2, part = it & 3, t = lo + sl;
+        const int p_lo = part * 49, p_hi = p_lo + 49;
+        float s = 0.f;
+        if (t < W1N) {
+          const int co = t / (CIN * K * K), r = t - co * (CIN * K * K), ci = r / (K * K), q = r - ci * (K * K);
+          const float* xt = xs + ci * H * H + (q / K) * H + (q % K);
+          const float* g = g1p + co * (P1 * P1);
+          const int* of = offs1 + co * (P1 * P1);
+#pragma unroll 7
+          for (int p = p_lo; p < p_hi; ++p) s = fmaf(g[p], xt[of[p]], s);
+        } else {
+          const float* g = g1p + (t - W1N) * (P1 * P1);
+          for (int p = p_lo; p < p_hi; ++p) s += g[p];
+        }
+        w1x[part * 128 + sl] = s;
+      }
+      __syncthreads();
+      for (int sl = tid; sl < nslot; sl += kThreads)
+        slab[S_PW1 + lo + sl] = w1x[sl] + w1x[128 + sl] + w1x[256 + sl] + w1x[384 + sl];
+    }
   }
+  cluster.sync();        // nobody leaves while a sibling may still write into its shared memory
+
+  grid_barrier(a.sync, gridDim.x, s_sense);
+  lenet_phase_b<R>(a, inv_B);
+}
+
+namespace lenet {
+constexpr size_t kClusterSmemBytes =
+    (size_t)(XN + 456 + A1N + 2416 + FLAT + F1 + 88 + 16 + 16 + 88 + F1 + FLAT + A1N + 6400 + 4 * A1N + CS * FLAT + CS * A1N + 4 * 128) * 4 +
+    (size_t)(A1N + FLAT) * 4 + 64;
 }
 
 namespace lenet {
@@ -585,7 +989,47 @@ extern "C" int mlt_lenet_step(void* master, void* s1, void* s2, const void* hype
   int dev = 0;
   MLT_CHECK_CUDA(cudaGetDevice(&dev));
   int rc = 0;
+  static const bool use_cluster = []{ const char* e = getenv("MLT_LENET_CLUSTER"); return !(e && e[0] == '0'); }();
   MLT_DISPATCH_RULE(rule, R, {
+    if (use_cluster) {
+      auto kern = lenet_step_cluster_kernel<R>;
+      static int grid_cl[64] = {};
+      cudaLaunchConfig_t cfg{};
+      cfg.blockDim = dim3(kThreads);
+      cfg.dynamicSmemBytes = kClusterSmemBytes;
+      cfg.stream = st;
+      cudaLaunchAttribute attrs[2];
+      attrs[0].id = cudaLaunchAttributeClusterDimension;
+      attrs[0].val.clusterDim.x = CS; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+      attrs[1].id = cudaLaunchAttributeCooperative;
+      attrs[1].val.cooperative = 1;
+      cfg.attrs = attrs;
+      if (grid_cl[dev & 63] == 0) {
+        MLT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kClusterSmemBytes));
+        int sms = 0, nclus = 0;
+        MLT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        cfg.gridDim = dim3((sms / CS) * CS);
+        cfg.numAttrs = 1;
+        MLT_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclus, kern, &cfg));
+        MLT_REQUIRE(nclus >= 1, "mlt_lenet_step: no 4-CTA cluster fits on this device");
+        grid_cl[dev & 63] = nclus * CS;
+      }
+      const int grid = grid_cl[dev & 63];
+      const long long min_grid = ceil_div64(numel, (long long)kThreads * kMaxPerThread);
+      MLT_REQUIRE(grid >= min_grid && grid <= kMaxCtas - 1, "mlt_lenet_step: grid %d cannot cover %lld parameters", grid, numel);
+      cfg.gridDim = dim3(grid);
+      static bool coop_ok = true;                     // cooperative + cluster launch; fall back to a plain cluster launch
+      cfg.numAttrs = coop_ok ? 2 : 1;                 // (all CTAs are co-resident by construction: grid <= active clusters)
+      cudaError_t le = cudaLaunchKernelEx(&cfg, kern, a);
+      if (le != cudaSuccess && coop_ok) {
+        (void)cudaGetLastError();
+        coop_ok = false;
+        cfg.numAttrs = 1;
+        le = cudaLaunchKernelEx(&cfg, kern, a);
+      }
+      MLT_CHECK_CUDA(le);
+      return 0;
+    }
     auto kern = lenet_step_kernel<R>;
     static int grid_cache[64] = {};
     if (grid_cache[dev & 63] == 0) {

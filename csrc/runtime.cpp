@@ -59,6 +59,8 @@ struct Loop {
   long long hyper_cap = 0;
   float* pin_loss = nullptr;            // [max_steps]
   long long loss_cap = 0;
+  float* dev_hyper = nullptr;           // [max_steps][8] device copy of the whole epoch's hyper rows (kernel steps)
+  long long dev_hyper_cap = 0;
   // statistics of the last run
   long long h2d_bytes = 0, d2h_bytes = 0, launches = 0;
   // Large samples (images): skip the host gather of x and let the copy engine gather instead - one cudaMemcpyAsync per
@@ -123,6 +125,7 @@ extern "C" int mlt_loop_destroy(void* loop) {
   }
   if (L->pin_hyper) cudaFreeHost(L->pin_hyper);
   if (L->pin_loss) cudaFreeHost(L->pin_loss);
+  if (L->dev_hyper) cudaFree(L->dev_hyper);
   cudaStreamDestroy(L->copy);
   delete L;
   return 0;
@@ -157,6 +160,18 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
     L->loss_cap = steps;
   }
   L->h2d_bytes = L->d2h_bytes = L->launches = 0;
+  // Single-kernel steps read their hyper-parameter row straight from a device table uploaded once per run, and write
+  // their loss straight into the pinned host array (a posted store over PCIe): no per-step copy operations at all.
+  const bool table_mode = step_kind == 0;
+  if (table_mode && hyper_rows) {
+    if (steps > L->dev_hyper_cap) {
+      if (L->dev_hyper) cudaFree(L->dev_hyper);
+      RT_CHECK(cudaMalloc((void**)&L->dev_hyper, (size_t)steps * 8 * sizeof(float)));
+      L->dev_hyper_cap = steps;
+    }
+    RT_CHECK(cudaMemcpyAsync(L->dev_hyper, L->pin_hyper, (size_t)steps * 8 * sizeof(float), cudaMemcpyHostToDevice, cs));
+    L->h2d_bytes += steps * 32;
+  }
 
   // ---- gather thread: fills pinned slots ahead of the launcher ---------------------------------------
   const int S = L->slots;
@@ -212,20 +227,23 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
     if ((rc = (int)cudaEventRecord(sl.ready, L->copy)) != 0) break;
     L->h2d_bytes += n * (long long)(L->x_row + L->y_row);
     if ((rc = (int)cudaStreamWaitEvent(cs, sl.ready, 0)) != 0) break;
-    if (hyper_rows) {
+    if (hyper_rows && !table_mode) {
       if ((rc = (int)cudaMemcpyAsync(hyper_dev, L->pin_hyper + i * 8, 8 * sizeof(float), cudaMemcpyHostToDevice, cs)) != 0) break;
       L->h2d_bytes += 32;
     }
     if (step_kind == 0) {
-      rc = mlt_lenet_step(lenet->master, lenet->s1, lenet->s2, lenet->hyper, lenet->numel, lenet->param_off, lenet->rule,
-                          sl.dev_x, sl.dev_y, (int)n, lenet->train, lenet->want_acc, lenet->acc3, lenet->loss_out,
+      const void* hy = hyper_rows ? (const void*)(L->dev_hyper + i * 8) : lenet->hyper;
+      void* lo = loss_dev ? (void*)(L->pin_loss + i) : lenet->loss_out;      // pinned host memory is device-addressable (UVA)
+      rc = mlt_lenet_step(lenet->master, lenet->s1, lenet->s2, hy, lenet->numel, lenet->param_off, lenet->rule,
+                          sl.dev_x, sl.dev_y, (int)n, lenet->train, lenet->want_acc, lenet->acc3, lo,
                           lenet->scratch, lenet->scratch_bytes, lenet->ctx, cs);
       if (rc != 0) break;
+      if (loss_dev) L->d2h_bytes += 4;
     } else {
       if ((rc = (int)cudaGraphLaunch((cudaGraphExec_t)graph_execs[s], cs)) != 0) break;
     }
     L->launches += 1;
-    if (loss_dev) {
+    if (loss_dev && !table_mode) {
       if ((rc = (int)cudaMemcpyAsync(L->pin_loss + i, loss_dev, sizeof(float), cudaMemcpyDeviceToHost, cs)) != 0) break;
       L->d2h_bytes += 4;
     }
