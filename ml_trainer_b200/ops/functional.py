@@ -468,11 +468,31 @@ class _AttentionFn(torch.autograd.Function):
         return dq, dk, dv, None
 
 
+def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False):
+    """Fused tcgen05 attention forward (csrc/attention_tcgen05.cu).  Returns ``out`` or ``(out, lse)``."""
+    B, S, HD = q.shape
+    q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+    out = torch.empty_like(q)
+    lse = torch.empty((B, heads, S), dtype=torch.float32, device=q.device) if want_lse else None
+    check(_lib.lib().mlt_attention_fwd(ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), _c_int(B), _c_int(S), _c_int(heads),
+                                       _c_int(HD // heads), stream_handle()), "mlt_attention_fwd")
+    launches.bump("attention_fwd_tcgen05")
+    return (out, lse) if want_lse else out
+
+
+def fused_attention_ok(q, heads: int) -> bool:
+    B, S, HD = q.shape
+    return HD // heads == 64 and S % 128 == 0 and 128 <= S <= 512
+
+
 def attention(q, k, v, heads: int):
     """Multi-head self-attention core (no mask, no dropout).  q, k, v: [B, S, heads*d]."""
     B, S, HD = q.shape
     d = HD // heads
     if use_native(q, k, v) and q.dtype == torch.bfloat16 and d % 8 == 0 and S % 8 == 0 and S <= 1024:
+        needs_grad = torch.is_grad_enabled() and (q.requires_grad or k.requires_grad or v.requires_grad)
+        if not needs_grad and fused_attention_ok(q, heads):
+            return attention_fused_fwd(q, k, v, heads)
         return _AttentionFn.apply(q, k, v, heads)
     qh, kh, vh = (t.view(B, S, heads, d).transpose(1, 2) for t in (q, k, v))
     o = TF.scaled_dot_product_attention(qh.float(), kh.float(), vh.float())

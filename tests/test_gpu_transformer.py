@@ -161,3 +161,21 @@ def test_native_graph_executor_matches_python_loop(tmp_path):
     for p, q in zip(a.model.parameters(), b.model.parameters()):
         assert torch.allclose(p.float(), q.float(), rtol=2e-2, atol=1e-3 * 28 * 2)
     assert a.last_native_stats["h2d_bytes"] > 0
+
+
+@pytest.mark.parametrize("B,S,heads", [(1, 128, 1), (2, 256, 3), (2, 512, 12), (3, 384, 2)])
+def test_fused_attention_forward(B, S, heads):
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(0)
+    d = 64
+    q, k, v = ((torch.randn(B, S, heads * d, device=DEV) * 0.7).to(torch.bfloat16) for _ in range(3))
+    out, lse = F.attention_fused_fwd(q, k, v, heads, want_lse=True)
+    torch.cuda.synchronize()
+    sp = lambda t: t.float().view(B, S, heads, d).transpose(1, 2)
+    ref = TF.scaled_dot_product_attention(sp(q), sp(k), sp(v)).transpose(1, 2).reshape(B, S, heads * d)
+    _close(out, ref, 2e-2, "fused attention out")
+    ref_lse = torch.logsumexp(sp(q) @ sp(k).transpose(-1, -2) / d ** 0.5, dim=-1)
+    _close(lse, ref_lse, 2e-3, "lse")
+    with torch.no_grad():
+        _close(F.attention(q, k, v, heads), ref, 2e-2, "dispatch under no_grad")
