@@ -1,16 +1,22 @@
-// Fused multi-head attention forward on tcgen05: softmax(Q K^T / sqrt(d)) V without the [S, S] score
-// matrix ever touching HBM.  Head dim 64, sequence length a multiple of 128 up to 512 (BERT-base: 512), no mask.
+// Fused multi-head attention on tcgen05: softmax(Q K^T / sqrt(d)) V and its backward without the [S, S]
+// score matrix ever touching HBM.  Head dim 64, sequence length a multiple of 128 up to 512 (BERT-base: 512), no mask.
 //
-// One CTA per (128-query tile, head, sample); 192 threads:
-//   warp 0     TMA: the Q tile, then all K and V chunks (128 keys each) of this head, every chunk on its own mbarrier.
-//   warp 1     MMA: S_j = Q K_j^T (M=128, N=128, K=64) into one of two TMEM score buffers, and O += P_j V_j
-//              (M=128, N=64, K=128; V is the MN-major B operand straight from its [key][d] layout).  S_{j+1} is issued
-//              before P_j is needed, so tensor cores and the softmax warps overlap.
-//   warps 2-5  online softmax, one query row per thread: tcgen05.ld the scores, running max / sum in registers,
-//              rescale the O accumulator in TMEM (tcgen05.ld/st) when the max moves, write P_j as bf16 into 128-byte
-//              swizzled shared memory (the A operand of the PV MMA).  At the end O / l goes out as bf16 and the
-//              log-sum-exp per row is kept for backward.
-// TMEM: columns [0,128) and [128,256) score buffers, [256,320) the O accumulator (512 allocated, one CTA per SM).
+// All three kernels share one shape: a CTA owns a 128-row tile (queries, or keys in the dK/dV kernel), walks the other
+// sequence axis in steps of 64 columns, and runs 320 threads, two CTAs per SM:
+//   warp 0      TMA producer: the resident tile(s) once, the streamed 64-row operand tiles through a 2-3 stage ring.
+//   warp 1      MMA issuer (one elected thread): score MMAs (M=128, N=64, K=64) into TMEM, then the accumulating
+//               output MMAs whose A operand is the bf16 tile the softmax warps wrote into 128-byte swizzled smem.
+//   warps 2-9   softmax: TMEM lane quadrant = warp % 4, column half = (warp - 2) / 4, so a thread owns 32 columns of one
+//               row per step.  tcgen05.ld the scores, exponentiate, write bf16 to smem, arrive on an mbarrier.
+// Two CTAs per SM (<= 113 KB smem, 256 TMEM columns each) keep two such dependency chains in flight per scheduler,
+// which is what hides the MMA -> commit -> tcgen05.ld latency of a single chain.
+//
+// forward   S_j = Q K_j^T (two TMEM score buffers), online softmax with a lazy rescale of the O accumulator in TMEM
+//           (only when the running max moved by more than 2^8), O += P_j V_j (V is the MN-major B operand), out = O / l,
+//           lse kept for backward.
+// backward  delta = rowsum(dO * O) (tiny kernel);  dQ kernel: dP = dO V^T, dS = P (dP - delta) scale, dQ += dS K;
+//           dK/dV kernel in the transposed orientation (rows are keys): S^T = K Q^T, dP^T = V dO^T, dV += P^T dO,
+//           dK += dS^T Q.  Each output tile is owned by exactly one CTA: no atomics, no cross-CTA reduction.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "../include/mlt_b200.h"
@@ -21,15 +27,23 @@ namespace mlt {
 using namespace ptx;
 
 namespace fa {
-constexpr int BQ = 128, BKEY = 128, D = 64;
-constexpr int kThreads = 192;
-constexpr int kQBytes = BQ * D * 2;            // 16 KB
-constexpr int kChunkBytes = BKEY * D * 2;      // 16 KB per K or V chunk
-constexpr int kPBytes = BQ * BKEY * 2;         // 32 KB: two [128 x 64] K-major sub-tiles
-constexpr int kMaxChunks = 4;                  // S <= 512
-constexpr int kSmemBytes = kQBytes + 2 * kMaxChunks * kChunkBytes + kPBytes + 1024 + 256;
-constexpr uint32_t kTmemCols = 512;
-constexpr uint32_t kColS = 0, kColO = 256;
+constexpr int kThreads = 320;
+constexpr int kSoftmaxThreads = 256;
+constexpr int kSoftmaxWarps = 8;              // barrier arrivals are one elected lane per warp
+constexpr int kTile = 128 * 64 * 2;            // 16 KB: a [128 x 64] bf16 tile, 128-byte rows, SW128
+constexpr int kHalf = 64 * 64 * 2;             // 8 KB: 64 rows of it
+constexpr int kMaxS = 512;
+constexpr uint32_t kTmemCols = 256;
+constexpr float kLog2e = 1.4426950408889634f;
+// forward: Q | 3 x (K half, V half) | 2 x P | row-max exchange | barriers
+constexpr int kFwdStages = 3;
+constexpr int kSmemFwd = kTile + kFwdStages * 2 * kHalf + 2 * kTile + 2 * 2 * 128 * 4 + 256 + 1024;
+// dQ: Q | dO | 3 x (K half, V half) | dS | barriers
+constexpr int kDqStages = 3;
+constexpr int kSmemDq = 2 * kTile + kDqStages * 2 * kHalf + kTile + 256 + 1024;
+// dK/dV: K | V | 2 x (Q half, dO half) | P | dS | lse, delta | barriers
+constexpr int kDkvStages = 2;
+constexpr int kSmemDkv = 2 * kTile + kDkvStages * 2 * kHalf + 2 * kTile + 2 * kMaxS * 4 + 256 + 1024;
 }  // namespace fa
 
 struct FaParams {
@@ -41,45 +55,93 @@ struct FaParams {
   float scale;
 };
 
-__global__ void __launch_bounds__(fa::kThreads, 1)
+struct FaBwdParams {
+  const __nv_bfloat16* out;   // forward output  [B, S, H*64]
+  const __nv_bfloat16* dout;  // its gradient
+  const float* lse;           // [B, H, S]
+  float* delta;               // [B, H, S]
+  __nv_bfloat16 *dq, *dk, *dv;
+  int B, S, H;
+  long long row_stride;
+  float scale_log2, scale;
+};
+
+__device__ __forceinline__ void softmax_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// All lanes of the warp have done their part (TMEM reads retired, or smem writes + proxy fence): one lane arrives.
+__device__ __forceinline__ void warp_arrive(uint64_t* bar, int lane) {
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar);
+}
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// 8 consecutive bf16 of row `row` of a K-major SW128 tile: 16-byte chunk index XOR (row & 7).
+__device__ __forceinline__ void store_row_chunk(uint8_t* tile_row, int row, int chunk, const float* v) {
+  uint4 pk;
+  pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]); pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
+  *reinterpret_cast<uint4*>(tile_row + ((chunk ^ (row & 7)) << 4)) = pk;
+}
+
+// 32 fp32 accumulator columns -> 32 bf16 in global memory, scaled.
+__device__ __forceinline__ void store_out32(__nv_bfloat16* g, uint32_t taddr, float mul) {
+  uint32_t r[32];
+  tmem_ld_32x32b_x32(taddr, r);
+  tmem_ld_wait();
+#pragma unroll
+  for (int i = 0; i < 32; i += 8) {
+    uint4 pk;
+    pk.x = pack_bf16(__uint_as_float(r[i]) * mul, __uint_as_float(r[i + 1]) * mul);
+    pk.y = pack_bf16(__uint_as_float(r[i + 2]) * mul, __uint_as_float(r[i + 3]) * mul);
+    pk.z = pack_bf16(__uint_as_float(r[i + 4]) * mul, __uint_as_float(r[i + 5]) * mul);
+    pk.w = pack_bf16(__uint_as_float(r[i + 6]) * mul, __uint_as_float(r[i + 7]) * mul);
+    *reinterpret_cast<uint4*>(g + i) = pk;
+  }
+}
+
+// ---- forward ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(fa::kThreads, 2)
 attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                              const __grid_constant__ CUtensorMap tmV, const FaParams p) {
   using namespace fa;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sQ = smem;
-  uint8_t* sK = sQ + kQBytes;
-  uint8_t* sV = sK + kMaxChunks * kChunkBytes;
-  uint8_t* sP = sV + kMaxChunks * kChunkBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sP + kPBytes);
-  uint64_t* q_full = bars;                 // 1
-  uint64_t* k_full = bars + 1;             // kMaxChunks
-  uint64_t* v_full = k_full + kMaxChunks;  // kMaxChunks
-  uint64_t* s_full = v_full + kMaxChunks;  // 2
-  uint64_t* s_free = s_full + 2;           // 2
-  uint64_t* p_full = s_free + 2;           // 1
-  uint64_t* p_free = p_full + 1;           // 1
-  uint64_t* o_done = p_free + 1;           // 1
+  uint8_t* sKV = sQ + kTile;                       // stage s: K half at s * 2 * kHalf, V half right after
+  uint8_t* sP = sKV + kFwdStages * 2 * kHalf;      // 2 x [128 q x 64 keys]
+  float* s_max = reinterpret_cast<float*>(sP + 2 * kTile);     // [2 buffers][2 halves][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_max + 2 * 2 * 128);
+  uint64_t* q_full = bars;                         // 1
+  uint64_t* kv_full = bars + 1;                    // kFwdStages
+  uint64_t* kv_free = kv_full + kFwdStages;        // kFwdStages
+  uint64_t* s_full = kv_free + kFwdStages;         // 2
+  uint64_t* s_free = s_full + 2;                   // 2
+  uint64_t* p_full = s_free + 2;                   // 2
+  uint64_t* p_free = p_full + 2;                   // 2
+  uint64_t* o_done = p_free + 2;                   // 1
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_done + 1);
+  constexpr uint32_t kColS = 0, kColO = 128;       // S buffers at 0 and 64, O at 128
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
-  const int NK = p.S / BKEY;
+  const int NH = p.S / 64;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV);
     mbar_init(q_full, 1);
-    for (int j = 0; j < kMaxChunks; ++j) { mbar_init(&k_full[j], 1); mbar_init(&v_full[j], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&s_full[i], 1); mbar_init(&s_free[i], 128); }
-    mbar_init(p_full, 128);
-    mbar_init(p_free, 1);
+    for (int j = 0; j < kFwdStages; ++j) { mbar_init(&kv_full[j], 1); mbar_init(&kv_free[j], 1); }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1); mbar_init(&s_free[i], kSoftmaxWarps);
+      mbar_init(&p_full[i], kSoftmaxWarps); mbar_init(&p_free[i], 1);
+    }
     mbar_init(o_done, 1);
     fence_mbar_init();
   }
-  if (warp == 1) {
-    tmem_alloc(tmem_slot, kTmemCols);
-    tmem_relinquish();
-  }
+  if (warp == 1) { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -87,134 +149,437 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
 
   if (warp == 0) {
     if (lane == 0) {
-      mbar_arrive_expect_tx(q_full, kQBytes);
-      tma_load_4d(sQ, &tmQ, q_full, 0, qt * BQ, h, b);
-      for (int j = 0; j < NK; ++j) {
-        mbar_arrive_expect_tx(&k_full[j], kChunkBytes);
-        tma_load_4d(sK + j * kChunkBytes, &tmK, &k_full[j], 0, j * BKEY, h, b);
-      }
-      for (int j = 0; j < NK; ++j) {
-        mbar_arrive_expect_tx(&v_full[j], kChunkBytes);
-        tma_load_4d(sV + j * kChunkBytes, &tmV, &v_full[j], 0, j * BKEY, h, b);
+      mbar_arrive_expect_tx(q_full, kTile);
+      tma_load_4d(sQ, &tmQ, q_full, 0, qt * 128, h, b);
+      for (int hs = 0; hs < NH; ++hs) {
+        const int st = hs % kFwdStages, n = hs / kFwdStages;
+        mbar_wait(&kv_free[st], (n & 1) ^ 1);
+        mbar_arrive_expect_tx(&kv_full[st], 2 * kHalf);
+        tma_load_4d(sKV + st * 2 * kHalf, &tmK, &kv_full[st], 0, hs * 64, h, b);
+        tma_load_4d(sKV + st * 2 * kHalf + kHalf, &tmV, &kv_full[st], 0, hs * 64, h, b);
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      const uint32_t idesc_s = make_idesc_bf16(BQ, BKEY, 0, 0);      // Q, K both K-major
-      const uint32_t idesc_o = make_idesc_bf16(BQ, D, 0, 1);         // P K-major, V MN-major
-      const uint32_t aQ = smem_u32(sQ), aP = smem_u32(sP);
-      auto issue_pv = [&](int j) {
-        mbar_wait(p_full, j & 1);
-        mbar_wait(&v_full[j], 0);
+      const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);       // Q, K both K-major
+      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);       // P K-major, V MN-major
+      const uint32_t aQ = smem_u32(sQ), aKV = smem_u32(sKV), aP = smem_u32(sP);
+      auto issue_pv = [&](int hs) {
+        const int u = hs & 1, st = hs % kFwdStages;
+        mbar_wait(&p_full[u], (hs >> 1) & 1);
         tc_fence_after();
-        const uint32_t aV = smem_u32(sV + j * kChunkBytes);
+        const uint32_t aV = aKV + st * 2 * kHalf + kHalf;
 #pragma unroll
-        for (int kk = 0; kk < BKEY / 16; ++kk) {
-          const uint64_t ad = make_smem_desc_sw128(aP + (kk >> 2) * (BQ * 128) + (kk & 3) * 32, 16, 1024);
-          const uint64_t bd = make_smem_desc_sw128(aV + kk * 2048, 8192, 1024);
-          umma_f16(tmem + kColO, ad, bd, idesc_o, (j > 0) || (kk > 0));
-        }
-        umma_commit(p_free);                      // P smem reusable, O holds chunk j
+        for (int kk = 0; kk < 4; ++kk)
+          umma_f16(tmem + kColO, make_smem_desc_sw128(aP + u * kTile + kk * 32, 16, 1024),
+                   make_smem_desc_sw128(aV + kk * 2048, 8192, 1024), idesc_o, (hs > 0) || (kk > 0));
+        umma_commit(&p_free[u]);                  // P buffer reusable, O holds step hs
+        umma_commit(&kv_free[st]);
       };
       mbar_wait(q_full, 0);
-      for (int j = 0; j < NK; ++j) {
-        mbar_wait(&k_full[j], 0);
-        mbar_wait(&s_free[j & 1], ((j >> 1) & 1) ^ 1);
+      for (int hs = 0; hs < NH; ++hs) {
+        const int u = hs & 1, st = hs % kFwdStages;
+        mbar_wait(&kv_full[st], (hs / kFwdStages) & 1);
+        mbar_wait(&s_free[u], ((hs >> 1) & 1) ^ 1);
         tc_fence_after();
-        const uint32_t aK = smem_u32(sK + j * kChunkBytes);
+        const uint32_t aK = aKV + st * 2 * kHalf;
 #pragma unroll
-        for (int k = 0; k < D / 16; ++k) {
-          const uint64_t ad = make_smem_desc_sw128(aQ + k * 32, 16, 1024);
-          const uint64_t bd = make_smem_desc_sw128(aK + k * 32, 16, 1024);
-          umma_f16(tmem + kColS + (j & 1) * BKEY, ad, bd, idesc_s, k != 0);
-        }
-        umma_commit(&s_full[j & 1]);
-        if (j > 0) issue_pv(j - 1);
+        for (int k = 0; k < 4; ++k)
+          umma_f16(tmem + kColS + u * 64, make_smem_desc_sw128(aQ + k * 32, 16, 1024),
+                   make_smem_desc_sw128(aK + k * 32, 16, 1024), idesc_s, k != 0);
+        umma_commit(&s_full[u]);
+        if (hs > 0) issue_pv(hs - 1);
       }
-      issue_pv(NK - 1);
+      issue_pv(NH - 1);
       umma_commit(o_done);
     }
   } else {
-    const int q = warp & 3;
-    const int row = q * 32 + lane;                      // query row within the tile
-    const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-    float m = -INFINITY, l = 0.f;
-    for (int j = 0; j < NK; ++j) {
-      mbar_wait(&s_full[j & 1], (j >> 1) & 1);
+    const int quad = warp & 3, hf = (warp - 2) >> 2;
+    const int row = quad * 32 + lane;                   // query row within the tile
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    float m = -INFINITY, l = 0.f;                       // l: this thread's half of the row sum
+    for (int hs = 0; hs < NH; ++hs) {
+      const int u = hs & 1;
+      mbar_wait(&s_full[u], (hs >> 1) & 1);
       tc_fence_after();
-      float s[BKEY];
-#pragma unroll
-      for (int c = 0; c < BKEY / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(tmem + lane_base + kColS + (j & 1) * BKEY + c * 32, r);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) s[c * 32 + i] = __uint_as_float(r[i]);
-      }
+      uint32_t r[32];
+      tmem_ld_32x32b_x32(tmem + lane_base + kColS + u * 64 + hf * 32, r);
+      tmem_ld_wait();
       tc_fence_before();
-      mbar_arrive(&s_free[j & 1]);                      // score buffer may be overwritten by S_{j+2}
-      float mx = m;
+      warp_arrive(&s_free[u], lane);                          // score buffer may be overwritten by S_{hs+2}
+      float mx0 = __uint_as_float(r[0]), mx1 = __uint_as_float(r[1]), mx2 = __uint_as_float(r[2]), mx3 = __uint_as_float(r[3]);
 #pragma unroll
-      for (int i = 0; i < BKEY; ++i) mx = fmaxf(mx, s[i]);
-      const float alpha = exp2f((m - mx) * p.scale_log2);       // m = -inf on the first chunk -> alpha = 0
-      float sum = 0.f;
-#pragma unroll
-      for (int i = 0; i < BKEY; ++i) { s[i] = exp2f((s[i] - mx) * p.scale_log2); sum += s[i]; }
-      l = l * alpha + sum;
-      m = mx;
-      // the PV MMA of the previous chunk must have finished: it reads P from smem and accumulates into O
-      mbar_wait(p_free, (j & 1) ^ 1);
-      tc_fence_after();
-      if (j > 0) {                                      // rescale the running output
-#pragma unroll
-        for (int c = 0; c < D / 32; ++c) {
-          uint32_t r[32];
-          tmem_ld_32x32b_x32(tmem + lane_base + kColO + c * 32, r);
+      for (int i = 4; i < 32; i += 4) {
+        mx0 = fmaxf(mx0, __uint_as_float(r[i])); mx1 = fmaxf(mx1, __uint_as_float(r[i + 1]));
+        mx2 = fmaxf(mx2, __uint_as_float(r[i + 2])); mx3 = fmaxf(mx3, __uint_as_float(r[i + 3]));
+      }
+      const float mine = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      float* xm = s_max + u * 256;
+      xm[hf * 128 + row] = mine;
+      softmax_bar();
+      const float mx = fmaxf(m, fmaxf(mine, xm[(hf ^ 1) * 128 + row]));
+      // lazy rescale: keep the old reference max unless some row of this warp moved by more than 2^8
+      const bool grow = (mx - m) * p.scale_log2 > 8.0f;           // also true on the first step (m = -inf)
+      if (__any_sync(0xffffffffu, grow)) {
+        const float alpha = fast_exp2((m - mx) * p.scale_log2);   // 0 on the first step
+        l *= alpha;
+        m = mx;
+        if (hs > 0) {
+          mbar_wait(&p_free[(hs - 1) & 1], ((hs - 1) >> 1) & 1);  // every PV issued so far has landed in O
+          tc_fence_after();
+          uint32_t o[32];
+          tmem_ld_32x32b_x32(tmem + lane_base + kColO + hf * 32, o);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-          tmem_st_32x32b_x32(tmem + lane_base + kColO + c * 32, r);
-        }
-        tmem_st_wait();
-      }
-      // P_j -> smem, two K-major sub-tiles of 64 keys; 16-byte chunk index XOR (row & 7) = the 128-byte swizzle
-#pragma unroll
-      for (int t = 0; t < 2; ++t) {
-        uint8_t* prow = sP + t * (BQ * 128) + row * 128;
-#pragma unroll
-        for (int c = 0; c < 8; ++c) {
-          const float* v = s + t * 64 + c * 8;
-          uint4 pk;
-          pk.x = pack_bf16(v[0], v[1]); pk.y = pack_bf16(v[2], v[3]); pk.z = pack_bf16(v[4], v[5]); pk.w = pack_bf16(v[6], v[7]);
-          *reinterpret_cast<uint4*>(prow + ((c ^ (row & 7)) << 4)) = pk;
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st_32x32b_x32(tmem + lane_base + kColO + hf * 32, o);
+          tmem_st_wait();
         }
       }
+      const float off = -m * p.scale_log2;
+      float pv[32];
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+      for (int i = 0; i < 32; i += 4) {
+        pv[i] = fast_exp2(fmaf(__uint_as_float(r[i]), p.scale_log2, off));         s0 += pv[i];
+        pv[i + 1] = fast_exp2(fmaf(__uint_as_float(r[i + 1]), p.scale_log2, off)); s1 += pv[i + 1];
+        pv[i + 2] = fast_exp2(fmaf(__uint_as_float(r[i + 2]), p.scale_log2, off)); s2 += pv[i + 2];
+        pv[i + 3] = fast_exp2(fmaf(__uint_as_float(r[i + 3]), p.scale_log2, off)); s3 += pv[i + 3];
+      }
+      l += (s0 + s1) + (s2 + s3);
+      mbar_wait(&p_free[u], ((hs >> 1) & 1) ^ 1);       // PV of step hs-2 no longer reads this P buffer
+      uint8_t* prow = sP + u * kTile + row * 128;
+#pragma unroll
+      for (int g = 0; g < 4; ++g) store_row_chunk(prow, row, hf * 4 + g, pv + g * 8);
       fence_proxy_async();
       tc_fence_before();
-      mbar_arrive(p_full);
+      warp_arrive(&p_full[u], lane);
     }
     // epilogue: O / l -> bf16, log-sum-exp
+    float* xl = s_max;                                  // reuse: the two halves of the row sum
+    softmax_bar();
+    xl[hf * 128 + row] = l;
+    softmax_bar();
+    const float lt = l + xl[(hf ^ 1) * 128 + row];
     mbar_wait(o_done, 0);
     tc_fence_after();
-    const float inv_l = 1.0f / l;
-    const int srow = qt * BQ + row;
-    __nv_bfloat16* orow = p.out + ((size_t)b * p.S + srow) * p.row_stride + (size_t)h * D;
+    const int srow = qt * 128 + row;
+    __nv_bfloat16* orow = p.out + ((size_t)b * p.S + srow) * p.row_stride + (size_t)h * 64 + hf * 32;
+    store_out32(orow, tmem + lane_base + kColO + hf * 32, 1.0f / lt);
+    if (hf == 0 && p.lse != nullptr) p.lse[((size_t)b * p.H + h) * p.S + srow] = m * p.scale + logf(lt);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, kTmemCols);
+}
+
+// ---- backward -----------------------------------------------------------------------------------------------------
+// delta[b, h, s] = sum_d dO[b, s, h, d] * O[b, s, h, d].  8 lanes per (row, head): fully coalesced 16-byte loads.
+__global__ void __launch_bounds__(256) attention_delta_kernel(const FaBwdParams p) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long unit = gid >> 3;                       // (b, s, h) flattened, h fastest
+  const int sub = (int)(gid & 7);
+  const long long total = (long long)p.B * p.S * p.H;
+  float acc = 0.f;
+  if (unit < total) {
+    const uint4 a = reinterpret_cast<const uint4*>(p.out)[unit * 8 + sub];
+    const uint4 g = reinterpret_cast<const uint4*>(p.dout)[unit * 8 + sub];
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, gw[4] = {g.x, g.y, g.z, g.w};
 #pragma unroll
-    for (int c = 0; c < D / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32b_x32(tmem + lane_base + kColO + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; i += 8) {
-        uint4 pk;
-        pk.x = pack_bf16(__uint_as_float(r[i]) * inv_l, __uint_as_float(r[i + 1]) * inv_l);
-        pk.y = pack_bf16(__uint_as_float(r[i + 2]) * inv_l, __uint_as_float(r[i + 3]) * inv_l);
-        pk.z = pack_bf16(__uint_as_float(r[i + 4]) * inv_l, __uint_as_float(r[i + 5]) * inv_l);
-        pk.w = pack_bf16(__uint_as_float(r[i + 6]) * inv_l, __uint_as_float(r[i + 7]) * inv_l);
-        *reinterpret_cast<uint4*>(orow + c * 32 + i) = pk;
+    for (int i = 0; i < 4; ++i) {
+      const float2 af = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[i]));
+      const float2 gf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&gw[i]));
+      acc = fmaf(af.x, gf.x, acc);
+      acc = fmaf(af.y, gf.y, acc);
+    }
+  }
+  acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+  if (sub == 0 && unit < total) {
+    const int hh = (int)(unit % p.H);
+    const long long bs = unit / p.H;
+    const int s = (int)(bs % p.S);
+    const long long b = bs / p.S;
+    p.delta[(b * p.H + hh) * p.S + s] = acc;
+  }
+}
+
+__global__ void __launch_bounds__(fa::kThreads, 2)
+attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                        const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+                        const FaBwdParams p) {
+  using namespace fa;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sdO = sQ + kTile;
+  uint8_t* sKV = sdO + kTile;                      // stage s: K half, V half
+  uint8_t* sdS = sKV + kDqStages * 2 * kHalf;      // [128 q x 64 keys]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + kTile);
+  uint64_t* q_full = bars;                         // 1 (Q and dO)
+  uint64_t* kv_full = bars + 1;                    // kDqStages
+  uint64_t* kv_free = kv_full + kDqStages;         // kDqStages
+  uint64_t* st_full = kv_free + kDqStages;         // 1
+  uint64_t* st_free = st_full + 1;                 // 1
+  uint64_t* ds_full = st_free + 1;                 // 1
+  uint64_t* ds_free = ds_full + 1;                 // 1
+  uint64_t* done = ds_free + 1;                    // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  constexpr uint32_t kColStage = 0, kColOut = 128; // [S(64) | dP(64)], dQ
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int NH = p.S / 64;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV); prefetch_tmap(&tmdO);
+    mbar_init(q_full, 1);
+    for (int j = 0; j < kDqStages; ++j) { mbar_init(&kv_full[j], 1); mbar_init(&kv_free[j], 1); }
+    mbar_init(st_full, 1); mbar_init(st_free, kSoftmaxWarps); mbar_init(ds_full, kSoftmaxWarps); mbar_init(ds_free, 1);
+    mbar_init(done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(q_full, 2 * kTile);
+      tma_load_4d(sQ, &tmQ, q_full, 0, qt * 128, h, b);
+      tma_load_4d(sdO, &tmdO, q_full, 0, qt * 128, h, b);
+      for (int hs = 0; hs < NH; ++hs) {
+        const int st = hs % kDqStages, n = hs / kDqStages;
+        mbar_wait(&kv_free[st], (n & 1) ^ 1);
+        mbar_arrive_expect_tx(&kv_full[st], 2 * kHalf);
+        tma_load_4d(sKV + st * 2 * kHalf, &tmK, &kv_full[st], 0, hs * 64, h, b);
+        tma_load_4d(sKV + st * 2 * kHalf + kHalf, &tmV, &kv_full[st], 0, hs * 64, h, b);
       }
     }
-    if (p.lse != nullptr) p.lse[((size_t)b * p.H + h) * p.S + srow] = m * p.scale + logf(l);
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);
+      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);
+      const uint32_t aQ = smem_u32(sQ), adO = smem_u32(sdO), aKV = smem_u32(sKV), adS = smem_u32(sdS);
+      auto issue_scores = [&](int hs) {
+        const int st = hs % kDqStages;
+        const uint32_t aK = aKV + st * 2 * kHalf, aV = aK + kHalf;
+        mbar_wait(&kv_full[st], (hs / kDqStages) & 1);
+        mbar_wait(st_free, (hs & 1) ^ 1);                 // the softmax warps have read step hs-1 out of TMEM
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 4; ++k)           // S = Q K^T
+          umma_f16(tmem + kColStage, make_smem_desc_sw128(aQ + k * 32, 16, 1024), make_smem_desc_sw128(aK + k * 32, 16, 1024), idesc_s, k != 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)           // dP = dO V^T
+          umma_f16(tmem + kColStage + 64, make_smem_desc_sw128(adO + k * 32, 16, 1024), make_smem_desc_sw128(aV + k * 32, 16, 1024), idesc_s, k != 0);
+        umma_commit(st_full);
+      };
+      mbar_wait(q_full, 0);
+      issue_scores(0);
+      for (int hs = 0; hs < NH; ++hs) {
+        if (hs + 1 < NH) issue_scores(hs + 1);            // overlaps the softmax of step hs
+        const int st = hs % kDqStages;
+        const uint32_t aK = aKV + st * 2 * kHalf;
+        mbar_wait(ds_full, hs & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)        // dQ += dS K   (K rows as the MN-major B operand)
+          umma_f16(tmem + kColOut, make_smem_desc_sw128(adS + kk * 32, 16, 1024), make_smem_desc_sw128(aK + kk * 2048, 8192, 1024),
+                   idesc_o, (hs > 0) || (kk > 0));
+        umma_commit(ds_free);
+        umma_commit(&kv_free[st]);
+      }
+      umma_commit(done);
+    }
+  } else {
+    const int quad = warp & 3, hf = (warp - 2) >> 2;
+    const int row = quad * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const int srow = qt * 128 + row;
+    const size_t soff = ((size_t)b * p.H + h) * p.S + srow;
+    const float lse2 = p.lse[soff] * kLog2e;
+    const float dsc = p.delta[soff] * p.scale;
+    uint8_t* drow = sdS + row * 128;
+    for (int hs = 0; hs < NH; ++hs) {
+      mbar_wait(st_full, hs & 1);
+      tc_fence_after();
+      uint32_t rs[32], rp[32];
+      tmem_ld_32x32b_x32(tmem + lane_base + kColStage + hf * 32, rs);
+      tmem_ld_32x32b_x32(tmem + lane_base + kColStage + 64 + hf * 32, rp);
+      tmem_ld_wait();
+      tc_fence_before();
+      warp_arrive(st_free, lane);
+      float ds[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        const float pr = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse2));
+        ds[i] = pr * fmaf(__uint_as_float(rp[i]), p.scale, -dsc);
+      }
+      mbar_wait(ds_free, (hs & 1) ^ 1);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) store_row_chunk(drow, row, hf * 4 + g, ds + g * 8);
+      fence_proxy_async();
+      warp_arrive(ds_full, lane);
+    }
+    mbar_wait(done, 0);
+    tc_fence_after();
+    store_out32(p.dq + ((size_t)b * p.S + srow) * p.row_stride + (size_t)h * 64 + hf * 32, tmem + lane_base + kColOut + hf * 32, 1.0f);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, kTmemCols);
+}
+
+__global__ void __launch_bounds__(fa::kThreads, 2)
+attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                          const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
+                          const FaBwdParams p) {
+  using namespace fa;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sK = smem;
+  uint8_t* sV = sK + kTile;
+  uint8_t* sQdO = sV + kTile;                      // stage s: Q half (64 queries), dO half
+  uint8_t* sP = sQdO + kDkvStages * 2 * kHalf;     // [128 keys x 64 queries]
+  uint8_t* sdS = sP + kTile;
+  float* s_lse2 = reinterpret_cast<float*>(sdS + kTile);       // [S]
+  float* s_dsc = s_lse2 + kMaxS;                               // [S]  delta * scale
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_dsc + kMaxS);
+  uint64_t* kv_full = bars;                        // 1
+  uint64_t* qdo_full = bars + 1;                   // kDkvStages
+  uint64_t* qdo_free = qdo_full + kDkvStages;      // kDkvStages
+  uint64_t* st_full = qdo_free + kDkvStages;       // 1
+  uint64_t* st_free = st_full + 1;                 // 1
+  uint64_t* pd_full = st_free + 1;                 // 1
+  uint64_t* pd_free = pd_full + 1;                 // 1
+  uint64_t* done = pd_free + 1;                    // 1
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  constexpr uint32_t kColStage = 0, kColdV = 128, kColdK = 192;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int NH = p.S / 64;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV); prefetch_tmap(&tmdO);
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < kDkvStages; ++i) { mbar_init(&qdo_full[i], 1); mbar_init(&qdo_free[i], 1); }
+    mbar_init(st_full, 1); mbar_init(st_free, kSoftmaxWarps); mbar_init(pd_full, kSoftmaxWarps); mbar_init(pd_free, 1);
+    mbar_init(done, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) { tmem_alloc(tmem_slot, kTmemCols); tmem_relinquish(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(kv_full, 2 * kTile);
+      tma_load_4d(sK, &tmK, kv_full, 0, kt * 128, h, b);
+      tma_load_4d(sV, &tmV, kv_full, 0, kt * 128, h, b);
+      for (int hs = 0; hs < NH; ++hs) {
+        const int st = hs % kDkvStages, n = hs / kDkvStages;
+        mbar_wait(&qdo_free[st], (n & 1) ^ 1);
+        mbar_arrive_expect_tx(&qdo_full[st], 2 * kHalf);
+        tma_load_4d(sQdO + st * 2 * kHalf, &tmQ, &qdo_full[st], 0, hs * 64, h, b);
+        tma_load_4d(sQdO + st * 2 * kHalf + kHalf, &tmdO, &qdo_full[st], 0, hs * 64, h, b);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);
+      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);
+      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aQdO = smem_u32(sQdO), aP = smem_u32(sP), adS = smem_u32(sdS);
+      auto issue_scores = [&](int hs) {
+        const int st = hs % kDkvStages;
+        const uint32_t aQ = aQdO + st * 2 * kHalf, adO = aQ + kHalf;
+        mbar_wait(&qdo_full[st], (hs / kDkvStages) & 1);
+        mbar_wait(st_free, (hs & 1) ^ 1);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < 4; ++k)         // S^T = K Q^T
+          umma_f16(tmem + kColStage, make_smem_desc_sw128(aK + k * 32, 16, 1024), make_smem_desc_sw128(aQ + k * 32, 16, 1024), idesc_s, k != 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)         // dP^T = V dO^T
+          umma_f16(tmem + kColStage + 64, make_smem_desc_sw128(aV + k * 32, 16, 1024), make_smem_desc_sw128(adO + k * 32, 16, 1024), idesc_s, k != 0);
+        umma_commit(st_full);
+      };
+      mbar_wait(kv_full, 0);
+      issue_scores(0);
+      for (int hs = 0; hs < NH; ++hs) {
+        if (hs + 1 < NH) issue_scores(hs + 1);
+        const int st = hs % kDkvStages;
+        const uint32_t aQ = aQdO + st * 2 * kHalf, adO = aQ + kHalf;
+        mbar_wait(pd_full, hs & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)      // dV += P^T dO   (A: [keys x 64 q] K-major, B: dO rows as MN-major)
+          umma_f16(tmem + kColdV, make_smem_desc_sw128(aP + kk * 32, 16, 1024), make_smem_desc_sw128(adO + kk * 2048, 8192, 1024),
+                   idesc_o, (hs > 0) || (kk > 0));
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)      // dK += dS^T Q
+          umma_f16(tmem + kColdK, make_smem_desc_sw128(adS + kk * 32, 16, 1024), make_smem_desc_sw128(aQ + kk * 2048, 8192, 1024),
+                   idesc_o, (hs > 0) || (kk > 0));
+        umma_commit(pd_free);
+        umma_commit(&qdo_free[st]);
+      }
+      umma_commit(done);
+    }
+  } else {
+    const int quad = warp & 3, hf = (warp - 2) >> 2;
+    const int row = quad * 32 + lane;                         // key row within the chunk
+    const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    const size_t sbase = ((size_t)b * p.H + h) * p.S;
+    for (int i = threadIdx.x - 64; i < p.S; i += kSoftmaxThreads) {
+      s_lse2[i] = p.lse[sbase + i] * kLog2e;
+      s_dsc[i] = p.delta[sbase + i] * p.scale;
+    }
+    softmax_bar();
+    uint8_t* prow = sP + row * 128;
+    uint8_t* drow = sdS + row * 128;
+    for (int hs = 0; hs < NH; ++hs) {
+      mbar_wait(st_full, hs & 1);
+      tc_fence_after();
+      uint32_t rs[32], rp[32];
+      tmem_ld_32x32b_x32(tmem + lane_base + kColStage + hf * 32, rs);
+      tmem_ld_32x32b_x32(tmem + lane_base + kColStage + 64 + hf * 32, rp);
+      tmem_ld_wait();
+      tc_fence_before();
+      warp_arrive(st_free, lane);
+      float pr[32], ds[32];
+      const float4* l4 = reinterpret_cast<const float4*>(s_lse2 + hs * 64 + hf * 32);
+      const float4* d4 = reinterpret_cast<const float4*>(s_dsc + hs * 64 + hf * 32);
+#pragma unroll
+      for (int i4 = 0; i4 < 8; ++i4) {
+        const float4 lq = l4[i4], dq = d4[i4];
+        const float lv[4] = {lq.x, lq.y, lq.z, lq.w}, dv[4] = {dq.x, dq.y, dq.z, dq.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = i4 * 4 + e;
+          pr[i] = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lv[e]));
+          ds[i] = pr[i] * fmaf(__uint_as_float(rp[i]), p.scale, -dv[e]);
+        }
+      }
+      mbar_wait(pd_free, (hs & 1) ^ 1);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        store_row_chunk(prow, row, hf * 4 + g, pr + g * 8);
+        store_row_chunk(drow, row, hf * 4 + g, ds + g * 8);
+      }
+      fence_proxy_async();
+      warp_arrive(pd_full, lane);
+    }
+    mbar_wait(done, 0);
+    tc_fence_after();
+    const size_t goff = ((size_t)b * p.S + kt * 128 + row) * p.row_stride + (size_t)h * 64 + hf * 32;
+    store_out32(p.dv + goff, tmem + lane_base + kColdV + hf * 32, 1.0f);
+    store_out32(p.dk + goff, tmem + lane_base + kColdK + hf * 32, 1.0f);
   }
   tc_fence_before();
   __syncthreads();
@@ -226,7 +591,7 @@ typedef CUresult (*EncodeTiledFn2)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-static int fa_make_map(CUtensorMap* m, const void* base, int S, int H, int B, long long row_stride) {
+static int fa_make_map(CUtensorMap* m, const void* base, int S, int H, int B, long long row_stride, int box_rows) {
   static EncodeTiledFn2 enc = nullptr;
   static std::once_flag once;
   std::call_once(once, [] {
@@ -241,12 +606,25 @@ static int fa_make_map(CUtensorMap* m, const void* base, int S, int H, int B, lo
   // [b][s][h][d]: dims innermost first {d, s, h, b}
   cuuint64_t dims[4] = {64, (cuuint64_t)S, (cuuint64_t)H, (cuuint64_t)B};
   cuuint64_t strides[3] = {(cuuint64_t)row_stride * 2, 64 * 2, (cuuint64_t)S * row_stride * 2};
-  cuuint32_t box[4] = {64, 128, 1, 1};
+  cuuint32_t box[4] = {64, (cuuint32_t)box_rows, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   MLT_REQUIRE(r == CUDA_SUCCESS, "attention: cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+static int fa_set_attrs() {
+  static bool attr_set[64] = {};
+  int dev = 0;
+  MLT_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemFwd));
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDq));
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDkv));
+    attr_set[dev & 63] = true;
+  }
   return 0;
 }
 
@@ -258,25 +636,51 @@ using namespace mlt;
 extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, void* out, void* lse, int B, int S, int H, int D,
                                  void* stream) {
   MLT_REQUIRE(D == 64, "mlt_attention_fwd: head dim %d unsupported (64)", D);
-  MLT_REQUIRE(S % 128 == 0 && S >= 128 && S <= 128 * fa::kMaxChunks, "mlt_attention_fwd: sequence length %d unsupported (128..512, multiple of 128)", S);
+  MLT_REQUIRE(S % 128 == 0 && S >= 128 && S <= fa::kMaxS, "mlt_attention_fwd: sequence length %d unsupported (128..512, multiple of 128)", S);
   MLT_REQUIRE(((uintptr_t)q % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0 && ((uintptr_t)out % 16) == 0,
               "mlt_attention_fwd: unaligned tensors");
   const long long rs = (long long)H * D;
   CUtensorMap tq, tk, tv;
-  if (fa_make_map(&tq, q, S, H, B, rs) || fa_make_map(&tk, k, S, H, B, rs) || fa_make_map(&tv, v, S, H, B, rs)) return 1;
+  if (fa_make_map(&tq, q, S, H, B, rs, 128) || fa_make_map(&tk, k, S, H, B, rs, 64) || fa_make_map(&tv, v, S, H, B, rs, 64)) return 1;
   FaParams p;
   p.out = (__nv_bfloat16*)out; p.lse = (float*)lse; p.S = S; p.H = H; p.row_stride = rs;
   p.scale = 1.0f / sqrtf((float)D);
-  p.scale_log2 = p.scale * 1.4426950408889634f;
-  static bool attr_set[64] = {};
-  int dev = 0;
-  MLT_CHECK_CUDA(cudaGetDevice(&dev));
-  if (!attr_set[dev & 63]) {
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemBytes));
-    attr_set[dev & 63] = true;
-  }
-  dim3 grid(S / fa::BQ, H, B);
-  attention_fwd_tcgen05_kernel<<<grid, fa::kThreads, fa::kSmemBytes, (cudaStream_t)stream>>>(tq, tk, tv, p);
+  p.scale_log2 = p.scale * fa::kLog2e;
+  if (fa_set_attrs()) return 1;
+  dim3 grid(S / 128, H, B);
+  attention_fwd_tcgen05_kernel<<<grid, fa::kThreads, fa::kSmemFwd, (cudaStream_t)stream>>>(tq, tk, tv, p);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+// Backward of mlt_attention_fwd.  out / lse are the forward's results, dout the gradient of out; delta is a [B, H, S] fp32
+// scratch the call fills.  dq, dk, dv: [B, S, H*64] bf16.
+extern "C" int mlt_attention_bwd(const void* q, const void* k, const void* v, const void* out, const void* dout, const void* lse,
+                                 void* delta, void* dq, void* dk, void* dv, int B, int S, int H, int D, void* stream) {
+  MLT_REQUIRE(D == 64, "mlt_attention_bwd: head dim %d unsupported (64)", D);
+  MLT_REQUIRE(S % 128 == 0 && S >= 128 && S <= fa::kMaxS, "mlt_attention_bwd: sequence length %d unsupported (128..512, multiple of 128)", S);
+  const void* al[] = {q, k, v, out, dout, dq, dk, dv};
+  for (const void* a : al) MLT_REQUIRE(((uintptr_t)a % 16) == 0, "mlt_attention_bwd: unaligned tensors");
+  const long long rs = (long long)H * D;
+  CUtensorMap tq, tk, tv, tdo, tq64, tk64, tv64, tdo64;
+  if (fa_make_map(&tq, q, S, H, B, rs, 128) || fa_make_map(&tk, k, S, H, B, rs, 128) || fa_make_map(&tv, v, S, H, B, rs, 128) ||
+      fa_make_map(&tdo, dout, S, H, B, rs, 128) || fa_make_map(&tq64, q, S, H, B, rs, 64) || fa_make_map(&tk64, k, S, H, B, rs, 64) ||
+      fa_make_map(&tv64, v, S, H, B, rs, 64) || fa_make_map(&tdo64, dout, S, H, B, rs, 64)) return 1;
+  FaBwdParams p;
+  p.out = (const __nv_bfloat16*)out; p.dout = (const __nv_bfloat16*)dout; p.lse = (const float*)lse; p.delta = (float*)delta;
+  p.dq = (__nv_bfloat16*)dq; p.dk = (__nv_bfloat16*)dk; p.dv = (__nv_bfloat16*)dv;
+  p.B = B; p.S = S; p.H = H; p.row_stride = rs;
+  p.scale = 1.0f / sqrtf((float)D);
+  p.scale_log2 = p.scale * fa::kLog2e;
+  if (fa_set_attrs()) return 1;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long dthreads = (long long)B * S * H * 8;
+  attention_delta_kernel<<<(unsigned)((dthreads + 255) / 256), 256, 0, st>>>(p);
+  MLT_LAUNCH_CHECK();
+  dim3 grid(S / 128, H, B);
+  attention_bwd_dq_kernel<<<grid, fa::kThreads, fa::kSmemDq, st>>>(tq, tk64, tv64, tdo, p);
+  MLT_LAUNCH_CHECK();
+  attention_bwd_dkdv_kernel<<<grid, fa::kThreads, fa::kSmemDkv, st>>>(tq64, tk, tv, tdo64, p);
   MLT_LAUNCH_CHECK();
   return 0;
 }

@@ -480,6 +480,31 @@ def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False):
     return (out, lse) if want_lse else out
 
 
+class _FusedAttentionFn(torch.autograd.Function):
+    """Flash attention on tcgen05: forward keeps only the per-row log-sum-exp, backward recomputes P on the tensor cores
+    (csrc/attention_tcgen05.cu: one dQ kernel, one dK/dV kernel, no atomics)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, heads):
+        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True)
+        ctx.save_for_backward(q.contiguous(), k.contiguous(), v.contiguous(), out, lse)
+        ctx.heads = heads
+        return out
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, out, lse = ctx.saved_tensors
+        B, S, HD = q.shape
+        do = do.contiguous()
+        dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+        delta = torch.empty_like(lse)
+        check(_lib.lib().mlt_attention_bwd(ptr(q), ptr(k), ptr(v), ptr(out), ptr(do), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
+                                           _c_int(B), _c_int(S), _c_int(ctx.heads), _c_int(HD // ctx.heads), stream_handle()),
+              "mlt_attention_bwd")
+        launches.bump("attention_bwd_tcgen05", 2)
+        return dq, dk, dv, None
+
+
 def fused_attention_ok(q, heads: int) -> bool:
     B, S, HD = q.shape
     return HD // heads == 64 and S % 128 == 0 and 128 <= S <= 512
@@ -491,8 +516,8 @@ def attention(q, k, v, heads: int):
     d = HD // heads
     if use_native(q, k, v) and q.dtype == torch.bfloat16 and d % 8 == 0 and S % 8 == 0 and S <= 1024:
         needs_grad = torch.is_grad_enabled() and (q.requires_grad or k.requires_grad or v.requires_grad)
-        if not needs_grad and fused_attention_ok(q, heads):
-            return attention_fused_fwd(q, k, v, heads)
+        if fused_attention_ok(q, heads):
+            return _FusedAttentionFn.apply(q, k, v, heads) if needs_grad else attention_fused_fwd(q, k, v, heads)
         return _AttentionFn.apply(q, k, v, heads)
     qh, kh, vh = (t.view(B, S, heads, d).transpose(1, 2) for t in (q, k, v))
     o = TF.scaled_dot_product_attention(qh.float(), kh.float(), vh.float())

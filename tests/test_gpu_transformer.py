@@ -179,3 +179,24 @@ def test_fused_attention_forward(B, S, heads):
     _close(lse, ref_lse, 2e-3, "lse")
     with torch.no_grad():
         _close(F.attention(q, k, v, heads), ref, 2e-2, "dispatch under no_grad")
+
+
+@pytest.mark.parametrize("B,S,heads", [(1, 128, 1), (2, 256, 3), (2, 512, 12), (1, 384, 2)])
+def test_fused_attention_backward(B, S, heads):
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(1)
+    d = 64
+    q, k, v = ((torch.randn(B, S, heads * d, device=DEV) * 0.7).to(torch.bfloat16).requires_grad_() for _ in range(3))
+    go = (torch.randn(B, S, heads * d, device=DEV) * 0.5).to(torch.bfloat16)
+    out = F.attention(q, k, v, heads)
+    out.backward(go)
+    torch.cuda.synchronize()
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    sp = lambda t: t.view(B, S, heads, d).transpose(1, 2)
+    ref = TF.scaled_dot_product_attention(sp(qf), sp(kf), sp(vf)).transpose(1, 2).reshape(B, S, heads * d)
+    ref.backward(go.float())
+    _close(out, ref, 2e-2, "fused attention out")
+    for name, got, want in (("dq", q.grad, qf.grad), ("dk", k.grad, kf.grad), ("dv", v.grad, vf.grad)):
+        err = (got.float() - want).abs().max().item() / (want.abs().max().item() + 1e-12)
+        assert err < 3e-2, f"{name}: relative max error {err}"
