@@ -66,6 +66,18 @@ struct FaBwdParams {
   float scale_log2, scale;
 };
 
+// Optional per-CTA timeline (analysis only): 8 x int64 per CTA when a buffer has been installed.
+__device__ long long* g_fa_dbg = nullptr;
+__device__ __forceinline__ long long gtimer() {
+  long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+#define FA_DBG(slot)                                                                                          \
+  do {                                                                                                        \
+    if (dbg != nullptr) dbg[((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * 8 + (slot)] = gtimer(); \
+  } while (0)
+
 __device__ __forceinline__ void softmax_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
 // All lanes of the warp have done their part (TMEM reads retired, or smem writes + proxy fence): one lane arrives.
@@ -160,39 +172,45 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);       // Q, K both K-major
-      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);       // P K-major, V MN-major
-      const uint32_t aQ = smem_u32(sQ), aKV = smem_u32(sKV), aP = smem_u32(sP);
-      auto issue_pv = [&](int hs) {
-        const int u = hs & 1, st = hs % kFwdStages;
-        mbar_wait(&p_full[u], (hs >> 1) & 1);
-        tc_fence_after();
-        const uint32_t aV = aKV + st * 2 * kHalf + kHalf;
+    // The whole warp walks the loop and waits; one elected lane issues (keeps the operands in uniform registers).
+    const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);       // Q, K both K-major
+    const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);       // P K-major, V MN-major
+    const uint32_t aQ = smem_u32(sQ), aKV = smem_u32(sKV), aP = smem_u32(sP);
+    auto issue_pv = [&](int hs) {
+      const int u = hs & 1, st = hs % kFwdStages;
+      mbar_wait(&p_full[u], (hs >> 1) & 1);
+      tc_fence_after();
+      const uint32_t aV = aKV + st * 2 * kHalf + kHalf;
+      if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
           umma_f16(tmem + kColO, make_smem_desc_sw128(aP + u * kTile + kk * 32, 16, 1024),
                    make_smem_desc_sw128(aV + kk * 2048, 8192, 1024), idesc_o, (hs > 0) || (kk > 0));
         umma_commit(&p_free[u]);                  // P buffer reusable, O holds step hs
         umma_commit(&kv_free[st]);
-      };
-      mbar_wait(q_full, 0);
-      for (int hs = 0; hs < NH; ++hs) {
-        const int u = hs & 1, st = hs % kFwdStages;
-        mbar_wait(&kv_full[st], (hs / kFwdStages) & 1);
-        mbar_wait(&s_free[u], ((hs >> 1) & 1) ^ 1);
-        tc_fence_after();
-        const uint32_t aK = aKV + st * 2 * kHalf;
+      }
+      __syncwarp();
+    };
+    mbar_wait(q_full, 0);
+    for (int hs = 0; hs < NH; ++hs) {
+      const int u = hs & 1, st = hs % kFwdStages;
+      mbar_wait(&kv_full[st], (hs / kFwdStages) & 1);
+      mbar_wait(&s_free[u], ((hs >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t aK = aKV + st * 2 * kHalf;
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           umma_f16(tmem + kColS + u * 64, make_smem_desc_sw128(aQ + k * 32, 16, 1024),
                    make_smem_desc_sw128(aK + k * 32, 16, 1024), idesc_s, k != 0);
         umma_commit(&s_full[u]);
-        if (hs > 0) issue_pv(hs - 1);
       }
-      issue_pv(NH - 1);
-      umma_commit(o_done);
+      __syncwarp();
+      if (hs > 0) issue_pv(hs - 1);
     }
+    issue_pv(NH - 1);
+    if (elect_one()) umma_commit(o_done);
+    __syncwarp();
   } else {
     const int quad = warp & 3, hf = (warp - 2) >> 2;
     const int row = quad * 32 + lane;                   // query row within the tile
@@ -331,6 +349,8 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int NH = p.S / 64;
+  long long* dbg = g_fa_dbg;
+  if (threadIdx.x == 0) FA_DBG(0);
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV); prefetch_tmap(&tmdO);
@@ -345,6 +365,7 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  if (threadIdx.x == 0) FA_DBG(1);
 
   if (warp == 0) {
     if (lane == 0) {
@@ -360,16 +381,16 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);
-      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);
-      const uint32_t aQ = smem_u32(sQ), adO = smem_u32(sdO), aKV = smem_u32(sKV), adS = smem_u32(sdS);
-      auto issue_scores = [&](int hs) {
-        const int st = hs % kDqStages;
-        const uint32_t aK = aKV + st * 2 * kHalf, aV = aK + kHalf;
-        mbar_wait(&kv_full[st], (hs / kDqStages) & 1);
-        mbar_wait(st_free, (hs & 1) ^ 1);                 // the softmax warps have read step hs-1 out of TMEM
-        tc_fence_after();
+    const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);
+    const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);
+    const uint32_t aQ = smem_u32(sQ), adO = smem_u32(sdO), aKV = smem_u32(sKV), adS = smem_u32(sdS);
+    auto issue_scores = [&](int hs) {
+      const int st = hs % kDqStages;
+      const uint32_t aK = aKV + st * 2 * kHalf, aV = aK + kHalf;
+      mbar_wait(&kv_full[st], (hs / kDqStages) & 1);
+      mbar_wait(st_free, (hs & 1) ^ 1);                 // the softmax warps have read step hs-1 out of TMEM
+      tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)           // S = Q K^T
           umma_f16(tmem + kColStage, make_smem_desc_sw128(aQ + k * 32, 16, 1024), make_smem_desc_sw128(aK + k * 32, 16, 1024), idesc_s, k != 0);
@@ -377,15 +398,20 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
         for (int k = 0; k < 4; ++k)           // dP = dO V^T
           umma_f16(tmem + kColStage + 64, make_smem_desc_sw128(adO + k * 32, 16, 1024), make_smem_desc_sw128(aV + k * 32, 16, 1024), idesc_s, k != 0);
         umma_commit(st_full);
-      };
-      mbar_wait(q_full, 0);
-      issue_scores(0);
-      for (int hs = 0; hs < NH; ++hs) {
-        if (hs + 1 < NH) issue_scores(hs + 1);            // overlaps the softmax of step hs
-        const int st = hs % kDqStages;
-        const uint32_t aK = aKV + st * 2 * kHalf;
-        mbar_wait(ds_full, hs & 1);
-        tc_fence_after();
+      }
+      __syncwarp();
+    };
+    mbar_wait(q_full, 0);
+    if (lane == 0) FA_DBG(2);
+    issue_scores(0);
+    if (lane == 0) FA_DBG(3);
+    for (int hs = 0; hs < NH; ++hs) {
+      if (hs + 1 < NH) issue_scores(hs + 1);            // overlaps the softmax of step hs
+      const int st = hs % kDqStages;
+      const uint32_t aK = aKV + st * 2 * kHalf;
+      mbar_wait(ds_full, hs & 1);
+      tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)        // dQ += dS K   (K rows as the MN-major B operand)
           umma_f16(tmem + kColOut, make_smem_desc_sw128(adS + kk * 32, 16, 1024), make_smem_desc_sw128(aK + kk * 2048, 8192, 1024),
@@ -393,8 +419,10 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
         umma_commit(ds_free);
         umma_commit(&kv_free[st]);
       }
-      umma_commit(done);
+      __syncwarp();
     }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
   } else {
     const int quad = warp & 3, hf = (warp - 2) >> 2;
     const int row = quad * 32 + lane;
@@ -406,6 +434,7 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     uint8_t* drow = sdS + row * 128;
     for (int hs = 0; hs < NH; ++hs) {
       mbar_wait(st_full, hs & 1);
+      if (threadIdx.x == 64 && hs == 0) FA_DBG(4);
       tc_fence_after();
       uint32_t rs[32], rp[32];
       tmem_ld_32x32b_x32(tmem + lane_base + kColStage + hf * 32, rs);
@@ -425,13 +454,16 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
       fence_proxy_async();
       warp_arrive(ds_full, lane);
     }
+    if (threadIdx.x == 64) FA_DBG(5);
     mbar_wait(done, 0);
+    if (threadIdx.x == 64) FA_DBG(6);
     tc_fence_after();
     store_out32(p.dq + ((size_t)b * p.S + srow) * p.row_stride + (size_t)h * 64 + hf * 32, tmem + lane_base + kColOut + hf * 32, 1.0f);
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, kTmemCols);
+  if (threadIdx.x == 32) FA_DBG(7);
 }
 
 __global__ void __launch_bounds__(fa::kThreads, 2)
@@ -492,16 +524,16 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);
-      const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);
-      const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aQdO = smem_u32(sQdO), aP = smem_u32(sP), adS = smem_u32(sdS);
-      auto issue_scores = [&](int hs) {
-        const int st = hs % kDkvStages;
-        const uint32_t aQ = aQdO + st * 2 * kHalf, adO = aQ + kHalf;
-        mbar_wait(&qdo_full[st], (hs / kDkvStages) & 1);
-        mbar_wait(st_free, (hs & 1) ^ 1);
-        tc_fence_after();
+    const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);
+    const uint32_t idesc_o = make_idesc_bf16(128, 64, 0, 1);
+    const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aQdO = smem_u32(sQdO), aP = smem_u32(sP), adS = smem_u32(sdS);
+    auto issue_scores = [&](int hs) {
+      const int st = hs % kDkvStages;
+      const uint32_t aQ = aQdO + st * 2 * kHalf, adO = aQ + kHalf;
+      mbar_wait(&qdo_full[st], (hs / kDkvStages) & 1);
+      mbar_wait(st_free, (hs & 1) ^ 1);
+      tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)         // S^T = K Q^T
           umma_f16(tmem + kColStage, make_smem_desc_sw128(aK + k * 32, 16, 1024), make_smem_desc_sw128(aQ + k * 32, 16, 1024), idesc_s, k != 0);
@@ -509,15 +541,18 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
         for (int k = 0; k < 4; ++k)         // dP^T = V dO^T
           umma_f16(tmem + kColStage + 64, make_smem_desc_sw128(aV + k * 32, 16, 1024), make_smem_desc_sw128(adO + k * 32, 16, 1024), idesc_s, k != 0);
         umma_commit(st_full);
-      };
-      mbar_wait(kv_full, 0);
-      issue_scores(0);
-      for (int hs = 0; hs < NH; ++hs) {
-        if (hs + 1 < NH) issue_scores(hs + 1);
-        const int st = hs % kDkvStages;
-        const uint32_t aQ = aQdO + st * 2 * kHalf, adO = aQ + kHalf;
-        mbar_wait(pd_full, hs & 1);
-        tc_fence_after();
+      }
+      __syncwarp();
+    };
+    mbar_wait(kv_full, 0);
+    issue_scores(0);
+    for (int hs = 0; hs < NH; ++hs) {
+      if (hs + 1 < NH) issue_scores(hs + 1);
+      const int st = hs % kDkvStages;
+      const uint32_t aQ = aQdO + st * 2 * kHalf, adO = aQ + kHalf;
+      mbar_wait(pd_full, hs & 1);
+      tc_fence_after();
+      if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)      // dV += P^T dO   (A: [keys x 64 q] K-major, B: dO rows as MN-major)
           umma_f16(tmem + kColdV, make_smem_desc_sw128(aP + kk * 32, 16, 1024), make_smem_desc_sw128(adO + kk * 2048, 8192, 1024),
@@ -529,8 +564,10 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
         umma_commit(pd_free);
         umma_commit(&qdo_free[st]);
       }
-      umma_commit(done);
+      __syncwarp();
     }
+    if (elect_one()) umma_commit(done);
+    __syncwarp();
   } else {
     const int quad = warp & 3, hf = (warp - 2) >> 2;
     const int row = quad * 32 + lane;                         // key row within the chunk
@@ -631,6 +668,13 @@ static int fa_set_attrs() {
 }  // namespace mlt
 
 using namespace mlt;
+
+// Analysis hook: install (or clear with NULL) a device buffer of 8 int64 per CTA that the dQ kernel fills with timestamps.
+extern "C" int mlt_attention_set_debug(void* buf) {
+  long long* b = (long long*)buf;
+  MLT_CHECK_CUDA(cudaMemcpyToSymbol(g_fa_dbg, &b, sizeof(b)));
+  return 0;
+}
 
 // q, k, v, out: [B, S, H*64] bf16 (row stride H*64);  lse: [B, H, S] fp32 or NULL.
 extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, void* out, void* lse, int B, int S, int H, int D,
