@@ -50,7 +50,7 @@ struct FaParams {
   __nv_bfloat16* out;        // [B, S, H*64]
   float* lse;                // [B, H, S]  (natural-log sum-exp of the scaled scores)
   int S, H;
-  long long row_stride;      // H * 64
+  long long row_stride;      // of out: H * 64
   float scale_log2;          // (1/sqrt(d)) * log2(e)
   float scale;
 };
@@ -62,7 +62,8 @@ struct FaBwdParams {
   float* delta;               // [B, H, S]
   __nv_bfloat16 *dq, *dk, *dv;
   int B, S, H;
-  long long row_stride;
+  long long row_stride;       // of out / dout: H * 64
+  long long ld_dqkv;          // row stride of dq, dk, dv (H * 64, or 3 * H * 64 when they are slices of one packed tensor)
   float scale_log2, scale;
 };
 
@@ -160,16 +161,20 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
   const uint32_t tmem = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_arrive_expect_tx(q_full, kTile);
       tma_load_4d(sQ, &tmQ, q_full, 0, qt * 128, h, b);
-      for (int hs = 0; hs < NH; ++hs) {
-        const int st = hs % kFwdStages, n = hs / kFwdStages;
-        mbar_wait(&kv_free[st], (n & 1) ^ 1);
+    }
+    __syncwarp();
+    for (int hs = 0; hs < NH; ++hs) {
+      const int st = hs % kFwdStages, n = hs / kFwdStages;
+      mbar_wait(&kv_free[st], (n & 1) ^ 1);
+      if (elect_one()) {
         mbar_arrive_expect_tx(&kv_full[st], 2 * kHalf);
         tma_load_4d(sKV + st * 2 * kHalf, &tmK, &kv_full[st], 0, hs * 64, h, b);
         tma_load_4d(sKV + st * 2 * kHalf + kHalf, &tmV, &kv_full[st], 0, hs * 64, h, b);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
     // The whole warp walks the loop and waits; one elected lane issues (keeps the operands in uniform registers).
@@ -368,17 +373,21 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
   if (threadIdx.x == 0) FA_DBG(1);
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_arrive_expect_tx(q_full, 2 * kTile);
       tma_load_4d(sQ, &tmQ, q_full, 0, qt * 128, h, b);
       tma_load_4d(sdO, &tmdO, q_full, 0, qt * 128, h, b);
-      for (int hs = 0; hs < NH; ++hs) {
-        const int st = hs % kDqStages, n = hs / kDqStages;
-        mbar_wait(&kv_free[st], (n & 1) ^ 1);
+    }
+    __syncwarp();
+    for (int hs = 0; hs < NH; ++hs) {
+      const int st = hs % kDqStages, n = hs / kDqStages;
+      mbar_wait(&kv_free[st], (n & 1) ^ 1);
+      if (elect_one()) {
         mbar_arrive_expect_tx(&kv_full[st], 2 * kHalf);
         tma_load_4d(sKV + st * 2 * kHalf, &tmK, &kv_full[st], 0, hs * 64, h, b);
         tma_load_4d(sKV + st * 2 * kHalf + kHalf, &tmV, &kv_full[st], 0, hs * 64, h, b);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
     const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);
@@ -458,7 +467,7 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     mbar_wait(done, 0);
     if (threadIdx.x == 64) FA_DBG(6);
     tc_fence_after();
-    store_out32(p.dq + ((size_t)b * p.S + srow) * p.row_stride + (size_t)h * 64 + hf * 32, tmem + lane_base + kColOut + hf * 32, 1.0f);
+    store_out32(p.dq + ((size_t)b * p.S + srow) * p.ld_dqkv + (size_t)h * 64 + hf * 32, tmem + lane_base + kColOut + hf * 32, 1.0f);
   }
   tc_fence_before();
   __syncthreads();
@@ -511,17 +520,21 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
   const uint32_t tmem = *tmem_slot;
 
   if (warp == 0) {
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_arrive_expect_tx(kv_full, 2 * kTile);
       tma_load_4d(sK, &tmK, kv_full, 0, kt * 128, h, b);
       tma_load_4d(sV, &tmV, kv_full, 0, kt * 128, h, b);
-      for (int hs = 0; hs < NH; ++hs) {
-        const int st = hs % kDkvStages, n = hs / kDkvStages;
-        mbar_wait(&qdo_free[st], (n & 1) ^ 1);
+    }
+    __syncwarp();
+    for (int hs = 0; hs < NH; ++hs) {
+      const int st = hs % kDkvStages, n = hs / kDkvStages;
+      mbar_wait(&qdo_free[st], (n & 1) ^ 1);
+      if (elect_one()) {
         mbar_arrive_expect_tx(&qdo_full[st], 2 * kHalf);
         tma_load_4d(sQdO + st * 2 * kHalf, &tmQ, &qdo_full[st], 0, hs * 64, h, b);
         tma_load_4d(sQdO + st * 2 * kHalf + kHalf, &tmdO, &qdo_full[st], 0, hs * 64, h, b);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
     const uint32_t idesc_s = make_idesc_bf16(128, 64, 0, 0);
@@ -614,7 +627,7 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     }
     mbar_wait(done, 0);
     tc_fence_after();
-    const size_t goff = ((size_t)b * p.S + kt * 128 + row) * p.row_stride + (size_t)h * 64 + hf * 32;
+    const size_t goff = ((size_t)b * p.S + kt * 128 + row) * p.ld_dqkv + (size_t)h * 64 + hf * 32;
     store_out32(p.dv + goff, tmem + lane_base + kColdV + hf * 32, 1.0f);
     store_out32(p.dk + goff, tmem + lane_base + kColdK + hf * 32, 1.0f);
   }
@@ -676,16 +689,19 @@ extern "C" int mlt_attention_set_debug(void* buf) {
   return 0;
 }
 
-// q, k, v, out: [B, S, H*64] bf16 (row stride H*64);  lse: [B, H, S] fp32 or NULL.
-extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, void* out, void* lse, int B, int S, int H, int D,
-                                 void* stream) {
+// q, k, v: [B, S, H*64] bf16 with row stride ld_qkv (0 = H*64; 3*H*64 for slices of a packed QKV projection);
+// out: [B, S, H*64] bf16;  lse: [B, H, S] fp32 or NULL.
+extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, long long ld_qkv, void* out, void* lse, int B, int S,
+                                 int H, int D, void* stream) {
   MLT_REQUIRE(D == 64, "mlt_attention_fwd: head dim %d unsupported (64)", D);
   MLT_REQUIRE(S % 128 == 0 && S >= 128 && S <= fa::kMaxS, "mlt_attention_fwd: sequence length %d unsupported (128..512, multiple of 128)", S);
   MLT_REQUIRE(((uintptr_t)q % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0 && ((uintptr_t)out % 16) == 0,
               "mlt_attention_fwd: unaligned tensors");
   const long long rs = (long long)H * D;
+  const long long ldq = ld_qkv > 0 ? ld_qkv : rs;
+  MLT_REQUIRE(ldq >= rs && ldq % 8 == 0, "mlt_attention_fwd: bad q/k/v row stride %lld", ldq);
   CUtensorMap tq, tk, tv;
-  if (fa_make_map(&tq, q, S, H, B, rs, 128) || fa_make_map(&tk, k, S, H, B, rs, 64) || fa_make_map(&tv, v, S, H, B, rs, 64)) return 1;
+  if (fa_make_map(&tq, q, S, H, B, ldq, 128) || fa_make_map(&tk, k, S, H, B, ldq, 64) || fa_make_map(&tv, v, S, H, B, ldq, 64)) return 1;
   FaParams p;
   p.out = (__nv_bfloat16*)out; p.lse = (float*)lse; p.S = S; p.H = H; p.row_stride = rs;
   p.scale = 1.0f / sqrtf((float)D);
@@ -698,22 +714,25 @@ extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, vo
 }
 
 // Backward of mlt_attention_fwd.  out / lse are the forward's results, dout the gradient of out; delta is a [B, H, S] fp32
-// scratch the call fills.  dq, dk, dv: [B, S, H*64] bf16.
-extern "C" int mlt_attention_bwd(const void* q, const void* k, const void* v, const void* out, const void* dout, const void* lse,
-                                 void* delta, void* dq, void* dk, void* dv, int B, int S, int H, int D, void* stream) {
+// scratch the call fills.  dq, dk, dv: [B, S, H*64] bf16 with row stride ld_dqkv (0 = H*64).
+extern "C" int mlt_attention_bwd(const void* q, const void* k, const void* v, long long ld_qkv, const void* out, const void* dout,
+                                 const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B, int S, int H,
+                                 int D, void* stream) {
   MLT_REQUIRE(D == 64, "mlt_attention_bwd: head dim %d unsupported (64)", D);
   MLT_REQUIRE(S % 128 == 0 && S >= 128 && S <= fa::kMaxS, "mlt_attention_bwd: sequence length %d unsupported (128..512, multiple of 128)", S);
   const void* al[] = {q, k, v, out, dout, dq, dk, dv};
   for (const void* a : al) MLT_REQUIRE(((uintptr_t)a % 16) == 0, "mlt_attention_bwd: unaligned tensors");
   const long long rs = (long long)H * D;
+  const long long ldq = ld_qkv > 0 ? ld_qkv : rs, ldd = ld_dqkv > 0 ? ld_dqkv : rs;
+  MLT_REQUIRE(ldq >= rs && ldq % 8 == 0 && ldd >= rs && ldd % 8 == 0, "mlt_attention_bwd: bad row strides %lld / %lld", ldq, ldd);
   CUtensorMap tq, tk, tv, tdo, tq64, tk64, tv64, tdo64;
-  if (fa_make_map(&tq, q, S, H, B, rs, 128) || fa_make_map(&tk, k, S, H, B, rs, 128) || fa_make_map(&tv, v, S, H, B, rs, 128) ||
-      fa_make_map(&tdo, dout, S, H, B, rs, 128) || fa_make_map(&tq64, q, S, H, B, rs, 64) || fa_make_map(&tk64, k, S, H, B, rs, 64) ||
-      fa_make_map(&tv64, v, S, H, B, rs, 64) || fa_make_map(&tdo64, dout, S, H, B, rs, 64)) return 1;
+  if (fa_make_map(&tq, q, S, H, B, ldq, 128) || fa_make_map(&tk, k, S, H, B, ldq, 128) || fa_make_map(&tv, v, S, H, B, ldq, 128) ||
+      fa_make_map(&tdo, dout, S, H, B, rs, 128) || fa_make_map(&tq64, q, S, H, B, ldq, 64) || fa_make_map(&tk64, k, S, H, B, ldq, 64) ||
+      fa_make_map(&tv64, v, S, H, B, ldq, 64) || fa_make_map(&tdo64, dout, S, H, B, rs, 64)) return 1;
   FaBwdParams p;
   p.out = (const __nv_bfloat16*)out; p.dout = (const __nv_bfloat16*)dout; p.lse = (const float*)lse; p.delta = (float*)delta;
   p.dq = (__nv_bfloat16*)dq; p.dk = (__nv_bfloat16*)dk; p.dv = (__nv_bfloat16*)dv;
-  p.B = B; p.S = S; p.H = H; p.row_stride = rs;
+  p.B = B; p.S = S; p.H = H; p.row_stride = rs; p.ld_dqkv = ldd;
   p.scale = 1.0f / sqrtf((float)D);
   p.scale_log2 = p.scale * fa::kLog2e;
   if (fa_set_attrs()) return 1;

@@ -116,7 +116,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 
   if (warp == 0) {
     // ===================================== TMA producer =====================================
-    if (lane == 0) {
+    // The whole warp walks the loop (warp-uniform control flow keeps operands in uniform registers); one elected lane issues.
+    {
       int stage = 0; uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int m_blk, n_blk;
@@ -130,8 +131,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           mbar_wait(&empty[stage], phase ^ 1);
           uint8_t* sA = smem + stage * Cfg::kStageBytes;
           uint8_t* sB = sA + Cfg::kABytes;
-          mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
           const int k0 = kb * BK;
+          if (elect_one()) {
+          mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
           if (!p.a_mn) {
             tma_load_4d(sA, &tmA, &full[stage], k0, m0, z1, z2);                       // box {64 k, 128 rows}
           } else {
@@ -144,13 +146,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j) tma_load_4d(sB + j * 8192, &tmB, &full[stage], n0 + 64 * j, k0, z1, z2);
           }
+          }
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ===================================== MMA issuer ========================================
-    if (lane == 0) {
+    {
       const uint32_t idesc = make_idesc_bf16(BM, BN, p.a_mn, p.b_mn);
       // per-UMMA_K advance of the descriptor start address, and LBO/SBO, for each operand's layout
       const uint32_t a_step = p.a_mn ? (UMMA_K * 128) : (UMMA_K * 2);
@@ -170,14 +174,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           tc_fence_after();
           const uint32_t sA = smem_u32(smem + stage * Cfg::kStageBytes);
           const uint32_t sB = sA + Cfg::kABytes;
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t adesc = make_smem_desc_sw128(sA + k * a_step, a_lbo, 1024);
-            const uint64_t bdesc = make_smem_desc_sw128(sB + k * b_step, b_lbo, 1024);
-            umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb_lo) || (k != 0));
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t adesc = make_smem_desc_sw128(sA + k * a_step, a_lbo, 1024);
+              const uint64_t bdesc = make_smem_desc_sw128(sB + k * b_step, b_lbo, 1024);
+              umma_f16(d_tmem, adesc, bdesc, idesc, (kb > kb_lo) || (k != 0));
+            }
+            umma_commit(&empty[stage]);                     // smem slot reusable once these MMAs retire
+            if (kb == kb_hi - 1) umma_commit(&tmem_full[as]);
           }
-          umma_commit(&empty[stage]);                       // smem slot reusable once these MMAs retire
-          if (kb == kb_hi - 1) umma_commit(&tmem_full[as]);
+          __syncwarp();
           if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
         }
         if (++as == 2) { as = 0; aphase ^= 1; }

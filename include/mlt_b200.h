@@ -184,12 +184,18 @@ int mlt_layernorm_bwd(const void* dy, const void* h, const void* mean, const voi
                       int H, void* stream);
 int mlt_softmax_rows(void* scores_bf16, long long rows, int L, float scale, void* stream);               /* in place */
 int mlt_softmax_rows_bwd(void* dp_bf16, const void* p_bf16, long long rows, int L, float scale, void* stream);
-/* Fused attention forward on tcgen05 (scores never leave the SM): q, k, v, out [B, S, H*64] bf16, lse [B, H, S] fp32 or NULL.
- * Head dim 64, S a multiple of 128 up to 512, no mask. */
-int mlt_attention_fwd(const void* q, const void* k, const void* v, void* out, void* lse, int B, int S, int H, int D, void* stream);
-/* Its backward: out / lse from the forward, dout the gradient of out, delta a [B, H, S] fp32 scratch; dq, dk, dv bf16. */
-int mlt_attention_bwd(const void* q, const void* k, const void* v, const void* out, const void* dout, const void* lse, void* delta,
-                      void* dq, void* dk, void* dv, int B, int S, int H, int D, void* stream);
+/* Fused attention on tcgen05 (scores never leave the SM).  q, k, v: [B, S, H*64] bf16 with row stride ld_qkv elements
+ * (0 = H*64; 3*H*64 when they are column slices of a packed QKV projection); out [B, S, H*64] bf16; lse [B, H, S] fp32 or
+ * NULL.  Head dim 64, S a multiple of 128 up to 512, no mask. */
+int mlt_attention_fwd(const void* q, const void* k, const void* v, long long ld_qkv, void* out, void* lse, int B, int S, int H,
+                      int D, void* stream);
+/* Its backward: out / lse from the forward, dout the gradient of out, delta a [B, H, S] fp32 scratch; dq, dk, dv bf16 with
+ * row stride ld_dqkv (0 = H*64). */
+int mlt_attention_bwd(const void* q, const void* k, const void* v, long long ld_qkv, const void* out, const void* dout,
+                      const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B, int S, int H, int D,
+                      void* stream);
+/* Analysis hook: device buffer of 8 int64 per CTA that the dQ kernel fills with %globaltimer stamps (NULL clears it). */
+int mlt_attention_set_debug(void* buf);
 int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
                           void* out_bf16, int T, int S, int H, void* stream);
 int mlt_embedding_bwd(const void* ids_i64, const void* dh_bf16, void* dword, long long V, void* dpos, int grads_bf16, int B,

@@ -6,7 +6,7 @@ base config with 2 labels), so state dicts move between the two implementations 
 HF model is the numerical oracle in the tests.  Forward takes ``input_ids [B, S]`` and returns logits.
 
 Hot ops ("BERT-base"): QKV / output / FFN GEMMs on tcgen05 with bias (+GELU, +pre-activation
-for backward) in the epilogue; attention as batched tcgen05 GEMMs + fused row softmax; residual+LayerNorm fused;
+for backward) in the epilogue, Q/K/V as ONE packed projection; fused tcgen05 flash attention; residual+LayerNorm fused;
 embedding gather-sum.  Dropout is identity here (p = 0): the benchmark configures the reference the same way.
 """
 from __future__ import annotations
@@ -64,8 +64,19 @@ class BertSelfAttention(nn.Module):
         self.key = nn.Linear(c.hidden_size, c.hidden_size)
         self.value = nn.Linear(c.hidden_size, c.hidden_size)
         self.heads = c.num_attention_heads
+        # Ask the FusedOptimizer to lay the three projections out back to back: one [3H, H] GEMM operand (and gradient
+        # sink) under the unchanged HuggingFace parameter names.
+        for i, lin in enumerate((self.query, self.key, self.value)):
+            lin.weight._mlt_pack = (("qkv.w", id(self)), i, 3)
+            lin.bias._mlt_pack = (("qkv.b", id(self)), i, 3)
 
     def forward(self, x):
+        from ..ops.gemm import linear_packed, linear_packed_ok
+
+        wpack = getattr(self.query.weight, "_mlt_packed", None)
+        bpack = getattr(self.query.bias, "_mlt_packed", None)
+        if bpack is not None and linear_packed_ok(x, wpack, bpack):
+            return F.attention_packed(linear_packed(x, wpack, bpack), self.heads)
         q = F.linear_act(x, self.query.weight, self.query.bias)
         k = F.linear_act(x, self.key.weight, self.key.bias)
         v = F.linear_act(x, self.value.weight, self.value.bias)

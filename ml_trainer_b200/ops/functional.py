@@ -468,41 +468,98 @@ class _AttentionFn(torch.autograd.Function):
         return dq, dk, dv, None
 
 
-def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False):
-    """Fused tcgen05 attention forward (csrc/attention_tcgen05.cu).  Returns ``out`` or ``(out, lse)``."""
+def _qkv_ld(q, k, v):
+    """Common row stride of q, k, v when they can be handed to the fused kernels without a copy, else None."""
     B, S, HD = q.shape
-    q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
-    out = torch.empty_like(q)
+    ld = q.stride(1)
+    for t in (q, k, v):
+        if t.stride(2) != 1 or t.stride(1) != ld or t.stride(0) != S * ld or t.data_ptr() % 16:
+            return None
+    return ld if ld % 8 == 0 and ld >= HD else None
+
+
+def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False):
+    """Fused tcgen05 attention forward (csrc/attention_tcgen05.cu).  Returns ``out`` or ``(out, lse)``.
+
+    q, k, v may be column slices of one packed ``[B, S, 3*H*d]`` projection (no copy is made)."""
+    B, S, HD = q.shape
+    ld = _qkv_ld(q, k, v)
+    if ld is None:
+        q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
+        ld = HD
+    out = torch.empty((B, S, HD), dtype=q.dtype, device=q.device)
     lse = torch.empty((B, heads, S), dtype=torch.float32, device=q.device) if want_lse else None
-    check(_lib.lib().mlt_attention_fwd(ptr(q), ptr(k), ptr(v), ptr(out), ptr(lse), _c_int(B), _c_int(S), _c_int(heads),
+    check(_lib.lib().mlt_attention_fwd(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(out), ptr(lse), _c_int(B), _c_int(S), _c_int(heads),
                                        _c_int(HD // heads), stream_handle()), "mlt_attention_fwd")
     launches.bump("attention_fwd_tcgen05")
     return (out, lse) if want_lse else out
 
 
+def _attention_bwd(q, k, v, out, lse, do, heads, dq, dk, dv):
+    B, S, HD = q.shape
+    ld = _qkv_ld(q, k, v)
+    ldd = _qkv_ld(dq, dk, dv)
+    assert ld is not None and ldd is not None
+    delta = torch.empty_like(lse)
+    check(_lib.lib().mlt_attention_bwd(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(out), ptr(do), ptr(lse), ptr(delta), ptr(dq), ptr(dk),
+                                       ptr(dv), _c_ll(ldd), _c_int(B), _c_int(S), _c_int(heads), _c_int(HD // heads), stream_handle()),
+          "mlt_attention_bwd")
+    launches.bump("attention_bwd_tcgen05", 3)
+
+
 class _FusedAttentionFn(torch.autograd.Function):
     """Flash attention on tcgen05: forward keeps only the per-row log-sum-exp, backward recomputes P on the tensor cores
-    (csrc/attention_tcgen05.cu: one dQ kernel, one dK/dV kernel, no atomics)."""
+    (csrc/attention_tcgen05.cu: delta, dQ and dK/dV kernels, no atomics)."""
 
     @staticmethod
     def forward(ctx, q, k, v, heads):
+        q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
         out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True)
-        ctx.save_for_backward(q.contiguous(), k.contiguous(), v.contiguous(), out, lse)
+        ctx.save_for_backward(q, k, v, out, lse)
         ctx.heads = heads
         return out
 
     @staticmethod
     def backward(ctx, do):
         q, k, v, out, lse = ctx.saved_tensors
-        B, S, HD = q.shape
-        do = do.contiguous()
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
-        delta = torch.empty_like(lse)
-        check(_lib.lib().mlt_attention_bwd(ptr(q), ptr(k), ptr(v), ptr(out), ptr(do), ptr(lse), ptr(delta), ptr(dq), ptr(dk), ptr(dv),
-                                           _c_int(B), _c_int(S), _c_int(ctx.heads), _c_int(HD // ctx.heads), stream_handle()),
-              "mlt_attention_bwd")
-        launches.bump("attention_bwd_tcgen05", 2)
+        _attention_bwd(q, k, v, out, lse, do.contiguous(), ctx.heads, dq, dk, dv)
         return dq, dk, dv, None
+
+
+class _PackedAttentionFn(torch.autograd.Function):
+    """Same kernels on a packed ``[B, S, 3*H*d]`` QKV projection: q, k, v are read as column slices and dq, dk, dv are
+    written straight into one packed gradient, so neither direction needs a split or a concat."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads):
+        HD = qkv.shape[-1] // 3
+        q, k, v = qkv[..., :HD], qkv[..., HD:2 * HD], qkv[..., 2 * HD:]
+        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True)
+        ctx.save_for_backward(qkv, out, lse)
+        ctx.heads = heads
+        return out
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, out, lse = ctx.saved_tensors
+        HD = qkv.shape[-1] // 3
+        dqkv = torch.empty_like(qkv)
+        _attention_bwd(qkv[..., :HD], qkv[..., HD:2 * HD], qkv[..., 2 * HD:], out, lse, do.contiguous(), ctx.heads,
+                       dqkv[..., :HD], dqkv[..., HD:2 * HD], dqkv[..., 2 * HD:])
+        return dqkv, None
+
+
+def attention_packed(qkv, heads: int):
+    """Self-attention core on a packed projection ``[B, S, 3*H*d]`` (q | k | v along the last dim)."""
+    HD = qkv.shape[-1] // 3
+    q = qkv[..., :HD]
+    if (use_native(qkv) and qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and fused_attention_ok(q, heads)
+            and qkv.data_ptr() % 16 == 0):
+        if torch.is_grad_enabled() and qkv.requires_grad:
+            return _PackedAttentionFn.apply(qkv, heads)
+        return attention_fused_fwd(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads)
+    return attention(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads)
 
 
 def fused_attention_ok(q, heads: int) -> bool:

@@ -119,6 +119,49 @@ class _LinearTCFn(torch.autograd.Function):
         return dx, gw, gb, None, None, None
 
 
+class _LinearTCPackedFn(torch.autograd.Function):
+    """One GEMM for several Linear layers that share their input (the Q, K, V projections): weights, biases and their
+    gradient sinks are single views over adjacent arena spans (``optim.fused.PackedParams``), so forward, dgrad and wgrad
+    are one tcgen05 GEMM each instead of three, and the dgrad needs no gradient accumulation."""
+
+    @staticmethod
+    def forward(ctx, x2, wpack, bpack):
+        w = wpack.data
+        y = gemm(x2, w, False, False, bias=bpack.data if bpack is not None else None)
+        ctx.save_for_backward(x2, w)
+        ctx.packs = (wpack, bpack)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .functional import colsum
+
+        x2, w = ctx.saved_tensors
+        wpack, bpack = ctx.packs
+        dy = dy.contiguous()
+        dx = gemm(dy, w, False, True) if ctx.needs_input_grad[0] else None
+        gemm(dy, x2, True, True, out=wpack.grad)
+        wpack.ready()
+        if bpack is not None:
+            colsum(dy, out=bpack.grad)
+            bpack.ready()
+        return dx, None, None
+
+
+def linear_packed(x, wpack, bpack=None):
+    """``x @ [W0; W1; ...]^T + [b0; b1; ...]`` for parameters packed by the FusedOptimizer; returns ``[..., sum(out_i)]``."""
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, x.shape[-1])
+    y = _LinearTCPackedFn.apply(x2, wpack, bpack)
+    return y.reshape(*lead, wpack.data.shape[0])
+
+
+def linear_packed_ok(x, wpack, bpack) -> bool:
+    return (wpack is not None and x.is_cuda and x.dtype == torch.bfloat16 and wpack.data.dtype == torch.bfloat16
+            and wpack.grad.dtype == torch.bfloat16 and gemm_supported(x.reshape(-1, x.shape[-1]), wpack.data)
+            and (bpack is None or bpack.data.dtype == torch.bfloat16))
+
+
 def linear_act_tc(x, weight, bias=None, act: Optional[str] = None):
     """Tensor-core linear for bf16 activations/weights; anything else goes to the PyTorch statement."""
     from .functional import _has_sink

@@ -41,6 +41,19 @@ def _round_up(x: int, a: int) -> int:
     return (x + a - 1) // a * a
 
 
+class PackedParams:
+    """Several parameters that sit back to back in the arena, seen as one tensor (``data``) with one gradient sink."""
+
+    def __init__(self, data, grad, members):
+        self.data, self.grad, self.members = data, grad, list(members)
+
+    def ready(self):
+        for p in self.members:
+            r = getattr(p, "_mlt_ready", None)
+            if r is not None:
+                r()
+
+
 class FusedOptimizer(torch.optim.Optimizer):
     def __init__(
         self,
@@ -72,8 +85,38 @@ class FusedOptimizer(torch.optim.Optimizer):
         self._build_arena(plist)
 
     # ------------------------------------------------------------------ arena
+    @staticmethod
+    def _apply_packs(order):
+        """Honour ``param._mlt_pack = (key, index, count)``: the members of a complete pack are laid out back to back
+        (in index order) so that ONE tensor view covers all of them - e.g. the Q, K and V projection weights of an
+        attention block become a single [3*H, H] GEMM operand and a single [3*H, H] gradient sink."""
+        groups = {}
+        for p in order:
+            tag = getattr(p, "_mlt_pack", None)
+            if tag is not None:
+                groups.setdefault(tag[0], {})[tag[1]] = p
+        complete = {}
+        for key, members in groups.items():
+            n = next(iter(members.values()))._mlt_pack[2]
+            ps = [members.get(i) for i in range(n)]
+            if any(q is None for q in ps):
+                continue
+            if any(q.numel() % ALIGN or q.shape[1:] != ps[0].shape[1:] or q.dtype != ps[0].dtype for q in ps):
+                continue
+            complete[key] = ps
+        out, seen = [], set()
+        for p in order:
+            if id(p) in seen:
+                continue
+            tag = getattr(p, "_mlt_pack", None)
+            members = complete.get(tag[0]) if tag is not None else None
+            for q in (members or [p]):
+                seen.add(id(q))
+                out.append(q)
+        return out, list(complete.values())
+
     def _build_arena(self, plist):
-        order = list(reversed(plist))           # gradient-ready order
+        order, packs = self._apply_packs(list(reversed(plist)))           # gradient-ready order
         self.params_in_order = order
         self.offsets, self.sizes = [], []
         off = 0
@@ -105,6 +148,11 @@ class FusedOptimizer(torch.optim.Optimizer):
                 p._mlt_grad_sink = self._view(self.grad, i)   # where backward kernels write
                 p._mlt_index = i
                 self.index_of[id(p)] = i
+            for members in packs:
+                i0 = self.index_of[id(members[0])]
+                lo, n = self.offsets[i0], sum(q.numel() for q in members)
+                shape = (sum(q.shape[0] for q in members),) + tuple(members[0].shape[1:])
+                members[0]._mlt_packed = PackedParams(self.model[lo:lo + n].view(shape), self.grad[lo:lo + n].view(shape), members)
 
     def _view(self, flat: torch.Tensor, i: int) -> torch.Tensor:
         o, n = self.offsets[i], self.sizes[i]
