@@ -73,6 +73,21 @@ __device__ __forceinline__ float gelu_bwd(float x) {
   const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
   return cdf + x * pdf;
 }
+// GELU and its derivative from one exponential (GEMM epilogues): erfc via Abramowitz-Stegun 7.1.26 (|error| < 1.5e-7, far
+// below the bf16 the results are rounded to); exp(-z^2/2) is shared between the erfc and the density term of the derivative.
+__device__ __forceinline__ void gelu_both(float z, float& g, float& dg) {
+  const float az = fabsf(z) * 0.70710678118654752f;
+  const float e = __expf(-az * az);                       // exp(-z^2 / 2)
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, az, 1.0f));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float half_erfc = 0.5f * poly * t * e;            // 0.5 * erfc(|z| / sqrt 2)
+  const float cdf = z >= 0.f ? 1.0f - half_erfc : half_erfc;
+  g = z * cdf;
+  dg = fmaf(z * 0.39894228040143268f, e, cdf);
+}
 template <int ACT> __device__ __forceinline__ float act_fwd(float x) {
   if (ACT == ACT_RELU) return fmaxf(x, 0.0f);
   if (ACT == ACT_GELU) return gelu_fwd(x);

@@ -129,12 +129,12 @@ colsum_vec_kernel(const T* __restrict__ x, O* __restrict__ out, float* __restric
   float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (c0 < N) {
     int r = r_lo + warp;
-    for (; r + 24 < r_hi; r += 32) {
-      float a[4][8];
+    for (; r + 56 < r_hi; r += 64) {          // 8 independent 16-byte loads per lane in flight
+      float a[8][8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) ColVec<T>::load(x + (size_t)(r + 8 * u) * ld + c0, a[u]);
+      for (int u = 0; u < 8; ++u) ColVec<T>::load(x + (size_t)(r + 8 * u) * ld + c0, a[u]);
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
+      for (int u = 0; u < 8; ++u)
 #pragma unroll
         for (int j = 0; j < V; ++j) acc[j] += a[u][j];
     }
@@ -221,7 +221,7 @@ extern "C" int mlt_act_backward(const void* dy, const void* saved, void* dz, lon
 extern "C" long long mlt_colsum_scratch_bytes(int M, int N) {
   // sized for the narrowest column tile (64) so either kernel variant fits
   const int tiles = ceil_div(N, 64);
-  return ((long long)tiles * 4 + 255) / 256 * 256 + (long long)(2 * kNumSMs) * N * 4;
+  return ((long long)tiles * 4 + 255) / 256 * 256 + (long long)(4 * kNumSMs) * N * 4;
 }
 
 // out[N] = sum over rows of x[M][N];  x bf16 or fp32, out bf16 or fp32.  scratch: mlt_colsum_scratch_bytes, zeroed once.
@@ -232,7 +232,7 @@ extern "C" int mlt_colsum(const void* x, int x_bf16, void* out, int out_bf16, vo
   const bool vec = (N % V == 0) && (ld % V == 0) && (((uintptr_t)x) % 16 == 0);
   const int tile_w = vec ? 32 * V : 64;
   const int tiles = ceil_div(N, tile_w);
-  int R = (2 * kNumSMs) / tiles;
+  int R = ((vec ? 4 : 2) * kNumSMs) / tiles;
   if (R > ceil_div(M, 64)) R = ceil_div(M, 64);
   if (R < 1) R = 1;
   MLT_REQUIRE(R == 1 || (scratch && scratch_bytes >= mlt_colsum_scratch_bytes(M, N)), "mlt_colsum: scratch too small");

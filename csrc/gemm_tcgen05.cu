@@ -37,7 +37,7 @@ struct GemmParams {
   const void* bias;
   int bias_f32;
   int act;        // Act
-  int aux_mode;   // 0 none | 1 store pre-activation (bf16) to aux | 2 multiply by act'(aux)
+  int aux_mode;   // 0 none | 1 store pre-activation (bf16) to aux | 2 multiply by act'(aux) | 3 store act'(pre) | 4 multiply by aux
   void* aux;
   long long ld_aux;
   int a_mn, b_mn;
@@ -233,36 +233,80 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
 #pragma unroll
             for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __ldg(bp + j);
+          } else if (full_chunk && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
+            const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 raw = __ldg(bp + j);
+              const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
+                v[8 * j + 2 * e] += f.x; v[8 * j + 2 * e + 1] += f.y;
+              }
+            }
           } else {
             const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
 #pragma unroll
             for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __bfloat162float(bp[j]);
           }
         }
-        if (live && row < p.M && p.aux_mode == 1) {          // keep the pre-activation for backward (direct stores)
+        bool act_done = false;
+        if (live && row < p.M && (p.aux_mode == 1 || p.aux_mode == 3)) {
+          // keep for backward, with direct stores: the pre-activation (1) or the activation's derivative there (3)
           __nv_bfloat16* ap = reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
+          float s[32];
+          if (p.aux_mode == 3 && p.act == ACT_GELU) {        // value and derivative share one exponential
+#pragma unroll
+            for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(v[j], g, dg); v[j] = g; s[j] = dg; }
+            act_done = true;
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) s[j] = p.aux_mode == 1 ? v[j] : act_grad_from_pre(p.act, v[j]);
+          }
           if (full_chunk) {
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
               uint4 pk;
-              pk.x = pack_bf16(v[j], v[j + 1]); pk.y = pack_bf16(v[j + 2], v[j + 3]);
-              pk.z = pack_bf16(v[j + 4], v[j + 5]); pk.w = pack_bf16(v[j + 6], v[j + 7]);
+              pk.x = pack_bf16(s[j], s[j + 1]); pk.y = pack_bf16(s[j + 2], s[j + 3]);
+              pk.z = pack_bf16(s[j + 4], s[j + 5]); pk.w = pack_bf16(s[j + 6], s[j + 7]);
               *reinterpret_cast<uint4*>(ap + j) = pk;
             }
           } else {
-            for (int j = 0; j < 32 && nb + j < p.N; ++j) ap[j] = __float2bfloat16_rn(v[j]);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (nb + j < p.N) ap[j] = __float2bfloat16_rn(s[j]);
           }
         }
-        if (p.aux_mode == 2) {                               // dX = (dY W) * act'(z)
+        if (p.aux_mode == 2 || p.aux_mode == 4) {            // dX = (dY W) * act'(z): z (2) or act'(z) itself (4) in aux
           if (live && row < p.M) {
             const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
+            float s[32];
+            if (full_chunk) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (full_chunk || nb + j < p.N) v[j] *= act_grad_from_pre(p.act, __bfloat162float(ap[j]));
+              for (int j = 0; j < 32; j += 8) {
+                const uint4 raw = *reinterpret_cast<const uint4*>(ap + j);
+                const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
+                  s[j + 2 * e] = f.x; s[j + 2 * e + 1] = f.y;
+                }
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) s[j] = nb + j < p.N ? __bfloat162float(ap[j]) : 0.f;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] *= p.aux_mode == 2 ? act_grad_from_pre(p.act, s[j]) : s[j];
           }
-        } else if (p.act != ACT_NONE) {
+        } else if (p.act != ACT_NONE && !act_done) {
+          if (p.act == ACT_GELU) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = act_fwd_rt(p.act, v[j]);
+            for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(v[j], g, dg); v[j] = g; }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = act_fwd_rt(p.act, v[j]);
+          }
         }
         // registers -> swizzled slab: 16-byte chunk index is XORed with (row & 7), the layout SWIZZLE_128B expects
         uint8_t* srow = slab + lane * 128;

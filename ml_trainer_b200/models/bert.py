@@ -131,6 +131,11 @@ class BertLayer(nn.Module):
 
     def forward(self, x):
         a = self.attention(x)
+        i, o = self.intermediate.dense, self.output.dense
+        if a.is_cuda and a.dtype == torch.bfloat16 and F.use_native(a, i.weight):
+            from ..ops.gemm import ffn_tc          # both FFN GEMMs + GELU (and its backward) as one autograd node
+
+            return self.output.LayerNorm(ffn_tc(a, i.weight, i.bias, o.weight, o.bias, "gelu"), residual=a)
         return self.output(self.intermediate(a), a)
 
 

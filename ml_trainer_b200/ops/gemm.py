@@ -119,6 +119,75 @@ class _LinearTCFn(torch.autograd.Function):
         return dx, gw, gb, None, None, None
 
 
+def _wgrad_into(dy, x2, wparam, weight):
+    """dW = dy^T x2, written into the parameter's arena sink when there is one."""
+    from .functional import _deliver, _sink
+
+    wsink = _sink(wparam)
+    dw = gemm(dy, x2, True, True, out=wsink if (wsink is not None and wsink.dtype in (torch.bfloat16, torch.float32)) else None,
+              out_dtype=weight.dtype if weight.dtype == torch.bfloat16 else torch.float32)
+    return _deliver(wparam, dw, wsink)
+
+
+def _bgrad_into(dy, bparam):
+    from .functional import _deliver, _sink, colsum
+
+    bsink = _sink(bparam)
+    return _deliver(bparam, colsum(dy, out=bsink), bsink)
+
+
+class _FFNFn(torch.autograd.Function):
+    """``act(x W1^T + b1) W2^T + b2`` as one autograd node (the transformer MLP block).
+
+    The first GEMM's epilogue applies bias + activation and also stores the activation's derivative act'(z1); the
+    dgrad GEMM of the second layer multiplies by it in ITS epilogue, so the backward of the activation costs no kernel
+    and dz1 is produced directly: 6 tcgen05 GEMMs + 2 column sums per block, no elementwise passes."""
+
+    @staticmethod
+    def forward(ctx, x2, w1, b1, w2, b2, act, params):
+        dact = torch.empty((x2.shape[0], w1.shape[0]), dtype=torch.bfloat16, device=x2.device)
+        f = gemm(x2, w1, False, False, bias=b1, act=act, aux_mode=3, aux=dact)
+        y = gemm(f, w2, False, False, bias=b2)
+        ctx.save_for_backward(x2, w1, w2, f, dact)
+        ctx.params = params
+        ctx.has_bias = (b1 is not None, b2 is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1, w2, f, dact = ctx.saved_tensors
+        w1p, b1p, w2p, b2p = ctx.params
+        dy = dy.contiguous()
+        dz = gemm(dy, w2, False, True, aux_mode=4, aux=dact)             # (dy W2) * act'(z1)
+        gw2 = _wgrad_into(dy, f, w2p, w2)
+        gb2 = _bgrad_into(dy, b2p) if ctx.has_bias[1] else None
+        dx = gemm(dz, w1, False, True) if ctx.needs_input_grad[0] else None
+        gw1 = _wgrad_into(dz, x2, w1p, w1)
+        gb1 = _bgrad_into(dz, b1p) if ctx.has_bias[0] else None
+        return dx, gw1, gb1, gw2, gb2, None, None
+
+
+def ffn_tc(x, w1, b1, w2, b2, act: str = "gelu"):
+    """Transformer MLP block on the tensor cores; falls back to two :func:`linear_act_tc` calls off the fast path."""
+    from .functional import _has_sink
+
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, x.shape[-1])
+    ok = (gemm_supported(x2, w1) and w2.is_cuda and w2.dtype == torch.bfloat16 and w2.stride(1) == 1 and w2.stride(0) % 8 == 0
+          and w1.shape[0] % 8 == 0 and w2.shape[0] % 8 == 0 and act in ("gelu", "relu", "tanh")
+          and all(b is None or b.dtype == torch.bfloat16 for b in (b1, b2)))
+    if not ok:
+        return linear_act_tc(linear_act_tc(x, w1, b1, act), w2, b2)
+    if not torch.is_grad_enabled():
+        return gemm(gemm(x2, w1, False, False, bias=b1, act=act), w2, False, False, bias=b2).reshape(*lead, w2.shape[0])
+    det = lambda t: None if t is None else t.detach()
+    if _has_sink(w1) and _has_sink(w2):
+        y = _FFNFn.apply(x2, det(w1), det(b1), det(w2), det(b2), act, (w1, b1, w2, b2))
+    else:
+        y = _FFNFn.apply(x2, w1, b1, w2, b2, act, (None, None, None, None))
+    return y.reshape(*lead, w2.shape[0])
+
+
 class _LinearTCPackedFn(torch.autograd.Function):
     """One GEMM for several Linear layers that share their input (the Q, K, V projections): weights, biases and their
     gradient sinks are single views over adjacent arena spans (``optim.fused.PackedParams``), so forward, dgrad and wgrad

@@ -140,3 +140,31 @@ def test_colsum(M, N, dtype):
     ref = x.float().sum(0)
     tol = 2e-2 * max(1.0, ref.abs().max().item()) if dtype == torch.bfloat16 else 1e-3 * M ** 0.5
     assert (out.float() - ref).abs().max().item() <= tol
+
+
+@pytest.mark.parametrize("T,H,I,act", [(512, 128, 512, "gelu"), (1000, 256, 1024, "gelu"), (300, 64, 264, "relu")])
+def test_ffn_block_matches_torch(T, H, I, act):
+    """Fused MLP block: activation derivative stored by the first GEMM, applied in the second layer's dgrad epilogue."""
+    from ml_trainer_b200.ops.gemm import ffn_tc
+
+    torch.manual_seed(3)
+    x = (torch.randn(T, H, device=DEV) * 0.5).to(torch.bfloat16).requires_grad_()
+    w1 = (torch.randn(I, H, device=DEV) * H ** -0.5).to(torch.bfloat16).requires_grad_()
+    b1 = (torch.randn(I, device=DEV) * 0.1).to(torch.bfloat16).requires_grad_()
+    w2 = (torch.randn(H, I, device=DEV) * I ** -0.5).to(torch.bfloat16).requires_grad_()
+    b2 = (torch.randn(H, device=DEV) * 0.1).to(torch.bfloat16).requires_grad_()
+    go = torch.randn(T, H, device=DEV).to(torch.bfloat16)
+    y = ffn_tc(x, w1, b1, w2, b2, act)
+    y.backward(go)
+    torch.cuda.synchronize()
+    f32 = [t.detach().float().requires_grad_() for t in (x, w1, b1, w2, b2)]
+    fn = torch.nn.functional.gelu if act == "gelu" else torch.relu
+    yr = torch.nn.functional.linear(fn(torch.nn.functional.linear(f32[0], f32[1], f32[2])), f32[3], f32[4])
+    yr.backward(go.float())
+    assert (y.float() - yr).abs().max().item() < 3e-2 * max(1.0, yr.abs().max().item())
+    for name, got, want in zip(("dx", "dw1", "db1", "dw2", "db2"), (x, w1, b1, w2, b2), f32):
+        rel = (got.grad.float() - want.grad).norm() / (want.grad.norm() + 1e-6)
+        assert rel < 2e-2, (name, rel.item())
+    with torch.no_grad():
+        y2 = ffn_tc(x, w1, b1, w2, b2, act)
+    assert (y2.float() - yr).abs().max().item() < 3e-2 * max(1.0, yr.abs().max().item())
