@@ -22,13 +22,19 @@ def timeit(fn, n=10):
 
 def main():
     rows = []
-    for (N, K, name) in [(768, 768, "qkv/out"), (3072, 768, "ffn1"), (768, 3072, "ffn2")]:
+    for (N, K, name) in [(768, 768, "out"), (2304, 768, "qkv"), (3072, 768, "ffn1"), (768, 3072, "ffn2")]:
         x = torch.randn(T, K, device=DEV).bfloat16()
         w = torch.randn(N, K, device=DEV).bfloat16()
         dy = torch.randn(T, N, device=DEV).bfloat16()
         fl = 2.0 * T * N * K
+        bias = torch.randn(N, device=DEV).bfloat16()
+        aux = torch.empty(T, N, device=DEV, dtype=torch.bfloat16)
+        auxk = torch.randn(T, K, device=DEV).bfloat16()
         for tag, ours, ref in [
             ("fwd  ", lambda: gemm(x, w), lambda: torch.matmul(x, w.t())),
+            ("fwd+bias", lambda: gemm(x, w, bias=bias), lambda: torch.addmm(bias, x, w.t())),
+            ("fwd+gelu+aux", lambda: gemm(x, w, bias=bias, act="gelu", aux_mode=3, aux=aux), None),
+            ("dgrad*aux", lambda: gemm(dy, w, False, True, aux_mode=4, aux=auxk), None),
             ("dgrad", lambda: gemm(dy, w, False, True), lambda: torch.matmul(dy, w)),
             ("wgrad", lambda: gemm(dy, x, True, True), lambda: torch.matmul(dy.t(), x)),
             ("wgrad-nosplit", lambda: gemm(dy, x, True, True, split_k=False), None),
@@ -48,6 +54,7 @@ def main():
     rows.append(("attn", "QK^T ", t1, fl / t1 / 1e6, float("nan"), float("nan")))
     rows.append(("attn", "PV   ", t2, fl / t2 / 1e6, float("nan"), float("nan")))
     rows.append(("attn", "P^TdO", t3, fl / t3 / 1e6, float("nan"), float("nan")))
+    rows = [r for r in rows if not (r[1] in ("fwd+gelu+aux",) and r[0] != "ffn1") and not (r[1] == "dgrad*aux" and r[0] != "ffn2")]
     print("%-8s %-14s %10s %10s %10s %10s" % ("layer", "gemm", "ours us", "TFLOP/s", "cublas us", "TFLOP/s"))
     for r in rows:
         print("%-8s %-14s %10.1f %10.1f %10.1f %10.1f" % r)

@@ -26,8 +26,8 @@ using namespace ptx;
 constexpr int BM = 128;        // tile rows (UMMA M)
 constexpr int BK = 64;         // k-block: 64 bf16 = 128 bytes = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kEpiWarps = 4;
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 8;       // two per TMEM lane quadrant, each takes half of the tile's columns
+constexpr int kGemmThreads = 64 + kEpiWarps * 32;
 
 struct GemmParams {
   int M, N, K;
@@ -47,14 +47,16 @@ struct GemmParams {
   int splits, kb_per_split;      // split-K: the batch index doubles as the K-slice id, partials go to an fp32 workspace
 };
 
-template <int BN>
+// AUX: the epilogue also writes a second bf16 tensor (pre-activation or activation derivative) through its own slabs and
+// TMA stores; those 32 KB come out of the operand ring (3 stages instead of 4 at BN = 256).
+template <int BN, bool AUX>
 struct GemmCfg {
   static constexpr int kABytes = BM * BK * 2;                // 16 KB
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kStages = BN == 256 ? (AUX ? 3 : 4) : (BN == 128 ? 6 : 8);
   static constexpr int kTmemCols = 2 * BN;                   // two accumulator stages (power of two >= 32)
-  static constexpr int kStagingBytes = kEpiWarps * 2 * 4096;   // per epilogue warp: two 32-row x 128-byte slabs for TMA stores
+  static constexpr int kStagingBytes = kEpiWarps * 4096 * (AUX ? 2 : 1);   // per epilogue warp: 32-row x 128-byte slab(s) for TMA stores
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -79,11 +81,12 @@ __device__ __forceinline__ float act_grad_from_pre(int act, float z) {
   }
 }
 
-template <int BN>
+template <int BN, bool AUX>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                         const __grid_constant__ CUtensorMap tmOut, const GemmParams p) {
-  using Cfg = GemmCfg<BN>;
+                         const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmAux,
+                         const GemmParams p) {
+  using Cfg = GemmCfg<BN, AUX>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;                 // 1024-byte aligned (stage sizes are)
@@ -102,7 +105,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     prefetch_tmap(&tmB);
     prefetch_tmap(&tmOut);
     for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], kEpiWarps * 32); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], kEpiWarps); }
     fence_mbar_init();
   }
   if (warp == 1) {
@@ -192,13 +195,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     }
   } else {
     // ===================================== epilogue ===========================================
-    // TMEM -> registers -> (bias / activation) -> 128-byte-swizzled smem slab -> TMA store.  Each warp owns the 32 rows
-    // of its TMEM lane quadrant and two 4 KB slabs (32 rows x 128 bytes = 64 bf16 or 32 fp32 columns), so stores of one
-    // slab overlap the conversion of the next; TMA clips rows >= M and columns >= N.
+    // TMEM -> registers -> (bias / activation) -> 128-byte-swizzled smem slab -> TMA store.  Eight warps: warp w reads
+    // TMEM lane quadrant w % 4 (32 rows) and takes the column half (w - 2) / 4 of the tile, through one 4 KB slab
+    // (32 rows x 128 bytes = 64 bf16 or 32 fp32 columns); TMA clips rows >= M and columns >= N.
     const int q = warp & 3;                                 // TMEM lane quadrant this warp may read
-    uint8_t* my_stage = staging + (warp - 2) * 8192;
+    const int half = (warp - 2) >> 2;
+    uint8_t* slab = staging + (warp - 2) * 4096;
+    uint8_t* aux_slab = staging + (kEpiWarps + warp - 2) * 4096;      // only present (and used) when AUX
     const int chunks_per_slab = p.out_f32 ? 1 : 2;          // a 32-column chunk is 128 B of fp32 or 64 B of bf16
-    uint32_t slab_count = 0;
+    constexpr int kChunks = BN / 32;
+    const int c_lo = BN >= 128 ? half * (kChunks / 2) : 0;
+    const int c_hi = BN >= 128 ? c_lo + kChunks / 2 : (half == 0 ? kChunks : 0);
+    const bool aux_in = p.aux_mode == 2 || p.aux_mode == 4;
     int as = 0; uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
@@ -207,20 +215,32 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int z1 = z % p.nb1, z2 = z / p.nb1;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * BN;
+      // aux operand of the first chunk: requested before the accumulator is ready, then one chunk ahead
+      const __nv_bfloat16* aux_row = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux;
+      uint4 pa[4] = {};
+      auto fetch_aux = [&](int c) {
+        const int nb = n0 + c * 32;
+        if (aux_in && row < p.M && nb + 32 <= p.N) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) pa[j] = *reinterpret_cast<const uint4*>(aux_row + nb + 8 * j);
+        }
+      };
+      if (c_lo < c_hi) fetch_aux(c_lo);
       mbar_wait(&tmem_full[as], aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
+      for (int c = c_lo; c < c_hi; ++c) {
         uint32_t r[32];
         tmem_ld_32x32b_x32(taddr + c * 32, r);
+        uint4 ca[4] = {pa[0], pa[1], pa[2], pa[3]};
+        if (c + 1 < c_hi) fetch_aux(c + 1);
         tmem_ld_wait();
         const int nb = n0 + c * 32;
-        const int within = c % chunks_per_slab;
-        uint8_t* slab = my_stage + (slab_count & 1) * 4096;
+        const int within = (c - c_lo) % chunks_per_slab;
         if (within == 0) {
-          // the store that last read this slab was issued two slabs ago
-          if (lane == 0) tma_store_wait_read<1>();
+          // the bulk store that last read this slab must have drained it
+          if (lane == 0) tma_store_wait_read<0>();
           __syncwarp();
         }
         float v[32];
@@ -252,7 +272,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           }
         }
         bool act_done = false;
-        if (live && row < p.M && (p.aux_mode == 1 || p.aux_mode == 3)) {
+        if ((AUX || (live && row < p.M)) && (p.aux_mode == 1 || p.aux_mode == 3)) {
           // keep for backward, with direct stores: the pre-activation (1) or the activation's derivative there (3)
           __nv_bfloat16* ap = reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
           float s[32];
@@ -264,7 +284,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
             for (int j = 0; j < 32; ++j) s[j] = p.aux_mode == 1 ? v[j] : act_grad_from_pre(p.act, v[j]);
           }
-          if (full_chunk) {
+          if (AUX) {                                         // swizzled slab, stored by TMA together with the output slab
+            uint8_t* arow = aux_slab + lane * 128;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              uint4 pk;
+              pk.x = pack_bf16(s[8 * j], s[8 * j + 1]); pk.y = pack_bf16(s[8 * j + 2], s[8 * j + 3]);
+              pk.z = pack_bf16(s[8 * j + 4], s[8 * j + 5]); pk.w = pack_bf16(s[8 * j + 6], s[8 * j + 7]);
+              *reinterpret_cast<uint4*>(arow + (((within * 4 + j) ^ (lane & 7)) << 4)) = pk;
+            }
+          } else if (full_chunk) {
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
               uint4 pk;
@@ -277,24 +306,22 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
             for (int j = 0; j < 32; ++j) if (nb + j < p.N) ap[j] = __float2bfloat16_rn(s[j]);
           }
         }
-        if (p.aux_mode == 2 || p.aux_mode == 4) {            // dX = (dY W) * act'(z): z (2) or act'(z) itself (4) in aux
+        if (aux_in) {                                        // dX = (dY W) * act'(z): z (2) or act'(z) itself (4) in aux
           if (live && row < p.M) {
-            const __nv_bfloat16* ap = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
             float s[32];
             if (full_chunk) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                const uint4 raw = *reinterpret_cast<const uint4*>(ap + j);
-                const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+              for (int j = 0; j < 4; ++j) {
+                const uint32_t w[4] = {ca[j].x, ca[j].y, ca[j].z, ca[j].w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                   const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
-                  s[j + 2 * e] = f.x; s[j + 2 * e + 1] = f.y;
+                  s[8 * j + 2 * e] = f.x; s[8 * j + 2 * e + 1] = f.y;
                 }
               }
             } else {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) s[j] = nb + j < p.N ? __bfloat162float(ap[j]) : 0.f;
+              for (int j = 0; j < 32; ++j) s[j] = nb + j < p.N ? __bfloat162float(aux_row[nb + j]) : 0.f;
             }
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] *= p.aux_mode == 2 ? act_grad_from_pre(p.act, s[j]) : s[j];
@@ -329,13 +356,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           if (lane == 0) {
             const int col0 = nb - within * 32;
             tma_store_4d(&tmOut, slab, col0, m_blk * BM + q * 32, z1, z2);
+            if (AUX) tma_store_4d(&tmAux, aux_slab, col0, m_blk * BM + q * 32, z1, z2);
             tma_store_commit();
           }
-          ++slab_count;
         }
       }
       tc_fence_before();
-      mbar_arrive(&tmem_empty[as]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[as]);
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
     if (lane == 0) tma_store_wait_all();                     // smem must outlive the last bulk stores
@@ -393,17 +421,19 @@ static int make_tmap(CUtensorMap* out, const void* base, long long inner, long l
   return 0;
 }
 
-template <int BN>
-static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
-  using Cfg = GemmCfg<BN>;
+template <int BN, bool AUX>
+static int launch_gemm_impl(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  using Cfg = GemmCfg<BN, AUX>;
   // output map: rows of 128 bytes (64 bf16 / 32 fp32 columns) x 32 rows per store, batch dims as for the operands
   CUtensorMap tmOut;
   if (make_tmap(&tmOut, p.out, p.N, p.M, p.ldo, p.out_f32 ? 32 : 64, 32, p.nb1, p.ob1, p.nb2, p.ob2, p.out_f32 ? 4 : 2)) return 1;
   p.num_m = ceil_div(p.M, BM);
   p.num_n = ceil_div(p.N, BN);
   p.num_k = ceil_div(p.K, BK);
+  CUtensorMap tmAux = tmOut;
+  if (AUX && make_tmap(&tmAux, p.aux, p.N, p.M, p.ld_aux, 64, 32, p.nb1, 0, p.nb2, 0, 2)) return 1;
   static bool attr_set[64] = {};             // function attributes are per device
-  auto kern = gemm_bf16_tcgen05_kernel<BN>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, AUX>;
   int dev = 0;
   MLT_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
@@ -412,9 +442,18 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParam
   }
   long long tiles = (long long)p.num_m * p.num_n * p.nb1 * p.nb2;      // with split-K, nb1 carries the number of K slices
   int grid = tiles > kNumSMs ? kNumSMs : (int)tiles;
-  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, tmOut, p);
+  kern<<<grid, kGemmThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, tmOut, tmAux, p);
   MLT_LAUNCH_CHECK();
   return 0;
+}
+
+template <int BN>
+static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  // the slab path for a stored aux tensor: bf16 output (so output and aux slabs cover the same 64 columns), one problem
+  const bool aux_slab = BN == 256 && (p.aux_mode == 1 || p.aux_mode == 3) && !p.out_f32 && p.nb1 * p.nb2 == 1 &&
+                        ((uintptr_t)p.aux % 16) == 0 && (p.ld_aux * 2) % 16 == 0;
+  if (BN == 256 && aux_slab) return launch_gemm_impl<256, true>(tmA, tmB, p, st);
+  return launch_gemm_impl<BN, false>(tmA, tmB, p, st);
 }
 
 // out[m][n] = sum_s ws[s][m][n]   (split-K epilogue; fp32 partials -> bf16 or fp32 output with row pitch ldo)
