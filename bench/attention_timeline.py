@@ -22,7 +22,8 @@ torch.cuda.synchronize()
 L.mlt_attention_set_debug(ctypes.c_void_p(0))
 t = buf.view(n, 8).cpu().double()
 t0 = t[:, 0].min()
-names = ["start", "setup_done", "q_landed", "scores0_issued", "scores0_ready", "loop_end", "mma_done", "exit"]
+names = ["start", "setup_done", "q_landed", "scores0_ready", "loop_end", "mma_done", "stores_issued", "exit"]
+t = t[:, [0, 1, 2, 4, 5, 6, 3, 7]]
 print("kernel span us", (t[:, 7].max() - t0).item() / 1e3)
 dt = (t[:, 1:] - t[:, :-1]) / 1e3
 for i in range(7):

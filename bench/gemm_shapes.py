@@ -34,7 +34,9 @@ def main():
             ("fwd  ", lambda: gemm(x, w), lambda: torch.matmul(x, w.t())),
             ("fwd+bias", lambda: gemm(x, w, bias=bias), lambda: torch.addmm(bias, x, w.t())),
             ("fwd+gelu+aux", lambda: gemm(x, w, bias=bias, act="gelu", aux_mode=3, aux=aux), None),
+            ("fwd+gelu+z", lambda: gemm(x, w, bias=bias, act="gelu", aux_mode=1, aux=aux), None),
             ("dgrad*aux", lambda: gemm(dy, w, False, True, aux_mode=4, aux=auxk), None),
+            ("dgrad*gelu'", lambda: gemm(dy, w, False, True, act="gelu", aux_mode=2, aux=auxk), None),
             ("dgrad", lambda: gemm(dy, w, False, True), lambda: torch.matmul(dy, w)),
             ("wgrad", lambda: gemm(dy, x, True, True), lambda: torch.matmul(dy.t(), x)),
             ("wgrad-nosplit", lambda: gemm(dy, x, True, True, split_k=False), None),
@@ -54,7 +56,7 @@ def main():
     rows.append(("attn", "QK^T ", t1, fl / t1 / 1e6, float("nan"), float("nan")))
     rows.append(("attn", "PV   ", t2, fl / t2 / 1e6, float("nan"), float("nan")))
     rows.append(("attn", "P^TdO", t3, fl / t3 / 1e6, float("nan"), float("nan")))
-    rows = [r for r in rows if not (r[1] in ("fwd+gelu+aux",) and r[0] != "ffn1") and not (r[1] == "dgrad*aux" and r[0] != "ffn2")]
+    rows = [r for r in rows if not (r[1] in ("fwd+gelu+aux", "fwd+gelu+z") and r[0] != "ffn1") and not (r[1] in ("dgrad*aux", "dgrad*gelu'") and r[0] != "ffn2")]
     print("%-8s %-14s %10s %10s %10s %10s" % ("layer", "gemm", "ours us", "TFLOP/s", "cublas us", "TFLOP/s"))
     for r in rows:
         print("%-8s %-14s %10.1f %10.1f %10.1f %10.1f" % r)

@@ -413,7 +413,6 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     mbar_wait(q_full, 0);
     if (lane == 0) FA_DBG(2);
     issue_scores(0);
-    if (lane == 0) FA_DBG(3);
     for (int hs = 0; hs < NH; ++hs) {
       if (hs + 1 < NH) issue_scores(hs + 1);            // overlaps the softmax of step hs
       const int st = hs % kDqStages;
@@ -468,6 +467,7 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     if (threadIdx.x == 64) FA_DBG(6);
     tc_fence_after();
     store_out32(p.dq + ((size_t)b * p.S + srow) * p.ld_dqkv + (size_t)h * 64 + hf * 32, tmem + lane_base + kColOut + hf * 32, 1.0f);
+    if (threadIdx.x == 64) FA_DBG(3);
   }
   tc_fence_before();
   __syncthreads();

@@ -276,13 +276,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           // keep for backward, with direct stores: the pre-activation (1) or the activation's derivative there (3)
           __nv_bfloat16* ap = reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
           float s[32];
-          if (p.aux_mode == 3 && p.act == ACT_GELU) {        // value and derivative share one exponential
+          if (p.aux_mode == 1) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) s[j] = v[j];
+          } else if (p.act == ACT_GELU && !p.out_f32) {      // bf16 result: value and derivative from one tanh.approx
 #pragma unroll
             for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(v[j], g, dg); v[j] = g; s[j] = dg; }
             act_done = true;
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) s[j] = p.aux_mode == 1 ? v[j] : act_grad_from_pre(p.act, v[j]);
+            for (int j = 0; j < 32; ++j) s[j] = act_grad_from_pre(p.act, v[j]);
           }
           if (AUX) {                                         // swizzled slab, stored by TMA together with the output slab
             uint8_t* arow = aux_slab + lane * 128;
@@ -323,11 +326,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
 #pragma unroll
               for (int j = 0; j < 32; ++j) s[j] = nb + j < p.N ? __bfloat162float(aux_row[nb + j]) : 0.f;
             }
+            if (p.aux_mode == 4) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= p.aux_mode == 2 ? act_grad_from_pre(p.act, s[j]) : s[j];
+              for (int j = 0; j < 32; ++j) v[j] *= s[j];
+            } else if (p.act == ACT_GELU && !p.out_f32) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(s[j], g, dg); v[j] *= dg; }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] *= act_grad_from_pre(p.act, s[j]);
+            }
           }
         } else if (p.act != ACT_NONE && !act_done) {
-          if (p.act == ACT_GELU) {
+          if (p.act == ACT_GELU && !p.out_f32) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(v[j], g, dg); v[j] = g; }
           } else {

@@ -143,12 +143,15 @@ class _FFNFn(torch.autograd.Function):
     dgrad GEMM of the second layer multiplies by it in ITS epilogue, so the backward of the activation costs no kernel
     and dz1 is produced directly: 6 tcgen05 GEMMs + 2 column sums per block, no elementwise passes."""
 
+    AUX_FWD, AUX_BWD = 3, 4          # store act'(z1) / multiply by it;  (1, 2) = store z1 / multiply by act'(z1)
+
     @staticmethod
     def forward(ctx, x2, w1, b1, w2, b2, act, params):
         dact = torch.empty((x2.shape[0], w1.shape[0]), dtype=torch.bfloat16, device=x2.device)
-        f = gemm(x2, w1, False, False, bias=b1, act=act, aux_mode=3, aux=dact)
+        f = gemm(x2, w1, False, False, bias=b1, act=act, aux_mode=_FFNFn.AUX_FWD, aux=dact)
         y = gemm(f, w2, False, False, bias=b2)
         ctx.save_for_backward(x2, w1, w2, f, dact)
+        ctx.act = act
         ctx.params = params
         ctx.has_bias = (b1 is not None, b2 is not None)
         return y
@@ -158,7 +161,7 @@ class _FFNFn(torch.autograd.Function):
         x2, w1, w2, f, dact = ctx.saved_tensors
         w1p, b1p, w2p, b2p = ctx.params
         dy = dy.contiguous()
-        dz = gemm(dy, w2, False, True, aux_mode=4, aux=dact)             # (dy W2) * act'(z1)
+        dz = gemm(dy, w2, False, True, act=ctx.act, aux_mode=_FFNFn.AUX_BWD, aux=dact)   # (dy W2) * act'(z1)
         gw2 = _wgrad_into(dy, f, w2p, w2)
         gb2 = _bgrad_into(dy, b2p) if ctx.has_bias[1] else None
         dx = gemm(dz, w1, False, True) if ctx.needs_input_grad[0] else None
