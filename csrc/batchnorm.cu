@@ -2,14 +2,19 @@
 // residual add fused into the normalisation pass, and the running-statistics update fused into the reduction.
 //   forward :  stats (per-channel sum / sum of squares, two-level reduction)  ->  apply (+residual, +ReLU)
 //   backward:  reduce (dgamma, dbeta with the ReLU mask applied on the fly)   ->  apply (dx, and the residual gradient)
-// Channel reductions use the column-tile scheme of elementwise.cu: a lane owns 8 channels (16 bytes), warps stride
-// over rows, CTAs of a channel tile combine through scratch partials + a ticket; the last CTA finalises.
-// Bandwidth-bound; roofline = bytes / HBM bandwidth.
+// Bandwidth-bound; roofline = bytes / HBM bandwidth.  Everything is addressed as a flat stream of 16-byte groups (8
+// channels): consecutive threads read consecutive groups whatever C is, and because the grid stride is a multiple of
+// C/8 a thread sees the SAME 8 channels on every iteration - its per-channel constants live in registers and the inner
+// loops are 16-byte loads, a handful of FMAs and 16-byte stores, several iterations in flight.
+// Channel reductions: a CTA covers 256/(C/8) rows per iteration, folds them through shared memory, CTAs of a channel
+// tile combine through fp32 atomics on a scratch accumulator + a ticket; the last CTA finalises.
 #include "common.cuh"
-#include "colreduce.cuh"
 #include "../include/mlt_b200.h"
 
 namespace mlt {
+
+constexpr int kBnThreads = 256;
+constexpr int kBnGroups = 32;         // channel groups (of 8) per CTA column tile: 256 channels, 512-byte row segments
 
 __device__ __forceinline__ void ld8(const __nv_bfloat16* p, float (&v)[8]) {
   const uint4 raw = *reinterpret_cast<const uint4*>(p);
@@ -27,22 +32,87 @@ __device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&v)[8]) {
 }
 template <typename P> __device__ __forceinline__ float ldp(const P* p, int i) { return to_float(p[i]); }
 
-__global__ void __launch_bounds__(256)
+// Two-quantity per-channel reduction over rows.  grid = (column tiles, R row slices).  F(offset_of_group, a[8], b[8])
+// accumulates one 8-channel group of one row.  A CTA folds its rows through shared memory and adds its per-channel
+// partials to acc[2][C] with fp32 atomics (a few hundred thousand per call, spread over 2*C addresses); the last CTA of
+// a tile (ticket) picks the totals up into tot[2][cw * 8] (shared memory), re-zeroes acc and returns true.
+template <typename F>
+__device__ __forceinline__ bool bn_reduce2(F f, float* acc, unsigned int* tickets, int M, int C, float* tot) {
+  const int C8 = C >> 3;
+  const int g_lo = blockIdx.x * kBnGroups;
+  const int cw = min(kBnGroups, C8 - g_lo);            // channel groups in this tile
+  const int rpi = kBnThreads / cw;                     // rows per iteration
+  const int cg = threadIdx.x % cw, rsub = threadIdx.x / cw;
+  const int R = gridDim.y;
+  const int rows_per = ceil_div(M, R);
+  const int r_lo = blockIdx.y * rows_per, r_hi = min(M, r_lo + rows_per);
+  float a[8], b[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a[j] = 0.f; b[j] = 0.f; }
+  if (rsub < rpi) {
+    const size_t col = (size_t)(g_lo + cg) * 8;
+    int r = r_lo + rsub;
+    for (; r + 3 * rpi < r_hi; r += 4 * rpi) {         // four independent rows in flight
+#pragma unroll
+      for (int u = 0; u < 4; ++u) f((size_t)(r + u * rpi) * C + col, a, b);
+    }
+    for (; r < r_hi; r += rpi) f((size_t)r * C + col, a, b);
+  }
+  __shared__ float sh[kBnThreads][17];
+  __shared__ bool is_last;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { sh[threadIdx.x][j] = a[j]; sh[threadIdx.x][8 + j] = b[j]; }
+  __syncthreads();
+  const int nch = cw * 8;
+  for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
+    const int g = ch >> 3, j = ch & 7;
+    float t0 = 0.f, t1 = 0.f;
+    for (int s = 0; s < rpi; ++s) { t0 += sh[s * cw + g][j]; t1 += sh[s * cw + g][8 + j]; }
+    if (R == 1) { tot[ch] = t0; tot[nch + ch] = t1; }
+    else {
+      atomicAdd(acc + g_lo * 8 + ch, t0);
+      atomicAdd(acc + C + g_lo * 8 + ch, t1);
+    }
+  }
+  if (R == 1) { __syncthreads(); return true; }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(&tickets[blockIdx.x], 1u);
+    is_last = tk == (unsigned int)R - 1;
+    if (is_last) tickets[blockIdx.x] = 0u;
+  }
+  __syncthreads();
+  if (!is_last) return false;
+  __threadfence();
+  for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
+    float* p0 = acc + g_lo * 8 + ch;
+    float* p1 = acc + C + g_lo * 8 + ch;
+    tot[ch] = __ldcg(p0); tot[nch + ch] = __ldcg(p1);
+    *p0 = 0.f; *p1 = 0.f;                              // ready for the next call on this stream
+  }
+  __syncthreads();
+  return true;
+}
+
+__global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ mean, float* __restrict__ rstd, float* __restrict__ run_mean,
                 float* __restrict__ run_var, float momentum, float eps, float* __restrict__ partial, unsigned int* __restrict__ tickets,
                 int M, int C) {
-  __shared__ float tot[2][kBnTile];
-  auto f = [&](int r, int c0, float (&a)[8], float (&b)[8]) {
+  __shared__ float tot[2 * kBnGroups * 8];
+  auto f = [&](size_t off, float (&a)[8], float (&b)[8]) {
     float v[8];
-    ld8(x + (size_t)r * C + c0, v);
+    ld8(x + off, v);
 #pragma unroll
     for (int j = 0; j < 8; ++j) { a[j] += v[j]; b[j] = fmaf(v[j], v[j], b[j]); }
   };
-  if (!column_reduce2(f, partial, tickets, M, C, tot)) return;
-  const int c = blockIdx.x * kBnTile + threadIdx.x;
-  if (c < C) {
-    const float m = tot[0][threadIdx.x] / (float)M;
-    const float var = fmaxf(tot[1][threadIdx.x] / (float)M - m * m, 0.f);
+  if (!bn_reduce2(f, partial, tickets, M, C, tot)) return;
+  const int g_lo = blockIdx.x * kBnGroups;
+  const int nch = min(kBnGroups, (C >> 3) - g_lo) * 8;
+  for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
+    const int c = g_lo * 8 + ch;
+    const float m = tot[ch] / (float)M;
+    const float var = fmaxf(tot[nch + ch] / (float)M - m * m, 0.f);
     mean[c] = m;
     rstd[c] = rsqrtf(var + eps);
     if (run_mean != nullptr) {
@@ -53,165 +123,232 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ mean, f
 }
 
 // y = [relu]( (x - mean) * rstd * gamma + beta [+ residual] )
-template <typename P>
-__global__ void __launch_bounds__(256)
+template <typename P, bool RES, bool RELU>
+__global__ void __launch_bounds__(kBnThreads)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd,
                 const P* __restrict__ gamma, const P* __restrict__ beta, const __nv_bfloat16* __restrict__ residual,
-                __nv_bfloat16* __restrict__ y, long long M, int C, int relu) {
-  const int C8 = C / 8;
-  const long long total = M * C8;
-  const long long step = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
-    const int c0 = (int)(i % C8) * 8;
+                __nv_bfloat16* __restrict__ y, long long total, int C8) {
+  const long long step = (long long)gridDim.x * kBnThreads;         // a multiple of C8 (host guarantees it)
+  long long i = (long long)blockIdx.x * kBnThreads + threadIdx.x;
+  const int c0 = (int)(i % C8) * 8;
+  float sc[8], sf[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    sc[j] = rstd[c0 + j] * ldp(gamma, c0 + j);
+    sf[j] = fmaf(-mean[c0 + j], sc[j], ldp(beta, c0 + j));
+  }
+  auto one = [&](long long e) {
     float v[8], r[8];
-    ld8(x + i * 8, v);
-    if (residual != nullptr) ld8(residual + i * 8, r);
+    ld8(x + e * 8, v);
+    if (RES) ld8(residual + e * 8, r);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float o = (v[j] - mean[c0 + j]) * rstd[c0 + j] * ldp(gamma, c0 + j) + ldp(beta, c0 + j);
-      if (residual != nullptr) o += r[j];
-      v[j] = relu ? fmaxf(o, 0.f) : o;
+      float o = fmaf(v[j], sc[j], sf[j]);
+      if (RES) o += r[j];
+      v[j] = RELU ? fmaxf(o, 0.f) : o;
     }
-    st8(y + i * 8, v);
+    st8(y + e * 8, v);
+  };
+  for (; i + 3 * step < total; i += 4 * step) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) one(i + u * step);
   }
+  for (; i < total; i += step) one(i);
 }
 
 // dgamma[c] = sum dz * xhat, dbeta[c] = sum dz, with dz = dy * (y > 0) when the forward had a ReLU
-template <typename G>
-__global__ void __launch_bounds__(256)
+template <typename G, bool RELU>
+__global__ void __launch_bounds__(kBnThreads)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
                      const float* __restrict__ mean, const float* __restrict__ rstd, G* __restrict__ dgamma, G* __restrict__ dbeta,
-                     float* __restrict__ sums, float* __restrict__ partial, unsigned int* __restrict__ tickets, int M, int C, int relu) {
-  __shared__ float tot[2][kBnTile];
-  auto f = [&](int r, int c0, float (&a)[8], float (&b)[8]) {
+                     float* __restrict__ sums, float* __restrict__ partial, unsigned int* __restrict__ tickets, int M, int C) {
+  __shared__ float tot[2 * kBnGroups * 8];
+  const int g_lo = blockIdx.x * kBnGroups;
+  const int cw = min(kBnGroups, (C >> 3) - g_lo);
+  const int c0 = (g_lo + (int)(threadIdx.x % cw)) * 8;
+  float mu[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) mu[j] = mean[c0 + j];
+  auto f = [&](size_t off, float (&a)[8], float (&b)[8]) {
     float g[8], v[8], o[8];
-    ld8(dy + (size_t)r * C + c0, g);
-    ld8(x + (size_t)r * C + c0, v);
-    if (relu) ld8(y + (size_t)r * C + c0, o);
+    ld8(dy + off, g);
+    ld8(x + off, v);
+    if (RELU) ld8(y + off, o);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float dz = (relu && !(o[j] > 0.f)) ? 0.f : g[j];
-      a[j] = fmaf(dz, (v[j] - mean[c0 + j]) * rstd[c0 + j], a[j]);
+      const float dz = (RELU && !(o[j] > 0.f)) ? 0.f : g[j];
+      a[j] = fmaf(dz, v[j] - mu[j], a[j]);          // sum dz (x - mean); the 1/std factor is applied once at the end
       b[j] += dz;
     }
   };
-  if (!column_reduce2(f, partial, tickets, M, C, tot)) return;
-  const int c = blockIdx.x * kBnTile + threadIdx.x;
-  if (c < C) {
-    dgamma[c] = from_float<G>(tot[0][threadIdx.x]);
-    dbeta[c] = from_float<G>(tot[1][threadIdx.x]);
-    sums[c] = tot[0][threadIdx.x];            // fp32 copies for the apply pass
-    sums[C + c] = tot[1][threadIdx.x];
+  if (!bn_reduce2(f, partial, tickets, M, C, tot)) return;
+  const int nch = cw * 8;
+  for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
+    const int c = g_lo * 8 + ch;
+    const float dg = tot[ch] * rstd[c], db = tot[nch + ch];
+    dgamma[c] = from_float<G>(dg);
+    dbeta[c] = from_float<G>(db);
+    sums[c] = dg;                                   // fp32 copies for the apply pass
+    sums[C + c] = db;
   }
 }
 
 // dx = gamma * rstd * (dz - dbeta/M - xhat * dgamma/M);  dres = dz (gradient of the fused residual input)
-template <typename P>
-__global__ void __launch_bounds__(256)
+template <typename P, bool RES, bool RELU>
+__global__ void __launch_bounds__(kBnThreads)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
                     const float* __restrict__ mean, const float* __restrict__ rstd, const P* __restrict__ gamma,
-                    const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, long long M,
-                    int C, int relu) {
-  const int C8 = C / 8;
-  const long long total = M * C8;
-  const long long step = (long long)gridDim.x * blockDim.x;
-  const float inv_M = 1.0f / (float)M;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
-    const int c0 = (int)(i % C8) * 8;
+                    const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, long long total,
+                    int C8, float inv_M) {
+  const long long step = (long long)gridDim.x * kBnThreads;
+  long long i = (long long)blockIdx.x * kBnThreads + threadIdx.x;
+  const int c0 = (int)(i % C8) * 8;
+  const int C = C8 * 8;
+  // dx = A dz + B (x - mean) + K   with A = gamma rstd, B = -A rstd dgamma / M, K = -A dbeta / M
+  float A[8], Bc[8], K[8], mu[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float rs = rstd[c0 + j];
+    A[j] = ldp(gamma, c0 + j) * rs;
+    Bc[j] = -A[j] * rs * sums[c0 + j] * inv_M;
+    K[j] = -A[j] * sums[C + c0 + j] * inv_M;
+    mu[j] = mean[c0 + j];
+  }
+  auto one = [&](long long e) {
     float g[8], v[8], o[8], d[8];
-    ld8(dy + i * 8, g);
-    ld8(x + i * 8, v);
-    if (relu) ld8(y + i * 8, o);
+    ld8(dy + e * 8, g);
+    ld8(x + e * 8, v);
+    if (RELU) ld8(y + e * 8, o);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float dz = (relu && !(o[j] > 0.f)) ? 0.f : g[j];
-      const float xh = (v[j] - mean[c0 + j]) * rstd[c0 + j];
-      d[j] = ldp(gamma, c0 + j) * rstd[c0 + j] * (dz - sums[C + c0 + j] * inv_M - xh * sums[c0 + j] * inv_M);
+      const float dz = (RELU && !(o[j] > 0.f)) ? 0.f : g[j];
+      d[j] = fmaf(A[j], dz, fmaf(Bc[j], v[j] - mu[j], K[j]));
       g[j] = dz;
     }
-    st8(dx + i * 8, d);
-    if (dres != nullptr) st8(dres + i * 8, g);
+    st8(dx + e * 8, d);
+    if (RES) st8(dres + e * 8, g);
+  };
+  for (; i + step < total; i += 2 * step) {
+    one(i);
+    one(i + step);
   }
+  for (; i < total; i += step) one(i);
 }
 
+static bool bn_shape_ok(int C) { return C > 0 && C % 8 == 0 && C <= 16384 && C / 8 <= 64 * kBnGroups; }
+static long long gcd_ll(long long a, long long b) { return b == 0 ? a : gcd_ll(b, a % b); }
 static int bn_rows_split(int M, int C) {
-  const int tiles = ceil_div(C, kBnTile);
+  const int C8 = C / 8;
+  const int tiles = ceil_div(C8, kBnGroups);
+  const int rpi = kBnThreads / (C8 < kBnGroups ? C8 : kBnGroups);
   int R = (4 * kNumSMs) / tiles;
-  if (R > ceil_div(M, 64)) R = ceil_div(M, 64);
+  const int cap = ceil_div(M, rpi * 8);               // at least 8 iterations per CTA
+  if (R > cap) R = cap;
   return R < 1 ? 1 : R;
 }
-static int bn_grid(long long items) {
-  long long b = ceil_div64(items, 256);
-  const long long cap = (long long)kNumSMs * 16;
-  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+// Grid for the elementwise passes: the stride (grid * 256) must be a multiple of C/8 so channels are loop-invariant.
+static int bn_grid(long long items, int C8) {
+  long long b = ceil_div64(items, kBnThreads);
+  const long long cap = (long long)kNumSMs * 8;
+  if (b > cap) b = cap;
+  const long long m = C8 / gcd_ll(C8, kBnThreads);       // grid * 256 must be a multiple of C8
+  b = (b + m - 1) / m * m;
+  return (int)(b < 1 ? m : b);
 }
 
 }  // namespace mlt
 
 using namespace mlt;
 
-// scratch: [tickets 256-byte aligned][partials R*2*C floats][sums 2*C floats]
+// scratch (zeroed once by the caller, shared by layers of any width): [tickets 256 B][accumulators, fixed 128 KB window]
+// [sums 2*C floats].  Tickets and accumulators are left zero by every call; sums are plain outputs and sit behind the
+// fixed window so a narrow layer's sums can never land where a wide layer accumulates.
+constexpr int kBnMaxC = 16384;
+constexpr long long kBnAccBytes = 2LL * kBnMaxC * 4;
 extern "C" long long mlt_bn_scratch_bytes(int M, int C) {
-  return ((long long)ceil_div(C, kBnTile) * 4 + 255) / 256 * 256 + ((long long)bn_rows_split(M, C) * 2 * C + 2 * C) * 4;
+  (void)M;
+  return 256 + kBnAccBytes + 2LL * C * 4;
 }
 
 static void bn_carve(void* scratch, int M, int C, unsigned int** tickets, float** partial, float** sums) {
+  (void)M; (void)C;
   *tickets = (unsigned int*)scratch;
-  *partial = (float*)((char*)scratch + ((long long)ceil_div(C, kBnTile) * 4 + 255) / 256 * 256);
-  *sums = *partial + (size_t)bn_rows_split(M, C) * 2 * C;
+  *partial = (float*)((char*)scratch + 256);
+  *sums = (float*)((char*)scratch + 256 + kBnAccBytes);
 }
 
 extern "C" int mlt_bn_stats(const void* x, void* mean, void* rstd, void* run_mean, void* run_var, float momentum, float eps,
                             void* scratch, long long scratch_bytes, int M, int C, void* stream) {
-  MLT_REQUIRE(C % 8 == 0 && M > 0, "mlt_bn_stats: channels (%d) must be a multiple of 8", C);
+  MLT_REQUIRE(M > 0 && bn_shape_ok(C), "mlt_bn_stats: channels (%d) must be a multiple of 8", C);
   MLT_REQUIRE(scratch && scratch_bytes >= mlt_bn_scratch_bytes(M, C), "mlt_bn_stats: scratch too small");
   unsigned int* tk; float *pa, *su;
   bn_carve(scratch, M, C, &tk, &pa, &su);
-  dim3 grid(ceil_div(C, kBnTile), bn_rows_split(M, C));
-  bn_stats_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (float*)mean, (float*)rstd, (float*)run_mean,
-                                                         (float*)run_var, momentum, eps, pa, tk, M, C);
+  dim3 grid(ceil_div(C / 8, kBnGroups), bn_rows_split(M, C));
+  bn_stats_kernel<<<grid, kBnThreads, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (float*)mean, (float*)rstd, (float*)run_mean,
+                                                                (float*)run_var, momentum, eps, pa, tk, M, C);
   MLT_LAUNCH_CHECK();
   return 0;
 }
 
+template <typename P>
+static void bn_apply_launch(int g, cudaStream_t st, const void* x, const void* mean, const void* rstd, const void* gamma,
+                            const void* beta, const void* residual, void* y, long long total, int C8, int relu) {
+#define BN_AP(RES, RELU)                                                                                                      \
+  bn_apply_kernel<P, RES, RELU><<<g, kBnThreads, 0, st>>>((const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd,        \
+      (const P*)gamma, (const P*)beta, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, total, C8)
+  if (residual) { if (relu) BN_AP(true, true); else BN_AP(true, false); }
+  else { if (relu) BN_AP(false, true); else BN_AP(false, false); }
+#undef BN_AP
+}
+
 extern "C" int mlt_bn_apply(const void* x, const void* mean, const void* rstd, const void* gamma, const void* beta, int params_bf16,
                             const void* residual, void* y, long long M, int C, int relu, void* stream) {
-  MLT_REQUIRE(C % 8 == 0, "mlt_bn_apply: channels must be a multiple of 8");
+  MLT_REQUIRE(bn_shape_ok(C), "mlt_bn_apply: channels (%d) must be a multiple of 8", C);
   cudaStream_t st = (cudaStream_t)stream;
-  const int g = bn_grid(M * (C / 8));
-  if (params_bf16)
-    bn_apply_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd,
-        (const __nv_bfloat16*)gamma, (const __nv_bfloat16*)beta, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, M, C, relu);
-  else
-    bn_apply_kernel<float><<<g, 256, 0, st>>>((const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd, (const float*)gamma,
-                                              (const float*)beta, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, M, C, relu);
+  const int C8 = C / 8;
+  const long long total = M * C8;
+  const int g = bn_grid(total, C8);
+  if (params_bf16) bn_apply_launch<__nv_bfloat16>(g, st, x, mean, rstd, gamma, beta, residual, y, total, C8, relu);
+  else bn_apply_launch<float>(g, st, x, mean, rstd, gamma, beta, residual, y, total, C8, relu);
   MLT_LAUNCH_CHECK();
   return 0;
+}
+
+template <typename P>
+static void bn_bwd_apply_launch(int g, cudaStream_t st, const void* dy, const void* y, const void* x, const void* mean,
+                                const void* rstd, const void* gamma, const float* su, void* dx, void* dres, long long total, int C8,
+                                float inv_M, int relu) {
+#define BN_BA(RES, RELU)                                                                                                      \
+  bn_bwd_apply_kernel<P, RES, RELU><<<g, kBnThreads, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,                 \
+      (const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd, (const P*)gamma, su, (__nv_bfloat16*)dx,                 \
+      (__nv_bfloat16*)dres, total, C8, inv_M)
+  if (dres) { if (relu) BN_BA(true, true); else BN_BA(true, false); }
+  else { if (relu) BN_BA(false, true); else BN_BA(false, false); }
+#undef BN_BA
 }
 
 extern "C" int mlt_bn_bwd(const void* dy, const void* y, const void* x, const void* mean, const void* rstd, const void* gamma,
                           int params_bf16, void* dx, void* dres, void* dgamma, void* dbeta, int grads_bf16, void* scratch,
                           long long scratch_bytes, int M, int C, int relu, void* stream) {
-  MLT_REQUIRE(C % 8 == 0 && M > 0, "mlt_bn_bwd: channels must be a multiple of 8");
+  MLT_REQUIRE(M > 0 && bn_shape_ok(C), "mlt_bn_bwd: channels (%d) must be a multiple of 8", C);
   MLT_REQUIRE(scratch && scratch_bytes >= mlt_bn_scratch_bytes(M, C), "mlt_bn_bwd: scratch too small");
   unsigned int* tk; float *pa, *su;
   bn_carve(scratch, M, C, &tk, &pa, &su);
   cudaStream_t st = (cudaStream_t)stream;
-  dim3 grid(ceil_div(C, kBnTile), bn_rows_split(M, C));
-  if (grads_bf16)
-    bn_bwd_reduce_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x,
-        (const float*)mean, (const float*)rstd, (__nv_bfloat16*)dgamma, (__nv_bfloat16*)dbeta, su, pa, tk, M, C, relu);
-  else
-    bn_bwd_reduce_kernel<float><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x,
-        (const float*)mean, (const float*)rstd, (float*)dgamma, (float*)dbeta, su, pa, tk, M, C, relu);
+  dim3 grid(ceil_div(C / 8, kBnGroups), bn_rows_split(M, C));
+#define BN_RD(G, RELU)                                                                                                        \
+  bn_bwd_reduce_kernel<G, RELU><<<grid, kBnThreads, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,                  \
+      (const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd, (G*)dgamma, (G*)dbeta, su, pa, tk, M, C)
+  if (grads_bf16) { if (relu) BN_RD(__nv_bfloat16, true); else BN_RD(__nv_bfloat16, false); }
+  else { if (relu) BN_RD(float, true); else BN_RD(float, false); }
+#undef BN_RD
   MLT_LAUNCH_CHECK();
-  const int g = bn_grid((long long)M * (C / 8));
-  if (params_bf16)
-    bn_bwd_apply_kernel<__nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x,
-        (const float*)mean, (const float*)rstd, (const __nv_bfloat16*)gamma, su, (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, M, C, relu);
-  else
-    bn_bwd_apply_kernel<float><<<g, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x,
-        (const float*)mean, (const float*)rstd, (const float*)gamma, su, (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, M, C, relu);
+  const int C8 = C / 8;
+  const long long total = (long long)M * C8;
+  const int g = bn_grid(total, C8);
+  const float inv_M = 1.0f / (float)M;
+  if (params_bf16) bn_bwd_apply_launch<__nv_bfloat16>(g, st, dy, y, x, mean, rstd, gamma, su, dx, dres, total, C8, inv_M, relu);
+  else bn_bwd_apply_launch<float>(g, st, dy, y, x, mean, rstd, gamma, su, dx, dres, total, C8, inv_M, relu);
   MLT_LAUNCH_CHECK();
   return 0;
 }
