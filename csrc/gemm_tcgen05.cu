@@ -15,6 +15,7 @@
 // Replaces the cuBLAS calls behind reference src/model.py:21-23 (fc layers) and every BERT / ResNet-FC GEMM.
 #include "common.cuh"
 #include "ptx.cuh"
+#include "im2col_tma.h"
 #include "../include/mlt_b200.h"
 #include <mutex>
 #include <unordered_map>
@@ -45,6 +46,10 @@ struct GemmParams {
   int nb1, nb2;                  // batch = nb1 * nb2 independent problems (attention: heads x samples)
   long long ob1, ob2;            // output batch strides (elements)
   int splits, kb_per_split;      // split-K: the batch index doubles as the K-slice id, partials go to an fp32 workspace
+  // implicit-GEMM convolution: one operand is the patch matrix of an NHWC tensor, read through a TMA im2col map.
+  //   1: A = patches [pixels x KH*KW*C], K-major (forward)      2: B = patches as the MN-major operand (weight gradient)
+  int im2col;
+  int cv_OW, cv_OH, cv_stride, cv_pad, cv_KW, cv_taps, cv_C;
 };
 
 // AUX: the epilogue also writes a second bf16 tensor (pre-activation or activation derivative) through its own slabs and
@@ -137,13 +142,35 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           const int k0 = kb * BK;
           if (elect_one()) {
           mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
-          if (!p.a_mn) {
+          if (p.im2col == 1) {
+            // k-block kb = (filter tap, 64-channel block); the 128 rows are consecutive output pixels starting at m0
+            const int cblocks = p.cv_C >> 6;
+            const int tap = kb / cblocks, c0 = (kb - tap * cblocks) << 6;
+            const int fr = tap / p.cv_KW, fs = tap - fr * p.cv_KW;
+            const int q0 = m0 % p.cv_OW, t = m0 / p.cv_OW;
+            const int p0 = t % p.cv_OH, img = t / p.cv_OH;
+            tma_load_im2col_4d(sA, &tmA, &full[stage], c0, q0 * p.cv_stride - p.cv_pad, p0 * p.cv_stride - p.cv_pad, img, fs, fr);
+          } else if (!p.a_mn) {
             tma_load_4d(sA, &tmA, &full[stage], k0, m0, z1, z2);                       // box {64 k, 128 rows}
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j) tma_load_4d(sA + j * 8192, &tmA, &full[stage], m0 + 64 * j, k0, z1, z2);   // box {64 rows, 64 k}
           }
-          if (!p.b_mn) {
+          if (p.im2col == 2) {
+            // reduction index = output pixel (64 per k-block), N index = patch column = tap * C + channel
+            const int q0 = k0 % p.cv_OW, t = k0 / p.cv_OW;
+            const int p0 = t % p.cv_OH, img = t / p.cv_OH;
+            const int w0 = q0 * p.cv_stride - p.cv_pad, h0 = p0 * p.cv_stride - p.cv_pad;
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) {
+              const int col = n0 + 64 * j;
+              int tap = col / p.cv_C;
+              const int c0 = col - tap * p.cv_C;
+              tap = min(tap, p.cv_taps - 1);                 // columns >= N: any valid tap, the store clips them
+              const int fr = tap / p.cv_KW, fs = tap - fr * p.cv_KW;
+              tma_load_im2col_4d(sB + j * 8192, &tmB, &full[stage], c0, w0, h0, img, fs, fr);
+            }
+          } else if (!p.b_mn) {
             tma_load_4d(sB, &tmB, &full[stage], k0, n0, z1, z2);                       // box {64 k, BN rows}
           } else {
 #pragma unroll
@@ -528,6 +555,7 @@ extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   p.a_mn = a_mn; p.b_mn = b_mn;
   p.nb1 = p.nb2 = 1; p.ob1 = p.ob2 = 0;
   p.splits = 1; p.kb_per_split = 0;
+  p.im2col = 0;
   cudaStream_t st = (cudaStream_t)stream;
   // split-K: weight-gradient shapes (few output tiles, very long K) would otherwise occupy a handful of SMs
   const int tiles = ceil_div(M, BM) * ceil_div(N, BN), num_k = ceil_div(K, BK);
@@ -580,7 +608,86 @@ extern "C" int mlt_gemm_bf16_batched(const void* A, long long lda, long long a_s
   p.a_mn = a_mn; p.b_mn = b_mn;
   p.nb1 = nb1; p.nb2 = nb2; p.ob1 = o_s1; p.ob2 = o_s2;
   p.splits = 1; p.kb_per_split = 0;
+  p.im2col = 0;
   cudaStream_t st = (cudaStream_t)stream;
+  if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
+  if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
+  return launch_gemm<64>(tmA, tmB, p, st);
+}
+
+// ---- implicit-GEMM convolution (NHWC bf16, Cin a multiple of 64) -------------------------------------------------
+static void conv_params(GemmParams& p, int mode, int H, int W, int C, int KH, int KW, int stride, int pad) {
+  p.im2col = mode;
+  p.cv_OH = (H + 2 * pad - KH) / stride + 1;
+  p.cv_OW = (W + 2 * pad - KW) / stride + 1;
+  p.cv_stride = stride; p.cv_pad = pad; p.cv_KW = KW; p.cv_taps = KH * KW; p.cv_C = C;
+}
+
+// y[B*OH*OW, Co] = patches(x) * w2^T, the patch matrix never materialised: the A tiles come straight out of x through a
+// TMA im2col map (one load per filter tap and 64-channel block).  w2: [Co, KH*KW*C] with row pitch ldw.
+extern "C" int mlt_conv_fwd_implicit(const void* x, int B, int H, int W, int C, const void* w2, long long ldw, int Co, int KH, int KW,
+                                     int stride, int pad, void* y, long long ldy, void* stream) {
+  MLT_REQUIRE(C % 64 == 0 && C > 0, "mlt_conv_fwd_implicit: Cin (%d) must be a multiple of 64", C);
+  GemmParams p;
+  conv_params(p, 1, H, W, C, KH, KW, stride, pad);
+  const long long M = (long long)B * p.cv_OH * p.cv_OW;
+  MLT_REQUIRE(M > 0 && M < (1LL << 31), "mlt_conv_fwd_implicit: bad output size");
+  const int K = KH * KW * C, N = Co;
+  int BN = (N >= 512 || (N % 256 == 0)) ? 256 : (N > 64 ? 128 : 64);
+  CUtensorMap tmA, tmB;
+  if (make_im2col_tmap(&tmA, x, B, H, W, C, KH, KW, stride, pad, 64, BM)) return 1;
+  if (make_tmap(&tmB, w2, K, N, ldw, BK, BN)) return 1;
+  p.M = (int)M; p.N = N; p.K = K;
+  p.out = y; p.ldo = ldy; p.out_f32 = 0;
+  p.bias = nullptr; p.bias_f32 = 0; p.act = ACT_NONE; p.aux_mode = 0; p.aux = nullptr; p.ld_aux = 0;
+  p.a_mn = 0; p.b_mn = 0;
+  p.nb1 = p.nb2 = 1; p.ob1 = p.ob2 = 0; p.splits = 1; p.kb_per_split = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
+  if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
+  return launch_gemm<64>(tmA, tmB, p, st);
+}
+
+// dW[Co, KH*KW*C] = dy^T * patches(x): dy [pixels, Co] is the MN-major A operand, the patches are the MN-major B operand
+// read through a TMA im2col map (64 pixels x 64 channels per load).  Split-K over the pixels as for any weight gradient.
+extern "C" int mlt_conv_wgrad_implicit(const void* dy, long long lddy, const void* x, int B, int H, int W, int C, int Co, int KH, int KW,
+                                       int stride, int pad, void* dw, long long lddw, int out_f32, void* splitk_ws,
+                                       long long splitk_ws_bytes, void* stream) {
+  MLT_REQUIRE(C % 64 == 0 && C > 0, "mlt_conv_wgrad_implicit: Cin (%d) must be a multiple of 64", C);
+  GemmParams p;
+  conv_params(p, 2, H, W, C, KH, KW, stride, pad);
+  const long long pixels = (long long)B * p.cv_OH * p.cv_OW;
+  MLT_REQUIRE(pixels > 0 && pixels < (1LL << 31), "mlt_conv_wgrad_implicit: bad output size");
+  const int M = Co, N = KH * KW * C, K = (int)pixels;
+  int BN = (N >= 512 || (N % 256 == 0)) ? 256 : (N > 64 ? 128 : 64);
+  CUtensorMap tmA, tmB;
+  if (make_tmap(&tmA, dy, M, K, lddy, 64, BK)) return 1;
+  if (make_im2col_tmap(&tmB, x, B, H, W, C, KH, KW, stride, pad, 64, 64)) return 1;
+  p.M = M; p.N = N; p.K = K;
+  p.out = dw; p.ldo = lddw; p.out_f32 = out_f32;
+  p.bias = nullptr; p.bias_f32 = 0; p.act = ACT_NONE; p.aux_mode = 0; p.aux = nullptr; p.ld_aux = 0;
+  p.a_mn = 1; p.b_mn = 1;
+  p.nb1 = p.nb2 = 1; p.ob1 = p.ob2 = 0; p.splits = 1; p.kb_per_split = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int tiles = ceil_div(M, BM) * ceil_div(N, BN), num_k = ceil_div(K, BK);
+  int splits = 1;
+  if (splitk_ws != nullptr && tiles * 2 <= kNumSMs && num_k >= 8) {
+    splits = kNumSMs / tiles;
+    if (splits > 16) splits = 16;
+    if (splits > num_k / 4) splits = num_k / 4;
+    if ((long long)splits * M * N * 4 > splitk_ws_bytes) splits = (int)(splitk_ws_bytes / ((long long)M * N * 4));
+  }
+  if (splits > 1) {
+    const int kbps = ceil_div(num_k, splits);
+    splits = ceil_div(num_k, kbps);
+    GemmParams q = p;
+    q.out = splitk_ws; q.ldo = N; q.out_f32 = 1;
+    q.nb1 = splits; q.nb2 = 1; q.ob1 = (long long)M * N; q.ob2 = 0;
+    q.splits = splits; q.kb_per_split = kbps;
+    int rc = BN == 256 ? launch_gemm<256>(tmA, tmB, q, st) : (BN == 128 ? launch_gemm<128>(tmA, tmB, q, st) : launch_gemm<64>(tmA, tmB, q, st));
+    if (rc) return rc;
+    return launch_splitk_reduce((const float*)splitk_ws, dw, lddw, out_f32, M, N, splits, st);
+  }
   if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
   if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
   return launch_gemm<64>(tmA, tmB, p, st);

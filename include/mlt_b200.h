@@ -196,6 +196,17 @@ int mlt_attention_bwd(const void* q, const void* k, const void* v, long long ld_
                       void* stream);
 /* Analysis hook: device buffer of 8 int64 per CTA that the dQ kernel fills with %globaltimer stamps (NULL clears it). */
 int mlt_attention_set_debug(void* buf);
+/* Implicit-GEMM convolution on tcgen05 for NHWC bf16 tensors with Cin a multiple of 64: the patch matrix is never written,
+ * operand tiles are gathered by TMA im2col loads.  w2 / dw: [Co, KH*KW*Cin]. */
+int mlt_conv_fwd_implicit(const void* x, int B, int H, int W, int C, const void* w2, long long ldw, int Co, int KH, int KW, int stride,
+                          int pad, void* y, long long ldy, void* stream);
+int mlt_conv_wgrad_implicit(const void* dy, long long lddy, const void* x, int B, int H, int W, int C, int Co, int KH, int KW,
+                            int stride, int pad, void* dw, long long lddw, int out_f32, void* splitk_ws, long long splitk_ws_bytes,
+                            void* stream);
+/* Test hook for the TMA im2col path: the [pixels x 64] patch tile of output pixels m0.., filter tap (r, s), channels c0..c0+63 of
+ * an NHWC bf16 tensor, loaded with one cp.async.bulk.tensor...im2col and written back un-swizzled. */
+int mlt_im2col_probe(const void* x, int B, int H, int W, int C, int KH, int KW, int stride, int pad, long long m0, int r, int s, int c0,
+                     int pixels, void* out, void* stream);
 int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
                           void* out_bf16, int T, int S, int H, void* stream);
 int mlt_embedding_bwd(const void* ids_i64, const void* dh_bf16, void* dword, long long V, void* dpos, int grads_bf16, int B,

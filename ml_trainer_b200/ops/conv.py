@@ -44,6 +44,36 @@ def _im2col(x, KH, KW, stride, pad, OH, OW):
     return col
 
 
+def _implicit_ok(x, C, direct) -> bool:
+    """TMA im2col path: patches are gathered by the GEMM's own loads (csrc/im2col_tma.cu) - needs 64-channel k-blocks."""
+    return (not direct) and C % 64 == 0 and x.dtype == torch.bfloat16 and x.data_ptr() % 16 == 0
+
+
+def _conv_fwd_implicit(x, w2, Co, KH, KW, stride, pad, OH, OW):
+    B, H, W, C = x.shape
+    y = torch.empty((B * OH * OW, Co), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().mlt_conv_fwd_implicit(ptr(x), _c_int(B), _c_int(H), _c_int(W), _c_int(C), ptr(w2), _c_ll(w2.stride(0)), _c_int(Co),
+                                           _c_int(KH), _c_int(KW), _c_int(stride), _c_int(pad), ptr(y), _c_ll(y.stride(0)),
+                                           stream_handle()), "mlt_conv_fwd_implicit")
+    launches.bump("conv_fwd_implicit_gemm")
+    return y
+
+
+def _conv_wgrad_implicit(dy2, x, Co, KH, KW, stride, pad, out, out_dtype):
+    from .gemm import SPLITK_WS_BYTES
+
+    B, H, W, C = x.shape
+    if out is None:
+        out = torch.empty((Co, KH * KW * C), dtype=out_dtype, device=x.device)
+    ws = scratch(x.device, "gemm_splitk", SPLITK_WS_BYTES)
+    check(_lib.lib().mlt_conv_wgrad_implicit(ptr(dy2), _c_ll(dy2.stride(0)), ptr(x), _c_int(B), _c_int(H), _c_int(W), _c_int(C), _c_int(Co),
+                                             _c_int(KH), _c_int(KW), _c_int(stride), _c_int(pad), ptr(out), _c_ll(out.stride(0)),
+                                             _c_int(int(out.dtype == torch.float32)), ptr(ws), _c_ll(ws.numel()), stream_handle()),
+          "mlt_conv_wgrad_implicit")
+    launches.bump("conv_wgrad_implicit_gemm")
+    return out
+
+
 class _ConvNHWCFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, stride, pad, wparam):
@@ -52,17 +82,24 @@ class _ConvNHWCFn(torch.autograd.Function):
         OH, OW = _out_hw(H, W, KH, stride, pad)
         x = x.contiguous()
         direct = KH == 1 and KW == 1 and stride == 1 and pad == 0
-        a = x.view(B * H * W, C) if direct else _im2col(x, KH, KW, stride, pad, OH, OW)
-        y = gemm(a, _w2d(weight), False, False)
+        implicit = _implicit_ok(x, C, direct)
+        if implicit:
+            a = None
+            y = _conv_fwd_implicit(x, _w2d(weight), Co, KH, KW, stride, pad, OH, OW)
+        else:
+            a = x.view(B * H * W, C) if direct else _im2col(x, KH, KW, stride, pad, OH, OW)
+            y = gemm(a, _w2d(weight), False, False)
         ctx.save_for_backward(x, weight)
-        ctx.cfg = (stride, pad, OH, OW, direct)
+        ctx.cfg = (stride, pad, OH, OW, direct, implicit)
         ctx.wparam = wparam
+        # an explicit patch matrix (the 3-channel stem only) is kept for the weight gradient instead of being re-gathered
+        ctx.col = None if (direct or implicit) else a
         return y.view(B, OH, OW, Co)
 
     @staticmethod
     def backward(ctx, dy):
         x, weight = ctx.saved_tensors
-        stride, pad, OH, OW, direct = ctx.cfg
+        stride, pad, OH, OW, direct, implicit = ctx.cfg
         wparam = ctx.wparam
         B, H, W, C = x.shape
         Co, Ci, KH, KW = weight.shape
@@ -79,14 +116,18 @@ class _ConvNHWCFn(torch.autograd.Function):
                                                  _c_int(KW), _c_int(stride), _c_int(pad), _c_int(OH), _c_int(OW), stream_handle()),
                       "mlt_col2im_nhwc")
                 launches.bump("col2im_nhwc")
-        a = x.view(B * H * W, C) if direct else _im2col(x, KH, KW, stride, pad, OH, OW)     # recomputed, not stored
+        a = x.view(B * H * W, C) if direct else ctx.col
+        ctx.col = None
         wsink = _sink(wparam)
         out = None
         if wsink is not None:
             v = wsink.permute(0, 2, 3, 1)
             if v.is_contiguous():
                 out = v.reshape(Co, KH * KW * Ci)
-        dw2 = gemm(dy2, a, True, True, out=out, out_dtype=weight.dtype)
+        if implicit:
+            dw2 = _conv_wgrad_implicit(dy2, x, Co, KH, KW, stride, pad, out, weight.dtype)
+        else:
+            dw2 = gemm(dy2, a, True, True, out=out, out_dtype=weight.dtype)
         if wsink is not None and out is None:
             wsink.copy_(dw2.view(Co, KH, KW, Ci).permute(0, 3, 1, 2))
         dw = None if wsink is not None else dw2.view(Co, KH, KW, Ci).permute(0, 3, 1, 2)

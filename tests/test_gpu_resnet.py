@@ -14,7 +14,9 @@ def _close(a, b, tol, what):
 
 
 @pytest.mark.parametrize("B,H,Cin,Cout,K,stride,pad", [(2, 16, 16, 32, 1, 1, 0), (2, 16, 16, 32, 3, 1, 1), (3, 15, 8, 24, 3, 2, 1),
-                                                      (2, 32, 8, 64, 7, 2, 3), (2, 14, 64, 128, 1, 2, 0), (4, 56, 64, 64, 3, 1, 1)])
+                                                      (2, 32, 8, 64, 7, 2, 3), (2, 14, 64, 128, 1, 2, 0), (4, 56, 64, 64, 3, 1, 1),
+                                                      (3, 28, 128, 128, 3, 2, 1), (2, 14, 256, 256, 3, 1, 1), (5, 9, 64, 320, 3, 1, 1),
+                                                      (2, 7, 512, 512, 3, 1, 1)])
 def test_conv2d_nhwc_fwd_bwd(B, H, Cin, Cout, K, stride, pad):
     from ml_trainer_b200.ops import conv as C
 
