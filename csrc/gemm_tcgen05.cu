@@ -48,6 +48,8 @@ struct GemmParams {
   int splits, kb_per_split;      // split-K: the batch index doubles as the K-slice id, partials go to an fp32 workspace
   // implicit-GEMM convolution: one operand is the patch matrix of an NHWC tensor, read through a TMA im2col map.
   //   1: A = patches [pixels x KH*KW*C], K-major (forward)      2: B = patches as the MN-major operand (weight gradient)
+  //   3: data gradient of a stride-1 convolution: A = patches of dy (as 1), B = the weights [Co][tap][C] read as the
+  //      MN-major operand with the tap flipped (batch coordinate of a 4-D tiled map)
   int im2col;
   int cv_OW, cv_OH, cv_stride, cv_pad, cv_KW, cv_taps, cv_C;
 };
@@ -142,7 +144,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
           const int k0 = kb * BK;
           if (elect_one()) {
           mbar_arrive_expect_tx(&full[stage], Cfg::kStageBytes);
-          if (p.im2col == 1) {
+          if (p.im2col == 1 || p.im2col == 3) {
             // k-block kb = (filter tap, 64-channel block); the 128 rows are consecutive output pixels starting at m0
             const int cblocks = p.cv_C >> 6;
             const int tap = kb / cblocks, c0 = (kb - tap * cblocks) << 6;
@@ -170,6 +172,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
               const int fr = tap / p.cv_KW, fs = tap - fr * p.cv_KW;
               tma_load_im2col_4d(sB + j * 8192, &tmB, &full[stage], c0, w0, h0, img, fs, fr);
             }
+          } else if (p.im2col == 3) {
+            const int cblocks = p.cv_C >> 6;
+            const int tap = kb / cblocks, co0 = (kb - tap * cblocks) << 6;
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tma_load_4d(sB + j * 8192, &tmB, &full[stage], n0 + 64 * j, co0, p.cv_taps - 1 - tap, 0);
           } else if (!p.b_mn) {
             tma_load_4d(sB, &tmB, &full[stage], k0, n0, z1, z2);                       // box {64 k, BN rows}
           } else {
@@ -688,6 +695,36 @@ extern "C" int mlt_conv_wgrad_implicit(const void* dy, long long lddy, const voi
     if (rc) return rc;
     return launch_splitk_reduce((const float*)splitk_ws, dw, lddw, out_f32, M, N, splits, st);
   }
+  if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
+  if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
+  return launch_gemm<64>(tmA, tmB, p, st);
+}
+
+// dx[B*H*W, C] of a STRIDE-1 convolution as an implicit GEMM: dx = patches(dy) * Wf^T, where the patches of dy use padding
+// KH-1-pad and the filter is read flipped.  Replaces the "dy * W -> [pixels, KH*KW*C] -> col2im" round trip.
+// dy: [B, OH, OW, Co] bf16 (Co a multiple of 64); w2: [Co, KH*KW, C] contiguous (the channels-last weight).
+extern "C" int mlt_conv_dgrad_implicit(const void* dy, int B, int OH, int OW, int Co, const void* w2, int C, int KH, int KW, int pad,
+                                       void* dx, long long lddx, void* stream) {
+  MLT_REQUIRE(Co % 64 == 0 && Co > 0, "mlt_conv_dgrad_implicit: Cout (%d) must be a multiple of 64", Co);
+  MLT_REQUIRE(KH - 1 - pad >= 0 && KW - 1 - pad >= 0, "mlt_conv_dgrad_implicit: padding larger than the filter");
+  GemmParams p;
+  // patches of dy: "input" OH x OW with Co channels, filter KH x KW, stride 1, padding KH-1-pad  ->  output H x W
+  conv_params(p, 3, OH, OW, Co, KH, KW, 1, KH - 1 - pad);
+  MLT_REQUIRE(KH == KW, "mlt_conv_dgrad_implicit: square filters only");
+  const long long M = (long long)B * p.cv_OH * p.cv_OW;
+  MLT_REQUIRE(M > 0 && M < (1LL << 31), "mlt_conv_dgrad_implicit: bad size");
+  const int K = KH * KW * Co, N = C;
+  int BN = (N >= 512 || (N % 256 == 0)) ? 256 : (N > 64 ? 128 : 64);
+  CUtensorMap tmA, tmB;
+  if (make_im2col_tmap(&tmA, dy, B, OH, OW, Co, KH, KW, 1, KH - 1 - pad, 64, BM)) return 1;
+  // weights as [tap][Co][C]: inner = C, rows = Co with pitch KH*KW*C, batch = tap with stride C
+  if (make_tmap(&tmB, w2, C, Co, (long long)KH * KW * C, 64, BK, KH * KW, C)) return 1;
+  p.M = (int)M; p.N = N; p.K = K;
+  p.out = dx; p.ldo = lddx; p.out_f32 = 0;
+  p.bias = nullptr; p.bias_f32 = 0; p.act = ACT_NONE; p.aux_mode = 0; p.aux = nullptr; p.ld_aux = 0;
+  p.a_mn = 0; p.b_mn = 1;
+  p.nb1 = p.nb2 = 1; p.ob1 = p.ob2 = 0; p.splits = 1; p.kb_per_split = 0;
+  cudaStream_t st = (cudaStream_t)stream;
   if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
   if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
   return launch_gemm<64>(tmA, tmB, p, st);

@@ -203,6 +203,10 @@ int mlt_conv_fwd_implicit(const void* x, int B, int H, int W, int C, const void*
 int mlt_conv_wgrad_implicit(const void* dy, long long lddy, const void* x, int B, int H, int W, int C, int Co, int KH, int KW,
                             int stride, int pad, void* dw, long long lddw, int out_f32, void* splitk_ws, long long splitk_ws_bytes,
                             void* stream);
+/* Data gradient of a stride-1 convolution as an implicit GEMM over the patches of dy with the filter read flipped;
+ * dy [B, OH, OW, Co] (Co a multiple of 64), w2 [Co, KH*KW, C] contiguous, dx [B*H*W, C]. */
+int mlt_conv_dgrad_implicit(const void* dy, int B, int OH, int OW, int Co, const void* w2, int C, int KH, int KW, int pad, void* dx,
+                            long long lddx, void* stream);
 /* Test hook for the TMA im2col path: the [pixels x 64] patch tile of output pixels m0.., filter tap (r, s), channels c0..c0+63 of
  * an NHWC bf16 tensor, loaded with one cp.async.bulk.tensor...im2col and written back un-swizzled. */
 int mlt_im2col_probe(const void* x, int B, int H, int W, int C, int KH, int KW, int stride, int pad, long long m0, int r, int s, int c0,

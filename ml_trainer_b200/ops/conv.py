@@ -106,7 +106,14 @@ class _ConvNHWCFn(torch.autograd.Function):
         dy2 = dy.contiguous().view(B * OH * OW, Co)
         w2 = _w2d(weight)
         dx = None
-        if ctx.needs_input_grad[0]:
+        if (ctx.needs_input_grad[0] and implicit and stride == 1 and KH == KW and Co % 64 == 0 and C % 8 == 0 and w2.is_contiguous()
+                and dy2.data_ptr() % 16 == 0):
+            # implicit GEMM over the patches of dy, filter read flipped: no [pixels, KH*KW*C] intermediate, no col2im
+            dx = torch.empty_like(x)
+            check(_lib.lib().mlt_conv_dgrad_implicit(ptr(dy2), _c_int(B), _c_int(OH), _c_int(OW), _c_int(Co), ptr(w2), _c_int(C), _c_int(KH),
+                                                     _c_int(KW), _c_int(pad), ptr(dx), _c_ll(C), stream_handle()), "mlt_conv_dgrad_implicit")
+            launches.bump("conv_dgrad_implicit_gemm")
+        elif ctx.needs_input_grad[0]:
             dcol = gemm(dy2, w2, False, True)                       # [M, KH*KW*C]
             if direct:
                 dx = dcol.view(B, H, W, C)
