@@ -52,6 +52,7 @@ class TrainerConfig:
     resume: Optional[str] = None   # path to a trainer_state.pth sidecar
     save_every: int = 1            # epochs between model.pth snapshots
     drop_last: bool = False
+    trace: bool = False            # NVTX ranges per step phase + a per-epoch device-time summary (utils/tracing.py)
 
     extra: dict = field(default_factory=dict, repr=False)
 

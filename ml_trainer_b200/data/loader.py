@@ -132,7 +132,9 @@ class PinnedPrefetcher:
             if t.is_pinned() and t.shape == h.shape:
                 continue
             h.copy_(t)
-        with torch.cuda.stream(self.copy_stream):
+        from ..utils.tracing import phase
+
+        with phase("h2d"), torch.cuda.stream(self.copy_stream):
             if self._released[slot] is not None:
                 self.copy_stream.wait_event(self._released[slot])
             for d, h, t in zip(self._dev[slot], self._host[slot], tensors):

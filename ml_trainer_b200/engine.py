@@ -111,13 +111,18 @@ class StepEngine:
 
     # ------------------------------------------------------------------- train
     def _train_body(self, inputs, targets):
+        from .utils.tracing import phase
+
         self.reducer.arm()
-        outputs, loss, dl = self._forward_loss(self.model, inputs, targets, train=True)
-        if dl is not None:
-            outputs.backward(dl)
-        else:
-            loss.backward()
-        self.reducer.finish_step()
+        with phase("forward+loss"):
+            outputs, loss, dl = self._forward_loss(self.model, inputs, targets, train=True)
+        with phase("backward"):
+            if dl is not None:
+                outputs.backward(dl)
+            else:
+                loss.backward()
+        with phase("reduce+update"):
+            self.reducer.finish_step()
         self.loss_static.copy_(loss.detach().float())
         self.last_loss = self.loss_static
 
@@ -167,5 +172,8 @@ class StepEngine:
         if self.fused is not None and model is self.model and self.fused.supports(inputs, targets):
             self.fused(inputs, targets, False, self.acc, self.metric == "accuracy", self._loss_buf)
             return None
-        outputs, _, _ = self._forward_loss(model, inputs, targets, train=False)
+        from .utils.tracing import phase
+
+        with phase("eval"):
+            outputs, _, _ = self._forward_loss(model, inputs, targets, train=False)
         return outputs

@@ -146,6 +146,12 @@ class Trainer:
             self._sync_initial_state()
         self.reducer = Reducer(self.optimizer, self.comm, bucket_mb=cfg.bucket_mb)
         self.scheduler = self._get_scheduler()
+        self.phase_timer = None
+        if self.cfg.trace:
+            from .utils import tracing
+
+            self.phase_timer = tracing.PhaseTimer()
+            tracing.enable(True, self.phase_timer)
         self.engine = StepEngine(self.model, self.criterion, self.criterion_type, self.metric, self.reducer,
                                  self.device, graph=cfg.graph, compute_dtype=self.compute_dtype,
                                  fused_step=cfg.fused_step)
@@ -513,6 +519,10 @@ class Trainer:
                 if self.rank == 0:
                     self.save(self.model_dir, epoch=epoch)
                 self.comm.barrier()
+            if self.phase_timer is not None:
+                self.phase_ms = self.phase_timer.summary()       # mean device ms per phase over the eager steps of this epoch
+                if self.phase_ms and self.rank == 0:
+                    logger.info("step phases (ms): " + ", ".join(f"{k} {v:.3f}" for k, v in sorted(self.phase_ms.items())))
             if self.metric:
                 logger.info(f"train loss: {self.train_losses[-1]} - train {self.metric}: {self.train_metrics[-1]}")
                 logger.info(f"valid loss: {self.val_losses[-1]} - valid {self.metric}: {self.val_metrics[-1]}\n\n")

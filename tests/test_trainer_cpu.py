@@ -188,3 +188,23 @@ def test_test_py_runs(tmp_path):
                        cwd=ROOT, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert os.path.exists(tmp_path / "model.pth")
+
+
+def test_tracing_phases_are_noops_on_cpu(tmp_path):
+    """trace=True must not change results and must not need a GPU (NVTX / CUDA events are skipped on CPU)."""
+    from ml_trainer_b200 import SyntheticDataset, Trainer, build_model
+    from ml_trainer_b200.utils import tracing
+
+    ds = SyntheticDataset((3, 32, 32), 10, length=64, seed=3)
+    losses = []
+    for trace in (False, True):
+        torch.manual_seed(11)
+        t = Trainer(build_model("mlmodel"), datasets=(ds, ds), epochs=1, batch_size=16, optimizer="sgd", lr=0.01, progress=False,
+                    model_dir=str(tmp_path / str(trace)), seed=5, trace=trace)
+        t.fit()
+        losses.append(t.train_losses[-1])
+        tracing.enable(False, None)
+    assert losses[0] == losses[1]
+    with tracing.phase("anything"):
+        pass
+    assert tracing.PhaseTimer().summary() == {}
