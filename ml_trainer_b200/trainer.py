@@ -213,6 +213,16 @@ class Trainer:
         for b in self.model.buffers():
             self.comm.broadcast(b, src=0)
 
+    def _sync_buffers(self):
+        """Rank 0's module buffers (BatchNorm running statistics) become everyone's.
+
+        DDP broadcasts them before EVERY forward.  Training-mode BatchNorm never reads them, so doing it
+        once before each evaluation gives the same numbers for one collective per epoch instead of one per step."""
+        if self.world_size > 1:
+            for b in self.model.buffers():
+                if b.is_floating_point():
+                    self.comm.broadcast(b, src=0)
+
     def _average_gradients(self):
         """Reference API (src/trainer.py:152-158): SUM all-reduce then divide by world size."""
         self.optimizer.collect_stray_grads()
@@ -415,6 +425,7 @@ class Trainer:
 
     @torch.no_grad()
     def _validate_one_epoch(self):
+        self._sync_buffers()
         loss, metric = self._eval_loop(self.model, self.val_loader, reduce=self.val_sampler is not None)
         self.val_losses.append(loss)
         if self.metric:
