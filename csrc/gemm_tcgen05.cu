@@ -88,6 +88,173 @@ __device__ __forceinline__ float act_grad_from_pre(int act, float z) {
   }
 }
 
+// One output tile's worth of epilogue work for one warp: rows [store_row0, +32) (this lane: `row`), 32-column chunks
+// c_lo .. c_hi-1 of the BN-wide accumulator at `taddr`.  TMEM -> registers -> (bias / activation / aux) -> swizzled smem
+// slab -> TMA store.  Waits on the accumulator's full barrier itself so the aux prefetch can be issued before it.
+template <int BN, bool AUX>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* tmOut, const CUtensorMap* tmAux, uint32_t taddr,
+                                              int row, int store_row0, int n0, int z1, int z2, uint8_t* slab, uint8_t* aux_slab,
+                                              int lane, int c_lo, int c_hi, uint64_t* full_bar, uint32_t full_parity) {
+  const int chunks_per_slab = p.out_f32 ? 1 : 2;          // a 32-column chunk is 128 B of fp32 or 64 B of bf16
+  const bool aux_in = p.aux_mode == 2 || p.aux_mode == 4;
+  // aux operand of the first chunk: requested before the accumulator is ready, then one chunk ahead
+  const __nv_bfloat16* aux_row = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux;
+  uint4 pa[4] = {};
+  auto fetch_aux = [&](int c) {
+    const int nb = n0 + c * 32;
+    if (aux_in && row < p.M && nb + 32 <= p.N) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) pa[j] = *reinterpret_cast<const uint4*>(aux_row + nb + 8 * j);
+    }
+  };
+  if (c_lo < c_hi) fetch_aux(c_lo);
+  mbar_wait(full_bar, full_parity);
+  tc_fence_after();
+#pragma unroll 1
+  for (int c = c_lo; c < c_hi; ++c) {
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(taddr + c * 32, r);
+    uint4 ca[4] = {pa[0], pa[1], pa[2], pa[3]};
+    if (c + 1 < c_hi) fetch_aux(c + 1);
+    tmem_ld_wait();
+    const int nb = n0 + c * 32;
+    const int within = (c - c_lo) % chunks_per_slab;
+    if (within == 0) {
+      // the bulk store that last read this slab must have drained it
+      if (lane == 0) tma_store_wait_read<0>();
+      __syncwarp();
+    }
+    float v[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+    const bool live = nb < p.N;                          // whole chunk beyond N: nothing to compute, TMA clips it
+    const bool full_chunk = nb + 32 <= p.N;
+    if (live && p.bias != nullptr) {
+      if (p.bias_f32) {
+        const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __ldg(bp + j);
+      } else if (full_chunk && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
+        const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint4 raw = __ldg(bp + j);
+          const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
+            v[8 * j + 2 * e] += f.x; v[8 * j + 2 * e + 1] += f.y;
+          }
+        }
+      } else {
+        const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __bfloat162float(bp[j]);
+      }
+    }
+    bool act_done = false;
+    if ((AUX || (live && row < p.M)) && (p.aux_mode == 1 || p.aux_mode == 3)) {
+      // keep for backward, with direct stores: the pre-activation (1) or the activation's derivative there (3)
+      __nv_bfloat16* ap = reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
+      float s[32];
+      if (p.aux_mode == 1) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s[j] = v[j];
+      } else if (p.act == ACT_GELU && !p.out_f32) {      // bf16 result: value and derivative from one tanh.approx
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(v[j], g, dg); v[j] = g; s[j] = dg; }
+        act_done = true;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) s[j] = act_grad_from_pre(p.act, v[j]);
+      }
+      if (AUX) {                                         // swizzled slab, stored by TMA together with the output slab
+        uint8_t* arow = aux_slab + lane * 128;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint4 pk;
+          pk.x = pack_bf16(s[8 * j], s[8 * j + 1]); pk.y = pack_bf16(s[8 * j + 2], s[8 * j + 3]);
+          pk.z = pack_bf16(s[8 * j + 4], s[8 * j + 5]); pk.w = pack_bf16(s[8 * j + 6], s[8 * j + 7]);
+          *reinterpret_cast<uint4*>(arow + (((within * 4 + j) ^ (lane & 7)) << 4)) = pk;
+        }
+      } else if (full_chunk) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 8) {
+          uint4 pk;
+          pk.x = pack_bf16(s[j], s[j + 1]); pk.y = pack_bf16(s[j + 2], s[j + 3]);
+          pk.z = pack_bf16(s[j + 4], s[j + 5]); pk.w = pack_bf16(s[j + 6], s[j + 7]);
+          *reinterpret_cast<uint4*>(ap + j) = pk;
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (nb + j < p.N) ap[j] = __float2bfloat16_rn(s[j]);
+      }
+    }
+    if (aux_in) {                                        // dX = (dY W) * act'(z): z (2) or act'(z) itself (4) in aux
+      if (live && row < p.M) {
+        float s[32];
+        if (full_chunk) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t w[4] = {ca[j].x, ca[j].y, ca[j].z, ca[j].w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
+              s[8 * j + 2 * e] = f.x; s[8 * j + 2 * e + 1] = f.y;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) s[j] = nb + j < p.N ? __bfloat162float(aux_row[nb + j]) : 0.f;
+        }
+        if (p.aux_mode == 4) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] *= s[j];
+        } else if (p.act == ACT_GELU && !p.out_f32) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(s[j], g, dg); v[j] *= dg; }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] *= act_grad_from_pre(p.act, s[j]);
+        }
+      }
+    } else if (p.act != ACT_NONE && !act_done) {
+      if (p.act == ACT_GELU && !p.out_f32) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(v[j], g, dg); v[j] = g; }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = act_fwd_rt(p.act, v[j]);
+      }
+    }
+    // registers -> swizzled slab: 16-byte chunk index is XORed with (row & 7), the layout SWIZZLE_128B expects
+    uint8_t* srow = slab + lane * 128;
+    if (p.out_f32) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(srow + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint4 pk;
+        pk.x = pack_bf16(v[8 * j], v[8 * j + 1]); pk.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+        pk.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]); pk.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+        *reinterpret_cast<uint4*>(srow + (((within * 4 + j) ^ (lane & 7)) << 4)) = pk;
+      }
+    }
+    if (within == chunks_per_slab - 1) {
+      fence_proxy_async();                               // generic-proxy smem writes -> visible to the TMA engine
+      __syncwarp();
+      if (lane == 0) {
+        const int col0 = nb - within * 32;
+        tma_store_4d(tmOut, slab, col0, store_row0, z1, z2);
+        if (AUX) tma_store_4d(tmAux, aux_slab, col0, store_row0, z1, z2);
+        tma_store_commit();
+      }
+    }
+  }
+}
+
 template <int BN, bool AUX>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -236,11 +403,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const int half = (warp - 2) >> 2;
     uint8_t* slab = staging + (warp - 2) * 4096;
     uint8_t* aux_slab = staging + (kEpiWarps + warp - 2) * 4096;      // only present (and used) when AUX
-    const int chunks_per_slab = p.out_f32 ? 1 : 2;          // a 32-column chunk is 128 B of fp32 or 64 B of bf16
     constexpr int kChunks = BN / 32;
     const int c_lo = BN >= 128 ? half * (kChunks / 2) : 0;
     const int c_hi = BN >= 128 ? c_lo + kChunks / 2 : (half == 0 ? kChunks : 0);
-    const bool aux_in = p.aux_mode == 2 || p.aux_mode == 4;
     int as = 0; uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
@@ -249,163 +414,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int z1 = z % p.nb1, z2 = z / p.nb1;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * BN;
-      // aux operand of the first chunk: requested before the accumulator is ready, then one chunk ahead
-      const __nv_bfloat16* aux_row = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux;
-      uint4 pa[4] = {};
-      auto fetch_aux = [&](int c) {
-        const int nb = n0 + c * 32;
-        if (aux_in && row < p.M && nb + 32 <= p.N) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) pa[j] = *reinterpret_cast<const uint4*>(aux_row + nb + 8 * j);
-        }
-      };
-      if (c_lo < c_hi) fetch_aux(c_lo);
-      mbar_wait(&tmem_full[as], aphase);
-      tc_fence_after();
-      const uint32_t taddr = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
-#pragma unroll 1
-      for (int c = c_lo; c < c_hi; ++c) {
-        uint32_t r[32];
-        tmem_ld_32x32b_x32(taddr + c * 32, r);
-        uint4 ca[4] = {pa[0], pa[1], pa[2], pa[3]};
-        if (c + 1 < c_hi) fetch_aux(c + 1);
-        tmem_ld_wait();
-        const int nb = n0 + c * 32;
-        const int within = (c - c_lo) % chunks_per_slab;
-        if (within == 0) {
-          // the bulk store that last read this slab must have drained it
-          if (lane == 0) tma_store_wait_read<0>();
-          __syncwarp();
-        }
-        float v[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        const bool live = nb < p.N;                          // whole chunk beyond N: nothing to compute, TMA clips it
-        const bool full_chunk = nb + 32 <= p.N;
-        if (live && p.bias != nullptr) {
-          if (p.bias_f32) {
-            const float* bp = reinterpret_cast<const float*>(p.bias) + nb;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __ldg(bp + j);
-          } else if (full_chunk && (reinterpret_cast<uintptr_t>(p.bias) & 15) == 0) {
-            const uint4* bp = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const uint4 raw = __ldg(bp + j);
-              const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
-                v[8 * j + 2 * e] += f.x; v[8 * j + 2 * e + 1] += f.y;
-              }
-            }
-          } else {
-            const __nv_bfloat16* bp = reinterpret_cast<const __nv_bfloat16*>(p.bias) + nb;
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (full_chunk || nb + j < p.N) v[j] += __bfloat162float(bp[j]);
-          }
-        }
-        bool act_done = false;
-        if ((AUX || (live && row < p.M)) && (p.aux_mode == 1 || p.aux_mode == 3)) {
-          // keep for backward, with direct stores: the pre-activation (1) or the activation's derivative there (3)
-          __nv_bfloat16* ap = reinterpret_cast<__nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux + nb;
-          float s[32];
-          if (p.aux_mode == 1) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) s[j] = v[j];
-          } else if (p.act == ACT_GELU && !p.out_f32) {      // bf16 result: value and derivative from one tanh.approx
-#pragma unroll
-            for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(v[j], g, dg); v[j] = g; s[j] = dg; }
-            act_done = true;
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) s[j] = act_grad_from_pre(p.act, v[j]);
-          }
-          if (AUX) {                                         // swizzled slab, stored by TMA together with the output slab
-            uint8_t* arow = aux_slab + lane * 128;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              uint4 pk;
-              pk.x = pack_bf16(s[8 * j], s[8 * j + 1]); pk.y = pack_bf16(s[8 * j + 2], s[8 * j + 3]);
-              pk.z = pack_bf16(s[8 * j + 4], s[8 * j + 5]); pk.w = pack_bf16(s[8 * j + 6], s[8 * j + 7]);
-              *reinterpret_cast<uint4*>(arow + (((within * 4 + j) ^ (lane & 7)) << 4)) = pk;
-            }
-          } else if (full_chunk) {
-#pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              uint4 pk;
-              pk.x = pack_bf16(s[j], s[j + 1]); pk.y = pack_bf16(s[j + 2], s[j + 3]);
-              pk.z = pack_bf16(s[j + 4], s[j + 5]); pk.w = pack_bf16(s[j + 6], s[j + 7]);
-              *reinterpret_cast<uint4*>(ap + j) = pk;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (nb + j < p.N) ap[j] = __float2bfloat16_rn(s[j]);
-          }
-        }
-        if (aux_in) {                                        // dX = (dY W) * act'(z): z (2) or act'(z) itself (4) in aux
-          if (live && row < p.M) {
-            float s[32];
-            if (full_chunk) {
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const uint32_t w[4] = {ca[j].x, ca[j].y, ca[j].z, ca[j].w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[e]));
-                  s[8 * j + 2 * e] = f.x; s[8 * j + 2 * e + 1] = f.y;
-                }
-              }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) s[j] = nb + j < p.N ? __bfloat162float(aux_row[nb + j]) : 0.f;
-            }
-            if (p.aux_mode == 4) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] *= s[j];
-            } else if (p.act == ACT_GELU && !p.out_f32) {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(s[j], g, dg); v[j] *= dg; }
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] *= act_grad_from_pre(p.act, s[j]);
-            }
-          }
-        } else if (p.act != ACT_NONE && !act_done) {
-          if (p.act == ACT_GELU && !p.out_f32) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(v[j], g, dg); v[j] = g; }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = act_fwd_rt(p.act, v[j]);
-          }
-        }
-        // registers -> swizzled slab: 16-byte chunk index is XORed with (row & 7), the layout SWIZZLE_128B expects
-        uint8_t* srow = slab + lane * 128;
-        if (p.out_f32) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<float4*>(srow + ((j ^ (lane & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            uint4 pk;
-            pk.x = pack_bf16(v[8 * j], v[8 * j + 1]); pk.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
-            pk.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]); pk.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
-            *reinterpret_cast<uint4*>(srow + (((within * 4 + j) ^ (lane & 7)) << 4)) = pk;
-          }
-        }
-        if (within == chunks_per_slab - 1) {
-          fence_proxy_async();                               // generic-proxy smem writes -> visible to the TMA engine
-          __syncwarp();
-          if (lane == 0) {
-            const int col0 = nb - within * 32;
-            tma_store_4d(&tmOut, slab, col0, m_blk * BM + q * 32, z1, z2);
-            if (AUX) tma_store_4d(&tmAux, aux_slab, col0, m_blk * BM + q * 32, z1, z2);
-            tma_store_commit();
-          }
-        }
-      }
+      epilogue_tile<BN, AUX>(p, &tmOut, &tmAux, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), row, m_blk * BM + q * 32, n0, z1, z2,
+                             slab, aux_slab, lane, c_lo, c_hi, &tmem_full[as], aphase);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[as]);
@@ -417,6 +427,161 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+}
+
+// ---- CTA-pair variant (cta_group::2) -------------------------------------------------------------------------
+// Two CTAs of a cluster (one TPC) own a 256 x 256 tile.  Each loads its own 128 rows of A and HALF of B (128 of the 256
+// columns) - 32 KB per stage instead of 48, so six stages fit and the B operand crosses shared memory once per pair -
+// and the leader's MMA warp issues tcgen05.mma.cta_group::2 (M = 256): the hardware reads both CTAs' shared memory and
+// writes each CTA's 128 accumulator rows into that CTA's TMEM.  TMA completions of both CTAs are counted on the leader's
+// `full` barrier; tcgen05.commit multicasts `empty` / `tmem_full` to both; the peer's epilogue warps arrive on the
+// leader's `tmem_empty` through the cluster window.  The epilogue is the single-CTA one, each CTA on its own rows.
+struct Gemm2Cfg {
+  static constexpr int kABytes = BM * BK * 2;                 // 128 rows of A
+  static constexpr int kBBytes = 128 * BK * 2;                // 128 of the tile's 256 B rows
+  static constexpr int kStageBytes = kABytes + kBBytes;       // 32 KB
+  static constexpr int kStages = 6;
+  static constexpr int kTmemCols = 512;                       // two 256-column accumulator stages
+  static constexpr int kStagingBytes = kEpiWarps * 4096;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 + 256;
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const __grid_constant__ CUtensorMap tmOut, const GemmParams p) {
+  using Cfg = Gemm2Cfg;
+  constexpr int BN = 256, TM = 256;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;
+  uint64_t* full = reinterpret_cast<uint64_t*>(staging + Cfg::kStagingBytes);
+  uint64_t* empty = full + Cfg::kStages;
+  uint64_t* tmem_full = empty + Cfg::kStages;
+  uint64_t* tmem_empty = tmem_full + 2;
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+  const int tiles_per_problem = p.num_m * p.num_n;
+  const int num_tiles = tiles_per_problem * p.nb1 * p.nb2;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmA);
+    prefetch_tmap(&tmB);
+    prefetch_tmap(&tmOut);
+    for (int s = 0; s < Cfg::kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tmem_full[a], 1); mbar_init(&tmem_empty[a], 2 * kEpiWarps); }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc_2cta(tmem_base_slot, Cfg::kTmemCols);
+    tmem_relinquish_2cta();
+  }
+  tc_fence_before();
+  cluster_sync_all();                       // barriers of both CTAs initialised and visible, TMEM allocated in both
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  if (warp == 0) {
+    // ===================================== TMA producer (both CTAs) =====================================
+    int stage = 0; uint32_t phase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int m_blk, n_blk;
+      const int z = tile / tiles_per_problem;
+      tile_coords(tile - z * tiles_per_problem, p.num_m, p.num_n, m_blk, n_blk);
+      const int z1 = p.splits > 1 ? 0 : z % p.nb1, z2 = p.splits > 1 ? 0 : z / p.nb1;
+      const int kb_lo = p.splits > 1 ? z * p.kb_per_split : 0;
+      const int kb_hi = p.splits > 1 ? min(p.num_k, kb_lo + p.kb_per_split) : p.num_k;
+      const int m0 = m_blk * TM + (int)rank * BM, n0 = n_blk * BN + (int)rank * 128;
+      for (int kb = kb_lo; kb < kb_hi; ++kb) {
+        mbar_wait(&empty[stage], phase ^ 1);
+        uint8_t* sA = smem + stage * Cfg::kStageBytes;
+        uint8_t* sB = sA + Cfg::kABytes;
+        const int k0 = kb * BK;
+        if (elect_one()) {
+          if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * Cfg::kStageBytes);     // both CTAs' bytes
+          if (!p.a_mn) {
+            tma_load_4d_2cta(sA, &tmA, &full[stage], k0, m0, z1, z2);                   // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) tma_load_4d_2cta(sA + j * 8192, &tmA, &full[stage], m0 + 64 * j, k0, z1, z2);
+          }
+          if (!p.b_mn) {
+            tma_load_4d_2cta(sB, &tmB, &full[stage], k0, n0, z1, z2);                   // box {64 k, 128 rows}
+          } else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) tma_load_4d_2cta(sB + j * 8192, &tmB, &full[stage], n0 + 64 * j, k0, z1, z2);
+          }
+        }
+        __syncwarp();
+        if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issuer (leader CTA only) ===================================
+    if (rank == 0) {
+      const uint32_t idesc = make_idesc_bf16(TM, BN, p.a_mn, p.b_mn);
+      const uint32_t a_step = p.a_mn ? (UMMA_K * 128) : (UMMA_K * 2);
+      const uint32_t b_step = p.b_mn ? (UMMA_K * 128) : (UMMA_K * 2);
+      const uint32_t a_lbo = p.a_mn ? 8192u : 16u, b_lbo = p.b_mn ? 8192u : 16u;
+      int stage = 0; uint32_t phase = 0;
+      int as = 0; uint32_t aphase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        mbar_wait(&tmem_empty[as], aphase ^ 1);          // both CTAs' epilogues have drained this accumulator stage
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        const int zs = tile / tiles_per_problem;
+        const int kb_lo = p.splits > 1 ? zs * p.kb_per_split : 0;
+        const int kb_hi = p.splits > 1 ? min(p.num_k, kb_lo + p.kb_per_split) : p.num_k;
+        for (int kb = kb_lo; kb < kb_hi; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sA = smem_u32(smem + stage * Cfg::kStageBytes);
+          const uint32_t sB = sA + Cfg::kABytes;
+          if (elect_one()) {
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t adesc = make_smem_desc_sw128(sA + k * a_step, a_lbo, 1024);
+              const uint64_t bdesc = make_smem_desc_sw128(sB + k * b_step, b_lbo, 1024);
+              umma_f16_2cta(d_tmem, adesc, bdesc, idesc, (kb > kb_lo) || (k != 0));
+            }
+            umma_commit_2cta(&empty[stage], 3);            // the slot is free in BOTH CTAs once these MMAs retire
+            if (kb == kb_hi - 1) umma_commit_2cta(&tmem_full[as], 3);
+          }
+          __syncwarp();
+          if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
+        }
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else {
+    // ===================================== epilogue (both CTAs, own 128 rows) ==============================
+    const int q = warp & 3;
+    const int half = (warp - 2) >> 2;
+    uint8_t* slab = staging + (warp - 2) * 4096;
+    constexpr int kChunks = BN / 32;
+    const int c_lo = half * (kChunks / 2), c_hi = c_lo + kChunks / 2;
+    int as = 0; uint32_t aphase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int m_blk, n_blk;
+      const int z = tile / tiles_per_problem;
+      tile_coords(tile - z * tiles_per_problem, p.num_m, p.num_n, m_blk, n_blk);
+      const int z1 = z % p.nb1, z2 = z / p.nb1;
+      const int row0 = m_blk * TM + (int)rank * BM + q * 32;
+      epilogue_tile<BN, false>(p, &tmOut, &tmOut, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), row0 + lane, row0, n_blk * BN, z1, z2,
+                               slab, slab, lane, c_lo, c_hi, &tmem_full[as], aphase);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(&tmem_empty[as], 0);
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+    if (lane == 0) tma_store_wait_all();
+    __syncwarp();
+  }
+  tc_fence_before();
+  cluster_sync_all();                       // no CTA leaves while its peer may still touch its smem / TMEM / barriers
+  if (warp == 1) tmem_dealloc_2cta(tmem_base, Cfg::kTmemCols);
 }
 
 // ---- host side: TMA descriptors ---------------------------------------------------------------------------
@@ -492,6 +657,37 @@ static int launch_gemm_impl(const CUtensorMap& tmA, const CUtensorMap& tmB, Gemm
   return 0;
 }
 
+// 0 = never, 1 = whenever the shape allows (default).  MLT_GEMM_2CTA overrides.
+static int gemm_2cta_mode() {
+  static int mode = -1;
+  if (mode < 0) {
+    const char* e = getenv("MLT_GEMM_2CTA");
+    mode = e ? atoi(e) : 1;
+  }
+  return mode;
+}
+
+static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
+  using Cfg = Gemm2Cfg;
+  CUtensorMap tmOut;
+  if (make_tmap(&tmOut, p.out, p.N, p.M, p.ldo, p.out_f32 ? 32 : 64, 32, p.nb1, p.ob1, p.nb2, p.ob2, p.out_f32 ? 4 : 2)) return 1;
+  p.num_m = ceil_div(p.M, 256);
+  p.num_n = ceil_div(p.N, 256);
+  p.num_k = ceil_div(p.K, BK);
+  static bool attr_set[64] = {};
+  int dev = 0;
+  MLT_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    attr_set[dev & 63] = true;
+  }
+  long long tiles = (long long)p.num_m * p.num_n * p.nb1 * p.nb2;
+  int clusters = tiles > kNumSMs / 2 ? kNumSMs / 2 : (int)tiles;
+  gemm_bf16_2cta_kernel<<<2 * clusters, kGemmThreads, Cfg::kSmemBytes, st>>>(tmA, tmB, tmOut, p);
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
 template <int BN>
 static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
   // the slab path for a stored aux tensor: bf16 output (so output and aux slabs cover the same 64 columns), one problem
@@ -548,11 +744,20 @@ extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   MLT_REQUIRE(aux_mode == 0 || (((uintptr_t)aux % 16) == 0 && (ld_aux * 2) % 16 == 0), "mlt_gemm_bf16: aux must be 16-byte aligned");
   int BN = block_n;
   if (BN == 0) BN = (N >= 512 || (N % 256 == 0)) ? 256 : (N > 64 ? 128 : 64);
-  MLT_REQUIRE(BN == 64 || BN == 128 || BN == 256, "mlt_gemm_bf16: block_n must be 0, 64, 128 or 256");
+  MLT_REQUIRE(BN == 64 || BN == 128 || BN == 256 || BN == 512, "mlt_gemm_bf16: block_n must be 0, 64, 128, 256 or 512 (= 256 on a CTA pair)");
+  // CTA-pair kernel (256 x 256 tiles, cta_group::2): block_n 512 forces it, block_n 0 picks it when the shape fills the pairs
+  bool pair = BN == 512;
+  if (BN == 512) BN = 256;
+  // (few-tile problems go to split-K on single CTAs: twice as many units to spread the K slices over)
+  if (block_n == 0 && BN == 256 && gemm_2cta_mode() == 1 && N >= 256 && ceil_div(M, 256) * ceil_div(N, 256) >= 32 && aux_mode != 1 &&
+      aux_mode != 3)
+    pair = true;
+  if (pair) MLT_REQUIRE(aux_mode != 1 && aux_mode != 3, "mlt_gemm_bf16: the CTA-pair kernel has no stored-aux epilogue");
+  const int TM = pair ? 256 : BM;
   CUtensorMap tmA, tmB;
   if (!a_mn) { if (make_tmap(&tmA, A, K, M, lda, BK, BM)) return 1; }
   else       { if (make_tmap(&tmA, A, M, K, lda, 64, BK)) return 1; }
-  if (!b_mn) { if (make_tmap(&tmB, B, K, N, ldb, BK, BN)) return 1; }
+  if (!b_mn) { if (make_tmap(&tmB, B, K, N, ldb, BK, pair ? 128 : BN)) return 1; }
   else       { if (make_tmap(&tmB, B, N, K, ldb, 64, BK)) return 1; }
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
@@ -565,10 +770,11 @@ extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   p.im2col = 0;
   cudaStream_t st = (cudaStream_t)stream;
   // split-K: weight-gradient shapes (few output tiles, very long K) would otherwise occupy a handful of SMs
-  const int tiles = ceil_div(M, BM) * ceil_div(N, BN), num_k = ceil_div(K, BK);
+  const int tiles = ceil_div(M, TM) * ceil_div(N, BN), num_k = ceil_div(K, BK);
+  const int units = pair ? kNumSMs / 2 : kNumSMs;          // CTAs, or CTA pairs
   int splits = 1;
-  if (splitk_ws != nullptr && bias == nullptr && act == ACT_NONE && aux_mode == 0 && tiles * 2 <= kNumSMs && num_k >= 8) {
-    splits = kNumSMs / tiles;
+  if (splitk_ws != nullptr && bias == nullptr && act == ACT_NONE && aux_mode == 0 && tiles * 2 <= units && num_k >= 8) {
+    splits = units / tiles;
     if (splits > 16) splits = 16;
     if (splits > num_k / 4) splits = num_k / 4;
     if ((long long)splits * M * N * 4 > splitk_ws_bytes) splits = (int)(splitk_ws_bytes / ((long long)M * N * 4));
@@ -580,10 +786,12 @@ extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void*
     q.out = splitk_ws; q.ldo = N; q.out_f32 = 1;
     q.nb1 = splits; q.nb2 = 1; q.ob1 = (long long)M * N; q.ob2 = 0;
     q.splits = splits; q.kb_per_split = kbps;
-    int rc = BN == 256 ? launch_gemm<256>(tmA, tmB, q, st) : (BN == 128 ? launch_gemm<128>(tmA, tmB, q, st) : launch_gemm<64>(tmA, tmB, q, st));
+    int rc = pair ? launch_gemm_2cta(tmA, tmB, q, st)
+                  : (BN == 256 ? launch_gemm<256>(tmA, tmB, q, st) : (BN == 128 ? launch_gemm<128>(tmA, tmB, q, st) : launch_gemm<64>(tmA, tmB, q, st)));
     if (rc) return rc;
     return launch_splitk_reduce((const float*)splitk_ws, out, ldo, out_f32, M, N, splits, st);
   }
+  if (pair) return launch_gemm_2cta(tmA, tmB, p, st);
   if (BN == 256) return launch_gemm<256>(tmA, tmB, p, st);
   if (BN == 128) return launch_gemm<128>(tmA, tmB, p, st);
   return launch_gemm<64>(tmA, tmB, p, st);

@@ -168,3 +168,16 @@ def test_ffn_block_matches_torch(T, H, I, act):
     with torch.no_grad():
         y2 = ffn_tc(x, w1, b1, w2, b2, act)
     assert (y2.float() - yr).abs().max().item() < 3e-2 * max(1.0, yr.abs().max().item())
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(512, 256, 128), (1024, 768, 320), (712, 1000, 192)])
+def test_gemm_cta_pair(a_mn, b_mn, M, N, K):
+    """cta_group::2 kernel (256 x 256 tile on a CTA pair), forced with block_n=512."""
+    from ml_trainer_b200.ops.gemm import gemm, gemm_reference
+
+    a, b = _operands(M, N, K, a_mn, b_mn, seed=11)
+    bias = torch.randn(N, device=DEV).to(torch.bfloat16)
+    d = gemm(a, b, a_mn, b_mn, block_n=512, bias=bias, split_k=False)
+    torch.cuda.synchronize()
+    _check(d, gemm_reference(a, b, a_mn, b_mn, bias=bias), K, f"pair {M}x{N}x{K} a_mn={a_mn} b_mn={b_mn}")
