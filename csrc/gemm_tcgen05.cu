@@ -667,6 +667,15 @@ static int gemm_2cta_mode() {
   return mode;
 }
 
+static int gemm_2cta_min_k() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("MLT_GEMM_2CTA_MIN_K");
+    v = e ? atoi(e) : 512;
+  }
+  return v;
+}
+
 static int launch_gemm_2cta(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
   using Cfg = Gemm2Cfg;
   CUtensorMap tmOut;
@@ -749,8 +758,8 @@ extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   bool pair = BN == 512;
   if (BN == 512) BN = 256;
   // (few-tile problems go to split-K on single CTAs: twice as many units to spread the K slices over)
-  if (block_n == 0 && BN == 256 && gemm_2cta_mode() == 1 && N >= 256 && ceil_div(M, 256) * ceil_div(N, 256) >= 32 && aux_mode != 1 &&
-      aux_mode != 3)
+  if (block_n == 0 && BN == 256 && gemm_2cta_mode() == 1 && N >= 256 && K >= gemm_2cta_min_k() && ceil_div(M, 256) * ceil_div(N, 256) >= 32 &&
+      aux_mode != 1 && aux_mode != 3)
     pair = true;
   if (pair) MLT_REQUIRE(aux_mode != 1 && aux_mode != 3, "mlt_gemm_bf16: the CTA-pair kernel has no stored-aux epilogue");
   const int TM = pair ? 256 : BM;
