@@ -9,91 +9,12 @@
 // Channel reductions: a CTA covers 256/(C/8) rows per iteration, folds them through shared memory, CTAs of a channel
 // tile combine through fp32 atomics on a scratch accumulator + a ticket; the last CTA finalises.
 #include "common.cuh"
+#include "colreduce.cuh"
 #include "../include/mlt_b200.h"
 
 namespace mlt {
 
-constexpr int kBnThreads = 256;
-constexpr int kBnGroups = 32;         // channel groups (of 8) per CTA column tile: 256 channels, 512-byte row segments
-
-__device__ __forceinline__ void ld8(const __nv_bfloat16* p, float (&v)[8]) {
-  const uint4 raw = *reinterpret_cast<const uint4*>(p);
-  const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[j]));
-    v[2 * j] = f.x; v[2 * j + 1] = f.y;
-  }
-}
-__device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&v)[8]) {
-  uint4 o;
-  o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]); o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
-  *reinterpret_cast<uint4*>(p) = o;
-}
 template <typename P> __device__ __forceinline__ float ldp(const P* p, int i) { return to_float(p[i]); }
-
-// Two-quantity per-channel reduction over rows.  grid = (column tiles, R row slices).  F(offset_of_group, a[8], b[8])
-// accumulates one 8-channel group of one row.  A CTA folds its rows through shared memory and adds its per-channel
-// partials to acc[2][C] with fp32 atomics (a few hundred thousand per call, spread over 2*C addresses); the last CTA of
-// a tile (ticket) picks the totals up into tot[2][cw * 8] (shared memory), re-zeroes acc and returns true.
-template <typename F>
-__device__ __forceinline__ bool bn_reduce2(F f, float* acc, unsigned int* tickets, int M, int C, float* tot) {
-  const int C8 = C >> 3;
-  const int g_lo = blockIdx.x * kBnGroups;
-  const int cw = min(kBnGroups, C8 - g_lo);            // channel groups in this tile
-  const int rpi = kBnThreads / cw;                     // rows per iteration
-  const int cg = threadIdx.x % cw, rsub = threadIdx.x / cw;
-  const int R = gridDim.y;
-  const int rows_per = ceil_div(M, R);
-  const int r_lo = blockIdx.y * rows_per, r_hi = min(M, r_lo + rows_per);
-  float a[8], b[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) { a[j] = 0.f; b[j] = 0.f; }
-  if (rsub < rpi) {
-    const size_t col = (size_t)(g_lo + cg) * 8;
-    int r = r_lo + rsub;
-    for (; r + 3 * rpi < r_hi; r += 4 * rpi) {         // four independent rows in flight
-#pragma unroll
-      for (int u = 0; u < 4; ++u) f((size_t)(r + u * rpi) * C + col, a, b);
-    }
-    for (; r < r_hi; r += rpi) f((size_t)r * C + col, a, b);
-  }
-  __shared__ float sh[kBnThreads][17];
-  __shared__ bool is_last;
-#pragma unroll
-  for (int j = 0; j < 8; ++j) { sh[threadIdx.x][j] = a[j]; sh[threadIdx.x][8 + j] = b[j]; }
-  __syncthreads();
-  const int nch = cw * 8;
-  for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
-    const int g = ch >> 3, j = ch & 7;
-    float t0 = 0.f, t1 = 0.f;
-    for (int s = 0; s < rpi; ++s) { t0 += sh[s * cw + g][j]; t1 += sh[s * cw + g][8 + j]; }
-    if (R == 1) { tot[ch] = t0; tot[nch + ch] = t1; }
-    else {
-      atomicAdd(acc + g_lo * 8 + ch, t0);
-      atomicAdd(acc + C + g_lo * 8 + ch, t1);
-    }
-  }
-  if (R == 1) { __syncthreads(); return true; }
-  __threadfence();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const unsigned int tk = atomicAdd(&tickets[blockIdx.x], 1u);
-    is_last = tk == (unsigned int)R - 1;
-    if (is_last) tickets[blockIdx.x] = 0u;
-  }
-  __syncthreads();
-  if (!is_last) return false;
-  __threadfence();
-  for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
-    float* p0 = acc + g_lo * 8 + ch;
-    float* p1 = acc + C + g_lo * 8 + ch;
-    tot[ch] = __ldcg(p0); tot[nch + ch] = __ldcg(p1);
-    *p0 = 0.f; *p1 = 0.f;                              // ready for the next call on this stream
-  }
-  __syncthreads();
-  return true;
-}
 
 __global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ mean, float* __restrict__ rstd, float* __restrict__ run_mean,
@@ -106,7 +27,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ mean, f
 #pragma unroll
     for (int j = 0; j < 8; ++j) { a[j] += v[j]; b[j] = fmaf(v[j], v[j], b[j]); }
   };
-  if (!bn_reduce2(f, partial, tickets, M, C, tot)) return;
+  if (!col_reduce_atomic<true>(f, partial, tickets, M, C, tot)) return;
   const int g_lo = blockIdx.x * kBnGroups;
   const int nch = min(kBnGroups, (C >> 3) - g_lo) * 8;
   for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
@@ -181,7 +102,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
       b[j] += dz;
     }
   };
-  if (!bn_reduce2(f, partial, tickets, M, C, tot)) return;
+  if (!col_reduce_atomic<true>(f, partial, tickets, M, C, tot)) return;
   const int nch = cw * 8;
   for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
     const int c = g_lo * 8 + ch;

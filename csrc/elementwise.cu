@@ -1,6 +1,7 @@
 // Bandwidth-bound helpers around the GEMMs: activation backward, bias gradient (column sum),
 // dtype casts.  Everything is vectorised to 16-byte accesses; the roofline is bytes / HBM bandwidth.
 #include "common.cuh"
+#include "colreduce.cuh"
 #include "../include/mlt_b200.h"
 
 namespace mlt {
@@ -181,6 +182,28 @@ colsum_vec_kernel(const T* __restrict__ x, O* __restrict__ out, float* __restric
   }
 }
 
+// Bias gradients of the big GEMM layers: contiguous bf16 [M, N] with N a multiple of 8, read as a flat stream of 16-byte
+// groups and folded through shared memory + fp32 atomics (colreduce.cuh) - the same scheme as the BatchNorm reductions.
+template <typename O>
+__global__ void __launch_bounds__(kBnThreads)
+colsum_flat_kernel(const __nv_bfloat16* __restrict__ x, O* __restrict__ out, float* __restrict__ acc, unsigned int* __restrict__ tickets,
+                   int M, int N, int accumulate) {
+  __shared__ float tot[2 * kBnGroups * 8];
+  auto f = [&](size_t off, float (&a)[8], float (&b)[8]) {
+    float v[8];
+    ld8(x + off, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] += v[j];
+  };
+  if (!col_reduce_atomic<false>(f, acc, tickets, M, N, tot)) return;
+  const int g_lo = blockIdx.x * kBnGroups;
+  const int nch = min(kBnGroups, (N >> 3) - g_lo) * 8;
+  for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
+    const int c = g_lo * 8 + ch;
+    out[c] = from_float<O>((accumulate ? to_float(out[c]) : 0.f) + tot[ch]);
+  }
+}
+
 template <typename S, typename D>
 __global__ void __launch_bounds__(256) cast_kernel(const S* __restrict__ src, D* __restrict__ dst, long long n) {
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -253,6 +276,32 @@ extern "C" int mlt_colsum(const void* x, int x_bf16, void* out, int out_bf16, vo
     else CS(colsum_kernel, float, float);
   }
 #undef CS
+  MLT_LAUNCH_CHECK();
+  return 0;
+}
+
+// Fast path of mlt_colsum for contiguous bf16 inputs with N % 8 == 0.  scratch (zeroed once, left zero by every call):
+// [tickets 256 B][N fp32 accumulators].
+extern "C" long long mlt_colsum_flat_scratch_bytes(int N) { return 256 + (long long)N * 4; }
+
+extern "C" int mlt_colsum_flat(const void* x, void* out, int out_bf16, void* scratch, long long scratch_bytes, int M, int N,
+                               int accumulate, void* stream) {
+  MLT_REQUIRE(M > 0 && N > 0 && N % 8 == 0 && N / 8 <= 64 * kBnGroups, "mlt_colsum_flat: N (%d) must be a multiple of 8 up to 16384", N);
+  MLT_REQUIRE(scratch && scratch_bytes >= mlt_colsum_flat_scratch_bytes(N), "mlt_colsum_flat: scratch too small");
+  MLT_REQUIRE(((uintptr_t)x % 16) == 0, "mlt_colsum_flat: input must be 16-byte aligned");
+  const int C8 = N / 8;
+  const int tiles = ceil_div(C8, kBnGroups);
+  const int rpi = kBnThreads / (C8 < kBnGroups ? C8 : kBnGroups);
+  int R = (4 * kNumSMs) / tiles;
+  const int cap = ceil_div(M, rpi * 8);
+  if (R > cap) R = cap;
+  if (R < 1) R = 1;
+  unsigned int* tickets = (unsigned int*)scratch;
+  float* acc = (float*)((char*)scratch + 256);
+  dim3 grid(tiles, R);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (out_bf16) colsum_flat_kernel<__nv_bfloat16><<<grid, kBnThreads, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, acc, tickets, M, N, accumulate);
+  else colsum_flat_kernel<float><<<grid, kBnThreads, 0, st>>>((const __nv_bfloat16*)x, (float*)out, acc, tickets, M, N, accumulate);
   MLT_LAUNCH_CHECK();
   return 0;
 }

@@ -132,6 +132,96 @@ layernorm_bwd_dx_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat1
   }
 }
 
+// One-pass LayerNorm backward: dx as above AND the parameter gradients.  Warps loop over rows (grid sized to the machine,
+// two CTAs per SM); a lane always owns the same columns, so dgamma / dbeta partials stay in registers across rows, are folded
+// per CTA with shared-memory atomics and per grid with fp32 atomics on a scratch accumulator (zero at rest); the last CTA
+// (ticket) writes dgamma / dbeta and re-zeroes the accumulator.  dy and h are read once instead of twice.
+template <typename P, typename GO, int NV>
+__global__ void __launch_bounds__(256, 2)
+layernorm_bwd_fused_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ h, const float* __restrict__ mean,
+                           const float* __restrict__ rstd, const P* __restrict__ gamma, __nv_bfloat16* __restrict__ dx,
+                           GO* __restrict__ dgamma, GO* __restrict__ dbeta, float* __restrict__ acc, unsigned int* __restrict__ ticket,
+                           int T, int H) {
+  extern __shared__ float fold[];                       // [2][H]
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31;
+  const int nvec = H / 8;
+  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) fold[i] = 0.f;
+  __syncthreads();
+  float ag[NV][8], ab[NV][8];
+#pragma unroll
+  for (int c = 0; c < NV; ++c) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { ag[c][j] = 0.f; ab[c][j] = 0.f; }
+  }
+  const int warps = gridDim.x * (blockDim.x >> 5);
+  for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < T; row += warps) {
+    const float mu = mean[row], rs = rstd[row];
+    float gd[NV][8], xh[NV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int c = 0; c < NV; ++c) {
+      const int iv = lane + 32 * c;
+      if (iv < nvec) {
+        float gm[8];
+        unpack8(*reinterpret_cast<const uint4*>(dy + (size_t)row * H + iv * 8), gd[c]);
+        unpack8(*reinterpret_cast<const uint4*>(h + (size_t)row * H + iv * 8), xh[c]);
+        load_param8<P>(gamma, iv * 8, gm);               // L1-resident; keeping it in registers costs occupancy
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[c][j] = (xh[c][j] - mu) * rs;
+          ag[c][j] = fmaf(gd[c][j], xh[c][j], ag[c][j]);
+          ab[c][j] += gd[c][j];
+          gd[c][j] *= gm[j];
+          s1 += gd[c][j];
+          s2 = fmaf(gd[c][j], xh[c][j], s2);
+        }
+      }
+    }
+    s1 = warp_sum(s1) / (float)H;
+    s2 = warp_sum(s2) / (float)H;
+#pragma unroll
+    for (int c = 0; c < NV; ++c) {
+      const int iv = lane + 32 * c;
+      if (iv < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rs * (gd[c][j] - s1 - xh[c][j] * s2);
+        *reinterpret_cast<uint4*>(dx + (size_t)row * H + iv * 8) = pack8(o);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NV; ++c) {
+    const int iv = lane + 32 * c;
+    if (iv < nvec) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        atomicAdd(&fold[iv * 8 + j], ag[c][j]);
+        atomicAdd(&fold[H + iv * 8 + j], ab[c][j]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) atomicAdd(acc + i, fold[i]);
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tk = atomicAdd(ticket, 1u);
+    is_last = tk == gridDim.x - 1;
+    if (is_last) *ticket = 0u;
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  for (int i = threadIdx.x; i < H; i += blockDim.x) {
+    dgamma[i] = from_float<GO>(__ldcg(acc + i));
+    dbeta[i] = from_float<GO>(__ldcg(acc + H + i));
+    acc[i] = 0.f;
+    acc[H + i] = 0.f;
+  }
+}
+
 // dgamma[c] = sum_rows dy * xhat;  dbeta[c] = sum_rows dy   (column reduction, see colreduce.cuh)
 template <typename GO>
 __global__ void __launch_bounds__(256)
@@ -251,8 +341,10 @@ extern "C" int mlt_layernorm_fwd(const void* x, const void* res, const void* gam
   return 0;
 }
 
+// scratch (zeroed once, left zero by every call): [ticket 256 B][2*H fp32 accumulators]
 extern "C" long long mlt_layernorm_bwd_scratch_bytes(int T, int H) {
-  return ((long long)ceil_div(H, kBnTile) * 4 + 255) / 256 * 256 + (long long)ln_rows_split(T, H) * 2 * H * 4;
+  (void)T;
+  return 256 + 2LL * 1024 * 4 + 0 * H;
 }
 
 extern "C" int mlt_layernorm_bwd(const void* dy, const void* h, const void* mean, const void* rstd, const void* gamma,
@@ -261,23 +353,24 @@ extern "C" int mlt_layernorm_bwd(const void* dy, const void* h, const void* mean
   MLT_REQUIRE(H % 8 == 0 && H <= 8 * 32 * kMaxVecPerLane, "mlt_layernorm_bwd: width %d unsupported", H);
   MLT_REQUIRE(scratch && scratch_bytes >= mlt_layernorm_bwd_scratch_bytes(T, H), "mlt_layernorm_bwd: scratch too small");
   cudaStream_t st = (cudaStream_t)stream;
-  const int grid = ceil_div(T, 8);
-  if (params_bf16)
-    layernorm_bwd_dx_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean,
-        (const float*)rstd, (const __nv_bfloat16*)gamma, (__nv_bfloat16*)dx, T, H);
-  else
-    layernorm_bwd_dx_kernel<float><<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean,
-        (const float*)rstd, (const float*)gamma, (__nv_bfloat16*)dx, T, H);
-  MLT_LAUNCH_CHECK();
-  unsigned int* tickets = (unsigned int*)scratch;
-  float* partial = (float*)((char*)scratch + ((long long)ceil_div(H, kBnTile) * 4 + 255) / 256 * 256);
-  dim3 g2(ceil_div(H, kBnTile), ln_rows_split(T, H));
-  if (grads_bf16)
-    layernorm_bwd_params_kernel<__nv_bfloat16><<<g2, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean,
-        (const float*)rstd, (__nv_bfloat16*)dgamma, (__nv_bfloat16*)dbeta, partial, tickets, T, H);
-  else
-    layernorm_bwd_params_kernel<float><<<g2, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h, (const float*)mean,
-        (const float*)rstd, (float*)dgamma, (float*)dbeta, partial, tickets, T, H);
+  unsigned int* ticket = (unsigned int*)scratch;
+  float* acc = (float*)((char*)scratch + 256);
+  int grid = 2 * kNumSMs;
+  if (grid > ceil_div(T, 8)) grid = ceil_div(T, 8);
+  const size_t smem = (size_t)2 * H * sizeof(float);
+  const int nv = ceil_div(H / 8, 32);                       // 16-byte vectors per lane: sizes the register arrays
+#define LN_BWD_NV(P, GO, NV)                                                                                                   \
+  layernorm_bwd_fused_kernel<P, GO, NV><<<grid, 256, smem, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)h,               \
+      (const float*)mean, (const float*)rstd, (const P*)gamma, (__nv_bfloat16*)dx, (GO*)dgamma, (GO*)dbeta, acc, ticket, T, H)
+#define LN_BWD(P, GO)                                                                                                          \
+  do {                                                                                                                         \
+    if (nv == 1) LN_BWD_NV(P, GO, 1); else if (nv == 2) LN_BWD_NV(P, GO, 2); else if (nv == 3) LN_BWD_NV(P, GO, 3);            \
+    else LN_BWD_NV(P, GO, 4);                                                                                                  \
+  } while (0)
+  if (params_bf16) { if (grads_bf16) LN_BWD(__nv_bfloat16, __nv_bfloat16); else LN_BWD(__nv_bfloat16, float); }
+  else { if (grads_bf16) LN_BWD(float, __nv_bfloat16); else LN_BWD(float, float); }
+#undef LN_BWD
+#undef LN_BWD_NV
   MLT_LAUNCH_CHECK();
   return 0;
 }

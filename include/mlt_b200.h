@@ -211,6 +211,11 @@ int mlt_conv_dgrad_implicit(const void* dy, int B, int OH, int OW, int Co, const
  * an NHWC bf16 tensor, loaded with one cp.async.bulk.tensor...im2col and written back un-swizzled. */
 int mlt_im2col_probe(const void* x, int B, int H, int W, int C, int KH, int KW, int stride, int pad, long long m0, int r, int s, int c0,
                      int pixels, void* out, void* stream);
+/* Column sums of a contiguous bf16 [M, N] matrix, N a multiple of 8 (bias gradients of the GEMM layers): flat 16-byte streams,
+ * fp32 atomics fold.  scratch: mlt_colsum_flat_scratch_bytes(N), zeroed once, left zero by every call. */
+long long mlt_colsum_flat_scratch_bytes(int N);
+int mlt_colsum_flat(const void* x, void* out, int out_bf16, void* scratch, long long scratch_bytes, int M, int N, int accumulate,
+                    void* stream);
 int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
                           void* out_bf16, int T, int S, int H, void* stream);
 int mlt_embedding_bwd(const void* ids_i64, const void* dh_bf16, void* dword, long long V, void* dpos, int grads_bf16, int B,

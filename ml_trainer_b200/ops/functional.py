@@ -342,6 +342,13 @@ def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         if out is None:
             out = torch.empty(N, dtype=x.dtype, device=x.device)
         L = _lib.lib()
+        if (x.dtype == torch.bfloat16 and x.is_contiguous() and N % 8 == 0 and N <= 16384 and M >= 1024 and x.data_ptr() % 16 == 0
+                and out.dtype in (torch.float32, torch.bfloat16)):
+            ws = scratch(x.device, "colsum_flat", 256 + 16384 * 4)
+            check(L.mlt_colsum_flat(ptr(x), ptr(out), _c_int(int(out.dtype == torch.bfloat16)), ptr(ws), _c_ll(ws.numel()), _c_int(M),
+                                    _c_int(N), _c_int(0), stream_handle()), "mlt_colsum_flat")
+            launches.bump("colsum_flat")
+            return out
         L.mlt_colsum_scratch_bytes.restype = _c_ll
         nbytes = L.mlt_colsum_scratch_bytes(_c_int(M), _c_int(N))
         ws = scratch(x.device, "colsum", nbytes)
