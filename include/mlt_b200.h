@@ -216,6 +216,10 @@ int mlt_im2col_probe(const void* x, int B, int H, int W, int C, int KH, int KW, 
 long long mlt_colsum_flat_scratch_bytes(int N);
 int mlt_colsum_flat(const void* x, void* out, int out_bf16, void* scratch, long long scratch_bytes, int M, int N, int accumulate,
                     void* stream);
+/* Dropout with a Philox4x32-10 mask that is a function of (seed, *step_ptr, call_id, element): the same call on the upstream
+ * gradient is the backward pass; *step_ptr lives in device memory so captured graphs replay with fresh masks. */
+int mlt_dropout(const void* x, void* y, long long n, float p, unsigned long long seed, const void* step_ptr, unsigned int call_id,
+                int is_bf16, void* stream);
 int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
                           void* out_bf16, int T, int S, int H, void* stream);
 int mlt_embedding_bwd(const void* ids_i64, const void* dh_bf16, void* dword, long long V, void* dpos, int grads_bf16, int B,

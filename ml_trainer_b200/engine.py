@@ -114,6 +114,10 @@ class StepEngine:
         from .utils.tracing import phase
 
         self.reducer.arm()
+        if getattr(self.model, "_mlt_uses_dropout", False):
+            from .ops.functional import dropout_begin_step
+
+            dropout_begin_step(self.device)
         with phase("forward+loss"):
             outputs, loss, dl = self._forward_loss(self.model, inputs, targets, train=True)
         with phase("backward"):

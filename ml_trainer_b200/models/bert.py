@@ -23,11 +23,13 @@ from . import register
 class BertConfig:
     def __init__(self, vocab_size=30522, hidden_size=768, num_hidden_layers=12, num_attention_heads=12,
                  intermediate_size=3072, max_position_embeddings=512, type_vocab_size=2, layer_norm_eps=1e-12,
-                 num_labels=2, initializer_range=0.02):
+                 num_labels=2, initializer_range=0.02, hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0):
         self.vocab_size, self.hidden_size, self.num_hidden_layers = vocab_size, hidden_size, num_hidden_layers
         self.num_attention_heads, self.intermediate_size = num_attention_heads, intermediate_size
         self.max_position_embeddings, self.type_vocab_size = max_position_embeddings, type_vocab_size
         self.layer_norm_eps, self.num_labels, self.initializer_range = layer_norm_eps, num_labels, initializer_range
+        # HuggingFace's default is 0.1 for both; the benchmark runs both arms at 0, so that is the default here
+        self.hidden_dropout_prob, self.attention_probs_dropout_prob = hidden_dropout_prob, attention_probs_dropout_prob
 
 
 class _LN(nn.Module):
@@ -50,11 +52,12 @@ class BertEmbeddings(nn.Module):
         self.position_embeddings = nn.Embedding(c.max_position_embeddings, c.hidden_size)
         self.token_type_embeddings = nn.Embedding(c.type_vocab_size, c.hidden_size)
         self.LayerNorm = _LN(c.hidden_size, c.layer_norm_eps)
+        self.p_drop = c.hidden_dropout_prob
 
     def forward(self, ids):
         h = F.bert_embeddings(ids, self.word_embeddings.weight, self.position_embeddings.weight,
                               self.token_type_embeddings.weight)
-        return self.LayerNorm(h)
+        return F.dropout(self.LayerNorm(h), self.p_drop, self.training)
 
 
 class BertSelfAttention(nn.Module):
@@ -64,6 +67,7 @@ class BertSelfAttention(nn.Module):
         self.key = nn.Linear(c.hidden_size, c.hidden_size)
         self.value = nn.Linear(c.hidden_size, c.hidden_size)
         self.heads = c.num_attention_heads
+        self.p_attn = c.attention_probs_dropout_prob
         # Ask the FusedOptimizer to lay the three projections out back to back: one [3H, H] GEMM operand (and gradient
         # sink) under the unchanged HuggingFace parameter names.
         for i, lin in enumerate((self.query, self.key, self.value)):
@@ -73,6 +77,8 @@ class BertSelfAttention(nn.Module):
     def forward(self, x):
         from ..ops.gemm import linear_packed, linear_packed_ok
 
+        if self.p_attn > 0.0 and self.training:
+            return self._forward_with_prob_dropout(x)
         wpack = getattr(self.query.weight, "_mlt_packed", None)
         bpack = getattr(self.query.bias, "_mlt_packed", None)
         if bpack is not None and linear_packed_ok(x, wpack, bpack):
@@ -83,14 +89,32 @@ class BertSelfAttention(nn.Module):
         return F.attention(q, k, v, self.heads)
 
 
+def _attn_prob_dropout(self, x):
+    """Attention with dropout on the probabilities: the fused kernels keep P on chip, so this (training-only, off in the
+    benchmark) configuration materialises it: projections on the tensor cores, softmax / dropout / PV as batched ops."""
+    B, S, HD = x.shape
+    d = HD // self.heads
+    q = F.linear_act(x, self.query.weight, self.query.bias).view(B, S, self.heads, d).transpose(1, 2)
+    k = F.linear_act(x, self.key.weight, self.key.bias).view(B, S, self.heads, d).transpose(1, 2)
+    v = F.linear_act(x, self.value.weight, self.value.bias).view(B, S, self.heads, d).transpose(1, 2)
+    p = torch.softmax((q @ k.transpose(-1, -2)).float() / math.sqrt(d), dim=-1).to(x.dtype)
+    p = F.dropout(p, self.p_attn, True)
+    return (p @ v).transpose(1, 2).reshape(B, S, HD)
+
+
+BertSelfAttention._forward_with_prob_dropout = _attn_prob_dropout
+
+
 class BertSelfOutput(nn.Module):
     def __init__(self, c):
         super().__init__()
         self.dense = nn.Linear(c.hidden_size, c.hidden_size)
         self.LayerNorm = _LN(c.hidden_size, c.layer_norm_eps)
+        self.p_drop = c.hidden_dropout_prob
 
     def forward(self, ctx, x):
-        return self.LayerNorm(F.linear_act(ctx, self.dense.weight, self.dense.bias), residual=x)
+        h = F.dropout(F.linear_act(ctx, self.dense.weight, self.dense.bias), self.p_drop, self.training)
+        return self.LayerNorm(h, residual=x)
 
 
 class BertAttention(nn.Module):
@@ -117,9 +141,11 @@ class BertOutput(nn.Module):
         super().__init__()
         self.dense = nn.Linear(c.intermediate_size, c.hidden_size)
         self.LayerNorm = _LN(c.hidden_size, c.layer_norm_eps)
+        self.p_drop = c.hidden_dropout_prob
 
     def forward(self, f, x):
-        return self.LayerNorm(F.linear_act(f, self.dense.weight, self.dense.bias), residual=x)
+        h = F.dropout(F.linear_act(f, self.dense.weight, self.dense.bias), self.p_drop, self.training)
+        return self.LayerNorm(h, residual=x)
 
 
 class BertLayer(nn.Module):
@@ -135,7 +161,8 @@ class BertLayer(nn.Module):
         if a.is_cuda and a.dtype == torch.bfloat16 and F.use_native(a, i.weight):
             from ..ops.gemm import ffn_tc          # both FFN GEMMs + GELU (and its backward) as one autograd node
 
-            return self.output.LayerNorm(ffn_tc(a, i.weight, i.bias, o.weight, o.bias, "gelu"), residual=a)
+            h = F.dropout(ffn_tc(a, i.weight, i.bias, o.weight, o.bias, "gelu"), self.output.p_drop, self.training)
+            return self.output.LayerNorm(h, residual=a)
         return self.output(self.intermediate(a), a)
 
 
@@ -178,6 +205,7 @@ class BertForSequenceClassification(nn.Module):
         c = self.config = config or BertConfig(**kw)
         self.bert = BertModel(c)
         self.classifier = nn.Linear(c.hidden_size, c.num_labels)
+        self._mlt_uses_dropout = c.hidden_dropout_prob > 0 or c.attention_probs_dropout_prob > 0
         self.apply(self._init_weights)
 
     def _init_weights(self, m):
@@ -190,7 +218,7 @@ class BertForSequenceClassification(nn.Module):
             nn.init.normal_(m.weight, mean=0.0, std=std)
 
     def forward(self, input_ids):
-        pooled = self.bert(input_ids)
+        pooled = F.dropout(self.bert(input_ids), self.config.hidden_dropout_prob, self.training)
         return F.linear_act(pooled, self.classifier.weight, self.classifier.bias).float()
 
 

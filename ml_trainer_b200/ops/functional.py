@@ -365,6 +365,67 @@ def colsum(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
 
 
 # ----------------------------------------------------------------------------------------------
+# dropout: Philox mask = f(seed, device step counter, call site, element); nothing stored for backward
+# ----------------------------------------------------------------------------------------------
+_drop = {"seed": 0x5DEECE66D, "call": 0, "step": {}}
+
+
+def dropout_seed(seed: int) -> None:
+    _drop["seed"] = int(seed) & 0xFFFFFFFFFFFFFFFF
+
+
+def _drop_step(device: torch.device) -> torch.Tensor:
+    t = _drop["step"].get(device.index)
+    if t is None:
+        t = torch.zeros(1, dtype=torch.int64, device=device)
+        _drop["step"][device.index] = t
+    return t
+
+
+def dropout_begin_step(device: torch.device) -> None:
+    """Called once per training step (inside the captured graph): advances the device-side step counter the masks are
+    keyed on and restarts the call-site numbering."""
+    _drop["call"] = 0
+    if device.type == "cuda":
+        _drop_step(device).add_(1)
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p, call_id):
+        x = x.contiguous()
+        y = torch.empty_like(x)
+        ctx.cfg = (p, call_id)
+        _DropoutFn._run(x, y, p, call_id)
+        return y
+
+    @staticmethod
+    def _run(x, y, p, call_id):
+        check(_lib.lib().mlt_dropout(ptr(x), ptr(y), _c_ll(x.numel()), ctypes.c_float(p), ctypes.c_ulonglong(_drop["seed"]),
+                                     ptr(_drop_step(x.device)), ctypes.c_uint(call_id), _c_int(int(x.dtype == torch.bfloat16)),
+                                     stream_handle()), "mlt_dropout")
+        launches.bump("dropout")
+
+    @staticmethod
+    def backward(ctx, dy):
+        p, call_id = ctx.cfg
+        dy = dy.contiguous()
+        dx = torch.empty_like(dy)
+        _DropoutFn._run(dy, dx, p, call_id)          # same mask: same (seed, step, call site)
+        return dx, None, None
+
+
+def dropout(x: torch.Tensor, p: float, training: bool = True) -> torch.Tensor:
+    """Inverted dropout.  Native path: mask regenerated in backward from a counter-based generator (csrc/dropout.cu)."""
+    if not training or p <= 0.0:
+        return x
+    if use_native(x) and x.dtype in (torch.float32, torch.bfloat16):
+        _drop["call"] += 1
+        return _DropoutFn.apply(x, float(p), _drop["call"])
+    return torch.nn.functional.dropout(x, p, True)
+
+
+# ----------------------------------------------------------------------------------------------
 # transformer pieces: LayerNorm (+ residual), attention core, embeddings  (bf16 activations)
 # ----------------------------------------------------------------------------------------------
 class _LayerNormFn(torch.autograd.Function):

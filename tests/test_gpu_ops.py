@@ -156,3 +156,28 @@ def test_fused_update_partial_ranges():
     delta = opt.master - before
     assert torch.allclose(delta[lo:hi], torch.full_like(delta[lo:hi], -0.1))
     assert delta[:lo].abs().max() == 0 and delta[hi:].abs().max() == 0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_dropout_philox_mask(dtype):
+    """Keep rate, scaling, backward regenerates the forward's mask, masks change with the device-side step counter."""
+    from ml_trainer_b200.ops import functional as F
+
+    dev = torch.device("cuda", 0)
+    p = 0.25
+    x = torch.ones(1 << 20, device=dev, dtype=dtype).requires_grad_()
+    F.dropout_begin_step(dev)
+    y = F.dropout(x, p, True)
+    keep = (y != 0).float().mean().item()
+    assert abs(keep - (1 - p)) < 5e-3, keep
+    nz = y[y != 0].float()
+    assert torch.allclose(nz, torch.full_like(nz, 1 / (1 - p)), rtol=1e-2)
+    g = torch.full_like(y, 2.0)
+    y.backward(g)
+    assert torch.equal((x.grad != 0), (y != 0))            # same mask in backward
+    assert torch.allclose(x.grad[x.grad != 0].float(), torch.full_like(nz, 2 / (1 - p)), rtol=1e-2)
+    F.dropout_begin_step(dev)
+    y2 = F.dropout(x.detach(), p, True)
+    diff = ((y2 != 0) != (y != 0)).float().mean().item()
+    assert 0.25 < diff < 0.5, diff                         # independent masks: 2 p (1 - p) = 0.375
+    assert F.dropout(x, p, False) is x

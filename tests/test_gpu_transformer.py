@@ -239,3 +239,29 @@ def test_packed_qkv_matches_separate_projections():
         a, b = grads[0][n], grads[1][n]
         rel = (a - b).norm() / (b.norm() + 1e-6)
         assert rel < 0.05, (n, rel.item())
+
+
+def test_trainer_bert_tiny_with_dropout(tmp_path):
+    """Hidden + attention-probability dropout through the Trainer: trains, and graph replays draw fresh masks."""
+    from ml_trainer_b200 import SyntheticDataset, Trainer, build_model
+
+    tr = SyntheticDataset((64,), 2, length=96, kind="tokens", vocab=1000, seed=1)
+    m = build_model("bert_tiny", hidden_dropout_prob=0.1, attention_probs_dropout_prob=0.1)
+    assert m._mlt_uses_dropout
+    t = Trainer(m, datasets=(tr, tr), epochs=4, batch_size=16, optimizer="adamw", lr=1e-3, dtype="bf16", model_dir=str(tmp_path),
+                progress=False, metric="accuracy")
+    t.fit()
+    assert t.train_losses[-1] < t.train_losses[0]
+    assert t.engine.graph_replays > 0
+    # same batch twice in train mode: outputs differ because the step counter moved; in eval mode they are identical
+    ids = torch.randint(0, 1000, (4, 64), device=DEV)
+    from ml_trainer_b200.ops import functional as F
+
+    t.model.train()
+    with torch.no_grad():
+        F.dropout_begin_step(torch.device(DEV)); a = t.model(ids)
+        F.dropout_begin_step(torch.device(DEV)); b = t.model(ids)
+    assert not torch.equal(a, b)
+    t.model.eval()
+    with torch.no_grad():
+        assert torch.equal(t.model(ids), t.model(ids))
