@@ -16,6 +16,20 @@ namespace mlt {
 
 template <typename P> __device__ __forceinline__ float ldp(const P* p, int i) { return to_float(p[i]); }
 
+// Which of the 8 elements at element offset `off` passed the forward ReLU: from the 1-bit-per-element mask the forward
+// wrote (one byte instead of 16), or recomputed from y when no mask was kept.
+template <bool RELU>
+__device__ __forceinline__ unsigned int relu_bits(const __nv_bfloat16* y, const unsigned char* mask, size_t off) {
+  if (!RELU) return 0xFFu;
+  if (mask != nullptr) return mask[off >> 3];
+  float o[8];
+  ld8(y + off, o);
+  unsigned int b = 0;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) b |= (o[j] > 0.f ? 1u : 0u) << j;
+  return b;
+}
+
 __global__ void __launch_bounds__(kBnThreads)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ mean, float* __restrict__ rstd, float* __restrict__ run_mean,
                 float* __restrict__ run_var, float momentum, float eps, float* __restrict__ partial, unsigned int* __restrict__ tickets,
@@ -48,7 +62,7 @@ template <typename P, bool RES, bool RELU>
 __global__ void __launch_bounds__(kBnThreads)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd,
                 const P* __restrict__ gamma, const P* __restrict__ beta, const __nv_bfloat16* __restrict__ residual,
-                __nv_bfloat16* __restrict__ y, long long total, int C8) {
+                __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ mask, long long total, int C8) {
   const long long step = (long long)gridDim.x * kBnThreads;         // a multiple of C8 (host guarantees it)
   long long i = (long long)blockIdx.x * kBnThreads + threadIdx.x;
   const int c0 = (int)(i % C8) * 8;
@@ -62,13 +76,16 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ m
     float v[8], r[8];
     ld8(x + e * 8, v);
     if (RES) ld8(residual + e * 8, r);
+    unsigned int bits = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       float o = fmaf(v[j], sc[j], sf[j]);
       if (RES) o += r[j];
+      if (RELU) bits |= (o > 0.f ? 1u : 0u) << j;
       v[j] = RELU ? fmaxf(o, 0.f) : o;
     }
     st8(y + e * 8, v);
+    if (RELU && mask != nullptr) mask[e] = (unsigned char)bits;      // 1 bit per element: all backward needs of y
   };
   for (; i + 3 * step < total; i += 4 * step) {
 #pragma unroll
@@ -80,9 +97,10 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ m
 // dgamma[c] = sum dz * xhat, dbeta[c] = sum dz, with dz = dy * (y > 0) when the forward had a ReLU
 template <typename G, bool RELU>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
-                     const float* __restrict__ mean, const float* __restrict__ rstd, G* __restrict__ dgamma, G* __restrict__ dbeta,
-                     float* __restrict__ sums, float* __restrict__ partial, unsigned int* __restrict__ tickets, int M, int C) {
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const unsigned char* __restrict__ mask,
+                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd,
+                     G* __restrict__ dgamma, G* __restrict__ dbeta, float* __restrict__ sums, float* __restrict__ partial,
+                     unsigned int* __restrict__ tickets, int M, int C) {
   __shared__ float tot[2 * kBnGroups * 8];
   const int g_lo = blockIdx.x * kBnGroups;
   const int cw = min(kBnGroups, (C >> 3) - g_lo);
@@ -91,13 +109,13 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 #pragma unroll
   for (int j = 0; j < 8; ++j) mu[j] = mean[c0 + j];
   auto f = [&](size_t off, float (&a)[8], float (&b)[8]) {
-    float g[8], v[8], o[8];
+    float g[8], v[8];
     ld8(dy + off, g);
     ld8(x + off, v);
-    if (RELU) ld8(y + off, o);
+    const unsigned int bits = relu_bits<RELU>(y, mask, off);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float dz = (RELU && !(o[j] > 0.f)) ? 0.f : g[j];
+      const float dz = (RELU && !((bits >> j) & 1u)) ? 0.f : g[j];
       a[j] = fmaf(dz, v[j] - mu[j], a[j]);          // sum dz (x - mean); the 1/std factor is applied once at the end
       b[j] += dz;
     }
@@ -117,8 +135,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 // dx = gamma * rstd * (dz - dbeta/M - xhat * dgamma/M);  dres = dz (gradient of the fused residual input)
 template <typename P, bool RES, bool RELU>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
-                    const float* __restrict__ mean, const float* __restrict__ rstd, const P* __restrict__ gamma,
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const unsigned char* __restrict__ mask,
+                    const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd, const P* __restrict__ gamma,
                     const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, long long total,
                     int C8, float inv_M) {
   const long long step = (long long)gridDim.x * kBnThreads;
@@ -136,13 +154,13 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     mu[j] = mean[c0 + j];
   }
   auto one = [&](long long e) {
-    float g[8], v[8], o[8], d[8];
+    float g[8], v[8], d[8];
     ld8(dy + e * 8, g);
     ld8(x + e * 8, v);
-    if (RELU) ld8(y + e * 8, o);
+    const unsigned int bits = relu_bits<RELU>(y, mask, (size_t)e * 8);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const float dz = (RELU && !(o[j] > 0.f)) ? 0.f : g[j];
+      const float dz = (RELU && !((bits >> j) & 1u)) ? 0.f : g[j];
       d[j] = fmaf(A[j], dz, fmaf(Bc[j], v[j] - mu[j], K[j]));
       g[j] = dz;
     }
@@ -213,42 +231,42 @@ extern "C" int mlt_bn_stats(const void* x, void* mean, void* rstd, void* run_mea
 
 template <typename P>
 static void bn_apply_launch(int g, cudaStream_t st, const void* x, const void* mean, const void* rstd, const void* gamma,
-                            const void* beta, const void* residual, void* y, long long total, int C8, int relu) {
+                            const void* beta, const void* residual, void* y, void* mask, long long total, int C8, int relu) {
 #define BN_AP(RES, RELU)                                                                                                      \
   bn_apply_kernel<P, RES, RELU><<<g, kBnThreads, 0, st>>>((const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd,        \
-      (const P*)gamma, (const P*)beta, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, total, C8)
+      (const P*)gamma, (const P*)beta, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, (unsigned char*)mask, total, C8)
   if (residual) { if (relu) BN_AP(true, true); else BN_AP(true, false); }
   else { if (relu) BN_AP(false, true); else BN_AP(false, false); }
 #undef BN_AP
 }
 
 extern "C" int mlt_bn_apply(const void* x, const void* mean, const void* rstd, const void* gamma, const void* beta, int params_bf16,
-                            const void* residual, void* y, long long M, int C, int relu, void* stream) {
+                            const void* residual, void* y, void* relu_mask, long long M, int C, int relu, void* stream) {
   MLT_REQUIRE(bn_shape_ok(C), "mlt_bn_apply: channels (%d) must be a multiple of 8", C);
   cudaStream_t st = (cudaStream_t)stream;
   const int C8 = C / 8;
   const long long total = M * C8;
   const int g = bn_grid(total, C8);
-  if (params_bf16) bn_apply_launch<__nv_bfloat16>(g, st, x, mean, rstd, gamma, beta, residual, y, total, C8, relu);
-  else bn_apply_launch<float>(g, st, x, mean, rstd, gamma, beta, residual, y, total, C8, relu);
+  if (params_bf16) bn_apply_launch<__nv_bfloat16>(g, st, x, mean, rstd, gamma, beta, residual, y, relu_mask, total, C8, relu);
+  else bn_apply_launch<float>(g, st, x, mean, rstd, gamma, beta, residual, y, relu_mask, total, C8, relu);
   MLT_LAUNCH_CHECK();
   return 0;
 }
 
 template <typename P>
-static void bn_bwd_apply_launch(int g, cudaStream_t st, const void* dy, const void* y, const void* x, const void* mean,
+static void bn_bwd_apply_launch(int g, cudaStream_t st, const void* dy, const void* y, const void* mask, const void* x, const void* mean,
                                 const void* rstd, const void* gamma, const float* su, void* dx, void* dres, long long total, int C8,
                                 float inv_M, int relu) {
 #define BN_BA(RES, RELU)                                                                                                      \
   bn_bwd_apply_kernel<P, RES, RELU><<<g, kBnThreads, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,                 \
-      (const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd, (const P*)gamma, su, (__nv_bfloat16*)dx,                 \
+      (const unsigned char*)mask, (const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd, (const P*)gamma, su, (__nv_bfloat16*)dx,                 \
       (__nv_bfloat16*)dres, total, C8, inv_M)
   if (dres) { if (relu) BN_BA(true, true); else BN_BA(true, false); }
   else { if (relu) BN_BA(false, true); else BN_BA(false, false); }
 #undef BN_BA
 }
 
-extern "C" int mlt_bn_bwd(const void* dy, const void* y, const void* x, const void* mean, const void* rstd, const void* gamma,
+extern "C" int mlt_bn_bwd(const void* dy, const void* y, const void* relu_mask, const void* x, const void* mean, const void* rstd, const void* gamma,
                           int params_bf16, void* dx, void* dres, void* dgamma, void* dbeta, int grads_bf16, void* scratch,
                           long long scratch_bytes, int M, int C, int relu, void* stream) {
   MLT_REQUIRE(M > 0 && bn_shape_ok(C), "mlt_bn_bwd: channels (%d) must be a multiple of 8", C);
@@ -259,7 +277,7 @@ extern "C" int mlt_bn_bwd(const void* dy, const void* y, const void* x, const vo
   dim3 grid(ceil_div(C / 8, kBnGroups), bn_rows_split(M, C));
 #define BN_RD(G, RELU)                                                                                                        \
   bn_bwd_reduce_kernel<G, RELU><<<grid, kBnThreads, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,                  \
-      (const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd, (G*)dgamma, (G*)dbeta, su, pa, tk, M, C)
+      (const unsigned char*)relu_mask, (const __nv_bfloat16*)x, (const float*)mean, (const float*)rstd, (G*)dgamma, (G*)dbeta, su, pa, tk, M, C)
   if (grads_bf16) { if (relu) BN_RD(__nv_bfloat16, true); else BN_RD(__nv_bfloat16, false); }
   else { if (relu) BN_RD(float, true); else BN_RD(float, false); }
 #undef BN_RD
@@ -268,8 +286,8 @@ extern "C" int mlt_bn_bwd(const void* dy, const void* y, const void* x, const vo
   const long long total = (long long)M * C8;
   const int g = bn_grid(total, C8);
   const float inv_M = 1.0f / (float)M;
-  if (params_bf16) bn_bwd_apply_launch<__nv_bfloat16>(g, st, dy, y, x, mean, rstd, gamma, su, dx, dres, total, C8, inv_M, relu);
-  else bn_bwd_apply_launch<float>(g, st, dy, y, x, mean, rstd, gamma, su, dx, dres, total, C8, inv_M, relu);
+  if (params_bf16) bn_bwd_apply_launch<__nv_bfloat16>(g, st, dy, y, relu_mask, x, mean, rstd, gamma, su, dx, dres, total, C8, inv_M, relu);
+  else bn_bwd_apply_launch<float>(g, st, dy, y, relu_mask, x, mean, rstd, gamma, su, dx, dres, total, C8, inv_M, relu);
   MLT_LAUNCH_CHECK();
   return 0;
 }

@@ -243,9 +243,11 @@ int mlt_avgpool_nhwc_bwd(const void* dy, void* dx, int B, int HW, int C, void* s
 long long mlt_bn_scratch_bytes(int M, int C);
 int mlt_bn_stats(const void* x, void* mean, void* rstd, void* run_mean, void* run_var, float momentum, float eps, void* scratch,
                  long long scratch_bytes, int M, int C, void* stream);
+/* relu_mask (optional, M*C/8 bytes): the forward writes one bit per element (output > 0); the backward then reads that byte
+ * per 8 elements instead of 16 bytes of y (pass y = NULL there). */
 int mlt_bn_apply(const void* x, const void* mean, const void* rstd, const void* gamma, const void* beta, int params_bf16,
-                 const void* residual, void* y, long long M, int C, int relu, void* stream);
-int mlt_bn_bwd(const void* dy, const void* y, const void* x, const void* mean, const void* rstd, const void* gamma, int params_bf16,
+                 const void* residual, void* y, void* relu_mask, long long M, int C, int relu, void* stream);
+int mlt_bn_bwd(const void* dy, const void* y, const void* relu_mask, const void* x, const void* mean, const void* rstd, const void* gamma, int params_bf16,
                void* dx, void* dres, void* dgamma, void* dbeta, int grads_bf16, void* scratch, long long scratch_bytes, int M, int C,
                int relu, void* stream);
 

@@ -186,17 +186,19 @@ class _BatchNormFn(torch.autograd.Function):
         check(L.mlt_bn_stats(ptr(x2), ptr(mean), ptr(rstd), ptr(run_mean), ptr(run_var), _c_f(momentum), _c_f(eps), ptr(ws),
                              _c_ll(ws.numel()), _c_int(M), _c_int(C), stream_handle()), "mlt_bn_stats")
         y = torch.empty_like(x2)
+        # backward only needs to know WHICH outputs the ReLU passed: one bit per element instead of re-reading y
+        mask = torch.empty(M * C // 8, dtype=torch.uint8, device=x.device) if relu else None
         check(L.mlt_bn_apply(ptr(x2), ptr(mean), ptr(rstd), ptr(gamma), ptr(beta), _c_int(int(gamma.dtype == torch.bfloat16)),
-                             ptr(r2), ptr(y), _c_ll(M), _c_int(C), _c_int(int(relu)), stream_handle()), "mlt_bn_apply")
+                             ptr(r2), ptr(y), ptr(mask), _c_ll(M), _c_int(C), _c_int(int(relu)), stream_handle()), "mlt_bn_apply")
         launches.bump("bn_fwd", 2)
-        ctx.save_for_backward(x2, y, mean, rstd, gamma)
+        ctx.save_for_backward(x2, mask, mean, rstd, gamma)
         ctx.cfg = (relu, residual is not None, x.shape)
         ctx.params = (gparam, bparam)
         return y.view(x.shape)
 
     @staticmethod
     def backward(ctx, dy):
-        x2, y, mean, rstd, gamma = ctx.saved_tensors
+        x2, mask, mean, rstd, gamma = ctx.saved_tensors
         relu, has_res, shape = ctx.cfg
         gparam, bparam = ctx.params
         M, C = x2.shape
@@ -210,7 +212,7 @@ class _BatchNormFn(torch.autograd.Function):
         L = _lib.lib()
         L.mlt_bn_scratch_bytes.restype = _c_ll
         ws = scratch(x2.device, "bn", L.mlt_bn_scratch_bytes(_c_int(M), _c_int(C)))
-        check(L.mlt_bn_bwd(ptr(dy2), ptr(y), ptr(x2), ptr(mean), ptr(rstd), ptr(gamma), _c_int(int(gamma.dtype == torch.bfloat16)),
+        check(L.mlt_bn_bwd(ptr(dy2), None, ptr(mask), ptr(x2), ptr(mean), ptr(rstd), ptr(gamma), _c_int(int(gamma.dtype == torch.bfloat16)),
                            ptr(dx), ptr(dres), ptr(dg), ptr(db), _c_int(int(gdt == torch.bfloat16)), ptr(ws), _c_ll(ws.numel()),
                            _c_int(M), _c_int(C), _c_int(int(relu)), stream_handle()), "mlt_bn_bwd")
         launches.bump("bn_bwd", 2)
@@ -234,7 +236,7 @@ def batch_norm_nhwc(x, bn: torch.nn.BatchNorm2d, relu: bool = False, residual: O
     y = torch.empty_like(x2)
     r2 = residual.contiguous().view(-1, C) if residual is not None else None
     check(_lib.lib().mlt_bn_apply(ptr(x2), ptr(bn.running_mean), ptr(rstd), ptr(bn.weight), ptr(bn.bias),
-                                  _c_int(int(bn.weight.dtype == torch.bfloat16)), ptr(r2), ptr(y), _c_ll(x2.shape[0]), _c_int(C),
+                                  _c_int(int(bn.weight.dtype == torch.bfloat16)), ptr(r2), ptr(y), None, _c_ll(x2.shape[0]), _c_int(C),
                                   _c_int(int(relu)), stream_handle()), "mlt_bn_apply")
     launches.bump("bn_apply")
     return y.view(x.shape)
