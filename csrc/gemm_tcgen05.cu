@@ -784,8 +784,8 @@ extern "C" int mlt_gemm_bf16(const void* A, long long lda, int a_mn, const void*
   int splits = 1;
   if (splitk_ws != nullptr && bias == nullptr && act == ACT_NONE && aux_mode == 0 && tiles * 2 <= units && num_k >= 8) {
     splits = units / tiles;
-    if (splits > 16) splits = 16;
-    if (splits > num_k / 4) splits = num_k / 4;
+    if (splits > 128) splits = 128;                 // tiny weight gradients (64 x 64 over 800 K pixels): one K slice per SM
+    if (splits > num_k / 8) splits = num_k / 8;     // at least 8 k-blocks (512 reduction rows) per slice
     if ((long long)splits * M * N * 4 > splitk_ws_bytes) splits = (int)(splitk_ws_bytes / ((long long)M * N * 4));
   }
   if (splits > 1) {
@@ -897,8 +897,8 @@ extern "C" int mlt_conv_wgrad_implicit(const void* dy, long long lddy, const voi
   int splits = 1;
   if (splitk_ws != nullptr && tiles * 2 <= kNumSMs && num_k >= 8) {
     splits = kNumSMs / tiles;
-    if (splits > 16) splits = 16;
-    if (splits > num_k / 4) splits = num_k / 4;
+    if (splits > 128) splits = 128;                 // tiny weight gradients (64 x 64 over 800 K pixels): one K slice per SM
+    if (splits > num_k / 8) splits = num_k / 8;     // at least 8 k-blocks (512 reduction rows) per slice
     if ((long long)splits * M * N * 4 > splitk_ws_bytes) splits = (int)(splitk_ws_bytes / ((long long)M * N * 4));
   }
   if (splits > 1) {
