@@ -41,7 +41,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ mean, f
 #pragma unroll
     for (int j = 0; j < 8; ++j) { a[j] += v[j]; b[j] = fmaf(v[j], v[j], b[j]); }
   };
-  if (!col_reduce_atomic<true>(f, partial, tickets, M, C, tot)) return;
+  if (!col_reduce_atomic<true, 8>(f, partial, tickets, M, C, tot)) return;
   const int g_lo = blockIdx.x * kBnGroups;
   const int nch = min(kBnGroups, (C >> 3) - g_lo) * 8;
   for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
@@ -180,7 +180,9 @@ static int bn_rows_split(int M, int C) {
   const int C8 = C / 8;
   const int tiles = ceil_div(C8, kBnGroups);
   const int rpi = kBnThreads / (C8 < kBnGroups ? C8 : kBnGroups);
-  int R = (4 * kNumSMs) / tiles;
+  static int mult = -1;
+  if (mult < 0) { const char* e = getenv("MLT_BN_R"); mult = e ? atoi(e) : 4; }
+  int R = (mult * kNumSMs) / tiles;
   const int cap = ceil_div(M, rpi * 8);               // at least 8 iterations per CTA
   if (R > cap) R = cap;
   return R < 1 ? 1 : R;

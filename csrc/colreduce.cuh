@@ -86,7 +86,7 @@ __device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&v)[8]) {
 // accumulates one 8-channel group of one row.  A CTA folds its rows through shared memory and adds its per-channel
 // partials to acc[2][C] with fp32 atomics (a few hundred thousand per call, spread over 2*C addresses); the last CTA of
 // a tile (ticket) picks the totals up into tot[2][cw * 8] (shared memory), re-zeroes acc and returns true.
-template <bool TWO, typename F>
+template <bool TWO, int U = 4, typename F>
 __device__ __forceinline__ bool col_reduce_atomic(F f, float* acc, unsigned int* tickets, int M, int C, float* tot) {
   const int C8 = C >> 3;
   const int g_lo = blockIdx.x * kBnGroups;
@@ -102,9 +102,9 @@ __device__ __forceinline__ bool col_reduce_atomic(F f, float* acc, unsigned int*
   if (rsub < rpi) {
     const size_t col = (size_t)(g_lo + cg) * 8;
     int r = r_lo + rsub;
-    for (; r + 3 * rpi < r_hi; r += 4 * rpi) {         // four independent rows in flight
+    for (; r + (U - 1) * rpi < r_hi; r += U * rpi) {   // U independent rows in flight
 #pragma unroll
-      for (int u = 0; u < 4; ++u) f((size_t)(r + u * rpi) * C + col, a, b);
+      for (int u = 0; u < U; ++u) f((size_t)(r + u * rpi) * C + col, a, b);
     }
     for (; r < r_hi; r += rpi) f((size_t)r * C + col, a, b);
   }

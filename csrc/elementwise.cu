@@ -195,7 +195,7 @@ colsum_flat_kernel(const __nv_bfloat16* __restrict__ x, O* __restrict__ out, flo
 #pragma unroll
     for (int j = 0; j < 8; ++j) a[j] += v[j];
   };
-  if (!col_reduce_atomic<false>(f, acc, tickets, M, N, tot)) return;
+  if (!col_reduce_atomic<false, 8>(f, acc, tickets, M, N, tot)) return;
   const int g_lo = blockIdx.x * kBnGroups;
   const int nch = min(kBnGroups, (N >> 3) - g_lo) * 8;
   for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
