@@ -40,6 +40,7 @@ __device__ __constant__ int kParamSize[NPARAM] = {W1N, C1, W2N, C2, F1 * FLAT, F
 constexpr int kThreads = 1024;             // 32 warps: the per-sample CTA is latency bound, it needs the warps
 constexpr int NW = kThreads / 32;
 constexpr int kMaxPerThread = 8;            // arena elements owned per thread in phase B
+constexpr int kMaxSlots = 8;                // input ring slots a multi-step launch can walk
 }  // namespace lenet
 
 struct LeNetArgs {
@@ -59,11 +60,28 @@ struct LeNetArgs {
   float* acc3;                   // {loss_sum, metric_sum, steps} or nullptr
   float* loss_out;               // scalar or nullptr
   P2PArgs comm;                  // world == 1: no communication
+  // ---- several steps in ONE launch (cluster kernel only): removes the ~10 us launch / drain gap between steps --------
+  int nsteps;                    // 0: a single step with the fields above;  >= 1: the multi-step protocol below
+  int nslots;                    // ring mode: step i reads xs[i % nslots] / ys[i % nslots]
+  const float* xs[lenet::kMaxSlots];
+  const long long* ys[lenet::kMaxSlots];
+  long long pool_n;              // pool mode (> 0): step i reads xs[0] + (i % pool_n) * B * XN (and ys[0] likewise)
+  const int* batch_sizes;        // per-step batch size (device), or nullptr: B
+  const Hyper* hyper_table;      // per-step hyper rows (device), or nullptr: hyper
+  float* loss_base;              // loss of step i -> loss_base[i] (device or pinned host), or nullptr
+  const unsigned int* ready;     // step i may start once *ready >= i + 1 (written by the copy stream), or nullptr
+  unsigned int* progress;        // *progress = i + 1 after step i (pinned host), or nullptr
 };
 
 __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
   unsigned int v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
 
@@ -90,12 +108,12 @@ __device__ __forceinline__ float dot4(const float4& a, const float4& b) { return
 // Phase B (after the grid barrier): batch loss / accuracy into the device accumulators, then every thread reduces the
 // gradient of the arena elements it owns over the batch, exchanges it with the peers (multi-GPU) and applies the rule.
 template <typename R>
-__device__ __forceinline__ void lenet_phase_b(const LeNetArgs& a, float inv_B) {
+__device__ __forceinline__ void lenet_phase_b(const LeNetArgs& a, float inv_B, int cur_B, const Hyper* cur_hyper, float* cur_loss) {
   using namespace lenet;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (blockIdx.x == 0 && warp == 0) {            // batch loss / accuracy -> device accumulators
     float l = 0.f, c = 0.f;
-    for (int b = lane; b < a.B; b += 32) {
+    for (int b = lane; b < cur_B; b += 32) {
       l += __ldcg(a.scratch + (size_t)b * S_STRIDE + S_DL + 10);
       c += __ldcg(a.scratch + (size_t)b * S_STRIDE + S_DL + 11);
     }
@@ -103,7 +121,7 @@ __device__ __forceinline__ void lenet_phase_b(const LeNetArgs& a, float inv_B) {
     c = warp_sum(c);
     if (lane == 0) {
       const float loss = l * inv_B;
-      if (a.loss_out) *a.loss_out = loss;
+      if (cur_loss) *cur_loss = loss;
       if (a.acc3) {
         a.acc3[0] += loss;
         if (a.want_acc) a.acc3[1] += c * inv_B;
@@ -113,12 +131,12 @@ __device__ __forceinline__ void lenet_phase_b(const LeNetArgs& a, float inv_B) {
   }
   if (!a.train) return;
 
-  const Hyper h = *a.hyper;
+  const Hyper h = *cur_hyper;
   const int per_cta = (int)ceil_div64(a.numel, (long long)gridDim.x * kThreads) * kThreads;   // elements owned by a CTA
   const long long e0 = (long long)blockIdx.x * per_cta;
   const int per_thread = per_cta / kThreads;
   float g[kMaxPerThread];
-  const int B = a.B;
+  const int B = cur_B;
 #pragma unroll
   for (int r = 0; r < kMaxPerThread; ++r) {
     g[r] = 0.f;
@@ -552,7 +570,7 @@ lenet_step_kernel(const LeNetArgs a) {
   // =========================================== barrier ===========================================
   grid_barrier(a.sync, gridDim.x, s_sense);
 
-  lenet_phase_b<R>(a, inv_B);
+  lenet_phase_b<R>(a, inv_B, a.B, a.hyper, a.loss_out);
 }
 
 // =====================================================================================================
@@ -564,6 +582,17 @@ lenet_step_kernel(const LeNetArgs a) {
 namespace lenet {
 constexpr int CS = 4;                       // CTAs per sample
 }
+
+// Optional per-CTA timeline (analysis only): 16 x int64 per CTA of %globaltimer stamps when a buffer has been installed.
+__device__ long long* g_lenet_dbg = nullptr;
+#define LN_DBG(slot)                                                                           \
+  do {                                                                                         \
+    if (ln_dbg != nullptr && threadIdx.x == 0) {                                               \
+      long long t_;                                                                            \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                   \
+      ln_dbg[blockIdx.x * 16 + (slot)] = t_;                                                   \
+    }                                                                                          \
+  } while (0)
 
 template <typename R>
 __global__ void __launch_bounds__(lenet::kThreads, 1)
@@ -608,6 +637,8 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
   };
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  long long* ln_dbg = g_lenet_dbg;
+  LN_DBG(0);
   __shared__ unsigned int s_sense;
   if (tid == 0) s_sense = ld_acquire_gpu(&a.sync[1]);
 
@@ -623,20 +654,59 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
   const float* Bf3 = a.master + a.off[P_F3B];
 
   const int cluster_id = blockIdx.x / CS, nclusters = gridDim.x / CS;
-  if (cluster_id < a.B) {
+  auto share = [&](int n, int& lo, int& hi) { const int per = (n + CS - 1) / CS; lo = min(n, cr * per); hi = min(n, lo + per); };
+  const int nsteps = a.nsteps >= 1 ? a.nsteps : 1;
+  const bool multi = a.nsteps >= 1;               // 0: the classic single-step launch
+  __shared__ int s_abort;
+  if (tid == 0) s_abort = 0;
+
+  for (int step = 0; step < nsteps; ++step) {
+  // ---- this step's inputs (multi-step launches walk a ring of slots or a device-resident pool) -------------------
+  const float* cur_x = a.x;
+  const long long* cur_y = a.y;
+  int cur_B = a.B;
+  const Hyper* cur_hyper = a.hyper;
+  float* cur_loss = a.loss_out;
+  if (multi) {
+    if (a.ready != nullptr) {                         // wait until the copy stream has landed this step's batch
+      if (tid == 0) {
+        const long long t0 = clock64();
+        while ((int)(ld_acquire_sys_u32(a.ready) - (unsigned int)(step + 1)) < 0) {
+          if (clock64() - t0 > (1LL << 33)) { s_abort = 1; break; }      // ~4 s: the producer died
+        }
+      }
+      __syncthreads();
+      if (s_abort) {
+        if (blockIdx.x == 0 && tid == 0 && a.progress) { *a.progress = 0xFFFFFFFFu; __threadfence_system(); }
+        return;                                        // every CTA polls the same word: all give up together
+      }
+    }
+    if (a.batch_sizes) cur_B = a.batch_sizes[step];
+    if (a.pool_n > 0) {
+      const long long slot = step % a.pool_n;
+      cur_x = a.xs[0] + slot * (long long)a.B * XN;
+      cur_y = a.ys[0] + slot * (long long)a.B;
+    } else {
+      cur_x = a.xs[step % a.nslots];
+      cur_y = a.ys[step % a.nslots];
+    }
+    if (a.hyper_table) cur_hyper = a.hyper_table + step;
+    if (a.loss_base) cur_loss = a.loss_base + step;
+  }
+  if (cluster_id < cur_B) {
     for (int i = tid; i < W1N; i += kThreads) w1s[i] = Wc1[i];
     if (tid < C1) w1s[W1N + tid] = Bc1[tid];
     for (int i = tid; i < W2N; i += kThreads) w2s[i] = Wc2[i];
     if (tid < C2) w2s[W2N + tid] = Bc2[tid];
   }
-  const float inv_B = 1.0f / (float)a.B;
-  auto share = [&](int n, int& lo, int& hi) { const int per = (n + CS - 1) / CS; lo = min(n, cr * per); hi = min(n, lo + per); };
+  const float inv_B = 1.0f / (float)cur_B;
 
-  for (int b = cluster_id; b < a.B; b += nclusters) {
+  for (int b = cluster_id; b < cur_B; b += nclusters) {
     float* slab = a.scratch + (size_t)b * S_STRIDE;
     cluster.sync();                    // previous sample fully consumed everywhere before anything is overwritten
+    LN_DBG(1);
     {
-      const float4* src = reinterpret_cast<const float4*>(a.x + (size_t)b * XN);
+      const float4* src = reinterpret_cast<const float4*>(cur_x + (size_t)b * XN);
       float4* dst = reinterpret_cast<float4*>(xs);
       for (int i = tid; i < XN / 4; i += kThreads) dst[i] = src[i];
     }
@@ -675,6 +745,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       bcast_i(offs1 + o, (2 * ph + (am >> 1)) * H + 2 * pw + (am & 1));
     }
     cluster.sync();
+    LN_DBG(2);
     // ---- conv2 + ReLU + pool: my 100 of the 400 outputs
     share(FLAT, lo, hi);
     for (int o = lo + tid; o < hi; o += kThreads) {
@@ -709,6 +780,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       slab[S_A2 + o] = m;
     }
     cluster.sync();
+    LN_DBG(3);
     // ---- fc1 + ReLU: my 30 neurons, one warp each
     share(F1, lo, hi);
     {
@@ -731,6 +803,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       }
     }
     cluster.sync();
+    LN_DBG(4);
     // ---- fc2 + ReLU: my 21 neurons
     share(F2, lo, hi);
     {
@@ -748,6 +821,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       }
     }
     cluster.sync();
+    LN_DBG(5);
     // ---- fc3, loss, dlogits, d2, d1: tiny, every CTA computes them for itself (no exchange needed)
     {
       const float4* xv = reinterpret_cast<const float4*>(z2s);
@@ -760,7 +834,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     }
     __syncthreads();
     if (warp == 0) {
-      const int tgt = (int)a.y[b];
+      const int tgt = (int)cur_y[b];
       const float v = lane < NC ? lgs[lane] : -INFINITY;
       float m = v; int am = lane < NC ? lane : 0x7fffffff;
 #pragma unroll
@@ -847,6 +921,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       bcast_f(g2x + cr * FLAT + k, s);
     }
     cluster.sync();
+    LN_DBG(6);
     for (int k = tid; k < FLAT; k += kThreads) {
       const float s = g2x[k] + g2x[FLAT + k] + g2x[2 * FLAT + k] + g2x[3 * FLAT + k];
       g2p[k] = a2s[k] > 0.f ? s : 0.f;
@@ -906,6 +981,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     for (int o = tid; o < A1N; o += kThreads)
       bcast_f(g1x + cr * A1N + o, dgp[o] + dgp[A1N + o] + dgp[2 * A1N + o] + dgp[3 * A1N + o]);
     cluster.sync();
+    LN_DBG(7);
     for (int o = tid; o < A1N; o += kThreads) {
       const float s = g1x[o] + g1x[A1N + o] + g1x[2 * A1N + o] + g1x[3 * A1N + o];
       g1p[o] = a1s[o] > 0.f ? s : 0.f;
@@ -938,9 +1014,21 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     }
   }
   cluster.sync();        // nobody leaves while a sibling may still write into its shared memory
+  LN_DBG(8);
 
   grid_barrier(a.sync, gridDim.x, s_sense);
-  lenet_phase_b<R>(a, inv_B);
+  LN_DBG(9);
+  lenet_phase_b<R>(a, inv_B, cur_B, cur_hyper, cur_loss);
+  LN_DBG(10);
+  if (multi) {
+    // the updated weights (and the loss) must be visible everywhere before the next step reads them
+    if (tid == 0) s_sense += 1;
+    grid_barrier(a.sync, gridDim.x, s_sense + 0u);
+    if (tid == 0) s_sense += 1;
+    if (blockIdx.x == 0 && tid == 0 && a.progress) { __threadfence_system(); *a.progress = (unsigned int)(step + 1); }
+    __syncthreads();
+  }
+  }  // step loop
 }
 
 namespace lenet {
@@ -964,32 +1052,15 @@ extern "C" long long mlt_lenet_scratch_bytes(int B) { return (long long)B * lene
 // param_off: arena element offsets of {conv1.w, conv1.b, conv2.w, conv2.b, fc1.w, fc1.b, fc2.w, fc2.b, fc3.w, fc3.b}.
 // scratch: mlt_lenet_scratch_bytes(B) bytes, zero-initialised once (its first 256 bytes hold the grid-barrier words).
 // ctx: NULL or world == 1 for single-GPU; otherwise gradients are all-reduced in-kernel through the symmetric arena.
-extern "C" int mlt_lenet_step(void* master, void* s1, void* s2, const void* hyper, long long numel, const long long* param_off,
-                              int rule, const void* x, const void* y_i64, int B, int train, int want_acc, void* acc3,
-                              void* loss_out, void* scratch, long long scratch_bytes, const mlt_p2p_ctx* ctx, void* stream) {
+// Launch the step kernel for the arguments in `a` (single step, or a.nsteps steps in one launch: cluster kernel only).
+static int lenet_launch(LeNetArgs& a, int rule, long long numel, void* stream) {
   using namespace lenet;
-  MLT_REQUIRE(B > 0, "mlt_lenet_step: empty batch");
-  MLT_REQUIRE(scratch != nullptr && scratch_bytes >= mlt_lenet_scratch_bytes(B), "mlt_lenet_step: scratch too small");
-  LeNetArgs a;
-  a.master = (float*)master; a.s1 = (float*)s1; a.s2 = (float*)s2; a.hyper = (const Hyper*)hyper; a.numel = numel;
-  for (int i = 0; i < NPARAM; ++i) a.off[i] = param_off[i];
-  a.x = (const float*)x; a.y = (const long long*)y_i64; a.B = B; a.train = train; a.want_acc = want_acc;
-  a.sync = (unsigned int*)scratch;
-  a.scratch = (float*)((char*)scratch + 256);
-  a.acc3 = (float*)acc3; a.loss_out = (float*)loss_out;
-  a.comm.world = 1; a.comm.rank = 0;
-  if (ctx != nullptr && ctx->world > 1) {
-    MLT_REQUIRE(numel * 4 <= ctx->recv_slot_bytes, "mlt_lenet_step: parameter arena exceeds the one-shot receive slot");
-    for (int i = 0; i < kMaxRanks; ++i) a.comm.base[i] = (char*)ctx->base[i];
-    a.comm.mc_base = (char*)ctx->mc_base;
-    a.comm.world = ctx->world; a.comm.rank = ctx->rank;
-    a.comm.flags_off = ctx->flags_off; a.comm.recv_off = ctx->recv_off; a.comm.recv_slot_bytes = ctx->recv_slot_bytes;
-  }
   cudaStream_t st = (cudaStream_t)stream;
   int dev = 0;
   MLT_CHECK_CUDA(cudaGetDevice(&dev));
   int rc = 0;
   static const bool use_cluster = []{ const char* e = getenv("MLT_LENET_CLUSTER"); return !(e && e[0] == '0'); }();
+  MLT_REQUIRE(a.nsteps < 1 || use_cluster, "multi-step launches need the cluster kernel (MLT_LENET_CLUSTER=0 is set)");
   MLT_DISPATCH_RULE(rule, R, {
     if (use_cluster) {
       auto kern = lenet_step_cluster_kernel<R>;
@@ -1030,6 +1101,7 @@ extern "C" int mlt_lenet_step(void* master, void* s1, void* s2, const void* hype
       MLT_CHECK_CUDA(le);
       return 0;
     }
+    MLT_REQUIRE(a.nsteps < 1, "multi-step launches need the cluster kernel");
     auto kern = lenet_step_kernel<R>;
     static int grid_cache[64] = {};
     if (grid_cache[dev & 63] == 0) {
@@ -1047,4 +1119,76 @@ extern "C" int mlt_lenet_step(void* master, void* s1, void* s2, const void* hype
     MLT_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(kThreads), params, kSmemBytes, st));
   });
   return rc;
+}
+
+
+extern "C" int mlt_lenet_step(void* master, void* s1, void* s2, const void* hyper, long long numel, const long long* param_off,
+                              int rule, const void* x, const void* y_i64, int B, int train, int want_acc, void* acc3,
+                              void* loss_out, void* scratch, long long scratch_bytes, const mlt_p2p_ctx* ctx, void* stream) {
+  using namespace lenet;
+  MLT_REQUIRE(B > 0, "mlt_lenet_step: empty batch");
+  MLT_REQUIRE(scratch != nullptr && scratch_bytes >= mlt_lenet_scratch_bytes(B), "mlt_lenet_step: scratch too small");
+  LeNetArgs a;
+  a.master = (float*)master; a.s1 = (float*)s1; a.s2 = (float*)s2; a.hyper = (const Hyper*)hyper; a.numel = numel;
+  for (int i = 0; i < NPARAM; ++i) a.off[i] = param_off[i];
+  a.x = (const float*)x; a.y = (const long long*)y_i64; a.B = B; a.train = train; a.want_acc = want_acc;
+  a.sync = (unsigned int*)scratch;
+  a.scratch = (float*)((char*)scratch + 256);
+  a.acc3 = (float*)acc3; a.loss_out = (float*)loss_out;
+  a.nsteps = 0; a.nslots = 0; a.pool_n = 0; a.batch_sizes = nullptr; a.hyper_table = nullptr; a.loss_base = nullptr;
+  a.ready = nullptr; a.progress = nullptr;
+  for (int i = 0; i < kMaxSlots; ++i) { a.xs[i] = nullptr; a.ys[i] = nullptr; }
+  a.comm.world = 1; a.comm.rank = 0;
+  if (ctx != nullptr && ctx->world > 1) {
+    MLT_REQUIRE(numel * 4 <= ctx->recv_slot_bytes, "mlt_lenet_step: parameter arena exceeds the one-shot receive slot");
+    for (int i = 0; i < kMaxRanks; ++i) a.comm.base[i] = (char*)ctx->base[i];
+    a.comm.mc_base = (char*)ctx->mc_base;
+    a.comm.world = ctx->world; a.comm.rank = ctx->rank;
+    a.comm.flags_off = ctx->flags_off; a.comm.recv_off = ctx->recv_off; a.comm.recv_slot_bytes = ctx->recv_slot_bytes;
+  }
+  return lenet_launch(a, rule, numel, stream);
+}
+
+// `nsteps` consecutive steps in ONE launch (no launch / drain gap between steps).  Inputs: either a ring of `nslots`
+// device buffers (xs[i], ys[i]; step i uses slot i % nslots once *ready >= i + 1, *ready being advanced by whoever fills the
+// slots, e.g. a copy stream) or, with pool_n > 0, a device-resident pool of pool_n batches of B samples at xs[0] / ys[0].
+// batch_sizes / hyper_table / loss_base: per-step device tables (each may be NULL: B, hyper, no per-step loss).
+// progress: optional word (pinned host memory) that receives i + 1 after step i, 0xFFFFFFFF if the kernel gave up waiting.
+extern "C" int mlt_lenet_steps(void* master, void* s1, void* s2, const void* hyper, long long numel, const long long* param_off,
+                               int rule, const void* const* xs, const void* const* ys, int nslots, long long pool_n, int B,
+                               const int* batch_sizes, const void* hyper_table, void* loss_base, const void* ready, void* progress,
+                               int nsteps, int train, int want_acc, void* acc3, void* scratch, long long scratch_bytes,
+                               const mlt_p2p_ctx* ctx, void* stream) {
+  using namespace lenet;
+  MLT_REQUIRE(B > 0 && nsteps > 0, "mlt_lenet_steps: empty run");
+  MLT_REQUIRE(nslots >= 1 && nslots <= kMaxSlots, "mlt_lenet_steps: 1..%d input slots", kMaxSlots);
+  MLT_REQUIRE(scratch != nullptr && scratch_bytes >= mlt_lenet_scratch_bytes(B), "mlt_lenet_steps: scratch too small");
+  LeNetArgs a;
+  a.master = (float*)master; a.s1 = (float*)s1; a.s2 = (float*)s2; a.hyper = (const Hyper*)hyper; a.numel = numel;
+  for (int i = 0; i < NPARAM; ++i) a.off[i] = param_off[i];
+  a.x = (const float*)xs[0]; a.y = (const long long*)ys[0]; a.B = B; a.train = train; a.want_acc = want_acc;
+  a.sync = (unsigned int*)scratch;
+  a.scratch = (float*)((char*)scratch + 256);
+  a.acc3 = (float*)acc3; a.loss_out = nullptr;
+  a.nsteps = nsteps;
+  a.nslots = nslots; a.pool_n = pool_n;
+  for (int i = 0; i < kMaxSlots; ++i) { a.xs[i] = i < nslots ? (const float*)xs[i] : nullptr; a.ys[i] = i < nslots ? (const long long*)ys[i] : nullptr; }
+  a.batch_sizes = batch_sizes; a.hyper_table = (const Hyper*)hyper_table; a.loss_base = (float*)loss_base;
+  a.ready = (const unsigned int*)ready; a.progress = (unsigned int*)progress;
+  a.comm.world = 1; a.comm.rank = 0;
+  if (ctx != nullptr && ctx->world > 1) {
+    MLT_REQUIRE(numel * 4 <= ctx->recv_slot_bytes, "mlt_lenet_steps: parameter arena exceeds the one-shot receive slot");
+    for (int i = 0; i < kMaxRanks; ++i) a.comm.base[i] = (char*)ctx->base[i];
+    a.comm.mc_base = (char*)ctx->mc_base;
+    a.comm.world = ctx->world; a.comm.rank = ctx->rank;
+    a.comm.flags_off = ctx->flags_off; a.comm.recv_off = ctx->recv_off; a.comm.recv_slot_bytes = ctx->recv_slot_bytes;
+  }
+  return lenet_launch(a, rule, numel, stream);
+}
+
+// Analysis hook: device buffer of 16 int64 per CTA that the cluster kernel fills with %globaltimer stamps (NULL clears it).
+extern "C" int mlt_lenet_set_debug(void* buf) {
+  long long* b = (long long*)buf;
+  MLT_CHECK_CUDA(cudaMemcpyToSymbol(mlt::g_lenet_dbg, &b, sizeof(b)));
+  return 0;
 }

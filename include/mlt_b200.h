@@ -220,6 +220,13 @@ int mlt_colsum_flat(const void* x, void* out, int out_bf16, void* scratch, long 
  * gradient is the backward pass; *step_ptr lives in device memory so captured graphs replay with fresh masks. */
 int mlt_dropout(const void* x, void* y, long long n, float p, unsigned long long seed, const void* step_ptr, unsigned int call_id,
                 int is_bf16, void* stream);
+/* `nsteps` LeNet steps in ONE launch (see csrc/lenet_step.cu): ring of nslots device buffers gated by *ready, or a device pool
+ * of pool_n batches; per-step batch sizes / hyper rows / losses from device tables; *progress (pinned host) = steps finished. */
+int mlt_lenet_steps(void* master, void* s1, void* s2, const void* hyper, long long numel, const long long* param_off, int rule,
+                    const void* const* xs, const void* const* ys, int nslots, long long pool_n, int B, const int* batch_sizes,
+                    const void* hyper_table, void* loss_base, const void* ready, void* progress, int nsteps, int train,
+                    int want_acc, void* acc3, void* scratch, long long scratch_bytes, const mlt_p2p_ctx* ctx, void* stream);
+int mlt_lenet_set_debug(void* buf);
 int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
                           void* out_bf16, int T, int S, int H, void* stream);
 int mlt_embedding_bwd(const void* ids_i64, const void* dh_bf16, void* dword, long long V, void* dpos, int grads_bf16, int B,

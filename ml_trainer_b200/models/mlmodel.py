@@ -104,3 +104,26 @@ class _FusedLeNetStep:
                                     ctypes.byref(self.ctx) if self.ctx is not None else None, stream_handle()),
               "mlt_lenet_step")
         launches.bump("lenet_step")
+
+    def run_pool(self, x_pool, y_pool, nsteps: int, train: bool = True, hyper_table=None, losses=None, acc3=None,
+                 want_acc: bool = False):
+        """``nsteps`` steps in ONE kernel launch over a device-resident pool of batches (step i uses batch i % P).
+
+        x_pool: [P, B, 3, 32, 32] fp32, y_pool: [P, B] int64, both contiguous on the device.  hyper_table: optional
+        [nsteps, 8] fp32 device tensor of per-step hyper rows (else the optimizer's current row is used for every step);
+        losses: optional [nsteps] fp32 device tensor that receives the per-step losses."""
+        from ..ops._lib import check, launches, ptr, stream_handle
+
+        P, B = int(x_pool.shape[0]), int(x_pool.shape[1])
+        assert x_pool.is_contiguous() and y_pool.is_contiguous() and x_pool.dtype == torch.float32 and y_pool.dtype == torch.int64
+        self.ensure_scratch(B, x_pool.device)
+        o = self.opt
+        s2 = o.s2 if o.s2.numel() > 1 else None
+        xs = (ctypes.c_void_p * 1)(x_pool.data_ptr())
+        ys = (ctypes.c_void_p * 1)(y_pool.data_ptr())
+        check(self.L.mlt_lenet_steps(ptr(o.master), ptr(o.s1), ptr(s2), ptr(o.hyper), ctypes.c_longlong(o.numel), self.off,
+                                     ctypes.c_int(self.rule), xs, ys, ctypes.c_int(1), ctypes.c_longlong(P), ctypes.c_int(B), None,
+                                     ptr(hyper_table), ptr(losses), None, None, ctypes.c_int(nsteps), ctypes.c_int(int(train)),
+                                     ctypes.c_int(int(want_acc)), ptr(acc3), ptr(self._scratch), ctypes.c_longlong(self._scratch.numel()),
+                                     ctypes.byref(self.ctx) if self.ctx is not None else None, stream_handle()), "mlt_lenet_steps")
+        launches.bump("lenet_step", 1)

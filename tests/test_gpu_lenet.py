@@ -107,3 +107,36 @@ def test_native_executor_honours_lr_schedule(tmp_path):
     assert outs[0].optimizer.param_groups[0]["lr"] == pytest.approx(outs[1].optimizer.param_groups[0]["lr"])
     for p, q in zip(outs[0].model.parameters(), outs[1].model.parameters()):
         assert torch.equal(p, q)
+
+
+@pytest.mark.parametrize("optimizer", ["sgd", "adamw"])
+def test_multi_step_launch_equals_single_steps(tmp_path, optimizer):
+    """K steps in ONE launch over a device pool == K single-step launches (same kernel body, in-kernel barriers between steps)."""
+    K, P, B = 7, 3, 32
+    torch.manual_seed(5)
+    xp = torch.randn(P, B, 3, 32, 32, device="cuda")
+    yp = torch.randint(0, 10, (P, B), device="cuda")
+    ts = []
+    for _ in range(2):
+        t = _trainer(tmp_path / str(len(ts)), True, optimizer)
+        ts.append(t)
+    a, b = ts
+    for (p, q) in zip(a.model.parameters(), b.model.parameters()):
+        q.data.copy_(p.data)
+    b.optimizer.master.copy_(a.optimizer.master)
+    fa, fb = a.engine.fused, b.engine.fused
+    # per-step hyper rows (AdamW bias corrections change every step)
+    rows = []
+    la = torch.zeros(K, device="cuda")
+    for i in range(K):
+        h = a.optimizer.begin_step(1.0)
+        rows.append(torch.tensor(h.pack(), dtype=torch.float32))
+        fa(xp[i % P], yp[i % P], True, None, False, la[i:i + 1])
+    table = torch.stack(rows).cuda()
+    lb = torch.zeros(K, device="cuda")
+    acc = torch.zeros(3, device="cuda")
+    fb.run_pool(xp, yp, K, True, hyper_table=table, losses=lb, acc3=acc, want_acc=True)
+    torch.cuda.synchronize()
+    assert torch.equal(la, lb), (la, lb)
+    assert torch.equal(a.optimizer.master, b.optimizer.master)
+    assert acc[2].item() == K and abs(acc[0].item() - lb.sum().item()) < 1e-4
