@@ -79,6 +79,29 @@ __device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
   return v;
 }
 
+// Bulk asynchronous copy global -> shared (the TMA engine, no tensor map): one instruction per contiguous block.
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned int bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned int)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, unsigned int bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   (unsigned int)__cvta_generic_to_shared(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"((unsigned int)__cvta_generic_to_shared(bar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait_parity(unsigned long long* bar, unsigned int parity) {
+  unsigned int ok = 0;
+  while (!ok) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"((unsigned int)__cvta_generic_to_shared(bar)), "r"(parity)
+        : "memory");
+  }
+}
+
 __device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
   unsigned int v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -622,6 +645,13 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
   float* w1x = g1x + CS * A1N;          // 4 x 128 : conv1 wgrad position-split partials
   int* offs1 = reinterpret_cast<int*>(w1x + 4 * 128);        // 1176
   int* offs2 = offs1 + A1N;                                  // 400
+  // fully-connected weights staged once per step with cp.async while the convolutions run: this CTA's 30 rows of fc1
+  // (forward and backward use the same rows), all of fc2 / fc3 and the three bias vectors - the fc stages are chains of
+  // tiny dependent products, and an L2 round trip per stage was most of their time
+  float* wf1s = reinterpret_cast<float*>(offs2 + FLAT);      // 30 x 400
+  float* wf2s = wf1s + 30 * FLAT;                            // 84 x 120
+  float* wf3s = wf2s + F2 * F1;                              // 10 x 84
+  float* bfs = wf3s + NC * F2;                               // 120 + 84 + 10 (+ pad)
   float* rsm[CS];
 #pragma unroll
   for (int r = 0; r < CS; ++r) rsm[r] = cluster.map_shared_rank(sm, r);
@@ -658,8 +688,15 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
   const int nsteps = a.nsteps >= 1 ? a.nsteps : 1;
   const bool multi = a.nsteps >= 1;               // 0: the classic single-step launch
   __shared__ int s_abort;
-  if (tid == 0) s_abort = 0;
+  __shared__ __align__(8) unsigned long long wbar;
+  if (tid == 0) {
+    s_abort = 0;
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned int)__cvta_generic_to_shared(&wbar)) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
 
+  unsigned int wcount = 0;                // bulk weight copies this CTA has issued (steps with fewer samples than clusters skip)
   for (int step = 0; step < nsteps; ++step) {
   // ---- this step's inputs (multi-step launches walk a ring of slots or a device-resident pool) -------------------
   const float* cur_x = a.x;
@@ -698,6 +735,19 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     if (tid < C1) w1s[W1N + tid] = Bc1[tid];
     for (int i = tid; i < W2N; i += kThreads) w2s[i] = Wc2[i];
     if (tid < C2) w2s[W2N + tid] = Bc2[tid];
+    ++wcount;
+    if (tid == 0) {                      // three bulk copies (TMA, no tensor map), completion counted on wbar
+      int f_lo, f_hi;
+      share(F1, f_lo, f_hi);
+      const unsigned int b1 = (unsigned int)(f_hi - f_lo) * FLAT * 4, b2 = F2 * F1 * 4, b3 = NC * F2 * 4;
+      mbar_expect_tx(&wbar, b1 + b2 + b3);
+      bulk_g2s(wf1s, Wf1 + (size_t)f_lo * FLAT, b1, &wbar);
+      bulk_g2s(wf2s, Wf2, b2, &wbar);
+      bulk_g2s(wf3s, Wf3, b3, &wbar);
+    }
+    if (tid < F1) bfs[tid] = Bf1[tid];
+    else if (tid < F1 + F2) bfs[tid] = Bf2[tid - F1];
+    else if (tid < F1 + F2 + NC) bfs[tid] = Bf3[tid - F1 - F2];
   }
   const float inv_B = 1.0f / (float)cur_B;
 
@@ -779,6 +829,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       bcast_i(offs2 + o, (2 * ph + (am >> 1)) * P1 + 2 * pw + (am & 1));
       slab[S_A2 + o] = m;
     }
+    mbar_wait_parity(&wbar, (wcount - 1u) & 1u);          // the fc weights of this step have landed
     cluster.sync();
     LN_DBG(3);
     // ---- fc1 + ReLU: my 30 neurons, one warp each
@@ -787,7 +838,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       const float4* xv = reinterpret_cast<const float4*>(a2s);
       const int n = lo + warp;
       if (n < hi) {
-        const float4* wr = reinterpret_cast<const float4*>(Wf1 + (size_t)n * FLAT);
+        const float4* wr = reinterpret_cast<const float4*>(wf1s + (size_t)(n - lo) * FLAT);
         float acc = 0.f;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -796,7 +847,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
         }
         acc = warp_sum(acc);
         if (lane == 0) {
-          const float v = fmaxf(acc + Bf1[n], 0.f);
+          const float v = fmaxf(acc + bfs[n], 0.f);
           bcast_f(z1s + n, v);
           slab[S_Z1 + n] = v;
         }
@@ -811,10 +862,10 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       const int n = lo + warp;
       if (n < hi) {
         float acc = 0.f;
-        if (lane < F1 / 4) acc = dot4(reinterpret_cast<const float4*>(Wf2 + (size_t)n * F1)[lane], xv[lane]);
+        if (lane < F1 / 4) acc = dot4(reinterpret_cast<const float4*>(wf2s + (size_t)n * F1)[lane], xv[lane]);
         acc = warp_sum(acc);
         if (lane == 0) {
-          const float v = fmaxf(acc + Bf2[n], 0.f);
+          const float v = fmaxf(acc + bfs[F1 + n], 0.f);
           bcast_f(z2s + n, v);
           slab[S_Z2 + n] = v;
         }
@@ -827,9 +878,9 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       const float4* xv = reinterpret_cast<const float4*>(z2s);
       if (warp < NC) {
         float acc = 0.f;
-        if (lane < F2 / 4) acc = dot4(reinterpret_cast<const float4*>(Wf3 + (size_t)warp * F2)[lane], xv[lane]);
+        if (lane < F2 / 4) acc = dot4(reinterpret_cast<const float4*>(wf3s + (size_t)warp * F2)[lane], xv[lane]);
         acc = warp_sum(acc);
-        if (lane == 0) lgs[warp] = acc + Bf3[warp];
+        if (lane == 0) lgs[warp] = acc + bfs[F1 + F2 + warp];
       }
     }
     __syncthreads();
@@ -863,7 +914,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     if (tid < F2) {
       float s = 0.f;
 #pragma unroll
-      for (int n = 0; n < NC; ++n) s = fmaf(dls[n], Wf3[n * F2 + tid], s);
+      for (int n = 0; n < NC; ++n) s = fmaf(dls[n], wf3s[n * F2 + tid], s);
       s = z2s[tid] > 0.f ? s : 0.f;
       d2s[tid] = s;
       if (cr == 0) slab[S_D2 + tid] = s;
@@ -874,7 +925,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       float s = 0.f;
       const int n_hi = min(F2, part * 11 + 11);
 #pragma unroll 11
-      for (int n = part * 11; n < n_hi; ++n) s = fmaf(d2s[n], Wf2[n * F1 + k], s);
+      for (int n = part * 11; n < n_hi; ++n) s = fmaf(d2s[n], wf2s[n * F1 + k], s);
       dz2[tid] = s;
     }
     __syncthreads();
@@ -895,7 +946,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       acc[0] = acc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int n = lo + rg; n < hi; n += 16) {
         const float dv = d1s[n];
-        const float4* wr = reinterpret_cast<const float4*>(Wf1 + (size_t)n * FLAT);
+        const float4* wr = reinterpret_cast<const float4*>(wf1s + (size_t)(n - lo) * FLAT);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           const int c4 = lane + 32 * (2 * half + c);
@@ -1034,7 +1085,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
 namespace lenet {
 constexpr size_t kClusterSmemBytes =
     (size_t)(XN + 456 + A1N + 2416 + FLAT + F1 + 88 + 16 + 16 + 88 + F1 + FLAT + A1N + 6400 + 4 * A1N + CS * FLAT + CS * A1N + 4 * 128) * 4 +
-    (size_t)(A1N + FLAT) * 4 + 64;
+    (size_t)(A1N + FLAT) * 4 + (size_t)(30 * FLAT + F2 * F1 + NC * F2 + 256) * 4 + 64;
 }
 
 namespace lenet {
