@@ -608,6 +608,9 @@ constexpr int CS = 4;                       // CTAs per sample
 
 // Optional per-CTA timeline (analysis only): 16 x int64 per CTA of %globaltimer stamps when a buffer has been installed.
 __device__ long long* g_lenet_dbg = nullptr;
+#ifndef MLT_LENET_TIMELINE
+#define LN_DBG(slot) do { (void)ln_dbg; } while (0)
+#else
 #define LN_DBG(slot)                                                                           \
   do {                                                                                         \
     if (ln_dbg != nullptr && threadIdx.x == 0) {                                               \
@@ -616,8 +619,12 @@ __device__ long long* g_lenet_dbg = nullptr;
       ln_dbg[blockIdx.x * 16 + (slot)] = t_;                                                   \
     }                                                                                          \
   } while (0)
+#endif
 
-template <typename R>
+// MULTI = false: one step per launch, weights read where they are used (the cold-L2 friendly form).
+// MULTI = true : a.nsteps steps per launch (ring / pool inputs, in-kernel barriers between steps) with the fully-connected
+//               weights staged in shared memory by bulk copies while the convolutions run.
+template <typename R, bool MULTI>
 __global__ void __launch_bounds__(lenet::kThreads, 1)
 lenet_step_cluster_kernel(const LeNetArgs a) {
   using namespace lenet;
@@ -667,7 +674,11 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
   };
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef MLT_LENET_TIMELINE
   long long* ln_dbg = g_lenet_dbg;
+#else
+  long long* ln_dbg = nullptr;
+#endif
   LN_DBG(0);
   __shared__ unsigned int s_sense;
   if (tid == 0) s_sense = ld_acquire_gpu(&a.sync[1]);
@@ -685,16 +696,27 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
 
   const int cluster_id = blockIdx.x / CS, nclusters = gridDim.x / CS;
   auto share = [&](int n, int& lo, int& hi) { const int per = (n + CS - 1) / CS; lo = min(n, cr * per); hi = min(n, lo + per); };
-  const int nsteps = a.nsteps >= 1 ? a.nsteps : 1;
-  const bool multi = a.nsteps >= 1;               // 0: the classic single-step launch
+  const int nsteps = MULTI ? a.nsteps : 1;
+  constexpr bool multi = MULTI;
   __shared__ int s_abort;
   __shared__ __align__(8) unsigned long long wbar;
-  if (tid == 0) {
-    s_abort = 0;
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned int)__cvta_generic_to_shared(&wbar)) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  if (MULTI) {
+    if (tid == 0) {
+      s_abort = 0;
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"((unsigned int)__cvta_generic_to_shared(&wbar)) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
   }
-  __syncthreads();
+  int f1_lo, f1_hi;
+  share(F1, f1_lo, f1_hi);
+  // where the fc stages read their weights: staged copies (MULTI) or the arena itself
+  const float* pW1 = MULTI ? wf1s : Wf1 + (size_t)f1_lo * FLAT;      // this CTA's rows of fc1
+  const float* pW2 = MULTI ? wf2s : Wf2;
+  const float* pW3 = MULTI ? wf3s : Wf3;
+  const float* pB1 = MULTI ? bfs : Bf1;
+  const float* pB2 = MULTI ? bfs + F1 : Bf2;
+  const float* pB3 = MULTI ? bfs + F1 + F2 : Bf3;
 
   unsigned int wcount = 0;                // bulk weight copies this CTA has issued (steps with fewer samples than clusters skip)
   for (int step = 0; step < nsteps; ++step) {
@@ -735,19 +757,19 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     if (tid < C1) w1s[W1N + tid] = Bc1[tid];
     for (int i = tid; i < W2N; i += kThreads) w2s[i] = Wc2[i];
     if (tid < C2) w2s[W2N + tid] = Bc2[tid];
-    ++wcount;
-    if (tid == 0) {                      // three bulk copies (TMA, no tensor map), completion counted on wbar
-      int f_lo, f_hi;
-      share(F1, f_lo, f_hi);
-      const unsigned int b1 = (unsigned int)(f_hi - f_lo) * FLAT * 4, b2 = F2 * F1 * 4, b3 = NC * F2 * 4;
-      mbar_expect_tx(&wbar, b1 + b2 + b3);
-      bulk_g2s(wf1s, Wf1 + (size_t)f_lo * FLAT, b1, &wbar);
-      bulk_g2s(wf2s, Wf2, b2, &wbar);
-      bulk_g2s(wf3s, Wf3, b3, &wbar);
+    if (MULTI) {
+      ++wcount;
+      if (tid == 0) {                    // three bulk copies (TMA, no tensor map), completion counted on wbar
+        const unsigned int b1 = (unsigned int)(f1_hi - f1_lo) * FLAT * 4, b2 = F2 * F1 * 4, b3 = NC * F2 * 4;
+        mbar_expect_tx(&wbar, b1 + b2 + b3);
+        bulk_g2s(wf1s, Wf1 + (size_t)f1_lo * FLAT, b1, &wbar);
+        bulk_g2s(wf2s, Wf2, b2, &wbar);
+        bulk_g2s(wf3s, Wf3, b3, &wbar);
+      }
+      if (tid < F1) bfs[tid] = Bf1[tid];
+      else if (tid < F1 + F2) bfs[tid] = Bf2[tid - F1];
+      else if (tid < F1 + F2 + NC) bfs[tid] = Bf3[tid - F1 - F2];
     }
-    if (tid < F1) bfs[tid] = Bf1[tid];
-    else if (tid < F1 + F2) bfs[tid] = Bf2[tid - F1];
-    else if (tid < F1 + F2 + NC) bfs[tid] = Bf3[tid - F1 - F2];
   }
   const float inv_B = 1.0f / (float)cur_B;
 
@@ -829,7 +851,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       bcast_i(offs2 + o, (2 * ph + (am >> 1)) * P1 + 2 * pw + (am & 1));
       slab[S_A2 + o] = m;
     }
-    mbar_wait_parity(&wbar, (wcount - 1u) & 1u);          // the fc weights of this step have landed
+    if (MULTI) mbar_wait_parity(&wbar, (wcount - 1u) & 1u);   // the fc weights of this step have landed
     cluster.sync();
     LN_DBG(3);
     // ---- fc1 + ReLU: my 30 neurons, one warp each
@@ -838,7 +860,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       const float4* xv = reinterpret_cast<const float4*>(a2s);
       const int n = lo + warp;
       if (n < hi) {
-        const float4* wr = reinterpret_cast<const float4*>(wf1s + (size_t)(n - lo) * FLAT);
+        const float4* wr = reinterpret_cast<const float4*>(pW1 + (size_t)(n - f1_lo) * FLAT);
         float acc = 0.f;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -847,7 +869,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
         }
         acc = warp_sum(acc);
         if (lane == 0) {
-          const float v = fmaxf(acc + bfs[n], 0.f);
+          const float v = fmaxf(acc + pB1[n], 0.f);
           bcast_f(z1s + n, v);
           slab[S_Z1 + n] = v;
         }
@@ -862,10 +884,10 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       const int n = lo + warp;
       if (n < hi) {
         float acc = 0.f;
-        if (lane < F1 / 4) acc = dot4(reinterpret_cast<const float4*>(wf2s + (size_t)n * F1)[lane], xv[lane]);
+        if (lane < F1 / 4) acc = dot4(reinterpret_cast<const float4*>(pW2 + (size_t)n * F1)[lane], xv[lane]);
         acc = warp_sum(acc);
         if (lane == 0) {
-          const float v = fmaxf(acc + bfs[F1 + n], 0.f);
+          const float v = fmaxf(acc + pB2[n], 0.f);
           bcast_f(z2s + n, v);
           slab[S_Z2 + n] = v;
         }
@@ -878,9 +900,9 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       const float4* xv = reinterpret_cast<const float4*>(z2s);
       if (warp < NC) {
         float acc = 0.f;
-        if (lane < F2 / 4) acc = dot4(reinterpret_cast<const float4*>(wf3s + (size_t)warp * F2)[lane], xv[lane]);
+        if (lane < F2 / 4) acc = dot4(reinterpret_cast<const float4*>(pW3 + (size_t)warp * F2)[lane], xv[lane]);
         acc = warp_sum(acc);
-        if (lane == 0) lgs[warp] = acc + bfs[F1 + F2 + warp];
+        if (lane == 0) lgs[warp] = acc + pB3[warp];
       }
     }
     __syncthreads();
@@ -914,7 +936,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     if (tid < F2) {
       float s = 0.f;
 #pragma unroll
-      for (int n = 0; n < NC; ++n) s = fmaf(dls[n], wf3s[n * F2 + tid], s);
+      for (int n = 0; n < NC; ++n) s = fmaf(dls[n], pW3[n * F2 + tid], s);
       s = z2s[tid] > 0.f ? s : 0.f;
       d2s[tid] = s;
       if (cr == 0) slab[S_D2 + tid] = s;
@@ -925,7 +947,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       float s = 0.f;
       const int n_hi = min(F2, part * 11 + 11);
 #pragma unroll 11
-      for (int n = part * 11; n < n_hi; ++n) s = fmaf(d2s[n], wf2s[n * F1 + k], s);
+      for (int n = part * 11; n < n_hi; ++n) s = fmaf(d2s[n], pW2[n * F1 + k], s);
       dz2[tid] = s;
     }
     __syncthreads();
@@ -946,7 +968,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
       acc[0] = acc[1] = make_float4(0.f, 0.f, 0.f, 0.f);
       for (int n = lo + rg; n < hi; n += 16) {
         const float dv = d1s[n];
-        const float4* wr = reinterpret_cast<const float4*>(wf1s + (size_t)(n - lo) * FLAT);
+        const float4* wr = reinterpret_cast<const float4*>(pW1 + (size_t)(n - f1_lo) * FLAT);
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           const int c4 = lane + 32 * (2 * half + c);
@@ -1085,7 +1107,8 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
 namespace lenet {
 constexpr size_t kClusterSmemBytes =
     (size_t)(XN + 456 + A1N + 2416 + FLAT + F1 + 88 + 16 + 16 + 88 + F1 + FLAT + A1N + 6400 + 4 * A1N + CS * FLAT + CS * A1N + 4 * 128) * 4 +
-    (size_t)(A1N + FLAT) * 4 + (size_t)(30 * FLAT + F2 * F1 + NC * F2 + 256) * 4 + 64;
+    (size_t)(A1N + FLAT) * 4 + 64;
+constexpr size_t kClusterSmemBytesMulti = kClusterSmemBytes + (size_t)(30 * FLAT + F2 * F1 + NC * F2 + 256) * 4;
 }
 
 namespace lenet {
@@ -1103,6 +1126,49 @@ extern "C" long long mlt_lenet_scratch_bytes(int B) { return (long long)B * lene
 // param_off: arena element offsets of {conv1.w, conv1.b, conv2.w, conv2.b, fc1.w, fc1.b, fc2.w, fc2.b, fc3.w, fc3.b}.
 // scratch: mlt_lenet_scratch_bytes(B) bytes, zero-initialised once (its first 256 bytes hold the grid-barrier words).
 // ctx: NULL or world == 1 for single-GPU; otherwise gradients are all-reduced in-kernel through the symmetric arena.
+template <typename R, bool MULTI>
+static int lenet_launch_cluster(LeNetArgs& a, long long numel, cudaStream_t st, int dev) {
+  using namespace lenet;
+  auto kern = lenet_step_cluster_kernel<R, MULTI>;
+  constexpr size_t kSmem = MULTI ? kClusterSmemBytesMulti : kClusterSmemBytes;
+  static int grid_cl[64] = {};
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = kSmem;
+  cfg.stream = st;
+  cudaLaunchAttribute attrs[2];
+  attrs[0].id = cudaLaunchAttributeClusterDimension;
+  attrs[0].val.clusterDim.x = CS; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
+  attrs[1].id = cudaLaunchAttributeCooperative;
+  attrs[1].val.cooperative = 1;
+  cfg.attrs = attrs;
+  if (grid_cl[dev & 63] == 0) {
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    int sms = 0, nclus = 0;
+    MLT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    cfg.gridDim = dim3((sms / CS) * CS);
+    cfg.numAttrs = 1;
+    MLT_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclus, kern, &cfg));
+    MLT_REQUIRE(nclus >= 1, "mlt_lenet_step: no 4-CTA cluster fits on this device");
+    grid_cl[dev & 63] = nclus * CS;
+  }
+  const int grid = grid_cl[dev & 63];
+  const long long min_grid = ceil_div64(numel, (long long)kThreads * kMaxPerThread);
+  MLT_REQUIRE(grid >= min_grid && grid <= kMaxCtas - 1, "mlt_lenet_step: grid %d cannot cover %lld parameters", grid, numel);
+  cfg.gridDim = dim3(grid);
+  static bool coop_ok = true;                     // cooperative + cluster launch; fall back to a plain cluster launch
+  cfg.numAttrs = coop_ok ? 2 : 1;                 // (all CTAs are co-resident by construction: grid <= active clusters)
+  cudaError_t le = cudaLaunchKernelEx(&cfg, kern, a);
+  if (le != cudaSuccess && coop_ok) {
+    (void)cudaGetLastError();
+    coop_ok = false;
+    cfg.numAttrs = 1;
+    le = cudaLaunchKernelEx(&cfg, kern, a);
+  }
+  MLT_CHECK_CUDA(le);
+  return 0;
+}
+
 // Launch the step kernel for the arguments in `a` (single step, or a.nsteps steps in one launch: cluster kernel only).
 static int lenet_launch(LeNetArgs& a, int rule, long long numel, void* stream) {
   using namespace lenet;
@@ -1113,45 +1179,7 @@ static int lenet_launch(LeNetArgs& a, int rule, long long numel, void* stream) {
   static const bool use_cluster = []{ const char* e = getenv("MLT_LENET_CLUSTER"); return !(e && e[0] == '0'); }();
   MLT_REQUIRE(a.nsteps < 1 || use_cluster, "multi-step launches need the cluster kernel (MLT_LENET_CLUSTER=0 is set)");
   MLT_DISPATCH_RULE(rule, R, {
-    if (use_cluster) {
-      auto kern = lenet_step_cluster_kernel<R>;
-      static int grid_cl[64] = {};
-      cudaLaunchConfig_t cfg{};
-      cfg.blockDim = dim3(kThreads);
-      cfg.dynamicSmemBytes = kClusterSmemBytes;
-      cfg.stream = st;
-      cudaLaunchAttribute attrs[2];
-      attrs[0].id = cudaLaunchAttributeClusterDimension;
-      attrs[0].val.clusterDim.x = CS; attrs[0].val.clusterDim.y = 1; attrs[0].val.clusterDim.z = 1;
-      attrs[1].id = cudaLaunchAttributeCooperative;
-      attrs[1].val.cooperative = 1;
-      cfg.attrs = attrs;
-      if (grid_cl[dev & 63] == 0) {
-        MLT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kClusterSmemBytes));
-        int sms = 0, nclus = 0;
-        MLT_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-        cfg.gridDim = dim3((sms / CS) * CS);
-        cfg.numAttrs = 1;
-        MLT_CHECK_CUDA(cudaOccupancyMaxActiveClusters(&nclus, kern, &cfg));
-        MLT_REQUIRE(nclus >= 1, "mlt_lenet_step: no 4-CTA cluster fits on this device");
-        grid_cl[dev & 63] = nclus * CS;
-      }
-      const int grid = grid_cl[dev & 63];
-      const long long min_grid = ceil_div64(numel, (long long)kThreads * kMaxPerThread);
-      MLT_REQUIRE(grid >= min_grid && grid <= kMaxCtas - 1, "mlt_lenet_step: grid %d cannot cover %lld parameters", grid, numel);
-      cfg.gridDim = dim3(grid);
-      static bool coop_ok = true;                     // cooperative + cluster launch; fall back to a plain cluster launch
-      cfg.numAttrs = coop_ok ? 2 : 1;                 // (all CTAs are co-resident by construction: grid <= active clusters)
-      cudaError_t le = cudaLaunchKernelEx(&cfg, kern, a);
-      if (le != cudaSuccess && coop_ok) {
-        (void)cudaGetLastError();
-        coop_ok = false;
-        cfg.numAttrs = 1;
-        le = cudaLaunchKernelEx(&cfg, kern, a);
-      }
-      MLT_CHECK_CUDA(le);
-      return 0;
-    }
+    if (use_cluster) return a.nsteps >= 1 ? lenet_launch_cluster<R, true>(a, numel, st, dev) : lenet_launch_cluster<R, false>(a, numel, st, dev);
     MLT_REQUIRE(a.nsteps < 1, "multi-step launches need the cluster kernel");
     auto kern = lenet_step_kernel<R>;
     static int grid_cache[64] = {};
