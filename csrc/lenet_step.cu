@@ -1098,8 +1098,8 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     if (tid == 0) s_sense += 1;
     grid_barrier(a.sync, gridDim.x, s_sense + 0u);
     if (tid == 0) s_sense += 1;
-    if (blockIdx.x == 0 && tid == 0 && a.progress) { __threadfence_system(); *a.progress = (unsigned int)(step + 1); }
-    __syncthreads();
+    // (no system fence: the host only uses the word to know the step's INPUT slot has been read; losses are read after the run)
+    if (blockIdx.x == 0 && tid == 0 && a.progress) *reinterpret_cast<volatile unsigned int*>(a.progress) = (unsigned int)(step + 1);
   }
   }  // step loop
 }

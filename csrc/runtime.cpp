@@ -61,6 +61,13 @@ struct Loop {
   long long loss_cap = 0;
   float* dev_hyper = nullptr;           // [max_steps][8] device copy of the whole epoch's hyper rows (kernel steps)
   long long dev_hyper_cap = 0;
+  // persistent LeNet runs (step kind 2): the whole epoch is ONE kernel launch that waits for each slot to be filled
+  unsigned int* dev_ready = nullptr;    // device word the copy stream advances to i + 1 after step i's batch has landed
+  unsigned int* pin_progress = nullptr; // pinned host word the kernel advances to i + 1 after step i
+  unsigned int* pin_seq = nullptr;      // pinned [max_steps] = 1, 2, 3, ... (source of the ready updates)
+  long long seq_cap = 0;
+  int* dev_bs = nullptr;                // [max_steps] per-step batch sizes
+  long long bs_cap = 0;
   // statistics of the last run
   long long h2d_bytes = 0, d2h_bytes = 0, launches = 0;
   // Large samples (images): skip the host gather of x and let the copy engine gather instead - one cudaMemcpyAsync per
@@ -126,6 +133,10 @@ extern "C" int mlt_loop_destroy(void* loop) {
   if (L->pin_hyper) cudaFreeHost(L->pin_hyper);
   if (L->pin_loss) cudaFreeHost(L->pin_loss);
   if (L->dev_hyper) cudaFree(L->dev_hyper);
+  if (L->dev_ready) cudaFree(L->dev_ready);
+  if (L->pin_progress) cudaFreeHost(L->pin_progress);
+  if (L->pin_seq) cudaFreeHost(L->pin_seq);
+  if (L->dev_bs) cudaFree(L->dev_bs);
   cudaStreamDestroy(L->copy);
   delete L;
   return 0;
@@ -137,6 +148,8 @@ extern "C" int mlt_loop_destroy(void* loop) {
 //   batch_sizes       per-step batch size (<= max_batch); NULL = every step uses `batch`
 //   hyper_rows        [steps][8] floats copied to `hyper_dev` before each step (NULL for evaluation)
 //   step kind 0       LeNet single-kernel step: lenet points at the fixed arguments of mlt_lenet_step
+//   step kind 2       the same LeNet step as ONE persistent launch for the whole run (mlt_lenet_steps): the kernel waits on a
+//                     device word the copy stream advances after each batch, the host watches a pinned progress word
 //   step kind 1       captured CUDA graphs, one cudaGraphExec_t per slot in graph_execs (inputs bound to the slot buffers)
 //   loss_dev          device scalar the step writes its loss to; copied to loss_host[step] every step
 extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, const long long* indices, long long steps,
@@ -148,26 +161,30 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
   cudaStream_t cs = (cudaStream_t)compute_stream;
   if (steps <= 0) return 0;
   if (batch > L->max_batch) { set_error("mlt_loop_run: batch %d exceeds the loop's max_batch %lld", batch, L->max_batch); return 1; }
+  // per-run tables are sized generously on first use: a pinned (re)allocation costs a few hundred microseconds, which would
+  // otherwise land inside the first longer epoch
+  const long long cap = steps < 8192 ? 8192 : steps + steps / 2;
   if (hyper_rows && steps > L->hyper_cap) {
     if (L->pin_hyper) cudaFreeHost(L->pin_hyper);
-    RT_CHECK(cudaHostAlloc((void**)&L->pin_hyper, (size_t)steps * 8 * sizeof(float), cudaHostAllocDefault));
-    L->hyper_cap = steps;
+    RT_CHECK(cudaHostAlloc((void**)&L->pin_hyper, (size_t)cap * 8 * sizeof(float), cudaHostAllocDefault));
+    L->hyper_cap = cap;
   }
   if (hyper_rows) std::memcpy(L->pin_hyper, hyper_rows, (size_t)steps * 8 * sizeof(float));
   if (loss_dev && steps > L->loss_cap) {
     if (L->pin_loss) cudaFreeHost(L->pin_loss);
-    RT_CHECK(cudaHostAlloc((void**)&L->pin_loss, (size_t)steps * sizeof(float), cudaHostAllocDefault));
-    L->loss_cap = steps;
+    RT_CHECK(cudaHostAlloc((void**)&L->pin_loss, (size_t)cap * sizeof(float), cudaHostAllocDefault));
+    L->loss_cap = cap;
   }
   L->h2d_bytes = L->d2h_bytes = L->launches = 0;
   // Single-kernel steps read their hyper-parameter row straight from a device table uploaded once per run, and write
   // their loss straight into the pinned host array (a posted store over PCIe): no per-step copy operations at all.
-  const bool table_mode = step_kind == 0;
+  const bool table_mode = step_kind == 0 || step_kind == 2;
+  const bool persistent = step_kind == 2;
   if (table_mode && hyper_rows) {
     if (steps > L->dev_hyper_cap) {
       if (L->dev_hyper) cudaFree(L->dev_hyper);
-      RT_CHECK(cudaMalloc((void**)&L->dev_hyper, (size_t)steps * 8 * sizeof(float)));
-      L->dev_hyper_cap = steps;
+      RT_CHECK(cudaMalloc((void**)&L->dev_hyper, (size_t)cap * 8 * sizeof(float)));
+      L->dev_hyper_cap = cap;
     }
     RT_CHECK(cudaMemcpyAsync(L->dev_hyper, L->pin_hyper, (size_t)steps * 8 * sizeof(float), cudaMemcpyHostToDevice, cs));
     L->h2d_bytes += steps * 32;
@@ -196,6 +213,37 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
   });
 
   int rc = 0;
+  if (persistent) {
+    // ONE launch for the whole run: the kernel walks the ring, gated by *dev_ready, and reports through *pin_progress
+    auto fail = [&](const char* what) { abort.store(true); gatherer.join(); set_error("mlt_loop_run: %s", what); return 1; };
+    if (S > 8 || steps > 0x7fffffffLL) return fail("persistent runs need <= 8 slots");
+    if (!L->dev_ready && cudaMalloc((void**)&L->dev_ready, 256) != cudaSuccess) return fail("cudaMalloc failed");
+    if (!L->pin_progress && cudaHostAlloc((void**)&L->pin_progress, 256, cudaHostAllocDefault) != cudaSuccess) return fail("cudaHostAlloc failed");
+    if (steps > L->seq_cap) {
+      if (L->pin_seq) cudaFreeHost(L->pin_seq);
+      if (cudaHostAlloc((void**)&L->pin_seq, (size_t)steps * 4, cudaHostAllocDefault) != cudaSuccess) return fail("cudaHostAlloc failed");
+      for (long long i = 0; i < steps; ++i) L->pin_seq[i] = (unsigned int)(i + 1);
+      L->seq_cap = steps;
+    }
+    if (batch_sizes && steps > L->bs_cap) {
+      if (L->dev_bs) cudaFree(L->dev_bs);
+      if (cudaMalloc((void**)&L->dev_bs, (size_t)steps * 4) != cudaSuccess) return fail("cudaMalloc failed");
+      L->bs_cap = steps;
+    }
+    if (batch_sizes && cudaMemcpyAsync(L->dev_bs, batch_sizes, (size_t)steps * 4, cudaMemcpyHostToDevice, cs) != cudaSuccess) return fail("batch-size upload failed");
+    if (cudaMemsetAsync(L->dev_ready, 0, 4, cs) != cudaSuccess) return fail("memset failed");
+    *(volatile unsigned int*)L->pin_progress = 0u;
+    const void* xs[8]; const void* ys[8];
+    for (int k = 0; k < S; ++k) { xs[k] = L->ring[k].dev_x; ys[k] = L->ring[k].dev_y; }
+    if (cudaStreamSynchronize(cs) != cudaSuccess) return fail("stream sync failed");      // tables and the zeroed ready word are in place
+    if (mlt_lenet_steps(lenet->master, lenet->s1, lenet->s2, lenet->hyper, lenet->numel, lenet->param_off, lenet->rule, xs, ys, S, 0,
+                        batch, batch_sizes ? L->dev_bs : nullptr, hyper_rows ? (const void*)L->dev_hyper : nullptr,
+                        loss_dev ? (void*)L->pin_loss : nullptr, L->dev_ready, L->pin_progress, (int)steps, lenet->train,
+                        lenet->want_acc, lenet->acc3, lenet->scratch, lenet->scratch_bytes, lenet->ctx, cs) != 0) {
+      abort.store(true); gatherer.join(); return 1;
+    }
+    L->launches += 1;
+  }
   for (long long i = 0; i < steps; ++i) {
     const int s = (int)(i % S);
     Slot& sl = L->ring[s];
@@ -209,7 +257,18 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
     }
     while (gathered[s].load(std::memory_order_acquire) != i + 1) std::this_thread::yield();
     // device buffers of this slot are free once the step that last used them has finished
-    if (sl.used) { if ((rc = (int)cudaStreamWaitEvent(L->copy, sl.released, 0)) != 0) break; }
+    if (persistent) {
+      if (i >= S) {
+        const unsigned int need = (unsigned int)(i - S + 1);
+        volatile unsigned int* prog = L->pin_progress;
+        long long spins = 0;
+        while (*prog < need) {
+          if (*prog == 0xFFFFFFFFu || ++spins > (1LL << 34)) { rc = (int)cudaErrorLaunchTimeout; break; }
+          if ((spins & 1023) == 0) std::this_thread::yield();
+        }
+        if (rc != 0) break;
+      }
+    } else if (sl.used) { if ((rc = (int)cudaStreamWaitEvent(L->copy, sl.released, 0)) != 0) break; }
     if (L->direct_x) {
       const long long* idx = indices + start[i];
       for (long long j = 0; j < n && rc == 0; ) {
@@ -226,6 +285,12 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
     if ((rc = (int)cudaMemcpyAsync(sl.dev_y, sl.pin_y, (size_t)n * L->y_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
     if ((rc = (int)cudaEventRecord(sl.ready, L->copy)) != 0) break;
     L->h2d_bytes += n * (long long)(L->x_row + L->y_row);
+    if (persistent) {
+      // publish "step i has landed" behind the copies on the same stream; the running kernel polls the word
+      if ((rc = (int)cudaMemcpyAsync(L->dev_ready, L->pin_seq + i, 4, cudaMemcpyHostToDevice, L->copy)) != 0) break;
+      if (loss_dev) L->d2h_bytes += 4;
+      continue;
+    }
     if ((rc = (int)cudaStreamWaitEvent(cs, sl.ready, 0)) != 0) break;
     if (hyper_rows && !table_mode) {
       if ((rc = (int)cudaMemcpyAsync(hyper_dev, L->pin_hyper + i * 8, 8 * sizeof(float), cudaMemcpyHostToDevice, cs)) != 0) break;
@@ -257,6 +322,10 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
   gatherer.join();
   if (rc != 0) return rc;
   RT_CHECK(cudaStreamSynchronize(cs));
+  if (persistent && *(volatile unsigned int*)L->pin_progress != (unsigned int)steps) {
+    set_error("mlt_loop_run: the persistent step kernel stopped after %u of %lld steps", *(volatile unsigned int*)L->pin_progress, steps);
+    return 1;
+  }
   if (loss_dev && loss_host) std::memcpy(loss_host, L->pin_loss, (size_t)steps * sizeof(float));
   return 0;
 }

@@ -140,3 +140,29 @@ def test_multi_step_launch_equals_single_steps(tmp_path, optimizer):
     assert torch.equal(la, lb), (la, lb)
     assert torch.equal(a.optimizer.master, b.optimizer.master)
     assert acc[2].item() == K and abs(acc[0].item() - lb.sum().item()) < 1e-4
+
+
+@pytest.mark.parametrize("persistent", ["1", "0"])
+def test_native_executor_persistent_and_per_step_modes(tmp_path, monkeypatch, persistent):
+    """Executor kinds 2 (one persistent launch per run) and 0 (one launch per step), ragged last batch, cosine LR per step."""
+    from ml_trainer_b200 import Loader, MLModel, SyntheticDataset, Trainer
+
+    monkeypatch.setenv("MLT_LENET_PERSISTENT", persistent)
+    outs = []
+    for native in (True, False):
+        torch.manual_seed(32)
+        tr = SyntheticDataset((3, 32, 32), 10, length=150, seed=3)        # 4 x 32 + 22
+        va = SyntheticDataset((3, 32, 32), 10, length=70, seed=4)
+        t = Trainer(MLModel(), datasets=(tr, va), epochs=3, batch_size=32, model_dir=str(tmp_path / f"{persistent}{native}"), progress=False,
+                    optimizer="adamw", lr=0.01, metric="accuracy", scheduler="CosineAnnealingWarmRestarts", native_loop=native, seed=32)
+        t.train_loader = Loader(tr, batch_size=32, shuffle=False, pin_memory=True)
+        t.val_loader = Loader(va, batch_size=32, shuffle=False, pin_memory=True)
+        t.fit()
+        outs.append(t)
+    a, b = outs
+    assert a._nloop.last_kind == (2 if persistent == "1" else 0)
+    assert a.train_losses == pytest.approx(b.train_losses, rel=1e-5)
+    assert a.val_losses == pytest.approx(b.val_losses, rel=1e-5)
+    assert a.val_metrics == pytest.approx(b.val_metrics, abs=1e-6)
+    for p, q in zip(a.model.parameters(), b.model.parameters()):
+        assert torch.allclose(p, q, rtol=1e-4, atol=1e-6)
