@@ -181,6 +181,26 @@ class FusedOptimizer(torch.optim.Optimizer):
         return Hyper(lr=float(g["lr"]), wd=float(g["weight_decay"]), b1=float(b1), b2=float(g["betas"][1]),
                      eps=float(g["eps"]), step=self.step_count + 1, grad_scale=grad_scale)
 
+    def hyper_rows(self, n: int, grad_scale: float = 1.0, lrs=None) -> torch.Tensor:
+        """The next ``n`` steps' hyper vectors as an ``[n, 8]`` fp32 tensor (what the native executors upload per run):
+        ``Hyper.pack()`` for steps ``step_count+1 .. step_count+n``, vectorised.  ``lrs``: optional per-step learning rates."""
+        import numpy as np
+
+        g = self.param_groups[0]
+        b1 = float(g["momentum"] if self.kind == "sgd" else g["betas"][0])
+        b2 = float(g["betas"][1])
+        steps = np.arange(self.step_count + 1, self.step_count + n + 1, dtype=np.float64)
+        rows = np.empty((n, 8), dtype=np.float64)
+        rows[:, 0] = float(g["lr"]) if lrs is None else np.asarray(lrs, dtype=np.float64)
+        rows[:, 1] = float(g["weight_decay"])
+        rows[:, 2] = b1
+        rows[:, 3] = b2
+        rows[:, 4] = float(g["eps"])
+        rows[:, 5] = 1.0 - np.power(b1, steps)
+        rows[:, 6] = np.sqrt(1.0 - np.power(b2, steps))
+        rows[:, 7] = grad_scale
+        return torch.from_numpy(rows.astype(np.float32))
+
     # ------------------------------------------------------------------- step
     def begin_step(self, grad_scale: float = 1.0, upload: bool = True) -> Hyper:
         """Advance the step counter and publish this step's hyper-parameters."""

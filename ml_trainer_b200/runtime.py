@@ -129,9 +129,18 @@ class NativeLoop:
 
 def epoch_indices(loader) -> tuple:
     """Flatten a Loader's batch order into (int64 index tensor, per-step batch sizes)."""
-    batches: List[List[int]] = [list(b) for b in loader.batch_sampler]
-    sizes = [len(b) for b in batches]
-    flat = torch.tensor([i for b in batches for i in b], dtype=torch.int64)
+    bs = loader.batch_sampler
+    if type(bs) is torch.utils.data.BatchSampler:
+        # stock batching: the order IS the sampler's order, cut every batch_size (one pass, no list per batch)
+        flat = torch.tensor(list(bs.sampler), dtype=torch.int64)
+        n, B = flat.numel(), bs.batch_size
+        full, rem = divmod(n, B)
+        sizes = [B] * full + ([rem] if rem and not bs.drop_last else [])
+        flat = flat[:sum(sizes)]
+    else:
+        batches: List[List[int]] = [list(b) for b in bs]
+        sizes = [len(b) for b in batches]
+        flat = torch.tensor([i for b in batches for i in b], dtype=torch.int64)
     pool = getattr(loader, "_pool", None)
     if pool is not None:
         flat = flat % pool

@@ -356,14 +356,17 @@ class Trainer:
         nb = len(sizes)
         hyper = None
         if train:
-            rows = []
-            for i in range(nb):          # the LR schedule is evaluated up front, one row of hyper-parameters per step
-                rows.append(opt.hyper_for_next_step(self.reducer.grad_scale).pack())
-                opt.step_count += 1
-                opt._opt_called = True
-                if self.scheduler_type == "CosineAnnealingWarmRestarts":
-                    self.scheduler.step(epoch - 1 + i / nb)  # as per pytorch docs
-            hyper = torch.tensor(rows, dtype=torch.float32)
+            # the LR schedule is evaluated up front, one row of hyper-parameters per step
+            lrs = None
+            if self.scheduler_type == "CosineAnnealingWarmRestarts":        # stepped per batch (as per pytorch docs)
+                lrs = []
+                for i in range(nb):
+                    lrs.append(float(opt.param_groups[0]["lr"]))
+                    opt._opt_called = True
+                    self.scheduler.step(epoch - 1 + i / nb)
+            hyper = opt.hyper_rows(nb, self.reducer.grad_scale, lrs)
+            opt.step_count += nb
+            opt._opt_called = True
         loop = self._native_loop_for(loader)
         x, y = loader._backing[0], loader._backing[1]
         losses = loop.run_lenet(eng.fused, x, y, idx, loader.batch_size, sizes, hyper, train, eng.acc,
