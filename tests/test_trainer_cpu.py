@@ -208,3 +208,20 @@ def test_tracing_phases_are_noops_on_cpu(tmp_path):
     with tracing.phase("anything"):
         pass
     assert tracing.PhaseTimer().summary() == {}
+
+
+def test_epoch_indices_matches_batch_sampler():
+    """The flattened epoch order handed to the native executor == what iterating the loader's batch sampler yields."""
+    from ml_trainer_b200 import Loader, SyntheticDataset
+    from ml_trainer_b200.runtime import epoch_indices
+
+    ds = SyntheticDataset((3, 32, 32), 10, length=77, seed=3)
+    for shuffle, drop_last in ((False, False), (True, False), (True, True)):
+        g = torch.Generator().manual_seed(5)
+        ld = Loader(ds, batch_size=16, shuffle=shuffle, drop_last=drop_last, generator=g)
+        g.manual_seed(5)
+        want = [list(b) for b in ld.batch_sampler]
+        g.manual_seed(5)
+        flat, sizes = epoch_indices(ld)
+        assert sizes == [len(b) for b in want]
+        assert flat.tolist() == [i for b in want for i in b]
