@@ -127,12 +127,46 @@ class NativeLoop:
         return losses
 
 
+def _sampler_order(sampler) -> torch.Tensor:
+    """The index order a stock sampler would yield, as one tensor.  The common samplers are reproduced with the SAME
+    random draws their ``__iter__`` makes (so a native epoch sees exactly the order a Python epoch would); anything else
+    is simply iterated."""
+    from torch.utils.data import RandomSampler, SequentialSampler
+    from torch.utils.data.distributed import DistributedSampler
+
+    if type(sampler) is SequentialSampler:
+        return torch.arange(len(sampler.data_source), dtype=torch.int64)
+    if type(sampler) is RandomSampler and not sampler.replacement and sampler.num_samples == len(sampler.data_source):
+        g = sampler.generator
+        if g is None:
+            g = torch.Generator()
+            g.manual_seed(int(torch.empty((), dtype=torch.int64).random_().item()))
+        return torch.randperm(len(sampler.data_source), generator=g)
+    if type(sampler) is DistributedSampler:
+        n = len(sampler.dataset)
+        if sampler.shuffle:
+            g = torch.Generator()
+            g.manual_seed(sampler.seed + sampler.epoch)
+            idx = torch.randperm(n, generator=g)
+        else:
+            idx = torch.arange(n, dtype=torch.int64)
+        if not sampler.drop_last:
+            pad = sampler.total_size - n
+            if pad > 0:
+                reps = -(-pad // n)
+                idx = torch.cat([idx, idx.repeat(reps)[:pad]])
+        else:
+            idx = idx[:sampler.total_size]
+        return idx[sampler.rank:sampler.total_size:sampler.num_replicas].contiguous()
+    return torch.tensor(list(sampler), dtype=torch.int64)
+
+
 def epoch_indices(loader) -> tuple:
     """Flatten a Loader's batch order into (int64 index tensor, per-step batch sizes)."""
     bs = loader.batch_sampler
     if type(bs) is torch.utils.data.BatchSampler:
         # stock batching: the order IS the sampler's order, cut every batch_size (one pass, no list per batch)
-        flat = torch.tensor(list(bs.sampler), dtype=torch.int64)
+        flat = _sampler_order(bs.sampler)
         n, B = flat.numel(), bs.batch_size
         full, rem = divmod(n, B)
         sizes = [B] * full + ([rem] if rem and not bs.drop_last else [])

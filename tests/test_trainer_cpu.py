@@ -225,3 +225,29 @@ def test_epoch_indices_matches_batch_sampler():
         flat, sizes = epoch_indices(ld)
         assert sizes == [len(b) for b in want]
         assert flat.tolist() == [i for b in want for i in b]
+
+
+def test_sampler_order_reproduces_stock_samplers():
+    from torch.utils.data import RandomSampler, SequentialSampler
+    from torch.utils.data.distributed import DistributedSampler
+
+    from ml_trainer_b200 import SyntheticDataset
+    from ml_trainer_b200.runtime import _sampler_order
+
+    ds = SyntheticDataset((3, 32, 32), 10, length=53, seed=3)
+    assert _sampler_order(SequentialSampler(ds)).tolist() == list(SequentialSampler(ds))
+    g = torch.Generator().manual_seed(9)
+    rs = RandomSampler(ds, generator=g)
+    want = list(rs)
+    g.manual_seed(9)
+    assert _sampler_order(rs).tolist() == want
+    torch.manual_seed(123)
+    want = list(RandomSampler(ds))                    # no generator: seeded from the global RNG
+    torch.manual_seed(123)
+    assert _sampler_order(RandomSampler(ds)).tolist() == want
+    for shuffle in (True, False):
+        for drop_last in (True, False):
+            for rank in (0, 2):
+                d = DistributedSampler(ds, num_replicas=4, rank=rank, shuffle=shuffle, drop_last=drop_last, seed=5)
+                d.set_epoch(3)
+                assert _sampler_order(d).tolist() == list(d), (shuffle, drop_last, rank)
