@@ -52,3 +52,24 @@ def test_trainer_runs_bert_tiny_on_cpu(tmp_path):
                 model_dir=str(tmp_path), progress=False)
     t.fit()
     assert t.train_losses[1] < t.train_losses[0]
+
+
+def test_attention_mask_matches_hf():
+    """HuggingFace-style key-padding mask (1 = attend, 0 = padding): same logits as HF on padded batches."""
+    from ml_trainer_b200 import build_model
+
+    torch.manual_seed(1)
+    kw = dict(vocab_size=1000, hidden_size=128, num_hidden_layers=2, num_attention_heads=2, intermediate_size=512,
+              max_position_embeddings=128, num_labels=2)
+    ours = build_model("bert_tiny").eval()
+    hf = _hf(kw).eval()
+    hf.load_state_dict(ours.state_dict(), strict=False)
+    ids = torch.randint(0, 1000, (3, 48))
+    mask = torch.ones(3, 48, dtype=torch.long)
+    mask[0, 30:] = 0
+    mask[2, 10:] = 0
+    with torch.no_grad():
+        lo = ours(ids, attention_mask=mask)
+        lh = hf(input_ids=ids, attention_mask=mask).logits
+        assert torch.allclose(lo, lh, atol=2e-5), (lo - lh).abs().max()
+        assert not torch.equal(lo, ours(ids))                      # the mask matters
