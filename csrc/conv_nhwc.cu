@@ -73,18 +73,28 @@ col2im_nhwc_kernel(const uint4* __restrict__ dcol, uint4* __restrict__ dx, int B
   }
 }
 
-// NCHW fp32 -> NHWC bf16 with the channel dim zero-padded to Cp (the 3-channel stem is padded to 8 for 16-byte vectors)
+// NCHW fp32 -> NHWC bf16 with the channel dim zero-padded to Cp (a multiple of 8; the 3-channel stem is padded to 8).
+// A thread produces 8 channels of one pixel: 8 plane reads that are coalesced across the warp (consecutive pixels) and one
+// 16-byte store.
 __global__ void __launch_bounds__(256)
-nchw_to_nhwc_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int B, int C, int H, int W, int Cp) {
-  const long long total = (long long)B * H * W * Cp;
+nchw_to_nhwc_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, int B, int C, int HW, int Cp8) {
+  const long long total = (long long)B * HW * Cp8;
   const long long step = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
-    const int c = (int)(i % Cp);
-    long long r = i / Cp;
-    const int w = (int)(r % W); r /= W;
-    const int h = (int)(r % H);
-    const int b = (int)(r / H);
-    y[i] = __float2bfloat16_rn(c < C ? x[(((size_t)b * C + c) * H + h) * W + w] : 0.f);
+    // pixel index fastest within a channel group so the warp's plane reads are contiguous
+    const long long hw = i % HW;
+    long long r = i / HW;
+    const int g = (int)(r % Cp8);
+    const long long b = r / Cp8;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = g * 8 + j;
+      v[j] = c < C ? __ldg(x + ((size_t)b * C + c) * HW + hw) : 0.f;
+    }
+    uint4 o;
+    o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]); o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+    reinterpret_cast<uint4*>(y)[((size_t)b * HW + hw) * Cp8 + g] = o;
   }
 }
 
@@ -122,41 +132,35 @@ maxpool_nhwc_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, unsi
   }
 }
 
+// grid = (ceil(W * C8 / 256), H, B): no per-element index decomposition; only the (at most ceil(K/stride)^2) windows that
+// cover an input pixel are visited, their loads are independent.
 __global__ void __launch_bounds__(256)
 maxpool_nhwc_bwd_kernel(const uint4* __restrict__ dy, const unsigned char* __restrict__ idx, uint4* __restrict__ dx, int B, int H,
                         int W, int C8, int K, int stride, int pad, int OH, int OW) {
-  const long long total = (long long)B * H * W * C8;
-  const long long step = (long long)gridDim.x * blockDim.x;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
-    const int c = (int)(i % C8);
-    long long r = i / C8;
-    const int w = (int)(r % W); r /= W;
-    const int h = (int)(r % H);
-    const int b = (int)(r / H);
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (int kh = 0; kh < K; ++kh) {
-      const int th = h + pad - kh;
-      if (th < 0 || th % stride != 0) continue;
-      const int oh = th / stride;
-      if (oh >= OH) continue;
-      for (int kw = 0; kw < K; ++kw) {
-        const int tw = w + pad - kw;
-        if (tw < 0 || tw % stride != 0) continue;
-        const int ow = tw / stride;
-        if (ow >= OW) continue;
-        const size_t o = (((size_t)b * OH + oh) * OW + ow) * C8 + c;
-        unsigned char am[8];
-        *reinterpret_cast<uint2*>(am) = *reinterpret_cast<const uint2*>(idx + o * 8);
-        float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        add8(g, dy[o]);
-        const unsigned char me = (unsigned char)(kh * K + kw);
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= W * C8) return;
+  const int w = t / C8, c = t - w * C8;
+  const int h = blockIdx.y, b = blockIdx.z;
+  // windows oh with oh*stride - pad <= h <= oh*stride - pad + K - 1
+  const int oh_lo = max(0, (h + pad - K + stride) / stride), oh_hi = min(OH - 1, (h + pad) / stride);
+  const int ow_lo = max(0, (w + pad - K + stride) / stride), ow_hi = min(OW - 1, (w + pad) / stride);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int oh = oh_lo; oh <= oh_hi; ++oh) {
+    const int kh = h + pad - oh * stride;
+    for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+      const int kw = w + pad - ow * stride;
+      const size_t o = (((size_t)b * OH + oh) * OW + ow) * C8 + c;
+      unsigned char am[8];
+      *reinterpret_cast<uint2*>(am) = *reinterpret_cast<const uint2*>(idx + o * 8);
+      float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      add8(g, dy[o]);
+      const unsigned char me = (unsigned char)(kh * K + kw);
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (am[j] == me) acc[j] += g[j];
-      }
+      for (int j = 0; j < 8; ++j)
+        if (am[j] == me) acc[j] += g[j];
     }
-    dx[i] = pack8f(acc);
   }
+  dx[(((size_t)b * H + h) * W + w) * C8 + c] = pack8f(acc);
 }
 
 // y[b][c] = mean over HW of x[b][hw][c]
@@ -220,9 +224,9 @@ extern "C" int mlt_col2im_nhwc(const void* dcol, void* dx, int B, int H, int W, 
 }
 
 extern "C" int mlt_nchw_to_nhwc_bf16(const void* x_f32, void* y_bf16, int B, int C, int H, int W, int Cp, void* stream) {
-  MLT_REQUIRE(Cp >= C, "mlt_nchw_to_nhwc_bf16: padded channel count smaller than C");
-  nchw_to_nhwc_bf16_kernel<<<grid_for((long long)B * H * W * Cp), 256, 0, (cudaStream_t)stream>>>((const float*)x_f32,
-                                                                                                (__nv_bfloat16*)y_bf16, B, C, H, W, Cp);
+  MLT_REQUIRE(Cp >= C && Cp % 8 == 0, "mlt_nchw_to_nhwc_bf16: the padded channel count must be a multiple of 8 and >= C");
+  nchw_to_nhwc_bf16_kernel<<<grid_for((long long)B * H * W * (Cp / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const float*)x_f32, (__nv_bfloat16*)y_bf16, B, C, H * W, Cp / 8);
   MLT_LAUNCH_CHECK();
   return 0;
 }
@@ -239,7 +243,8 @@ extern "C" int mlt_maxpool_nhwc_fwd(const void* x, void* y, void* idx_u8, int B,
 extern "C" int mlt_maxpool_nhwc_bwd(const void* dy, const void* idx_u8, void* dx, int B, int H, int W, int C, int K, int stride,
                                     int pad, int OH, int OW, void* stream) {
   MLT_REQUIRE(C % 8 == 0, "mlt_maxpool_nhwc_bwd: unsupported shape");
-  maxpool_nhwc_bwd_kernel<<<grid_for((long long)B * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+  MLT_REQUIRE(H <= 65535 && B <= 65535, "mlt_maxpool_nhwc_bwd: H and B must fit a grid dimension");
+  maxpool_nhwc_bwd_kernel<<<dim3(ceil_div(W * (C / 8), 256), H, B), 256, 0, (cudaStream_t)stream>>>(
       (const uint4*)dy, (const unsigned char*)idx_u8, (uint4*)dx, B, H, W, C / 8, K, stride, pad, OH, OW);
   MLT_LAUNCH_CHECK();
   return 0;
