@@ -1,20 +1,50 @@
-import sys, time, torch
+"""Where does a short native epoch spend its host time?  K-step epochs of MLModel through Trainer.train_epoch with
+wall-clock timers around the Python stages and the C++ executor's own timestamps.  Usage: python bench/epoch_profile.py [K] [R]"""
+import json
+import sys
+import time
+
+import torch
+
 sys.path.insert(0, ".")
-from ml_trainer_b200 import SyntheticDataset, Trainer, build_model, Loader
 import ml_trainer_b200.runtime as rt
-K=200
-warm = SyntheticDataset((3,32,32),10,length=32*24,seed=7,pool=8192)
-timed = SyntheticDataset((3,32,32),10,length=32*K,seed=32,pool=min(32*K,8192))
-tr = Trainer(build_model("mlmodel"), datasets=(warm, warm), epochs=1, batch_size=32, optimizer="sgd", lr=1e-3, momentum=0.9, metric=None, progress=False, model_dir="/tmp/ep", seed=32)
+from ml_trainer_b200 import Loader, SyntheticDataset, Trainer, build_model
+
+K = int(sys.argv[1]) if len(sys.argv) > 1 else 20
+R = int(sys.argv[2]) if len(sys.argv) > 2 else 7
+warm = SyntheticDataset((3, 32, 32), 10, length=32 * 24, seed=7, pool=8192)
+timed = SyntheticDataset((3, 32, 32), 10, length=32 * K, seed=32, pool=min(32 * K, 8192))
+tr = Trainer(build_model("mlmodel"), datasets=(warm, warm), epochs=1, batch_size=32, optimizer="sgd", lr=1e-3, momentum=0.9,
+             metric=None, progress=False, model_dir="/tmp/ep", seed=32)
 tr.train_epoch(1)
 tr.train_loader = Loader(timed, batch_size=32, shuffle=True, pin_memory=True, num_workers=0)
-orig_ei = rt.epoch_indices
-def ei(l):
-    t=time.perf_counter(); r=orig_ei(l); print("epoch_indices ms", (time.perf_counter()-t)*1e3); return r
-rt.epoch_indices = ei
-orig_run = rt.NativeLoop.run_lenet
-def run(self,*a,**k):
-    t=time.perf_counter(); r=orig_run(self,*a,**k); print("run_lenet ms", (time.perf_counter()-t)*1e3, "steps", len(r)); return r
-rt.NativeLoop.run_lenet = run
-for ep in (2,3):
-    torch.cuda.synchronize(); t=time.perf_counter(); tr.train_epoch(ep); torch.cuda.synchronize(); print("train_epoch ms", (time.perf_counter()-t)*1e3)
+stages = {}
+
+
+def timed_fn(name, fn):
+    def w(*a, **k):
+        t = time.perf_counter()
+        r = fn(*a, **k)
+        stages.setdefault(name, []).append((time.perf_counter() - t) * 1e6)
+        return r
+    return w
+
+
+rt.epoch_indices = timed_fn("epoch_indices", rt.epoch_indices)
+rt.NativeLoop.run_lenet = timed_fn("run_lenet", rt.NativeLoop.run_lenet)
+tr.optimizer.hyper_rows = timed_fn("hyper_rows", tr.optimizer.hyper_rows)
+tr._reduce_epoch = timed_fn("reduce_epoch", tr._reduce_epoch)
+tr._run_native_epoch = timed_fn("run_native_epoch", tr._run_native_epoch)
+rows = []
+for ep in range(2, 2 + R):
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t = time.perf_counter()
+    s.record()
+    tr.train_epoch(ep)
+    e.record()
+    torch.cuda.synchronize()
+    rows.append({"wall_us": (time.perf_counter() - t) * 1e6, "event_us": s.elapsed_time(e) * 1e3,
+                 "native": tr.last_native_stats.get("host_us")})
+out = {"K": K, "epochs": rows, "stages_us": {k: [round(x, 1) for x in v] for k, v in stages.items()}}
+print(json.dumps(out, indent=1))

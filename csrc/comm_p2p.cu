@@ -76,14 +76,14 @@ allreduce_oneshot_update_kernel(const P2PArgs a) {
   // 1. push my chunk into slot [parity][me] of every peer
   for (int p = 0; p < a.world; ++p) {
     if (p == me) continue;
-    char* dst = a.base[p] + a.recv_off + ((long long)parity * a.world + me) * a.recv_slot_bytes;
+    char* dst = a.base[p] + a.recv_off + ((long long)parity * a.world + me) * a.recv_slot_bytes + a.recv_bucket_off;
     for (long long v = v_lo + threadIdx.x; v < v_hi; v += blockDim.x)
       st_peer(dst + v * 16, *reinterpret_cast<const uint4*>(my_grad + v * 16));
   }
-  // 2. publish + wait for the same chunk from every peer
-  cta_exchange(a, me, 0, cta);
+  // 2. publish + wait for the same chunk from every peer (a lost peer: leave weights and state untouched)
+  if (!cta_exchange(a, me, 0, cta)) return;
   // 3. reduce in rank order from local memory, update, write weights
-  const char* recv = a.base[me] + a.recv_off + (long long)parity * a.world * a.recv_slot_bytes;
+  const char* recv = a.base[me] + a.recv_off + (long long)parity * a.world * a.recv_slot_bytes + a.recv_bucket_off;
   char* model = a.base[me] + a.model_off;
   for (long long v = v_lo + threadIdx.x; v < v_hi; v += blockDim.x) {
     float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -132,7 +132,7 @@ allreduce_twoshot_update_kernel(const P2PArgs a) {
   const long long per_cta = ceil_div64(r_hi - r_lo, gridDim.x);
   const long long v_lo = min(r_hi, r_lo + (long long)cta * per_cta), v_hi = min(r_hi, v_lo + per_cta);
   // 1. everyone's gradients are final (each rank's kernel runs after its backward on the same stream)
-  cta_exchange(a, me, 0, cta);
+  if (!cta_exchange(a, me, 0, cta)) return;
   // 2. reduce my slice, update, scatter the new weights
   for (long long v = v_lo + threadIdx.x; v < v_hi; v += blockDim.x) {
     float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -164,9 +164,13 @@ allreduce_twoshot_update_kernel(const P2PArgs a) {
 // K5: broadcast (init parameter sync, BN buffer sync): root stores into every peer, then a flag exchange.
 // K6: small-vector all-reduce (loss / metric sums) and barrier: push into slot [me] of every peer, exchange, sum.
 // =====================================================================================================
+// The root must not store before every peer's EARLIER work on this stream has finished (a peer's own initialisation
+// copy into the same range, enqueued before its broadcast kernel, would otherwise land after - and over - the root's
+// data): a first exchange says "my stream has reached the broadcast", only then does the root push.
 __global__ void __launch_bounds__(256)
 bcast_store_kernel(const P2PArgs a, long long off, long long nbytes, int root) {
   const int slot = blockIdx.y, me = a.rank + slot, cta = blockIdx.x;
+  if (!cta_exchange(a, me, 0, cta)) return;
   if (me == root) {
     const long long nvec = nbytes / 16;
     const char* src = a.base[me] + off;
@@ -191,7 +195,7 @@ reduce_scalars_kernel(const P2PArgs a, long long scalar_off, float* const* vals,
     float* dst = reinterpret_cast<float*>(a.base[p] + scalar_off) + ((long long)parity * a.world + me) * 32;
     for (int j = threadIdx.x; j < k; j += 32) dst[j] = v[j];
   }
-  cta_exchange(a, me, 0, kMaxCtas - 1);
+  if (!cta_exchange(a, me, 0, kMaxCtas - 1)) return;
   const float* mine = reinterpret_cast<const float*>(a.base[me] + scalar_off) + (long long)parity * a.world * 32;
   for (int j = threadIdx.x; j < k; j += 32) {
     float s = 0.f;
@@ -217,6 +221,8 @@ static int fill_args(P2PArgs& a, const mlt_p2p_ctx* c, int ranks_here) {
   a.flags_off = c->flags_off;
   a.recv_off = c->recv_off;
   a.recv_slot_bytes = c->recv_slot_bytes;
+  a.mc_flags = (c->mc_flags != 0 && c->mc_base != nullptr && ranks_here == 1) ? 1 : 0;
+  a.recv_bucket_off = 0;
   return 0;
 }
 
@@ -237,14 +243,25 @@ extern "C" int mlt_p2p_allreduce_update(const mlt_p2p_ctx* ctx, int algo, int ru
                                         long long model_off, int model_is_master, void* const* master, void* const* s1,
                                         void* const* s2, void* const* hyper, long long n, int nblocks, int ranks_here,
                                         void* stream) {
+  return mlt_p2p_allreduce_update_at(ctx, algo, rule, grad_is_bf16, grad_off, model_off, model_is_master, master, s1, s2, hyper, n,
+                                     nblocks, ranks_here, 0, stream);
+}
+
+extern "C" int mlt_p2p_allreduce_update_at(const mlt_p2p_ctx* ctx, int algo, int rule, int grad_is_bf16, long long grad_off,
+                                           long long model_off, int model_is_master, void* const* master, void* const* s1,
+                                           void* const* s2, void* const* hyper, long long n, int nblocks, int ranks_here,
+                                           long long recv_bucket_off, void* stream) {
   P2PArgs a;
   if (fill_args(a, ctx, ranks_here)) return 1;
+  MLT_REQUIRE(recv_bucket_off >= 0 && recv_bucket_off % 16 == 0, "p2p: receive-slot offset must be a non-negative multiple of 16");
+  a.recv_bucket_off = recv_bucket_off;
   MLT_REQUIRE(n > 0 && n % 8 == 0, "p2p: bucket length %lld must be a positive multiple of 8", n);
   MLT_REQUIRE(grad_off % 16 == 0 && model_off % 16 == 0, "p2p: arena offsets must be 16-byte aligned");
   MLT_REQUIRE(algo != 2 || ctx->mc_base != nullptr, "p2p: NVLS variant requested but no multicast mapping exists");
   const long long bytes = n * (grad_is_bf16 ? 2 : 4);
-  MLT_REQUIRE(algo != 0 || bytes <= ctx->recv_slot_bytes, "p2p: one-shot bucket of %lld bytes exceeds the %lld-byte receive slot",
-              bytes, ctx->recv_slot_bytes);
+  MLT_REQUIRE(algo != 0 || recv_bucket_off + bytes <= ctx->recv_slot_bytes,
+              "p2p: one-shot bucket of %lld bytes at slot offset %lld exceeds the %lld-byte receive slot", bytes, recv_bucket_off,
+              ctx->recv_slot_bytes);
   a.grad_off = grad_off; a.model_off = model_off; a.n = n; a.model_is_master = model_is_master;
   for (int i = 0; i < ranks_here; ++i) {
     a.master[i] = (float*)master[i]; a.s1[i] = (float*)s1[i]; a.s2[i] = s2 ? (float*)s2[i] : nullptr;
@@ -319,11 +336,27 @@ extern "C" int mlt_p2p_check_error(const mlt_p2p_ctx* ctx, unsigned int* out6_ho
   char* fb = (char*)ctx->base[ctx->rank] + ctx->flags_off + offsetof(FlagBlock, err);
   MLT_CHECK_CUDA(cudaMemcpy(e, fb, sizeof(e), cudaMemcpyDeviceToHost));
   for (int i = 0; i < 6; ++i) out6_host[i] = e[i];
-  if (e[0] != 0) {
+  if (e[0] == 1) {
     MLT_CHECK_CUDA(cudaMemset(fb, 0, sizeof(e)));
-    set_error("p2p: rank %u timed out waiting for peer %u (cta %u, kind %u): expected ticket %u, saw %u", e[1], e[2], e[3],
-              e[6], e[4], e[5]);
+    set_error("p2p: rank %u timed out waiting for peer %u (cta %u, kind %u): expected ticket %u, saw %u; the update was skipped",
+              e[1], e[2], e[3], e[6], e[4], e[5]);
     return 2;
   }
+  if (e[0] != 0) {
+    MLT_CHECK_CUDA(cudaMemset(fb, 0, sizeof(e)));
+    set_error("p2p: rank %d was stopped by a peer that timed out waiting in a collective; the update was skipped", ctx->rank);
+    return 3;
+  }
+  return 0;
+}
+
+// Wait limit of every flag wait on this rank, in seconds (<= 0 restores the default of ~20 s).
+extern "C" int mlt_p2p_set_timeout(const mlt_p2p_ctx* ctx, double seconds) {
+  int dev = 0, khz = 0;
+  MLT_CHECK_CUDA(cudaGetDevice(&dev));
+  MLT_CHECK_CUDA(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
+  const unsigned long long cycles = seconds > 0 ? (unsigned long long)(seconds * 1e3 * (double)khz) : 0ull;
+  char* fb = (char*)ctx->base[ctx->rank] + ctx->flags_off + offsetof(FlagBlock, spin_limit);
+  MLT_CHECK_CUDA(cudaMemcpy(fb, &cycles, sizeof(cycles), cudaMemcpyHostToDevice));
   return 0;
 }

@@ -200,16 +200,28 @@ __device__ __forceinline__ void lenet_phase_b(const LeNetArgs& a, float inv_B, i
     // one-shot push of this CTA's gradient elements into every peer's receive slot, then a per-CTA flag exchange
     const int me = cm.rank;
     parity = (flags_of(cm, me)->tick[0][blockIdx.x] + 1) & 1u;
-    for (int p = 0; p < cm.world; ++p) {
-      if (p == me) continue;
-      float* dst = reinterpret_cast<float*>(cm.base[p] + cm.recv_off + ((long long)parity * cm.world + me) * cm.recv_slot_bytes);
+    const long long slot_off = cm.recv_off + ((long long)parity * cm.world + me) * cm.recv_slot_bytes;
+    if (cm.mc_flags) {
+      // ONE store per element through the multicast mapping: the switch writes it into slot [parity][me] of every rank
+      // (mine too), instead of world-1 unicast stores per element
+      float* dst = reinterpret_cast<float*>(cm.mc_base + slot_off);
 #pragma unroll
       for (int r = 0; r < kMaxPerThread; ++r) {
         const long long e = e0 + (long long)r * kThreads + tid;
-        if (r < per_thread && e < a.numel) dst[e] = g[r];
+        if (r < per_thread && e < a.numel) mc_st_f32(dst + e, g[r]);
+      }
+    } else {
+      for (int p = 0; p < cm.world; ++p) {
+        if (p == me) continue;
+        float* dst = reinterpret_cast<float*>(cm.base[p] + slot_off);
+#pragma unroll
+        for (int r = 0; r < kMaxPerThread; ++r) {
+          const long long e = e0 + (long long)r * kThreads + tid;
+          if (r < per_thread && e < a.numel) dst[e] = g[r];
+        }
       }
     }
-    cta_exchange(cm, me, 0, blockIdx.x);
+    if (!cta_exchange(cm, me, 0, blockIdx.x)) return;        // a lost peer: weights and optimizer state stay untouched
   }
 #pragma unroll
   for (int r = 0; r < kMaxPerThread; ++r) {
@@ -1217,13 +1229,14 @@ extern "C" int mlt_lenet_step(void* master, void* s1, void* s2, const void* hype
   a.nsteps = 0; a.nslots = 0; a.pool_n = 0; a.batch_sizes = nullptr; a.hyper_table = nullptr; a.loss_base = nullptr;
   a.ready = nullptr; a.progress = nullptr;
   for (int i = 0; i < kMaxSlots; ++i) { a.xs[i] = nullptr; a.ys[i] = nullptr; }
-  a.comm.world = 1; a.comm.rank = 0;
+  a.comm.world = 1; a.comm.rank = 0; a.comm.mc_flags = 0; a.comm.recv_bucket_off = 0; a.comm.mc_base = nullptr;
   if (ctx != nullptr && ctx->world > 1) {
     MLT_REQUIRE(numel * 4 <= ctx->recv_slot_bytes, "mlt_lenet_step: parameter arena exceeds the one-shot receive slot");
     for (int i = 0; i < kMaxRanks; ++i) a.comm.base[i] = (char*)ctx->base[i];
     a.comm.mc_base = (char*)ctx->mc_base;
     a.comm.world = ctx->world; a.comm.rank = ctx->rank;
     a.comm.flags_off = ctx->flags_off; a.comm.recv_off = ctx->recv_off; a.comm.recv_slot_bytes = ctx->recv_slot_bytes;
+    a.comm.mc_flags = (ctx->mc_flags != 0 && ctx->mc_base != nullptr) ? 1 : 0;
   }
   return lenet_launch(a, rule, numel, stream);
 }
@@ -1254,13 +1267,14 @@ extern "C" int mlt_lenet_steps(void* master, void* s1, void* s2, const void* hyp
   for (int i = 0; i < kMaxSlots; ++i) { a.xs[i] = i < nslots ? (const float*)xs[i] : nullptr; a.ys[i] = i < nslots ? (const long long*)ys[i] : nullptr; }
   a.batch_sizes = batch_sizes; a.hyper_table = (const Hyper*)hyper_table; a.loss_base = (float*)loss_base;
   a.ready = (const unsigned int*)ready; a.progress = (unsigned int*)progress;
-  a.comm.world = 1; a.comm.rank = 0;
+  a.comm.world = 1; a.comm.rank = 0; a.comm.mc_flags = 0; a.comm.recv_bucket_off = 0; a.comm.mc_base = nullptr;
   if (ctx != nullptr && ctx->world > 1) {
     MLT_REQUIRE(numel * 4 <= ctx->recv_slot_bytes, "mlt_lenet_steps: parameter arena exceeds the one-shot receive slot");
     for (int i = 0; i < kMaxRanks; ++i) a.comm.base[i] = (char*)ctx->base[i];
     a.comm.mc_base = (char*)ctx->mc_base;
     a.comm.world = ctx->world; a.comm.rank = ctx->rank;
     a.comm.flags_off = ctx->flags_off; a.comm.recv_off = ctx->recv_off; a.comm.recv_slot_bytes = ctx->recv_slot_bytes;
+    a.comm.mc_flags = (ctx->mc_flags != 0 && ctx->mc_base != nullptr) ? 1 : 0;
   }
   return lenet_launch(a, rule, numel, stream);
 }

@@ -10,11 +10,17 @@
 //                   event `released` (the slot's buffers may be overwritten).
 // Slots form a ring (default 3), so the gather and upload of step i+1.. overlap the compute of step i.
 // Nothing here synchronises with the device except when a ring slot is still in flight and at the end of the run.
+//
+// Fixed cost per run is kept to a few tens of microseconds: the gather thread lives as long as the loop (parked on a
+// condition variable between runs; the caller gathers step 0 itself while it wakes), the per-run tables are allocated once,
+// and a slot's inputs and targets share ONE pinned buffer and ONE device buffer, so a full batch goes device-ward as one copy.
 #include <cuda_runtime.h>
 
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -38,10 +44,10 @@ using mlt::set_error;
 namespace {
 
 struct Slot {
-  void* pin_x = nullptr;
-  void* pin_y = nullptr;
-  void* dev_x = nullptr;
-  void* dev_y = nullptr;
+  void* pin_x = nullptr;            // pinned staging: [max_batch x rows | pad to 256 B | max_batch y rows]
+  void* pin_y = nullptr;            // = pin_x + y_off
+  void* dev_x = nullptr;            // device buffer, same layout
+  void* dev_y = nullptr;            // = dev_x + y_off
   cudaEvent_t ready = nullptr;      // H2D of this slot finished (copy stream)
   cudaEvent_t copied = nullptr;     // same event viewed from the host: pinned staging reusable
   cudaEvent_t released = nullptr;   // compute finished with the device buffers
@@ -73,6 +79,25 @@ struct Loop {
   // Large samples (images): skip the host gather of x and let the copy engine gather instead - one cudaMemcpyAsync per
   // sample straight from the (page-locked) dataset into the slot's device buffer.
   bool direct_x = false;
+  size_t y_off = 0;                     // byte offset of the targets inside a slot's buffers
+  // ---- gather thread (one per loop, parked between runs) ------------------------------------------------------
+  struct Job {
+    const char* hx = nullptr; const char* hy = nullptr;
+    const long long* indices = nullptr; const long long* start = nullptr;
+    long long first = 0, steps = 0;
+  } job;
+  std::thread worker;
+  std::mutex mu;
+  std::condition_variable cv;
+  long long job_seq = 0;                // guarded by mu
+  bool stop = false;                    // guarded by mu
+  std::atomic<long long> done_seq{0};   // last job the worker finished
+  std::atomic<bool> abort{false};
+  std::unique_ptr<std::atomic<long long>[]> gathered;   // [slots] step id (+1) whose data sits in the slot's pinned buffers
+  std::unique_ptr<std::atomic<long long>[]> free_for;   // [slots] slot may be refilled for any step <= this value
+  std::vector<long long> start;         // prefix sums of the per-step batch sizes of the current run
+  // host-side timing of the last run, microseconds since entry: [first launch enqueued, all launches enqueued, device drained]
+  double t_us[4] = {0, 0, 0, 0};
 };
 
 // rows `idx[0..n)` of a [N][row] byte matrix -> dst
@@ -87,6 +112,39 @@ void gather_rows(char* dst, const char* src, size_t row, const long long* idx, l
   for (long long i = 0; i < n; ++i) std::memcpy(dst + (size_t)i * row, src + (size_t)idx[i] * row, row);
 }
 
+void gather_step(Loop* L, const Loop::Job& j, long long i) {
+  const int s = (int)(i % L->slots);
+  const long long n = j.start[i + 1] - j.start[i];
+  if (!L->direct_x) gather_rows((char*)L->ring[s].pin_x, j.hx, L->x_row, j.indices + j.start[i], n);
+  gather_rows((char*)L->ring[s].pin_y, j.hy, L->y_row, j.indices + j.start[i], n);
+  L->gathered[s].store(i + 1, std::memory_order_release);
+}
+
+void worker_main(Loop* L) {
+  long long seen = 0;
+  for (;;) {
+    Loop::Job j;
+    {
+      std::unique_lock<std::mutex> lk(L->mu);
+      L->cv.wait(lk, [&] { return L->stop || L->job_seq != seen; });
+      if (L->stop) return;
+      seen = L->job_seq;
+      j = L->job;
+    }
+    for (long long i = j.first; i < j.steps && !L->abort.load(std::memory_order_relaxed); ++i) {
+      const int s = (int)(i % L->slots);
+      while (L->free_for[s].load(std::memory_order_acquire) < i && !L->abort.load(std::memory_order_relaxed)) std::this_thread::yield();
+      if (L->abort.load(std::memory_order_relaxed)) break;
+      gather_step(L, j, i);
+    }
+    L->done_seq.store(seen, std::memory_order_release);
+  }
+}
+
+double now_us() {
+  return std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
 }  // namespace
 
 extern "C" void* mlt_loop_create(int device, int slots, long long max_batch, long long x_row_bytes, long long y_row_bytes) {
@@ -99,19 +157,29 @@ extern "C" void* mlt_loop_create(int device, int slots, long long max_batch, lon
   L->y_row = (size_t)y_row_bytes;
   L->ring.resize(L->slots);
   bool ok = cudaStreamCreateWithFlags(&L->copy, cudaStreamNonBlocking) == cudaSuccess;
+  L->y_off = ((size_t)max_batch * L->x_row + 255) / 256 * 256;
+  const size_t slot_bytes = L->y_off + (size_t)max_batch * L->y_row;
   for (auto& s : L->ring) {
-    ok = ok && cudaHostAlloc(&s.pin_x, (size_t)max_batch * L->x_row, cudaHostAllocDefault) == cudaSuccess;
-    ok = ok && cudaHostAlloc(&s.pin_y, (size_t)max_batch * L->y_row, cudaHostAllocDefault) == cudaSuccess;
-    ok = ok && cudaMalloc(&s.dev_x, (size_t)max_batch * L->x_row) == cudaSuccess;
-    ok = ok && cudaMalloc(&s.dev_y, (size_t)max_batch * L->y_row) == cudaSuccess;
+    ok = ok && cudaHostAlloc(&s.pin_x, slot_bytes, cudaHostAllocDefault) == cudaSuccess;
+    ok = ok && cudaMalloc(&s.dev_x, slot_bytes) == cudaSuccess;
+    if (ok) { s.pin_y = (char*)s.pin_x + L->y_off; s.dev_y = (char*)s.dev_x + L->y_off; }
     ok = ok && cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming) == cudaSuccess;
     ok = ok && cudaEventCreateWithFlags(&s.released, cudaEventDisableTiming) == cudaSuccess;
   }
+  // per-run tables, sized for 8192 steps up front (they grow on demand)
+  const long long cap = 8192;
+  ok = ok && cudaHostAlloc((void**)&L->pin_hyper, (size_t)cap * 8 * sizeof(float), cudaHostAllocDefault) == cudaSuccess;
+  ok = ok && cudaHostAlloc((void**)&L->pin_loss, (size_t)cap * sizeof(float), cudaHostAllocDefault) == cudaSuccess;
+  ok = ok && cudaMalloc((void**)&L->dev_hyper, (size_t)cap * 8 * sizeof(float)) == cudaSuccess;
   if (!ok) {
     set_error("mlt_loop_create: allocation failed (%s)", cudaGetErrorString(cudaGetLastError()));
     delete L;
     return nullptr;
   }
+  L->hyper_cap = L->loss_cap = L->dev_hyper_cap = cap;
+  L->gathered.reset(new std::atomic<long long>[L->slots]);
+  L->free_for.reset(new std::atomic<long long>[L->slots]);
+  L->worker = std::thread(worker_main, L);
   return L;
 }
 
@@ -124,10 +192,15 @@ extern "C" int mlt_loop_set_direct_rows(void* loop, int on) { ((Loop*)loop)->dir
 extern "C" int mlt_loop_destroy(void* loop) {
   Loop* L = (Loop*)loop;
   if (!L) return 0;
+  if (L->worker.joinable()) {
+    { std::lock_guard<std::mutex> lk(L->mu); L->stop = true; }
+    L->cv.notify_all();
+    L->worker.join();
+  }
   cudaSetDevice(L->device);
   cudaDeviceSynchronize();
   for (auto& s : L->ring) {
-    cudaFreeHost(s.pin_x); cudaFreeHost(s.pin_y); cudaFree(s.dev_x); cudaFree(s.dev_y);
+    cudaFreeHost(s.pin_x); cudaFree(s.dev_x);
     cudaEventDestroy(s.ready); cudaEventDestroy(s.released);
   }
   if (L->pin_hyper) cudaFreeHost(L->pin_hyper);
@@ -157,6 +230,7 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
                             const mlt_lenet_call* lenet, void* const* graph_execs, const void* loss_dev, float* loss_host,
                             void* compute_stream) {
   Loop* L = (Loop*)loop;
+  const double t_enter = now_us();
   RT_CHECK(cudaSetDevice(L->device));
   cudaStream_t cs = (cudaStream_t)compute_stream;
   if (steps <= 0) return 0;
@@ -190,27 +264,32 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
     L->h2d_bytes += steps * 32;
   }
 
-  // ---- gather thread: fills pinned slots ahead of the launcher ---------------------------------------
+  // ---- gather: the caller fills the pinned slot of step 0 itself while the parked gather thread wakes up for steps 1.. ----
   const int S = L->slots;
-  std::vector<std::atomic<long long>> gathered(S);      // step id (+1) whose data sits in the slot's pinned buffers
-  std::vector<std::atomic<long long>> free_for(S);      // slot may be refilled for any step <= this value
-  for (int s = 0; s < S; ++s) { gathered[s].store(0); free_for[s].store(s); }
-  std::atomic<bool> abort{false};
+  for (int s = 0; s < S; ++s) { L->gathered[s].store(0); L->free_for[s].store(s); }
+  L->abort.store(false);
   const char* hx = (const char*)host_x;
   const char* hy = (const char*)host_y;
   auto bs_of = [&](long long i) { return batch_sizes ? (long long)batch_sizes[i] : (long long)batch; };
-  std::vector<long long> start(steps + 1, 0);
+  std::vector<long long>& start = L->start;
+  start.assign(steps + 1, 0);
   for (long long i = 0; i < steps; ++i) start[i + 1] = start[i] + bs_of(i);
-  std::thread gatherer([&] {
-    for (long long i = 0; i < steps && !abort.load(); ++i) {
-      const int s = (int)(i % S);
-      while (free_for[s].load(std::memory_order_acquire) < i && !abort.load()) std::this_thread::yield();
-      const long long n = bs_of(i);
-      if (!L->direct_x) gather_rows((char*)L->ring[s].pin_x, hx, L->x_row, indices + start[i], n);
-      gather_rows((char*)L->ring[s].pin_y, hy, L->y_row, indices + start[i], n);
-      gathered[s].store(i + 1, std::memory_order_release);
-    }
-  });
+  long long my_seq;
+  {
+    std::lock_guard<std::mutex> lk(L->mu);
+    L->job.hx = hx; L->job.hy = hy; L->job.indices = indices; L->job.start = start.data();
+    L->job.first = 1; L->job.steps = steps;
+    my_seq = ++L->job_seq;
+  }
+  L->cv.notify_one();
+  gather_step(L, L->job, 0);
+  std::atomic<bool>& abort = L->abort;
+  auto& gathered = L->gathered;
+  auto& free_for = L->free_for;
+  struct Joiner {            // every exit path waits until the gather thread is done with this run's pointers
+    Loop* L; long long seq;
+    void join() { while (L->done_seq.load(std::memory_order_acquire) != seq) std::this_thread::yield(); }
+  } gatherer{L, my_seq};
 
   int rc = 0;
   if (persistent) {
@@ -279,10 +358,14 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
         j += run;
       }
       if (rc != 0) break;
+    } else if (n == L->max_batch) {
+      // full batch: inputs and targets are adjacent in the slot, ONE copy carries both
+      if ((rc = (int)cudaMemcpyAsync(sl.dev_x, sl.pin_x, L->y_off + (size_t)n * L->y_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
     } else {
       if ((rc = (int)cudaMemcpyAsync(sl.dev_x, sl.pin_x, (size_t)n * L->x_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
     }
-    if ((rc = (int)cudaMemcpyAsync(sl.dev_y, sl.pin_y, (size_t)n * L->y_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
+    if (L->direct_x || n != L->max_batch)
+      if ((rc = (int)cudaMemcpyAsync(sl.dev_y, sl.pin_y, (size_t)n * L->y_row, cudaMemcpyHostToDevice, L->copy)) != 0) break;
     if ((rc = (int)cudaEventRecord(sl.ready, L->copy)) != 0) break;
     L->h2d_bytes += n * (long long)(L->x_row + L->y_row);
     if (persistent) {
@@ -308,6 +391,7 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
       if ((rc = (int)cudaGraphLaunch((cudaGraphExec_t)graph_execs[s], cs)) != 0) break;
     }
     L->launches += 1;
+    if (i == 0) L->t_us[0] = now_us() - t_enter;
     if (loss_dev && !table_mode) {
       if ((rc = (int)cudaMemcpyAsync(L->pin_loss + i, loss_dev, sizeof(float), cudaMemcpyDeviceToHost, cs)) != 0) break;
       L->d2h_bytes += 4;
@@ -321,12 +405,21 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
   }
   gatherer.join();
   if (rc != 0) return rc;
+  L->t_us[1] = now_us() - t_enter;
   RT_CHECK(cudaStreamSynchronize(cs));
+  L->t_us[2] = now_us() - t_enter;
   if (persistent && *(volatile unsigned int*)L->pin_progress != (unsigned int)steps) {
     set_error("mlt_loop_run: the persistent step kernel stopped after %u of %lld steps", *(volatile unsigned int*)L->pin_progress, steps);
     return 1;
   }
   if (loss_dev && loss_host) std::memcpy(loss_host, L->pin_loss, (size_t)steps * sizeof(float));
+  return 0;
+}
+
+// Host-side timing of the last run in microseconds since entry: out3 = {first step enqueued, all steps enqueued, device drained}.
+extern "C" int mlt_loop_timing(void* loop, double* out3) {
+  Loop* L = (Loop*)loop;
+  for (int i = 0; i < 3; ++i) out3[i] = L->t_us[i];
   return 0;
 }
 

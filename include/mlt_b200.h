@@ -125,6 +125,8 @@ typedef struct {
   long long flags_off;        /* byte offset of the flag block (mlt_p2p_flag_block_bytes()) */
   long long recv_off;         /* byte offset of the one-shot receive slots: [2][world][recv_slot_bytes] */
   long long recv_slot_bytes;
+  int mc_flags;               /* != 0 (needs mc_base): flags and the in-step gradient push go out as ONE multimem.st each */
+  int reserved;
 } mlt_p2p_ctx;
 
 long long mlt_p2p_flag_block_bytes(void);
@@ -135,9 +137,19 @@ long long mlt_p2p_flag_block_bytes(void);
 int mlt_p2p_allreduce_update(const mlt_p2p_ctx* ctx, int algo, int rule, int grad_is_bf16, long long grad_off,
                              long long model_off, int model_is_master, void* const* master, void* const* s1,
                              void* const* s2, void* const* hyper, long long n, int nblocks, int ranks_here, void* stream);
+/* The same, with the bucket's own byte offset inside the one-shot receive slots (buckets of one step must not share slot
+ * bytes: their CTAs' double-buffer parities are independent).  recv_bucket_off + bucket bytes <= recv_slot_bytes. */
+int mlt_p2p_allreduce_update_at(const mlt_p2p_ctx* ctx, int algo, int rule, int grad_is_bf16, long long grad_off,
+                                long long model_off, int model_is_master, void* const* master, void* const* s1,
+                                void* const* s2, void* const* hyper, long long n, int nblocks, int ranks_here,
+                                long long recv_bucket_off, void* stream);
 int mlt_p2p_broadcast(const mlt_p2p_ctx* ctx, long long off, long long nbytes, int root, int ranks_here, void* stream);
 int mlt_p2p_reduce_scalars(const mlt_p2p_ctx* ctx, long long scalar_off, void* vals_dev, int k, int ranks_here, void* stream);
 int mlt_p2p_check_error(const mlt_p2p_ctx* ctx, unsigned int* out6_host);
+/* wait limit of every flag wait of this rank's collectives in seconds (<= 0: the default, ~20 s).  When a wait runs past it the
+ * kernel records a diagnostic, poisons this rank and its peers (later collectives return without touching weights) and
+ * mlt_p2p_check_error reports it. */
+int mlt_p2p_set_timeout(const mlt_p2p_ctx* ctx, double seconds);
 
 /* ---- the reference model's whole train step as one kernel: src/model.py:7-24 + src/trainer.py:181-188 ------------- */
 long long mlt_lenet_scratch_bytes(int B);
@@ -173,6 +185,8 @@ int mlt_loop_run(void* loop, const void* host_x, const void* host_y, const long 
                  const int* batch_sizes, const float* hyper_rows, void* hyper_dev, int step_kind, const mlt_lenet_call* lenet,
                  void* const* graph_execs, const void* loss_dev, float* loss_host, void* compute_stream);
 int mlt_loop_stats(void* loop, long long* h2d_bytes, long long* d2h_bytes, long long* launches);
+/* host-side timing of the last run, microseconds since entry: {first step enqueued, all steps enqueued, device drained} */
+int mlt_loop_timing(void* loop, double* out3);
 
 /* ---- transformer pieces: ATen layer_norm / softmax / embedding kernels of the BERT workload --------------------- */
 /* y = LN(x [+ res]) * gamma + beta (bf16 activations; gamma/beta fp32 or bf16); hsum (optional) receives x + res. */

@@ -227,7 +227,7 @@ def batch_norm_nhwc(x, bn: torch.nn.BatchNorm2d, relu: bool = False, residual: O
         if bn.num_batches_tracked is not None:
             bn.num_batches_tracked.add_(1)
         mom = bn.momentum if bn.momentum is not None else 0.1
-        if _has_sink(bn.weight):
+        if _has_sink(bn.weight, bn.bias):
             return _BatchNormFn.apply(x, residual, bn.weight.detach(), bn.bias.detach(), bn.running_mean, bn.running_var,
                                       mom, bn.eps, relu, bn.weight, bn.bias)
         return _BatchNormFn.apply(x, residual, bn.weight, bn.bias, bn.running_mean, bn.running_var, mom, bn.eps, relu, None, None)

@@ -150,8 +150,35 @@ def argmax_accuracy(logits: torch.Tensor, targets: torch.Tensor) -> torch.Tensor
 # ----------------------------------------------------------------------------------------------
 # gradient sinks
 # ----------------------------------------------------------------------------------------------
+# A parameter may be used more than once in one forward pass (a module applied twice, tied weights).  Gradient sinks are
+# WRITTEN, not accumulated, so uses are counted per step: ``_has_sink`` (forward) counts them, and in backward the first
+# arrival writes the sink, later arrivals write a temporary that is added into it, and the reducer hears "ready" only
+# when the last use has delivered (its bucket must not be reduced - nor the weight updated - before that).
+_STEP = [0]
+
+
+def new_step() -> None:
+    """Start a new step: use counters of every parameter restart lazily (called by ``FusedOptimizer.begin_step``)."""
+    _STEP[0] += 1
+
+
+def _note_use(p) -> None:
+    if p is None:
+        return
+    if getattr(p, "_mlt_stamp", -1) != _STEP[0]:
+        p._mlt_stamp, p._mlt_uses, p._mlt_done = _STEP[0], 0, 0
+    p._mlt_uses += 1
+
+
 def _sink(param) -> Optional[torch.Tensor]:
-    return getattr(param, "_mlt_grad_sink", None) if param is not None else None
+    """Where this backward call should write the parameter's gradient: the arena sink for the first arrival of the step,
+    ``None`` (= allocate a temporary; ``_deliver`` adds it into the sink) for later arrivals of a reused parameter."""
+    if param is None:
+        return None
+    s = getattr(param, "_mlt_grad_sink", None)
+    if s is not None and getattr(param, "_mlt_uses", 1) > 1 and getattr(param, "_mlt_done", 0) > 0:
+        return None
+    return s
 
 
 def _deliver(param, grad_written: Optional[torch.Tensor], sink: Optional[torch.Tensor]):
@@ -159,12 +186,20 @@ def _deliver(param, grad_written: Optional[torch.Tensor], sink: Optional[torch.T
 
     With a sink the kernel already wrote into the arena: tell the reducer and hand autograd ``None``.
     """
-    if sink is not None:
-        ready = getattr(param, "_mlt_ready", None)
-        if ready is not None:
-            ready()
-        return None
-    return grad_written
+    real = getattr(param, "_mlt_grad_sink", None) if param is not None else None
+    if real is None:
+        return grad_written
+    uses = getattr(param, "_mlt_uses", 1)
+    if uses > 1:
+        if sink is None and grad_written is not None:
+            real.add_(grad_written.reshape(real.shape).to(real.dtype))
+        param._mlt_done = getattr(param, "_mlt_done", 0) + 1
+        if param._mlt_done < uses:
+            return None
+    ready = getattr(param, "_mlt_ready", None)
+    if ready is not None:
+        ready()
+    return None
 
 
 # ----------------------------------------------------------------------------------------------
@@ -225,7 +260,7 @@ def conv_relu_pool(x, weight, bias=None, relu=True, pool=True):
     taps = weight.shape[1] * weight.shape[2] * weight.shape[3]
     if use_native(x, weight) and x.dtype == torch.float32 and taps <= DIRECT_CONV_MAX_TAPS:
         return _ConvReluPoolFn.apply(x, weight.detach(), None if bias is None else bias.detach(), relu, pool, weight, bias) \
-            if _has_sink(weight) else _ConvReluPoolFn.apply(x, weight, bias, relu, pool, None, None)
+            if _has_sink(weight, bias) else _ConvReluPoolFn.apply(x, weight, bias, relu, pool, None, None)
     y = TF.conv2d(x, weight, bias)
     if relu:
         y = TF.relu(y)
@@ -234,8 +269,15 @@ def conv_relu_pool(x, weight, bias=None, relu=True, pool=True):
     return y
 
 
-def _has_sink(p) -> bool:
-    return getattr(p, "_mlt_grad_sink", None) is not None and torch.is_grad_enabled() and p.requires_grad
+def _has_sink(p, *also) -> bool:
+    """True when ``p``'s gradient goes straight into the optimizer arena.  Called once per USE in the forward pass (it counts
+    the use of ``p`` and of the parameters in ``also`` that ride along, e.g. the bias)."""
+    ok = getattr(p, "_mlt_grad_sink", None) is not None and torch.is_grad_enabled() and p.requires_grad
+    if ok:
+        _note_use(p)
+        for q in also:
+            _note_use(q)
+    return ok
 
 
 class _LinearSmallFn(torch.autograd.Function):
@@ -298,7 +340,7 @@ def linear_act(x, weight, bias=None, act: Optional[str] = None):
             (bias is None or bias.dtype == x.dtype) and act in (None, "none", "relu", "tanh")
         if small_ok and (B * K * N <= SMALL_LINEAR_MAX or (x.dtype == torch.bfloat16 and (N % 8 != 0 or K % 8 != 0))):
             a = ACT_IDS[act]
-            if _has_sink(weight):
+            if _has_sink(weight, bias):
                 y = _LinearSmallFn.apply(x2, weight.detach(), None if bias is None else bias.detach(), a, weight, bias)
             else:
                 y = _LinearSmallFn.apply(x2, weight, bias, a, None, None)
@@ -476,7 +518,7 @@ class _LayerNormFn(torch.autograd.Function):
 def layer_norm(x, gamma, beta, eps: float = 1e-12, residual=None):
     H = x.shape[-1]
     if use_native(x, gamma) and x.dtype == torch.bfloat16 and H % 8 == 0 and H <= 1024 and gamma.dtype in (torch.bfloat16, torch.float32):
-        if _has_sink(gamma):
+        if _has_sink(gamma, beta):
             return _LayerNormFn.apply(x, residual, gamma.detach(), beta.detach(), eps, gamma, beta)
         return _LayerNormFn.apply(x, residual, gamma, beta, eps, None, None)
     h = x if residual is None else x + residual
@@ -691,7 +733,7 @@ class _EmbeddingFn(torch.autograd.Function):
 
 def bert_embeddings(ids, word, pos, typ):
     if use_native(ids, word) and word.dtype in (torch.bfloat16, torch.float32) and word.shape[1] % 2 == 0:
-        if _has_sink(word):
+        if _has_sink(word, pos, typ):
             return _EmbeddingFn.apply(ids, word.detach(), pos.detach(), typ.detach(), word, pos, typ)
         return _EmbeddingFn.apply(ids, word, pos, typ, None, None, None)
     S = ids.shape[1]

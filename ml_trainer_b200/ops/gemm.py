@@ -184,7 +184,7 @@ def ffn_tc(x, w1, b1, w2, b2, act: str = "gelu"):
     if not torch.is_grad_enabled():
         return gemm(gemm(x2, w1, False, False, bias=b1, act=act), w2, False, False, bias=b2).reshape(*lead, w2.shape[0])
     det = lambda t: None if t is None else t.detach()
-    if _has_sink(w1) and _has_sink(w2):
+    if _has_sink(w1, b1) and _has_sink(w2, b2):
         y = _FFNFn.apply(x2, det(w1), det(b1), det(w2), det(b2), act, (w1, b1, w2, b2))
     else:
         y = _FFNFn.apply(x2, w1, b1, w2, b2, act, (None, None, None, None))
@@ -212,11 +212,17 @@ class _LinearTCPackedFn(torch.autograd.Function):
         wpack, bpack = ctx.packs
         dy = dy.contiguous()
         dx = gemm(dy, w, False, True) if ctx.needs_input_grad[0] else None
-        gemm(dy, x2, True, True, out=wpack.grad)
-        wpack.ready()
+        if wpack.first_arrival():
+            gemm(dy, x2, True, True, out=wpack.grad)
+        else:                                    # the packed layers are applied more than once per forward pass
+            wpack.grad.add_(gemm(dy, x2, True, True, out_dtype=wpack.grad.dtype))
+        wpack.deliver()
         if bpack is not None:
-            colsum(dy, out=bpack.grad)
-            bpack.ready()
+            if bpack.first_arrival():
+                colsum(dy, out=bpack.grad)
+            else:
+                bpack.grad.add_(colsum(dy).to(bpack.grad.dtype))
+            bpack.deliver()
         return dx, None, None
 
 
@@ -224,6 +230,10 @@ def linear_packed(x, wpack, bpack=None):
     """``x @ [W0; W1; ...]^T + [b0; b1; ...]`` for parameters packed by the FusedOptimizer; returns ``[..., sum(out_i)]``."""
     lead = x.shape[:-1]
     x2 = x.reshape(-1, x.shape[-1])
+    if torch.is_grad_enabled():
+        wpack.note_use()
+        if bpack is not None:
+            bpack.note_use()
     y = _LinearTCPackedFn.apply(x2, wpack, bpack)
     return y.reshape(*lead, wpack.data.shape[0])
 
@@ -245,7 +255,7 @@ def linear_act_tc(x, weight, bias=None, act: Optional[str] = None):
         from .functional import _torch_act
 
         return _torch_act(y, act)
-    if _has_sink(weight):
+    if _has_sink(weight, bias):
         y = _LinearTCFn.apply(x2, weight.detach(), None if bias is None else bias.detach(), act, weight, bias)
     else:
         y = _LinearTCFn.apply(x2, weight, bias, act, None, None)

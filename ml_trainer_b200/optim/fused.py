@@ -53,6 +53,25 @@ class PackedParams:
             if r is not None:
                 r()
 
+    # uses per step are counted on the first member (see ops.functional: sinks are written, not accumulated)
+    def note_use(self):
+        from ..ops.functional import _note_use
+
+        _note_use(self.members[0])
+
+    def first_arrival(self) -> bool:
+        p = self.members[0]
+        return not (getattr(p, "_mlt_uses", 1) > 1 and getattr(p, "_mlt_done", 0) > 0)
+
+    def deliver(self):
+        p = self.members[0]
+        uses = getattr(p, "_mlt_uses", 1)
+        if uses > 1:
+            p._mlt_done = getattr(p, "_mlt_done", 0) + 1
+            if p._mlt_done < uses:
+                return
+        self.ready()
+
 
 class FusedOptimizer(torch.optim.Optimizer):
     def __init__(
@@ -130,8 +149,10 @@ class FusedOptimizer(torch.optim.Optimizer):
         self.grad = self._alloc(off, self.compute_dtype, dev)
         self.model = self.master if self.compute_dtype == torch.float32 else self._alloc(off, self.compute_dtype, dev)
         nstate = RULE_STATES[self.kind]
-        self.s1 = torch.zeros(off, dtype=torch.float32, device=dev)
-        self.s2 = torch.zeros(off if nstate > 1 else 1, dtype=torch.float32, device=dev)
+        # optimizer state comes from the same allocator as the weights: with the NVLink backend that is peer-addressable
+        # arena memory, which lets a checkpoint pull the slices other ranks own (sharded update kernels)
+        self.s1 = self._alloc(off, torch.float32, dev)
+        self.s2 = self._alloc(off, torch.float32, dev) if nstate > 1 else torch.zeros(1, dtype=torch.float32, device=dev)
         self.hyper = torch.zeros(HYPER_LEN, dtype=torch.float32, device=dev)
         self.index_of = {}
         # conv weights marked channels-last live physically as [Cout, KH, KW, Cin] (the GEMM operand layout of the
@@ -204,13 +225,14 @@ class FusedOptimizer(torch.optim.Optimizer):
     # ------------------------------------------------------------------- step
     def begin_step(self, grad_scale: float = 1.0, upload: bool = True) -> Hyper:
         """Advance the step counter and publish this step's hyper-parameters."""
+        from ..ops import functional as F
+
+        F.new_step()                 # per-step use counters of parameters that appear more than once in the forward pass
         h = self.hyper_for_next_step(grad_scale)
         self.step_count += 1
         self._opt_called = True      # what torch's lr_scheduler looks at to order step() calls
         self._hyper_host = h
         if upload and self.device.type == "cuda":
-            from ..ops import functional as F
-
             F.upload_hyper(self.hyper, h.pack())
         return h
 

@@ -39,8 +39,20 @@ class Comm:
     name: str = "local"
     fused: bool = False          # True when allreduce_update also applies the optimizer rule
 
-    def prepare(self, param_elems: int, compute_dtype: torch.dtype) -> None:
-        """Size any backend-owned memory for a model of ``param_elems`` (padded) parameters.  Collective."""
+    def prepare(self, param_elems: int, compute_dtype: torch.dtype, n_states: int = 2) -> None:
+        """Size any backend-owned memory for a model of ``param_elems`` (padded) parameters and ``n_states`` fp32
+        optimizer-state vectors.  Collective."""
+
+    def check_errors(self) -> None:
+        """Raise if a collective recorded a failure (a peer that stopped answering).  Host-side, cheap."""
+
+    def owned_slices(self, optimizer, lo: int, hi: int):
+        """Element ranges ``[(rank, lo, hi), ...]`` of bucket ``[lo, hi)`` whose fp32 master / optimizer state is only
+        up to date on ``rank`` (sharded-update collectives); empty when every rank updates the whole bucket."""
+        return []
+
+    def consolidate(self, optimizer, buckets) -> None:
+        """Make every rank's fp32 master weights and optimizer state complete (before a checkpoint)."""
 
     # -- collectives ---------------------------------------------------------
     def all_reduce_mean(self, flat: torch.Tensor, stream=None) -> None:

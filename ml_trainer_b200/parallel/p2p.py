@@ -33,7 +33,8 @@ _c_int, _c_ll, _c_vp = ctypes.c_int, ctypes.c_longlong, ctypes.c_void_p
 
 class P2PCtx(ctypes.Structure):
     _fields_ = [("base", _c_vp * 8), ("mc_base", _c_vp), ("world", _c_int), ("rank", _c_int),
-                ("flags_off", _c_ll), ("recv_off", _c_ll), ("recv_slot_bytes", _c_ll)]
+                ("flags_off", _c_ll), ("recv_off", _c_ll), ("recv_slot_bytes", _c_ll), ("mc_flags", _c_int),
+                ("reserved", _c_int)]
 
 
 class _DevMem:
@@ -129,15 +130,19 @@ class P2PComm(Comm):
         self.L.mlt_p2p_flag_block_bytes.restype = _c_ll
 
     # ------------------------------------------------------------------ arena
-    def prepare(self, param_elems: int, compute_dtype: torch.dtype):
-        """Create the arena sized for ``param_elems`` parameters (collective; same arguments on every rank)."""
+    def prepare(self, param_elems: int, compute_dtype: torch.dtype, n_states: int = 2):
+        """Create the arena sized for ``param_elems`` parameters (collective; same arguments on every rank).
+
+        The heap holds the fp32 master, the compute-dtype weights and gradients AND the fp32 optimizer state: the sharded
+        collectives update master / state only on the owning rank, and a checkpoint pulls the owners' slices over NVLink
+        (``consolidate``), which needs them in peer-addressable memory."""
         if self.arena is not None:
             return
         esize = 2 if compute_dtype == torch.bfloat16 else 4
         flags = _align(int(self.L.mlt_p2p_flag_block_bytes()), 4096)
         scalars = _align(2 * 8 * 32 * 4, 4096)
         recv = 2 * self.world_size * self.oneshot_max
-        heap = param_elems * (4 + esize + (esize if compute_dtype == torch.bfloat16 else 0)) + (1 << 20)
+        heap = param_elems * (4 + esize + (esize if compute_dtype == torch.bfloat16 else 0) + 4 * max(int(n_states), 0)) + (1 << 20)
         self.flags_off, self.scalar_off = 0, flags
         self.recv_off = flags + scalars
         self.heap_off = self._heap = _align(self.recv_off + recv, 4096)
@@ -153,6 +158,11 @@ class P2PComm(Comm):
         self.ctx.mc_base = self.arena.mc_base or None
         self.ctx.world, self.ctx.rank = self.world_size, self.rank
         self.ctx.flags_off, self.ctx.recv_off, self.ctx.recv_slot_bytes = self.flags_off, self.recv_off, self.oneshot_max
+        self.ctx.mc_flags = int(self.arena.multicast and os.environ.get("MLT_MC_FLAGS", "1") != "0")
+        timeout_s = float(os.environ.get("MLT_P2P_TIMEOUT_S", "20"))
+        check(self.L.mlt_p2p_set_timeout(ctypes.byref(self.ctx), ctypes.c_double(timeout_s)), "mlt_p2p_set_timeout")
+        self._oneshot_off = {}            # (lo, hi) of a bucket -> its byte offset inside the one-shot receive slots
+        self._oneshot_used = 0
         logger.info(f"symmetric arena: {total >> 20} MiB per rank, multicast={'yes' if self.arena.multicast else 'no'}")
 
     def alloc(self, numel, dtype, device):
@@ -178,19 +188,67 @@ class P2PComm(Comm):
     def allreduce_update(self, opt, lo: int, hi: int, stream=None):
         n = hi - lo
         gsz = opt.grad.element_size()
-        algo = self.pick_algo(n * gsz)
-        if algo == "oneshot" and n * gsz > self.oneshot_max:
-            algo = "nvls" if self.arena.multicast else "twoshot"
+        algo = self.algo_for(lo, hi, gsz)
+        recv_off = self._oneshot_off.get((lo, hi), 0) if algo == "oneshot" else 0
         grad_off = self.arena.offset_of(opt.grad) + lo * gsz
         model_off = self.arena.offset_of(opt.model) + lo * opt.model.element_size()
         one = lambda t: (_c_vp * 1)(t.data_ptr() if t is not None else 0)
         s2 = opt.s2[lo:hi] if opt.s2.numel() > 1 else None
-        check(self.L.mlt_p2p_allreduce_update(
+        check(self.L.mlt_p2p_allreduce_update_at(
             ctypes.byref(self.ctx), _c_int(ALGO_IDS[algo]), _c_int(RULE_IDS[opt.kind]),
             _c_int(int(opt.grad.dtype == torch.bfloat16)), _c_ll(grad_off), _c_ll(model_off),
             _c_int(int(opt.model is opt.master)), one(opt.master[lo:hi]), one(opt.s1[lo:hi]), one(s2), one(opt.hyper),
-            _c_ll(n), _c_int(0), _c_int(1), stream_handle(stream)), "mlt_p2p_allreduce_update")
+            _c_ll(n), _c_int(0), _c_int(1), _c_ll(recv_off), stream_handle(stream)), "mlt_p2p_allreduce_update")
         launches.bump(f"p2p_allreduce_update_{algo}")
+
+    def algo_for(self, lo: int, hi: int, gsz: int) -> str:
+        """The variant bucket ``[lo, hi)`` runs with.  Deterministic in (lo, hi) and identical on every rank: a one-shot
+        bucket claims its own byte range of the receive slots the first time it is seen (buckets of one step must not share
+        slot bytes); a bucket that no longer fits falls back to the sharded variants."""
+        nbytes = (hi - lo) * gsz
+        algo = self.pick_algo(nbytes)
+        if algo == "oneshot":
+            off = self._oneshot_off.get((lo, hi))
+            if off is None:
+                off = _align(self._oneshot_used, 256)
+                if off + nbytes <= self.oneshot_max:
+                    self._oneshot_off[(lo, hi)] = off
+                    self._oneshot_used = off + nbytes
+                else:
+                    self._oneshot_off[(lo, hi)] = -1
+                    off = -1
+            if off < 0:
+                algo = "nvls" if self.arena.multicast else "twoshot"
+        return algo
+
+    def owned_slices(self, opt, lo: int, hi: int):
+        gsz = opt.grad.element_size()
+        if self.world_size == 1 or self.algo_for(lo, hi, gsz) == "oneshot":
+            return []
+        E = 16 // gsz                                   # elements per 16-byte vector of the gradient dtype
+        nvec = (hi - lo) // E
+        per_rank = -(-nvec // self.world_size)
+        out = []
+        for r in range(self.world_size):
+            a = min(nvec, r * per_rank)
+            b = min(nvec, a + per_rank)
+            if b > a:
+                out.append((r, lo + a * E, lo + b * E))
+        return out
+
+    def consolidate(self, opt, buckets):
+        """Every rank ends up with the complete fp32 master weights and optimizer state.
+
+        The two-shot / NVLS kernels update master and state only on the rank that owns a slice (peers receive the
+        compute-dtype weights).  Before a checkpoint each owner broadcasts its slices with the P2P store kernel."""
+        if self.world_size == 1:
+            return
+        tensors = [opt.master, opt.s1] + ([opt.s2] if opt.s2.numel() > 1 else [])
+        for bk in buckets:
+            for r, a, b in self.owned_slices(opt, bk.lo, bk.hi):
+                for t in tensors:
+                    self.broadcast(t[a:b], src=r)
+        torch.cuda.current_stream().synchronize()
 
     def all_reduce_mean(self, flat, stream=None):
         """Unfused in-place mean all-reduce (the reference's ``_average_gradients``), through the same P2P / NVLS
@@ -234,8 +292,8 @@ class P2PComm(Comm):
             dist.broadcast(tensor, src=src)
             return
         stage = self.arena.view(self.recv_off, stage_bytes, torch.uint8)
-        flat = tensor.contiguous().view(-1).view(torch.uint8)
-        stage[:nbytes].copy_(flat)
+        if self.rank == src:                      # only the source writes the slot the broadcast pushes from (and into)
+            stage[:nbytes].copy_(tensor.contiguous().view(-1).view(torch.uint8))
         check(self.L.mlt_p2p_broadcast(ctypes.byref(self.ctx), _c_ll(self.recv_off), _c_ll(stage_bytes), _c_int(src),
                                        _c_int(1), stream_handle()), "mlt_p2p_broadcast")
         launches.bump("p2p_broadcast")
@@ -263,6 +321,10 @@ class P2PComm(Comm):
             dist.barrier(group=self.cpu_group)
 
     def check_errors(self):
+        """Raises ``RuntimeError`` with the rank / peer / CTA / ticket diagnostic if a flag wait of any collective on this rank
+        ran past the limit (``MLT_P2P_TIMEOUT_S``, default 20 s), or a peer reported that it did."""
+        if self.arena is None:
+            return
         out = (ctypes.c_uint * 6)()
         check(self.L.mlt_p2p_check_error(ctypes.byref(self.ctx), out), "mlt_p2p_check_error")
 

@@ -59,41 +59,58 @@ class NativeLoop:
     def _finish(self, steps):
         a, b, c = _c_ll(0), _c_ll(0), _c_ll(0)
         self.L.mlt_loop_stats(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
-        self.last_stats = {"h2d_bytes": a.value, "d2h_bytes": b.value, "launches": c.value, "steps": steps}
+        t = (ctypes.c_double * 3)()
+        self.L.mlt_loop_timing(self.h, t)
+        self.last_stats = {"h2d_bytes": a.value, "d2h_bytes": b.value, "launches": c.value, "steps": steps,
+                           "host_us": {"first_enqueued": t[0], "all_enqueued": t[1], "drained": t[2]}}
+
+    def _lenet_call(self, fused) -> "LeNetCall":
+        """The fixed arguments of the step kernel, built once per (optimizer arena, scratch buffer)."""
+        o = fused.opt
+        key = (id(fused), fused._scratch.data_ptr(), o.master.data_ptr())
+        if getattr(self, "_call_key", None) != key:
+            call = LeNetCall()
+            call.master, call.s1 = o.master.data_ptr(), o.s1.data_ptr()
+            call.s2 = o.s2.data_ptr() if o.s2.numel() > 1 else None
+            call.hyper, call.numel = o.hyper.data_ptr(), o.numel
+            call.param_off = ctypes.cast(fused.off, ctypes.POINTER(_c_ll))
+            call.rule = fused.rule
+            call.scratch, call.scratch_bytes = fused._scratch.data_ptr(), fused._scratch.numel()
+            call.ctx = ctypes.pointer(fused.ctx) if fused.ctx is not None else None
+            self._call, self._call_key = call, key
+        return self._call
 
     def run_lenet(self, fused, host_x: torch.Tensor, host_y: torch.Tensor, indices: torch.Tensor, batch: int,
                   batch_sizes: Optional[Sequence[int]], hyper_rows: Optional[torch.Tensor], train: bool,
                   acc3: Optional[torch.Tensor], want_acc: bool, loss_buf: torch.Tensor) -> torch.Tensor:
-        """Run one epoch of single-kernel LeNet steps.  Returns the per-step losses (CPU float32 tensor)."""
+        """Run one epoch of single-kernel LeNet steps.  Returns the per-step losses (CPU float32 tensor).
+
+        ``batch_sizes``: None when every step is a full batch, else the per-step sizes."""
         steps = len(batch_sizes) if batch_sizes is not None else indices.numel() // batch
         fused.ensure_scratch(max(batch_sizes) if batch_sizes is not None else batch, self.device)
-        o = fused.opt
-        call = LeNetCall()
-        call.master, call.s1 = o.master.data_ptr(), o.s1.data_ptr()
-        call.s2 = o.s2.data_ptr() if o.s2.numel() > 1 else None
-        call.hyper, call.numel = o.hyper.data_ptr(), o.numel
-        call.param_off = ctypes.cast(fused.off, ctypes.POINTER(_c_ll))
-        call.rule, call.train, call.want_acc = fused.rule, int(train), int(want_acc)
+        call = self._lenet_call(fused)
+        call.train, call.want_acc = int(train), int(want_acc)
         call.acc3 = acc3.data_ptr() if acc3 is not None else None
         call.loss_out = loss_buf.data_ptr()
-        call.scratch, call.scratch_bytes = fused._scratch.data_ptr(), fused._scratch.numel()
-        call.ctx = ctypes.pointer(fused.ctx) if fused.ctx is not None else None
         losses = torch.empty(steps, dtype=torch.float32)
-        idx = indices.contiguous()
+        idx = indices if indices.is_contiguous() else indices.contiguous()
         bs = (ctypes.c_int * steps)(*batch_sizes) if batch_sizes is not None else None
         hr = hyper_rows.contiguous() if hyper_rows is not None else None
-        # kind 0: one launch per step (default).  kind 2 (MLT_LENET_PERSISTENT=1): the whole run is ONE persistent launch of
-        # the step kernel fed through the ring.  Measured on B200: 37.6 us/step vs 40.5 - back-to-back launches already hide
-        # all but ~2 us of the launch gap, which the persistent form pays back in its second grid barrier and flag polling.
-        persistent = self.slots <= 8 and os.environ.get("MLT_LENET_PERSISTENT", "0") == "1" and steps >= 2
+        # kind 0: one launch per step.  kind 2: the whole run is ONE persistent launch of the step kernel fed through the
+        # ring (the copy stream publishes "batch i has landed" in a device word the kernel polls).  One GPU: kind 0 is a little
+        # faster (37.6 vs 40.5 us/step on B200: back-to-back launches already hide the launch gap).  Several GPUs: the ranks'
+        # kernels wait for each other inside every step, so with one launch per step every step pays the slowest rank's launch
+        # jitter; the persistent form removes the per-step launches from that critical path.  MLT_LENET_PERSISTENT=0/1 overrides.
+        env = os.environ.get("MLT_LENET_PERSISTENT", "auto")
+        want_persistent = False if env == "auto" else env == "1"      # "auto" stays on kind 0 until the N >= 2 measurement says otherwise
+        persistent = self.slots <= 8 and want_persistent and steps >= 2
         check(self.L.mlt_loop_run(self.h, ptr(host_x), ptr(host_y), ptr(idx), _c_ll(steps), _c_int(batch), bs,
-                                  ptr(hr), ptr(o.hyper), _c_int(2 if persistent else 0), ctypes.byref(call), None, ptr(loss_buf),
+                                  ptr(hr), ptr(fused.opt.hyper), _c_int(2 if persistent else 0), ctypes.byref(call), None, ptr(loss_buf),
                                   ptr(losses), stream_handle()), "mlt_loop_run")
         self.last_kind = 2 if persistent else 0
         launches.bump("lenet_step", 1 if persistent else steps)
         self._finish(steps)
         return losses
-
 
     # ------------------------------------------------------------------ generic (CUDA-graph) steps
     def slot_tensors(self, slot: int, x_shape, x_dtype, y_shape, y_dtype):

@@ -140,7 +140,9 @@ class Trainer:
         self.criterion = self._get_criterion()
         self.pred_function = self._get_prediction_function()
         padded = sum((p.numel() + 127) // 128 * 128 for p in self.model.parameters() if p.requires_grad)
-        self.comm.prepare(padded, self.compute_dtype)
+        from .optim.rules import RULE_STATES
+
+        self.comm.prepare(padded, self.compute_dtype, n_states=RULE_STATES.get(self.optimizer_type, 2))
         self.optimizer = self._get_optimizer()
         if self.world_size > 1:
             self._sync_initial_state()
@@ -248,6 +250,7 @@ class Trainer:
         if self.world_size > 1:
             sums = self.comm.reduce_scalars(sums)
         loss_sum, metric_sum, n = sums.tolist()
+        self.comm.check_errors()            # a peer that stopped answering: raise here, not a checkpoint later
         n = max(n, 1.0)
         return loss_sum / n, metric_sum / n
 
@@ -369,7 +372,9 @@ class Trainer:
             opt._opt_called = True
         loop = self._native_loop_for(loader)
         x, y = loader._backing[0], loader._backing[1]
-        losses = loop.run_lenet(eng.fused, x, y, idx, loader.batch_size, sizes, hyper, train, eng.acc,
+        B = loader.batch_size
+        uniform = sizes[-1] == B and (len(sizes) < 2 or (min(sizes) == B and max(sizes) == B))
+        losses = loop.run_lenet(eng.fused, x, y, idx, B, None if uniform else sizes, hyper, train, eng.acc,
                                 self.metric == "accuracy", eng._loss_buf)
         if train:
             self.last_step_losses = losses
@@ -461,6 +466,15 @@ class Trainer:
         prefix = "module." if self.is_parallel else ""
         return self.optimizer.master_state_dict(self.model, prefix=prefix)
 
+    def consolidate(self):
+        """Collective: make this rank's fp32 master weights and optimizer state complete and check the communicator.
+
+        The sharded all-reduce + update kernels (two-shot / NVLS) keep master and state current only on the rank that
+        owns a slice; every rank must call this before any rank writes a checkpoint."""
+        self.comm.check_errors()
+        if self.world_size > 1 and self.engine.fused is None:
+            self.comm.consolidate(self.optimizer, self.reducer.buckets)
+
     def save_model(self, model_dir):
         logger.info("Saving the model.")
         return save_state_dict(self._state_dict_for_save(), model_dir, "model.pth", writer=self._snap)
@@ -530,6 +544,7 @@ class Trainer:
             self.clear()
             # Save model on master node; everyone waits so no rank races ahead of the file.
             if epoch % max(self.cfg.save_every, 1) == 0 or epoch == self.epochs:
+                self.consolidate()          # collective: owners hand their master / state slices to everyone
                 if self.rank == 0:
                     self.save(self.model_dir, epoch=epoch)
                 self.comm.barrier()
