@@ -64,6 +64,7 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-flush", action="store_true")
     ap.add_argument("--seq-len", type=int, default=512)
+    ap.add_argument("--child", action="store_true", help=argparse.SUPPRESS)      # a secondary model measured in its own process
     a = ap.parse_args()
     if a.secondary is None:
         a.secondary = "resnet50,bert_base" if a.model == "mlmodel" and not a.batch else "none"
@@ -189,6 +190,47 @@ def make_datasets(model, global_batch, steps, seq_len, seed=32):
 
 def median(xs):
     return float(statistics.median(xs)) if xs else float("nan")
+
+
+def measure_in_child(a, model, index, timeout_s):
+    """Measure ``model`` with this same script in a fresh process per rank (its own CUDA context, allocator and process group),
+    so nothing one model leaves behind - graph pools, page-locked datasets, communicators - can touch the next.  Every rank
+    of a multi-GPU job spawns its own child with the same rank environment and a rendezvous port of its own."""
+    env = dict(os.environ)
+    rank, _, world = env_rank()
+    if world > 1:
+        env["MASTER_PORT"] = str(int(env.get("MASTER_PORT", "29500")) + 97 * (index + 1))
+        env.pop("TORCHELASTIC_USE_AGENT_STORE", None)      # the child ranks rendezvous on their own store, not torchrun's
+    cmd = [sys.executable, os.path.abspath(__file__), "--gpus", str(a.gpus), "--steps", str(a.steps), "--warmup", str(a.warmup),
+           "--impl", a.impl, "--model", model, "--secondary", "none", "--repeats", str(a.repeats), "--scaling", a.scaling,
+           "--seq-len", str(a.seq_len), "--budget-s", str(max(timeout_s - 20.0, 30.0)), "--child"]
+    for flag, val in (("--metric", a.metric), ("--optimizer", a.optimizer), ("--backend", a.backend), ("--comm-algo", a.comm_algo)):
+        if val:
+            cmd += [flag, str(val)]
+    for flag, on in (("--no-graph", a.no_graph), ("--no-flush", a.no_flush), ("--no-pool", a.no_pool)):
+        if on:
+            cmd.append(flag)
+    t0 = time.time()
+    try:
+        r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout_s)
+    except subprocess.TimeoutExpired:
+        return {"error": f"timed out after {timeout_s:.0f} s"}
+    if r.stderr:
+        sys.stderr.write(r.stderr[-4000:])
+    if rank != 0:
+        return None
+    rec = None
+    for line in reversed(r.stdout.strip().splitlines()):
+        if line.startswith("{"):
+            try:
+                rec = json.loads(line)
+                break
+            except ValueError:
+                pass
+    if rec is None:
+        return {"error": f"child exited {r.returncode} without a record", "stderr_tail": r.stderr[-600:]}
+    rec["wall_s"] = round(time.time() - t0, 1)
+    return rec
 
 
 # --------------------------------------------------------------------------------------------------
@@ -393,29 +435,17 @@ def run_ours(a):
     keeper = LineKeeper(a.budget_s, rank == 0)
     rec = measure_ours(a, a.model)
     keeper.rec = rec
-    # rough wall-clock need of one secondary model (build + capture + R x K steps, both views); skip what cannot fit
-    need = {"resnet50": 150.0, "bert_base": 120.0}
     dev = torch.device("cuda", local_rank)
-    for m in a.secondary:
+    # each secondary model runs in its own process (see measure_in_child); skip what cannot fit in the time left
+    need = {"resnet50": 150.0, "bert_base": 120.0}
+    for i, m in enumerate(a.secondary):
         left = -reduce_max(-keeper.left(), dev)           # the same decision on every rank
         if left < need.get(m, 120.0):
             if rec is not None:
                 rec.setdefault("secondary", {})[m] = {"skipped": "time budget"}
             continue
-        t0 = time.time()
-        try:
-            sub = measure_ours(a, m)
-        except Exception as ex:  # noqa: BLE001  (a secondary must never cost the primary line)
-            import traceback
-
-            traceback.print_exc()
-            sub = {"error": f"{type(ex).__name__}: {ex}"[:400]}
-            if world > 1:          # ranks may now disagree about what comes next: report and stop here
-                if rec is not None:
-                    rec.setdefault("secondary", {})[m] = sub
-                break
+        sub = measure_in_child(a, m, i, left - 15.0)
         if rec is not None and sub is not None:
-            sub["wall_s"] = round(time.time() - t0, 1)
             rec.setdefault("secondary", {})[m] = sub
     keeper.emit()
     keeper.timer.cancel()
@@ -447,10 +477,8 @@ def _reference_imports():
 
 
 def measure_reference(a, model_name, keeper, RefTrainer, RefLoader, RefModel):
-    """Returns (record or None, seconds of budget left as agreed by all ranks).  The reference's Trainer calls
-    ``init_process_group`` in its constructor, so the group is destroyed again before the next model."""
+    """Returns (record or None, seconds of budget left as agreed by all ranks)."""
     import torch
-    import torch.distributed as dist
 
     rank, local_rank, world = env_rank()
     dev = torch.device("cuda", local_rank)
@@ -507,8 +535,6 @@ def measure_reference(a, model_name, keeper, RefTrainer, RefLoader, RefModel):
 
     gc.collect()
     torch.cuda.empty_cache()
-    if world > 1 and dist.is_initialized():
-        dist.destroy_process_group()
     if rank != 0:
         return None, left
     sps = gb * steps / (ms / 1e3)
@@ -529,6 +555,7 @@ def measure_reference(a, model_name, keeper, RefTrainer, RefLoader, RefModel):
 
 
 def run_reference(a):
+    os.environ["TQDM_DISABLE"] = "1"          # tqdm reads it when it is first imported: no progress bars in the timed region
     ref_dir = os.path.join(ROOT, "baseline", "_ref")
     if not os.path.exists(os.path.join(ref_dir, "src", "trainer.py")):
         try:
@@ -555,25 +582,15 @@ def run_reference(a):
     rec, left = measure_reference(a, a.model, keeper, *refs)
     keeper.rec = rec
     need = {"resnet50": 150.0, "bert_base": 100.0}
-    for m in a.secondary:
+    for i, m in enumerate(a.secondary):
+        if i > 0:
+            left = -reduce_max(-keeper.left(), dev)
         if left < need.get(m, 120.0):
             if rec is not None:
                 rec.setdefault("secondary", {})[m] = {"skipped": "time budget"}
             continue
-        t0 = time.time()
-        try:
-            sub, left = measure_reference(a, m, keeper, *refs)
-        except Exception as ex:  # noqa: BLE001
-            import traceback
-
-            traceback.print_exc()
-            sub = {"error": f"{type(ex).__name__}: {ex}"[:400]}
-            if world > 1:
-                if rec is not None:
-                    rec.setdefault("secondary", {})[m] = sub
-                break
+        sub = measure_in_child(a, m, i, left - 15.0)
         if rec is not None and sub is not None:
-            sub["wall_s"] = round(time.time() - t0, 1)
             rec.setdefault("secondary", {})[m] = sub
     keeper.emit()
     keeper.timer.cancel()

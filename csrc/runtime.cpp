@@ -80,6 +80,12 @@ struct Loop {
   // sample straight from the (page-locked) dataset into the slot's device buffer.
   bool direct_x = false;
   size_t y_off = 0;                     // byte offset of the targets inside a slot's buffers
+  // uint8 image datasets: augment on the device before every step (augment.cu)
+  bool aug_on = false;
+  mlt_augment_cfg aug{};
+  void* aug_out = nullptr;
+  int aug_bf16 = 0, aug_train = 1;
+  unsigned long long aug_pos0 = 0;
   // ---- gather thread (one per loop, parked between runs) ------------------------------------------------------
   struct Job {
     const char* hx = nullptr; const char* hy = nullptr;
@@ -189,6 +195,14 @@ extern "C" int mlt_loop_num_slots(void* loop) { return ((Loop*)loop)->slots; }
 // on != 0: the dataset's x tensor is page-locked; copy samples device-ward one by one instead of gathering on the host
 extern "C" int mlt_loop_set_direct_rows(void* loop, int on) { ((Loop*)loop)->direct_x = on != 0; return 0; }
 
+extern "C" int mlt_loop_set_augment(void* loop, const mlt_augment_cfg* cfg, void* out_dev, int out_bf16, unsigned long long pos0,
+                                    int train) {
+  Loop* L = (Loop*)loop;
+  L->aug_on = cfg != nullptr && out_dev != nullptr;
+  if (L->aug_on) { L->aug = *cfg; L->aug_out = out_dev; L->aug_bf16 = out_bf16; L->aug_pos0 = pos0; L->aug_train = train; }
+  return 0;
+}
+
 extern "C" int mlt_loop_destroy(void* loop) {
   Loop* L = (Loop*)loop;
   if (!L) return 0;
@@ -254,6 +268,10 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
   // their loss straight into the pinned host array (a posted store over PCIe): no per-step copy operations at all.
   const bool table_mode = step_kind == 0 || step_kind == 2;
   const bool persistent = step_kind == 2;
+  if (persistent && L->aug_on) {
+    set_error("mlt_loop_run: the persistent step kernel owns every SM; it cannot be combined with the per-step augmentation kernel");
+    return 1;
+  }
   if (table_mode && hyper_rows) {
     if (steps > L->dev_hyper_cap) {
       if (L->dev_hyper) cudaFree(L->dev_hyper);
@@ -375,6 +393,12 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
       continue;
     }
     if ((rc = (int)cudaStreamWaitEvent(cs, sl.ready, 0)) != 0) break;
+    if (L->aug_on) {      // uint8 rows -> cropped / flipped / normalised batch the step reads
+      if ((rc = mlt_augment_u8(sl.dev_x, L->aug_out, L->aug_bf16, (int)n, &L->aug, L->aug_pos0 + (unsigned long long)start[i], L->aug_train, cs)) != 0) {
+        abort.store(true); gatherer.join(); return rc;
+      }
+      L->launches += 1;
+    }
     if (hyper_rows && !table_mode) {
       if ((rc = (int)cudaMemcpyAsync(hyper_dev, L->pin_hyper + i * 8, 8 * sizeof(float), cudaMemcpyHostToDevice, cs)) != 0) break;
       L->h2d_bytes += 32;
@@ -383,7 +407,7 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
       const void* hy = hyper_rows ? (const void*)(L->dev_hyper + i * 8) : lenet->hyper;
       void* lo = loss_dev ? (void*)(L->pin_loss + i) : lenet->loss_out;      // pinned host memory is device-addressable (UVA)
       rc = mlt_lenet_step(lenet->master, lenet->s1, lenet->s2, hy, lenet->numel, lenet->param_off, lenet->rule,
-                          sl.dev_x, sl.dev_y, (int)n, lenet->train, lenet->want_acc, lenet->acc3, lo,
+                          L->aug_on ? L->aug_out : sl.dev_x, sl.dev_y, (int)n, lenet->train, lenet->want_acc, lenet->acc3, lo,
                           lenet->scratch, lenet->scratch_bytes, lenet->ctx, cs);
       if (rc != 0) break;
       if (loss_dev) L->d2h_bytes += 4;

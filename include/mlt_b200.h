@@ -53,6 +53,17 @@ int mlt_softmax_xent(const void* logits, int is_bf16, const void* targets_i64, v
                      void* acc3, void* workspace16, int B, int C, int want_acc, void* stream);
 int mlt_argmax_accuracy(const void* logits, int is_bf16, const void* targets_i64, void* out_scalar, int B, int C,
                         void* stream);
+/* The reference's other criteria and metric, fused like the cross-entropy (src/trainer.py:140-150, 160-163).
+ * mlt_regression_loss: kind 0 = L1Loss, 1 = MSELoss (also custom_loss_function, src/utils/functions.py:15-17); loss, its
+ * gradient w.r.t. pred (NULL: forward only) and, for rows of C, the mcrmse metric; acc3 = {loss_sum, metric_sum, steps}.
+ * workspace: mlt_regression_loss_ws_bytes(C) bytes, zero before the first call, left zero by every call.
+ * mlt_nll_loss: NLLLoss on log-probabilities + gradient + arg-max accuracy; 16-byte workspace as mlt_softmax_xent. */
+long long mlt_regression_loss_ws_bytes(int C);
+int mlt_regression_loss(int kind, const void* pred, int pred_bf16, const void* target, int target_bf16, void* dpred,
+                        void* loss_out, void* acc3, void* workspace, long long ws_bytes, long long n, int C, int want_mcrmse,
+                        void* stream);
+int mlt_nll_loss(const void* logp, int is_bf16, const void* targets_i64, void* dlogp, void* loss_out, void* acc3,
+                 void* workspace16, int B, int C, int want_acc, void* stream);
 
 /* ---- small-shape CNN path: src/model.py:18-23 (conv/relu/pool/fc of MLModel) and their backward ---- */
 int mlt_conv2d_direct_fwd(const void* x, const void* w, const void* bias, void* y, void* pool_idx, int B, int Cin,
@@ -160,6 +171,23 @@ int mlt_lenet_step(void* master, void* s1, void* s2, const void* hyper, long lon
                    int rule, const void* x, const void* y_i64, int B, int train, int want_acc, void* acc3,
                    void* loss_out, void* scratch, long long scratch_bytes, const mlt_p2p_ctx* ctx, void* stream);
 
+/* ---- image augmentation on the device: the reference's CIFAR pipeline (src/utils/functions.py:5-12) as one kernel ---------- */
+typedef struct {
+  int C, H, W;                /* source image (uint8) */
+  int out_h, out_w;           /* output window (== H, W for random crops) */
+  int pad;                    /* zero padding before the crop (RandomCrop(size, padding)) */
+  int flip;                   /* != 0: horizontal flip with probability 1/2 */
+  int hwc;                    /* != 0: source is [N, H, W, C] (CIFAR's own layout), else [N, C, H, W] */
+  float mean[4], std[4];      /* Normalize(mean, std) on the [0, 1] image */
+  unsigned long long seed;
+} mlt_augment_cfg;
+/* uint8 batch on the device -> normalised [B, C, out_h, out_w] fp32 / bf16; sample b draws from stream position pos0 + b;
+ * train == 0: centre window, no flip. */
+int mlt_augment_u8(const void* src_u8, void* dst, int dst_bf16, int B, const mlt_augment_cfg* cfg, unsigned long long pos0, int train,
+                   void* stream);
+/* the random draw of one stream position: out3 = {top, left, flip} */
+int mlt_augment_params(const mlt_augment_cfg* cfg, unsigned long long pos, int* out3);
+
 /* ---- native epoch executor + data feeder: the Python hot loop of src/trainer.py:180-197, in C++ ------------------ */
 typedef struct {            /* fixed arguments of mlt_lenet_step; x / y / B come from the executor's ring slots */
   void *master, *s1, *s2;
@@ -177,7 +205,11 @@ void* mlt_loop_create(int device, int slots, long long max_batch, long long x_ro
 void* mlt_loop_slot_x(void* loop, int slot);
 void* mlt_loop_slot_y(void* loop, int slot);
 int mlt_loop_num_slots(void* loop);
-int mlt_loop_set_direct_rows(void* loop, int on);   /* x rows are page-locked: gather by DMA (one copy per sample) */
+int mlt_loop_set_direct_rows(void* loop, int on);
+/* uint8 image datasets: every step first runs mlt_augment_u8 from the slot's uint8 rows into `out_dev` ([max_batch, C, out_h, out_w],
+ * owned by the caller) and the step reads `out_dev`.  cfg NULL switches it off.  pos0: stream position of the next run's first
+ * sample; train as in mlt_augment_u8. */
+int mlt_loop_set_augment(void* loop, const mlt_augment_cfg* cfg, void* out_dev, int out_bf16, unsigned long long pos0, int train);   /* x rows are page-locked: gather by DMA (one copy per sample) */
 int mlt_loop_destroy(void* loop);
 /* Runs `steps` steps: host gather -> pinned -> H2D (copy stream) -> hyper row H2D -> step -> loss D2H, ring-buffered.
  * step_kind 0: single-kernel LeNet step (`lenet`);  1: one captured cudaGraphExec_t per slot (`graph_execs`). */
@@ -196,6 +228,14 @@ long long mlt_layernorm_bwd_scratch_bytes(int T, int H);
 int mlt_layernorm_bwd(const void* dy, const void* h, const void* mean, const void* rstd, const void* gamma, int params_bf16,
                       void* dx, void* dgamma, void* dbeta, int grads_bf16, void* scratch, long long scratch_bytes, int T,
                       int H, void* stream);
+/* RMSNorm (+ residual add) forward / one-pass backward (csrc/rmsnorm.cu): bf16 [T, H] activations, H a multiple of 8 up to 8192,
+ * gamma fp32 or bf16, rstd fp32 [T].  hsum (optional, with res) receives the rounded pre-norm sum h = x + res.
+ * backward: dx and dgamma from one read of dy and h; scratch = mlt_rmsnorm_bwd_scratch_bytes(), zeroed once, left zero. */
+int mlt_rmsnorm_fwd(const void* x, const void* res, const void* gamma, int params_bf16, void* y, void* hsum, void* rstd, int T, int H,
+                    float eps, void* stream);
+long long mlt_rmsnorm_bwd_scratch_bytes(void);
+int mlt_rmsnorm_bwd(const void* dy, const void* h, const void* rstd, const void* gamma, int params_bf16, void* dx, void* dgamma,
+                    int grads_bf16, void* scratch, long long scratch_bytes, int T, int H, void* stream);
 int mlt_softmax_rows(void* scores_bf16, long long rows, int L, float scale, void* stream);               /* in place */
 int mlt_softmax_rows_bwd(void* dp_bf16, const void* p_bf16, long long rows, int L, float scale, void* stream);
 /* Fused attention on tcgen05 (scores never leave the SM).  q, k, v: [B, S, H*64] bf16 with row stride ld_qkv elements

@@ -39,6 +39,18 @@ def build_datasets(args):
         return mk(args.synthetic_train, args.seed), mk(args.synthetic_val, args.seed + 1)
     import torchvision
 
+    if args.custom_function and args.device_augment:
+        # The reference's recipe (RandomCrop(32, 4) + RandomHorizontalFlip + ToTensor + Normalize, src/utils/functions.py:5-12)
+        # without PIL in the loop: the images stay uint8 in one tensor, batches go to the GPU as uint8 and one kernel
+        # crops / flips / normalises them (ml_trainer_b200/data/augment.py).  On a CPU-only box the same class applies
+        # the same arithmetic on the host.
+        from ml_trainer_b200 import DeviceAugment, U8ImageDataset
+
+        raw_train = torchvision.datasets.CIFAR10(root=args.data_dir, train=True, download=False)
+        raw_val = torchvision.datasets.CIFAR10(root=args.data_dir, train=False, download=False)
+        aug = DeviceAugment((3, 32, 32), padding=4, flip=True, seed=args.seed)
+        return (U8ImageDataset.from_torchvision(raw_train, aug, train=True),
+                U8ImageDataset.from_torchvision(raw_val, DeviceAugment((3, 32, 32), padding=0, flip=False), train=False))
     if args.custom_function:
         from src.utils.functions import custom_pre_process_function
 
@@ -114,6 +126,9 @@ def get_parser():
     parser.add_argument("--synthetic_val", type=int, default=512)
     parser.add_argument("--seq_len", type=int, default=512)
     parser.add_argument("--no_progress", action="store_true")
+    parser.add_argument("--device_augment", type=_str2bool, default=True,
+                        help="with --custom_function: keep CIFAR uint8 and crop / flip / normalise in a GPU kernel (default: True); "
+                             "False uses the torchvision PIL pipeline exactly as the reference does")
     return parser
 
 

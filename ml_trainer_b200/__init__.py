@@ -7,6 +7,7 @@ src/dataloader.py, src/utils/*):
     Trainer(model, datasets=(train, val), epochs=E, batch_size=B, is_parallel=False, **config).fit()
 """
 from .config import TrainerConfig, validate_kwargs
+from .data.augment import DeviceAugment, U8ImageDataset
 from .data.loader import Loader, PinnedPrefetcher, SyntheticDataset
 from .models import MLModel, available_models, build_model
 from .trainer import Trainer
@@ -17,6 +18,6 @@ __version__ = "0.1.0"
 
 __all__ = [
     "Trainer", "TrainerConfig", "validate_kwargs", "MLModel", "build_model", "available_models",
-    "Loader", "PinnedPrefetcher", "SyntheticDataset", "load_model", "load_history", "plot_history",
+    "Loader", "PinnedPrefetcher", "SyntheticDataset", "DeviceAugment", "U8ImageDataset", "load_model", "load_history", "plot_history",
     "custom_loss_function", "custom_pre_process_function",
 ]

@@ -56,6 +56,10 @@ class SyntheticDataset(Dataset):
 def _tensor_backing(dataset) -> Optional[Tuple[torch.Tensor, ...]]:
     if isinstance(dataset, SyntheticDataset):
         return dataset.tensors
+    from .augment import U8ImageDataset
+
+    if isinstance(dataset, U8ImageDataset):
+        return dataset.tensors
     if isinstance(dataset, TensorDataset) and all(isinstance(t, torch.Tensor) and t.device.type == "cpu"
                                                   for t in dataset.tensors):
         return dataset.tensors
@@ -72,6 +76,9 @@ class Loader(DataLoader):
                       and kw.get("collate_fn") is None and self.batch_sampler is not None)
         self._backing = backing
         self._pool = getattr(dataset, "_pool", None)
+        # uint8 image datasets: batches travel as uint8 and are augmented on the device (data/augment.py)
+        self._augment = getattr(dataset, "augment", None) if backing is not None and backing[0].dtype == torch.uint8 else None
+        self._augment_train = bool(getattr(dataset, "train", True))
 
     def __iter__(self):
         if not self._fast:
@@ -89,6 +96,13 @@ class Loader(DataLoader):
                 buf = torch.empty((index.numel(), *t.shape[1:]), dtype=t.dtype, pin_memory=pin)
                 torch.index_select(t, 0, index, out=buf)
                 out.append(buf)
+            aug = self._augment
+            if aug is not None and not getattr(self, "_augment_on_device", False):
+                # host statement of the augmentation (CPU training, or a consumer that does not augment on the device)
+                pos0, train = aug.position, self._augment_train
+                out[0] = torch.stack([aug.apply_cpu(out[0][k], pos0 + k, train) for k in range(index.numel())])
+                if train:
+                    aug.position += index.numel()
             yield tuple(out)
 
 

@@ -45,7 +45,7 @@ class StepEngine:
         self.last_loss: Optional[torch.Tensor] = None
         # single-kernel step (forward + loss + backward + all-reduce + update) when the model provides one
         self.fused = None
-        if fused_step and getattr(criterion, "native_fused", False) and hasattr(model, "make_fused_step") \
+        if fused_step and getattr(criterion, "is_cross_entropy", False) and hasattr(model, "make_fused_step") \
                 and device.type == "cuda" and metric in (None, "accuracy"):
             self.fused = model.make_fused_step(reducer.opt, reducer.comm)
         if self.fused is not None:
@@ -89,12 +89,11 @@ class StepEngine:
                 and not getattr(model, "_mlt_accepts_fp32_input", False):
             inputs = inputs.to(self.compute_dtype)       # inside the captured graph; library models convert themselves
         outputs = model(inputs)
-        fused = (getattr(self.criterion, "native_fused", False) and outputs.dim() == 2
-                 and targets.dtype == torch.int64)
-        if fused:
-            want_acc = self.metric == "accuracy"
-            loss, dl = self.criterion.fused_step(outputs.detach(), targets, self.acc, want_acc, need_grad=train)
-            if self.metric and not want_acc:
+        crit = self.criterion
+        if getattr(crit, "native_fused", False) and crit.accepts(outputs, targets):
+            in_kernel = self.metric is not None and self.metric in crit.metrics     # metric accumulated by the loss kernel
+            loss, dl = crit.fused_step(outputs.detach(), targets, self.acc, in_kernel, need_grad=train)
+            if self.metric and not in_kernel:
                 with torch.no_grad():
                     self.acc[1] += M.evaluate(self.metric, outputs.detach(), targets).float()
             return outputs, loss, dl

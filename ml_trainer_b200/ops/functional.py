@@ -135,6 +135,93 @@ def cross_entropy(logits, targets):
     return _CrossEntropyFn.apply(logits, targets)
 
 
+REGRESSION_KINDS = {"l1": 0, "l2": 1, "custom": 1}
+
+
+def regression_loss(pred: torch.Tensor, target: torch.Tensor, kind: str = "l2", acc3: Optional[torch.Tensor] = None,
+                    want_mcrmse: bool = False, need_grad: bool = True):
+    """Mean L1 / L2 loss over all elements and d(loss)/d(pred) in one pass; returns ``(loss, dpred)``.
+
+    ``kind``: ``l1`` (torch ``L1Loss``), ``l2`` (``MSELoss``) or ``custom`` (the reference's ``custom_loss_function``,
+    mean((out - target)**2), src/utils/functions.py:15-17).  With ``want_mcrmse`` the reference's second metric (mean over
+    columns of the column-wise RMSE, src/trainer.py:160-163) is accumulated into ``acc3[1]`` by the same kernel."""
+    k = REGRESSION_KINDS[kind]
+    if (use_native(pred, target) and pred.dtype in (torch.float32, torch.bfloat16) and target.dtype in (torch.float32, torch.bfloat16)
+            and pred.shape == target.shape and pred.numel() > 0):
+        pred, target = pred.contiguous(), target.contiguous()
+        C = pred.shape[-1] if (want_mcrmse and pred.dim() >= 2) else 0
+        if want_mcrmse and not (0 < C <= 1024):
+            want_mcrmse, C = False, 0
+        loss = torch.empty((), dtype=torch.float32, device=pred.device)
+        dp = torch.empty_like(pred) if need_grad else None
+        L = _lib.lib()
+        L.mlt_regression_loss_ws_bytes.restype = _c_ll
+        ws = scratch(pred.device, "regloss", max(int(L.mlt_regression_loss_ws_bytes(_c_int(1024))), 256))
+        check(L.mlt_regression_loss(_c_int(k), ptr(pred), _c_int(int(pred.dtype == torch.bfloat16)), ptr(target),
+                                    _c_int(int(target.dtype == torch.bfloat16)), ptr(dp), ptr(loss), ptr(acc3), ptr(ws),
+                                    _c_ll(ws.numel()), _c_ll(pred.numel()), _c_int(C), _c_int(int(want_mcrmse)), stream_handle()),
+              "mlt_regression_loss")
+        launches.bump("regression_loss")
+        return loss, dp
+    d = pred.float() - target.float()
+    loss = d.abs().mean() if k == 0 else (d * d).mean()
+    dp = None
+    if need_grad:
+        dp = (torch.sign(d) if k == 0 else 2.0 * d) / d.numel()
+        dp = dp.to(pred.dtype)
+    if acc3 is not None:
+        acc3[0] += loss.detach()
+        if want_mcrmse:
+            acc3[1] += torch.mean(torch.sqrt(torch.mean(d.reshape(-1, d.shape[-1]) ** 2, dim=0)))
+        acc3[2] += 1.0
+    return loss, dp
+
+
+def nll_loss(logp: torch.Tensor, targets: torch.Tensor, acc3: Optional[torch.Tensor] = None, want_acc: bool = False,
+             need_grad: bool = True):
+    """Mean negative log-likelihood of log-probabilities ``logp`` [B, C] (torch ``NLLLoss``; the reference's ``neg-loss``,
+    src/trainer.py:143-144) with its gradient and the arg-max accuracy from one kernel; returns ``(loss, dlogp)``."""
+    B, C = logp.shape
+    if use_native(logp, targets) and logp.dtype in (torch.float32, torch.bfloat16):
+        logp = logp.contiguous()
+        loss = torch.empty((), dtype=torch.float32, device=logp.device)
+        dl = torch.empty_like(logp) if need_grad else None
+        ws = scratch(logp.device, "xent", 16)
+        check(_lib.lib().mlt_nll_loss(ptr(logp), _c_int(int(logp.dtype == torch.bfloat16)), ptr(targets), ptr(dl), ptr(loss),
+                                      ptr(acc3), ptr(ws), _c_int(B), _c_int(C), _c_int(int(want_acc)), stream_handle()), "mlt_nll_loss")
+        launches.bump("nll_loss")
+        return loss, dl
+    loss = TF.nll_loss(logp.float(), targets)
+    dl = None
+    if need_grad:
+        dl = torch.zeros_like(logp)
+        dl[torch.arange(B, device=logp.device), targets] = -1.0 / B
+    if acc3 is not None:
+        acc3[0] += loss.detach()
+        if want_acc:
+            acc3[1] += (logp.argmax(-1) == targets).float().mean()
+        acc3[2] += 1.0
+    return loss, dl
+
+
+class _FusedLossFn(torch.autograd.Function):
+    """Autograd face of the fused loss kernels for callers outside the engine: forward keeps the gradient the kernel produced."""
+
+    @staticmethod
+    def forward(ctx, x, target, which):
+        if which == "nll":
+            loss, d = nll_loss(x, target, need_grad=True)
+        else:
+            loss, d = regression_loss(x, target, which, need_grad=True)
+        ctx.save_for_backward(d)
+        return loss.to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, g):
+        (d,) = ctx.saved_tensors
+        return d * g.to(d.dtype), None, None
+
+
 def argmax_accuracy(logits: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
     if use_native(logits, targets) and logits.dim() == 2:
         out = torch.empty((), dtype=torch.float32, device=logits.device)
@@ -523,6 +610,60 @@ def layer_norm(x, gamma, beta, eps: float = 1e-12, residual=None):
         return _LayerNormFn.apply(x, residual, gamma, beta, eps, None, None)
     h = x if residual is None else x + residual
     return TF.layer_norm(h.float(), (H,), gamma.float(), beta.float(), eps).to(x.dtype)
+
+
+class _RMSNormFn(torch.autograd.Function):
+    """RMSNorm(x [+ residual]) * gamma (csrc/rmsnorm.cu); saves the pre-norm sum and rstd, one-pass backward."""
+
+    @staticmethod
+    def forward(ctx, x, residual, gamma, eps, gparam):
+        shape = x.shape
+        H = shape[-1]
+        x2 = x.contiguous().view(-1, H)
+        T = x2.shape[0]
+        r2 = residual.contiguous().view(-1, H) if residual is not None else None
+        y = torch.empty_like(x2)
+        hsum = torch.empty_like(x2) if r2 is not None else None
+        rstd = torch.empty(T, dtype=torch.float32, device=x.device)
+        check(_lib.lib().mlt_rmsnorm_fwd(ptr(x2), ptr(r2), ptr(gamma), _c_int(int(gamma.dtype == torch.bfloat16)), ptr(y), ptr(hsum),
+                                         ptr(rstd), _c_int(T), _c_int(H), ctypes.c_float(eps), stream_handle()), "mlt_rmsnorm_fwd")
+        launches.bump("rmsnorm_fwd")
+        ctx.save_for_backward(hsum if hsum is not None else x2, rstd, gamma)
+        ctx.shape, ctx.has_res, ctx.gparam, ctx.gdtype = shape, r2 is not None, gparam, gamma.dtype
+        return y.view(shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        h, rstd, gamma = ctx.saved_tensors
+        gparam = ctx.gparam
+        T, H = h.shape
+        dy2 = dy.contiguous().view(T, H)
+        dx = torch.empty_like(h)
+        gsink = _sink(gparam)
+        gdt = gsink.dtype if gsink is not None else ctx.gdtype
+        dg = gsink if gsink is not None else torch.empty(H, dtype=gdt, device=h.device)
+        L = _lib.lib()
+        L.mlt_rmsnorm_bwd_scratch_bytes.restype = _c_ll
+        ws = scratch(h.device, "rms_bwd", L.mlt_rmsnorm_bwd_scratch_bytes())
+        check(L.mlt_rmsnorm_bwd(ptr(dy2), ptr(h), ptr(rstd), ptr(gamma), _c_int(int(gamma.dtype == torch.bfloat16)), ptr(dx), ptr(dg),
+                                _c_int(int(gdt == torch.bfloat16)), ptr(ws), _c_ll(ws.numel()), _c_int(T), _c_int(H), stream_handle()),
+              "mlt_rmsnorm_bwd")
+        launches.bump("rmsnorm_bwd")
+        dxv = dx.view(ctx.shape)
+        return dxv, (dxv if ctx.has_res else None), _deliver(gparam, dg, gsink), None, None
+
+
+def rms_norm(x, gamma, eps: float = 1e-6, residual=None):
+    """``RMSNorm(x [+ residual]) * gamma`` over the last dimension (what ``torch.nn.RMSNorm`` computes)."""
+    H = x.shape[-1]
+    if (use_native(x, gamma) and x.dtype == torch.bfloat16 and H % 8 == 0 and 8 <= H <= 8192
+            and gamma.dtype in (torch.bfloat16, torch.float32) and x.numel() > 0):
+        if _has_sink(gamma):
+            return _RMSNormFn.apply(x, residual, gamma.detach(), eps, gamma)
+        return _RMSNormFn.apply(x, residual, gamma, eps, None)
+    h = x if residual is None else x + residual
+    hf = h.float()
+    return (hf * torch.rsqrt(hf.pow(2).mean(-1, keepdim=True) + eps) * gamma.float()).to(x.dtype)
 
 
 class _AttentionFn(torch.autograd.Function):

@@ -210,6 +210,13 @@ class FusedOptimizer(torch.optim.Optimizer):
         g = self.param_groups[0]
         b1 = float(g["momentum"] if self.kind == "sgd" else g["betas"][0])
         b2 = float(g["betas"][1])
+        if lrs is None and self.kind in ("sgd", "adagrad"):
+            # these rules read no bias corrections: every row of the epoch is the same eight numbers
+            key = (n, float(g["lr"]), float(g["weight_decay"]), b1, b2, float(g["eps"]), float(grad_scale))
+            if getattr(self, "_rows_key", None) != key:
+                row = torch.tensor([key[1], key[2], b1, b2, key[5], 1.0 - b1, (1.0 - b2) ** 0.5, key[6]], dtype=torch.float32)
+                self._rows_cache, self._rows_key = row.repeat(n, 1).contiguous(), key
+            return self._rows_cache
         steps = np.arange(self.step_count + 1, self.step_count + n + 1, dtype=np.float64)
         rows = np.empty((n, 8), dtype=np.float64)
         rows[:, 0] = float(g["lr"]) if lrs is None else np.asarray(lrs, dtype=np.float64)

@@ -112,6 +112,7 @@ class SymmArena:
 class P2PComm(Comm):
     name = "p2p"
     fused = True
+    _instances = 0          # communicators built so far in this process (same count on every rank: part of the arena's name)
 
     def __init__(self, device: torch.device, oneshot_max_bytes: Optional[int] = None, algo: str = "auto"):
         self.device = device
@@ -123,6 +124,8 @@ class P2PComm(Comm):
         self.algo = algo
         self.oneshot_max = int(oneshot_max_bytes or os.environ.get("MLT_ONESHOT_MAX_BYTES", 1 << 20))
         self.cpu_group = dist.new_group(backend="gloo")      # host-side phases of the bootstrap only
+        P2PComm._instances += 1
+        self._serial = P2PComm._instances
         self.arena: Optional[SymmArena] = None
         self._heap = 0
         self._vals = None
@@ -147,7 +150,7 @@ class P2PComm(Comm):
         self.recv_off = flags + scalars
         self.heap_off = self._heap = _align(self.recv_off + recv, 4096)
         total = self.heap_off + _align(heap, 1 << 21)
-        tag = os.environ.get("MLT_JOB_TAG") or f"{os.environ.get('MASTER_PORT', '0')}-{os.getppid()}"
+        tag = (os.environ.get("MLT_JOB_TAG") or f"{os.environ.get('MASTER_PORT', '0')}-{os.getppid()}") + f"-{self._serial}"
         tags = [None] * self.world_size
         dist.all_gather_object(tags, tag if self.rank == 0 else None, group=self.cpu_group)
         tag = tags[0]

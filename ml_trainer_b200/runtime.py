@@ -124,6 +124,18 @@ class NativeLoop:
         y = torch.as_tensor(_DevMem(yp, yb, self), device=self.device).view(y_dtype).view(y_shape)
         return x, y
 
+    def set_augment(self, aug, out: Optional[torch.Tensor] = None, pos0: int = 0, train: bool = True):
+        """uint8 image rows: every step first runs the augmentation kernel from the slot's rows into ``out``."""
+        if aug is None:
+            if getattr(self, "_aug_set", False):
+                self.L.mlt_loop_set_augment(self.h, None, None, _c_int(0), ctypes.c_ulonglong(0), _c_int(0))
+                self._aug_set = False
+            return
+        self._aug_keep = (aug, out)
+        self.L.mlt_loop_set_augment(self.h, ctypes.byref(aug.cfg), _c_vp(out.data_ptr()), _c_int(int(out.dtype == torch.bfloat16)),
+                                    ctypes.c_ulonglong(int(pos0)), _c_int(int(train)))
+        self._aug_set = True
+
     def set_direct_rows(self, on: bool):
         self.L.mlt_loop_set_direct_rows(self.h, _c_int(int(on)))
 

@@ -175,18 +175,12 @@ class Trainer:
 
     def _get_criterion(self):
         kind = self.criterion_type
-        if kind == "cross_entropy":
-            from .ops.modules import CrossEntropyLoss
+        from .ops import modules as M_
 
-            return CrossEntropyLoss()
-        if kind == "neg-loss":
-            return torch.nn.NLLLoss()
-        if kind == "l1":
-            return torch.nn.L1Loss()
-        if kind == "l2":
-            return torch.nn.MSELoss()
-        if kind == "custom":
-            return custom_loss_function
+        table = {"cross_entropy": M_.CrossEntropyLoss, "neg-loss": M_.NLLLoss, "l1": M_.L1Loss, "l2": M_.MSELoss,
+                 "custom": M_.CustomLoss}      # every criterion: loss + gradient + metric from one kernel (csrc/loss.cu)
+        if kind in table:
+            return table[kind]()
         raise ValueError(f"unknown criterion {kind!r}; expected one of {CRITERIA}")
 
     def _get_scheduler(self):
@@ -239,7 +233,34 @@ class Trainer:
 
     # -------------------------------------------------------------------- loops
     def _feed(self, loader):
-        return PinnedPrefetcher(loader, self.device, slots=max(self.cfg.prefetch, 1))   # dtype casts happen in the step
+        aug = getattr(loader, "_augment", None)
+        if aug is None or self.device.type != "cuda":
+            return PinnedPrefetcher(loader, self.device, slots=max(self.cfg.prefetch, 1))   # dtype casts happen in the step
+        # uint8 image batches: upload as uint8, then crop / flip / normalise on the device (csrc/augment.cu)
+        loader._augment_on_device = True
+        feed = PinnedPrefetcher(loader, self.device, slots=max(self.cfg.prefetch, 1))
+        train = loader._augment_train
+
+        class _Augmented:
+            h2d_bytes = property(lambda s_: feed.h2d_bytes)
+
+            def __len__(s_):
+                return len(feed)
+
+            def __iter__(s_):
+                # a small ring of output buffers: stable addresses (captured CUDA graphs are keyed by them), and the
+                # previous batch may still be in use by the step that was launched with it
+                ring, k = [None] * (feed.slots + 1), 0
+                for x, y in feed:
+                    buf = ring[k]
+                    if buf is None or buf.shape[0] != x.shape[0]:
+                        buf = torch.empty((x.shape[0], *aug.out_shape), dtype=torch.float32, device=x.device)
+                        if x.shape[0] == loader.batch_size:
+                            ring[k] = buf
+                    yield aug.apply_cuda(x, out=buf, train=train), y
+                    k = (k + 1) % len(ring)
+
+        return _Augmented()
 
     def _bar(self, it, total):
         disable = (not self.cfg.progress) or self.rank != 0
@@ -261,14 +282,18 @@ class Trainer:
         if f is None or model is not self.model or not self.cfg.native_loop or not getattr(loader, "_fast", False):
             return False
         x, y = loader._backing[0], loader._backing[1]
-        return (x.dtype == torch.float32 and x.dim() == 4 and tuple(x.shape[1:]) == (3, 32, 32) and x.is_contiguous()
-                and y.dtype == torch.int64 and y.dim() == 1 and y.is_contiguous())
+        if not (y.dtype == torch.int64 and y.dim() == 1 and y.is_contiguous() and x.is_contiguous()):
+            return False
+        aug = getattr(loader, "_augment", None)
+        if aug is not None:                     # uint8 rows, augmented on the device into the step's [B, 3, 32, 32] input
+            return x.dtype == torch.uint8 and tuple(aug.out_shape) == (3, 32, 32)
+        return x.dtype == torch.float32 and x.dim() == 4 and tuple(x.shape[1:]) == (3, 32, 32)
 
     def _native_graph_ok(self, loader, model) -> bool:
         """Whole-epoch C++ execution of CUDA-graph steps: any model, in-memory tensor dataset, full batches."""
         eng = self.engine
         return (eng.fused is None and eng.use_graph and model is self.model and self.cfg.native_loop
-                and getattr(loader, "_fast", False) and self.device.type == "cuda"
+                and getattr(loader, "_fast", False) and self.device.type == "cuda" and getattr(loader, "_augment", None) is None
                 and all(t.is_contiguous() for t in loader._backing[:2]) and len(loader._backing) == 2)
 
     def _train_epoch_native_graph(self, epoch):
@@ -287,16 +312,8 @@ class Trainer:
             self._slot_views = [loop.slot_tensors(s, (B, *x_be.shape[1:]), x_be.dtype, (B, *y_be.shape[1:]), y_be.dtype)
                                 for s in range(loop.slots)]
             self._slot_views_key = id(loop)
-            row_bytes = x_be[0].numel() * x_be.element_size()
-            if row_bytes >= 32768 and x_be.numel() * x_be.element_size() <= (8 << 30):
-                try:                                   # page-lock the dataset once: samples then go device-ward by DMA
-                    if not x_be.is_pinned():
-                        rc = torch.cuda.cudart().cudaHostRegister(x_be.data_ptr(), x_be.numel() * x_be.element_size(), 0)
-                        if int(rc) != 0:
-                            raise RuntimeError(f"cudaHostRegister -> {rc}")
-                    loop.set_direct_rows(True)
-                except Exception:                      # registration refused (ulimit): keep the host gather
-                    loop.set_direct_rows(False)
+        # large samples (images): page-lock the dataset once, samples then go device-ward by DMA straight from it
+        loop.set_direct_rows(self._page_lock(x_be))
         pin_losses = torch.zeros(nb, dtype=torch.float32).pin_memory()
         step = 0
 
@@ -341,6 +358,40 @@ class Trainer:
         self.last_step_losses = pin_losses
         return nb
 
+    def _page_lock(self, x: torch.Tensor) -> bool:
+        """Page-lock an in-memory dataset tensor whose rows are large enough for per-sample DMA (>= 32 KB) so the executor can
+        copy samples device-ward without a host gather.  Registrations are remembered per tensor and undone in ``close()``:
+        memory that is freed while still registered poisons later CUDA calls."""
+        row_bytes = x[0].numel() * x.element_size()
+        nbytes = x.numel() * x.element_size()
+        if row_bytes < 32768 or nbytes > (8 << 30) or self.device.type != "cuda":
+            return False
+        if x.is_pinned():
+            return True
+        reg = self.__dict__.setdefault("_registered", {})
+        key = x.data_ptr()
+        if key in reg:
+            return True
+        try:
+            rc = torch.cuda.cudart().cudaHostRegister(key, nbytes, 0)
+            if int(rc) != 0:
+                raise RuntimeError(f"cudaHostRegister -> {rc}")
+        except Exception:                              # registration refused (ulimit -l): keep the host gather
+            return False
+        reg[key] = x                                   # keeps the tensor alive for as long as it is registered
+        return True
+
+    def _page_unlock_all(self):
+        reg = self.__dict__.get("_registered") or {}
+        if reg and torch.cuda.is_available():
+            torch.cuda.synchronize(self.device)
+            for ptr_ in list(reg):
+                try:
+                    torch.cuda.cudart().cudaHostUnregister(ptr_)
+                except Exception:
+                    pass
+        reg.clear()
+
     def _native_loop_for(self, loader):
         from .runtime import NativeLoop
 
@@ -351,7 +402,7 @@ class Trainer:
             self._nloop_key = key
         return self._nloop
 
-    def _run_native_epoch(self, loader, epoch, train: bool):
+    def _run_native_epoch(self, loader, epoch, train: bool, use_acc: bool = True):
         from .runtime import epoch_indices
 
         eng, opt = self.engine, self.optimizer
@@ -373,8 +424,18 @@ class Trainer:
         loop = self._native_loop_for(loader)
         x, y = loader._backing[0], loader._backing[1]
         B = loader.batch_size
+        aug = getattr(loader, "_augment", None)
+        if aug is not None:
+            if getattr(self, "_aug_out", None) is None or self._aug_out.shape[0] < B:
+                self._aug_out = torch.empty((B, *aug.out_shape), dtype=torch.float32, device=self.device)
+            is_train = train and loader._augment_train
+            loop.set_augment(aug, self._aug_out, aug.position, is_train)
+            if is_train:
+                aug.position += int(idx.numel())
+        else:
+            loop.set_augment(None)
         uniform = sizes[-1] == B and (len(sizes) < 2 or (min(sizes) == B and max(sizes) == B))
-        losses = loop.run_lenet(eng.fused, x, y, idx, B, None if uniform else sizes, hyper, train, eng.acc,
+        losses = loop.run_lenet(eng.fused, x, y, idx, B, None if uniform else sizes, hyper, train, eng.acc if use_acc else None,
                                 self.metric == "accuracy", eng._loss_buf)
         if train:
             self.last_step_losses = losses
@@ -382,21 +443,31 @@ class Trainer:
         return nb
 
     def _train_one_epoch(self, epoch):
-        self.model.train()
+        if not self.model.training:
+            self.model.train()
         if self.train_sampler is not None:
             self.train_sampler.set_epoch(epoch)
         eng = self.engine
-        eng.reset_accumulators()
         nb = len(self.train_loader)
         if self._native_ok(self.train_loader, self.model):
-            self._run_native_epoch(self.train_loader, epoch, train=True)
+            # every step's loss lands in pinned host memory anyway (the kernel stores it there), so without a metric the
+            # epoch mean needs no device accumulator: no zeroing kernel before the epoch, no read-back after it
+            use_acc = bool(self.metric)
+            if use_acc:
+                eng.reset_accumulators()
+            self._run_native_epoch(self.train_loader, epoch, train=True, use_acc=use_acc)
             if self.scheduler_type == "StepLR":
                 self.scheduler.step()
-            loss, metric = self._reduce_epoch(eng.accumulators())
+            if use_acc:
+                sums = eng.accumulators()
+            else:
+                sums = torch.tensor([float(self.last_step_losses.sum(dtype=torch.float64)), 0.0, float(nb)], dtype=torch.float32)
+            loss, metric = self._reduce_epoch(sums)
             self.train_losses.append(loss)
             if self.metric:
                 self.train_metrics.append(metric)
             return
+        eng.reset_accumulators()
         if self._native_graph_ok(self.train_loader, self.model):
             self._train_epoch_native_graph(epoch)
             if self.scheduler_type == "StepLR":
@@ -597,7 +668,18 @@ class Trainer:
 
     def close(self):
         self.reducer.remove()
+        if getattr(self, "_nloop", None) is not None:
+            self._nloop.close()
+            self._nloop = None
+            self._nloop_key = None
+        self._page_unlock_all()
         self.comm.close()
+
+    def __del__(self):  # best effort: never leave a freed dataset page-locked
+        try:
+            self._page_unlock_all()
+        except Exception:
+            pass
 
     def validate_kwargs(self, kwargs, allowed_kwargs, error_message="Keyword argument not understood:"):
         """Checks that all keyword arguments are in the set of allowed keys."""

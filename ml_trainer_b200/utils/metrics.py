@@ -38,7 +38,15 @@ def accuracy(outputs: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
 
 
 def mcrmse(outputs: torch.Tensor, targets: torch.Tensor) -> torch.Tensor:
-    """Mean column-wise RMSE."""
+    """Mean column-wise RMSE (reference src/trainer.py:160-163); one kernel on the GPU (csrc/loss.cu)."""
+    if outputs.is_cuda and outputs.dim() == 2 and outputs.shape == targets.shape and 0 < outputs.shape[1] <= 1024 \
+            and outputs.dtype in (torch.float32, torch.bfloat16) and targets.dtype in (torch.float32, torch.bfloat16):
+        from ..ops import functional as F
+
+        if F.native_available():
+            acc = torch.zeros(3, dtype=torch.float32, device=outputs.device)
+            F.regression_loss(outputs, targets, "l2", acc, True, need_grad=False)
+            return acc[1]
     colwise_mse = torch.mean(torch.square(targets.float() - outputs.float()), dim=0)
     return torch.mean(torch.sqrt(colwise_mse), dim=0)
 

@@ -24,11 +24,15 @@ def main():
     torch.manual_seed(32)
     t = Trainer(MLModel(), datasets=(tr, va), epochs=2, batch_size=32, is_parallel=True, save_history=True,
                 model_dir=out_dir, backend=backend, optimizer=optimizer, lr=0.01, progress=False, metric="accuracy",
-                comm_algo=os.environ.get("MLT_COMM_ALGO", "auto"))
+                comm_algo=os.environ.get("MLT_COMM_ALGO", "auto"), fused_step=os.environ.get("MLT_FUSED_STEP", "1") == "1")
     rank, world = dist.get_rank(), dist.get_world_size()
     assert t.batch_size == 32 // world
     assert len(t.train_loader.sampler) == 128 // world
+    from ml_trainer_b200.ops import _lib
+
+    _lib.launches.reset()
     t.fit()
+    launches = dict(_lib.launches.by_name)
     ours = {k: v.detach().cpu().clone() for k, v in t.model.state_dict().items()}
 
     # oracle: stock DDP + torch.optim on the same shards, same order (set_epoch like ours)
@@ -55,7 +59,8 @@ def main():
     gathered = [None] * world
     dist.all_gather_object(gathered, hist)
     if rank == 0:
-        torch.save({"ours": ours, "ddp": theirs, "hist": gathered, "world": world}, os.path.join(out_dir, "result.pt"))
+        torch.save({"ours": ours, "ddp": theirs, "hist": gathered, "world": world, "launches": launches},
+                   os.path.join(out_dir, "result.pt"))
     dist.barrier()
     t.close()
     dist.destroy_process_group()

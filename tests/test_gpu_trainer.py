@@ -92,3 +92,51 @@ def test_smoke_entry():
     import __graft_entry__ as g
 
     g.smoke()
+
+
+class _Twice(torch.nn.Module):
+    """One Linear applied twice per forward pass (and a second, single-use one): its gradient is the SUM of two uses."""
+
+    def __init__(self, d, out):
+        super().__init__()
+        self.shared = torch.nn.Linear(d, d)
+        self.head = torch.nn.Linear(d, out)
+
+    def forward(self, x):
+        x = x.flatten(1)
+        h = torch.tanh(self.shared(x))
+        h = torch.tanh(self.shared(h))
+        return self.head(h)
+
+
+@pytest.mark.parametrize("d,dtype", [(48, "fp32"), (512, "bf16")])       # CUDA-core linear path / tcgen05 GEMM path
+def test_parameter_used_twice_accumulates(tmp_path, d, dtype):
+    """native backward kernels WRITE weight gradients into the arena, so a reused parameter must accumulate over
+    its uses and report "ready" once, after the last.  Oracle: torch autograd on an fp32 copy."""
+    from ml_trainer_b200 import SyntheticDataset, Trainer
+
+    torch.manual_seed(5)
+    ref = _Twice(d, 10)
+    model = copy.deepcopy(ref)
+    B = 2048 if dtype == "bf16" else 32
+    data = SyntheticDataset((d,), 10, length=B, seed=9)
+    tr = Trainer(model, datasets=(data, data), epochs=1, batch_size=B, model_dir=str(tmp_path), progress=False, optimizer="sgd",
+                 lr=0.1, momentum=0.0, metric=None, graph=False, dtype=dtype, seed=32)
+    x, y = next(iter(tr.train_loader))
+    tr.engine.train_step(x.cuda(), y.cuda())
+    torch.cuda.synchronize()
+    ref = ref.cuda()
+    xr = x.cuda().float()
+    torch.nn.functional.cross_entropy(ref(xr), y.cuda()).backward()
+    g_ref = ref.shared.weight.grad
+    i = tr.optimizer.index_of[id(tr.model.shared.weight)]
+    g = tr.optimizer.grad_view(i).float()
+    tol = dict(rtol=2e-3, atol=2e-5) if dtype == "fp32" else dict(rtol=6e-2, atol=2e-2 * float(g_ref.abs().max()) + 1e-6)
+    assert torch.allclose(g, g_ref, **tol), float((g - g_ref).abs().max())
+    # and a single use would have produced a visibly different gradient (the test can tell the two apart)
+    gb = tr.optimizer.grad_view(tr.optimizer.index_of[id(tr.model.shared.bias)]).float()
+    assert torch.allclose(gb, ref.shared.bias.grad, **tol)
+    w_new = tr.optimizer.master_view(i)
+    with torch.no_grad():
+        w_exp = ref.shared.weight - 0.1 * g_ref
+    assert torch.allclose(w_new, w_exp, rtol=1e-2 if dtype == "bf16" else 1e-4, atol=1e-3 if dtype == "bf16" else 1e-5)

@@ -251,3 +251,50 @@ def test_sampler_order_reproduces_stock_samplers():
                 d = DistributedSampler(ds, num_replicas=4, rank=rank, shuffle=shuffle, drop_last=drop_last, seed=5)
                 d.set_epoch(3)
                 assert _sampler_order(d).tolist() == list(d), (shuffle, drop_last, rank)
+
+
+def test_device_augment_host_statement_matches_torch_ops():
+    """uint8 pipeline: the host statement of crop / flip / normalise equals pad + slice + flip + (x/255 - mean)/std, the draw of a
+    stream position is what the C library states (same Philox), and a Trainer trains from a U8ImageDataset on the CPU."""
+    import ctypes
+
+    import torch
+
+    from ml_trainer_b200 import DeviceAugment, Loader, MLModel, Trainer, U8ImageDataset
+    from ml_trainer_b200.ops import _lib
+    from ml_trainer_b200.utils.functions import CIFAR_MEAN, CIFAR_STD
+
+    aug = DeviceAugment((3, 32, 32), padding=4, seed=77)
+    L = _lib.lib_or_none()
+    if L is not None:
+        out = (ctypes.c_int * 3)()
+        for pos in (0, 1, 5, 123456, 2 ** 35 + 9):
+            assert L.mlt_augment_params(ctypes.byref(aug.cfg), ctypes.c_ulonglong(pos), out) == 0
+            assert tuple(out) == aug.params(pos)
+    draws = [aug.params(i) for i in range(4000)]
+    assert {d[0] for d in draws} == set(range(9)) and {d[1] for d in draws} == set(range(9)) and {d[2] for d in draws} == {0, 1}
+    assert 0.45 < sum(d[2] for d in draws) / len(draws) < 0.55
+    g = torch.Generator().manual_seed(0)
+    img = torch.randint(0, 256, (32, 32, 3), dtype=torch.uint8, generator=g)
+    for pos in range(6):
+        top, left, flip = aug.params(pos)
+        x = img.permute(2, 0, 1).float() / 255.0
+        x = torch.nn.functional.pad(x, (4, 4, 4, 4))[:, top:top + 32, left:left + 32]
+        if flip:
+            x = x.flip(-1)
+        want = (x - torch.tensor(CIFAR_MEAN).view(3, 1, 1)) / torch.tensor(CIFAR_STD).view(3, 1, 1)
+        assert torch.allclose(aug.apply_cpu(img, pos), want, atol=1e-6)
+    ev = aug.apply_cpu(img, None, train=False)
+    assert torch.allclose(ev, (img.permute(2, 0, 1).float() / 255.0 - torch.tensor(CIFAR_MEAN).view(3, 1, 1)) / torch.tensor(CIFAR_STD).view(3, 1, 1), atol=1e-6)
+    data = torch.randint(0, 256, (96, 32, 32, 3), dtype=torch.uint8, generator=g)
+    labels = torch.randint(0, 10, (96,), generator=g)
+    ds = U8ImageDataset(data, labels, augment=aug)
+    va = U8ImageDataset(data[:32], labels[:32], augment=aug, train=False)
+    ld = Loader(ds, batch_size=32, shuffle=False)
+    assert ld._fast and ld._augment is aug
+    xb, yb = next(iter(ld))
+    assert xb.shape == (32, 3, 32, 32) and xb.dtype == torch.float32 and torch.equal(yb, labels[:32])
+    import tempfile
+
+    h = Trainer(MLModel(), datasets=(ds, va), epochs=1, batch_size=32, progress=False, model_dir=tempfile.mkdtemp()).fit()
+    assert len(h["train_loss"]) == 1 and h["train_loss"][0] == h["train_loss"][0]
