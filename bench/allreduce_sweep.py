@@ -48,7 +48,8 @@ def med_time(fn, iters, warm=5):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--max-mb", type=float, default=256)
+    ap.add_argument("--max-mb", type=float, default=1024)
+    ap.add_argument("--step", type=int, default=2, help="ratio between consecutive sizes")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--out", default="gpurun_out/allreduce_sweep.json")
@@ -68,10 +69,10 @@ def main():
     b = 1024
     while b <= a.max_mb * 2 ** 20:
         sizes.append(b)
-        b *= 4
+        b *= a.step
     nmax = sizes[-1] // esz
     comm = P2PComm(dev, oneshot_max_bytes=4 << 20)
-    comm.prepare(nmax + 4096, gdt)
+    comm.prepare(nmax + 4096, gdt, n_states=1)
     p = torch.nn.Parameter(torch.zeros(nmax, device=dev))
     opt = FusedOptimizer([p], kind="sgd", lr=1e-3, momentum=0.9, compute_dtype=gdt, allocator=comm.alloc)
     opt.grad.normal_()
@@ -91,7 +92,14 @@ def main():
             if algo == "nvls" and not comm.arena.multicast:
                 continue
             comm.algo = algo
+            comm._oneshot_off.clear()            # every size is its own "bucket plan": start the receive-slot layout afresh
+            comm._oneshot_used = 0
             t = med_time(lambda: comm.allreduce_update(opt, 0, n), a.iters)
+            # values check: every replica holds bit-identical weights after the timed updates
+            parts = [torch.empty_like(opt.model[:n]) for _ in range(world)]
+            dist.all_gather(parts, opt.model[:n].contiguous())
+            row[f"{algo}_replicas_identical"] = all(torch.equal(parts[0], q) for q in parts[1:])
+            del parts
             row[f"{algo}_fused_us"] = round(t, 2)
             row[f"{algo}_busbw_GBs"] = round(2 * (world - 1) / world * n * esz / t / 1e3, 1)
         gs = g_nccl[:n]
@@ -115,8 +123,12 @@ def main():
             print(json.dumps(row), flush=True)
     if rank == 0:
         os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
+        # crossover points: the largest size up to which each variant is the fastest fused one (what pick_algo should use)
+        best = [(r["bytes"], min((r[k], k.split("_")[0]) for k in r if k.endswith("_fused_us"))[1]) for r in rows]
+        cross = {"oneshot_max_bytes": max([b for b, w in best if w == "oneshot"], default=0),
+                 "twoshot_max_bytes": max([b for b, w in best if w in ("oneshot", "twoshot")], default=0), "winners": best}
         with open(a.out, "w") as f:
-            json.dump({"world": world, "dtype": a.dtype, "multicast": bool(comm.arena.multicast), "rows": rows}, f, indent=1)
+            json.dump({"world": world, "dtype": a.dtype, "multicast": bool(comm.arena.multicast), "crossover": cross, "rows": rows}, f, indent=1)
     comm.check_errors()
     dist.barrier()
     comm.close()

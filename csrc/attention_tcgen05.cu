@@ -1,5 +1,7 @@
 // Fused multi-head attention on tcgen05: softmax(Q K^T / sqrt(d)) V and its backward without the [S, S]
-// score matrix ever touching HBM.  Head dim 64, sequence length a multiple of 128 up to 512 (BERT-base: 512), no mask.
+// score matrix ever touching HBM.  Head dim 64, sequence length a multiple of 64 up to 512 (BERT-base: 512), optional
+// key-padding mask as an additive per-key bias (HuggingFace's extended attention mask: 0 for real tokens, a large negative
+// number for padding), staged once per CTA in shared memory and added to the scaled scores in all three kernels.
 //
 // All three kernels share one shape: a CTA owns a 128-row tile (queries, or keys in the dK/dV kernel), walks the other
 // sequence axis in steps of 64 columns, and runs 320 threads, two CTAs per SM:
@@ -37,10 +39,10 @@ constexpr uint32_t kTmemCols = 256;
 constexpr float kLog2e = 1.4426950408889634f;
 // forward: Q | 3 x (K half, V half) | 2 x P | row-max exchange | barriers
 constexpr int kFwdStages = 3;
-constexpr int kSmemFwd = kTile + kFwdStages * 2 * kHalf + 2 * kTile + 2 * 2 * 128 * 4 + 256 + 1024;
+constexpr int kSmemFwd = kTile + kFwdStages * 2 * kHalf + 2 * kTile + 2 * 2 * 128 * 4 + kMaxS * 4 + 256 + 1024;
 // dQ: Q | dO | 3 x (K half, V half) | dS | barriers
 constexpr int kDqStages = 3;
-constexpr int kSmemDq = 2 * kTile + kDqStages * 2 * kHalf + kTile + 256 + 1024;
+constexpr int kSmemDq = 2 * kTile + kDqStages * 2 * kHalf + kTile + kMaxS * 4 + 256 + 1024;
 // dK/dV: K | V | 2 x (Q half, dO half) | P | dS | lse, delta | barriers
 constexpr int kDkvStages = 2;
 constexpr int kSmemDkv = 2 * kTile + kDkvStages * 2 * kHalf + 2 * kTile + 2 * kMaxS * 4 + 256 + 1024;
@@ -53,6 +55,7 @@ struct FaParams {
   long long row_stride;      // of out: H * 64
   float scale_log2;          // (1/sqrt(d)) * log2(e)
   float scale;
+  const float* kbias;        // [B, S] additive key bias in natural-log units (added to the scaled scores), or nullptr
 };
 
 struct FaBwdParams {
@@ -65,6 +68,7 @@ struct FaBwdParams {
   long long row_stride;       // of out / dout: H * 64
   long long ld_dqkv;          // row stride of dq, dk, dv (H * 64, or 3 * H * 64 when they are slices of one packed tensor)
   float scale_log2, scale;
+  const float* kbias;         // as in FaParams
 };
 
 // Optional per-CTA timeline (analysis only): 8 x int64 per CTA when a buffer has been installed.
@@ -117,6 +121,7 @@ __device__ __forceinline__ void store_out32(__nv_bfloat16* g, uint32_t taddr, fl
 }
 
 // ---- forward ------------------------------------------------------------------------------------------------------
+template <bool BIAS>
 __global__ void __launch_bounds__(fa::kThreads, 2)
 attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                              const __grid_constant__ CUtensorMap tmV, const FaParams p) {
@@ -127,7 +132,8 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
   uint8_t* sKV = sQ + kTile;                       // stage s: K half at s * 2 * kHalf, V half right after
   uint8_t* sP = sKV + kFwdStages * 2 * kHalf;      // 2 x [128 q x 64 keys]
   float* s_max = reinterpret_cast<float*>(sP + 2 * kTile);     // [2 buffers][2 halves][128 rows]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_max + 2 * 2 * 128);
+  float* s_kb = s_max + 2 * 2 * 128;                            // [S] key bias * log2(e)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_kb + kMaxS);
   uint64_t* q_full = bars;                         // 1
   uint64_t* kv_full = bars + 1;                    // kFwdStages
   uint64_t* kv_free = kv_full + kFwdStages;        // kFwdStages
@@ -220,6 +226,12 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
     const int quad = warp & 3, hf = (warp - 2) >> 2;
     const int row = quad * 32 + lane;                   // query row within the tile
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
+    if (BIAS) {                                         // key bias of this sample, pre-multiplied into the exp2 domain
+      for (int i = threadIdx.x - 64; i < p.S; i += kSoftmaxThreads) s_kb[i] = p.kbias[(size_t)b * p.S + i] * kLog2e;
+      softmax_bar();
+    }
+    // m is the running reference maximum: of the raw scores without a bias, of the scaled + biased exponents (log2 domain) with one
+    const float sl2 = p.scale_log2;
     float m = -INFINITY, l = 0.f;                       // l: this thread's half of the row sum
     for (int hs = 0; hs < NH; ++hs) {
       const int u = hs & 1;
@@ -230,6 +242,17 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
       tmem_ld_wait();
       tc_fence_before();
       warp_arrive(&s_free[u], lane);                          // score buffer may be overwritten by S_{hs+2}
+      if (BIAS) {
+        const float4* kb4 = reinterpret_cast<const float4*>(s_kb + hs * 64 + hf * 32);
+#pragma unroll
+        for (int i4 = 0; i4 < 8; ++i4) {
+          const float4 kb = kb4[i4];
+          r[i4 * 4] = __float_as_uint(fmaf(__uint_as_float(r[i4 * 4]), sl2, kb.x));
+          r[i4 * 4 + 1] = __float_as_uint(fmaf(__uint_as_float(r[i4 * 4 + 1]), sl2, kb.y));
+          r[i4 * 4 + 2] = __float_as_uint(fmaf(__uint_as_float(r[i4 * 4 + 2]), sl2, kb.z));
+          r[i4 * 4 + 3] = __float_as_uint(fmaf(__uint_as_float(r[i4 * 4 + 3]), sl2, kb.w));
+        }
+      }
       float mx0 = __uint_as_float(r[0]), mx1 = __uint_as_float(r[1]), mx2 = __uint_as_float(r[2]), mx3 = __uint_as_float(r[3]);
 #pragma unroll
       for (int i = 4; i < 32; i += 4) {
@@ -242,9 +265,10 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
       softmax_bar();
       const float mx = fmaxf(m, fmaxf(mine, xm[(hf ^ 1) * 128 + row]));
       // lazy rescale: keep the old reference max unless some row of this warp moved by more than 2^8
-      const bool grow = (mx - m) * p.scale_log2 > 8.0f;           // also true on the first step (m = -inf)
+      const float to_exp = BIAS ? 1.0f : sl2;                     // converts a difference of m's into the exp2 domain
+      const bool grow = (mx - m) * to_exp > 8.0f;                 // also true on the first step (m = -inf)
       if (__any_sync(0xffffffffu, grow)) {
-        const float alpha = fast_exp2((m - mx) * p.scale_log2);   // 0 on the first step
+        const float alpha = fast_exp2((m - mx) * to_exp);         // 0 on the first step
         l *= alpha;
         m = mx;
         if (hs > 0) {
@@ -259,15 +283,22 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
           tmem_st_wait();
         }
       }
-      const float off = -m * p.scale_log2;
+      const float off = -m * to_exp;
       float pv[32];
       float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
       for (int i = 0; i < 32; i += 4) {
-        pv[i] = fast_exp2(fmaf(__uint_as_float(r[i]), p.scale_log2, off));         s0 += pv[i];
-        pv[i + 1] = fast_exp2(fmaf(__uint_as_float(r[i + 1]), p.scale_log2, off)); s1 += pv[i + 1];
-        pv[i + 2] = fast_exp2(fmaf(__uint_as_float(r[i + 2]), p.scale_log2, off)); s2 += pv[i + 2];
-        pv[i + 3] = fast_exp2(fmaf(__uint_as_float(r[i + 3]), p.scale_log2, off)); s3 += pv[i + 3];
+        if (BIAS) {
+          pv[i] = fast_exp2(__uint_as_float(r[i]) + off);         s0 += pv[i];
+          pv[i + 1] = fast_exp2(__uint_as_float(r[i + 1]) + off); s1 += pv[i + 1];
+          pv[i + 2] = fast_exp2(__uint_as_float(r[i + 2]) + off); s2 += pv[i + 2];
+          pv[i + 3] = fast_exp2(__uint_as_float(r[i + 3]) + off); s3 += pv[i + 3];
+        } else {
+          pv[i] = fast_exp2(fmaf(__uint_as_float(r[i]), sl2, off));         s0 += pv[i];
+          pv[i + 1] = fast_exp2(fmaf(__uint_as_float(r[i + 1]), sl2, off)); s1 += pv[i + 1];
+          pv[i + 2] = fast_exp2(fmaf(__uint_as_float(r[i + 2]), sl2, off)); s2 += pv[i + 2];
+          pv[i + 3] = fast_exp2(fmaf(__uint_as_float(r[i + 3]), sl2, off)); s3 += pv[i + 3];
+        }
       }
       l += (s0 + s1) + (s2 + s3);
       mbar_wait(&p_free[u], ((hs >> 1) & 1) ^ 1);       // PV of step hs-2 no longer reads this P buffer
@@ -287,9 +318,12 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
     mbar_wait(o_done, 0);
     tc_fence_after();
     const int srow = qt * 128 + row;
-    __nv_bfloat16* orow = p.out + ((size_t)b * p.S + srow) * p.row_stride + (size_t)h * 64 + hf * 32;
-    store_out32(orow, tmem + lane_base + kColO + hf * 32, 1.0f / lt);
-    if (hf == 0 && p.lse != nullptr) p.lse[((size_t)b * p.H + h) * p.S + srow] = m * p.scale + logf(lt);
+    if (srow < p.S) {                                   // S % 128 == 64: the last tile's upper half is padding (TMA zero fill)
+      __nv_bfloat16* orow = p.out + ((size_t)b * p.S + srow) * p.row_stride + (size_t)h * 64 + hf * 32;
+      store_out32(orow, tmem + lane_base + kColO + hf * 32, 1.0f / lt);
+      if (hf == 0 && p.lse != nullptr)
+        p.lse[((size_t)b * p.H + h) * p.S + srow] = (BIAS ? m * (1.0f / kLog2e) : m * p.scale) + logf(lt);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -328,6 +362,7 @@ __global__ void __launch_bounds__(256) attention_delta_kernel(const FaBwdParams 
   }
 }
 
+template <bool BIAS>
 __global__ void __launch_bounds__(fa::kThreads, 2)
 attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                         const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
@@ -339,7 +374,8 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
   uint8_t* sdO = sQ + kTile;
   uint8_t* sKV = sdO + kTile;                      // stage s: K half, V half
   uint8_t* sdS = sKV + kDqStages * 2 * kHalf;      // [128 q x 64 keys]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sdS + kTile);
+  float* s_kb = reinterpret_cast<float*>(sdS + kTile);          // [S] key bias * log2(e)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_kb + kMaxS);
   uint64_t* q_full = bars;                         // 1 (Q and dO)
   uint64_t* kv_full = bars + 1;                    // kDqStages
   uint64_t* kv_free = kv_full + kDqStages;         // kDqStages
@@ -436,10 +472,15 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     const int row = quad * 32 + lane;
     const uint32_t lane_base = (uint32_t)(quad * 32) << 16;
     const int srow = qt * 128 + row;
-    const size_t soff = ((size_t)b * p.H + h) * p.S + srow;
-    const float lse2 = p.lse[soff] * kLog2e;
-    const float dsc = p.delta[soff] * p.scale;
+    const bool live = srow < p.S;                       // S % 128 == 64: rows past the end are padding
+    const size_t soff = ((size_t)b * p.H + h) * p.S + (live ? srow : 0);
+    const float lse2 = live ? p.lse[soff] * kLog2e : 0.f;
+    const float dsc = live ? p.delta[soff] * p.scale : 0.f;
     uint8_t* drow = sdS + row * 128;
+    if (BIAS) {
+      for (int i = threadIdx.x - 64; i < p.S; i += kSoftmaxThreads) s_kb[i] = p.kbias[(size_t)b * p.S + i] * kLog2e;
+      softmax_bar();
+    }
     for (int hs = 0; hs < NH; ++hs) {
       mbar_wait(st_full, hs & 1);
       if (threadIdx.x == 64 && hs == 0) FA_DBG(4);
@@ -451,10 +492,25 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
       tc_fence_before();
       warp_arrive(st_free, lane);
       float ds[32];
+      if (BIAS) {
+        const float4* kb4 = reinterpret_cast<const float4*>(s_kb + hs * 64 + hf * 32);
 #pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        const float pr = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse2));
-        ds[i] = pr * fmaf(__uint_as_float(rp[i]), p.scale, -dsc);
+        for (int i4 = 0; i4 < 8; ++i4) {
+          const float4 kq = kb4[i4];
+          const float kv4[4] = {kq.x, kq.y, kq.z, kq.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int i = i4 * 4 + e;
+            const float pr = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, kv4[e] - lse2));
+            ds[i] = pr * fmaf(__uint_as_float(rp[i]), p.scale, -dsc);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float pr = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse2));
+          ds[i] = pr * fmaf(__uint_as_float(rp[i]), p.scale, -dsc);
+        }
       }
       mbar_wait(ds_free, (hs & 1) ^ 1);
 #pragma unroll
@@ -466,7 +522,8 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     mbar_wait(done, 0);
     if (threadIdx.x == 64) FA_DBG(6);
     tc_fence_after();
-    store_out32(p.dq + ((size_t)b * p.S + srow) * p.ld_dqkv + (size_t)h * 64 + hf * 32, tmem + lane_base + kColOut + hf * 32, 1.0f);
+    if (live)
+      store_out32(p.dq + ((size_t)b * p.S + srow) * p.ld_dqkv + (size_t)h * 64 + hf * 32, tmem + lane_base + kColOut + hf * 32, 1.0f);
     if (threadIdx.x == 64) FA_DBG(3);
   }
   tc_fence_before();
@@ -475,6 +532,7 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
   if (threadIdx.x == 32) FA_DBG(7);
 }
 
+template <bool BIAS>
 __global__ void __launch_bounds__(fa::kThreads, 2)
 attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                           const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
@@ -593,6 +651,10 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     softmax_bar();
     uint8_t* prow = sP + row * 128;
     uint8_t* drow = sdS + row * 128;
+    const int krow = kt * 128 + row;                          // this thread's key
+    const bool live = krow < p.S;
+    // rows are keys here: the key bias is one number per thread (a padded-out key row gets a bias that zeroes its P)
+    const float kb = live ? (BIAS ? p.kbias[(size_t)b * p.S + krow] * kLog2e : 0.f) : -3.0e4f;
     for (int hs = 0; hs < NH; ++hs) {
       mbar_wait(st_full, hs & 1);
       tc_fence_after();
@@ -612,7 +674,7 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int i = i4 * 4 + e;
-          pr[i] = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lv[e]));
+          pr[i] = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, kb - lv[e]));
           ds[i] = pr[i] * fmaf(__uint_as_float(rp[i]), p.scale, -dv[e]);
         }
       }
@@ -627,9 +689,11 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     }
     mbar_wait(done, 0);
     tc_fence_after();
-    const size_t goff = ((size_t)b * p.S + kt * 128 + row) * p.ld_dqkv + (size_t)h * 64 + hf * 32;
-    store_out32(p.dv + goff, tmem + lane_base + kColdV + hf * 32, 1.0f);
-    store_out32(p.dk + goff, tmem + lane_base + kColdK + hf * 32, 1.0f);
+    if (live) {
+      const size_t goff = ((size_t)b * p.S + krow) * p.ld_dqkv + (size_t)h * 64 + hf * 32;
+      store_out32(p.dv + goff, tmem + lane_base + kColdV + hf * 32, 1.0f);
+      store_out32(p.dk + goff, tmem + lane_base + kColdK + hf * 32, 1.0f);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -670,9 +734,12 @@ static int fa_set_attrs() {
   int dev = 0;
   MLT_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemFwd));
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dq_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDq));
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dkdv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDkv));
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemFwd));
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemFwd));
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDq));
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDq));
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dkdv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDkv));
+    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dkdv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDkv));
     attr_set[dev & 63] = true;
   }
   return 0;
@@ -690,11 +757,12 @@ extern "C" int mlt_attention_set_debug(void* buf) {
 }
 
 // q, k, v: [B, S, H*64] bf16 with row stride ld_qkv (0 = H*64; 3*H*64 for slices of a packed QKV projection);
-// out: [B, S, H*64] bf16;  lse: [B, H, S] fp32 or NULL.
-extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, long long ld_qkv, void* out, void* lse, int B, int S,
-                                 int H, int D, void* stream) {
+// out: [B, S, H*64] bf16;  lse: [B, H, S] fp32 or NULL.  key_bias: NULL, or [B, S] fp32 added to every score of that key after
+// the 1/sqrt(d) scaling (HuggingFace's extended attention mask: 0 for tokens, a large negative number for padding).
+extern "C" int mlt_attention_fwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, void* out,
+                                        void* lse, int B, int S, int H, int D, void* stream) {
   MLT_REQUIRE(D == 64, "mlt_attention_fwd: head dim %d unsupported (64)", D);
-  MLT_REQUIRE(S % 128 == 0 && S >= 128 && S <= fa::kMaxS, "mlt_attention_fwd: sequence length %d unsupported (128..512, multiple of 128)", S);
+  MLT_REQUIRE(S % 64 == 0 && S >= 64 && S <= fa::kMaxS, "mlt_attention_fwd: sequence length %d unsupported (64..512, multiple of 64)", S);
   MLT_REQUIRE(((uintptr_t)q % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0 && ((uintptr_t)out % 16) == 0,
               "mlt_attention_fwd: unaligned tensors");
   const long long rs = (long long)H * D;
@@ -706,20 +774,27 @@ extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, lo
   p.out = (__nv_bfloat16*)out; p.lse = (float*)lse; p.S = S; p.H = H; p.row_stride = rs;
   p.scale = 1.0f / sqrtf((float)D);
   p.scale_log2 = p.scale * fa::kLog2e;
+  p.kbias = (const float*)key_bias;
   if (fa_set_attrs()) return 1;
-  dim3 grid(S / 128, H, B);
-  attention_fwd_tcgen05_kernel<<<grid, fa::kThreads, fa::kSmemFwd, (cudaStream_t)stream>>>(tq, tk, tv, p);
+  dim3 grid((S + 127) / 128, H, B);
+  if (key_bias) attention_fwd_tcgen05_kernel<true><<<grid, fa::kThreads, fa::kSmemFwd, (cudaStream_t)stream>>>(tq, tk, tv, p);
+  else attention_fwd_tcgen05_kernel<false><<<grid, fa::kThreads, fa::kSmemFwd, (cudaStream_t)stream>>>(tq, tk, tv, p);
   MLT_LAUNCH_CHECK();
   return 0;
 }
 
-// Backward of mlt_attention_fwd.  out / lse are the forward's results, dout the gradient of out; delta is a [B, H, S] fp32
-// scratch the call fills.  dq, dk, dv: [B, S, H*64] bf16 with row stride ld_dqkv (0 = H*64).
-extern "C" int mlt_attention_bwd(const void* q, const void* k, const void* v, long long ld_qkv, const void* out, const void* dout,
-                                 const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B, int S, int H,
-                                 int D, void* stream) {
+extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, long long ld_qkv, void* out, void* lse, int B, int S,
+                                 int H, int D, void* stream) {
+  return mlt_attention_fwd_masked(q, k, v, ld_qkv, nullptr, out, lse, B, S, H, D, stream);
+}
+
+// Backward of mlt_attention_fwd[_masked].  out / lse are the forward's results, dout the gradient of out; delta is a [B, H, S] fp32
+// scratch the call fills.  dq, dk, dv: [B, S, H*64] bf16 with row stride ld_dqkv (0 = H*64).  key_bias as in the forward.
+extern "C" int mlt_attention_bwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias,
+                                        const void* out, const void* dout, const void* lse, void* delta, void* dq, void* dk, void* dv,
+                                        long long ld_dqkv, int B, int S, int H, int D, void* stream) {
   MLT_REQUIRE(D == 64, "mlt_attention_bwd: head dim %d unsupported (64)", D);
-  MLT_REQUIRE(S % 128 == 0 && S >= 128 && S <= fa::kMaxS, "mlt_attention_bwd: sequence length %d unsupported (128..512, multiple of 128)", S);
+  MLT_REQUIRE(S % 64 == 0 && S >= 64 && S <= fa::kMaxS, "mlt_attention_bwd: sequence length %d unsupported (64..512, multiple of 64)", S);
   const void* al[] = {q, k, v, out, dout, dq, dk, dv};
   for (const void* a : al) MLT_REQUIRE(((uintptr_t)a % 16) == 0, "mlt_attention_bwd: unaligned tensors");
   const long long rs = (long long)H * D;
@@ -735,15 +810,28 @@ extern "C" int mlt_attention_bwd(const void* q, const void* k, const void* v, lo
   p.B = B; p.S = S; p.H = H; p.row_stride = rs; p.ld_dqkv = ldd;
   p.scale = 1.0f / sqrtf((float)D);
   p.scale_log2 = p.scale * fa::kLog2e;
+  p.kbias = (const float*)key_bias;
   if (fa_set_attrs()) return 1;
   cudaStream_t st = (cudaStream_t)stream;
   const long long dthreads = (long long)B * S * H * 8;
   attention_delta_kernel<<<(unsigned)((dthreads + 255) / 256), 256, 0, st>>>(p);
   MLT_LAUNCH_CHECK();
-  dim3 grid(S / 128, H, B);
-  attention_bwd_dq_kernel<<<grid, fa::kThreads, fa::kSmemDq, st>>>(tq, tk64, tv64, tdo, p);
-  MLT_LAUNCH_CHECK();
-  attention_bwd_dkdv_kernel<<<grid, fa::kThreads, fa::kSmemDkv, st>>>(tq64, tk, tv, tdo64, p);
+  dim3 grid((S + 127) / 128, H, B);
+  if (key_bias) {
+    attention_bwd_dq_kernel<true><<<grid, fa::kThreads, fa::kSmemDq, st>>>(tq, tk64, tv64, tdo, p);
+    MLT_LAUNCH_CHECK();
+    attention_bwd_dkdv_kernel<true><<<grid, fa::kThreads, fa::kSmemDkv, st>>>(tq64, tk, tv, tdo64, p);
+  } else {
+    attention_bwd_dq_kernel<false><<<grid, fa::kThreads, fa::kSmemDq, st>>>(tq, tk64, tv64, tdo, p);
+    MLT_LAUNCH_CHECK();
+    attention_bwd_dkdv_kernel<false><<<grid, fa::kThreads, fa::kSmemDkv, st>>>(tq64, tk, tv, tdo64, p);
+  }
   MLT_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int mlt_attention_bwd(const void* q, const void* k, const void* v, long long ld_qkv, const void* out, const void* dout,
+                                 const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B, int S, int H,
+                                 int D, void* stream) {
+  return mlt_attention_bwd_masked(q, k, v, ld_qkv, nullptr, out, dout, lse, delta, dq, dk, dv, ld_dqkv, B, S, H, D, stream);
 }

@@ -249,6 +249,13 @@ int mlt_attention_bwd(const void* q, const void* k, const void* v, long long ld_
                       const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B, int S, int H, int D,
                       void* stream);
 /* Analysis hook: device buffer of 8 int64 per CTA that the dQ kernel fills with %globaltimer stamps (NULL clears it). */
+/* The same with a key-padding mask: key_bias [B, S] fp32 (NULL = none) is added to every score of that key after the 1/sqrt(d)
+ * scaling - HuggingFace's extended attention mask (0 for tokens, a large negative number for padding).  S: multiple of 64, <= 512. */
+int mlt_attention_fwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, void* out, void* lse,
+                             int B, int S, int H, int D, void* stream);
+int mlt_attention_bwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, const void* out,
+                             const void* dout, const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B,
+                             int S, int H, int D, void* stream);
 int mlt_attention_set_debug(void* buf);
 /* Implicit-GEMM convolution on tcgen05 for NHWC bf16 tensors with Cin a multiple of 64: the patch matrix is never written,
  * operand tiles are gathered by TMA im2col loads.  w2 / dw: [Co, KH*KW*Cin]. */

@@ -729,10 +729,30 @@ def _qkv_ld(q, k, v):
     return ld if ld % 8 == 0 and ld >= HD else None
 
 
-def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False):
+def _key_bias(key_bias, B, S, device):
+    """``[B, S]`` fp32 contiguous additive key bias (HF's extended mask ``[B, 1, 1, S]`` is accepted), or None."""
+    if key_bias is None:
+        return None
+    if getattr(key_bias, "_mlt_key_bias", False):        # prepared once per forward pass by the model (prepare_key_bias)
+        return key_bias
+    kb = key_bias.reshape(B, S) if key_bias.numel() == B * S else key_bias.expand(B, 1, 1, S).reshape(B, S)
+    kb = kb.to(device=device, dtype=torch.float32).clamp_min(-30000.0)       # finfo.min would overflow the exp2-domain arithmetic
+    return kb.contiguous()
+
+
+def prepare_key_bias(attention_mask: torch.Tensor) -> torch.Tensor:
+    """HuggingFace-style ``attention_mask`` [B, S] (1 = token, 0 = padding) -> the additive key bias the attention kernels take,
+    prepared once per forward pass (every layer reuses it)."""
+    kb = ((1.0 - attention_mask.float()) * -30000.0).contiguous()
+    kb._mlt_key_bias = True
+    return kb
+
+
+def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False, key_bias=None):
     """Fused tcgen05 attention forward (csrc/attention_tcgen05.cu).  Returns ``out`` or ``(out, lse)``.
 
-    q, k, v may be column slices of one packed ``[B, S, 3*H*d]`` projection (no copy is made)."""
+    q, k, v may be column slices of one packed ``[B, S, 3*H*d]`` projection (no copy is made).  ``key_bias``: optional
+    ``[B, S]`` additive bias per key (0 for tokens, a large negative number for padding), added after the 1/sqrt(d) scaling."""
     B, S, HD = q.shape
     ld = _qkv_ld(q, k, v)
     if ld is None:
@@ -740,21 +760,21 @@ def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False):
         ld = HD
     out = torch.empty((B, S, HD), dtype=q.dtype, device=q.device)
     lse = torch.empty((B, heads, S), dtype=torch.float32, device=q.device) if want_lse else None
-    check(_lib.lib().mlt_attention_fwd(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(out), ptr(lse), _c_int(B), _c_int(S), _c_int(heads),
-                                       _c_int(HD // heads), stream_handle()), "mlt_attention_fwd")
+    check(_lib.lib().mlt_attention_fwd_masked(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(key_bias), ptr(out), ptr(lse), _c_int(B), _c_int(S),
+                                              _c_int(heads), _c_int(HD // heads), stream_handle()), "mlt_attention_fwd")
     launches.bump("attention_fwd_tcgen05")
     return (out, lse) if want_lse else out
 
 
-def _attention_bwd(q, k, v, out, lse, do, heads, dq, dk, dv):
+def _attention_bwd(q, k, v, out, lse, do, heads, dq, dk, dv, key_bias=None):
     B, S, HD = q.shape
     ld = _qkv_ld(q, k, v)
     ldd = _qkv_ld(dq, dk, dv)
     assert ld is not None and ldd is not None
     delta = torch.empty_like(lse)
-    check(_lib.lib().mlt_attention_bwd(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(out), ptr(do), ptr(lse), ptr(delta), ptr(dq), ptr(dk),
-                                       ptr(dv), _c_ll(ldd), _c_int(B), _c_int(S), _c_int(heads), _c_int(HD // heads), stream_handle()),
-          "mlt_attention_bwd")
+    check(_lib.lib().mlt_attention_bwd_masked(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(key_bias), ptr(out), ptr(do), ptr(lse), ptr(delta),
+                                              ptr(dq), ptr(dk), ptr(dv), _c_ll(ldd), _c_int(B), _c_int(S), _c_int(heads),
+                                              _c_int(HD // heads), stream_handle()), "mlt_attention_bwd")
     launches.bump("attention_bwd_tcgen05", 3)
 
 
@@ -763,19 +783,19 @@ class _FusedAttentionFn(torch.autograd.Function):
     (csrc/attention_tcgen05.cu: delta, dQ and dK/dV kernels, no atomics)."""
 
     @staticmethod
-    def forward(ctx, q, k, v, heads):
+    def forward(ctx, q, k, v, heads, key_bias=None):
         q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
-        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True)
+        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True, key_bias=key_bias)
         ctx.save_for_backward(q, k, v, out, lse)
-        ctx.heads = heads
+        ctx.heads, ctx.key_bias = heads, key_bias
         return out
 
     @staticmethod
     def backward(ctx, do):
         q, k, v, out, lse = ctx.saved_tensors
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
-        _attention_bwd(q, k, v, out, lse, do.contiguous(), ctx.heads, dq, dk, dv)
-        return dq, dk, dv, None
+        _attention_bwd(q, k, v, out, lse, do.contiguous(), ctx.heads, dq, dk, dv, ctx.key_bias)
+        return dq, dk, dv, None, None
 
 
 class _PackedAttentionFn(torch.autograd.Function):
@@ -783,12 +803,12 @@ class _PackedAttentionFn(torch.autograd.Function):
     written straight into one packed gradient, so neither direction needs a split or a concat."""
 
     @staticmethod
-    def forward(ctx, qkv, heads):
+    def forward(ctx, qkv, heads, key_bias=None):
         HD = qkv.shape[-1] // 3
         q, k, v = qkv[..., :HD], qkv[..., HD:2 * HD], qkv[..., 2 * HD:]
-        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True)
+        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True, key_bias=key_bias)
         ctx.save_for_backward(qkv, out, lse)
-        ctx.heads = heads
+        ctx.heads, ctx.key_bias = heads, key_bias
         return out
 
     @staticmethod
@@ -797,38 +817,44 @@ class _PackedAttentionFn(torch.autograd.Function):
         HD = qkv.shape[-1] // 3
         dqkv = torch.empty_like(qkv)
         _attention_bwd(qkv[..., :HD], qkv[..., HD:2 * HD], qkv[..., 2 * HD:], out, lse, do.contiguous(), ctx.heads,
-                       dqkv[..., :HD], dqkv[..., HD:2 * HD], dqkv[..., 2 * HD:])
-        return dqkv, None
+                       dqkv[..., :HD], dqkv[..., HD:2 * HD], dqkv[..., 2 * HD:], ctx.key_bias)
+        return dqkv, None, None
 
 
-def attention_packed(qkv, heads: int):
+def attention_packed(qkv, heads: int, key_bias=None):
     """Self-attention core on a packed projection ``[B, S, 3*H*d]`` (q | k | v along the last dim)."""
     HD = qkv.shape[-1] // 3
     q = qkv[..., :HD]
     if (use_native(qkv) and qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and fused_attention_ok(q, heads)
             and qkv.data_ptr() % 16 == 0):
+        kb = _key_bias(key_bias, qkv.shape[0], qkv.shape[1], qkv.device)
         if torch.is_grad_enabled() and qkv.requires_grad:
-            return _PackedAttentionFn.apply(qkv, heads)
-        return attention_fused_fwd(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads)
-    return attention(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads)
+            return _PackedAttentionFn.apply(qkv, heads, kb)
+        return attention_fused_fwd(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads, key_bias=kb)
+    return attention(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads, key_bias)
 
 
 def fused_attention_ok(q, heads: int) -> bool:
     B, S, HD = q.shape
-    return HD // heads == 64 and S % 128 == 0 and 128 <= S <= 512
+    return HD // heads == 64 and S % 64 == 0 and 64 <= S <= 512
 
 
-def attention(q, k, v, heads: int):
-    """Multi-head self-attention core (no mask, no dropout).  q, k, v: [B, S, heads*d]."""
+def attention(q, k, v, heads: int, key_bias=None):
+    """Multi-head self-attention core.  q, k, v: [B, S, heads*d]; ``key_bias``: optional additive ``[B, S]`` (or HF's
+    ``[B, 1, 1, S]``) key-padding bias.  Head dim 64 and S a multiple of 64 up to 512 run as one fused tcgen05 kernel per
+    direction; other shapes use batched GEMMs + row softmax."""
     B, S, HD = q.shape
     d = HD // heads
     if use_native(q, k, v) and q.dtype == torch.bfloat16 and d % 8 == 0 and S % 8 == 0 and S <= 1024:
         needs_grad = torch.is_grad_enabled() and (q.requires_grad or k.requires_grad or v.requires_grad)
         if fused_attention_ok(q, heads):
-            return _FusedAttentionFn.apply(q, k, v, heads) if needs_grad else attention_fused_fwd(q, k, v, heads)
-        return _AttentionFn.apply(q, k, v, heads)
+            kb = _key_bias(key_bias, B, S, q.device)
+            return _FusedAttentionFn.apply(q, k, v, heads, kb) if needs_grad else attention_fused_fwd(q, k, v, heads, key_bias=kb)
+        if key_bias is None:
+            return _AttentionFn.apply(q, k, v, heads)
     qh, kh, vh = (t.view(B, S, heads, d).transpose(1, 2) for t in (q, k, v))
-    o = TF.scaled_dot_product_attention(qh.float(), kh.float(), vh.float())
+    mask = None if key_bias is None else key_bias.reshape(B, 1, 1, S).float()
+    o = TF.scaled_dot_product_attention(qh.float(), kh.float(), vh.float(), attn_mask=mask)
     return o.transpose(1, 2).reshape(B, S, HD).to(q.dtype)
 
 

@@ -331,7 +331,7 @@ def test_rmsnorm_fwd_bwd(T, H, pdtype, with_res):
     gf = gamma.detach().float().requires_grad_(True)
     h = xf + rf if with_res else xf
     if with_res:
-        h = h.bfloat16().float() + (h - h.detach())      # the kernel rounds the pre-norm sum once (what backward reads)
+        h = h + (h.bfloat16().float() - h).detach()      # the kernel rounds the pre-norm sum once (what backward reads)
     yf = h * torch.rsqrt(h.pow(2).mean(-1, keepdim=True) + 1e-6) * gf
     yf.backward(dy.float())
     assert torch.allclose(y.float(), yf, rtol=2e-2, atol=2e-2)

@@ -132,7 +132,8 @@ def test_trainer_bert_tiny_bf16(tmp_path):
     t.fit()
     assert t.train_losses[-1] < t.train_losses[0]
     names = set(_lib.launches.by_name)
-    assert {"gemm_bf16_tcgen05", "gemm_bf16_tcgen05_batched", "layernorm_fwd", "layernorm_bwd", "softmax_rows",
+    # head dim 64, S = 64: the fused tcgen05 attention kernels (S may be any multiple of 64 up to 512)
+    assert {"gemm_bf16_tcgen05", "attention_fwd_tcgen05", "attention_bwd_tcgen05", "layernorm_fwd", "layernorm_bwd",
             "embedding_fwd", "embedding_bwd"} <= names, names
     sd = torch.load(tmp_path / "model.pth")
     assert all(v.dtype == torch.float32 for v in sd.values() if v.is_floating_point())
@@ -163,7 +164,7 @@ def test_native_graph_executor_matches_python_loop(tmp_path):
     assert a.last_native_stats["h2d_bytes"] > 0
 
 
-@pytest.mark.parametrize("B,S,heads", [(1, 128, 1), (2, 256, 3), (2, 512, 12), (3, 384, 2)])
+@pytest.mark.parametrize("B,S,heads", [(1, 128, 1), (2, 256, 3), (2, 512, 12), (3, 384, 2), (2, 64, 2), (2, 192, 3), (1, 448, 1)])
 def test_fused_attention_forward(B, S, heads):
     from ml_trainer_b200.ops import functional as F
 
@@ -181,7 +182,7 @@ def test_fused_attention_forward(B, S, heads):
         _close(F.attention(q, k, v, heads), ref, 2e-2, "dispatch under no_grad")
 
 
-@pytest.mark.parametrize("B,S,heads", [(1, 128, 1), (2, 256, 3), (2, 512, 12), (1, 384, 2)])
+@pytest.mark.parametrize("B,S,heads", [(1, 128, 1), (2, 256, 3), (2, 512, 12), (1, 384, 2), (2, 64, 2), (2, 192, 3), (1, 320, 2)])
 def test_fused_attention_backward(B, S, heads):
     from ml_trainer_b200.ops import functional as F
 
@@ -200,6 +201,68 @@ def test_fused_attention_backward(B, S, heads):
     for name, got, want in (("dq", q.grad, qf.grad), ("dk", k.grad, kf.grad), ("dv", v.grad, vf.grad)):
         err = (got.float() - want).abs().max().item() / (want.abs().max().item() + 1e-12)
         assert err < 3e-2, f"{name}: relative max error {err}"
+
+
+@pytest.mark.parametrize("B,S,heads", [(3, 128, 2), (2, 512, 12), (4, 192, 3), (2, 64, 1)])
+@pytest.mark.parametrize("packed", [False, True])
+def test_fused_attention_key_padding_mask(B, S, heads, packed):
+    """Key-padding mask as a per-key additive bias inside the fused kernels, forward and backward, against fp32
+    scaled_dot_product_attention with a boolean mask.  Padded QUERY rows are excluded from the comparison of
+    the outputs (they attend uniformly to garbage in both implementations but nothing reads them)."""
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(S + heads)
+    d = 64
+    HD = heads * d
+    lengths = torch.randint(S // 4, S + 1, (B,))
+    lengths[0] = S                                           # one full-length sample
+    amask = (torch.arange(S)[None, :] < lengths[:, None]).to(DEV)          # [B, S] True = token
+    kb = F.prepare_key_bias(amask.long())
+    if packed:
+        qkv = (torch.randn(B, S, 3 * HD, device=DEV) * 0.7).to(torch.bfloat16).requires_grad_()
+        out = F.attention_packed(qkv, heads, kb)
+        q, k, v = qkv[..., :HD], qkv[..., HD:2 * HD], qkv[..., 2 * HD:]
+    else:
+        q, k, v = ((torch.randn(B, S, HD, device=DEV) * 0.7).to(torch.bfloat16).requires_grad_() for _ in range(3))
+        out = F.attention(q, k, v, heads, kb)
+    go = (torch.randn(B, S, HD, device=DEV) * 0.5).to(torch.bfloat16) * amask[:, :, None]      # no gradient enters at padded rows
+    out.backward(go)
+    torch.cuda.synchronize()
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    sp = lambda t: t.reshape(B, S, heads, d).transpose(1, 2)
+    ref = TF.scaled_dot_product_attention(sp(qf), sp(kf), sp(vf), attn_mask=amask[:, None, None, :]).transpose(1, 2).reshape(B, S, HD)
+    ref.backward(go.float())
+    valid = amask[:, :, None].float()
+    _close(out.float() * valid, ref * valid, 2e-2, "masked attention out")
+    grads = (qkv.grad[..., :HD], qkv.grad[..., HD:2 * HD], qkv.grad[..., 2 * HD:]) if packed else (q.grad, k.grad, v.grad)
+    for name, got, want in zip(("dq", "dk", "dv"), grads, (qf.grad, kf.grad, vf.grad)):
+        err = (got.float() - want).abs().max().item() / (want.abs().max().item() + 1e-12)
+        assert err < 3e-2, f"{name}: relative max error {err}"
+    # padded keys receive no gradient at all
+    assert float((grads[1].float() * (1 - valid)).abs().max()) < 1e-3
+    assert float((grads[2].float() * (1 - valid)).abs().max()) < 1e-3
+
+
+def test_bert_masked_batch_uses_fused_attention():
+    """A padded batch (HuggingFace attention_mask) stays on the fused attention kernels and matches the fp32 CPU statement."""
+    from ml_trainer_b200 import build_model
+    from ml_trainer_b200.ops import _lib
+
+    torch.manual_seed(0)
+    ref = build_model("bert_tiny")
+    nat = build_model("bert_tiny")
+    nat.load_state_dict(ref.state_dict())
+    nat = nat.to(DEV).to(torch.bfloat16)
+    ids = torch.randint(0, 1000, (4, 64))
+    mask = torch.ones(4, 64, dtype=torch.long)
+    mask[1, 40:] = 0
+    mask[3, 9:] = 0
+    _lib.launches.reset()
+    lo = nat(ids.to(DEV), attention_mask=mask.to(DEV))
+    lr = ref(ids, attention_mask=mask)
+    _close(lo.cpu(), lr, 3e-2, "masked logits")
+    names = dict(_lib.launches.by_name)
+    assert names.get("attention_fwd_tcgen05", 0) == 2 and "softmax_rows" not in names, names
 
 
 def test_packed_qkv_matches_separate_projections():
