@@ -141,3 +141,23 @@ class U8ImageDataset(Dataset):
         pos = self._served
         self._served += 1
         return self.augment.apply_cpu(self.inputs[i], pos if self.train else None, self.train), self.targets[i]
+
+
+CIFAR10_CLASSES = ("airplane", "automobile", "bird", "cat", "deer", "dog", "frog", "horse", "ship", "truck")
+
+
+def synthetic_cifar(n: int, seed: int = 0):
+    """A CIFAR-10-shaped stand-in for boxes without the dataset: ``(data uint8 [n, 32, 32, 3], labels int64 [n])``.
+
+    Every class has its own colour and a bright square whose position depends on the class, under per-image noise, so a
+    small CNN can actually learn it (the notebooks and examples show a falling loss, not a flat one)."""
+    g = torch.Generator().manual_seed(seed)
+    labels = torch.randint(0, 10, (n,), generator=g)
+    base = torch.randint(0, 256, (10, 3), generator=torch.Generator().manual_seed(1234)).float()
+    img = base[labels].view(n, 1, 1, 3).expand(n, 32, 32, 3).clone()
+    img += torch.randn(n, 32, 32, 3, generator=g) * 40.0
+    for c in range(10):
+        idx = (labels == c).nonzero().flatten()
+        y0, x0 = 2 + 5 * (c // 5) * 3, 2 + 6 * (c % 5)
+        img[idx, y0:y0 + 8, x0:x0 + 6, :] = 255.0 - base[c]
+    return img.clamp_(0, 255).to(torch.uint8), labels
