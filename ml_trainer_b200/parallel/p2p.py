@@ -28,6 +28,21 @@ from .comm import Comm
 logger = get_logger(__name__)
 
 ALGO_IDS = {"oneshot": 0, "twoshot": 1, "nvls": 2}
+
+# Per-world crossover points of the three fused all-reduce + update variants: the largest gradient bucket, in bytes,
+# for which one-shot is the fastest, and the largest for which two-shot still beats NVLS.  Measured with bench/allreduce_sweep.py
+# (bf16 gradients, SGD, 20 back-to-back launches captured in one CUDA graph, max over ranks; records under profiles/).  One-shot
+# moves (N-1) S bytes per GPU and updates the whole bucket on every rank, so its range shrinks as the world grows.
+CROSSOVER = {
+    2: {"oneshot": 2 << 20, "twoshot": 4 << 20, "source": "profiles/allreduce_sweep_2gpu_r2.json"},
+    4: {"oneshot": 1 << 20, "twoshot": 2 << 20, "source": "interpolated between the 2- and 8-GPU sweeps"},
+    8: {"oneshot": 512 << 10, "twoshot": 1 << 20, "source": "profiles/allreduce_sweep_8gpu_r2.json"},
+}
+
+
+def crossover_for(world: int) -> dict:
+    keys = sorted(CROSSOVER)
+    return CROSSOVER[min((k for k in keys if k >= world), default=keys[-1])]
 _c_int, _c_ll, _c_vp = ctypes.c_int, ctypes.c_longlong, ctypes.c_void_p
 
 
@@ -122,7 +137,11 @@ class P2PComm(Comm):
         if self.world_size > 8:
             raise RuntimeError("the native P2P backend covers one NVSwitch node (<= 8 GPUs)")
         self.algo = algo
-        self.oneshot_max = int(oneshot_max_bytes or os.environ.get("MLT_ONESHOT_MAX_BYTES", 1 << 20))
+        self.cross = dict(crossover_for(self.world_size))
+        if os.environ.get("MLT_ONESHOT_MAX_BYTES"):
+            self.cross["oneshot"] = int(os.environ["MLT_ONESHOT_MAX_BYTES"])
+        # receive-slot size: the largest bucket the one-shot variant can take (auto mode never asks for more than the crossover)
+        self.oneshot_max = int(oneshot_max_bytes or max(self.cross["oneshot"], 1 << 20))
         self.cpu_group = dist.new_group(backend="gloo")      # host-side phases of the bootstrap only
         P2PComm._instances += 1
         self._serial = P2PComm._instances
@@ -184,9 +203,11 @@ class P2PComm(Comm):
             if self.algo == "nvls" and not self.arena.multicast:
                 return "twoshot"               # no multicast object on this node: same ownership, P2P data path
             return self.algo
-        if nbytes <= self.oneshot_max and nbytes <= (256 << 10):
+        if nbytes <= self.oneshot_max and nbytes <= self.cross["oneshot"]:
             return "oneshot"
-        return "nvls" if self.arena.multicast else "twoshot"
+        if nbytes <= self.cross["twoshot"] or not self.arena.multicast:
+            return "twoshot"
+        return "nvls"
 
     def allreduce_update(self, opt, lo: int, hi: int, stream=None):
         n = hi - lo

@@ -114,6 +114,8 @@ def test_bert_tiny_native_matches_fp32_reference():
     rp = dict(ref.named_parameters())
     worst = 0.0
     for n, p in nat.named_parameters():
+        if n.endswith("key.bias"):
+            continue            # softmax is invariant to a constant added to every key: this gradient is exactly 0 up to rounding
         g, e = p.grad.float().cpu(), rp[n].grad
         rel = (g - e).norm() / (e.norm() + 1e-6)
         worst = max(worst, rel.item())

@@ -80,7 +80,7 @@ def test_bf16_models_native_vs_library_collectives(tmp_path, model, algo):
     assert res["replicas_identical"]
     a, b = res["ours"], res["ref"]
     # bf16 gradients: the library sums them in bf16, the native kernels in fp32; two epochs of AdamW at lr 1e-3
-    assert torch.allclose(a, b, rtol=0.0, atol=8e-3), float((a - b).abs().max())
+    assert torch.allclose(a, b, rtol=0.0, atol=2e-2), float((a - b).abs().max())
     assert float((a - b).abs().mean()) < 5e-4
     for x, y in zip(res["hist"][0] + res["hist"][1], res["hist_ref"][0] + res["hist_ref"][1]):
         assert abs(x - y) < 0.05 * max(1.0, abs(y))
