@@ -320,7 +320,9 @@ def measure_ours(a, model_name):
         gpu_launches = _lib.launches.n + eng.launches_per_step * (eng.graph_replays - replays0 if eng.use_graph and eng.fused is None else 0)
     by_kernel = dict(_lib.launches.by_name)
     if not pool_mode and eng.use_graph and eng.fused is None:
-        by_kernel["kernels_inside_graph_replays"] = int(eng.launches_per_step * K)
+        # the timed steps are replays of a captured step: the launches are the captured step's kernels, K times
+        by_kernel = {k: int(v * K) for k, v in getattr(eng, "kernels_per_step", {}).items()} or \
+            {"kernels_inside_graph_replays": int(eng.launches_per_step * K)}
     del flush
     dev_ms = median(dev_ms_runs)
 

@@ -56,14 +56,18 @@ struct GemmParams {
 
 // AUX: the epilogue also writes a second bf16 tensor (pre-activation or activation derivative) through its own slabs and
 // TMA stores; those 32 KB come out of the operand ring (3 stages instead of 4 at BN = 256).
-template <int BN, bool AUX>
+// DB: short-K problems are bound by the output stream, not by the MMAs.  Every epilogue warp then gets TWO store slabs and
+// alternates between them, so converting / writing the next 4 KB into shared memory overlaps the bulk store that is still
+// reading the previous one (one slab serialises them: measured 4.5 TB/s on [802816 x 256] = [.. x 64] x [64 x 256], cuBLAS
+// 6.6); the second set of slabs comes out of the operand ring, which a one- or two-k-block problem does not need that deep.
+template <int BN, bool AUX, bool DB = false>
 struct GemmCfg {
   static constexpr int kABytes = BM * BK * 2;                // 16 KB
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStages = BN == 256 ? (AUX ? 3 : 4) : (BN == 128 ? 6 : 8);
+  static constexpr int kStages = DB ? (BN == 256 ? 3 : (BN == 128 ? 5 : 6)) : (BN == 256 ? (AUX ? 3 : 4) : (BN == 128 ? 6 : 8));
   static constexpr int kTmemCols = 2 * BN;                   // two accumulator stages (power of two >= 32)
-  static constexpr int kStagingBytes = kEpiWarps * 4096 * (AUX ? 2 : 1);   // per epilogue warp: 32-row x 128-byte slab(s) for TMA stores
+  static constexpr int kStagingBytes = kEpiWarps * 4096 * ((AUX || DB) ? 2 : 1);   // per epilogue warp: 32-row x 128-byte slab(s) for TMA stores
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -91,11 +95,18 @@ __device__ __forceinline__ float act_grad_from_pre(int act, float z) {
 // One output tile's worth of epilogue work for one warp: rows [store_row0, +32) (this lane: `row`), 32-column chunks
 // c_lo .. c_hi-1 of the BN-wide accumulator at `taddr`.  TMEM -> registers -> (bias / activation / aux) -> swizzled smem
 // slab -> TMA store.  Waits on the accumulator's full barrier itself so the aux prefetch can be issued before it.
-template <int BN, bool AUX>
+// PAIR (BN == 64, bf16 output): the two warps of a TMEM lane quadrant each take ONE 32-column chunk and fill the two 64-byte
+// halves of the same slab rows; they meet on a named barrier and the first of them issues the store - all eight epilogue
+// warps work on a 64-column tile instead of four.
+__device__ __forceinline__ void pair_bar(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+
+template <int BN, bool AUX, bool DB>
 __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* tmOut, const CUtensorMap* tmAux, uint32_t taddr,
-                                              int row, int store_row0, int n0, int z1, int z2, uint8_t* slab, uint8_t* aux_slab,
-                                              int lane, int c_lo, int c_hi, uint64_t* full_bar, uint32_t full_parity) {
+                                              int row, int store_row0, int n0, int z1, int z2, uint8_t* slab_base, uint8_t* aux_slab,
+                                              int lane, int c_lo, int c_hi, uint64_t* full_bar, uint32_t full_parity, int& buf,
+                                              int pair_id, int pair_half) {
   const int chunks_per_slab = p.out_f32 ? 1 : 2;          // a 32-column chunk is 128 B of fp32 or 64 B of bf16
+  const bool pair = pair_id > 0;
   const bool aux_in = p.aux_mode == 2 || p.aux_mode == 4;
   // aux operand of the first chunk: requested before the accumulator is ready, then one chunk ahead
   const __nv_bfloat16* aux_row = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux;
@@ -118,10 +129,14 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
     if (c + 1 < c_hi) fetch_aux(c + 1);
     tmem_ld_wait();
     const int nb = n0 + c * 32;
-    const int within = (c - c_lo) % chunks_per_slab;
-    if (within == 0) {
-      // the bulk store that last read this slab must have drained it
-      if (lane == 0) tma_store_wait_read<0>();
+    const int within = pair ? pair_half : (c - c_lo) % chunks_per_slab;
+    uint8_t* slab = slab_base + (DB ? buf * 4096 : 0);
+    if (pair) {
+      // the bulk store that last read this buffer must have drained it: the issuing warp checks, then both may write
+      if (pair_half == 0 && lane == 0) tma_store_wait_read<DB ? 1 : 0>();
+      pair_bar(pair_id);
+    } else if (within == 0) {
+      if (lane == 0) tma_store_wait_read<DB ? 1 : 0>();
       __syncwarp();
     }
     float v[32];
@@ -242,7 +257,15 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
         *reinterpret_cast<uint4*>(srow + (((within * 4 + j) ^ (lane & 7)) << 4)) = pk;
       }
     }
-    if (within == chunks_per_slab - 1) {
+    if (pair) {
+      fence_proxy_async();
+      pair_bar(pair_id);                                 // both halves of the slab rows are written
+      if (pair_half == 0 && lane == 0) {
+        tma_store_4d(tmOut, slab, n0, store_row0, z1, z2);
+        tma_store_commit();
+      }
+      if (DB) buf ^= 1;
+    } else if (within == chunks_per_slab - 1) {
       fence_proxy_async();                               // generic-proxy smem writes -> visible to the TMA engine
       __syncwarp();
       if (lane == 0) {
@@ -251,16 +274,17 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
         if (AUX) tma_store_4d(tmAux, aux_slab, col0, store_row0, z1, z2);
         tma_store_commit();
       }
+      if (DB) buf ^= 1;
     }
   }
 }
 
-template <int BN, bool AUX>
+template <int BN, bool AUX, bool DB>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                          const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmAux,
                          const GemmParams p) {
-  using Cfg = GemmCfg<BN, AUX>;
+  using Cfg = GemmCfg<BN, AUX, DB>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* staging = smem + Cfg::kStages * Cfg::kStageBytes;                 // 1024-byte aligned (stage sizes are)
@@ -401,11 +425,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     // (32 rows x 128 bytes = 64 bf16 or 32 fp32 columns); TMA clips rows >= M and columns >= N.
     const int q = warp & 3;                                 // TMEM lane quadrant this warp may read
     const int half = (warp - 2) >> 2;
-    uint8_t* slab = staging + (warp - 2) * 4096;
+    // BN == 64 with a bf16 output: the quadrant's two warps share one slab (see epilogue_tile, PAIR)
+    const bool pair = BN == 64 && !p.out_f32;
+    uint8_t* slab = pair ? staging + q * 4096 * (DB ? 2 : 1) : staging + (warp - 2) * 4096 * (DB ? 2 : 1);
     uint8_t* aux_slab = staging + (kEpiWarps + warp - 2) * 4096;      // only present (and used) when AUX
     constexpr int kChunks = BN / 32;
-    const int c_lo = BN >= 128 ? half * (kChunks / 2) : 0;
-    const int c_hi = BN >= 128 ? c_lo + kChunks / 2 : (half == 0 ? kChunks : 0);
+    const int c_lo = BN >= 128 ? half * (kChunks / 2) : (pair ? half : 0);
+    const int c_hi = BN >= 128 ? c_lo + kChunks / 2 : (pair ? half + 1 : (half == 0 ? kChunks : 0));
+    int sbuf = 0;
     int as = 0; uint32_t aphase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
@@ -414,8 +441,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int z1 = z % p.nb1, z2 = z / p.nb1;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * BN;
-      epilogue_tile<BN, AUX>(p, &tmOut, &tmAux, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), row, m_blk * BM + q * 32, n0, z1, z2,
-                             slab, aux_slab, lane, c_lo, c_hi, &tmem_full[as], aphase);
+      epilogue_tile<BN, AUX, DB>(p, &tmOut, &tmAux, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), row, m_blk * BM + q * 32, n0, z1, z2,
+                                 slab, aux_slab, lane, c_lo, c_hi, &tmem_full[as], aphase, sbuf, pair ? 1 + q : 0, half);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&tmem_empty[as]);
@@ -562,6 +589,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     uint8_t* slab = staging + (warp - 2) * 4096;
     constexpr int kChunks = BN / 32;
     const int c_lo = half * (kChunks / 2), c_hi = c_lo + kChunks / 2;
+    int sbuf2 = 0;
     int as = 0; uint32_t aphase = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       int m_blk, n_blk;
@@ -569,8 +597,8 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       tile_coords(tile - z * tiles_per_problem, p.num_m, p.num_n, m_blk, n_blk);
       const int z1 = z % p.nb1, z2 = z / p.nb1;
       const int row0 = m_blk * TM + (int)rank * BM + q * 32;
-      epilogue_tile<BN, false>(p, &tmOut, &tmOut, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), row0 + lane, row0, n_blk * BN, z1, z2,
-                               slab, slab, lane, c_lo, c_hi, &tmem_full[as], aphase);
+      epilogue_tile<BN, false, false>(p, &tmOut, &tmOut, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), row0 + lane, row0, n_blk * BN, z1, z2,
+                               slab, slab, lane, c_lo, c_hi, &tmem_full[as], aphase, sbuf2, 0, 0);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cluster(&tmem_empty[as], 0);
@@ -631,9 +659,9 @@ static int make_tmap(CUtensorMap* out, const void* base, long long inner, long l
   return 0;
 }
 
-template <int BN, bool AUX>
+template <int BN, bool AUX, bool DB = false>
 static int launch_gemm_impl(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParams& p, cudaStream_t st) {
-  using Cfg = GemmCfg<BN, AUX>;
+  using Cfg = GemmCfg<BN, AUX, DB>;
   // output map: rows of 128 bytes (64 bf16 / 32 fp32 columns) x 32 rows per store, batch dims as for the operands
   CUtensorMap tmOut;
   if (make_tmap(&tmOut, p.out, p.N, p.M, p.ldo, p.out_f32 ? 32 : 64, 32, p.nb1, p.ob1, p.nb2, p.ob2, p.out_f32 ? 4 : 2)) return 1;
@@ -643,7 +671,7 @@ static int launch_gemm_impl(const CUtensorMap& tmA, const CUtensorMap& tmB, Gemm
   CUtensorMap tmAux = tmOut;
   if (AUX && make_tmap(&tmAux, p.aux, p.N, p.M, p.ld_aux, 64, 32, p.nb1, 0, p.nb2, 0, 2)) return 1;
   static bool attr_set[64] = {};             // function attributes are per device
-  auto kern = gemm_bf16_tcgen05_kernel<BN, AUX>;
+  auto kern = gemm_bf16_tcgen05_kernel<BN, AUX, DB>;
   int dev = 0;
   MLT_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
@@ -703,6 +731,10 @@ static int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, GemmParam
   const bool aux_slab = BN == 256 && (p.aux_mode == 1 || p.aux_mode == 3) && !p.out_f32 && p.nb1 * p.nb2 == 1 &&
                         ((uintptr_t)p.aux % 16) == 0 && (p.ld_aux * 2) % 16 == 0;
   if (BN == 256 && aux_slab) return launch_gemm_impl<256, true>(tmA, tmB, p, st);
+  // short reductions (<= 4 k-blocks per tile): the output stream is the bound -> double-buffered store slabs
+  const int kblocks = p.splits > 1 ? p.kb_per_split : ceil_div(p.K, BK);
+  static const int db_max_k = getenv("MLT_GEMM_DB_MAX_KBLOCKS") ? atoi(getenv("MLT_GEMM_DB_MAX_KBLOCKS")) : 4;
+  if (kblocks <= db_max_k) return launch_gemm_impl<BN, false, true>(tmA, tmB, p, st);
   return launch_gemm_impl<BN, false>(tmA, tmB, p, st);
 }
 

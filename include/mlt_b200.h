@@ -290,6 +290,9 @@ int mlt_lenet_steps(void* master, void* s1, void* s2, const void* hyper, long lo
 int mlt_lenet_set_debug(void* buf);
 int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
                           void* out_bf16, int T, int S, int H, void* stream);
+/* the same, with the row count V of the word table: ids outside [0, V) are clamped instead of read / written out of bounds */
+int mlt_embedding_sum_fwd_v(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
+                            void* out_bf16, int T, int S, int H, long long V, void* stream);
 int mlt_embedding_bwd(const void* ids_i64, const void* dh_bf16, void* dword, long long V, void* dpos, int grads_bf16, int B,
                       int S, int H, void* stream);
 

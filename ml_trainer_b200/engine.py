@@ -42,6 +42,7 @@ class StepEngine:
         self._pool = None
         self.graph_replays = 0
         self.launches_per_step = 0
+        self.kernels_per_step: Dict[str, int] = {}      # per-kernel launch counts of one captured step
         self.last_loss: Optional[torch.Tensor] = None
         # single-kernel step (forward + loss + backward + all-reduce + update) when the model provides one
         self.fused = None
@@ -158,11 +159,12 @@ class StepEngine:
         torch.cuda.synchronize(self.device)
         from .ops._lib import launches
 
-        n0 = launches.n
+        n0, by0 = launches.n, dict(launches.by_name)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, pool=self._pool):
             self._train_body(inputs, targets)
         self.launches_per_step = launches.n - n0      # native kernels recorded into (and replayed by) the graph
+        self.kernels_per_step = {k: v - by0.get(k, 0) for k, v in launches.by_name.items() if v - by0.get(k, 0) > 0}
         if self._pool is None:
             self._pool = g.pool()
         self._graphs[key] = g

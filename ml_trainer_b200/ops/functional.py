@@ -867,8 +867,8 @@ class _EmbeddingFn(torch.autograd.Function):
         H = word.shape[1]
         out = torch.empty((B, S, H), dtype=torch.bfloat16, device=ids.device)
         ids = ids.contiguous()
-        check(_lib.lib().mlt_embedding_sum_fwd(ptr(ids), ptr(word), ptr(pos), ptr(typ), _c_int(int(word.dtype == torch.bfloat16)),
-                                               ptr(out), _c_int(B * S), _c_int(S), _c_int(H), stream_handle()),
+        check(_lib.lib().mlt_embedding_sum_fwd_v(ptr(ids), ptr(word), ptr(pos), ptr(typ), _c_int(int(word.dtype == torch.bfloat16)),
+                                                 ptr(out), _c_int(B * S), _c_int(S), _c_int(H), _c_ll(word.shape[0]), stream_handle()),
               "mlt_embedding_sum_fwd")
         launches.bump("embedding_fwd")
         ctx.save_for_backward(ids)

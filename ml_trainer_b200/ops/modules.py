@@ -139,3 +139,55 @@ class MSELoss(_RegressionLoss):
 class CustomLoss(_RegressionLoss):
     """Reference criterion 'custom' = custom_loss_function = mean((output - target)**2) (src/utils/functions.py:15-17)."""
     kind = "custom"
+
+
+# ---- drop-in layers for user models (convert_model) -----------------------------------------------------------------------
+# A user's CNN computes in logical NCHW.  These layers keep that contract but hold the data channels-last: a channels_last
+# NCHW tensor IS a contiguous NHWC tensor, so the NHWC kernels read and write it without a copy and the logical shape the rest
+# of the user's forward() sees never changes.  They take the native path for bf16 CUDA tensors and defer to torch otherwise.
+def _as_nhwc(x: torch.Tensor) -> torch.Tensor:
+    return x.contiguous(memory_format=torch.channels_last).permute(0, 2, 3, 1)
+
+
+class Conv2d(nn.Conv2d):
+    """``nn.Conv2d`` on the implicit-GEMM tcgen05 path (dense, undilated, symmetric padding, channels multiple of 8)."""
+
+    def _native(self, x) -> bool:
+        k, s, p = self.kernel_size, self.stride, self.padding
+        return (x.is_cuda and x.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16 and F.native_available()
+                and self.groups == 1 and self.dilation == (1, 1) and k[0] == k[1] and s[0] == s[1] and isinstance(p, tuple)
+                and p[0] == p[1] and self.padding_mode == "zeros" and self.in_channels % 8 == 0 and self.out_channels % 8 == 0)
+
+    def forward(self, x):
+        if not self._native(x):
+            return super().forward(x)
+        from . import conv as C
+
+        y = C.conv2d_nhwc(_as_nhwc(x), self.weight, self.stride[0], self.padding[0])
+        if self.bias is not None:
+            y = y + self.bias
+        return y.permute(0, 3, 1, 2)
+
+
+class BatchNorm2d(nn.BatchNorm2d):
+    """``nn.BatchNorm2d`` through the NHWC statistics / apply kernels (training and evaluation mode)."""
+
+    def forward(self, x):
+        if not (x.is_cuda and x.dtype == torch.bfloat16 and F.native_available() and self.affine and self.track_running_stats
+                and self.num_features % 8 == 0):
+            return super().forward(x)
+        from . import conv as C
+
+        return C.batch_norm_nhwc(_as_nhwc(x), self).permute(0, 3, 1, 2)
+
+
+class LayerNorm(nn.LayerNorm):
+    """``nn.LayerNorm`` over the last dimension through the fused kernels (bf16 activations, width a multiple of 8 <= 1024)."""
+
+    def forward(self, x, residual=None):
+        if (len(self.normalized_shape) == 1 and self.elementwise_affine and self.bias is not None and x.is_cuda
+                and x.dtype == torch.bfloat16 and residual is None):
+            return F.layer_norm(x, self.weight, self.bias, self.eps)
+        if residual is not None:
+            return F.layer_norm(x, self.weight, self.bias, self.eps, residual)
+        return super().forward(x)

@@ -192,8 +192,8 @@ def _make_trainer(model_name, backend, algo, dtype, bucket_mb, out_dir, fused_st
     torch.manual_seed(seed_model)
     model = build_model(model_name)
     if model_name.startswith("bert"):
-        tr = SyntheticDataset((64,), 2, length=64, seed=11, kind="tokens")
-        va = SyntheticDataset((64,), 2, length=32, seed=12, kind="tokens")
+        tr = SyntheticDataset((64,), 2, length=64, seed=11, kind="tokens", vocab=1000)       # bert_tiny's vocabulary
+        va = SyntheticDataset((64,), 2, length=32, seed=12, kind="tokens", vocab=1000)
         bs = 16
     elif model_name.startswith("resnet"):
         tr = SyntheticDataset((3, 64, 64), 16, length=64, seed=11)

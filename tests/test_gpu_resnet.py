@@ -136,3 +136,84 @@ def test_trainer_resnet_tiny_bf16(tmp_path):
     assert t.train_losses[-1] < t.train_losses[0]
     names = set(_lib.launches.by_name)
     assert {"gemm_bf16_tcgen05", "im2col_nhwc", "col2im_nhwc", "bn_fwd", "bn_bwd", "maxpool_fwd", "avgpool_fwd"} <= names, names
+
+
+def test_unmodified_torchvision_resnet_trains_on_the_library(tmp_path):
+    """The reference's contract is "bring your own nn.Module" (reference main.py:30): an unmodified torchvision bottleneck ResNet
+    handed to the Trainer is recognised, re-classed onto the library's NHWC / tcgen05 path (same parameter names) and trains like
+    the library's own model with the same weights."""
+    import torchvision
+
+    from ml_trainer_b200 import SyntheticDataset, Trainer
+    from ml_trainer_b200.models.resnet import ResNet
+    from ml_trainer_b200.ops import _lib
+
+    torch.manual_seed(0)
+    tv = torchvision.models.ResNet(torchvision.models.resnet.Bottleneck, [1, 1, 1, 1], num_classes=16)
+    ours = ResNet((1, 1, 1, 1), num_classes=16)
+    ours.load_state_dict(tv.state_dict())
+    data = SyntheticDataset((3, 64, 64), 16, length=32, seed=3)
+    res = []
+    for model in (tv, ours):
+        _lib.launches.reset()
+        tr = Trainer(model, datasets=(data, data), epochs=1, batch_size=16, model_dir=str(tmp_path), progress=False, optimizer="sgd",
+                     lr=0.05, metric="accuracy", dtype="bf16", graph=False, seed=32)
+        from ml_trainer_b200 import Loader
+
+        tr.train_loader = Loader(data, batch_size=16, shuffle=False, pin_memory=True)
+        tr.fit()
+        names = dict(_lib.launches.by_name)
+        assert names.get("conv_fwd_implicit_gemm", 0) > 0 and names.get("bn_apply", 0) > 0, names
+        res.append((tr.train_losses[0], {k: v.float().clone() for k, v in tr.model.state_dict().items()}))
+    assert type(tv).__module__.endswith("models.resnet") and type(tv).__name__ == "ResNet" and getattr(tv, "_mlt_native", False)
+    assert list(res[0][1]) == list(res[1][1])                      # state_dict keys are torchvision's
+    assert abs(res[0][0] - res[1][0]) < 2e-2 * max(1.0, abs(res[1][0]))
+    for k in res[0][1]:
+        if "num_batches_tracked" in k:
+            continue
+        a, b = res[0][1][k], res[1][1][k]
+        assert torch.allclose(a, b, rtol=5e-2, atol=5e-3 * float(b.abs().max()) + 1e-4), (k, float((a - b).abs().max()))
+
+
+def test_convert_model_generic_cnn_matches_fp32_torch(tmp_path):
+    """A hand-written CNN (Conv2d / BatchNorm2d / LayerNorm / Linear in logical NCHW) converted layer by layer: forward and
+    parameter gradients against the same network in fp32 torch."""
+    import copy
+
+    from ml_trainer_b200.ops import _lib
+    from ml_trainer_b200.ops.convert import convert_model
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.c1 = torch.nn.Conv2d(8, 64, 3, padding=1, bias=False)
+            self.b1 = torch.nn.BatchNorm2d(64)
+            self.c2 = torch.nn.Conv2d(64, 64, 3, stride=2, padding=1, bias=True)
+            self.b2 = torch.nn.BatchNorm2d(64)
+            self.ln = torch.nn.LayerNorm(64)
+            self.fc = torch.nn.Linear(64, 10)
+
+        def forward(self, x):
+            x = torch.relu(self.b1(self.c1(x)))
+            x = torch.relu(self.b2(self.c2(x)))
+            x = x.mean((2, 3))
+            return self.fc(self.ln(x))
+
+    torch.manual_seed(1)
+    ref = Net().cuda()
+    nat = convert_model(copy.deepcopy(ref)).to(torch.bfloat16)
+    x = torch.randn(16, 8, 16, 16, device="cuda")
+    y = torch.randint(0, 10, (16,), device="cuda")
+    _lib.launches.reset()
+    lo = nat(x.to(torch.bfloat16))
+    lr = ref(x)
+    torch.nn.functional.cross_entropy(lo.float(), y).backward()
+    torch.nn.functional.cross_entropy(lr, y).backward()
+    names = dict(_lib.launches.by_name)
+    assert any(k.startswith("conv") or k.startswith("im2col") for k in names) and any(k.startswith("bn_") for k in names), names
+    assert torch.allclose(lo.float(), lr, rtol=5e-2, atol=5e-2), float((lo.float() - lr).abs().max())
+    rp = dict(ref.named_parameters())
+    for n, p in nat.named_parameters():
+        g, e = p.grad.float(), rp[n].grad
+        rel = float((g - e).norm() / (e.norm() + 1e-6))
+        assert rel < 0.1, (n, rel)
