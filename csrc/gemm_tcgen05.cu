@@ -279,6 +279,93 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
   }
 }
 
+// The lean epilogue: no bias, no stored / multiplied aux tensor, activation none or ReLU - every convolution GEMM and every
+// data / weight gradient GEMM.  The generic epilogue above re-derives its options per 32-column chunk (~970 instructions per
+// warp and 128 x 256 tile, measured; two epilogue warps per scheduler cannot hide that much dependent issue latency, so a
+// short-K problem ran at the epilogue's pace: 113 us where the output stream needs 78).  Here a warp's whole share of the tile is
+// one straight line: tcgen05.ld, cvt.rn.bf16x2 (or nothing for fp32), st.shared with swizzle offsets computed once, one bulk store
+// per 4 KB slab.
+__device__ __forceinline__ uint32_t cvt_bf16x2(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+template <int BN, bool DB, bool F32>
+__device__ __forceinline__ void epilogue_tile_lean(const CUtensorMap* tmOut, uint32_t taddr, int store_row0, int n0, int z1, int z2,
+                                                   uint8_t* slab_base, int lane, int c_lo, int c_hi, uint64_t* full_bar,
+                                                   uint32_t full_parity, int& buf, int pair_id, int pair_half, bool relu) {
+  const uint32_t srow = smem_u32(slab_base) + lane * 128;
+  const uint32_t sw = (uint32_t)(lane & 7);
+  mbar_wait(full_bar, full_parity);
+  tc_fence_after();
+  if (pair_id > 0) {                                     // BN == 64, bf16: this warp owns ONE chunk = one 64-byte half of the slab rows
+    uint32_t r[32];
+    tmem_ld_32x32b_x32(taddr + c_lo * 32, r);
+    if (pair_half == 0 && lane == 0) tma_store_wait_read<DB ? 1 : 0>();
+    pair_bar(pair_id);
+    tmem_ld_wait();
+    const uint32_t base = srow + (DB ? buf * 4096 : 0);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { v[e] = __uint_as_float(r[8 * j + e]); if (relu) v[e] = fmaxf(v[e], 0.f); }
+      sts128(base + ((((uint32_t)(pair_half * 4 + j)) ^ sw) << 4), cvt_bf16x2(v[0], v[1]), cvt_bf16x2(v[2], v[3]), cvt_bf16x2(v[4], v[5]),
+             cvt_bf16x2(v[6], v[7]));
+    }
+    fence_proxy_async();
+    pair_bar(pair_id);
+    if (pair_half == 0 && lane == 0) {
+      tma_store_4d(tmOut, slab_base + (DB ? buf * 4096 : 0), n0, store_row0, z1, z2);
+      tma_store_commit();
+    }
+    if (DB) buf ^= 1;
+    return;
+  }
+  constexpr int kPerSlab = F32 ? 1 : 2;                  // 32-column chunks per 128-byte slab row
+#pragma unroll 1
+  for (int c = c_lo; c < c_hi; c += kPerSlab) {
+    uint32_t r[32], r2[32];
+    tmem_ld_32x32b_x32(taddr + c * 32, r);
+    if (!F32) tmem_ld_32x32b_x32(taddr + (c + 1) * 32, r2);
+    if (lane == 0) tma_store_wait_read<DB ? 1 : 0>();     // the bulk store that last read this buffer has drained it
+    __syncwarp();
+    tmem_ld_wait();
+    const uint32_t base = srow + (DB ? buf * 4096 : 0);
+    if (F32) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) w[e] = relu ? __float_as_uint(fmaxf(__uint_as_float(r[4 * j + e]), 0.f)) : r[4 * j + e];
+        sts128(base + (((uint32_t)j ^ sw) << 4), w[0], w[1], w[2], w[3]);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float v[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          v[e] = __uint_as_float(j < 4 ? r[8 * j + e] : r2[8 * (j - 4) + e]);
+          if (relu) v[e] = fmaxf(v[e], 0.f);
+        }
+        sts128(base + (((uint32_t)j ^ sw) << 4), cvt_bf16x2(v[0], v[1]), cvt_bf16x2(v[2], v[3]), cvt_bf16x2(v[4], v[5]), cvt_bf16x2(v[6], v[7]));
+      }
+    }
+    fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) {
+      tma_store_4d(tmOut, slab_base + (DB ? buf * 4096 : 0), n0 + c * 32, store_row0, z1, z2);
+      tma_store_commit();
+    }
+    if (DB) buf ^= 1;
+  }
+}
+
 template <int BN, bool AUX, bool DB>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -434,6 +521,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
     const int c_hi = BN >= 128 ? c_lo + kChunks / 2 : (pair ? half + 1 : (half == 0 ? kChunks : 0));
     int sbuf = 0;
     int as = 0; uint32_t aphase = 0;
+    // lean path: nothing but (ReLU and) the store (TMA clips rows >= M and columns >= N, so ragged tiles need no care)
+    const bool lean = !AUX && p.bias == nullptr && p.aux_mode == 0 && (p.act == ACT_NONE || p.act == ACT_RELU);
+    const bool relu = p.act == ACT_RELU;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int m_blk, n_blk;
       const int z = tile / tiles_per_problem;
@@ -441,7 +531,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_c
       const int z1 = z % p.nb1, z2 = z / p.nb1;
       const int row = m_blk * BM + q * 32 + lane;
       const int n0 = n_blk * BN;
-      epilogue_tile<BN, AUX, DB>(p, &tmOut, &tmAux, tmem_base + as * BN + ((uint32_t)(q * 32) << 16), row, m_blk * BM + q * 32, n0, z1, z2,
+      const uint32_t tacc = tmem_base + as * BN + ((uint32_t)(q * 32) << 16);
+      if (lean) {
+        if (p.out_f32) epilogue_tile_lean<BN, DB, true>(&tmOut, tacc, m_blk * BM + q * 32, n0, z1, z2, slab, lane, c_lo, c_hi, &tmem_full[as],
+                                                        aphase, sbuf, 0, half, relu);
+        else epilogue_tile_lean<BN, DB, false>(&tmOut, tacc, m_blk * BM + q * 32, n0, z1, z2, slab, lane, c_lo, c_hi, &tmem_full[as], aphase,
+                                               sbuf, pair ? 1 + q : 0, half, relu);
+      } else
+      epilogue_tile<BN, AUX, DB>(p, &tmOut, &tmAux, tacc, row, m_blk * BM + q * 32, n0, z1, z2,
                                  slab, aux_slab, lane, c_lo, c_hi, &tmem_full[as], aphase, sbuf, pair ? 1 + q : 0, half);
       tc_fence_before();
       __syncwarp();

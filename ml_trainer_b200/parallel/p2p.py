@@ -276,29 +276,56 @@ class P2PComm(Comm):
 
     def all_reduce_mean(self, flat, stream=None):
         """Unfused in-place mean all-reduce (the reference's ``_average_gradients``), through the same P2P / NVLS
-        kernels with the "mean only" rule: the reduced values are written back over the gradients on every rank."""
+        kernels with the "mean only" rule: the reduced values are written back over the gradients on every rank.
+        A tensor outside the arena (or oddly aligned) is staged through the arena's receive slots in chunks."""
         if self.world_size == 1:
             return
         off = self.arena.offset_of(flat) if self.arena is not None else None
         n = flat.numel()
-        esz = flat.element_size()
-        if off is None or off % 16 != 0 or n % 8 != 0 or flat.dtype not in (torch.float32, torch.bfloat16):
-            dist.all_reduce(flat, op=dist.ReduceOp.SUM)          # tensors outside the arena: library collective
-            flat.div_(self.world_size)
+        if flat.dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError("P2PComm.all_reduce_mean handles fp32 and bf16 tensors")
+        if off is None or off % 16 != 0 or n % 8 != 0 or not flat.is_contiguous():
+            self._staged_all_reduce_mean(flat)
             return
+        self._mean_kernel(off, n, flat.dtype, stream, oneshot_ok=True)
+
+    def _mean_kernel(self, off: int, n: int, dtype: torch.dtype, stream=None, oneshot_ok: bool = True):
+        esz = 2 if dtype == torch.bfloat16 else 4
         algo = self.pick_algo(n * esz)
-        if algo == "oneshot" and n * esz > self.oneshot_max:
-            algo = "nvls" if self.arena.multicast else "twoshot"
-        tmp_p = torch.empty(n, dtype=torch.float32, device=self.device)
-        tmp_s = torch.empty(n, dtype=torch.float32, device=self.device)
-        hyper = torch.zeros(8, dtype=torch.float32, device=self.device)
-        hyper[7] = 1.0 / self.world_size
+        if algo == "oneshot" and (not oneshot_ok or n * esz > self.oneshot_max):
+            algo = "twoshot"
+        if not hasattr(self, "_mean_tmp") or self._mean_tmp[0].numel() < n:
+            self._mean_tmp = (torch.empty(n, dtype=torch.float32, device=self.device), torch.empty(n, dtype=torch.float32, device=self.device))
+            self._mean_hyper = torch.zeros(8, dtype=torch.float32, device=self.device)
+            self._mean_hyper[7] = 1.0 / self.world_size
+        tmp_p, tmp_s = self._mean_tmp
         one = lambda t: (_c_vp * 1)(t.data_ptr() if t is not None else 0)
         check(self.L.mlt_p2p_allreduce_update(
-            ctypes.byref(self.ctx), _c_int(ALGO_IDS[algo]), _c_int(5), _c_int(int(flat.dtype == torch.bfloat16)), _c_ll(off),
-            _c_ll(off), _c_int(0), one(tmp_p), one(tmp_s), one(None), one(hyper), _c_ll(n), _c_int(0), _c_int(1),
+            ctypes.byref(self.ctx), _c_int(ALGO_IDS[algo]), _c_int(5), _c_int(int(dtype == torch.bfloat16)), _c_ll(off),
+            _c_ll(off), _c_int(0), one(tmp_p), one(tmp_s), one(None), one(self._mean_hyper), _c_ll(n), _c_int(0), _c_int(1),
             stream_handle(stream)), "mlt_p2p_allreduce_update(mean only)")
         launches.bump(f"p2p_allreduce_{algo}")
+
+    def _staged_all_reduce_mean(self, flat):
+        """Tensors the kernels cannot address directly: copy chunks into the (otherwise idle) receive-slot region of the arena,
+        reduce there with the sharded kernel (each rank reads and writes only its own slice of every peer's copy), copy back."""
+        esz = flat.element_size()
+        region = 2 * self.world_size * self.oneshot_max
+        cap = region // esz // 1024 * 1024                       # elements per chunk (a multiple of world * 8)
+        src = flat.reshape(-1) if flat.is_contiguous() else flat.contiguous().view(-1)
+        n = src.numel()
+        for lo in range(0, n, cap):
+            m = min(cap, n - lo)
+            mp = (m + 1023) // 1024 * 1024
+            stage = self.arena.view(self.recv_off, mp, flat.dtype)
+            stage[:m].copy_(src[lo:lo + m])
+            if mp > m:
+                stage[m:].zero_()
+            self._mean_kernel(self.recv_off, mp, flat.dtype, None, oneshot_ok=False)     # one-shot would receive into this very region
+            src[lo:lo + m].copy_(stage[:m])
+            self.device_barrier()                                 # nobody may restage before every rank has copied out
+        if src.data_ptr() != flat.data_ptr():
+            flat.copy_(src.view(flat.shape))
 
     def broadcast(self, tensor, src=0):
         if self.world_size == 1:
@@ -310,21 +337,22 @@ class P2PComm(Comm):
                                            stream_handle()), "mlt_p2p_broadcast")
             launches.bump("p2p_broadcast")
             return
-        # tensors outside the arena (module buffers): bounce through the first receive slot
-        stage_bytes = _align(nbytes, 16)
-        if stage_bytes > self.oneshot_max:
-            dist.broadcast(tensor, src=src)
-            return
-        stage = self.arena.view(self.recv_off, stage_bytes, torch.uint8)
-        if self.rank == src:                      # only the source writes the slot the broadcast pushes from (and into)
-            stage[:nbytes].copy_(tensor.contiguous().view(-1).view(torch.uint8))
-        check(self.L.mlt_p2p_broadcast(ctypes.byref(self.ctx), _c_ll(self.recv_off), _c_ll(stage_bytes), _c_int(src),
-                                       _c_int(1), stream_handle()), "mlt_p2p_broadcast")
-        launches.bump("p2p_broadcast")
-        tensor.copy_(stage[:nbytes].view(tensor.dtype).view(tensor.shape))
-        # peers must not reuse the slot before everyone copied out
-        torch.cuda.current_stream().synchronize()
-        dist.barrier(group=self.cpu_group)
+        # tensors outside the arena (module buffers): bounce through the receive-slot region, in chunks when they are large
+        region = 2 * self.world_size * self.oneshot_max
+        flat = tensor.contiguous().view(-1).view(torch.uint8)
+        for lo in range(0, nbytes, region):
+            m = min(region, nbytes - lo)
+            mp = _align(m, 16)
+            stage = self.arena.view(self.recv_off, mp, torch.uint8)
+            if self.rank == src:                      # only the source writes the region the broadcast pushes from (and into)
+                stage[:m].copy_(flat[lo:lo + m])
+            check(self.L.mlt_p2p_broadcast(ctypes.byref(self.ctx), _c_ll(self.recv_off), _c_ll(mp), _c_int(src), _c_int(1),
+                                           stream_handle()), "mlt_p2p_broadcast")
+            launches.bump("p2p_broadcast")
+            flat[lo:lo + m].copy_(stage[:m])
+            self.device_barrier()                     # peers must not reuse the region before everyone copied out
+        if flat.data_ptr() != tensor.data_ptr():
+            tensor.copy_(flat.view(tensor.dtype).view(tensor.shape))
 
     def reduce_scalars(self, values):
         if self.world_size == 1:
@@ -339,7 +367,19 @@ class P2PComm(Comm):
         launches.bump("p2p_reduce_scalars")
         return self._vals[:k].clone().view(values.shape)
 
+    def device_barrier(self):
+        """All ranks have reached this point (and finished the work queued before it on the current stream): the scalar
+        all-reduce kernel is a device-side barrier - its flag exchange completes only when every rank's kernel runs.  For
+        waits that are short by construction (staging buffers); it is subject to the kernels' wait limit."""
+        if self.world_size > 1:
+            if not hasattr(self, "_bar_val"):
+                self._bar_val = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self.reduce_scalars(self._bar_val)
+            torch.cuda.current_stream().synchronize()
+
     def barrier(self):
+        """Host-level barrier (the bootstrap's gloo group): what the Trainer uses around file writes, where one rank may
+        legitimately keep the others waiting for longer than any kernel should spin."""
         if self.world_size > 1:
             torch.cuda.current_stream().synchronize()
             dist.barrier(group=self.cpu_group)
