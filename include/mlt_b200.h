@@ -113,6 +113,10 @@ long long mlt_colsum_scratch_bytes(int M, int N);
 int mlt_colsum(const void* x, int x_bf16, void* out, int out_bf16, void* scratch, long long scratch_bytes, int M, int N,
                long long ld, int accumulate, void* stream);
 int mlt_cast(const void* src, int src_bf16, void* dst, int dst_bf16, long long n, void* stream);
+/* fp32 [R, C] (row pitch ldx) -> the tripled bf16 operand of the three-term split GEMM (x = hi + lo):
+ * mode 0: out [R, 3C] = [t0 | t1 | t2] along the columns, mode 1: out [3R, C] stacked along the rows;
+ * pattern 0: (hi, hi, lo), pattern 1: (hi, lo, hi).  One operand takes pattern 0, the other pattern 1. */
+int mlt_split3_bf16(const void* x_f32, long long ldx, void* out_bf16, long long R, long long C, int mode, int pattern, void* stream);
 
 /* ---- communication runtime: replaces init_process_group + DistributedDataParallel (src/trainer.py:59,98) --------- */
 /* Symmetric arena: one VMM allocation per rank, exported as a POSIX fd, passed to the peers over unix sockets

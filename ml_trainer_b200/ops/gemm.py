@@ -244,6 +244,84 @@ def linear_packed_ok(x, wpack, bpack) -> bool:
             and (bpack is None or bpack.data.dtype == torch.bfloat16))
 
 
+def split3(x: torch.Tensor, stack_rows: bool, pattern: int) -> torch.Tensor:
+    """fp32 [R, C] -> the tripled bf16 operand of the three-term split (see csrc/elementwise.cu::split3_kernel)."""
+    R, C = x.shape
+    out = torch.empty((3 * R, C) if stack_rows else (R, 3 * C), dtype=torch.bfloat16, device=x.device)
+    check(_lib.lib().mlt_split3_bf16(ptr(x), _c_ll(x.stride(0)), ptr(out), _c_ll(R), _c_ll(C), _c_int(int(stack_rows)), _c_int(pattern),
+                                     stream_handle()), "mlt_split3_bf16")
+    launches.bump("split3_bf16")
+    return out
+
+
+class _LinearF32SplitFn(torch.autograd.Function):
+    """fp32 ``act(x W^T + b)`` on the bf16 tensor cores through the three-term split (~2^-16 relative, fp32 accumulation):
+    forward, data gradient and weight gradient are one tcgen05 GEMM each over a tripled reduction dimension.  This is what a
+    user's fp32 ``nn.Linear`` runs on instead of a cuBLAS call (reference contract: any ``nn.Module``, main.py:30)."""
+
+    @staticmethod
+    def forward(ctx, x2, weight, bias, act, wparam, bparam):
+        a = split3(x2, False, 0)                     # [M, 3K]  (hi, hi, lo)
+        b = split3(weight, False, 1)                 # [N, 3K]  (hi, lo, hi)
+        need_pre = act not in (None, "none")
+        y = gemm(a, b, False, False, out_dtype=torch.float32, bias=bias, act=None if need_pre else act, split_k=False)
+        ctx.save_for_backward(x2, weight, y if need_pre else x2.new_empty(0))
+        ctx.cfg = (act, bias is not None, need_pre)
+        ctx.params = (wparam, bparam)
+        if need_pre:                                 # the pre-activation is kept for backward; the activation itself is one pass
+            from .functional import _torch_act
+
+            return _torch_act(y, act)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .functional import _deliver, _sink, act_backward, colsum
+
+        x2, weight, pre = ctx.saved_tensors
+        act, has_bias, need_pre = ctx.cfg
+        wparam, bparam = ctx.params
+        dy = dy.contiguous().float()
+        if need_pre:
+            dy = act_backward(dy, pre, act, from_pre=True)
+        dx = None
+        if ctx.needs_input_grad[0]:                  # dX = dY W: reduce over N
+            dx = gemm(split3(dy, False, 0), split3(weight, True, 1), False, True, out_dtype=torch.float32, split_k=False)
+        wsink = _sink(wparam)
+        dw = gemm(split3(dy, True, 0), split3(x2, True, 1), True, True, out_dtype=torch.float32,     # dW = dY^T X: reduce over M
+                  out=wsink if (wsink is not None and wsink.dtype == torch.float32 and wsink.is_contiguous()) else None, split_k=False)
+        gw = _deliver(wparam, dw, wsink if (wsink is not None and wsink.dtype == torch.float32 and wsink.is_contiguous()) else None) \
+            if wparam is not None else dw
+        gb = None
+        if has_bias:
+            bsink = _sink(bparam)
+            db = colsum(dy, out=bsink)
+            gb = _deliver(bparam, db, bsink) if bparam is not None else db
+        return dx, gw, gb, None, None, None
+
+
+def f32_split_ok(x2: torch.Tensor, weight: torch.Tensor) -> bool:
+    M, K = x2.shape
+    N = weight.shape[0]
+    return (x2.is_cuda and x2.dtype == torch.float32 and weight.dtype == torch.float32 and x2.stride(1) == 1 and weight.stride(1) == 1
+            and K % 8 == 0 and N % 8 == 0 and M % 8 == 0)
+
+
+def linear_act_f32(x, weight, bias=None, act: Optional[str] = None):
+    """fp32 linear on the tensor cores (three-term bf16 split); shapes the GEMM cannot take go to the PyTorch statement."""
+    from .functional import _has_sink, _torch_act
+
+    lead = x.shape[:-1]
+    x2 = x.reshape(-1, x.shape[-1])
+    if not f32_split_ok(x2, weight) or act not in (None, "none", "relu", "tanh", "gelu"):
+        return _torch_act(TF.linear(x, weight, bias), act)
+    if _has_sink(weight, bias):
+        y = _LinearF32SplitFn.apply(x2, weight.detach(), None if bias is None else bias.detach(), act, weight, bias)
+    else:
+        y = _LinearF32SplitFn.apply(x2, weight, bias, act, None, None)
+    return y.reshape(*lead, weight.shape[0])
+
+
 def linear_act_tc(x, weight, bias=None, act: Optional[str] = None):
     """Tensor-core linear for bf16 activations/weights; anything else goes to the PyTorch statement."""
     from .functional import _has_sink
@@ -251,6 +329,8 @@ def linear_act_tc(x, weight, bias=None, act: Optional[str] = None):
     lead = x.shape[:-1]
     x2 = x.reshape(-1, x.shape[-1])
     if not (gemm_supported(x2, weight) and weight.shape[0] % 8 == 0):
+        if x2.dtype == torch.float32 and weight.dtype == torch.float32:
+            return linear_act_f32(x, weight, bias, act)         # fp32 layers: three-term bf16 split on the same tcgen05 GEMM
         y = TF.linear(x, weight, bias)
         from .functional import _torch_act
 

@@ -27,10 +27,17 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 WORLD = int(os.environ.get("MLT_TEST_WORLD", "2"))
 
 
-def run(tmp_path, *args, env=None, world=WORLD):
+def run(tmp_path, *args, env=None, world=WORLD, expect=None):
+    """Launch the worker on ``world`` ranks.  The rendezvous port is picked by probing, so another process can take it before
+    the store binds (EADDRINUSE at start-up): when the expected result file is missing the launch is repeated once."""
     e = {"MLT_LOG_LEVEL": "WARNING"}
     e.update(env or {})
-    return launch([sys.executable, os.path.join(HERE, "p2p_worker.py"), str(tmp_path), *map(str, args)], world, env_extra=e)
+    rc = 1
+    for _ in range(2):
+        rc = launch([sys.executable, os.path.join(HERE, "p2p_worker.py"), str(tmp_path), *map(str, args)], world, env_extra=e)
+        if expect is None or os.path.exists(os.path.join(str(tmp_path), expect)):
+            break
+    return rc
 
 
 @pytest.mark.parametrize("optimizer,algo,fused", [("sgd", "oneshot", 0), ("adamw", "twoshot", 0), ("sgd", "nvls", 0),
@@ -55,7 +62,7 @@ def test_ws2_p2p_matches_ddp(tmp_path, optimizer, algo, fused):
 
 
 def test_allreduce_update_kernels_vs_library(tmp_path):
-    rc = run(tmp_path, "kernels")
+    rc = run(tmp_path, "kernels", expect="kernels.json")
     rep = json.load(open(tmp_path / "kernels.json"))
     assert rc == 0 and not rep["failures"], json.dumps(rep["failures"][:4])
     algos = {r["algo"] for r in rep["report"]}
@@ -65,14 +72,14 @@ def test_allreduce_update_kernels_vs_library(tmp_path):
 
 
 def test_stress_small_collectives(tmp_path):
-    rc = run(tmp_path, "stress")
+    rc = run(tmp_path, "stress", expect="stress.json")
     rep = json.load(open(tmp_path / "stress.json"))
     assert rc == 0 and not rep["bad"] and rep["error"] is None and rep["replicas_identical"], rep
 
 
 @pytest.mark.parametrize("model,algo", [("bert_tiny", "twoshot"), ("bert_tiny", "nvls"), ("resnet_tiny", "nvls")])
 def test_bf16_models_native_vs_library_collectives(tmp_path, model, algo):
-    rc = run(tmp_path, "train", model, algo, "bf16", 0.05)
+    rc = run(tmp_path, "train", model, algo, "bf16", 0.05, expect="train.pt")
     assert rc == 0
     res = torch.load(tmp_path / "train.pt", weights_only=False)
     assert res["buckets"] >= 3, res["buckets"]
@@ -88,14 +95,14 @@ def test_bf16_models_native_vs_library_collectives(tmp_path, model, algo):
 
 @pytest.mark.parametrize("algo", ["twoshot", "nvls"])
 def test_checkpoint_under_sharded_updates(tmp_path, algo):
-    rc = run(tmp_path, "ckpt", algo, "bf16")
+    rc = run(tmp_path, "ckpt", algo, "bf16", expect="ckpt.json")
     rep = json.load(open(tmp_path / "ckpt.json"))
     assert rc == 0 and rep["ok"], json.dumps(rep)
 
 
 @pytest.mark.parametrize("model", ["mlmodel", "resnet_tiny"])
 def test_initial_state_follows_rank0(tmp_path, model):
-    rc = run(tmp_path, "init", model)
+    rc = run(tmp_path, "init", model, expect="init.json")
     rep = json.load(open(tmp_path / "init.json"))
     assert rc == 0 and rep["ok"], rep
 
