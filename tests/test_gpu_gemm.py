@@ -206,4 +206,4 @@ def test_fp32_linear_runs_on_the_tensor_cores_via_three_term_split(M, K, N, act)
     yd.backward(go.double())
     for name, got, want in (("y", y, yd), ("dx", x.grad, xd.grad), ("dw", w.grad, wd.grad), ("db", b.grad, bd.grad)):
         err = float((got.double() - want).abs().max() / (want.abs().max() + 1e-12))
-        assert err < 2e-5, (name, err)          # bf16 alone: ~4e-3, TF32: ~5e-4
+        assert err < 5e-5, (name, err)          # one bf16 product: ~4e-3, TF32: ~5e-4
