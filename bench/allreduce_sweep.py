@@ -94,6 +94,9 @@ def main():
             comm.algo = algo
             comm._oneshot_off.clear()            # every size is its own "bucket plan": start the receive-slot layout afresh
             comm._oneshot_used = 0
+            # every run starts from the same state on every rank: the sharded variants leave fp32 master / momentum current
+            # only on the owning rank, which a following one-shot run (it updates everything everywhere) would inherit
+            opt.master[:n].zero_(); opt.s1[:n].zero_(); opt.model[:n].zero_()
             t = med_time(lambda: comm.allreduce_update(opt, 0, n), a.iters)
             # values check: every replica holds bit-identical weights after the timed updates
             parts = [torch.empty_like(opt.model[:n]) for _ in range(world)]

@@ -103,9 +103,14 @@ def cmd_kernels(out_dir):
                         lo, hi = 0, opt.numel
                     comm.consolidate(opt, [_B])
                     tol = dict(rtol=2e-5, atol=2e-6) if kind == "sgd" else dict(rtol=1e-4, atol=1e-4)
+                    if kind != "sgd" and world > 2:
+                        # more than two addends: the kernels' fixed rank order and the library's tree differ in the last bit of
+                        # the sum, and Adam turns a sign flip of a ~0 gradient into a full +-lr step: compare in the mean
+                        tol = dict(rtol=1e-3, atol=3 * 2 * 0.05)
                     if algo == "nvls" and gdt == torch.bfloat16:         # the switch may round the bf16 result differently from RNE
                         tol = dict(rtol=2e-3, atol=3 * 0.05 * 8 * 2.0 ** -8)
-                    ok_master = torch.allclose(opt.master, exp_p, **tol)
+                    mean_tol = 1e-3 if (algo == "nvls" and gdt == torch.bfloat16) else 1e-4
+                    ok_master = torch.allclose(opt.master, exp_p, **tol) and float((opt.master - exp_p).abs().mean()) < mean_tol
                     # the compute-dtype weights are exactly the rounded master weights (checked after the slices were gathered)
                     ok_model = torch.equal(opt.model.float(), opt.master.to(gdt).float())
                     tol_s = dict(tol)
@@ -334,10 +339,50 @@ def cmd_fault(out_dir, fused):
     os._exit(code)                                    # no clean shutdown: the peer is gone
 
 
+# ------------------------------------------------------------------------------------------------ lenet
+def cmd_lenet(out_dir, steps="200"):
+    """The single-kernel MLModel step with its in-kernel exchange, back to back through the native executor and as one
+    multi-step launch: replicas must stay bit-identical and the loss must fall."""
+    rank, world, dev = setup()
+    n = int(steps)
+    tr = SyntheticDataset((3, 32, 32), 10, length=32 * world * n, seed=11, pool=4096)
+    va = SyntheticDataset((3, 32, 32), 10, length=64 * world, seed=12)
+    t = Trainer(build_model("mlmodel"), datasets=(tr, va), epochs=1, batch_size=32 * world, is_parallel=True, model_dir=out_dir,
+                backend="p2p", optimizer="sgd", lr=0.01, progress=False, metric=None, seed=32)
+    assert t.engine.fused is not None
+    t.train_epoch(1)
+    torch.cuda.synchronize()
+    losses = t.last_step_losses.clone()
+    same_exec = gather_equal(t.optimizer.master)
+    # one multi-step launch over a device pool (what bench.py times)
+    xp = torch.randn(64, 32, 3, 32, 32, device=dev)
+    yp = torch.randint(0, 10, (64, 32), device=dev)
+    t.optimizer.begin_step(t.reducer.grad_scale)
+    t.engine.fused.run_pool(xp, yp, n, True)
+    torch.cuda.synchronize()
+    same_pool = gather_equal(t.optimizer.master)
+    err = None
+    try:
+        t.comm.check_errors()
+    except RuntimeError as ex:
+        err = str(ex)
+    finite = bool(torch.isfinite(t.optimizer.master).all())
+    res = dict(same_after_executor=same_exec, same_after_pool=same_pool, finite=finite, error=err,
+               loss_first=float(losses[:10].mean()), loss_last=float(losses[-10:].mean()), steps=n)
+    ok = same_exec and same_pool and finite and err is None
+    oks = [None] * world
+    dist.all_gather_object(oks, (ok, res))
+    if rank == 0:
+        json.dump({"ok": all(o for o, _ in oks), "per_rank": [r for _, r in oks]}, open(os.path.join(out_dir, "lenet.json"), "w"), indent=1)
+    dist.barrier()
+    t.close()
+    return 0 if all(o for o, _ in oks) else 1
+
+
 def main():
     out_dir, cmd, args = sys.argv[1], sys.argv[2], sys.argv[3:]
     rc = {"kernels": cmd_kernels, "stress": cmd_stress, "train": cmd_train, "ckpt": cmd_ckpt, "init": cmd_init,
-          "fault": cmd_fault, "diag": cmd_diag}[cmd](out_dir, *args)
+          "fault": cmd_fault, "diag": cmd_diag, "lenet": cmd_lenet}[cmd](out_dir, *args)
     if dist.is_initialized():
         dist.destroy_process_group()
     sys.exit(rc)

@@ -71,6 +71,16 @@ def test_allreduce_update_kernels_vs_library(tmp_path):
     assert all(r["replicas_identical"] for r in rep["report"])
 
 
+def test_single_kernel_step_keeps_replicas_identical(tmp_path):
+    """MLModel's one-kernel step (in-kernel gradient exchange) back to back - through the C++ executor and as one multi-step
+    launch, as bench.py runs it: bit-identical replicas, falling loss, clean flags."""
+    rc = run(tmp_path, "lenet", 200, expect="lenet.json")
+    rep = json.load(open(tmp_path / "lenet.json"))
+    assert rc == 0 and rep["ok"], json.dumps(rep)
+    r0 = rep["per_rank"][0]
+    assert r0["loss_last"] < r0["loss_first"]
+
+
 def test_stress_small_collectives(tmp_path):
     rc = run(tmp_path, "stress", expect="stress.json")
     rep = json.load(open(tmp_path / "stress.json"))
