@@ -34,9 +34,12 @@ ALGO_IDS = {"oneshot": 0, "twoshot": 1, "nvls": 2}
 # (bf16 gradients, SGD, 20 back-to-back launches captured in one CUDA graph, max over ranks; records under profiles/).  One-shot
 # moves (N-1) S bytes per GPU and updates the whole bucket on every rank, so its range shrinks as the world grows.
 CROSSOVER = {
+    # 2 GPUs: one-shot 7-16 us up to 1 MiB (two-shot / NVLS 10-26 us), NVLS ahead from 8 MiB (38 us vs 39 / -)
     2: {"oneshot": 2 << 20, "twoshot": 4 << 20, "source": "profiles/allreduce_sweep_2gpu_r2.json"},
-    4: {"oneshot": 1 << 20, "twoshot": 2 << 20, "source": "interpolated between the 2- and 8-GPU sweeps"},
-    8: {"oneshot": 512 << 10, "twoshot": 1 << 20, "source": "profiles/allreduce_sweep_8gpu_r2.json"},
+    4: {"oneshot": 128 << 10, "twoshot": 128 << 10, "source": "between the 2- and 8-GPU sweeps (no 4-GPU box was measured)"},
+    # 8 GPUs: one-shot only wins up to 4 KiB (10 us vs 12-13); NVLS stays at 12-24 us up to 1 MiB while one-shot grows to 33 us
+    # and two-shot sits at 23-70 us, so two-shot is never the choice when the multicast object exists
+    8: {"oneshot": 4 << 10, "twoshot": 4 << 10, "source": "profiles/allreduce_sweep_8gpu_r2.json"},
 }
 
 
@@ -141,7 +144,7 @@ class P2PComm(Comm):
         if os.environ.get("MLT_ONESHOT_MAX_BYTES"):
             self.cross["oneshot"] = int(os.environ["MLT_ONESHOT_MAX_BYTES"])
         # receive-slot size: the largest bucket the one-shot variant can take (auto mode never asks for more than the crossover)
-        self.oneshot_max = int(oneshot_max_bytes or max(self.cross["oneshot"], 1 << 20))
+        self.oneshot_max = int(oneshot_max_bytes or max(self.cross["oneshot"], 2 << 20))
         self.cpu_group = dist.new_group(backend="gloo")      # host-side phases of the bootstrap only
         P2PComm._instances += 1
         self._serial = P2PComm._instances
@@ -203,9 +206,11 @@ class P2PComm(Comm):
             if self.algo == "nvls" and not self.arena.multicast:
                 return "twoshot"               # no multicast object on this node: same ownership, P2P data path
             return self.algo
+        if not self.arena.multicast:               # no NVLS: one-shot beats two-shot up to 2 MiB at 2 and at 8 GPUs (same sweeps)
+            return "oneshot" if nbytes <= min(self.oneshot_max, 2 << 20) else "twoshot"
         if nbytes <= self.oneshot_max and nbytes <= self.cross["oneshot"]:
             return "oneshot"
-        if nbytes <= self.cross["twoshot"] or not self.arena.multicast:
+        if nbytes <= self.cross["twoshot"]:
             return "twoshot"
         return "nvls"
 
