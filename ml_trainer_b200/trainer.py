@@ -392,13 +392,22 @@ class Trainer:
                     pass
         reg.clear()
 
-    def _native_loop_for(self, loader):
+    def _native_loop_for(self, loader, deep: bool = False):
         from .runtime import NativeLoop
 
         x, y = loader._backing[0], loader._backing[1]
-        key = (loader.batch_size, x[0].numel() * x.element_size(), y.element_size())
+        key = (loader.batch_size, x[0].numel() * x.element_size(), y.element_size(), deep)
+        loops = self.__dict__.setdefault("_nloops", {})
+        if key in loops:
+            self._nloop, self._nloop_key = loops[key], key
         if getattr(self, "_nloop_key", None) != key:
-            self._nloop = NativeLoop(self.device, key[0], key[1], key[2], slots=max(self.cfg.prefetch + 1, 3))
+            # The single-kernel step (393 KB batches) gets a deep ring: the host then enqueues a dozen steps ahead of the GPU,
+            # which is what absorbs a late host thread when several ranks wait for each other inside every step.  Graph-replay
+            # steps keep the shallow ring (one captured graph per slot, and ResNet batches are 38 MB each).
+            slots = max(self.cfg.prefetch + 1, 3)
+            if deep and key[0] * (key[1] + key[2]) <= (2 << 20):
+                slots = max(slots, int(os.environ.get("MLT_RING_SLOTS", "12")))
+            self._nloop = loops[key] = NativeLoop(self.device, key[0], key[1], key[2], slots=slots)
             self._nloop_key = key
         return self._nloop
 
@@ -421,7 +430,7 @@ class Trainer:
             hyper = opt.hyper_rows(nb, self.reducer.grad_scale, lrs)
             opt.step_count += nb
             opt._opt_called = True
-        loop = self._native_loop_for(loader)
+        loop = self._native_loop_for(loader, deep=True)
         x, y = loader._backing[0], loader._backing[1]
         B = loader.batch_size
         aug = getattr(loader, "_augment", None)
@@ -668,10 +677,11 @@ class Trainer:
 
     def close(self):
         self.reducer.remove()
-        if getattr(self, "_nloop", None) is not None:
-            self._nloop.close()
-            self._nloop = None
-            self._nloop_key = None
+        for lp in (self.__dict__.get("_nloops") or {}).values():
+            lp.close()
+        self.__dict__["_nloops"] = {}
+        self._nloop = None
+        self._nloop_key = None
         self._page_unlock_all()
         self.comm.close()
 
