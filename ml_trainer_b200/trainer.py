@@ -401,12 +401,12 @@ class Trainer:
         if key in loops:
             self._nloop, self._nloop_key = loops[key], key
         if getattr(self, "_nloop_key", None) != key:
-            # The single-kernel step (393 KB batches) gets a deep ring: the host then enqueues a dozen steps ahead of the GPU,
-            # which is what absorbs a late host thread when several ranks wait for each other inside every step.  Graph-replay
-            # steps keep the shallow ring (one captured graph per slot, and ResNet batches are 38 MB each).
+            # Ring depth: 3 slots.  A deeper ring (MLT_RING_SLOTS, single-kernel step only) lets the host enqueue further ahead
+            # of the GPU; measured at 8 GPUs it is SLOWER (12 slots: 118 us/step end to end, 3 slots: 100 us/step,
+            # profiles/r2/bench_ours_n8_ring{12,3}.json), so it stays an experiment switch.
             slots = max(self.cfg.prefetch + 1, 3)
             if deep and key[0] * (key[1] + key[2]) <= (2 << 20):
-                slots = max(slots, int(os.environ.get("MLT_RING_SLOTS", "12")))
+                slots = max(slots, int(os.environ.get("MLT_RING_SLOTS", "3")))
             self._nloop = loops[key] = NativeLoop(self.device, key[0], key[1], key[2], slots=slots)
             self._nloop_key = key
         return self._nloop
