@@ -32,6 +32,11 @@ def main():
         res["fwd_us"] = timeit(lambda: F.attention_fused_fwd(q, k, v, H, want_lse=True))
     out = F.attention(q, k, v, H)
     res["bwd_us"] = timeit(lambda: out.backward(go, retain_graph=True))
+    F.dropout_begin_step(q.device)
+    with torch.no_grad():
+        res["fwd_dropout_us"] = timeit(lambda: F.attention_fused_fwd(q, k, v, H, want_lse=True, drop=(0.1, 1)))
+    outd = F.attention(q, k, v, H, None, 0.1, True)
+    res["bwd_dropout_us"] = timeit(lambda: outd.backward(go, retain_graph=True))
     sp = lambda t: t.view(B, S, H, d).transpose(1, 2)
     with torch.no_grad():
         res["sdpa_fwd_us"] = timeit(lambda: torch.nn.functional.scaled_dot_product_attention(sp(q), sp(k), sp(v)))

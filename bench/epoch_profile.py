@@ -35,8 +35,16 @@ rt.NativeLoop.run_lenet = timed_fn("run_lenet", rt.NativeLoop.run_lenet)
 tr.optimizer.hyper_rows = timed_fn("hyper_rows", tr.optimizer.hyper_rows)
 tr._reduce_epoch = timed_fn("reduce_epoch", tr._reduce_epoch)
 tr._run_native_epoch = timed_fn("run_native_epoch", tr._run_native_epoch)
+import ctypes  # noqa: E402
+
+from ml_trainer_b200.ops import _lib  # noqa: E402
+
+stamps = torch.zeros(2 * K * (R + 1), dtype=torch.int64, device="cuda")
+LIB = _lib.lib()
 rows = []
 for ep in range(2, 2 + R):
+    stamps.zero_()
+    LIB.mlt_lenet_set_stamps(ctypes.c_void_p(stamps.data_ptr()), ctypes.c_int(K))
     torch.cuda.synchronize()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t = time.perf_counter()
@@ -44,7 +52,17 @@ for ep in range(2, 2 + R):
     tr.train_epoch(ep)
     e.record()
     torch.cuda.synchronize()
+    st = stamps[:2 * K].view(K, 2).cpu().double()
+    gpu = {}
+    if float(st[:, 0].min()) > 0:
+        dur = (st[:, 1] - st[:, 0]) / 1e3
+        gap = (st[1:, 0] - st[:-1, 1]) / 1e3
+        gpu = {"step_us_mean": round(dur.mean().item(), 2), "step_us_max": round(dur.max().item(), 2),
+               "gap_us_mean": round(gap.mean().item(), 2), "gap_us_max": round(gap.max().item(), 2),
+               "first_start_to_last_end_us": round(((st[-1, 1] - st[0, 0]) / 1e3).item(), 1),
+               "gaps_us": [round(g, 1) for g in gap.tolist()]}
     rows.append({"wall_us": (time.perf_counter() - t) * 1e6, "event_us": s.elapsed_time(e) * 1e3,
-                 "native": tr.last_native_stats.get("host_us")})
+                 "native": tr.last_native_stats.get("host_us"), "gpu_steps": gpu})
+LIB.mlt_lenet_set_stamps(None, ctypes.c_int(0))
 out = {"K": K, "epochs": rows, "stages_us": {k: [round(x, 1) for x in v] for k, v in stages.items()}}
 print(json.dumps(out, indent=1))

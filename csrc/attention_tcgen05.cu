@@ -48,6 +48,18 @@ constexpr int kDkvStages = 2;
 constexpr int kSmemDkv = 2 * kTile + kDkvStages * 2 * kHalf + 2 * kTile + 2 * kMaxS * 4 + 256 + 1024;
 }  // namespace fa
 
+// Dropout on the attention probabilities.  The keep / drop decision of element (sample, head, query i, key j) is one byte of a
+// 32-bit counter hash: the word belongs to the 2 x 2 block (i / 2, j / 2), byte (i & 1) * 2 + (j & 1) is the element's, and the
+// element is kept when that byte is below `thr` (keep probability thr / 256, survivors scaled by 256 / thr, so the estimate
+// stays unbiased at a drop rate quantised to 1/256).  A 2 x 2 block costs a thread one hash per two of its elements in
+// either orientation (rows are queries in the forward and dQ kernels, keys in the dK/dV kernel), and all three kernels
+// regenerate the same mask from (seed, *step, call) - nothing is stored.
+struct FaDrop {
+  const long long* step;     // device step counter (read at kernel start: a replayed CUDA graph draws fresh masks), or nullptr
+  uint32_t seed_lo, seed_hi, call, thr;
+  float scale;               // 256 / thr
+};
+
 struct FaParams {
   __nv_bfloat16* out;        // [B, S, H*64]
   float* lse;                // [B, H, S]  (natural-log sum-exp of the scaled scores)
@@ -56,6 +68,7 @@ struct FaParams {
   float scale_log2;          // (1/sqrt(d)) * log2(e)
   float scale;
   const float* kbias;        // [B, S] additive key bias in natural-log units (added to the scaled scores), or nullptr
+  FaDrop drop;
 };
 
 struct FaBwdParams {
@@ -69,6 +82,7 @@ struct FaBwdParams {
   long long ld_dqkv;          // row stride of dq, dk, dv (H * 64, or 3 * H * 64 when they are slices of one packed tensor)
   float scale_log2, scale;
   const float* kbias;         // as in FaParams
+  FaDrop drop;
 };
 
 // Optional per-CTA timeline (analysis only): 8 x int64 per CTA when a buffer has been installed.
@@ -97,6 +111,46 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+__device__ __forceinline__ uint32_t fa_mix32(uint32_t x) {
+  x = (x ^ (x >> 16)) * 0x7feb352du;
+  x = (x ^ (x >> 15)) * 0x846ca68bu;
+  return x ^ (x >> 16);
+}
+__device__ __forceinline__ uint2 fa_drop_key(const FaDrop& d) {
+  const long long step = d.step != nullptr ? *d.step : 0;
+  return make_uint2(fa_mix32(d.seed_lo ^ (d.call * 0x9E3779B9u) ^ (uint32_t)step),
+                    fa_mix32(d.seed_hi ^ (d.call * 0x85EBCA6Bu) ^ (uint32_t)((unsigned long long)step >> 32) ^ 0x5bd1e995u));
+}
+__device__ __forceinline__ uint32_t fa_drop_word(uint2 key, uint32_t idx) {
+  uint32_t x = idx ^ key.x;
+  x = (x ^ (x >> 16)) * 0x7feb352du;
+  x = (x ^ (x >> 15) ^ key.y) * 0x846ca68bu;
+  return x ^ (x >> 16);
+}
+// Keep bits of 32 consecutive keys of one query row: bit c = element (i, j0 + c); idx0 = index of block (i / 2, j0 / 2).
+__device__ __forceinline__ uint32_t fa_keep_row(uint2 key, uint32_t idx0, int odd_row, uint32_t thr) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    const uint32_t hw = fa_drop_word(key, idx0 + t) >> (odd_row * 16);
+    m |= ((hw & 0xFFu) < thr ? 1u : 0u) << (2 * t);
+    m |= (((hw >> 8) & 0xFFu) < thr ? 1u : 0u) << (2 * t + 1);
+  }
+  return m;
+}
+// Keep bits of 32 consecutive queries of one key: bit c = element (i0 + c, j); idx0 = index of block (i0 / 2, j / 2), and one
+// block row further is `stride` indices on.
+__device__ __forceinline__ uint32_t fa_keep_col(uint2 key, uint32_t idx0, uint32_t stride, int odd_col, uint32_t thr) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int t = 0; t < 16; ++t) {
+    const uint32_t w = fa_drop_word(key, idx0 + t * stride) >> (odd_col * 8);
+    m |= ((w & 0xFFu) < thr ? 1u : 0u) << (2 * t);
+    m |= (((w >> 16) & 0xFFu) < thr ? 1u : 0u) << (2 * t + 1);
+  }
+  return m;
+}
+
 // 8 consecutive bf16 of row `row` of a K-major SW128 tile: 16-byte chunk index XOR (row & 7).
 __device__ __forceinline__ void store_row_chunk(uint8_t* tile_row, int row, int chunk, const float* v) {
   uint4 pk;
@@ -121,7 +175,7 @@ __device__ __forceinline__ void store_out32(__nv_bfloat16* g, uint32_t taddr, fl
 }
 
 // ---- forward ------------------------------------------------------------------------------------------------------
-template <bool BIAS>
+template <bool BIAS, bool DROP>
 __global__ void __launch_bounds__(fa::kThreads, 2)
 attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                              const __grid_constant__ CUtensorMap tmV, const FaParams p) {
@@ -233,6 +287,12 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
     // m is the running reference maximum: of the raw scores without a bias, of the scaled + biased exponents (log2 domain) with one
     const float sl2 = p.scale_log2;
     float m = -INFINITY, l = 0.f;                       // l: this thread's half of the row sum
+    uint2 dkey = make_uint2(0u, 0u);
+    uint32_t didx = 0;                                  // hash index of this row's first 2 x 2 block
+    if (DROP) {
+      dkey = fa_drop_key(p.drop);
+      didx = ((uint32_t)(b * p.H + h) * (uint32_t)(p.S >> 1) + (uint32_t)((qt * 128 + row) >> 1)) * (uint32_t)(p.S >> 1);
+    }
     for (int hs = 0; hs < NH; ++hs) {
       const int u = hs & 1;
       mbar_wait(&s_full[u], (hs >> 1) & 1);
@@ -300,7 +360,12 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
           pv[i + 3] = fast_exp2(fmaf(__uint_as_float(r[i + 3]), sl2, off)); s3 += pv[i + 3];
         }
       }
-      l += (s0 + s1) + (s2 + s3);
+      l += (s0 + s1) + (s2 + s3);                       // the normaliser is the sum of ALL probabilities, dropped ones included
+      if (DROP) {
+        const uint32_t keep = fa_keep_row(dkey, didx + (uint32_t)((hs * 64 + hf * 32) >> 1), row & 1, p.drop.thr);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) pv[i] = ((keep >> i) & 1u) ? pv[i] : 0.f;
+      }
       mbar_wait(&p_free[u], ((hs >> 1) & 1) ^ 1);       // PV of step hs-2 no longer reads this P buffer
       uint8_t* prow = sP + u * kTile + row * 128;
 #pragma unroll
@@ -320,7 +385,7 @@ attention_fwd_tcgen05_kernel(const __grid_constant__ CUtensorMap tmQ, const __gr
     const int srow = qt * 128 + row;
     if (srow < p.S) {                                   // S % 128 == 64: the last tile's upper half is padding (TMA zero fill)
       __nv_bfloat16* orow = p.out + ((size_t)b * p.S + srow) * p.row_stride + (size_t)h * 64 + hf * 32;
-      store_out32(orow, tmem + lane_base + kColO + hf * 32, 1.0f / lt);
+      store_out32(orow, tmem + lane_base + kColO + hf * 32, (DROP ? p.drop.scale : 1.0f) / lt);
       if (hf == 0 && p.lse != nullptr)
         p.lse[((size_t)b * p.H + h) * p.S + srow] = (BIAS ? m * (1.0f / kLog2e) : m * p.scale) + logf(lt);
     }
@@ -362,7 +427,7 @@ __global__ void __launch_bounds__(256) attention_delta_kernel(const FaBwdParams 
   }
 }
 
-template <bool BIAS>
+template <bool BIAS, bool DROP>
 __global__ void __launch_bounds__(fa::kThreads, 2)
 attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                         const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
@@ -481,6 +546,14 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
       for (int i = threadIdx.x - 64; i < p.S; i += kSoftmaxThreads) s_kb[i] = p.kbias[(size_t)b * p.S + i] * kLog2e;
       softmax_bar();
     }
+    // dP = (dO V^T) * keep / (1 - p): a dropped element contributes only the -delta term
+    const float psc = DROP ? p.scale * p.drop.scale : p.scale;
+    uint2 dkey = make_uint2(0u, 0u);
+    uint32_t didx = 0;
+    if (DROP) {
+      dkey = fa_drop_key(p.drop);
+      didx = ((uint32_t)(b * p.H + h) * (uint32_t)(p.S >> 1) + (uint32_t)(srow >> 1)) * (uint32_t)(p.S >> 1);
+    }
     for (int hs = 0; hs < NH; ++hs) {
       mbar_wait(st_full, hs & 1);
       if (threadIdx.x == 64 && hs == 0) FA_DBG(4);
@@ -492,6 +565,8 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
       tc_fence_before();
       warp_arrive(st_free, lane);
       float ds[32];
+      uint32_t keep = 0xFFFFFFFFu;
+      if (DROP) keep = fa_keep_row(dkey, didx + (uint32_t)((hs * 64 + hf * 32) >> 1), row & 1, p.drop.thr);
       if (BIAS) {
         const float4* kb4 = reinterpret_cast<const float4*>(s_kb + hs * 64 + hf * 32);
 #pragma unroll
@@ -502,14 +577,16 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
           for (int e = 0; e < 4; ++e) {
             const int i = i4 * 4 + e;
             const float pr = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, kv4[e] - lse2));
-            ds[i] = pr * fmaf(__uint_as_float(rp[i]), p.scale, -dsc);
+            const float g = fmaf(__uint_as_float(rp[i]), psc, -dsc);
+            ds[i] = pr * ((!DROP || ((keep >> i) & 1u)) ? g : -dsc);
           }
         }
       } else {
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const float pr = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, -lse2));
-          ds[i] = pr * fmaf(__uint_as_float(rp[i]), p.scale, -dsc);
+          const float g = fmaf(__uint_as_float(rp[i]), psc, -dsc);
+          ds[i] = pr * ((!DROP || ((keep >> i) & 1u)) ? g : -dsc);
         }
       }
       mbar_wait(ds_free, (hs & 1) ^ 1);
@@ -532,7 +609,7 @@ attention_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
   if (threadIdx.x == 32) FA_DBG(7);
 }
 
-template <bool BIAS>
+template <bool BIAS, bool DROP>
 __global__ void __launch_bounds__(fa::kThreads, 2)
 attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                           const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmdO,
@@ -655,6 +732,14 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     const bool live = krow < p.S;
     // rows are keys here: the key bias is one number per thread (a padded-out key row gets a bias that zeroes its P)
     const float kb = live ? (BIAS ? p.kbias[(size_t)b * p.S + krow] * kLog2e : 0.f) : -3.0e4f;
+    const float psc = DROP ? p.scale * p.drop.scale : p.scale;
+    const uint32_t S2 = (uint32_t)(p.S >> 1);
+    uint2 dkey = make_uint2(0u, 0u);
+    uint32_t didx = 0;                                        // hash index of block (query 0, this key / 2)
+    if (DROP) {
+      dkey = fa_drop_key(p.drop);
+      didx = (uint32_t)(b * p.H + h) * S2 * S2 + (uint32_t)(krow >> 1);
+    }
     for (int hs = 0; hs < NH; ++hs) {
       mbar_wait(st_full, hs & 1);
       tc_fence_after();
@@ -675,7 +760,21 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
         for (int e = 0; e < 4; ++e) {
           const int i = i4 * 4 + e;
           pr[i] = fast_exp2(fmaf(__uint_as_float(rs[i]), p.scale_log2, kb - lv[e]));
-          ds[i] = pr[i] * fmaf(__uint_as_float(rp[i]), p.scale, -dv[e]);
+          ds[i] = pr[i] * fmaf(__uint_as_float(rp[i]), psc, -dv[e]);
+        }
+      }
+      if (DROP) {      // dropped elements: dS keeps only the -delta term, and P^T (the dV operand) is zero there
+        const uint32_t keep = fa_keep_col(dkey, didx + (uint32_t)((hs * 64 + hf * 32) >> 1) * S2, S2, row & 1, p.drop.thr);
+        const float4* d4b = reinterpret_cast<const float4*>(s_dsc + hs * 64 + hf * 32);
+#pragma unroll
+        for (int i4 = 0; i4 < 8; ++i4) {
+          const float4 dq = d4b[i4];
+          const float dv[4] = {dq.x, dq.y, dq.z, dq.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int i = i4 * 4 + e;
+            if (!((keep >> i) & 1u)) { ds[i] = -pr[i] * dv[e]; pr[i] = 0.f; }
+          }
         }
       }
       mbar_wait(pd_free, (hs & 1) ^ 1);
@@ -691,7 +790,7 @@ attention_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_
     tc_fence_after();
     if (live) {
       const size_t goff = ((size_t)b * p.S + krow) * p.ld_dqkv + (size_t)h * 64 + hf * 32;
-      store_out32(p.dv + goff, tmem + lane_base + kColdV + hf * 32, 1.0f);
+      store_out32(p.dv + goff, tmem + lane_base + kColdV + hf * 32, DROP ? p.drop.scale : 1.0f);
       store_out32(p.dk + goff, tmem + lane_base + kColdK + hf * 32, 1.0f);
     }
   }
@@ -729,19 +828,35 @@ static int fa_make_map(CUtensorMap* m, const void* base, int S, int H, int B, lo
   return 0;
 }
 
+template <bool BIAS, bool DROP>
+static cudaError_t fa_set_attrs_for() {
+  cudaError_t e = cudaFuncSetAttribute(attention_fwd_tcgen05_kernel<BIAS, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemFwd);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_bwd_dq_kernel<BIAS, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDq);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_bwd_dkdv_kernel<BIAS, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDkv);
+  return e;
+}
+
 static int fa_set_attrs() {
   static bool attr_set[64] = {};
   int dev = 0;
   MLT_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_tcgen05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemFwd));
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_tcgen05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemFwd));
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dq_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDq));
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dq_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDq));
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dkdv_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDkv));
-    MLT_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_dkdv_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::kSmemDkv));
+    MLT_CHECK_CUDA((fa_set_attrs_for<false, false>()));
+    MLT_CHECK_CUDA((fa_set_attrs_for<true, false>()));
+    MLT_CHECK_CUDA((fa_set_attrs_for<false, true>()));
+    MLT_CHECK_CUDA((fa_set_attrs_for<true, true>()));
     attr_set[dev & 63] = true;
   }
+  return 0;
+}
+
+static int fa_fill_drop(FaDrop* d, float p_drop, unsigned long long seed, const void* step_ptr, unsigned int call_id) {
+  MLT_REQUIRE(p_drop >= 0.f && p_drop < 1.f, "attention: dropout probability %f must be in [0, 1)", (double)p_drop);
+  int thr = (int)lrintf((1.0f - p_drop) * 256.0f);
+  thr = thr < 1 ? 1 : (thr > 256 ? 256 : thr);
+  d->step = (const long long*)step_ptr;
+  d->seed_lo = (uint32_t)seed; d->seed_hi = (uint32_t)(seed >> 32); d->call = call_id;
+  d->thr = (uint32_t)thr; d->scale = 256.0f / (float)thr;
   return 0;
 }
 
@@ -759,8 +874,11 @@ extern "C" int mlt_attention_set_debug(void* buf) {
 // q, k, v: [B, S, H*64] bf16 with row stride ld_qkv (0 = H*64; 3*H*64 for slices of a packed QKV projection);
 // out: [B, S, H*64] bf16;  lse: [B, H, S] fp32 or NULL.  key_bias: NULL, or [B, S] fp32 added to every score of that key after
 // the 1/sqrt(d) scaling (HuggingFace's extended attention mask: 0 for tokens, a large negative number for padding).
-extern "C" int mlt_attention_fwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, void* out,
-                                        void* lse, int B, int S, int H, int D, void* stream) {
+// p_drop > 0: dropout on the probabilities inside the kernel (FaDrop above); the mask is a function of (seed, *step_ptr, call_id)
+// and the backward call must be given the same three.
+extern "C" int mlt_attention_fwd_ex(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, void* out,
+                                    void* lse, int B, int S, int H, int D, float p_drop, unsigned long long seed, const void* step_ptr,
+                                    unsigned int call_id, void* stream) {
   MLT_REQUIRE(D == 64, "mlt_attention_fwd: head dim %d unsupported (64)", D);
   MLT_REQUIRE(S % 64 == 0 && S >= 64 && S <= fa::kMaxS, "mlt_attention_fwd: sequence length %d unsupported (64..512, multiple of 64)", S);
   MLT_REQUIRE(((uintptr_t)q % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0 && ((uintptr_t)out % 16) == 0,
@@ -775,12 +893,22 @@ extern "C" int mlt_attention_fwd_masked(const void* q, const void* k, const void
   p.scale = 1.0f / sqrtf((float)D);
   p.scale_log2 = p.scale * fa::kLog2e;
   p.kbias = (const float*)key_bias;
+  if (fa_fill_drop(&p.drop, p_drop, seed, step_ptr, call_id)) return 1;
   if (fa_set_attrs()) return 1;
   dim3 grid((S + 127) / 128, H, B);
-  if (key_bias) attention_fwd_tcgen05_kernel<true><<<grid, fa::kThreads, fa::kSmemFwd, (cudaStream_t)stream>>>(tq, tk, tv, p);
-  else attention_fwd_tcgen05_kernel<false><<<grid, fa::kThreads, fa::kSmemFwd, (cudaStream_t)stream>>>(tq, tk, tv, p);
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool drop = p_drop > 0.f;
+#define MLT_FA_FWD(BIAS, DROP) attention_fwd_tcgen05_kernel<BIAS, DROP><<<grid, fa::kThreads, fa::kSmemFwd, st>>>(tq, tk, tv, p)
+  if (key_bias) { if (drop) MLT_FA_FWD(true, true); else MLT_FA_FWD(true, false); }
+  else { if (drop) MLT_FA_FWD(false, true); else MLT_FA_FWD(false, false); }
+#undef MLT_FA_FWD
   MLT_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int mlt_attention_fwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, void* out,
+                                        void* lse, int B, int S, int H, int D, void* stream) {
+  return mlt_attention_fwd_ex(q, k, v, ld_qkv, key_bias, out, lse, B, S, H, D, 0.f, 0ull, nullptr, 0u, stream);
 }
 
 extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, long long ld_qkv, void* out, void* lse, int B, int S,
@@ -790,9 +918,10 @@ extern "C" int mlt_attention_fwd(const void* q, const void* k, const void* v, lo
 
 // Backward of mlt_attention_fwd[_masked].  out / lse are the forward's results, dout the gradient of out; delta is a [B, H, S] fp32
 // scratch the call fills.  dq, dk, dv: [B, S, H*64] bf16 with row stride ld_dqkv (0 = H*64).  key_bias as in the forward.
-extern "C" int mlt_attention_bwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias,
-                                        const void* out, const void* dout, const void* lse, void* delta, void* dq, void* dk, void* dv,
-                                        long long ld_dqkv, int B, int S, int H, int D, void* stream) {
+extern "C" int mlt_attention_bwd_ex(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias,
+                                    const void* out, const void* dout, const void* lse, void* delta, void* dq, void* dk, void* dv,
+                                    long long ld_dqkv, int B, int S, int H, int D, float p_drop, unsigned long long seed,
+                                    const void* step_ptr, unsigned int call_id, void* stream) {
   MLT_REQUIRE(D == 64, "mlt_attention_bwd: head dim %d unsupported (64)", D);
   MLT_REQUIRE(S % 64 == 0 && S >= 64 && S <= fa::kMaxS, "mlt_attention_bwd: sequence length %d unsupported (64..512, multiple of 64)", S);
   const void* al[] = {q, k, v, out, dout, dq, dk, dv};
@@ -811,23 +940,32 @@ extern "C" int mlt_attention_bwd_masked(const void* q, const void* k, const void
   p.scale = 1.0f / sqrtf((float)D);
   p.scale_log2 = p.scale * fa::kLog2e;
   p.kbias = (const float*)key_bias;
+  if (fa_fill_drop(&p.drop, p_drop, seed, step_ptr, call_id)) return 1;
   if (fa_set_attrs()) return 1;
   cudaStream_t st = (cudaStream_t)stream;
   const long long dthreads = (long long)B * S * H * 8;
   attention_delta_kernel<<<(unsigned)((dthreads + 255) / 256), 256, 0, st>>>(p);
   MLT_LAUNCH_CHECK();
   dim3 grid((S + 127) / 128, H, B);
-  if (key_bias) {
-    attention_bwd_dq_kernel<true><<<grid, fa::kThreads, fa::kSmemDq, st>>>(tq, tk64, tv64, tdo, p);
-    MLT_LAUNCH_CHECK();
-    attention_bwd_dkdv_kernel<true><<<grid, fa::kThreads, fa::kSmemDkv, st>>>(tq64, tk, tv, tdo64, p);
-  } else {
-    attention_bwd_dq_kernel<false><<<grid, fa::kThreads, fa::kSmemDq, st>>>(tq, tk64, tv64, tdo, p);
-    MLT_LAUNCH_CHECK();
-    attention_bwd_dkdv_kernel<false><<<grid, fa::kThreads, fa::kSmemDkv, st>>>(tq64, tk, tv, tdo64, p);
-  }
+  const bool drop = p_drop > 0.f;
+#define MLT_FA_BWD(BIAS, DROP)                                                                                       \
+  do {                                                                                                               \
+    attention_bwd_dq_kernel<BIAS, DROP><<<grid, fa::kThreads, fa::kSmemDq, st>>>(tq, tk64, tv64, tdo, p);            \
+    MLT_LAUNCH_CHECK();                                                                                              \
+    attention_bwd_dkdv_kernel<BIAS, DROP><<<grid, fa::kThreads, fa::kSmemDkv, st>>>(tq64, tk, tv, tdo64, p);         \
+  } while (0)
+  if (key_bias) { if (drop) MLT_FA_BWD(true, true); else MLT_FA_BWD(true, false); }
+  else { if (drop) MLT_FA_BWD(false, true); else MLT_FA_BWD(false, false); }
+#undef MLT_FA_BWD
   MLT_LAUNCH_CHECK();
   return 0;
+}
+
+extern "C" int mlt_attention_bwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias,
+                                        const void* out, const void* dout, const void* lse, void* delta, void* dq, void* dk, void* dv,
+                                        long long ld_dqkv, int B, int S, int H, int D, void* stream) {
+  return mlt_attention_bwd_ex(q, k, v, ld_qkv, key_bias, out, dout, lse, delta, dq, dk, dv, ld_dqkv, B, S, H, D, 0.f, 0ull, nullptr, 0u,
+                              stream);
 }
 
 extern "C" int mlt_attention_bwd(const void* q, const void* k, const void* v, long long ld_qkv, const void* out, const void* dout,

@@ -620,6 +620,16 @@ constexpr int CS = 4;                       // CTAs per sample
 
 // Optional per-CTA timeline (analysis only): 16 x int64 per CTA of %globaltimer stamps when a buffer has been installed.
 __device__ long long* g_lenet_dbg = nullptr;
+// Optional per-STEP stamps (analysis only, bench/epoch_profile.py): CTA 0 appends {step start, step end} in %globaltimer
+// nanoseconds to g_lenet_stamps (capacity g_lenet_stamp_cap pairs); [0] of the counter is the number of steps stamped so far.
+__device__ long long* g_lenet_stamps = nullptr;
+__device__ unsigned int g_lenet_stamp_cap = 0;
+__device__ unsigned int g_lenet_stamp_n = 0;
+__device__ __forceinline__ long long ln_gtimer() {
+  long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 #ifndef MLT_LENET_TIMELINE
 #define LN_DBG(slot) do { (void)ln_dbg; } while (0)
 #else
@@ -763,6 +773,11 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     }
     if (a.hyper_table) cur_hyper = a.hyper_table + step;
     if (a.loss_base) cur_loss = a.loss_base + step;
+  }
+  unsigned int stamp_at = 0xFFFFFFFFu;
+  if (blockIdx.x == 0 && tid == 0 && g_lenet_stamps != nullptr) {
+    stamp_at = atomicAdd(&g_lenet_stamp_n, 1u);
+    if (stamp_at < g_lenet_stamp_cap) g_lenet_stamps[2 * stamp_at] = ln_gtimer(); else stamp_at = 0xFFFFFFFFu;
   }
   if (cluster_id < cur_B) {
     for (int i = tid; i < W1N; i += kThreads) w1s[i] = Wc1[i];
@@ -1113,6 +1128,7 @@ lenet_step_cluster_kernel(const LeNetArgs a) {
     // (no system fence: the host only uses the word to know the step's INPUT slot has been read; losses are read after the run)
     if (blockIdx.x == 0 && tid == 0 && a.progress) *reinterpret_cast<volatile unsigned int*>(a.progress) = (unsigned int)(step + 1);
   }
+  if (stamp_at != 0xFFFFFFFFu) g_lenet_stamps[2 * stamp_at + 1] = ln_gtimer();
   }  // step loop
 }
 
@@ -1277,6 +1293,17 @@ extern "C" int mlt_lenet_steps(void* master, void* s1, void* s2, const void* hyp
     a.comm.mc_flags = (ctx->mc_flags != 0 && ctx->mc_base != nullptr) ? 1 : 0;
   }
   return lenet_launch(a, rule, numel, stream);
+}
+
+// Analysis hook: device buffer of `pairs` x 2 int64 that CTA 0 of the step kernel fills with {start, end} %globaltimer stamps, one
+// pair per training step in launch order (NULL clears it and resets the count).
+extern "C" int mlt_lenet_set_stamps(void* buf, int pairs) {
+  long long* b = (long long*)buf;
+  unsigned int cap = buf ? (unsigned int)pairs : 0u, zero = 0u;
+  MLT_CHECK_CUDA(cudaMemcpyToSymbol(mlt::g_lenet_stamps, &b, sizeof(b)));
+  MLT_CHECK_CUDA(cudaMemcpyToSymbol(mlt::g_lenet_stamp_cap, &cap, sizeof(cap)));
+  MLT_CHECK_CUDA(cudaMemcpyToSymbol(mlt::g_lenet_stamp_n, &zero, sizeof(zero)));
+  return 0;
 }
 
 // Analysis hook: device buffer of 16 int64 per CTA that the cluster kernel fills with %globaltimer stamps (NULL clears it).

@@ -244,7 +244,7 @@ int mlt_softmax_rows(void* scores_bf16, long long rows, int L, float scale, void
 int mlt_softmax_rows_bwd(void* dp_bf16, const void* p_bf16, long long rows, int L, float scale, void* stream);
 /* Fused attention on tcgen05 (scores never leave the SM).  q, k, v: [B, S, H*64] bf16 with row stride ld_qkv elements
  * (0 = H*64; 3*H*64 when they are column slices of a packed QKV projection); out [B, S, H*64] bf16; lse [B, H, S] fp32 or
- * NULL.  Head dim 64, S a multiple of 128 up to 512, no mask. */
+ * NULL.  Head dim 64, S a multiple of 64 up to 512, no mask. */
 int mlt_attention_fwd(const void* q, const void* k, const void* v, long long ld_qkv, void* out, void* lse, int B, int S, int H,
                       int D, void* stream);
 /* Its backward: out / lse from the forward, dout the gradient of out, delta a [B, H, S] fp32 scratch; dq, dk, dv bf16 with
@@ -252,7 +252,6 @@ int mlt_attention_fwd(const void* q, const void* k, const void* v, long long ld_
 int mlt_attention_bwd(const void* q, const void* k, const void* v, long long ld_qkv, const void* out, const void* dout,
                       const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B, int S, int H, int D,
                       void* stream);
-/* Analysis hook: device buffer of 8 int64 per CTA that the dQ kernel fills with %globaltimer stamps (NULL clears it). */
 /* The same with a key-padding mask: key_bias [B, S] fp32 (NULL = none) is added to every score of that key after the 1/sqrt(d)
  * scaling - HuggingFace's extended attention mask (0 for tokens, a large negative number for padding).  S: multiple of 64, <= 512. */
 int mlt_attention_fwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, void* out, void* lse,
@@ -260,6 +259,17 @@ int mlt_attention_fwd_masked(const void* q, const void* k, const void* v, long l
 int mlt_attention_bwd_masked(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, const void* out,
                              const void* dout, const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B,
                              int S, int H, int D, void* stream);
+/* The same with dropout on the attention probabilities drawn inside the kernels (p_drop in [0, 1), resolution 1/256; 0 = none).
+ * The mask is a counter hash of (seed, *step_ptr, call_id, sample, head, query, key): nothing is stored, and the backward call
+ * regenerates it from the same three values.  step_ptr: device int64 (NULL = 0), read when the kernel starts. */
+int mlt_attention_fwd_ex(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, void* out, void* lse,
+                         int B, int S, int H, int D, float p_drop, unsigned long long seed, const void* step_ptr,
+                         unsigned int call_id, void* stream);
+int mlt_attention_bwd_ex(const void* q, const void* k, const void* v, long long ld_qkv, const void* key_bias, const void* out,
+                         const void* dout, const void* lse, void* delta, void* dq, void* dk, void* dv, long long ld_dqkv, int B,
+                         int S, int H, int D, float p_drop, unsigned long long seed, const void* step_ptr, unsigned int call_id,
+                         void* stream);
+/* Analysis hook: device buffer of 8 int64 per CTA that the dQ kernel fills with %globaltimer stamps (NULL clears it). */
 int mlt_attention_set_debug(void* buf);
 /* Implicit-GEMM convolution on tcgen05 for NHWC bf16 tensors with Cin a multiple of 64: the patch matrix is never written,
  * operand tiles are gathered by TMA im2col loads.  w2 / dw: [Co, KH*KW*Cin]. */
@@ -292,6 +302,8 @@ int mlt_lenet_steps(void* master, void* s1, void* s2, const void* hyper, long lo
                     const void* hyper_table, void* loss_base, const void* ready, void* progress, int nsteps, int train,
                     int want_acc, void* acc3, void* scratch, long long scratch_bytes, const mlt_p2p_ctx* ctx, void* stream);
 int mlt_lenet_set_debug(void* buf);
+/* Analysis hook: {start, end} %globaltimer stamps of every training step (CTA 0), `pairs` x 2 int64 on the device; NULL clears. */
+int mlt_lenet_set_stamps(void* buf, int pairs);
 int mlt_embedding_sum_fwd(const void* ids_i64, const void* word, const void* pos, const void* type, int params_bf16,
                           void* out_bf16, int T, int S, int H, void* stream);
 /* the same, with the row count V of the word table: ids outside [0, V) are clamped instead of read / written out of bounds */

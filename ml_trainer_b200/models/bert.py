@@ -6,12 +6,11 @@ base config with 2 labels), so state dicts move between the two implementations 
 HF model is the numerical oracle in the tests.  Forward takes ``input_ids [B, S]`` and returns logits.
 
 Hot ops ("BERT-base"): QKV / output / FFN GEMMs on tcgen05 with bias (+GELU, +pre-activation
-for backward) in the epilogue, Q/K/V as ONE packed projection; fused tcgen05 flash attention; residual+LayerNorm fused;
-embedding gather-sum.  Dropout is identity here (p = 0): the benchmark configures the reference the same way.
+for backward) in the epilogue, Q/K/V as ONE packed projection; fused tcgen05 flash attention (key-padding mask and
+dropout on the probabilities inside the kernel); residual+LayerNorm fused; embedding gather-sum.  Both dropout rates default
+to 0: the benchmark configures the reference the same way.
 """
 from __future__ import annotations
-
-import math
 
 import torch
 from torch import nn
@@ -77,37 +76,16 @@ class BertSelfAttention(nn.Module):
     def forward(self, x, mask_bias=None):
         from ..ops.gemm import linear_packed, linear_packed_ok
 
-        if self.p_attn > 0.0 and self.training:
-            return self._forward_with_prob_dropout(x, mask_bias)
-        # the key-padding mask rides into the fused kernels as a per-key additive bias (csrc/attention_tcgen05.cu)
+        # the key-padding mask rides into the fused kernels as a per-key additive bias, and dropout on the probabilities is
+        # drawn inside them from a counter hash (csrc/attention_tcgen05.cu): P never leaves the SM in either case
         wpack = getattr(self.query.weight, "_mlt_packed", None)
         bpack = getattr(self.query.bias, "_mlt_packed", None)
         if bpack is not None and linear_packed_ok(x, wpack, bpack):
-            return F.attention_packed(linear_packed(x, wpack, bpack), self.heads, mask_bias)
+            return F.attention_packed(linear_packed(x, wpack, bpack), self.heads, mask_bias, self.p_attn, self.training)
         q = F.linear_act(x, self.query.weight, self.query.bias)
         k = F.linear_act(x, self.key.weight, self.key.bias)
         v = F.linear_act(x, self.value.weight, self.value.bias)
-        return F.attention(q, k, v, self.heads, mask_bias)
-
-
-def _attn_prob_dropout(self, x, mask_bias=None):
-    """Attention with dropout on the probabilities (and optionally a key-padding mask).  The fused kernels keep P on chip and
-    do not draw a dropout mask, so this configuration (not used by the benchmark: both arms run with dropout 0) materialises
-    P: projections on the tensor cores, softmax / Philox dropout / PV as batched ops."""
-    B, S, HD = x.shape
-    d = HD // self.heads
-    q = F.linear_act(x, self.query.weight, self.query.bias).view(B, S, self.heads, d).transpose(1, 2)
-    k = F.linear_act(x, self.key.weight, self.key.bias).view(B, S, self.heads, d).transpose(1, 2)
-    v = F.linear_act(x, self.value.weight, self.value.bias).view(B, S, self.heads, d).transpose(1, 2)
-    scores = (q @ k.transpose(-1, -2)).float() / math.sqrt(d)
-    if mask_bias is not None:
-        scores = scores + mask_bias.reshape(B, 1, 1, S)  # additive bias: 0 keep, large negative = padding
-    p = torch.softmax(scores, dim=-1).to(x.dtype)
-    p = F.dropout(p, self.p_attn, self.training)
-    return (p @ v).transpose(1, 2).reshape(B, S, HD)
-
-
-BertSelfAttention._forward_with_prob_dropout = _attn_prob_dropout
+        return F.attention(q, k, v, self.heads, mask_bias, self.p_attn, self.training)
 
 
 class BertSelfOutput(nn.Module):

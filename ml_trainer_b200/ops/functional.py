@@ -504,10 +504,12 @@ def dropout_seed(seed: int) -> None:
 
 
 def _drop_step(device: torch.device) -> torch.Tensor:
-    t = _drop["step"].get(device.index)
+    device = torch.device(device)
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    t = _drop["step"].get(idx)
     if t is None:
         t = torch.zeros(1, dtype=torch.int64, device=device)
-        _drop["step"][device.index] = t
+        _drop["step"][idx] = t
     return t
 
 
@@ -748,11 +750,59 @@ def prepare_key_bias(attention_mask: torch.Tensor) -> torch.Tensor:
     return kb
 
 
-def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False, key_bias=None):
+def _drop_args(drop, device):
+    """ctypes tail ``(p, seed, step_ptr, call_id)`` of the ``_ex`` attention entry points; ``drop`` is None or ``(p, call_id)``."""
+    if drop is None:
+        return ctypes.c_float(0.0), ctypes.c_ulonglong(0), None, ctypes.c_uint(0)
+    return ctypes.c_float(drop[0]), ctypes.c_ulonglong(_drop["seed"]), ptr(_drop_step(device)), ctypes.c_uint(drop[1])
+
+
+def _new_drop(p_drop: float, training: bool):
+    """A fresh call site for in-kernel attention dropout, or None when dropout is off."""
+    if not training or p_drop <= 0.0:
+        return None
+    _drop["call"] += 1
+    return (float(p_drop), _drop["call"])
+
+
+def _mix32(x: torch.Tensor) -> torch.Tensor:
+    M = 0xFFFFFFFF
+    x = ((x ^ (x >> 16)) * 0x7FEB352D) & M
+    x = ((x ^ (x >> 15)) * 0x846CA68B) & M
+    return x ^ (x >> 16)
+
+
+def attention_keep_mask(B: int, heads: int, S: int, p_drop: float, call_id: int, step: int = None, seed: int = None,
+                        device="cpu") -> tuple:
+    """Host statement of the mask the fused attention kernels draw (csrc/attention_tcgen05.cu, ``FaDrop``): returns
+    ``(keep [B, heads, S, S] bool, scale)`` with ``scale = 256 / thr``.  Used by the tests as the oracle's mask."""
+    M = 0xFFFFFFFF
+    seed = _drop["seed"] if seed is None else seed
+    if step is None:
+        step = int(_drop_step(device).item()) if torch.device(device).type == "cuda" else 0
+    thr = min(max(int(round((1.0 - p_drop) * 256.0)), 1), 256)
+    as_t = lambda v: torch.tensor(v & M, dtype=torch.int64)
+    k0 = _mix32(as_t((seed & M) ^ ((call_id * 0x9E3779B9) & M) ^ (step & M)))
+    k1 = _mix32(as_t(((seed >> 32) & M) ^ ((call_id * 0x85EBCA6B) & M) ^ ((step >> 32) & M) ^ 0x5BD1E995))
+    S2 = S // 2
+    bh = torch.arange(B * heads, dtype=torch.int64).view(-1, 1, 1)
+    i = torch.arange(S, dtype=torch.int64).view(1, -1, 1)
+    j = torch.arange(S, dtype=torch.int64).view(1, 1, -1)
+    idx = (((bh * S2 + (i >> 1)) & M) * S2 + (j >> 1)) & M
+    x = idx ^ k0
+    x = ((x ^ (x >> 16)) * 0x7FEB352D) & M
+    x = ((x ^ (x >> 15) ^ k1) * 0x846CA68B) & M
+    x = x ^ (x >> 16)
+    byte = (x >> (((i & 1) * 2 + (j & 1)) * 8)) & 0xFF
+    return (byte < thr).view(B, heads, S, S).to(device), 256.0 / thr
+
+
+def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False, key_bias=None, drop=None):
     """Fused tcgen05 attention forward (csrc/attention_tcgen05.cu).  Returns ``out`` or ``(out, lse)``.
 
     q, k, v may be column slices of one packed ``[B, S, 3*H*d]`` projection (no copy is made).  ``key_bias``: optional
-    ``[B, S]`` additive bias per key (0 for tokens, a large negative number for padding), added after the 1/sqrt(d) scaling."""
+    ``[B, S]`` additive bias per key (0 for tokens, a large negative number for padding), added after the 1/sqrt(d) scaling.
+    ``drop``: None, or ``(p, call_id)`` for dropout on the probabilities drawn inside the kernel."""
     B, S, HD = q.shape
     ld = _qkv_ld(q, k, v)
     if ld is None:
@@ -760,21 +810,22 @@ def attention_fused_fwd(q, k, v, heads: int, want_lse: bool = False, key_bias=No
         ld = HD
     out = torch.empty((B, S, HD), dtype=q.dtype, device=q.device)
     lse = torch.empty((B, heads, S), dtype=torch.float32, device=q.device) if want_lse else None
-    check(_lib.lib().mlt_attention_fwd_masked(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(key_bias), ptr(out), ptr(lse), _c_int(B), _c_int(S),
-                                              _c_int(heads), _c_int(HD // heads), stream_handle()), "mlt_attention_fwd")
+    check(_lib.lib().mlt_attention_fwd_ex(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(key_bias), ptr(out), ptr(lse), _c_int(B), _c_int(S),
+                                          _c_int(heads), _c_int(HD // heads), *_drop_args(drop, q.device), stream_handle()),
+          "mlt_attention_fwd")
     launches.bump("attention_fwd_tcgen05")
     return (out, lse) if want_lse else out
 
 
-def _attention_bwd(q, k, v, out, lse, do, heads, dq, dk, dv, key_bias=None):
+def _attention_bwd(q, k, v, out, lse, do, heads, dq, dk, dv, key_bias=None, drop=None):
     B, S, HD = q.shape
     ld = _qkv_ld(q, k, v)
     ldd = _qkv_ld(dq, dk, dv)
     assert ld is not None and ldd is not None
     delta = torch.empty_like(lse)
-    check(_lib.lib().mlt_attention_bwd_masked(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(key_bias), ptr(out), ptr(do), ptr(lse), ptr(delta),
-                                              ptr(dq), ptr(dk), ptr(dv), _c_ll(ldd), _c_int(B), _c_int(S), _c_int(heads),
-                                              _c_int(HD // heads), stream_handle()), "mlt_attention_bwd")
+    check(_lib.lib().mlt_attention_bwd_ex(ptr(q), ptr(k), ptr(v), _c_ll(ld), ptr(key_bias), ptr(out), ptr(do), ptr(lse), ptr(delta),
+                                          ptr(dq), ptr(dk), ptr(dv), _c_ll(ldd), _c_int(B), _c_int(S), _c_int(heads),
+                                          _c_int(HD // heads), *_drop_args(drop, q.device), stream_handle()), "mlt_attention_bwd")
     launches.bump("attention_bwd_tcgen05", 3)
 
 
@@ -783,19 +834,19 @@ class _FusedAttentionFn(torch.autograd.Function):
     (csrc/attention_tcgen05.cu: delta, dQ and dK/dV kernels, no atomics)."""
 
     @staticmethod
-    def forward(ctx, q, k, v, heads, key_bias=None):
+    def forward(ctx, q, k, v, heads, key_bias=None, drop=None):
         q, k, v = q.contiguous(), k.contiguous(), v.contiguous()
-        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True, key_bias=key_bias)
+        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True, key_bias=key_bias, drop=drop)
         ctx.save_for_backward(q, k, v, out, lse)
-        ctx.heads, ctx.key_bias = heads, key_bias
+        ctx.heads, ctx.key_bias, ctx.drop = heads, key_bias, drop
         return out
 
     @staticmethod
     def backward(ctx, do):
         q, k, v, out, lse = ctx.saved_tensors
         dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
-        _attention_bwd(q, k, v, out, lse, do.contiguous(), ctx.heads, dq, dk, dv, ctx.key_bias)
-        return dq, dk, dv, None, None
+        _attention_bwd(q, k, v, out, lse, do.contiguous(), ctx.heads, dq, dk, dv, ctx.key_bias, ctx.drop)
+        return dq, dk, dv, None, None, None
 
 
 class _PackedAttentionFn(torch.autograd.Function):
@@ -803,12 +854,12 @@ class _PackedAttentionFn(torch.autograd.Function):
     written straight into one packed gradient, so neither direction needs a split or a concat."""
 
     @staticmethod
-    def forward(ctx, qkv, heads, key_bias=None):
+    def forward(ctx, qkv, heads, key_bias=None, drop=None):
         HD = qkv.shape[-1] // 3
         q, k, v = qkv[..., :HD], qkv[..., HD:2 * HD], qkv[..., 2 * HD:]
-        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True, key_bias=key_bias)
+        out, lse = attention_fused_fwd(q, k, v, heads, want_lse=True, key_bias=key_bias, drop=drop)
         ctx.save_for_backward(qkv, out, lse)
-        ctx.heads, ctx.key_bias = heads, key_bias
+        ctx.heads, ctx.key_bias, ctx.drop = heads, key_bias, drop
         return out
 
     @staticmethod
@@ -817,21 +868,23 @@ class _PackedAttentionFn(torch.autograd.Function):
         HD = qkv.shape[-1] // 3
         dqkv = torch.empty_like(qkv)
         _attention_bwd(qkv[..., :HD], qkv[..., HD:2 * HD], qkv[..., 2 * HD:], out, lse, do.contiguous(), ctx.heads,
-                       dqkv[..., :HD], dqkv[..., HD:2 * HD], dqkv[..., 2 * HD:], ctx.key_bias)
-        return dqkv, None, None
+                       dqkv[..., :HD], dqkv[..., HD:2 * HD], dqkv[..., 2 * HD:], ctx.key_bias, ctx.drop)
+        return dqkv, None, None, None
 
 
-def attention_packed(qkv, heads: int, key_bias=None):
-    """Self-attention core on a packed projection ``[B, S, 3*H*d]`` (q | k | v along the last dim)."""
+def attention_packed(qkv, heads: int, key_bias=None, p_drop: float = 0.0, training: bool = False):
+    """Self-attention core on a packed projection ``[B, S, 3*H*d]`` (q | k | v along the last dim).  ``p_drop``: dropout on the
+    attention probabilities (active when ``training``), drawn inside the fused kernels."""
     HD = qkv.shape[-1] // 3
     q = qkv[..., :HD]
     if (use_native(qkv) and qkv.dtype == torch.bfloat16 and qkv.is_contiguous() and fused_attention_ok(q, heads)
             and qkv.data_ptr() % 16 == 0):
         kb = _key_bias(key_bias, qkv.shape[0], qkv.shape[1], qkv.device)
+        drop = _new_drop(p_drop, training)
         if torch.is_grad_enabled() and qkv.requires_grad:
-            return _PackedAttentionFn.apply(qkv, heads, kb)
-        return attention_fused_fwd(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads, key_bias=kb)
-    return attention(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads, key_bias)
+            return _PackedAttentionFn.apply(qkv, heads, kb, drop)
+        return attention_fused_fwd(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads, key_bias=kb, drop=drop)
+    return attention(q, qkv[..., HD:2 * HD], qkv[..., 2 * HD:], heads, key_bias, p_drop, training)
 
 
 def fused_attention_ok(q, heads: int) -> bool:
@@ -839,22 +892,33 @@ def fused_attention_ok(q, heads: int) -> bool:
     return HD // heads == 64 and S % 64 == 0 and 64 <= S <= 512
 
 
-def attention(q, k, v, heads: int, key_bias=None):
+def attention(q, k, v, heads: int, key_bias=None, p_drop: float = 0.0, training: bool = False):
     """Multi-head self-attention core.  q, k, v: [B, S, heads*d]; ``key_bias``: optional additive ``[B, S]`` (or HF's
-    ``[B, 1, 1, S]``) key-padding bias.  Head dim 64 and S a multiple of 64 up to 512 run as one fused tcgen05 kernel per
-    direction; other shapes use batched GEMMs + row softmax."""
+    ``[B, 1, 1, S]``) key-padding bias; ``p_drop``: dropout on the probabilities while ``training``.  Head dim 64 and S a
+    multiple of 64 up to 512 run as one fused tcgen05 kernel per direction (mask and dropout included); other bf16 shapes
+    without mask or dropout use batched tcgen05 GEMMs + row softmax; the rest (and the CPU) is stated with torch ops."""
     B, S, HD = q.shape
     d = HD // heads
+    dropping = training and p_drop > 0.0
     if use_native(q, k, v) and q.dtype == torch.bfloat16 and d % 8 == 0 and S % 8 == 0 and S <= 1024:
         needs_grad = torch.is_grad_enabled() and (q.requires_grad or k.requires_grad or v.requires_grad)
         if fused_attention_ok(q, heads):
             kb = _key_bias(key_bias, B, S, q.device)
-            return _FusedAttentionFn.apply(q, k, v, heads, kb) if needs_grad else attention_fused_fwd(q, k, v, heads, key_bias=kb)
-        if key_bias is None:
+            drop = _new_drop(p_drop, training)
+            if needs_grad:
+                return _FusedAttentionFn.apply(q, k, v, heads, kb, drop)
+            return attention_fused_fwd(q, k, v, heads, key_bias=kb, drop=drop)
+        if key_bias is None and not dropping:
             return _AttentionFn.apply(q, k, v, heads)
     qh, kh, vh = (t.view(B, S, heads, d).transpose(1, 2) for t in (q, k, v))
     mask = None if key_bias is None else key_bias.reshape(B, 1, 1, S).float()
-    o = TF.scaled_dot_product_attention(qh.float(), kh.float(), vh.float(), attn_mask=mask)
+    if dropping:
+        scores = (qh.float() @ kh.float().transpose(-1, -2)) * (1.0 / d ** 0.5)
+        if mask is not None:
+            scores = scores + mask
+        o = dropout(torch.softmax(scores, dim=-1), p_drop, True) @ vh.float()
+    else:
+        o = TF.scaled_dot_product_attention(qh.float(), kh.float(), vh.float(), attn_mask=mask)
     return o.transpose(1, 2).reshape(B, S, HD).to(q.dtype)
 
 

@@ -245,6 +245,86 @@ def test_fused_attention_key_padding_mask(B, S, heads, packed):
     assert float((grads[2].float() * (1 - valid)).abs().max()) < 1e-3
 
 
+@pytest.mark.parametrize("B,S,heads", [(2, 128, 2), (1, 512, 3), (3, 192, 1), (2, 64, 2)])
+@pytest.mark.parametrize("masked", [False, True])
+@pytest.mark.parametrize("packed", [False, True])
+def test_fused_attention_dropout(B, S, heads, masked, packed):
+    """Dropout on the attention probabilities inside the fused kernels: forward and the three gradients against an fp32
+    statement that applies the SAME keep mask (``attention_keep_mask`` restates the kernels' counter hash on the host), so the
+    comparison is exact up to bf16 rounding - and it shows that all three kernels regenerate one and the same mask."""
+    from ml_trainer_b200.ops import _lib
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(S * 3 + heads)
+    d, p_drop = 64, 0.1
+    HD = heads * d
+    dev = torch.device(DEV)
+    F.dropout_seed(0x1234ABCD5678)
+    F.dropout_begin_step(dev)
+    F.dropout_begin_step(dev)
+    kb, amask = None, torch.ones(B, S, dtype=torch.bool, device=DEV)
+    if masked:
+        lengths = torch.randint(S // 4, S + 1, (B,))
+        lengths[0] = S
+        amask = (torch.arange(S)[None, :] < lengths[:, None]).to(DEV)
+        kb = F.prepare_key_bias(amask.long())
+    _lib.launches.reset()
+    if packed:
+        qkv = (torch.randn(B, S, 3 * HD, device=DEV) * 0.7).to(torch.bfloat16).requires_grad_()
+        out = F.attention_packed(qkv, heads, kb, p_drop, True)
+        q, k, v = qkv[..., :HD], qkv[..., HD:2 * HD], qkv[..., 2 * HD:]
+    else:
+        q, k, v = ((torch.randn(B, S, HD, device=DEV) * 0.7).to(torch.bfloat16).requires_grad_() for _ in range(3))
+        out = F.attention(q, k, v, heads, kb, p_drop, True)
+    call_id = F._drop["call"]
+    go = (torch.randn(B, S, HD, device=DEV) * 0.5).to(torch.bfloat16) * amask[:, :, None]
+    out.backward(go)
+    torch.cuda.synchronize()
+    names = dict(_lib.launches.by_name)
+    assert names.get("attention_fwd_tcgen05") == 1 and names.get("attention_bwd_tcgen05") == 3 and "dropout" not in names, names
+
+    keep, scale = F.attention_keep_mask(B, heads, S, p_drop, call_id, device=DEV)
+    assert abs(keep.float().mean().item() - 230 / 256) < 0.01
+    qf, kf, vf = (t.detach().float().requires_grad_() for t in (q, k, v))
+    sp = lambda t: t.reshape(B, S, heads, d).transpose(1, 2)
+    scores = sp(qf) @ sp(kf).transpose(-1, -2) / d ** 0.5
+    scores = scores.masked_fill(~amask[:, None, None, :], float("-inf"))
+    ref = ((torch.softmax(scores, -1) * keep * scale) @ sp(vf)).transpose(1, 2).reshape(B, S, HD)
+    ref.backward(go.float())
+    valid = amask[:, :, None].float()
+    _close(out.float() * valid, ref * valid, 2e-2, "attention out with dropout")
+    grads = (qkv.grad[..., :HD], qkv.grad[..., HD:2 * HD], qkv.grad[..., 2 * HD:]) if packed else (q.grad, k.grad, v.grad)
+    for name, got, want in zip(("dq", "dk", "dv"), grads, (qf.grad, kf.grad, vf.grad)):
+        err = (got.float() - want).abs().max().item() / (want.abs().max().item() + 1e-12)
+        assert err < 3e-2, f"{name}: relative max error {err}"
+    # another step draws another mask; the same (step, call site) draws the same one
+    with torch.no_grad():
+        F._drop["call"] = call_id - 1
+        again = F.attention(q, k, v, heads, kb, p_drop, True)
+        F.dropout_begin_step(dev)
+        F._drop["call"] = call_id - 1
+        other = F.attention(q, k, v, heads, kb, p_drop, True)
+    assert torch.equal(again, out.detach())
+    assert not torch.equal(other, out.detach())
+
+
+def test_attention_dropout_rate_is_unbiased():
+    """Mean of the dropped output over many call sites approaches the undropped output (survivors are scaled by 256 / thr)."""
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(5)
+    B, S, heads, HD = 2, 128, 2, 128
+    q, k, v = ((torch.randn(B, S, HD, device=DEV) * 0.5).to(torch.bfloat16) for _ in range(3))
+    F.dropout_begin_step(torch.device(DEV))
+    base = F.attention(q, k, v, heads).float()
+    acc = torch.zeros_like(base)
+    n = 200
+    for _ in range(n):
+        acc += F.attention(q, k, v, heads, None, 0.25, True).float()
+    err = (acc / n - base).abs().max().item() / base.abs().max().item()
+    assert err < 0.08, err
+
+
 def test_bert_masked_batch_uses_fused_attention():
     """A padded batch (HuggingFace attention_mask) stays on the fused attention kernels and matches the fp32 CPU statement."""
     from ml_trainer_b200 import build_model
