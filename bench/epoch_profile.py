@@ -52,6 +52,7 @@ for ep in range(2, 2 + R):
     tr.train_epoch(ep)
     e.record()
     torch.cuda.synchronize()
+    wall = (time.perf_counter() - t) * 1e6
     st = stamps[:2 * K].view(K, 2).cpu().double()
     gpu = {}
     if float(st[:, 0].min()) > 0:
@@ -61,7 +62,7 @@ for ep in range(2, 2 + R):
                "gap_us_mean": round(gap.mean().item(), 2), "gap_us_max": round(gap.max().item(), 2),
                "first_start_to_last_end_us": round(((st[-1, 1] - st[0, 0]) / 1e3).item(), 1),
                "gaps_us": [round(g, 1) for g in gap.tolist()]}
-    rows.append({"wall_us": (time.perf_counter() - t) * 1e6, "event_us": s.elapsed_time(e) * 1e3,
+    rows.append({"wall_us": wall, "event_us": s.elapsed_time(e) * 1e3,
                  "native": tr.last_native_stats.get("host_us"), "gpu_steps": gpu})
 LIB.mlt_lenet_set_stamps(None, ctypes.c_int(0))
 out = {"K": K, "epochs": rows, "stages_us": {k: [round(x, 1) for x in v] for k, v in stages.items()}}

@@ -15,10 +15,12 @@
 // condition variable between runs; the caller gathers step 0 itself while it wakes), the per-run tables are allocated once,
 // and a slot's inputs and targets share ONE pinned buffer and ONE device buffer, so a full batch goes device-ward as one copy.
 #include <cuda_runtime.h>
+#include <emmintrin.h>
 
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -92,30 +94,50 @@ struct Loop {
     const long long* indices = nullptr; const long long* start = nullptr;
     long long first = 0, steps = 0;
   } job;
-  std::thread worker;
+  // kMaxWorkers gather threads at most (MLT_GATHER_THREADS, default 2): worker w fills the steps first + w, first + w + W, ...
+  static constexpr int kMaxWorkers = 4;
+  int nworkers = 1;
+  std::thread worker[kMaxWorkers];
   std::mutex mu;
   std::condition_variable cv;
   long long job_seq = 0;                // guarded by mu
   bool stop = false;                    // guarded by mu
-  std::atomic<long long> done_seq{0};   // last job the worker finished
+  std::atomic<long long> done_seq[kMaxWorkers];   // last job each worker finished
   std::atomic<bool> abort{false};
   std::unique_ptr<std::atomic<long long>[]> gathered;   // [slots] step id (+1) whose data sits in the slot's pinned buffers
   std::unique_ptr<std::atomic<long long>[]> free_for;   // [slots] slot may be refilled for any step <= this value
   std::vector<long long> start;         // prefix sums of the per-step batch sizes of the current run
-  // host-side timing of the last run, microseconds since entry: [first launch enqueued, all launches enqueued, device drained]
+  // host-side timing of the last run, microseconds since entry: [first launch enqueued, all launches enqueued, device drained];
+  // [3] = time the enqueueing thread spent waiting for gathered batches
   double t_us[4] = {0, 0, 0, 0};
 };
+
+// Copy into a pinned staging buffer.  The CPU never reads the destination (the copy engine does), so large rows are written with
+// non-temporal stores: no read-for-ownership of the destination lines and no cache pollution.  The caller publishes the slot
+// with a release store AFTER the sfence below.
+void stage_copy(char* dst, const char* src, size_t bytes) {
+  if (bytes < 2048 || ((uintptr_t)dst & 15)) { std::memcpy(dst, src, bytes); return; }
+  const size_t blocks = bytes / 64;
+  const __m128i* s = (const __m128i*)src;
+  __m128i* d = (__m128i*)dst;
+  for (size_t b = 0; b < blocks; ++b) {
+    const __m128i v0 = _mm_loadu_si128(s + 4 * b), v1 = _mm_loadu_si128(s + 4 * b + 1);
+    const __m128i v2 = _mm_loadu_si128(s + 4 * b + 2), v3 = _mm_loadu_si128(s + 4 * b + 3);
+    _mm_stream_si128(d + 4 * b, v0); _mm_stream_si128(d + 4 * b + 1, v1);
+    _mm_stream_si128(d + 4 * b + 2, v2); _mm_stream_si128(d + 4 * b + 3, v3);
+  }
+  if (bytes % 64) std::memcpy(dst + blocks * 64, src + blocks * 64, bytes % 64);
+}
 
 // rows `idx[0..n)` of a [N][row] byte matrix -> dst
 void gather_rows(char* dst, const char* src, size_t row, const long long* idx, long long n) {
   bool contiguous = true;
   for (long long i = 1; i < n; ++i)
     if (idx[i] != idx[i - 1] + 1) { contiguous = false; break; }
-  if (contiguous) {
-    std::memcpy(dst, src + (size_t)idx[0] * row, (size_t)n * row);
-    return;
-  }
-  for (long long i = 0; i < n; ++i) std::memcpy(dst + (size_t)i * row, src + (size_t)idx[i] * row, row);
+  if (contiguous) stage_copy(dst, src + (size_t)idx[0] * row, (size_t)n * row);
+  else
+    for (long long i = 0; i < n; ++i) stage_copy(dst + (size_t)i * row, src + (size_t)idx[i] * row, row);
+  _mm_sfence();
 }
 
 void gather_step(Loop* L, const Loop::Job& j, long long i) {
@@ -126,7 +148,7 @@ void gather_step(Loop* L, const Loop::Job& j, long long i) {
   L->gathered[s].store(i + 1, std::memory_order_release);
 }
 
-void worker_main(Loop* L) {
+void worker_main(Loop* L, int w) {
   long long seen = 0;
   for (;;) {
     Loop::Job j;
@@ -137,13 +159,13 @@ void worker_main(Loop* L) {
       seen = L->job_seq;
       j = L->job;
     }
-    for (long long i = j.first; i < j.steps && !L->abort.load(std::memory_order_relaxed); ++i) {
+    for (long long i = j.first + w; i < j.steps && !L->abort.load(std::memory_order_relaxed); i += L->nworkers) {
       const int s = (int)(i % L->slots);
       while (L->free_for[s].load(std::memory_order_acquire) < i && !L->abort.load(std::memory_order_relaxed)) std::this_thread::yield();
       if (L->abort.load(std::memory_order_relaxed)) break;
       gather_step(L, j, i);
     }
-    L->done_seq.store(seen, std::memory_order_release);
+    L->done_seq[w].store(seen, std::memory_order_release);
   }
 }
 
@@ -185,7 +207,12 @@ extern "C" void* mlt_loop_create(int device, int slots, long long max_batch, lon
   L->hyper_cap = L->loss_cap = L->dev_hyper_cap = cap;
   L->gathered.reset(new std::atomic<long long>[L->slots]);
   L->free_for.reset(new std::atomic<long long>[L->slots]);
-  L->worker = std::thread(worker_main, L);
+  const char* gt = std::getenv("MLT_GATHER_THREADS");
+  L->nworkers = gt ? std::atoi(gt) : 2;
+  if (L->nworkers < 1) L->nworkers = 1;
+  if (L->nworkers > Loop::kMaxWorkers) L->nworkers = Loop::kMaxWorkers;
+  if (L->nworkers > L->slots - 1) L->nworkers = L->slots - 1;        // a worker per slot that is not being consumed
+  for (int w = 0; w < L->nworkers; ++w) { L->done_seq[w].store(0); L->worker[w] = std::thread(worker_main, L, w); }
   return L;
 }
 
@@ -206,11 +233,10 @@ extern "C" int mlt_loop_set_augment(void* loop, const mlt_augment_cfg* cfg, void
 extern "C" int mlt_loop_destroy(void* loop) {
   Loop* L = (Loop*)loop;
   if (!L) return 0;
-  if (L->worker.joinable()) {
-    { std::lock_guard<std::mutex> lk(L->mu); L->stop = true; }
-    L->cv.notify_all();
-    L->worker.join();
-  }
+  { std::lock_guard<std::mutex> lk(L->mu); L->stop = true; }
+  L->cv.notify_all();
+  for (int w = 0; w < L->nworkers; ++w)
+    if (L->worker[w].joinable()) L->worker[w].join();
   cudaSetDevice(L->device);
   cudaDeviceSynchronize();
   for (auto& s : L->ring) {
@@ -245,6 +271,7 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
                             void* compute_stream) {
   Loop* L = (Loop*)loop;
   const double t_enter = now_us();
+  L->t_us[3] = 0;
   RT_CHECK(cudaSetDevice(L->device));
   cudaStream_t cs = (cudaStream_t)compute_stream;
   if (steps <= 0) return 0;
@@ -299,14 +326,17 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
     L->job.first = 1; L->job.steps = steps;
     my_seq = ++L->job_seq;
   }
-  L->cv.notify_one();
+  L->cv.notify_all();
   gather_step(L, L->job, 0);
   std::atomic<bool>& abort = L->abort;
   auto& gathered = L->gathered;
   auto& free_for = L->free_for;
   struct Joiner {            // every exit path waits until the gather thread is done with this run's pointers
     Loop* L; long long seq;
-    void join() { while (L->done_seq.load(std::memory_order_acquire) != seq) std::this_thread::yield(); }
+    void join() {
+      for (int w = 0; w < L->nworkers; ++w)
+        while (L->done_seq[w].load(std::memory_order_acquire) != seq) std::this_thread::yield();
+    }
   } gatherer{L, my_seq};
 
   int rc = 0;
@@ -352,7 +382,11 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
       if (cudaEventQuery(pv.ready) != cudaSuccess) cudaEventSynchronize(pv.ready);
       free_for[(i - 1) % S].store(i - 1 + S, std::memory_order_release);
     }
-    while (gathered[s].load(std::memory_order_acquire) != i + 1) std::this_thread::yield();
+    if (gathered[s].load(std::memory_order_acquire) != i + 1) {
+      const double tw = now_us();
+      while (gathered[s].load(std::memory_order_acquire) != i + 1) std::this_thread::yield();
+      L->t_us[3] += now_us() - tw;
+    }
     // device buffers of this slot are free once the step that last used them has finished
     if (persistent) {
       if (i >= S) {
@@ -441,6 +475,8 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
 }
 
 // Host-side timing of the last run in microseconds since entry: out3 = {first step enqueued, all steps enqueued, device drained}.
+// mlt_loop_gather_wait_us: how long the enqueueing thread waited for gathered batches in that run.
+extern "C" double mlt_loop_gather_wait_us(void* loop) { return ((Loop*)loop)->t_us[3]; }
 extern "C" int mlt_loop_timing(void* loop, double* out3) {
   Loop* L = (Loop*)loop;
   for (int i = 0; i < 3; ++i) out3[i] = L->t_us[i];

@@ -223,6 +223,8 @@ int mlt_loop_run(void* loop, const void* host_x, const void* host_y, const long 
 int mlt_loop_stats(void* loop, long long* h2d_bytes, long long* d2h_bytes, long long* launches);
 /* host-side timing of the last run, microseconds since entry: {first step enqueued, all steps enqueued, device drained} */
 int mlt_loop_timing(void* loop, double* out3);
+/* ... and how long the enqueueing thread waited for the gather threads (MLT_GATHER_THREADS, default 2) in that run */
+double mlt_loop_gather_wait_us(void* loop);
 
 /* ---- transformer pieces: ATen layer_norm / softmax / embedding kernels of the BERT workload --------------------- */
 /* y = LN(x [+ res]) * gamma + beta (bf16 activations; gamma/beta fp32 or bf16); hsum (optional) receives x + res. */

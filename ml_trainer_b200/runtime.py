@@ -61,8 +61,10 @@ class NativeLoop:
         self.L.mlt_loop_stats(self.h, ctypes.byref(a), ctypes.byref(b), ctypes.byref(c))
         t = (ctypes.c_double * 3)()
         self.L.mlt_loop_timing(self.h, t)
+        self.L.mlt_loop_gather_wait_us.restype = ctypes.c_double
+        gw = self.L.mlt_loop_gather_wait_us(self.h)
         self.last_stats = {"h2d_bytes": a.value, "d2h_bytes": b.value, "launches": c.value, "steps": steps,
-                           "host_us": {"first_enqueued": t[0], "all_enqueued": t[1], "drained": t[2]}}
+                           "host_us": {"first_enqueued": t[0], "all_enqueued": t[1], "drained": t[2], "gather_wait": gw}}
 
     def _lenet_call(self, fused) -> "LeNetCall":
         """The fixed arguments of the step kernel, built once per (optimizer arena, scratch buffer)."""

@@ -401,12 +401,13 @@ class Trainer:
         if key in loops:
             self._nloop, self._nloop_key = loops[key], key
         if getattr(self, "_nloop_key", None) != key:
-            # Ring depth: 3 slots.  A deeper ring (MLT_RING_SLOTS, single-kernel step only) lets the host enqueue further ahead
-            # of the GPU; measured at 8 GPUs it is SLOWER (12 slots: 118 us/step end to end, 3 slots: 100 us/step,
-            # profiles/r2/bench_ours_n8_ring{12,3}.json), so it stays an experiment switch.
+            # Ring depth.  A deep ring lets the host enqueue a dozen single-kernel steps ahead of the GPU.  Measured (K = 20, end to
+            # end): one GPU 44.7 us/step with 12 slots against 47.7 with 3 (profiles/r2/bench_ours_n1_ring{12,3}.json); eight GPUs
+            # the other way round, 118 against 100 us/step (bench_ours_n8_ring{12,3}.json) - so deep only without peers.
+            # Graph-replay steps keep the shallow ring (one captured graph per slot; ResNet batches are 38 MB each).
             slots = max(self.cfg.prefetch + 1, 3)
             if deep and key[0] * (key[1] + key[2]) <= (2 << 20):
-                slots = max(slots, int(os.environ.get("MLT_RING_SLOTS", "3")))
+                slots = max(slots, int(os.environ.get("MLT_RING_SLOTS", "12" if self.world_size == 1 else "3")))
             self._nloop = loops[key] = NativeLoop(self.device, key[0], key[1], key[2], slots=slots)
             self._nloop_key = key
         return self._nloop
