@@ -393,6 +393,8 @@ def run_e2e_ours(tr, timed, K, R, dev, world, rank):
             "api": "Trainer.train_epoch (what fit() runs): in-memory dataset -> pinned staging -> copy-stream H2D -> step",
             "executor": "native C++ epoch executor" if (tr._native_ok(tr.train_loader, tr.model) or
                                                         tr._native_graph_ok(tr.train_loader, tr.model)) else "python loop + PinnedPrefetcher",
+            "executor_host_us": {k: round(v, 1) for k, v in (st.get("host_us") or {}).items()},
+            "cpus_available": len(os.sched_getaffinity(0)),
             "final_loss": float(losses[steps - 1]) if losses is not None else None}
 
 

@@ -252,9 +252,60 @@ except ImportError as ex:
     ]
 
 
+def nb03():
+    return [
+        md("""
+# 03 - Testing a trained model
+The reference's `03_ML_Testing.ipynb`, cell for cell: transforms -> CIFAR-10 test split -> `Loader` -> `load_model` ->
+`Trainer(model)` -> `trainer.test`.  The checkpoint is the one notebook 01 wrote (`model_output/model.pth`); it loads through
+the same `load_model` the reference ships (both the plain and the `module.`-prefixed key style).  Without `cifar10-dataset/` on
+disk (no network here) the CIFAR-shaped synthetic validation set of notebook 01 stands in.
+"""),
+        code("""
+import os, sys
+sys.path.insert(0, '..')
+import torchvision
+from torchvision.utils import make_grid
+from src.model import MLModel
+from src.trainer import Trainer
+from src.dataloader import Loader
+from src.utils.utils import load_model
+from ml_trainer_b200 import DeviceAugment, U8ImageDataset
+from ml_trainer_b200.data import synthetic_cifar
+"""),
+        code("training_dir = 'cifar10-dataset'"),
+        code("""
+# Test-time transform: the reference's ToTensor + Normalize (its RandomCrop / flip belong to training only); one object that
+# runs as a GPU kernel on uint8 batches, or bit for bit the same on the host
+def _get_transforms():
+    return DeviceAugment((3, 32, 32), padding=0, flip=False,
+                         mean=(0.4914, 0.4822, 0.4465), std=(0.2023, 0.1994, 0.2010))
+"""),
+        code("""
+if os.path.isdir(training_dir):
+    raw_val = torchvision.datasets.CIFAR10(root=training_dir, train=False, download=False)
+    val_set = U8ImageDataset.from_torchvision(raw_val, _get_transforms(), train=False)
+else:
+    print('no CIFAR-10 on disk: using the CIFAR-shaped synthetic stand-in of notebook 01')
+    val_set = U8ImageDataset(*synthetic_cifar(1024, seed=1), augment=_get_transforms(), train=False)
+"""),
+        code("val_set.inputs.view(-1, 32, 32, 3).shape"),
+        code("test_loader = Loader(val_set, batch_size=32, shuffle=True)"),
+        code("""
+model = MLModel()
+model = load_model(model, 'model_output/model.pth')
+"""),
+        code("trainer = Trainer(model)"),
+        code("test_loss, test_accuracy = trainer.test(model, test_loader)\nprint(f'test loss {test_loss:.4f}')"),
+        code("print(f'Model accuracy on test: {test_accuracy}')"),
+    ]
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["01", "02"]
+    which = sys.argv[1:] or ["01", "02", "03"]
     if "01" in which:
         write("01_ML_Training_local.ipynb", run_cells(nb01()))
     if "02" in which:
         write("02_ML_Training_distributed.ipynb", run_cells(nb02()))
+    if "03" in which:
+        write("03_ML_Testing.ipynb", run_cells(nb03()))
