@@ -372,7 +372,16 @@ def run_e2e_ours(tr, timed, K, R, dev, world, rank):
                              pin_memory=True, num_workers=0)
     steps = len(tr.train_loader)
     ms_runs, wall_runs = [], []
+    stamps = None
+    if os.environ.get("MLT_BENCH_STAMPS") == "1" and getattr(tr.engine, "fused", None) is not None:
+        # analysis only: {start, end} %globaltimer stamps of every step of the LAST run (csrc/lenet_step.cu, CTA 0)
+        import ctypes
+
+        from ml_trainer_b200.ops import _lib
+        stamps = torch.zeros(2 * steps, dtype=torch.int64, device=dev)
     for r in range(R):
+        if stamps is not None and r == R - 1:
+            _lib.lib().mlt_lenet_set_stamps(ctypes.c_void_p(stamps.data_ptr()), ctypes.c_int(steps))
         barrier_sync(dev)
         s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         t0 = time.perf_counter()
@@ -383,6 +392,13 @@ def run_e2e_ours(tr, timed, K, R, dev, world, rank):
         wall_runs.append(reduce_max((time.perf_counter() - t0) * 1e3, dev))
         ms_runs.append(reduce_max(max(s.elapsed_time(e), 0.0), dev))
     ms, wall_ms = median(ms_runs), median(wall_runs)
+    gpu_steps = None
+    if stamps is not None:
+        _lib.lib().mlt_lenet_set_stamps(None, ctypes.c_int(0))
+        t = stamps.view(steps, 2).cpu().double()
+        if float(t.min()) > 0:
+            gpu_steps = {"body_us": [round(v, 1) for v in ((t[:, 1] - t[:, 0]) / 1e3).tolist()],
+                         "gap_us": [round(v, 1) for v in ((t[1:, 0] - t[:-1, 1]) / 1e3).tolist()]}
     st = getattr(tr, "last_native_stats", {}) or {}
     losses = tr.last_step_losses
     gb = tr.global_batch_size
@@ -395,6 +411,7 @@ def run_e2e_ours(tr, timed, K, R, dev, world, rank):
                                                         tr._native_graph_ok(tr.train_loader, tr.model)) else "python loop + PinnedPrefetcher",
             "executor_host_us": {k: round(v, 1) for k, v in (st.get("host_us") or {}).items()},
             "cpus_available": len(os.sched_getaffinity(0)),
+            **({"gpu_steps_last_run": gpu_steps} if gpu_steps else {}),
             "final_loss": float(losses[steps - 1]) if losses is not None else None}
 
 

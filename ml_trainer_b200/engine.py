@@ -37,6 +37,7 @@ class StepEngine:
         self._one = torch.ones((), dtype=torch.float32, device=device)
         want = graph if isinstance(graph, bool) else (str(graph).lower() in ("1", "true", "auto", "yes"))
         self.use_graph = bool(want) and device.type == "cuda"
+        self._graph_forced = graph is True        # graph=True: a failed capture is an error; "auto": fall back to eager steps
         self._graphs: Dict[Tuple, torch.cuda.CUDAGraph] = {}
         self._eager_steps = 0
         self._pool = None
@@ -161,12 +162,31 @@ class StepEngine:
 
         n0, by0 = launches.n, dict(launches.by_name)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g, pool=self._pool):
+        try:
+            with torch.cuda.graph(g, pool=self._pool):
+                self._train_body(inputs, targets)
+        except Exception as ex:  # noqa: BLE001 - a user module that syncs (.item()), branches on data, allocates outside the pool
+            if self._graph_forced:
+                raise
+            import logging
+
+            from .ops import functional as F
+
+            logging.getLogger("ml_trainer_b200").warning(
+                "CUDA-graph capture of the training step failed (%s: %s); continuing with eager steps", type(ex).__name__, ex)
+            self.use_graph = False
+            self._graphs.clear()
+            torch.cuda.synchronize(self.device)
+            self.model.zero_grad(set_to_none=True)
+            F.new_step()                      # forget the uses the aborted forward pass registered
             self._train_body(inputs, targets)
+            return
         self.launches_per_step = launches.n - n0      # native kernels recorded into (and replayed by) the graph
         self.kernels_per_step = {k: v - by0.get(k, 0) for k, v in launches.by_name.items() if v - by0.get(k, 0) > 0}
         if self._pool is None:
             self._pool = g.pool()
+        if len(self._graphs) >= 32:           # input buffers keep changing (no stable ring of slots): do not grow without bound
+            self._graphs.pop(next(iter(self._graphs)))
         self._graphs[key] = g
         g.replay()          # capture does not execute; run the step that was just recorded
         self.graph_replays += 1

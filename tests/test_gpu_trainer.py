@@ -1,6 +1,7 @@
 """Trainer on a B200: native kernels, eager vs CUDA-graph vs the CPU statement of the same training run."""
 import copy
 
+import numpy as np
 import pytest
 import torch
 
@@ -140,3 +141,33 @@ def test_parameter_used_twice_accumulates(tmp_path, d, dtype):
     with torch.no_grad():
         w_exp = ref.shared.weight - 0.1 * g_ref
     assert torch.allclose(w_new, w_exp, rtol=1e-2 if dtype == "bf16" else 1e-4, atol=1e-3 if dtype == "bf16" else 1e-5)
+
+
+class _Syncs(torch.nn.Module):
+    """A user module that cannot be captured in a CUDA graph: it reads a value back to the host in forward."""
+
+    def __init__(self, d, classes):
+        super().__init__()
+        self.a = torch.nn.Linear(d, 64)
+        self.b = torch.nn.Linear(64, classes)
+        self.seen = 0.0
+
+    def forward(self, x):
+        h = torch.relu(self.a(x.flatten(1)))
+        self.seen = float(h.abs().max().item())          # device -> host sync: illegal while a stream is capturing
+        return self.b(h)
+
+
+def test_uncapturable_module_falls_back_to_eager_steps(tmp_path):
+    """graph='auto' must not break 'bring your own nn.Module' - a failed capture ends in eager steps."""
+    from ml_trainer_b200 import SyntheticDataset, Trainer
+
+    torch.manual_seed(3)
+    data = SyntheticDataset((32,), 4, length=32 * 8, seed=2)
+    tr = Trainer(_Syncs(32, 4), datasets=(data, data), epochs=3, batch_size=32, model_dir=str(tmp_path), progress=False,
+                 optimizer="sgd", lr=0.05, metric="accuracy", seed=1)
+    assert tr.engine.use_graph
+    tr.fit()
+    assert not tr.engine.use_graph and tr.engine.graph_replays == 0
+    assert all(np.isfinite(v) for v in tr.train_losses) and tr.train_losses[-1] < tr.train_losses[0]
+    assert tr.model.seen > 0
