@@ -16,6 +16,9 @@
 // and a slot's inputs and targets share ONE pinned buffer and ONE device buffer, so a full batch goes device-ward as one copy.
 #include <cuda_runtime.h>
 #include <emmintrin.h>
+#include <linux/futex.h>
+#include <sys/syscall.h>
+#include <unistd.h>
 
 #include <atomic>
 #include <chrono>
@@ -104,6 +107,11 @@ struct Loop {
   bool stop = false;                    // guarded by mu
   std::atomic<long long> done_seq[kMaxWorkers];   // last job each worker finished
   std::atomic<bool> abort{false};
+  // Waiting without burning a core: the two counters below are bumped (and futex-woken) whenever `gathered` / `free_for`
+  // change; a waiter spins briefly, then sleeps on the counter.  Eight ranks x three threads that all spin do not fit a box that
+  // gives each rank a handful of cores.  MLT_WAIT_SPIN=1 restores pure spinning.
+  std::atomic<uint32_t> w_gathered{0}, w_free{0};
+  bool pure_spin = false;
   std::unique_ptr<std::atomic<long long>[]> gathered;   // [slots] step id (+1) whose data sits in the slot's pinned buffers
   std::unique_ptr<std::atomic<long long>[]> free_for;   // [slots] slot may be refilled for any step <= this value
   std::vector<long long> start;         // prefix sums of the per-step batch sizes of the current run
@@ -111,6 +119,27 @@ struct Loop {
   // [3] = time the enqueueing thread spent waiting for gathered batches
   double t_us[4] = {0, 0, 0, 0};
 };
+
+void futex_wake_all(std::atomic<uint32_t>& word) {
+  word.fetch_add(1, std::memory_order_release);
+  syscall(SYS_futex, reinterpret_cast<uint32_t*>(&word), FUTEX_WAKE_PRIVATE, 0x7fffffff, nullptr, nullptr, 0);
+}
+
+// Block until ready() holds; `word` is bumped by whoever may make it true (after the state change).
+template <typename Pred>
+void wait_until(std::atomic<uint32_t>& word, bool pure_spin, Pred ready) {
+  for (int spin = 0; spin < 256; ++spin) {
+    if (ready()) return;
+    _mm_pause();
+  }
+  for (;;) {
+    const uint32_t seen = word.load(std::memory_order_acquire);
+    if (ready()) return;
+    if (pure_spin) { std::this_thread::yield(); continue; }
+    timespec ts{0, 500000};               // wake up at least every 0.5 ms (abort flags are polled by the predicates)
+    syscall(SYS_futex, reinterpret_cast<uint32_t*>(&word), FUTEX_WAIT_PRIVATE, seen, &ts, nullptr, 0);
+  }
+}
 
 // Copy into a pinned staging buffer.  The CPU never reads the destination (the copy engine does), so large rows are written with
 // non-temporal stores: no read-for-ownership of the destination lines and no cache pollution.  The caller publishes the slot
@@ -146,6 +175,7 @@ void gather_step(Loop* L, const Loop::Job& j, long long i) {
   if (!L->direct_x) gather_rows((char*)L->ring[s].pin_x, j.hx, L->x_row, j.indices + j.start[i], n);
   gather_rows((char*)L->ring[s].pin_y, j.hy, L->y_row, j.indices + j.start[i], n);
   L->gathered[s].store(i + 1, std::memory_order_release);
+  futex_wake_all(L->w_gathered);
 }
 
 void worker_main(Loop* L, int w) {
@@ -161,7 +191,9 @@ void worker_main(Loop* L, int w) {
     }
     for (long long i = j.first + w; i < j.steps && !L->abort.load(std::memory_order_relaxed); i += L->nworkers) {
       const int s = (int)(i % L->slots);
-      while (L->free_for[s].load(std::memory_order_acquire) < i && !L->abort.load(std::memory_order_relaxed)) std::this_thread::yield();
+      wait_until(L->w_free, L->pure_spin, [&] {
+        return L->free_for[s].load(std::memory_order_acquire) >= i || L->abort.load(std::memory_order_relaxed);
+      });
       if (L->abort.load(std::memory_order_relaxed)) break;
       gather_step(L, j, i);
     }
@@ -207,6 +239,8 @@ extern "C" void* mlt_loop_create(int device, int slots, long long max_batch, lon
   L->hyper_cap = L->loss_cap = L->dev_hyper_cap = cap;
   L->gathered.reset(new std::atomic<long long>[L->slots]);
   L->free_for.reset(new std::atomic<long long>[L->slots]);
+  const char* ws = std::getenv("MLT_WAIT_SPIN");
+  L->pure_spin = ws && std::atoi(ws) == 1;
   const char* gt = std::getenv("MLT_GATHER_THREADS");
   L->nworkers = gt ? std::atoi(gt) : 2;
   if (L->nworkers < 1) L->nworkers = 1;
@@ -334,6 +368,7 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
   struct Joiner {            // every exit path waits until the gather thread is done with this run's pointers
     Loop* L; long long seq;
     void join() {
+      futex_wake_all(L->w_free);           // a worker asleep on a slot (abort paths) sees the flag now
       for (int w = 0; w < L->nworkers; ++w)
         while (L->done_seq[w].load(std::memory_order_acquire) != seq) std::this_thread::yield();
     }
@@ -381,10 +416,11 @@ extern "C" int mlt_loop_run(void* loop, const void* host_x, const void* host_y, 
       Slot& pv = L->ring[(i - 1) % S];
       if (cudaEventQuery(pv.ready) != cudaSuccess) cudaEventSynchronize(pv.ready);
       free_for[(i - 1) % S].store(i - 1 + S, std::memory_order_release);
+      futex_wake_all(L->w_free);
     }
     if (gathered[s].load(std::memory_order_acquire) != i + 1) {
       const double tw = now_us();
-      while (gathered[s].load(std::memory_order_acquire) != i + 1) std::this_thread::yield();
+      wait_until(L->w_gathered, L->pure_spin, [&] { return gathered[s].load(std::memory_order_acquire) == i + 1; });
       L->t_us[3] += now_us() - tw;
     }
     // device buffers of this slot are free once the step that last used them has finished

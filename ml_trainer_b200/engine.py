@@ -153,7 +153,10 @@ class StepEngine:
         if self._eager_steps < WARMUP:
             self._eager_steps += 1
             opt.begin_step(self.reducer.grad_scale)
-            self._train_body(inputs, targets)
+            if self._graph_forced or getattr(self.model, "_mlt_native", False):
+                self._train_body(inputs, targets)
+            else:
+                self._eager_step_watching_for_syncs(inputs, targets)
             return
         # capture: hyper-parameters are uploaded outside the graph, everything else inside
         opt.begin_step(self.reducer.grad_scale)
@@ -162,6 +165,7 @@ class StepEngine:
 
         n0, by0 = launches.n, dict(launches.by_name)
         g = torch.cuda.CUDAGraph()
+        prev_stream = torch.cuda.current_stream(self.device)
         try:
             with torch.cuda.graph(g, pool=self._pool):
                 self._train_body(inputs, targets)
@@ -176,7 +180,7 @@ class StepEngine:
                 "CUDA-graph capture of the training step failed (%s: %s); continuing with eager steps", type(ex).__name__, ex)
             self.use_graph = False
             self._graphs.clear()
-            torch.cuda.synchronize(self.device)
+            self._heal_after_failed_capture(prev_stream)
             self.model.zero_grad(set_to_none=True)
             F.new_step()                      # forget the uses the aborted forward pass registered
             self._train_body(inputs, targets)
@@ -190,6 +194,42 @@ class StepEngine:
         self._graphs[key] = g
         g.replay()          # capture does not execute; run the step that was just recorded
         self.graph_replays += 1
+
+    def _eager_step_watching_for_syncs(self, inputs, targets):
+        """A warm-up step of a user-supplied module with torch's sync detector on: a forward / loss that reads values back to the
+        host (``.item()``, ``bool(tensor)``, ``.cpu()``: what data-dependent control flow looks like from here) cannot be
+        captured, so graphs are switched off BEFORE a doomed capture is ever started.  The step itself runs normally."""
+        import logging
+        import warnings
+
+        mode = torch.cuda.get_sync_debug_mode()
+        torch.cuda.set_sync_debug_mode("warn")
+        try:
+            with warnings.catch_warnings(record=True) as caught:
+                warnings.simplefilter("always")
+                self._train_body(inputs, targets)
+        finally:
+            torch.cuda.set_sync_debug_mode(mode)
+        if any("synchroniz" in str(w.message) for w in caught):
+            logging.getLogger("ml_trainer_b200").warning(
+                "the training step synchronises with the host (e.g. .item() in forward): CUDA graphs are off for this model")
+            self.use_graph = False
+
+    def _heal_after_failed_capture(self, prev_stream):
+        """torch leaves three things behind when ``capture_end`` raises: the capture side stream stays current, and the default
+        CUDA generator stays in 'capturing' mode (every later torch.randn on the device would assert).  Restore the stream and
+        run one trivial successful capture, whose epilogue resets the generator."""
+        torch.cuda.set_stream(prev_stream)
+        torch.cuda.synchronize(self.device)
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._one.mul_(1.0)
+            del g
+        except Exception:  # noqa: BLE001
+            pass
+        torch.cuda.set_stream(prev_stream)
+        torch.cuda.synchronize(self.device)
 
     # -------------------------------------------------------------------- eval
     @torch.no_grad()

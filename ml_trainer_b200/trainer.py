@@ -408,6 +408,8 @@ class Trainer:
             slots = max(self.cfg.prefetch + 1, 3)
             if deep and key[0] * (key[1] + key[2]) <= (2 << 20):
                 slots = max(slots, int(os.environ.get("MLT_RING_SLOTS", "12" if self.world_size == 1 else "3")))
+                if os.environ.get("MLT_LENET_PERSISTENT", "auto") == "1":
+                    slots = min(slots, 8)          # the persistent step kernel takes at most 8 ring slots
             self._nloop = loops[key] = NativeLoop(self.device, key[0], key[1], key[2], slots=slots)
             self._nloop_key = key
         return self._nloop

@@ -158,16 +158,36 @@ class _Syncs(torch.nn.Module):
         return self.b(h)
 
 
-def test_uncapturable_module_falls_back_to_eager_steps(tmp_path):
-    """graph='auto' must not break 'bring your own nn.Module' - a failed capture ends in eager steps."""
+class _RefusesCapture(_Syncs):
+    """Fails only while a stream is capturing (stands for any module whose forward breaks inside a capture)."""
+
+    def forward(self, x):
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("this module cannot be captured")
+        self.seen = 1.0
+        return self.b(torch.relu(self.a(x.flatten(1))))
+
+
+@pytest.mark.parametrize("model_cls,precheck", [(_Syncs, True), (_Syncs, False), (_RefusesCapture, True)])
+def test_uncapturable_module_falls_back_to_eager_steps(tmp_path, monkeypatch, model_cls, precheck):
+    """graph='auto' must not break 'bring your own nn.Module'.  A module that syncs with the host is spotted
+    during the eager warm-up steps (precheck); without that check, or with a module that fails only inside the capture, the
+    failed capture ends in eager steps too - and torch's current stream and device generator are usable afterwards (a capture
+    that dies in capture_end leaves both in capture mode)."""
+    import ml_trainer_b200.engine as E
     from ml_trainer_b200 import SyntheticDataset, Trainer
 
+    if not precheck:
+        monkeypatch.setattr(E.StepEngine, "_eager_step_watching_for_syncs", lambda self, x, y: self._train_body(x, y))
     torch.manual_seed(3)
     data = SyntheticDataset((32,), 4, length=32 * 8, seed=2)
-    tr = Trainer(_Syncs(32, 4), datasets=(data, data), epochs=3, batch_size=32, model_dir=str(tmp_path), progress=False,
+    tr = Trainer(model_cls(32, 4), datasets=(data, data), epochs=3, batch_size=32, model_dir=str(tmp_path), progress=False,
                  optimizer="sgd", lr=0.05, metric="accuracy", seed=1)
     assert tr.engine.use_graph
+    stream_before = torch.cuda.current_stream()
     tr.fit()
     assert not tr.engine.use_graph and tr.engine.graph_replays == 0
     assert all(np.isfinite(v) for v in tr.train_losses) and tr.train_losses[-1] < tr.train_losses[0]
     assert tr.model.seen > 0
+    assert torch.cuda.current_stream() == stream_before
+    assert torch.isfinite(torch.randn(8, device="cuda")).all()          # the device generator is not stuck in capture mode
