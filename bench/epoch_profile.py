@@ -10,14 +10,25 @@ sys.path.insert(0, ".")
 import ml_trainer_b200.runtime as rt
 from ml_trainer_b200 import Loader, SyntheticDataset, Trainer, build_model
 
+import os  # noqa: E402
+
 K = int(sys.argv[1]) if len(sys.argv) > 1 else 20
 R = int(sys.argv[2]) if len(sys.argv) > 2 else 7
-warm = SyntheticDataset((3, 32, 32), 10, length=32 * 24, seed=7, pool=8192)
-timed = SyntheticDataset((3, 32, 32), 10, length=32 * K, seed=32, pool=min(32 * K, 8192))
-tr = Trainer(build_model("mlmodel"), datasets=(warm, warm), epochs=1, batch_size=32, optimizer="sgd", lr=1e-3, momentum=0.9,
-             metric=None, progress=False, model_dir="/tmp/ep", seed=32)
+WORLD, RANK = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+if WORLD > 1:        # under torchrun: one process per GPU, 32 samples per rank (weak scaling, as bench.py)
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+warm = SyntheticDataset((3, 32, 32), 10, length=32 * 24 * WORLD, seed=7, pool=8192)
+timed = SyntheticDataset((3, 32, 32), 10, length=32 * K * WORLD, seed=32, pool=min(32 * K * WORLD, 8192))
+tr = Trainer(build_model("mlmodel"), datasets=(warm, warm), epochs=1, batch_size=32 * WORLD, optimizer="sgd", lr=1e-3, momentum=0.9,
+             metric=None, progress=False, model_dir=f"/tmp/ep{RANK}", seed=32, is_parallel=WORLD > 1, backend="p2p")
 tr.train_epoch(1)
-tr.train_loader = Loader(timed, batch_size=32, shuffle=True, pin_memory=True, num_workers=0)
+if WORLD > 1:
+    from torch.utils.data.distributed import DistributedSampler
+
+    tr.train_sampler = DistributedSampler(timed, num_replicas=WORLD, rank=RANK)
+    tr.train_loader = Loader(timed, batch_size=32, sampler=tr.train_sampler, pin_memory=True, num_workers=0)
+else:
+    tr.train_loader = Loader(timed, batch_size=32, shuffle=True, pin_memory=True, num_workers=0)
 stages = {}
 
 
@@ -34,6 +45,9 @@ rt.epoch_indices = timed_fn("epoch_indices", rt.epoch_indices)
 rt.NativeLoop.run_lenet = timed_fn("run_lenet", rt.NativeLoop.run_lenet)
 tr.optimizer.hyper_rows = timed_fn("hyper_rows", tr.optimizer.hyper_rows)
 tr._reduce_epoch = timed_fn("reduce_epoch", tr._reduce_epoch)
+tr.comm.reduce_scalars = timed_fn("reduce_scalars", tr.comm.reduce_scalars)
+tr.comm.check_errors = timed_fn("check_errors", tr.comm.check_errors)
+tr.train_epoch = timed_fn("train_epoch", tr.train_epoch)
 tr._run_native_epoch = timed_fn("run_native_epoch", tr._run_native_epoch)
 import ctypes  # noqa: E402
 
@@ -46,6 +60,8 @@ for ep in range(2, 2 + R):
     stamps.zero_()
     LIB.mlt_lenet_set_stamps(ctypes.c_void_p(stamps.data_ptr()), ctypes.c_int(K))
     torch.cuda.synchronize()
+    if WORLD > 1:
+        tr.comm.barrier()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t = time.perf_counter()
     s.record()
@@ -65,5 +81,8 @@ for ep in range(2, 2 + R):
     rows.append({"wall_us": wall, "event_us": s.elapsed_time(e) * 1e3,
                  "native": tr.last_native_stats.get("host_us"), "gpu_steps": gpu})
 LIB.mlt_lenet_set_stamps(None, ctypes.c_int(0))
-out = {"K": K, "epochs": rows, "stages_us": {k: [round(x, 1) for x in v] for k, v in stages.items()}}
-print(json.dumps(out, indent=1))
+out = {"K": K, "world": WORLD, "rank": RANK, "epochs": rows, "stages_us": {k: [round(x, 1) for x in v] for k, v in stages.items()}}
+if RANK == 0:
+    print(json.dumps(out, indent=1))
+if WORLD > 1:
+    tr.close()

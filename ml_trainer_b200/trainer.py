@@ -402,8 +402,9 @@ class Trainer:
             self._nloop, self._nloop_key = loops[key], key
         if getattr(self, "_nloop_key", None) != key:
             # Ring depth.  A deep ring lets the host enqueue a dozen single-kernel steps ahead of the GPU.  Measured (K = 20, end to
-            # end): one GPU 44.7 us/step with 12 slots against 47.7 with 3 (profiles/r2/bench_ours_n1_ring{12,3}.json); eight GPUs
-            # the other way round, 118 against 100 us/step (bench_ours_n8_ring{12,3}.json) - so deep only without peers.
+            # end): one GPU 44.7 us/step with 12 slots against 47.7 with 3 (profiles/r2/bench_ours_n1_ring{12,3}.json); at eight
+            # GPUs it buys nothing (83.9 against 82.6 us/step, bench_ours_n8_with_step_stamps.json / _headline.json; with the
+            # old spinning waits it was slower, 118 against 100) - so deep only without peers.
             # Graph-replay steps keep the shallow ring (one captured graph per slot; ResNet batches are 38 MB each).
             slots = max(self.cfg.prefetch + 1, 3)
             if deep and key[0] * (key[1] + key[2]) <= (2 << 20):

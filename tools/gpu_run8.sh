@@ -1,13 +1,23 @@
 #!/bin/bash
-# eight-GPU validation: single-kernel step replicas, collectives at world 8, executor ring depth, bucket sweep to 1 GB
+# eight-GPU check of the headline: default settings (the record), the same with per-step GPU stamps, old waits / one gather
+# thread, and a deep ring
+N=${1:-8}
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
-N=${1:-8}
+nproc
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-MLT_TEST_WORLD=$N timeout 600 python -m pytest tests/test_multigpu.py -q -k "single_kernel or kernels" > gpurun_out/pytest_multigpu_w$N.log 2>&1; tail -5 gpurun_out/pytest_multigpu_w$N.log
-timeout 400 $TR --master-port 29713 bench.py --gpus $N --steps 20 --warmup 5 --secondary none > gpurun_out/bench_ours_n${N}_ring12.json 2> gpurun_out/bench_ours_n${N}_ring12.err; echo "bench ring12 rc=$?"
-tail -c 300 gpurun_out/bench_ours_n${N}_ring12.json
-MLT_RING_SLOTS=3 timeout 400 $TR --master-port 29715 bench.py --gpus $N --steps 20 --warmup 5 --secondary none > gpurun_out/bench_ours_n${N}_ring3.json 2> gpurun_out/bench_ours_n${N}_ring3.err; echo "bench ring3 rc=$?"
-tail -c 300 gpurun_out/bench_ours_n${N}_ring3.json
-timeout 400 $TR --master-port 29717 bench.py --gpus $N --steps 200 --warmup 5 --secondary none --repeats 3 > gpurun_out/bench_ours_n${N}_k200.json 2> gpurun_out/bench_ours_n${N}_k200.err; echo "bench k200 rc=$?"
-timeout 600 $TR --master-port 29719 bench/allreduce_sweep.py --max-mb 1024 --out gpurun_out/allreduce_sweep_${N}gpu.json > gpurun_out/sweep_n$N.log 2>&1; echo "sweep rc=$?"
+B="bench.py --gpus $N --steps 20 --warmup 5 --secondary none"
+timeout 300 $TR --master-port 29711 $B > gpurun_out/bench_ours_n${N}_default.json 2> gpurun_out/bench_ours_n${N}_default.err; echo "default rc=$?"
+MLT_BENCH_STAMPS=1 timeout 300 $TR --master-port 29713 $B > gpurun_out/bench_ours_n${N}_stamps.json 2> gpurun_out/bench_ours_n${N}_stamps.err; echo "stamps rc=$?"
+MLT_WAIT_SPIN=1 MLT_GATHER_THREADS=1 timeout 300 $TR --master-port 29715 $B > gpurun_out/bench_ours_n${N}_oldwaits.json 2> gpurun_out/bench_ours_n${N}_oldwaits.err; echo "oldwaits rc=$?"
+MLT_RING_SLOTS=12 MLT_BENCH_STAMPS=1 timeout 300 $TR --master-port 29717 $B > gpurun_out/bench_ours_n${N}_ring12b.json 2> gpurun_out/bench_ours_n${N}_ring12b.err; echo "ring12 rc=$?"
+python - <<P
+import json
+for n in ("default","stamps","oldwaits","ring12b"):
+    try:
+        d=json.load(open(f"gpurun_out/bench_ours_n${N}_{n}.json")); e=d["e2e"]
+        print(n, d["value"], d["ms_per_step"], e["value"], e["ms_per_step"], e.get("runs_ms"), e.get("executor_host_us"), e.get("cpus_available"))
+        g=e.get("gpu_steps_last_run")
+        if g: print("   body", g["body_us"]); print("   gap ", g["gap_us"])
+    except Exception as ex: print(n, ex)
+P
