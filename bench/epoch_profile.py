@@ -46,6 +46,7 @@ rt.NativeLoop.run_lenet = timed_fn("run_lenet", rt.NativeLoop.run_lenet)
 tr.optimizer.hyper_rows = timed_fn("hyper_rows", tr.optimizer.hyper_rows)
 tr._reduce_epoch = timed_fn("reduce_epoch", tr._reduce_epoch)
 tr.comm.reduce_scalars = timed_fn("reduce_scalars", tr.comm.reduce_scalars)
+tr.comm.reduce_scalars_host = timed_fn("reduce_scalars_host", tr.comm.reduce_scalars_host)
 tr.comm.check_errors = timed_fn("check_errors", tr.comm.check_errors)
 tr.train_epoch = timed_fn("train_epoch", tr.train_epoch)
 tr._run_native_epoch = timed_fn("run_native_epoch", tr._run_native_epoch)

@@ -330,20 +330,45 @@ extern "C" int mlt_p2p_reduce_scalars(const mlt_p2p_ctx* ctx, long long scalar_o
   return 0;
 }
 
+static int p2p_eval_error(const mlt_p2p_ctx* ctx, const unsigned int* e, char* fb);
+
+// The epoch-end form for host values: pin (pinned host memory, >= 40 x 4 bytes) holds k floats on entry; on return pin[0..k) holds
+// their sums over all ranks and the timeout diagnostic of this rank has been read in the same round trip - ONE stream
+// synchronisation instead of a pageable upload, a clone, a read-back and a separate error read.  vals_dev_table / vals_dev: the
+// device pointer table and the k-float device buffer it points to (as for mlt_p2p_reduce_scalars).  Returns like
+// mlt_p2p_check_error.
+extern "C" int mlt_p2p_reduce_scalars_host(const mlt_p2p_ctx* ctx, long long scalar_off, void* vals_dev_table, void* vals_dev, void* pin,
+                                           int k, void* stream) {
+  MLT_REQUIRE(k >= 1 && k <= 32, "p2p reduce_scalars: k=%d out of range (1..32)", k);
+  cudaStream_t st = (cudaStream_t)stream;
+  float* hp = (float*)pin;
+  char* fb = (char*)ctx->base[ctx->rank] + ctx->flags_off + offsetof(FlagBlock, err);
+  MLT_CHECK_CUDA(cudaMemcpyAsync(vals_dev, hp, (size_t)k * sizeof(float), cudaMemcpyHostToDevice, st));
+  if (mlt_p2p_reduce_scalars(ctx, scalar_off, vals_dev_table, k, 1, stream)) return 1;
+  MLT_CHECK_CUDA(cudaMemcpyAsync(hp, vals_dev, (size_t)k * sizeof(float), cudaMemcpyDeviceToHost, st));
+  MLT_CHECK_CUDA(cudaMemcpyAsync(hp + 32, fb, 8 * sizeof(unsigned int), cudaMemcpyDeviceToHost, st));
+  MLT_CHECK_CUDA(cudaStreamSynchronize(st));
+  return p2p_eval_error(ctx, reinterpret_cast<const unsigned int*>(hp + 32), fb);
+}
+
 // Reads (and clears) the timeout diagnostic of the local arena.  out6 = {code, rank, peer, cta, expected, seen}.
 extern "C" int mlt_p2p_check_error(const mlt_p2p_ctx* ctx, unsigned int* out6_host) {
   unsigned int e[8];
   char* fb = (char*)ctx->base[ctx->rank] + ctx->flags_off + offsetof(FlagBlock, err);
   MLT_CHECK_CUDA(cudaMemcpy(e, fb, sizeof(e), cudaMemcpyDeviceToHost));
   for (int i = 0; i < 6; ++i) out6_host[i] = e[i];
+  return p2p_eval_error(ctx, e, fb);
+}
+
+static int p2p_eval_error(const mlt_p2p_ctx* ctx, const unsigned int* e, char* fb) {
   if (e[0] == 1) {
-    MLT_CHECK_CUDA(cudaMemset(fb, 0, sizeof(e)));
+    MLT_CHECK_CUDA(cudaMemset(fb, 0, 8 * sizeof(unsigned int)));
     set_error("p2p: rank %u timed out waiting for peer %u (cta %u, kind %u): expected ticket %u, saw %u; the update was skipped",
               e[1], e[2], e[3], e[6], e[4], e[5]);
     return 2;
   }
   if (e[0] != 0) {
-    MLT_CHECK_CUDA(cudaMemset(fb, 0, sizeof(e)));
+    MLT_CHECK_CUDA(cudaMemset(fb, 0, 8 * sizeof(unsigned int)));
     set_error("p2p: rank %d was stopped by a peer that timed out waiting in a collective; the update was skipped", ctx->rank);
     return 3;
   }

@@ -161,6 +161,10 @@ int mlt_p2p_allreduce_update_at(const mlt_p2p_ctx* ctx, int algo, int rule, int 
 int mlt_p2p_broadcast(const mlt_p2p_ctx* ctx, long long off, long long nbytes, int root, int ranks_here, void* stream);
 int mlt_p2p_reduce_scalars(const mlt_p2p_ctx* ctx, long long scalar_off, void* vals_dev, int k, int ranks_here, void* stream);
 int mlt_p2p_check_error(const mlt_p2p_ctx* ctx, unsigned int* out6_host);
+/* Epoch-end form: k floats in pinned host memory `pin` (>= 160 bytes) are summed over all ranks in place and this rank's timeout
+ * diagnostic is read in the same round trip (one stream synchronisation).  Returns like mlt_p2p_check_error. */
+int mlt_p2p_reduce_scalars_host(const mlt_p2p_ctx* ctx, long long scalar_off, void* vals_dev_table, void* vals_dev, void* pin, int k,
+                                void* stream);
 /* wait limit of every flag wait of this rank's collectives in seconds (<= 0: the default, ~20 s).  When a wait runs past it the
  * kernel records a diagnostic, poisons this rank and its peers (later collectives return without touching weights) and
  * mlt_p2p_check_error reports it. */

@@ -43,6 +43,15 @@ class Comm:
         """Size any backend-owned memory for a model of ``param_elems`` (padded) parameters and ``n_states`` fp32
         optimizer-state vectors.  Collective."""
 
+    def reduce_scalars_host(self, values):
+        """Host floats summed over all ranks, plus the error check; back ends with a cheaper fused form override this."""
+        dev = getattr(self, "device", None)
+        if dev is None or getattr(self, "name", "") == "gloo":
+            dev = "cpu"
+        out = self.reduce_scalars(torch.tensor([float(v) for v in values], dtype=torch.float32, device=dev)).tolist()
+        self.check_errors()
+        return out
+
     def check_errors(self) -> None:
         """Raise if a collective recorded a failure (a peer that stopped answering).  Host-side, cheap."""
 

@@ -372,6 +372,26 @@ class P2PComm(Comm):
         launches.bump("p2p_reduce_scalars")
         return self._vals[:k].clone().view(values.shape)
 
+    def reduce_scalars_host(self, values):
+        """Sum a short list of host floats over all ranks AND read this rank's timeout diagnostic, in one round trip to the
+        device (what the Trainer does at the end of every epoch).  Raises like :meth:`check_errors`."""
+        if self.world_size == 1 or self.arena is None:
+            return [float(v) for v in values]
+        k = len(values)
+        if self._vals is None:
+            self._vals = torch.zeros(32, dtype=torch.float32, device=self.device)
+            self._vals_ptr = torch.tensor([self._vals.data_ptr()], dtype=torch.int64, device=self.device)
+        if getattr(self, "_pin_vals", None) is None:
+            self._pin_vals = torch.zeros(40, dtype=torch.float32).pin_memory()
+        pin = self._pin_vals
+        for i, v in enumerate(values):
+            pin[i] = float(v)
+        check(self.L.mlt_p2p_reduce_scalars_host(ctypes.byref(self.ctx), _c_ll(self.scalar_off), ptr(self._vals_ptr), ptr(self._vals),
+                                                 ctypes.c_void_p(pin.data_ptr()), _c_int(k), stream_handle()),
+              "mlt_p2p_reduce_scalars_host")
+        launches.bump("p2p_reduce_scalars")
+        return pin[:k].tolist()
+
     def device_barrier(self):
         """All ranks have reached this point (and finished the work queued before it on the current stream): the scalar
         all-reduce kernel is a device-side barrier - its flag exchange completes only when every rank's kernel runs.  For

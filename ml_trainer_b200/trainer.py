@@ -266,12 +266,21 @@ class Trainer:
         disable = (not self.cfg.progress) or self.rank != 0
         return tqdm(it, unit="batch", total=total, disable=disable)
 
-    def _reduce_epoch(self, sums: torch.Tensor):
-        """``sums`` = [loss_sum, metric_sum, batches] -> cross-rank mean loss / metric."""
-        if self.world_size > 1:
-            sums = self.comm.reduce_scalars(sums)
-        loss_sum, metric_sum, n = sums.tolist()
-        self.comm.check_errors()            # a peer that stopped answering: raise here, not a checkpoint later
+    def _reduce_epoch(self, sums):
+        """``sums`` = [loss_sum, metric_sum, batches] (device tensor, or host floats) -> cross-rank mean loss / metric."""
+        if isinstance(sums, torch.Tensor) and sums.device.type == "cpu":
+            sums = sums.tolist()
+        if isinstance(sums, (list, tuple)):
+            # host values (the native epoch loop hands back per-step losses in pinned memory): sum over the ranks and read the
+            # peers-stopped-answering word in ONE round trip to the device
+            loss_sum, metric_sum, n = self.comm.reduce_scalars_host(sums) if self.world_size > 1 else sums
+            if self.world_size == 1:
+                self.comm.check_errors()
+        else:
+            if self.world_size > 1:
+                sums = self.comm.reduce_scalars(sums)
+            loss_sum, metric_sum, n = sums.tolist()
+            self.comm.check_errors()            # a peer that stopped answering: raise here, not a checkpoint later
         n = max(n, 1.0)
         return loss_sum / n, metric_sum / n
 
@@ -474,7 +483,7 @@ class Trainer:
             if use_acc:
                 sums = eng.accumulators()
             else:
-                sums = torch.tensor([float(self.last_step_losses.sum(dtype=torch.float64)), 0.0, float(nb)], dtype=torch.float32)
+                sums = [float(self.last_step_losses.sum(dtype=torch.float64)), 0.0, float(nb)]
             loss, metric = self._reduce_epoch(sums)
             self.train_losses.append(loss)
             if self.metric:
