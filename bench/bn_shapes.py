@@ -45,7 +45,13 @@ def main():
         with torch.no_grad():
             fwd = timeit(lambda: C.batch_norm_nhwc(x, bn, relu=relu, residual=r))
         y = C.batch_norm_nhwc(x, bn, relu=relu, residual=r)
-        bwd = timeit(lambda: y.backward(go, retain_graph=True))
+        def run_bwd():
+            x.grad = None                      # a leaf that already holds a gradient would add an accumulation kernel
+            if r is not None:
+                r.grad = None
+            y.backward(go, retain_graph=True)
+
+        bwd = timeit(run_bwd)
         nb = M * ch * 2
         # forward: stats reads x; apply reads x (+ residual), writes y (+ 1/16 mask).  backward: reduce reads dy, x (+ mask);
         # apply reads dy, x (+ mask), writes dx (+ dres)

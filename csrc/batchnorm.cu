@@ -30,18 +30,23 @@ __device__ __forceinline__ unsigned int relu_bits(const __nv_bfloat16* y, const 
   return b;
 }
 
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, 3)
 bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ mean, float* __restrict__ rstd, float* __restrict__ run_mean,
                 float* __restrict__ run_var, float momentum, float eps, float* __restrict__ partial, unsigned int* __restrict__ tickets,
                 int M, int C) {
   __shared__ float tot[2 * kBnGroups * 8];
-  auto f = [&](size_t off, float (&a)[8], float (&b)[8]) {
-    float v[8];
-    ld8(x + off, v);
+  struct {
+    const __nv_bfloat16* x;
+    __device__ __forceinline__ uint4 load(size_t off) const { return ld8raw(x + off); }
+    __device__ __forceinline__ void pin(const uint4& raw) const { asm volatile("" ::"r"(raw.x) : "memory"); }
+    __device__ __forceinline__ void use(const uint4& raw, float (&a)[8], float (&b)[8]) const {
+      float v[8];
+      cvt8(raw, v);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { a[j] += v[j]; b[j] = fmaf(v[j], v[j], b[j]); }
-  };
-  if (!col_reduce_atomic<true, 8>(f, partial, tickets, M, C, tot)) return;
+      for (int j = 0; j < 8; ++j) { a[j] += v[j]; b[j] = fmaf(v[j], v[j], b[j]); }
+    }
+  } f{x};
+  if (!col_reduce_atomic<true, 8, true>(f, partial, tickets, M, C, tot)) return;
   const int g_lo = blockIdx.x * kBnGroups;
   const int nch = min(kBnGroups, (C >> 3) - g_lo) * 8;
   for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {
@@ -59,7 +64,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ mean, f
 
 // y = [relu]( (x - mean) * rstd * gamma + beta [+ residual] )
 template <typename P, bool RES, bool RELU>
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, 3)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd,
                 const P* __restrict__ gamma, const P* __restrict__ beta, const __nv_bfloat16* __restrict__ residual,
                 __nv_bfloat16* __restrict__ y, unsigned char* __restrict__ mask, long long total, int C8) {
@@ -87,9 +92,36 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ m
     st8(y + e * 8, v);
     if (RELU && mask != nullptr) mask[e] = (unsigned char)bits;      // 1 bit per element: all backward needs of y
   };
-  for (; i + 3 * step < total; i += 4 * step) {
+  // four positions per iteration, all loads first (x, and the residual when there is one), then the arithmetic and the stores
+  auto finish = [&](long long e, const uint4& xr, const uint4& rr) {
+    float v[8], r[8];
+    cvt8(xr, v);
+    if (RES) cvt8(rr, r);
+    unsigned int bits = 0;
 #pragma unroll
-    for (int u = 0; u < 4; ++u) one(i + u * step);
+    for (int j = 0; j < 8; ++j) {
+      float o = fmaf(v[j], sc[j], sf[j]);
+      if (RES) o += r[j];
+      if (RELU) bits |= (o > 0.f ? 1u : 0u) << j;
+      v[j] = RELU ? fmaxf(o, 0.f) : o;
+    }
+    st8(y + e * 8, v);
+    if (RELU && mask != nullptr) mask[e] = (unsigned char)bits;
+  };
+  for (; i + 3 * step < total; i += 4 * step) {
+    uint4 xr[4], rr[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      xr[u] = ld8raw(x + (i + u * step) * 8);
+      if (RES) rr[u] = ld8raw(residual + (i + u * step) * 8); else rr[u] = make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      asm volatile("" ::"r"(xr[u].x) : "memory");
+      if (RES) asm volatile("" ::"r"(rr[u].x) : "memory");
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) finish(i + u * step, xr[u], rr[u]);
   }
   for (; i < total; i += step) one(i);
 }
@@ -176,25 +208,29 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
 
 static bool bn_shape_ok(int C) { return C > 0 && C % 8 == 0 && C <= 16384 && C / 8 <= 64 * kBnGroups; }
 static long long gcd_ll(long long a, long long b) { return b == 0 ? a : gcd_ll(b, a % b); }
-// Row split of the two reduction passes: 4 CTAs per SM each (measured on ResNet-50: 6 or 8 for the statistics pass changes
-// nothing, 25.5 / 25.7 / 25.7 ms per step).  MLT_BN_R / MLT_BN_R_STATS override the multipliers.
+// Row split of the two reduction passes.  The statistics pass keeps eight 16-byte loads in flight per thread (67 registers, three
+// CTAs per SM), so its grid is 3 CTAs per SM: one full wave.  MLT_BN_R / MLT_BN_R_STATS override the multipliers.
 static int bn_rows_split(int M, int C, bool stats = false) {
   const int C8 = C / 8;
   const int tiles = ceil_div(C8, kBnGroups);
   const int rpi = kBnThreads / (C8 < kBnGroups ? C8 : kBnGroups);
   static int mult_r = -1, mult_s = -1;
   if (mult_r < 0) { const char* e = getenv("MLT_BN_R"); mult_r = e ? atoi(e) : 4; }
-  if (mult_s < 0) { const char* e = getenv("MLT_BN_R_STATS"); mult_s = e ? atoi(e) : 4; }
+  if (mult_s < 0) { const char* e = getenv("MLT_BN_R_STATS"); mult_s = e ? atoi(e) : 3; }
   const int mult = stats ? mult_s : mult_r;
   int R = (mult * kNumSMs) / tiles;
   const int cap = ceil_div(M, rpi * 8);               // at least 8 iterations per CTA
   if (R > cap) R = cap;
   return R < 1 ? 1 : R;
 }
-// Grid for the elementwise passes: the stride (grid * 256) must be a multiple of C/8 so channels are loop-invariant.
+// Grid for the elementwise passes: the stride (grid * 256) must be a multiple of C/8 so channels are loop-invariant.  Three CTAs per
+// SM are resident (66-77 registers with the batched loads), so 3 x 148 CTAs is one full wave; measured over the ResNet-50 shapes the
+// forward passes take 4.29 ms at 3 against 4.55 ms at 8 (profiles/r2/bn_shapes_*.json), the whole step 24.8 against 25.2 ms.
 static int bn_grid(long long items, int C8) {
   long long b = ceil_div64(items, kBnThreads);
-  const long long cap = (long long)kNumSMs * 8;
+  static int mult = -1;
+  if (mult < 0) { const char* e = getenv("MLT_BN_GRID_MULT"); mult = e ? atoi(e) : 3; if (mult < 1) mult = 1; }
+  const long long cap = (long long)kNumSMs * mult;
   if (b > cap) b = cap;
   const long long m = C8 / gcd_ll(C8, kBnThreads);       // grid * 256 must be a multiple of C8
   b = (b + m - 1) / m * m;

@@ -76,6 +76,21 @@ __device__ __forceinline__ void ld8(const __nv_bfloat16* p, float (&v)[8]) {
     v[2 * j] = f.x; v[2 * j + 1] = f.y;
   }
 }
+// volatile: the compiler keeps a run of these together instead of sinking each next to its consumer (which, with in-order issue,
+// leaves one or two loads in flight per thread)
+__device__ __forceinline__ uint4 ld8raw(const __nv_bfloat16* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void cvt8(const uint4& raw, float (&v)[8]) {
+  const uint32_t w[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[j]));
+    v[2 * j] = f.x; v[2 * j + 1] = f.y;
+  }
+}
 __device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&v)[8]) {
   uint4 o;
   o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]); o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
@@ -86,7 +101,10 @@ __device__ __forceinline__ void st8(__nv_bfloat16* p, const float (&v)[8]) {
 // accumulates one 8-channel group of one row.  A CTA folds its rows through shared memory and adds its per-channel
 // partials to acc[2][C] with fp32 atomics (a few hundred thousand per call, spread over 2*C addresses); the last CTA of
 // a tile (ticket) picks the totals up into tot[2][cw * 8] (shared memory), re-zeroes acc and returns true.
-template <bool TWO, int U = 4, typename F>
+// LOADFIRST: F has two call forms, f.load(off) -> raw value and f.use(raw, a, b); the U loads of an iteration are issued
+// before any of them is consumed (a single-stream pass needs that many 16-byte loads in flight per thread to fill HBM: with
+// load-use-load-use order ncu showed bn_stats at 52 % of DRAM peak, 28 % issue-active, long-scoreboard stalls).
+template <bool TWO, int U = 4, bool LOADFIRST = false, typename F>
 __device__ __forceinline__ bool col_reduce_atomic(F f, float* acc, unsigned int* tickets, int M, int C, float* tot) {
   const int C8 = C >> 3;
   const int g_lo = blockIdx.x * kBnGroups;
@@ -102,11 +120,24 @@ __device__ __forceinline__ bool col_reduce_atomic(F f, float* acc, unsigned int*
   if (rsub < rpi) {
     const size_t col = (size_t)(g_lo + cg) * 8;
     int r = r_lo + rsub;
-    for (; r + (U - 1) * rpi < r_hi; r += U * rpi) {   // U independent rows in flight
+    if constexpr (LOADFIRST) {
+      for (; r + (U - 1) * rpi < r_hi; r += U * rpi) {
+        decltype(f.load((size_t)0)) raw[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) f((size_t)(r + u * rpi) * C + col, a, b);
+        for (int u = 0; u < U; ++u) raw[u] = f.load((size_t)(r + u * rpi) * C + col);
+#pragma unroll
+        for (int u = 0; u < U; ++u) f.pin(raw[u]);       // every load has been issued before the first value is touched
+#pragma unroll
+        for (int u = 0; u < U; ++u) f.use(raw[u], a, b);
+      }
+      for (; r < r_hi; r += rpi) f.use(f.load((size_t)r * C + col), a, b);
+    } else {
+      for (; r + (U - 1) * rpi < r_hi; r += U * rpi) {   // U independent rows in flight
+#pragma unroll
+        for (int u = 0; u < U; ++u) f((size_t)(r + u * rpi) * C + col, a, b);
+      }
+      for (; r < r_hi; r += rpi) f((size_t)r * C + col, a, b);
     }
-    for (; r < r_hi; r += rpi) f((size_t)r * C + col, a, b);
   }
   __shared__ float sh[kBnThreads][17];
   __shared__ bool is_last;
