@@ -433,7 +433,7 @@ class LineKeeper:
             if self.is_printer and self.rec is not None:
                 if note:
                     self.rec.setdefault("notes", []).append(note)
-                print(json.dumps(self.rec), flush=True)
+                print(json.dumps(self.rec), file=OUT, flush=True)
 
     def _expire(self):
         self.emit("watchdog: time budget reached before every secondary model finished")
@@ -585,13 +585,13 @@ def run_reference(a):
 
             install_reference.install()
         except Exception as ex:  # noqa: BLE001
-            print(json.dumps({"impl": "reference", "unavailable": f"reference not installed: {ex}"[:300]}))
+            print(json.dumps({"impl": "reference", "unavailable": f"reference not installed: {ex}"[:300]}), file=OUT, flush=True)
             return
     import torch
 
     rank, local_rank, world = env_rank()
     if not torch.cuda.is_available():
-        print(json.dumps({"impl": "reference", "unavailable": "no CUDA device"}))
+        print(json.dumps({"impl": "reference", "unavailable": "no CUDA device"}), file=OUT, flush=True)
         return
     sys.path.insert(0, ROOT)
     from ml_trainer_b200.data.loader import SyntheticDataset  # noqa: F401  (datasets come from this repo; import before the path swap)
@@ -617,8 +617,21 @@ def run_reference(a):
     keeper.timer.cancel()
 
 
+OUT = sys.stdout
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries print there too (NCCL announces its version on fd 1 when a process
+    group comes up), so keep a private handle on the real stdout for the record and point fd 1 at stderr for everybody else."""
+    global OUT
+    sys.stdout.flush()
+    OUT = os.fdopen(os.dup(1), "w", buffering=1)
+    os.dup2(2, 1)
+
+
 if __name__ == "__main__":
     args = parse()
+    claim_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:

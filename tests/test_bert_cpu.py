@@ -73,3 +73,37 @@ def test_attention_mask_matches_hf():
         lh = hf(input_ids=ids, attention_mask=mask).logits
         assert torch.allclose(lo, lh, atol=2e-5), (lo - lh).abs().max()
         assert not torch.equal(lo, ours(ids))                      # the mask matters
+
+
+def test_attention_keep_mask_statement():
+    """The host statement of the in-kernel attention dropout mask (ops/functional.py::attention_keep_mask): keep rate equals
+    thr / 256, the mask is a pure function of (seed, step, call site), and changing any of the three changes it."""
+    from ml_trainer_b200.ops import functional as F
+
+    keep, scale = F.attention_keep_mask(2, 3, 128, 0.1, call_id=4, step=7, seed=1234)
+    assert keep.shape == (2, 3, 128, 128) and keep.dtype == torch.bool
+    thr = round(0.9 * 256)
+    assert abs(scale - 256.0 / thr) < 1e-9
+    assert abs(keep.float().mean().item() - thr / 256) < 0.01
+    # rows and columns are not constant (a 2 x 2 block shares one hash word, its four bytes differ)
+    assert 0.5 < keep[0, 0, 0].float().mean() < 1.0 and 0.5 < keep[0, 0, :, 0].float().mean() < 1.0
+    again, _ = F.attention_keep_mask(2, 3, 128, 0.1, call_id=4, step=7, seed=1234)
+    assert torch.equal(keep, again)
+    for kw in (dict(call_id=5, step=7, seed=1234), dict(call_id=4, step=8, seed=1234), dict(call_id=4, step=7, seed=1235)):
+        other, _ = F.attention_keep_mask(2, 3, 128, 0.1, **kw)
+        assert not torch.equal(keep, other)
+    # heads and samples draw different masks
+    assert not torch.equal(keep[0, 0], keep[0, 1]) and not torch.equal(keep[0, 0], keep[1, 0])
+
+
+def test_attention_probability_dropout_on_cpu():
+    """CPU statement of attention with dropout on the probabilities: eval is deterministic, train differs and keeps the scale."""
+    from ml_trainer_b200.ops import functional as F
+
+    torch.manual_seed(0)
+    q, k, v = (torch.randn(2, 16, 64) for _ in range(3))
+    base = F.attention(q, k, v, 2)
+    assert torch.allclose(F.attention(q, k, v, 2, None, 0.5, False), base)
+    outs = torch.stack([F.attention(q, k, v, 2, None, 0.5, True) for _ in range(400)])
+    assert not torch.allclose(outs[0], base)
+    assert (outs.mean(0) - base).abs().max() < 0.25 * base.abs().max()
