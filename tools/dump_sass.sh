@@ -14,10 +14,14 @@ dump() {  # name-fragment (mangled substring), output file
 dump "gemm_bf16_tcgen05_kernelILi128ELb0" gemm_bf16_tcgen05_bn128
 dump "gemm_bf16_tcgen05_kernelILi256ELb0" gemm_bf16_tcgen05_bn256
 dump "gemm_bf16_2cta_kernel" gemm_bf16_2cta_cta_group2
-dump "attention_fwd_tcgen05_kernelILb0" attention_fwd_tcgen05
-dump "attention_fwd_tcgen05_kernelILb1" attention_fwd_tcgen05_keybias
-dump "attention_bwd_dq_kernelILb0" attention_bwd_dq
-dump "attention_bwd_dkdv_kernelILb0" attention_bwd_dkdv
+dump "attention_fwd_tcgen05_kernelILb0ELb0" attention_fwd_tcgen05
+dump "attention_fwd_tcgen05_kernelILb1ELb0" attention_fwd_tcgen05_keybias
+dump "attention_fwd_tcgen05_kernelILb1ELb1" attention_fwd_tcgen05_keybias_dropout
+dump "attention_bwd_dq_kernelILb0ELb0" attention_bwd_dq
+dump "attention_bwd_dkdv_kernelILb0ELb0" attention_bwd_dkdv
+dump "attention_bwd_dkdv_kernelILb1ELb1" attention_bwd_dkdv_keybias_dropout
+dump "bn_stats_kernel" bn_stats
+dump "bn_apply_kernelI13__nv_bfloat16Lb1ELb1" bn_apply_residual_relu
 dump "lenet_step_cluster_kernelINS_7SgdRuleELb0" lenet_step_cluster_sgd_single
 dump "lenet_step_cluster_kernelINS_7SgdRuleELb1" lenet_step_cluster_sgd_multi
 dump "allreduce_twoshot_update_kernelINS_9AdamWRuleE13__nv_bfloat16Lb1" allreduce_nvls_update_adamw_bf16
