@@ -185,17 +185,23 @@ colsum_vec_kernel(const T* __restrict__ x, O* __restrict__ out, float* __restric
 // Bias gradients of the big GEMM layers: contiguous bf16 [M, N] with N a multiple of 8, read as a flat stream of 16-byte
 // groups and folded through shared memory + fp32 atomics (colreduce.cuh) - the same scheme as the BatchNorm reductions.
 template <typename O>
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, 3)
 colsum_flat_kernel(const __nv_bfloat16* __restrict__ x, O* __restrict__ out, float* __restrict__ acc, unsigned int* __restrict__ tickets,
                    int M, int N, int accumulate) {
   __shared__ float tot[2 * kBnGroups * 8];
-  auto f = [&](size_t off, float (&a)[8], float (&b)[8]) {
-    float v[8];
-    ld8(x + off, v);
+  struct {                                       // eight loads in flight per thread (see colreduce.cuh, LOADFIRST)
+    const __nv_bfloat16* x;
+    __device__ __forceinline__ uint4 load(size_t off) const { return ld8raw(x + off); }
+    __device__ __forceinline__ void pin(const uint4& raw) const { asm volatile("" ::"r"(raw.x) : "memory"); }
+    __device__ __forceinline__ void use(const uint4& raw, float (&a)[8], float (&b)[8]) const {
+      float v[8];
+      cvt8(raw, v);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) a[j] += v[j];
-  };
-  if (!col_reduce_atomic<false, 8>(f, acc, tickets, M, N, tot)) return;
+      for (int j = 0; j < 8; ++j) a[j] += v[j];
+      (void)b;
+    }
+  } f{x};
+  if (!col_reduce_atomic<false, 8, true>(f, acc, tickets, M, N, tot)) return;
   const int g_lo = blockIdx.x * kBnGroups;
   const int nch = min(kBnGroups, (N >> 3) - g_lo) * 8;
   for (int ch = threadIdx.x; ch < nch; ch += kBnThreads) {

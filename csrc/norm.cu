@@ -34,7 +34,7 @@ template <> __device__ __forceinline__ void load_param8<__nv_bfloat16>(const __n
 
 // y = LN(x [+ res]) * gamma + beta.  Writes y, optionally the pre-norm sum h = x + res, and mean / rstd per row.
 template <typename P>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res, const P* __restrict__ gamma,
                      const P* __restrict__ beta, __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ hsum,
                      float* __restrict__ mean_out, float* __restrict__ rstd_out, int T, int H, float eps) {
@@ -44,14 +44,27 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
   const int nvec = H / 8;
   float v[kMaxVecPerLane][8];
   float sum = 0.f;
+  // every load of the row first (a warp owns one row: its only latency hiding is the number of loads it has in flight; with the
+  // loads sunk next to their consumers a lane waited for memory four times per row), then the arithmetic
+  uint4 rx[kMaxVecPerLane], rr[kMaxVecPerLane];
+#pragma unroll
+  for (int c = 0; c < kMaxVecPerLane; ++c) {
+    const int iv = lane + 32 * c;
+    rx[c] = make_uint4(0u, 0u, 0u, 0u);
+    rr[c] = make_uint4(0u, 0u, 0u, 0u);
+    if (iv < nvec) {
+      rx[c] = *reinterpret_cast<const uint4*>(x + (size_t)row * H + iv * 8);
+      if (res != nullptr) rr[c] = *reinterpret_cast<const uint4*>(res + (size_t)row * H + iv * 8);
+    }
+  }
 #pragma unroll
   for (int c = 0; c < kMaxVecPerLane; ++c) {
     const int iv = lane + 32 * c;
     if (iv < nvec) {
-      unpack8(*reinterpret_cast<const uint4*>(x + (size_t)row * H + iv * 8), v[c]);
+      unpack8(rx[c], v[c]);
       if (res != nullptr) {
         float r[8];
-        unpack8(*reinterpret_cast<const uint4*>(res + (size_t)row * H + iv * 8), r);
+        unpack8(rr[c], r);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[c][j] += r[j];
         if (hsum != nullptr) {
@@ -159,13 +172,24 @@ layernorm_bwd_fused_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bflo
     const float mu = mean[row], rs = rstd[row];
     float gd[NV][8], xh[NV][8];
     float s1 = 0.f, s2 = 0.f;
+    uint4 rg[NV], rh[NV];                               // the row's loads go out together, then the arithmetic
+#pragma unroll
+    for (int c = 0; c < NV; ++c) {
+      const int iv = lane + 32 * c;
+      rg[c] = make_uint4(0u, 0u, 0u, 0u);
+      rh[c] = make_uint4(0u, 0u, 0u, 0u);
+      if (iv < nvec) {
+        rg[c] = *reinterpret_cast<const uint4*>(dy + (size_t)row * H + iv * 8);
+        rh[c] = *reinterpret_cast<const uint4*>(h + (size_t)row * H + iv * 8);
+      }
+    }
 #pragma unroll
     for (int c = 0; c < NV; ++c) {
       const int iv = lane + 32 * c;
       if (iv < nvec) {
         float gm[8];
-        unpack8(*reinterpret_cast<const uint4*>(dy + (size_t)row * H + iv * 8), gd[c]);
-        unpack8(*reinterpret_cast<const uint4*>(h + (size_t)row * H + iv * 8), xh[c]);
+        unpack8(rg[c], gd[c]);
+        unpack8(rh[c], xh[c]);
         load_param8<P>(gamma, iv * 8, gm);               // L1-resident; keeping it in registers costs occupancy
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
