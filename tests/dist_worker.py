@@ -56,10 +56,12 @@ def main():
             opt.step()
     theirs = {k: v.detach().cpu().clone() for k, v in ref.state_dict().items()}
     hist = t.history
+    # the epoch-end form for host values: sums over the ranks, error check included
+    host_sum = t.comm.reduce_scalars_host([float(rank + 1), 2.5, 10.0 * (rank + 1)])
     gathered = [None] * world
     dist.all_gather_object(gathered, hist)
     if rank == 0:
-        torch.save({"ours": ours, "ddp": theirs, "hist": gathered, "world": world, "launches": launches},
+        torch.save({"ours": ours, "ddp": theirs, "hist": gathered, "world": world, "launches": launches, "host_sum": host_sum},
                    os.path.join(out_dir, "result.pt"))
     dist.barrier()
     t.close()

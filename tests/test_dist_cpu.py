@@ -23,6 +23,7 @@ def test_ws2_gloo_matches_ddp(tmp_path, optimizer):
     # cross-rank reduced history: identical on both ranks (the reference leaves per-rank values unreduced)
     h0, h1 = res["hist"]
     assert h0 == h1 and len(h0["train_loss"]) == 2
+    assert res["host_sum"] == pytest.approx([3.0, 5.0, 30.0])          # reduce_scalars_host: 1 + 2, 2.5 + 2.5, 10 + 20
     # rank 0 wrote module.-prefixed keys, exactly one history file
     sd = torch.load(tmp_path / "model.pth")
     assert all(k.startswith("module.") for k in sd)

@@ -53,6 +53,7 @@ def test_ws2_p2p_matches_ddp(tmp_path, optimizer, algo, fused):
         assert torch.allclose(a, b, rtol=2e-3, atol=atol), f"{k}: max diff {(a - b).abs().max()}"
     h0, h1 = res["hist"]
     assert h0 == h1
+    assert res["host_sum"] == pytest.approx([3.0, 5.0, 30.0])         # epoch-end reduction of host values + error check in one trip
     names = res["launches"]
     if fused:
         assert names.get("lenet_step", 0) > 0 and not any(k.startswith("p2p_allreduce_update") for k in names), names
