@@ -191,3 +191,24 @@ def test_uncapturable_module_falls_back_to_eager_steps(tmp_path, monkeypatch, mo
     assert tr.model.seen > 0
     assert torch.cuda.current_stream() == stream_before
     assert torch.isfinite(torch.randn(8, device="cuda")).all()          # the device generator is not stuck in capture mode
+
+
+def test_capturable_user_module_keeps_cuda_graphs(tmp_path):
+    """The sync detector of the warm-up steps must not fire on the library's own ops: a plain user MLP ends up replaying graphs."""
+    from ml_trainer_b200 import SyntheticDataset, Trainer
+
+    class Plain(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a, self.b = torch.nn.Linear(32, 64), torch.nn.Linear(64, 4)
+
+        def forward(self, x):
+            return self.b(torch.relu(self.a(x.flatten(1))))
+
+    torch.manual_seed(3)
+    data = SyntheticDataset((32,), 4, length=32 * 8, seed=2)
+    tr = Trainer(Plain(), datasets=(data, data), epochs=2, batch_size=32, model_dir=str(tmp_path), progress=False,
+                 optimizer="adamw", lr=0.01, metric="accuracy", seed=1)
+    tr.fit()
+    assert tr.engine.use_graph and tr.engine.graph_replays > 0
+    assert tr.train_losses[-1] < tr.train_losses[0]
