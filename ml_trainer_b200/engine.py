@@ -203,14 +203,14 @@ class StepEngine:
         import warnings
 
         mode = torch.cuda.get_sync_debug_mode()
-        torch.cuda.set_sync_debug_mode("warn")
-        try:
-            with warnings.catch_warnings(record=True) as caught:
-                warnings.simplefilter("always")
+        with warnings.catch_warnings(record=True) as caught:
+            warnings.simplefilter("always")
+            torch.cuda.set_sync_debug_mode("warn")        # (announces itself as a prototype feature: recorded, not shown)
+            try:
                 self._train_body(inputs, targets)
-        finally:
-            torch.cuda.set_sync_debug_mode(mode)
-        if any("synchroniz" in str(w.message) for w in caught):
+            finally:
+                torch.cuda.set_sync_debug_mode(mode)
+        if any("synchroniz" in str(w.message) and "prototype" not in str(w.message) for w in caught):
             logging.getLogger("ml_trainer_b200").warning(
                 "the training step synchronises with the host (e.g. .item() in forward): CUDA graphs are off for this model")
             self.use_graph = False
