@@ -38,7 +38,7 @@ struct GemmParams {
   const void* bias;
   int bias_f32;
   int act;        // Act
-  int aux_mode;   // 0 none | 1 store pre-activation (bf16) to aux | 2 multiply by act'(aux) | 3 store act'(pre) | 4 multiply by aux
+  int aux_mode;   // 0 none | 1 store pre-activation (bf16) to aux | 2 multiply by act'(aux) | 3 store act'(pre) | 4 multiply by aux | 5 add aux
   void* aux;
   long long ld_aux;
   int a_mn, b_mn;
@@ -107,7 +107,7 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
                                               int pair_id, int pair_half) {
   const int chunks_per_slab = p.out_f32 ? 1 : 2;          // a 32-column chunk is 128 B of fp32 or 64 B of bf16
   const bool pair = pair_id > 0;
-  const bool aux_in = p.aux_mode == 2 || p.aux_mode == 4;
+  const bool aux_in = p.aux_mode == 2 || p.aux_mode == 4 || p.aux_mode == 5;
   // aux operand of the first chunk: requested before the accumulator is ready, then one chunk ahead
   const __nv_bfloat16* aux_row = reinterpret_cast<const __nv_bfloat16*>(p.aux) + (size_t)row * p.ld_aux;
   uint4 pa[4] = {};
@@ -225,6 +225,9 @@ __device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtenso
         if (p.aux_mode == 4) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] *= s[j];
+        } else if (p.aux_mode == 5) {                    // D = A B^T + aux (aux may be the output itself: a tile reads what it overwrites)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] += s[j];
         } else if (p.act == ACT_GELU && !p.out_f32) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) { float g, dg; gelu_both(s[j], g, dg); v[j] *= dg; }

@@ -11,6 +11,8 @@ CPU path: the same modules through plain ``torch.nn.functional`` calls.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn.functional as TF
 from torch import nn
@@ -23,6 +25,9 @@ def _conv(cin, cout, k, stride=1, pad=0):
     m = nn.Conv2d(cin, cout, k, stride=stride, padding=pad, bias=False)
     m.weight._mlt_channels_last = True      # FusedOptimizer lays it out as [Cout, KH, KW, Cin]
     return m
+
+
+_SKIP_GRAD_FUSION = os.environ.get("MLT_SKIP_GRAD_FUSION", "1") != "0"
 
 
 class Bottleneck(nn.Module):
@@ -52,14 +57,19 @@ class Bottleneck(nn.Module):
     def forward_nhwc(self, x):
         from ..ops import conv as C
 
-        o = C.batch_norm_nhwc(C.conv2d_nhwc(x, self.conv1.weight), self.bn1, relu=True)
+        # identity skip: the block input gets its skip gradient added inside conv1's data-gradient GEMM (ops/conv.py::SkipGrad)
+        skip = None
+        if (self.downsample is None and self.bn3.training and torch.is_grad_enabled() and x.requires_grad
+                and _SKIP_GRAD_FUSION):
+            skip = C.SkipGrad()
+        o = C.batch_norm_nhwc(C.conv2d_nhwc(x, self.conv1.weight, skip=skip), self.bn1, relu=True)
         o = C.batch_norm_nhwc(C.conv2d_nhwc(o, self.conv2.weight, self.stride, 1), self.bn2, relu=True)
         o = C.conv2d_nhwc(o, self.conv3.weight)
         if self.downsample is not None:
             idt = C.batch_norm_nhwc(C.conv2d_nhwc(x, self.downsample[0].weight, self.stride, 0), self.downsample[1])
         else:
             idt = x
-        return C.batch_norm_nhwc(o, self.bn3, relu=True, residual=idt)      # relu(bn3(conv3) + identity), one pass
+        return C.batch_norm_nhwc(o, self.bn3, relu=True, residual=idt, skip=skip)      # relu(bn3(conv3) + identity), one pass
 
 
 class ResNet(nn.Module):
