@@ -40,8 +40,8 @@ class _LN(nn.Module):
         self.bias = nn.Parameter(torch.zeros(h))
         self.eps = eps
 
-    def forward(self, x, residual=None):
-        return F.layer_norm(x, self.weight, self.bias, self.eps, residual=residual)
+    def forward(self, x, residual=None, skip=None):
+        return F.layer_norm(x, self.weight, self.bias, self.eps, residual=residual, skip=skip)
 
 
 class BertEmbeddings(nn.Module):
@@ -73,7 +73,14 @@ class BertSelfAttention(nn.Module):
             lin.weight._mlt_pack = (("qkv.w", id(self)), i, 3)
             lin.bias._mlt_pack = (("qkv.b", id(self)), i, 3)
 
-    def forward(self, x, mask_bias=None):
+    def packed_ok(self, x) -> bool:
+        from ..ops.gemm import linear_packed_ok
+
+        wpack = getattr(self.query.weight, "_mlt_packed", None)
+        bpack = getattr(self.query.bias, "_mlt_packed", None)
+        return bpack is not None and linear_packed_ok(x, wpack, bpack)
+
+    def forward(self, x, mask_bias=None, skip=None):
         from ..ops.gemm import linear_packed, linear_packed_ok
 
         # the key-padding mask rides into the fused kernels as a per-key additive bias, and dropout on the probabilities is
@@ -81,7 +88,7 @@ class BertSelfAttention(nn.Module):
         wpack = getattr(self.query.weight, "_mlt_packed", None)
         bpack = getattr(self.query.bias, "_mlt_packed", None)
         if bpack is not None and linear_packed_ok(x, wpack, bpack):
-            return F.attention_packed(linear_packed(x, wpack, bpack), self.heads, mask_bias, self.p_attn, self.training)
+            return F.attention_packed(linear_packed(x, wpack, bpack, skip=skip), self.heads, mask_bias, self.p_attn, self.training)
         q = F.linear_act(x, self.query.weight, self.query.bias)
         k = F.linear_act(x, self.key.weight, self.key.bias)
         v = F.linear_act(x, self.value.weight, self.value.bias)
@@ -95,9 +102,9 @@ class BertSelfOutput(nn.Module):
         self.LayerNorm = _LN(c.hidden_size, c.layer_norm_eps)
         self.p_drop = c.hidden_dropout_prob
 
-    def forward(self, ctx, x):
+    def forward(self, ctx, x, skip=None):
         h = F.dropout(F.linear_act(ctx, self.dense.weight, self.dense.bias), self.p_drop, self.training)
-        return self.LayerNorm(h, residual=x)
+        return self.LayerNorm(h, residual=x, skip=skip)
 
 
 class BertAttention(nn.Module):
@@ -107,7 +114,13 @@ class BertAttention(nn.Module):
         self.output = BertSelfOutput(c)
 
     def forward(self, x, mask_bias=None):
-        return self.output(self.self(x, mask_bias), x)
+        # x feeds the Q/K/V projection and, as the residual, the LayerNorm after the block: the LayerNorm's input gradient is
+        # added inside the projection's data-gradient GEMM instead of by a separate kernel (ops/functional.py::SkipGrad)
+        skip = None
+        if (F.SKIP_GRAD_FUSION and torch.is_grad_enabled() and x.requires_grad and self.self.packed_ok(x)
+                and F.layer_norm_native_ok(x, self.output.LayerNorm.weight)):
+            skip = F.SkipGrad()
+        return self.output(self.self(x, mask_bias, skip), x, skip)
 
 
 class BertIntermediate(nn.Module):
@@ -142,10 +155,15 @@ class BertLayer(nn.Module):
         a = self.attention(x, mask_bias)
         i, o = self.intermediate.dense, self.output.dense
         if a.is_cuda and a.dtype == torch.bfloat16 and F.use_native(a, i.weight):
-            from ..ops.gemm import ffn_tc          # both FFN GEMMs + GELU (and its backward) as one autograd node
+            from ..ops.gemm import ffn_fast_path_ok, ffn_tc          # both FFN GEMMs + GELU (and its backward) as one autograd node
 
-            h = F.dropout(ffn_tc(a, i.weight, i.bias, o.weight, o.bias, "gelu"), self.output.p_drop, self.training)
-            return self.output.LayerNorm(h, residual=a)
+            skip = None
+            if (F.SKIP_GRAD_FUSION and torch.is_grad_enabled() and a.requires_grad
+                    and ffn_fast_path_ok(a, i.weight, i.bias, o.weight, o.bias, "gelu")
+                    and F.layer_norm_native_ok(a, self.output.LayerNorm.weight)):
+                skip = F.SkipGrad()
+            h = F.dropout(ffn_tc(a, i.weight, i.bias, o.weight, o.bias, "gelu", skip=skip), self.output.p_drop, self.training)
+            return self.output.LayerNorm(h, residual=a, skip=skip)
         return self.output(self.intermediate(a), a)
 
 

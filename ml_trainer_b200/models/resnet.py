@@ -11,8 +11,6 @@ CPU path: the same modules through plain ``torch.nn.functional`` calls.
 """
 from __future__ import annotations
 
-import os
-
 import torch
 import torch.nn.functional as TF
 from torch import nn
@@ -25,9 +23,6 @@ def _conv(cin, cout, k, stride=1, pad=0):
     m = nn.Conv2d(cin, cout, k, stride=stride, padding=pad, bias=False)
     m.weight._mlt_channels_last = True      # FusedOptimizer lays it out as [Cout, KH, KW, Cin]
     return m
-
-
-_SKIP_GRAD_FUSION = os.environ.get("MLT_SKIP_GRAD_FUSION", "1") != "0"
 
 
 class Bottleneck(nn.Module):
@@ -60,7 +55,7 @@ class Bottleneck(nn.Module):
         # identity skip: the block input gets its skip gradient added inside conv1's data-gradient GEMM (ops/conv.py::SkipGrad)
         skip = None
         if (self.downsample is None and self.bn3.training and torch.is_grad_enabled() and x.requires_grad
-                and _SKIP_GRAD_FUSION):
+                and F.SKIP_GRAD_FUSION):
             skip = C.SkipGrad()
         o = C.batch_norm_nhwc(C.conv2d_nhwc(x, self.conv1.weight, skip=skip), self.bn1, relu=True)
         o = C.batch_norm_nhwc(C.conv2d_nhwc(o, self.conv2.weight, self.stride, 1), self.bn2, relu=True)

@@ -16,7 +16,7 @@ import torch.nn.functional as TF
 
 from . import _lib
 from ._lib import check, launches, ptr, stream_handle
-from .functional import _deliver, _has_sink, _sink, scratch, use_native
+from .functional import SkipGrad, _deliver, _has_sink, _sink, scratch, use_native
 from .gemm import gemm
 
 _c_int, _c_ll, _c_f = ctypes.c_int, ctypes.c_longlong, ctypes.c_float
@@ -72,19 +72,6 @@ def _conv_wgrad_implicit(dy2, x, Co, KH, KW, stride, pad, out, out_dtype):
           "mlt_conv_wgrad_implicit")
     launches.bump("conv_wgrad_implicit_gemm")
     return out
-
-
-class SkipGrad:
-    """Side channel for the gradient of an identity skip connection.  In ``y = relu(bn(conv_c(..conv_a(x)..)) + x)`` the input
-    ``x`` receives two gradients: the data gradient of ``conv_a`` and the masked output gradient that BatchNorm's backward hands
-    to its residual input.  Autograd would add them with one more elementwise kernel (three passes over the block input; 1.2 ms
-    of a ResNet-50 step).  With a ``SkipGrad`` shared by the two calls, BatchNorm's backward parks the residual gradient here
-    and returns none, and ``conv_a``'s data-gradient GEMM adds it in its epilogue (``aux_mode`` 5, in place)."""
-
-    __slots__ = ("dres",)
-
-    def __init__(self):
-        self.dres = None
 
 
 class _ConvNHWCFn(torch.autograd.Function):

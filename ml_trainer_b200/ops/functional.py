@@ -12,6 +12,7 @@ AccumulateGrad kernel and no flatten copy (SURVEY §7.3 "grads produced directly
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional
 
 import torch
@@ -559,17 +560,36 @@ def dropout(x: torch.Tensor, p: float, training: bool = True) -> torch.Tensor:
 # ----------------------------------------------------------------------------------------------
 # transformer pieces: LayerNorm (+ residual), attention core, embeddings  (bf16 activations)
 # ----------------------------------------------------------------------------------------------
+SKIP_GRAD_FUSION = os.environ.get("MLT_SKIP_GRAD_FUSION", "1") != "0"
+
+
+class SkipGrad:
+    """Side channel for the gradient of an identity skip connection.  In ``y = relu(bn(conv_c(..conv_a(x)..)) + x)`` the input
+    ``x`` receives two gradients: the data gradient of ``conv_a`` and the masked output gradient that BatchNorm's backward hands
+    to its residual input.  Autograd would add them with one more elementwise kernel (three passes over the block input; 1.2 ms
+    of a ResNet-50 step).  With a ``SkipGrad`` shared by the two calls, BatchNorm's backward parks the residual gradient here
+    and returns none, and ``conv_a``'s data-gradient GEMM adds it in its epilogue (``aux_mode`` 5).  The same pattern serves the transformer
+    block: ``LN(f(x) + x)`` parks LayerNorm's input gradient, the data-gradient GEMM of ``f``'s first layer (the packed Q/K/V
+    projection, the first MLP layer) picks it up."""
+
+    __slots__ = ("dres",)
+
+    def __init__(self):
+        self.dres = None
+
+
 class _LayerNormFn(torch.autograd.Function):
     """``LN(x [+ residual]) * gamma + beta``; the residual add is fused, its gradient is the LN input gradient."""
 
     @staticmethod
-    def forward(ctx, x, residual, gamma, beta, eps, gparam, bparam):
+    def forward(ctx, x, residual, gamma, beta, eps, gparam, bparam, skip=None):
         H = x.shape[-1]
         x2 = x.reshape(-1, H).contiguous()
         r2 = residual.reshape(-1, H).contiguous() if residual is not None else None
         T = x2.shape[0]
         y = torch.empty_like(x2)
         hsum = torch.empty_like(x2) if r2 is not None else None
+        ctx.skip = skip if residual is not None else None
         mean = torch.empty(T, dtype=torch.float32, device=x.device)
         rstd = torch.empty(T, dtype=torch.float32, device=x.device)
         check(_lib.lib().mlt_layernorm_fwd(ptr(x2), ptr(r2), ptr(gamma), ptr(beta), _c_int(int(gamma.dtype == torch.bfloat16)),
@@ -601,15 +621,26 @@ class _LayerNormFn(torch.autograd.Function):
                                   _c_int(T), _c_int(H), stream_handle()), "mlt_layernorm_bwd")
         launches.bump("layernorm_bwd")
         dxv = dx.view(ctx.shape)
-        return dxv, (dxv if ctx.has_res else None), _deliver(gparam, dg, gsink), _deliver(bparam, db, bsink), None, None, None
+        gres = dxv if ctx.has_res else None
+        if ctx.skip is not None and ctx.has_res:
+            ctx.skip.dres, gres = dx, None            # [T, H]: added by the data-gradient GEMM that produces the other half
+        return dxv, gres, _deliver(gparam, dg, gsink), _deliver(bparam, db, bsink), None, None, None, None
 
 
-def layer_norm(x, gamma, beta, eps: float = 1e-12, residual=None):
+def layer_norm_native_ok(x, gamma) -> bool:
     H = x.shape[-1]
-    if use_native(x, gamma) and x.dtype == torch.bfloat16 and H % 8 == 0 and H <= 1024 and gamma.dtype in (torch.bfloat16, torch.float32):
+    return bool(use_native(x, gamma) and x.dtype == torch.bfloat16 and H % 8 == 0 and H <= 1024
+                and gamma.dtype in (torch.bfloat16, torch.float32))
+
+
+def layer_norm(x, gamma, beta, eps: float = 1e-12, residual=None, skip=None):
+    """``skip`` (with ``residual``): see :class:`SkipGrad`; only pass one when :func:`layer_norm_native_ok` holds."""
+    H = x.shape[-1]
+    if layer_norm_native_ok(x, gamma):
         if _has_sink(gamma, beta):
-            return _LayerNormFn.apply(x, residual, gamma.detach(), beta.detach(), eps, gamma, beta)
-        return _LayerNormFn.apply(x, residual, gamma, beta, eps, None, None)
+            return _LayerNormFn.apply(x, residual, gamma.detach(), beta.detach(), eps, gamma, beta, skip)
+        return _LayerNormFn.apply(x, residual, gamma, beta, eps, None, None, skip)
+    assert skip is None, "layer_norm: a SkipGrad needs the native path"
     h = x if residual is None else x + residual
     return TF.layer_norm(h.float(), (H,), gamma.float(), beta.float(), eps).to(x.dtype)
 

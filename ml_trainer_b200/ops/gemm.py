@@ -146,7 +146,8 @@ class _FFNFn(torch.autograd.Function):
     AUX_FWD, AUX_BWD = 3, 4          # store act'(z1) / multiply by it;  (1, 2) = store z1 / multiply by act'(z1)
 
     @staticmethod
-    def forward(ctx, x2, w1, b1, w2, b2, act, params):
+    def forward(ctx, x2, w1, b1, w2, b2, act, params, skip=None):
+        ctx.skip = skip
         dact = torch.empty((x2.shape[0], w1.shape[0]), dtype=torch.bfloat16, device=x2.device)
         f = gemm(x2, w1, False, False, bias=b1, act=act, aux_mode=_FFNFn.AUX_FWD, aux=dact)
         y = gemm(f, w2, False, False, bias=b2)
@@ -164,30 +165,52 @@ class _FFNFn(torch.autograd.Function):
         dz = gemm(dy, w2, False, True, act=ctx.act, aux_mode=_FFNFn.AUX_BWD, aux=dact)   # (dy W2) * act'(z1)
         gw2 = _wgrad_into(dy, f, w2p, w2)
         gb2 = _bgrad_into(dy, b2p) if ctx.has_bias[1] else None
-        dx = gemm(dz, w1, False, True) if ctx.needs_input_grad[0] else None
+        dx = _dgrad_plus_skip(dz, w1, ctx.skip) if ctx.needs_input_grad[0] else None
+        if ctx.skip is not None:
+            ctx.skip.dres = None
         gw1 = _wgrad_into(dz, x2, w1p, w1)
         gb1 = _bgrad_into(dz, b1p) if ctx.has_bias[0] else None
-        return dx, gw1, gb1, gw2, gb2, None, None
+        return dx, gw1, gb1, gw2, gb2, None, None, None
 
 
-def ffn_tc(x, w1, b1, w2, b2, act: str = "gelu"):
-    """Transformer MLP block on the tensor cores; falls back to two :func:`linear_act_tc` calls off the fast path."""
+def _dgrad_plus_skip(dy, w, skip):
+    """``dy @ w`` (the data gradient of a linear layer), plus the gradient an identity skip connection parked in ``skip``
+    (ops/functional.py::SkipGrad) - added in the GEMM's epilogue instead of by a separate elementwise kernel."""
+    parked = skip.dres if skip is not None else None
+    if parked is None:
+        return gemm(dy, w, False, True)
+    skip.dres = None
+    if parked.dtype == torch.bfloat16 and parked.dim() == 2 and parked.stride(1) == 1 and parked.data_ptr() % 16 == 0 \
+            and parked.stride(0) % 8 == 0 and parked.shape == (dy.shape[0], w.shape[1]):
+        return gemm(dy, w, False, True, aux_mode=5, aux=parked)
+    return gemm(dy, w, False, True) + parked.reshape(dy.shape[0], w.shape[1])
+
+
+def ffn_fast_path_ok(x, w1, b1, w2, b2, act: str = "gelu") -> bool:
+    x2 = x.reshape(-1, x.shape[-1])
+    return bool(gemm_supported(x2, w1) and w2.is_cuda and w2.dtype == torch.bfloat16 and w2.stride(1) == 1 and w2.stride(0) % 8 == 0
+                and w1.shape[0] % 8 == 0 and w2.shape[0] % 8 == 0 and act in ("gelu", "relu", "tanh")
+                and all(b is None or b.dtype == torch.bfloat16 for b in (b1, b2)))
+
+
+def ffn_tc(x, w1, b1, w2, b2, act: str = "gelu", skip=None):
+    """Transformer MLP block on the tensor cores; falls back to two :func:`linear_act_tc` calls off the fast path.
+    ``skip``: a SkipGrad shared with the LayerNorm that adds this block's input back (only on the fast path, with grad)."""
     from .functional import _has_sink
 
     lead = x.shape[:-1]
     x2 = x.reshape(-1, x.shape[-1])
-    ok = (gemm_supported(x2, w1) and w2.is_cuda and w2.dtype == torch.bfloat16 and w2.stride(1) == 1 and w2.stride(0) % 8 == 0
-          and w1.shape[0] % 8 == 0 and w2.shape[0] % 8 == 0 and act in ("gelu", "relu", "tanh")
-          and all(b is None or b.dtype == torch.bfloat16 for b in (b1, b2)))
+    ok = ffn_fast_path_ok(x, w1, b1, w2, b2, act)
+    assert skip is None or (ok and torch.is_grad_enabled()), "ffn_tc: a SkipGrad needs the fast path"
     if not ok:
         return linear_act_tc(linear_act_tc(x, w1, b1, act), w2, b2)
     if not torch.is_grad_enabled():
         return gemm(gemm(x2, w1, False, False, bias=b1, act=act), w2, False, False, bias=b2).reshape(*lead, w2.shape[0])
     det = lambda t: None if t is None else t.detach()
     if _has_sink(w1, b1) and _has_sink(w2, b2):
-        y = _FFNFn.apply(x2, det(w1), det(b1), det(w2), det(b2), act, (w1, b1, w2, b2))
+        y = _FFNFn.apply(x2, det(w1), det(b1), det(w2), det(b2), act, (w1, b1, w2, b2), skip)
     else:
-        y = _FFNFn.apply(x2, w1, b1, w2, b2, act, (None, None, None, None))
+        y = _FFNFn.apply(x2, w1, b1, w2, b2, act, (None, None, None, None), skip)
     return y.reshape(*lead, w2.shape[0])
 
 
@@ -197,7 +220,8 @@ class _LinearTCPackedFn(torch.autograd.Function):
     are one tcgen05 GEMM each instead of three, and the dgrad needs no gradient accumulation."""
 
     @staticmethod
-    def forward(ctx, x2, wpack, bpack):
+    def forward(ctx, x2, wpack, bpack, skip=None):
+        ctx.skip = skip
         w = wpack.data
         y = gemm(x2, w, False, False, bias=bpack.data if bpack is not None else None)
         ctx.save_for_backward(x2, w)
@@ -211,7 +235,9 @@ class _LinearTCPackedFn(torch.autograd.Function):
         x2, w = ctx.saved_tensors
         wpack, bpack = ctx.packs
         dy = dy.contiguous()
-        dx = gemm(dy, w, False, True) if ctx.needs_input_grad[0] else None
+        dx = _dgrad_plus_skip(dy, w, ctx.skip) if ctx.needs_input_grad[0] else None
+        if ctx.skip is not None:
+            ctx.skip.dres = None
         if wpack.first_arrival():
             gemm(dy, x2, True, True, out=wpack.grad)
         else:                                    # the packed layers are applied more than once per forward pass
@@ -223,10 +249,10 @@ class _LinearTCPackedFn(torch.autograd.Function):
             else:
                 bpack.grad.add_(colsum(dy).to(bpack.grad.dtype))
             bpack.deliver()
-        return dx, None, None
+        return dx, None, None, None
 
 
-def linear_packed(x, wpack, bpack=None):
+def linear_packed(x, wpack, bpack=None, skip=None):
     """``x @ [W0; W1; ...]^T + [b0; b1; ...]`` for parameters packed by the FusedOptimizer; returns ``[..., sum(out_i)]``."""
     lead = x.shape[:-1]
     x2 = x.reshape(-1, x.shape[-1])
@@ -234,7 +260,7 @@ def linear_packed(x, wpack, bpack=None):
         wpack.note_use()
         if bpack is not None:
             bpack.note_use()
-    y = _LinearTCPackedFn.apply(x2, wpack, bpack)
+    y = _LinearTCPackedFn.apply(x2, wpack, bpack, skip)
     return y.reshape(*lead, wpack.data.shape[0])
 
 
