@@ -342,7 +342,7 @@ def cmd_fault(out_dir, fused):
 # ------------------------------------------------------------------------------------------------ lenet
 def cmd_lenet(out_dir, steps="200"):
     """The single-kernel MLModel step with its in-kernel exchange, back to back through the native executor and as one
-    multi-step launch: replicas must stay bit-identical and the loss must fall."""
+    multi-step launch: replicas must stay bit-identical and the loss must not run away."""
     rank, world, dev = setup()
     n = int(steps)
     tr = SyntheticDataset((3, 32, 32), 10, length=32 * world * n, seed=11, pool=4096)
