@@ -166,7 +166,7 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 
 // dx = gamma * rstd * (dz - dbeta/M - xhat * dgamma/M);  dres = dz (gradient of the fused residual input)
 template <typename P, bool RES, bool RELU>
-__global__ void __launch_bounds__(kBnThreads)
+__global__ void __launch_bounds__(kBnThreads, 2)
 bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const unsigned char* __restrict__ mask,
                     const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ rstd, const P* __restrict__ gamma,
                     const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres, long long total,
@@ -199,6 +199,35 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
     st8(dx + e * 8, d);
     if (RES) st8(dres + e * 8, g);
   };
+  // four positions per iteration with every load issued first (dy, x and the mask byte of each), then arithmetic and stores
+  auto finish = [&](long long e, const uint4& gr, const uint4& xr, unsigned int bits) {
+    float g[8], v[8], d[8];
+    cvt8(gr, g);
+    cvt8(xr, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float dz = (RELU && !((bits >> j) & 1u)) ? 0.f : g[j];
+      d[j] = fmaf(A[j], dz, fmaf(Bc[j], v[j] - mu[j], K[j]));
+      g[j] = dz;
+    }
+    st8(dx + e * 8, d);
+    if (RES) st8(dres + e * 8, g);
+  };
+  if (!RELU || mask != nullptr) {
+    for (; i + 3 * step < total; i += 4 * step) {
+      uint4 gr[4], xr[4];
+      unsigned int bits[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long long e = i + u * step;
+        gr[u] = ld8raw(dy + e * 8);
+        xr[u] = ld8raw(x + e * 8);
+        bits[u] = RELU ? (unsigned int)mask[e] : 0xFFu;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) finish(i + u * step, gr[u], xr[u], bits[u]);
+    }
+  }
   for (; i + step < total; i += 2 * step) {
     one(i);
     one(i + step);
@@ -226,10 +255,11 @@ static int bn_rows_split(int M, int C, bool stats = false) {
 // Grid for the elementwise passes: the stride (grid * 256) must be a multiple of C/8 so channels are loop-invariant.  Three CTAs per
 // SM are resident (66-77 registers with the batched loads), so 3 x 148 CTAs is one full wave; measured over the ResNet-50 shapes the
 // forward passes take 4.29 ms at 3 against 4.55 ms at 8 (profiles/r2/bn_shapes_*.json), the whole step 24.8 against 25.2 ms.
-static int bn_grid(long long items, int C8) {
+static int bn_grid(long long items, int C8, int resident_per_sm = 3) {
   long long b = ceil_div64(items, kBnThreads);
-  static int mult = -1;
-  if (mult < 0) { const char* e = getenv("MLT_BN_GRID_MULT"); mult = e ? atoi(e) : 3; if (mult < 1) mult = 1; }
+  static int env_mult = -1;
+  if (env_mult < 0) { const char* e = getenv("MLT_BN_GRID_MULT"); env_mult = e ? atoi(e) : 0; if (env_mult < 0) env_mult = 0; }
+  const int mult = env_mult > 0 ? env_mult : resident_per_sm;
   const long long cap = (long long)kNumSMs * mult;
   if (b > cap) b = cap;
   const long long m = C8 / gcd_ll(C8, kBnThreads);       // grid * 256 must be a multiple of C8
@@ -326,7 +356,7 @@ extern "C" int mlt_bn_bwd(const void* dy, const void* y, const void* relu_mask, 
   MLT_LAUNCH_CHECK();
   const int C8 = C / 8;
   const long long total = (long long)M * C8;
-  const int g = bn_grid(total, C8);
+  const int g = bn_grid(total, C8, 2);          // 92-96 registers with the batched loads: two CTAs per SM are resident
   const float inv_M = 1.0f / (float)M;
   if (params_bf16) bn_bwd_apply_launch<__nv_bfloat16>(g, st, dy, y, relu_mask, x, mean, rstd, gamma, su, dx, dres, total, C8, inv_M, relu);
   else bn_bwd_apply_launch<float>(g, st, dy, y, relu_mask, x, mean, rstd, gamma, su, dx, dres, total, C8, inv_M, relu);
