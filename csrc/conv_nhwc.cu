@@ -73,6 +73,42 @@ col2im_nhwc_kernel(const uint4* __restrict__ dcol, uint4* __restrict__ dx, int B
   }
 }
 
+// The same with a compile-time window (square K, stride S, pad P): at most ceil(K / S)^2 taps reach an input pixel; their loads are
+// issued together, then summed in the generic kernel's order (kh ascending, kw ascending).
+template <int K, int S, int P>
+__global__ void __launch_bounds__(256)
+col2im_nhwc_fixed_kernel(const uint4* __restrict__ dcol, uint4* __restrict__ dx, int B, int H, int W, int C8, int OH, int OW) {
+  constexpr int T = (K + S - 1) / S;
+  const long long total = (long long)B * H * W * C8;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
+    const int c = (int)(i % C8);
+    long long r = i / C8;
+    const int w = (int)(r % W); r /= W;
+    const int h = (int)(r % H);
+    const int b = (int)(r / H);
+    const int kh0 = (h + P) % S, kw0 = (w + P) % S;
+    uint4 raw[T * T];
+    bool ok[T * T];
+#pragma unroll
+    for (int a = 0; a < T; ++a) {
+#pragma unroll
+      for (int e = 0; e < T; ++e) {
+        const int kh = kh0 + a * S, kw = kw0 + e * S;
+        const int oh = (h + P - kh) / S, ow = (w + P - kw) / S;
+        const bool in = kh < K && kw < K && h + P - kh >= 0 && w + P - kw >= 0 && oh < OH && ow < OW;
+        ok[a * T + e] = in;
+        raw[a * T + e] = in ? dcol[((((size_t)b * OH + oh) * OW + ow) * K * K + kh * K + kw) * C8 + c] : make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int q = 0; q < T * T; ++q)
+      if (ok[q]) add8(acc, raw[q]);
+    dx[i] = pack8f(acc);
+  }
+}
+
 // NCHW fp32 -> NHWC bf16 with the channel dim zero-padded to Cp (a multiple of 8; the 3-channel stem is padded to 8).
 // A thread produces 8 channels of one pixel: 8 plane reads that are coalesced across the warp (consecutive pixels) and one
 // 16-byte store.
@@ -304,6 +340,14 @@ extern "C" int mlt_col2im_nhwc(const void* dcol, void* dx, int B, int H, int W, 
                                int OW, void* stream) {
   MLT_REQUIRE(C % 8 == 0, "mlt_col2im_nhwc: channels (%d) must be a multiple of 8", C);
   const long long total = (long long)B * H * W * (C / 8);
+  if (KH == KW && stride == 2 && ((KH == 3 && pad == 1) || (KH == 1 && pad == 0))) {       // ResNet's two stride-2 convolutions
+    if (KH == 3)
+      col2im_nhwc_fixed_kernel<3, 2, 1><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const uint4*)dcol, (uint4*)dx, B, H, W, C / 8, OH, OW);
+    else
+      col2im_nhwc_fixed_kernel<1, 2, 0><<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const uint4*)dcol, (uint4*)dx, B, H, W, C / 8, OH, OW);
+    MLT_LAUNCH_CHECK();
+    return 0;
+  }
   col2im_nhwc_kernel<<<grid_for(total), 256, 0, (cudaStream_t)stream>>>((const uint4*)dcol, (uint4*)dx, B, H, W, C / 8, KH, KW, stride,
                                                                        pad, OH, OW);
   MLT_LAUNCH_CHECK();
