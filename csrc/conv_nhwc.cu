@@ -29,35 +29,45 @@ im2col_nhwc_kernel(const uint4* __restrict__ x, uint4* __restrict__ col, int B, 
   }
 }
 
-// The 8-channel (padded 3-channel) stem: one thread copies one filter ROW of one output pixel - KW consecutive pixels of the
-// image, KW consecutive 16-byte chunks of the patch matrix - with every load issued before the first store and 32-bit index
-// arithmetic.  (The element-per-thread kernel above spends five 64-bit divisions and one dependent load per 16 bytes: 1.1 ms for
-// ResNet-50's 7x7/2 stem at batch 256, whose 2.5 GB patch matrix needs 0.4 ms to write.)
-template <int KW>
+// The 8-channel (padded 3-channel) stem with a compile-time filter: consecutive threads copy consecutive 16-byte chunks of the
+// patch matrix (coalesced stores, and loads that walk consecutive pixels of a filter row), four chunks per thread and iteration
+// with the four loads issued first; the tap index comes from divisions by constants and everything is 32-bit.  (The generic
+// kernel above spends five 64-bit divisions and one dependent load per 16 bytes: 1.1 ms for ResNet-50's 7x7/2 stem at batch 256,
+// whose 2.5 GB patch matrix needs 0.4 ms to write.  A thread-per-filter-row variant was slower still, 1.27 ms: its stores are
+// 112 bytes apart across a warp.)
+template <int KH, int KW>
 __global__ void __launch_bounds__(256, 4)
-im2col_rows_c8_kernel(const uint4* __restrict__ x, uint4* __restrict__ col, int B, int H, int W, int KH, int stride, int pad, int OH,
-                      int OW) {
-  const unsigned int total = (unsigned int)B * OH * OW * KH;                 // (output pixel, filter row) pairs
+im2col_c8_fixed_kernel(const uint4* __restrict__ x, uint4* __restrict__ col, int B, int H, int W, int stride, int pad, int OH, int OW) {
+  const unsigned int total = (unsigned int)B * OH * OW * (KH * KW);
   const unsigned int step = gridDim.x * blockDim.x;
-  for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += step) {
-    const unsigned int m = i / (unsigned int)KH;
-    const int kh = (int)(i - m * (unsigned int)KH);
+  auto locate = [&](unsigned int i, bool& in) -> size_t {
+    const unsigned int m = i / (unsigned int)(KH * KW);
+    const int t = (int)(i - m * (unsigned int)(KH * KW));
+    const int kh = t / KW, kw = t - kh * KW;
     const int ow = (int)(m % (unsigned int)OW);
-    const unsigned int t = m / (unsigned int)OW;
-    const int oh = (int)(t % (unsigned int)OH);
-    const int b = (int)(t / (unsigned int)OH);
-    const int h = oh * stride - pad + kh, w0 = ow * stride - pad;
-    const bool row_in = h >= 0 && h < H;
-    const uint4* src = x + ((size_t)b * H + (row_in ? h : 0)) * W;
-    uint4 v[KW];
+    const unsigned int r = m / (unsigned int)OW;
+    const int oh = (int)(r % (unsigned int)OH);
+    const int b = (int)(r / (unsigned int)OH);
+    const int h = oh * stride - pad + kh, w = ow * stride - pad + kw;
+    in = h >= 0 && h < H && w >= 0 && w < W;
+    return in ? ((size_t)b * H + h) * W + w : 0;
+  };
+  unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i < total && total - i > 3 * step; i += 4 * step) {
+    uint4 v[4];
 #pragma unroll
-    for (int kw = 0; kw < KW; ++kw) {
-      const int w = w0 + kw;
-      v[kw] = (row_in && w >= 0 && w < W) ? src[w] : make_uint4(0u, 0u, 0u, 0u);
+    for (int u = 0; u < 4; ++u) {
+      bool in;
+      const size_t src = locate(i + u * step, in);
+      v[u] = in ? x[src] : make_uint4(0u, 0u, 0u, 0u);
     }
-    uint4* dst = col + (size_t)i * KW;
 #pragma unroll
-    for (int kw = 0; kw < KW; ++kw) dst[kw] = v[kw];
+    for (int u = 0; u < 4; ++u) col[i + u * step] = v[u];
+  }
+  for (; i < total; i += step) {
+    bool in;
+    const size_t src = locate(i, in);
+    col[i] = in ? x[src] : make_uint4(0u, 0u, 0u, 0u);
   }
 }
 
@@ -362,9 +372,9 @@ extern "C" int mlt_im2col_nhwc(const void* x, void* col, int B, int H, int W, in
                                int OW, void* stream) {
   MLT_REQUIRE(C % 8 == 0, "mlt_im2col_nhwc: channels (%d) must be a multiple of 8", C);
   const long long total = (long long)B * OH * OW * KH * KW * (C / 8);
-  if (C == 8 && KW == 7 && (long long)B * OH * OW * KH < (1LL << 31)) {              // the (channel-padded) ResNet stem
-    im2col_rows_c8_kernel<7><<<grid_for((long long)B * OH * OW * KH), 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)col, B, H, W,
-                                                                                                     KH, stride, pad, OH, OW);
+  if (C == 8 && KH == 7 && KW == 7 && total < (1LL << 32) - 4LL * kNumSMs * 16 * 256) {     // the (channel-padded) ResNet stem
+    im2col_c8_fixed_kernel<7, 7><<<grid_for(total / 4), 256, 0, (cudaStream_t)stream>>>((const uint4*)x, (uint4*)col, B, H, W, stride, pad,
+                                                                                       OH, OW);
     MLT_LAUNCH_CHECK();
     return 0;
   }
