@@ -846,15 +846,33 @@ splitk_reduce_kernel(const float* __restrict__ ws, O* __restrict__ out, long lon
   const long long stride = (long long)gridDim.x * blockDim.x;
   const long long plane = (long long)M * N;
   for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < total4; v += stride) {
-    float4 a = *reinterpret_cast<const float4*>(ws + v * 4);
-    for (int s = 1; s < splits; ++s) {
-      const float4 b = *reinterpret_cast<const float4*>(ws + s * plane + v * 4);
+    const float* p = ws + v * 4;
+    float4 a = *reinterpret_cast<const float4*>(p);
+    int s = 1;
+    for (; s + 3 < splits; s += 4) {                    // four partial planes per round, their loads issued together
+      const float4 b0 = *reinterpret_cast<const float4*>(p + (s + 0) * plane);
+      const float4 b1 = *reinterpret_cast<const float4*>(p + (s + 1) * plane);
+      const float4 b2 = *reinterpret_cast<const float4*>(p + (s + 2) * plane);
+      const float4 b3 = *reinterpret_cast<const float4*>(p + (s + 3) * plane);
+      a.x += b0.x; a.y += b0.y; a.z += b0.z; a.w += b0.w;      // (same order of additions as one plane at a time)
+      a.x += b1.x; a.y += b1.y; a.z += b1.z; a.w += b1.w;
+      a.x += b2.x; a.y += b2.y; a.z += b2.z; a.w += b2.w;
+      a.x += b3.x; a.y += b3.y; a.z += b3.z; a.w += b3.w;
+    }
+    for (; s < splits; ++s) {
+      const float4 b = *reinterpret_cast<const float4*>(p + s * plane);
       a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
     }
     const long long e = v * 4;
     const int m = (int)(e / N), n = (int)(e - (long long)m * N);
-    O* o = out + (size_t)m * ldo + n;
-    o[0] = from_float<O>(a.x); o[1] = from_float<O>(a.y); o[2] = from_float<O>(a.z); o[3] = from_float<O>(a.w);
+    O* o = out + (size_t)m * ldo + n;                   // N % 4 == 0 and a 16-byte row pitch: 4 outputs never straddle a row
+    if constexpr (sizeof(O) == 2) {
+      uint2 pk;
+      pk.x = pack_bf16(a.x, a.y); pk.y = pack_bf16(a.z, a.w);
+      *reinterpret_cast<uint2*>(o) = pk;
+    } else {
+      *reinterpret_cast<float4*>(o) = a;
+    }
   }
 }
 

@@ -108,9 +108,23 @@ class ResNet(nn.Module):
         x = torch.flatten(self.avgpool(x), 1)
         return self.fc(x)
 
+    def _bump_batch_counters(self):
+        """``num_batches_tracked += 1`` for all 53 BatchNorm layers as one multi-tensor call instead of 53 one-element kernels; the
+        layers are told that their counter has been taken care of for this forward pass."""
+        bns = self.__dict__.get("_bn_layers")
+        if bns is None:
+            bns = [m for m in self.modules() if isinstance(m, nn.BatchNorm2d) and m.num_batches_tracked is not None]
+            self.__dict__["_bn_layers"] = bns             # (plain attribute: not a sub-module registration)
+        live = [m for m in bns if m.training]
+        if live:
+            torch._foreach_add_([m.num_batches_tracked for m in live], 1)
+        for m in bns:
+            m._mlt_counter_done = m.training
+
     def _forward_native(self, x):
         from ..ops import conv as C
 
+        self._bump_batch_counters()
         h = C.to_nhwc_bf16(x, 8)                                            # [B, H, W, 8], channels 3..7 are zero
         w = C.pad_weight_channels(self.conv1.weight, 8)                      # stem filter padded the same way
         h = C.batch_norm_nhwc(C.conv2d_nhwc(h, w, 2, 3), self.bn1, relu=True)

@@ -241,7 +241,9 @@ def batch_norm_nhwc(x, bn: torch.nn.BatchNorm2d, relu: bool = False, residual: O
     ``skip``: see :class:`SkipGrad` (only meaningful with ``residual``)."""
     C = x.shape[-1]
     if bn.training:
-        if bn.num_batches_tracked is not None:
+        if getattr(bn, "_mlt_counter_done", False):
+            bn._mlt_counter_done = False              # the model bumped all its counters in one call (models/resnet.py)
+        elif bn.num_batches_tracked is not None:
             bn.num_batches_tracked.add_(1)
         mom = bn.momentum if bn.momentum is not None else 0.1
         if _has_sink(bn.weight, bn.bias):
