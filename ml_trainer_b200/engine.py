@@ -196,7 +196,8 @@ class StepEngine:
         self.graph_replays += 1
 
     def _eager_step_watching_for_syncs(self, inputs, targets):
-        """A warm-up step of a user-supplied module with torch's sync detector on: a forward / loss that reads values back to the
+        """The reference accepts any ``nn.Module`` (/root/reference/main.py:30, src/trainer.py:41-47).  A warm-up step of a
+        user-supplied module with torch's sync detector on: a forward / loss that reads values back to the
         host (``.item()``, ``bool(tensor)``, ``.cpu()``: what data-dependent control flow looks like from here) cannot be
         captured, so graphs are switched off BEFORE a doomed capture is ever started.  The step itself runs normally."""
         import logging
