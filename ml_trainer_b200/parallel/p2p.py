@@ -374,8 +374,9 @@ class P2PComm(Comm):
 
     def reduce_scalars_host(self, values):
         """Sum a short list of host floats over all ranks AND read this rank's timeout diagnostic, in one round trip to the
-        device (what the Trainer does at the end of every epoch: the reference all-reduces its epoch loss / metric the same
-        way, /root/reference/src/trainer.py:152-158, sum then divide by the world size).  Raises like :meth:`check_errors`."""
+        device (what the Trainer does at the end of every epoch so that every rank logs the same loss / metric; the reference
+        leaves these per-rank, its only cross-rank arithmetic is the sum-then-divide of /root/reference/src/trainer.py:152-158).
+        Raises like :meth:`check_errors`."""
         if self.world_size == 1 or self.arena is None:
             return [float(v) for v in values]
         k = len(values)
