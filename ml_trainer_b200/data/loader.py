@@ -83,7 +83,16 @@ class Loader(DataLoader):
     def __iter__(self):
         if not self._fast:
             return super().__iter__()
+        self.draw_base_seed()
         return self._fast_iter()
+
+    def draw_base_seed(self) -> int:
+        """Every ``iter(DataLoader)`` draws one 64-bit base seed from the loader's generator (the global RNG when there is
+        none) before its sampler draws anything (torch/utils/data/dataloader.py, ``_BaseDataLoaderIter.__init__``).  The
+        vectorised path and the native epoch executors make the same draw, so a run consumes the random stream exactly as the
+        reference's stock ``DataLoader`` does: same seed, same shuffles, same loss curves
+        (tests/test_reference_parity_cpu.py)."""
+        return int(torch.empty((), dtype=torch.int64).random_(generator=self.generator).item())
 
     def _fast_iter(self) -> Iterator[Tuple[torch.Tensor, ...]]:
         pin = bool(self.pin_memory) and torch.cuda.is_available()

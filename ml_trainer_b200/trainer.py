@@ -311,6 +311,7 @@ class Trainer:
         from .runtime import epoch_indices
 
         eng, opt, loader = self.engine, self.optimizer, self.train_loader
+        loader.draw_base_seed()                 # what iter(DataLoader) would draw before the sampler (same random stream)
         idx, sizes = epoch_indices(loader)
         B = loader.batch_size
         nb = len(sizes)
@@ -428,6 +429,7 @@ class Trainer:
         from .runtime import epoch_indices
 
         eng, opt = self.engine, self.optimizer
+        loader.draw_base_seed()                 # what iter(DataLoader) would draw before the sampler (same random stream)
         idx, sizes = epoch_indices(loader)
         nb = len(sizes)
         hyper = None
