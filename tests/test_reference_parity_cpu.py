@@ -18,7 +18,7 @@ REF = os.path.join(ROOT, "baseline", "_ref")
 
 REF_SCRIPT = r"""
 import json, os, sys
-ref, out = sys.argv[1], sys.argv[2]
+ref, out, optimizer, scheduler = sys.argv[1], sys.argv[2], sys.argv[3], (sys.argv[4] if sys.argv[4] != "none" else None)
 os.environ["TQDM_DISABLE"] = "1"
 sys.path[:0] = [ref, os.path.join(ref, "_shims")]
 import logging
@@ -32,8 +32,9 @@ xt, yt = torch.randn(256, 3, 32, 32, generator=g), torch.randint(0, 10, (256,), 
 xv, yv = torch.randn(64, 3, 32, 32, generator=g), torch.randint(0, 10, (64,), generator=g)
 torch.manual_seed(32)
 model = MLModel()
-t = Trainer(model, datasets=(TensorDataset(xt, yt), TensorDataset(xv, yv)), epochs=3, batch_size=32, seed=32, optimizer="sgd",
-            lr=0.01, momentum=0.9, criterion="cross_entropy", metric="accuracy", pred_function="softmax", model_dir=out)
+t = Trainer(model, datasets=(TensorDataset(xt, yt), TensorDataset(xv, yv)), epochs=3, batch_size=32, seed=32, optimizer=optimizer,
+            lr=0.01, momentum=0.9, criterion="cross_entropy", metric="accuracy", pred_function="softmax", model_dir=out,
+            scheduler=scheduler)
 os.makedirs(out, exist_ok=True)
 t.fit()
 json.dump({"train_loss": t.train_losses, "val_loss": t.val_losses, "train_metric": [float(v) for v in t.train_metrics],
@@ -44,14 +45,16 @@ torch.save({k: v.cpu() for k, v in t.model.state_dict().items()}, os.path.join(o
 
 @pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "src")), reason="reference arm not installed (baseline/_ref)")
 @pytest.mark.skipif(torch.cuda.is_available(), reason="CPU statement of both arms (the GPU tier has its own oracles)")
-def test_loss_curves_match_the_reference_trainer(tmp_path):
+@pytest.mark.parametrize("optimizer,scheduler", [("sgd", None), ("adamw", "StepLR"), ("adam", "CosineAnnealingWarmRestarts"),
+                                                 ("adagrad", None)])
+def test_loss_curves_match_the_reference_trainer(tmp_path, optimizer, scheduler):
     from torch.utils.data import TensorDataset
 
     from ml_trainer_b200 import MLModel, Trainer
 
     env = dict(os.environ, CUDA_VISIBLE_DEVICES="")
-    r = subprocess.run([sys.executable, "-c", REF_SCRIPT, REF, str(tmp_path / "ref")], env=env, capture_output=True, text=True,
-                       timeout=600, cwd=str(tmp_path))
+    r = subprocess.run([sys.executable, "-c", REF_SCRIPT, REF, str(tmp_path / "ref"), optimizer, scheduler or "none"], env=env,
+                       capture_output=True, text=True, timeout=600, cwd=str(tmp_path))
     assert r.returncode == 0, r.stderr[-2000:]
     ref_hist = json.load(open(tmp_path / "ref" / "ref_history.json"))
     ref_w = torch.load(tmp_path / "ref" / "ref_weights.pt")
@@ -61,9 +64,9 @@ def test_loss_curves_match_the_reference_trainer(tmp_path):
     xv, yv = torch.randn(64, 3, 32, 32, generator=g), torch.randint(0, 10, (64,), generator=g)
     torch.manual_seed(32)
     model = MLModel()
-    t = Trainer(model, datasets=(TensorDataset(xt, yt), TensorDataset(xv, yv)), epochs=3, batch_size=32, seed=32, optimizer="sgd",
+    t = Trainer(model, datasets=(TensorDataset(xt, yt), TensorDataset(xv, yv)), epochs=3, batch_size=32, seed=32, optimizer=optimizer,
                 lr=0.01, momentum=0.9, criterion="cross_entropy", metric="accuracy", pred_function="softmax",
-                model_dir=str(tmp_path / "ours"), progress=False)
+                model_dir=str(tmp_path / "ours"), progress=False, scheduler=scheduler)
     t.fit()
     for key, ours in (("train_loss", t.train_losses), ("val_loss", t.val_losses), ("train_metric", t.train_metrics),
                       ("val_metric", t.val_metrics)):
